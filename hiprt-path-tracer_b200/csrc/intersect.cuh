@@ -1,0 +1,207 @@
+// Scene queries used by the kernels: closest hit with shading data, shadow rays, shadow-light rays.
+// reference: src/Device/includes/Intersect.h:30-410, Texture.h:208-222 (uv_interpolate).
+#pragma once
+
+#include "bsdf_principled.cuh"
+#include "traverse.cuh"
+
+namespace pt
+{
+struct HitInfo
+{
+    float3 inter_point;
+    float3 shading_normal;
+    float3 geometric_normal;
+    float2 texcoords;
+    float2 uv;
+    float t;
+    int primitive_index;
+};
+
+struct RayPayload
+{
+    RGB throughput;
+    RGB ray_color;
+    int next_ray_state;   // 0 BOUNCE, 1 MISSED
+    Material material;
+    RayVolumeState volume_state;
+};
+
+PT_DEV const Bvh8Device& scene_bvh(const HIPRTRenderData& rd) { return *reinterpret_cast<const Bvh8Device*>(rd.geom); }
+
+#ifdef PT_COUNTERS
+__device__ TraversalCounters g_traversal_counters;
+#define PT_COUNTERS_PTR (&g_traversal_counters)
+#else
+#define PT_COUNTERS_PTR nullptr
+#endif
+
+PT_DEV int3 triangle_vertex_indices(const HIPRTRenderData& rd, int primitive_index)
+{
+    const int* idx = rd.buffers.triangles_indices + (size_t)primitive_index * 3;
+    return make_int3(__ldg(idx), __ldg(idx + 1), __ldg(idx + 2));
+}
+
+PT_DEV float2 ld2(const void* base, size_t index)
+{
+    const float* p = reinterpret_cast<const float*>(base) + index * 2;
+    return make_float2(__ldg(p), __ldg(p + 1));
+}
+
+// uv_interpolate: data[B] * u + data[C] * v + data[A] * (1 - u - v)
+PT_DEV float2 interpolate_texcoords(const HIPRTRenderData& rd, int3 vi, float2 uv)
+{
+    float2 a = ld2(rd.buffers.texcoords, vi.x), b = ld2(rd.buffers.texcoords, vi.y), c = ld2(rd.buffers.texcoords, vi.z);
+    float w = 1.0f - uv.x - uv.y;
+    return make_float2(b.x * uv.x + c.x * uv.y + a.x * w, b.y * uv.x + c.y * uv.y + a.y * w);
+}
+
+PT_DEV float3 interpolate_normals(const HIPRTRenderData& rd, int3 vi, float2 uv)
+{
+    float3 a = ld3(rd.buffers.vertex_normals, vi.x), b = ld3(rd.buffers.vertex_normals, vi.y), c = ld3(rd.buffers.vertex_normals, vi.z);
+    return b * uv.x + c * uv.y + a * (1.0f - uv.x - uv.y);
+}
+
+// normal_mapping (Intersect.h:30-62)
+PT_DEV float3 normal_mapping(const HIPRTRenderData& rd, int normal_map_texture_index, int3 vi, float2 texcoords, float3 surface_normal)
+{
+    float2 P0_uv = ld2(rd.buffers.texcoords, vi.x), P1_uv = ld2(rd.buffers.texcoords, vi.y), P2_uv = ld2(rd.buffers.texcoords, vi.z);
+    float2 d10 = make_float2(P1_uv.x - P0_uv.x, P1_uv.y - P0_uv.y);
+    float2 d20 = make_float2(P2_uv.x - P0_uv.x, P2_uv.y - P0_uv.y);
+
+    float3 P0 = ld3(rd.buffers.vertices_positions, vi.x), P1 = ld3(rd.buffers.vertices_positions, vi.y), P2 = ld3(rd.buffers.vertices_positions, vi.z);
+    float3 e01 = P1 - P0;
+    float3 e02 = P2 - P0;
+
+    float det_inverse = 1.0f / (d10.x * d20.y - d10.y * d20.x);
+    float3 T = (e01 * d20.y - e02 * d10.y) * det_inverse;
+    float3 B = (e02 * d10.x - e01 * d20.x) * det_inverse;
+
+    RGBA n = sample_tex2d_rgba(material_texture(rd, normal_map_texture_index), texcoords, false);
+    float3 normal_tangent_space = normalize(f3(n.r - 0.5f, n.g - 0.5f, n.b - 0.5f));
+    return local_to_world_frame(normalize(T), normalize(B), surface_normal, normal_tangent_space);
+}
+
+// get_shading_normal (Intersect.h:64-83)
+PT_DEV float3 get_shading_normal(const HIPRTRenderData& rd, float3 geometric_normal, int primitive_index, int3 vi, float2 uv, float2 texcoords)
+{
+    int mat_index = __ldg(rd.buffers.material_indices + primitive_index);
+    float3 surface_normal;
+    if (__ldg(rd.buffers.has_vertex_normals + vi.x))
+        surface_normal = normalize(interpolate_normals(rd, vi, uv));
+    else
+        surface_normal = geometric_normal;
+
+    int normal_map = material_field_i(rd, mat_index, offsetof(RendererMaterial, normal_map_texture_index));
+    if (normal_map != B200PT_NO_TEXTURE)
+        surface_normal = normal_mapping(rd, normal_map, vi, texcoords, surface_normal);
+    return surface_normal;
+}
+
+// Geometric normal as the oracle produces it: Triangle::intersect normalises cross(e1, e2) (Triangle.h:53) and
+// trace_ray normalises the result once more (Intersect.h:152).
+PT_DEV float3 hit_geometric_normal(const HIPRTRenderData& rd, const Hit& hit)
+{
+    return normalize(normalize(bvh8_triangle_normal(scene_bvh(rd), hit.tri_slot)));
+}
+
+// trace_ray (Intersect.h:114-219). Returns true if a hit was found.
+PT_DEV bool trace_ray(const HIPRTRenderData& rd, float3 origin, float3 direction, RayPayload& payload, HitInfo& out, int last_hit_primitive_index, Rng& rng)
+{
+    Hit hit;
+    bool skipping_volume_boundary = false;
+    do
+    {
+        if (!bvh8_trace<false>(scene_bvh(rd), origin, direction, INFINITY, last_hit_primitive_index, hit, PT_COUNTERS_PTR))
+            return false;
+
+        int3 vi = triangle_vertex_indices(rd, hit.prim);
+        float2 uv = make_float2(hit.u, hit.v);
+        out.inter_point = origin + hit.t * direction;
+        out.primitive_index = hit.prim;
+        out.texcoords = interpolate_texcoords(rd, vi, uv);
+        out.geometric_normal = hit_geometric_normal(rd, hit);
+        out.shading_normal = get_shading_normal(rd, out.geometric_normal, hit.prim, vi, uv, out.texcoords);
+        out.t = hit.t;
+        out.uv = uv;
+
+        if (is_inside_volume(payload.volume_state))
+            payload.volume_state.distance_in_volume += hit.t;
+
+        int material_index = __ldg(rd.buffers.material_indices + hit.prim);
+        get_intersection_material(rd, material_index, out.texcoords, payload.material);
+
+        if ((!is_inside_volume(payload.volume_state) || payload.material.specular_transmission == 0.0f) && !payload.material.thin_walled)
+        {
+            out.geometric_normal *= dot(out.geometric_normal, -direction) < 0.0f ? -1.0f : 1.0f;
+            out.shading_normal *= dot(out.shading_normal, out.geometric_normal) < 0.0f ? -1.0f : 1.0f;
+            float NdotV = dot(out.shading_normal, -direction);
+            out.shading_normal += (2.0f * clampf(0.0f, 1.0f, -NdotV)) * -direction;
+        }
+
+        skipping_volume_boundary = interior_stack_push(payload.volume_state, material_index, payload.material.dielectric_priority);
+        if (skipping_volume_boundary)
+        {
+            origin = out.inter_point;
+            // counted twice on skipped boundaries, as in the reference (Intersect.h:161-162, 203)
+            payload.volume_state.distance_in_volume += hit.t;
+        }
+    } while (skipping_volume_boundary);
+
+    if (payload.material.dispersion_scale > 0.0f && payload.material.specular_transmission > 0.0f && payload.volume_state.sampled_wavelength == 0.0f)
+        payload.volume_state.sampled_wavelength = -sample_wavelength_uniformly(rng);
+
+    return true;
+}
+
+// evaluate_shadow_ray (Intersect.h:224-286): true if occluded. Alpha testing off: one any-hit query.
+PT_DEV bool evaluate_shadow_ray(const HIPRTRenderData& rd, float3 origin, float3 direction, float t_max, int last_hit_primitive_index, Rng& rng)
+{
+    (void)rng;
+    Hit hit;
+    return bvh8_trace<true>(scene_bvh(rd), origin, direction, t_max - 1.0e-4f, last_hit_primitive_index, hit, PT_COUNTERS_PTR);
+}
+
+struct ShadowLightRayHitInfo
+{
+    int hit_prim_index;
+    float hit_distance;
+    float3 hit_shading_normal;
+    RGB hit_emission;
+};
+
+// evaluate_shadow_light_ray (Intersect.h:293-410): closest hit, then the emission + shading normal of what was hit
+PT_DEV bool evaluate_shadow_light_ray(const HIPRTRenderData& rd, float3 origin, float3 direction, float t_max, ShadowLightRayHitInfo& out, int last_hit_primitive_index, Rng& rng)
+{
+    (void)rng;
+    Hit hit;
+    if (!bvh8_trace<false>(scene_bvh(rd), origin, direction, INFINITY, last_hit_primitive_index, hit, PT_COUNTERS_PTR))
+        return false;
+    if (!(hit.t < t_max - 1.0e-4f))
+        return false;
+
+    int material_index = __ldg(rd.buffers.material_indices + hit.prim);
+    int emission_texture_index = material_field_i(rd, material_index, offsetof(RendererMaterial, emission_texture_index));
+    int3 vi = triangle_vertex_indices(rd, hit.prim);
+    float2 uv = make_float2(hit.u, hit.v);
+    float2 texcoords = interpolate_texcoords(rd, vi, uv);
+    if (emission_texture_index != B200PT_NO_TEXTURE)
+    {
+        // get_material_property leaves the (uninitialised) output untouched for CONSTANT_EMISSIVE_TEXTURE; black here
+        out.hit_emission = RGB(0.0f);
+        if (has_texture(emission_texture_index))
+        {
+            RGBA c = sample_tex2d_rgba(material_texture(rd, emission_texture_index), texcoords, false);
+            out.hit_emission = RGB(c.r, c.g, c.b);
+        }
+    }
+    else
+        out.hit_emission = material_buffer_emission(rd, material_index);
+
+    float3 ng = normalize(normalize(bvh8_triangle_normal(scene_bvh(rd), hit.tri_slot)));
+    out.hit_shading_normal = get_shading_normal(rd, ng, hit.prim, vi, uv, texcoords);
+    out.hit_distance = hit.t;
+    out.hit_prim_index = hit.prim;
+    return true;
+}
+} // namespace pt

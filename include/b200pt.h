@@ -1,0 +1,157 @@
+/*
+ * b200pt.h -- thin C-ABI CUDA layer for the HIPRT-Path-Tracer render hot path on NVIDIA B200 (sm_100a).
+ *
+ * This library replaces, for the CameraRays -> [ReSTIR DI passes] -> FullPathTracer path only, what the reference
+ * renderer obtains from Orochi + HIPRT + its run-time kernel compiler:
+ *
+ *   reference call site                                                  replaced by
+ *   -------------------------------------------------------------------  ------------------------------------------
+ *   HIPRTOrochiCtx::init            src/HIPRT-Orochi/HIPRTOrochiCtx.h:29-57   b200pt_ctx_create / _make_current
+ *   OrochiBuffer<T>::resize/upload  src/HIPRT-Orochi/OrochiBuffer.h:91-147    b200pt_malloc / _free / _memcpy_*
+ *   OrochiTexture / OrochiTexture3D src/HIPRT-Orochi/OrochiTexture.cpp:47-142 b200pt_tex2d_create / _tex3d_create
+ *   OrochiEnvmap alias-table upload src/HIPRT-Orochi/OrochiEnvmap.cpp:53-76   b200pt_malloc + b200pt_memcpy_h2d
+ *   HIPRTGeometry::build_bvh        src/HIPRT-Orochi/HIPRTScene.h:59-86       b200pt_bvh_build (compressed BVH8)
+ *   GPUKernel::compile (NVRTC)      src/Compiler/GPUKernel.cpp:72-96          none: kernels are built offline for
+ *                                                                             sm_100a; b200pt_kernel_variant_select
+ *   GPUKernel::launch_asynchronous  src/Compiler/GPUKernel.cpp:169-245        b200pt_launch_<KernelName>
+ *   oroStream* / oroEvent*          src/Renderer/GPURenderer.cpp:75-85,494-499 b200pt_stream_* / b200pt_event_*
+ *
+ * Conventions: every entry point returns 0 on success or a negative b200pt_error; it never exits the process and
+ * never throws across the ABI (the reference's OROCHI_CHECK_ERROR logs and exit()s, HIPRTOrochiUtils.cpp:15-48).
+ * b200pt_last_error() gives the message of the last failure on the calling thread. There is NO CPU fallback: without
+ * a CUDA device every compute entry point fails with B200PT_ERROR_NO_DEVICE.
+ * Kernel launches are asynchronous on the given stream; struct arguments are snapshotted at call time, exactly like
+ * the by-value kernel arguments of the reference (src/Renderer/GPURenderer.cpp:468,482).
+ */
+#ifndef B200PT_H
+#define B200PT_H
+
+#include "b200pt_types.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200PT_API __attribute__((visibility("default")))
+
+typedef enum b200pt_error
+{
+    B200PT_SUCCESS = 0,
+    B200PT_ERROR_INVALID_ARGUMENT = -1,
+    B200PT_ERROR_NO_DEVICE = -2,
+    B200PT_ERROR_CUDA = -3,
+    B200PT_ERROR_OUT_OF_MEMORY = -4,
+    B200PT_ERROR_VARIANT_NOT_COMPILED = -5,
+    B200PT_ERROR_NOT_READY = -6
+} b200pt_error;
+
+typedef struct b200pt_ctx b200pt_ctx;       /* one per GPU (the reference has a single shared context, device 0) */
+typedef struct b200pt_bvh b200pt_bvh;
+typedef struct b200pt_stream_t* b200pt_stream;   /* NULL = the context's main stream (GPURenderer::m_main_stream) */
+typedef struct b200pt_event_t* b200pt_event;
+
+/* Device-visible texture descriptors: what RenderBuffers::material_textures[i], BRDFsData::* and
+ * WorldSettings::envmap point to. Sampling follows the reference's CPU rule: nearest texel, repeat addressing,
+ * v flipped, x = int(u * (w - 1)) (src/Image/Image.cpp:161-195, 492-526, 737-779). */
+typedef struct b200pt_tex2d
+{
+    const void* texels;            /* device pointer, row-major, `channels` interleaved */
+    int width, height;
+    int channels;                  /* 1..4 */
+    int bytes_per_channel;         /* 1 = unorm8 (Image8Bit), 4 = float32 (Image32Bit) */
+} b200pt_tex2d;
+
+typedef struct b200pt_tex3d
+{
+    const float* texels;           /* device pointer, depth slices of row-major width x height x channels */
+    int width, height, depth;
+    int channels;
+} b200pt_tex3d;
+
+/* Compile-time kernel options of the reference (src/HostDeviceCommon/KernelOptions.h:91-366) that select a prebuilt
+ * kernel variant. Values are the reference's macro values. */
+typedef struct b200pt_options
+{
+    int direct_light_sampling_strategy;   /* LSS_*: 0 none, 1 uniform one light, 2 BSDF, 3 MIS light+BSDF, 4 RIS, 5 ReSTIR DI */
+    int envmap_sampling_strategy;         /* ESS_*: 0 no sampling, 1 binary search, 2 alias table */
+    int ggx_sample_function;              /* 0 GGX_VNDF_SAMPLING, 1 GGX_VNDF_SPHERICAL_CAPS */
+    int restir_di_later_bounces_strategy; /* RESTIR_DI_LATER_BOUNCES_*: 0 uniform, 1 BSDF, 2 MIS, 3 RIS */
+} b200pt_options;
+
+/* Image-space shard of a launch: pixels with x0 <= x < x1, y0 <= y < y1 are processed; pixel_index stays x + y * res.x
+ * so that a sharded render is bit-identical to the unsharded one. NULL = the whole image. */
+typedef struct b200pt_tile { int x0, y0, x1, y1; } b200pt_tile;
+
+/* Traversal statistics of the counting build (for Mrays/s and the node-fetch roofline). */
+typedef struct b200pt_counters
+{
+    unsigned long long rays;        /* BVH queries: trace_ray iterations + shadow rays + shadow-light rays */
+    unsigned long long nodes;       /* 80-byte BVH8 nodes fetched */
+    unsigned long long triangles;   /* 48-byte triangles fetched */
+} b200pt_counters;
+
+/* ---- context, memory, streams, events ------------------------------------------------------------------------ */
+B200PT_API int b200pt_device_count(void);
+B200PT_API int b200pt_ctx_create(int device_index, b200pt_ctx** out_ctx);
+B200PT_API int b200pt_ctx_destroy(b200pt_ctx* ctx);
+B200PT_API int b200pt_ctx_make_current(b200pt_ctx* ctx);                 /* oroCtxSetCurrent, GPURenderer.cpp:74 */
+B200PT_API const char* b200pt_last_error(void);
+B200PT_API const char* b200pt_version(void);
+
+B200PT_API int b200pt_malloc(b200pt_ctx* ctx, size_t bytes, void** out_dptr);
+B200PT_API int b200pt_free(b200pt_ctx* ctx, void* dptr);
+B200PT_API int b200pt_memset(b200pt_ctx* ctx, void* dptr, int value, size_t bytes, b200pt_stream stream);
+B200PT_API int b200pt_memcpy_h2d(b200pt_ctx* ctx, void* dst_dptr, const void* src_host, size_t bytes, b200pt_stream stream);
+B200PT_API int b200pt_memcpy_d2h(b200pt_ctx* ctx, void* dst_host, const void* src_dptr, size_t bytes, b200pt_stream stream);
+B200PT_API int b200pt_memcpy_d2d(b200pt_ctx* ctx, void* dst_dptr, const void* src_dptr, size_t bytes, b200pt_stream stream);
+B200PT_API int b200pt_host_alloc_pinned(b200pt_ctx* ctx, size_t bytes, void** out_host);
+B200PT_API int b200pt_host_free_pinned(b200pt_ctx* ctx, void* host);
+
+B200PT_API int b200pt_stream_create(b200pt_ctx* ctx, b200pt_stream* out_stream);
+B200PT_API int b200pt_stream_destroy(b200pt_ctx* ctx, b200pt_stream stream);
+B200PT_API int b200pt_stream_query(b200pt_ctx* ctx, b200pt_stream stream);     /* 0 = idle, B200PT_ERROR_NOT_READY = busy */
+B200PT_API int b200pt_stream_sync(b200pt_ctx* ctx, b200pt_stream stream);
+B200PT_API int b200pt_event_create(b200pt_ctx* ctx, b200pt_event* out_event);
+B200PT_API int b200pt_event_destroy(b200pt_ctx* ctx, b200pt_event event);
+B200PT_API int b200pt_event_record(b200pt_ctx* ctx, b200pt_event event, b200pt_stream stream);
+B200PT_API int b200pt_event_elapsed_ms(b200pt_ctx* ctx, b200pt_event start, b200pt_event stop, float* out_ms);
+
+/* ---- textures ------------------------------------------------------------------------------------------------ */
+/* Uploads host texels and returns the DEVICE address of a b200pt_tex2d / b200pt_tex3d descriptor.
+ * 3-channel 8-bit images are accepted (the reference's GPU path rejects them, OrochiTexture.cpp:50-55; its CPU path does not). */
+B200PT_API int b200pt_tex2d_create(b200pt_ctx* ctx, const void* host_texels, int width, int height, int channels, int bytes_per_channel, void** out_descriptor_dptr);
+B200PT_API int b200pt_tex3d_create(b200pt_ctx* ctx, const float* host_texels, int width, int height, int depth, int channels, void** out_descriptor_dptr);
+B200PT_API int b200pt_tex_destroy(b200pt_ctx* ctx, void* descriptor_dptr);
+/* Builds the contiguous device array of b200pt_tex2d that RenderBuffers::material_textures points to. */
+B200PT_API int b200pt_tex2d_array_create(b200pt_ctx* ctx, void* const* descriptor_dptrs, int count, void** out_array_dptr);
+
+/* ---- acceleration structure ---------------------------------------------------------------------------------- */
+/* vertices: 3 floats per vertex; triangle_indices: 3 ints per triangle (host pointers). The primitive index reported
+ * by the kernels is the index into triangle_indices / 3, as in the reference. flags: reserved, pass 0. */
+B200PT_API int b200pt_bvh_build(b200pt_ctx* ctx, const float* vertices, int vertex_count, const int* triangle_indices, int triangle_count, unsigned flags, b200pt_bvh** out_bvh);
+B200PT_API int b200pt_bvh_destroy(b200pt_ctx* ctx, b200pt_bvh* bvh);
+B200PT_API void* b200pt_bvh_device_handle(b200pt_bvh* bvh);             /* value for HIPRTRenderData::geom */
+B200PT_API int b200pt_bvh_info(b200pt_bvh* bvh, unsigned* out_node_count, unsigned* out_triangle_count, float* out_sah_cost, double* out_build_seconds);
+
+/* ---- kernels (names of the reference's kernels kept; src/Device/kernels) --------------------------------------- */
+B200PT_API int b200pt_kernel_variant_select(b200pt_ctx* ctx, const b200pt_options* options);
+B200PT_API int b200pt_launch_CameraRays(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream);
+B200PT_API int b200pt_launch_FullPathTracer(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream);
+B200PT_API int b200pt_launch_ReSTIR_DI_LightsPresampling(b200pt_ctx* ctx, const LightPresamplingParameters* parameters, b200pt_stream stream);
+B200PT_API int b200pt_launch_ReSTIR_DI_InitialCandidates(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream);
+B200PT_API int b200pt_launch_ReSTIR_DI_SpatiotemporalReuse(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream);
+
+/* ---- ray batches: the traversal core on its own (parity pins on hit ids; roofline measurement) ------------------ */
+/* rays: n x 6 floats (origin, direction) on the device. last_prim: n ints or NULL (-1). Outputs on the device. */
+B200PT_API int b200pt_trace_closest(b200pt_ctx* ctx, b200pt_bvh* bvh, const float* d_rays, const int* d_last_prim, long long n, int* d_out_prim, float* d_out_t, float* d_out_uv, b200pt_stream stream);
+B200PT_API int b200pt_trace_shadow(b200pt_ctx* ctx, b200pt_bvh* bvh, const float* d_rays, const float* d_t_max, const int* d_last_prim, long long n, unsigned char* d_out_occluded, b200pt_stream stream);
+
+/* ---- counters (counting build of the same kernels; the timing build has them compiled out) --------------------- */
+B200PT_API int b200pt_counters_enable(b200pt_ctx* ctx, int enable);
+B200PT_API int b200pt_counters_read(b200pt_ctx* ctx, b200pt_counters* out, int reset);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* B200PT_H */
