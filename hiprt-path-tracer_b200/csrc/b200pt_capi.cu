@@ -1,0 +1,292 @@
+// Implementation of the C ABI declared in include/b200pt.h (see that header for the reference call sites each
+// entry point replaces). No CPU fallback: every compute entry point needs a CUDA device.
+#include "bvh8_build.h"
+#include "launch.h"
+
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+struct b200pt_ctx
+{
+    int device = 0;
+    cudaStream_t main_stream = nullptr;
+    pt::VariantOptions options = {3, 0, 3, 0};
+    bool counting = false;
+    pt::TraversalCounters* d_counters = nullptr;
+};
+
+struct b200pt_bvh
+{
+    pt::Bvh8Device view;
+    pt::Bvh8Device* d_view = nullptr;
+    void* d_nodes = nullptr;
+    void* d_triangles = nullptr;
+    float sah_cost = 0.0f;
+    double build_seconds = 0.0;
+};
+
+namespace
+{
+thread_local std::string g_last_error;
+
+int fail(int code, const std::string& message)
+{
+    g_last_error = message;
+    return code;
+}
+
+int cuda_fail(cudaError_t e, const char* what)
+{
+    int code = e == cudaErrorMemoryAllocation ? B200PT_ERROR_OUT_OF_MEMORY : (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver) ? B200PT_ERROR_NO_DEVICE : B200PT_ERROR_CUDA;
+    return fail(code, std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")");
+}
+
+#define CUDA_TRY(expr)                         \
+    do                                         \
+    {                                          \
+        cudaError_t e_ = (expr);               \
+        if (e_ != cudaSuccess)                 \
+            return cuda_fail(e_, #expr);       \
+    } while (0)
+
+#define REQUIRE(cond)                                                            \
+    do                                                                           \
+    {                                                                            \
+        if (!(cond))                                                             \
+            return fail(B200PT_ERROR_INVALID_ARGUMENT, "invalid argument: " #cond); \
+    } while (0)
+
+cudaStream_t stream_of(b200pt_ctx* ctx, b200pt_stream s) { return s ? reinterpret_cast<cudaStream_t>(s) : ctx->main_stream; }
+
+pt::Tile tile_of(const b200pt_tile* tile, b200pt_int2 res)
+{
+    pt::Tile t = {0, 0, res.x, res.y};
+    if (tile)
+    {
+        t.x0 = tile->x0 < 0 ? 0 : tile->x0;
+        t.y0 = tile->y0 < 0 ? 0 : tile->y0;
+        t.x1 = tile->x1 > res.x ? res.x : tile->x1;
+        t.y1 = tile->y1 > res.y ? res.y : tile->y1;
+    }
+    return t;
+}
+} // namespace
+
+extern "C" {
+
+int b200pt_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess)
+    {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+const char* b200pt_last_error(void) { return g_last_error.c_str(); }
+const char* b200pt_version(void) { return "b200pt 0.1 (sm_100a; BVH8 software traversal; megakernel path tracer)"; }
+
+int b200pt_ctx_create(int device_index, b200pt_ctx** out_ctx)
+{
+    REQUIRE(out_ctx != nullptr);
+    *out_ctx = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+    {
+        cudaGetLastError();
+        return fail(B200PT_ERROR_NO_DEVICE, "no CUDA device available: the b200pt hot path has no CPU fallback");
+    }
+    REQUIRE(device_index >= 0 && device_index < n);
+    CUDA_TRY(cudaSetDevice(device_index));
+    b200pt_ctx* ctx = new b200pt_ctx();
+    ctx->device = device_index;
+    e = cudaStreamCreateWithFlags(&ctx->main_stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess)
+    {
+        delete ctx;
+        return cuda_fail(e, "cudaStreamCreate");
+    }
+    e = cudaMalloc(&ctx->d_counters, sizeof(pt::TraversalCounters));
+    if (e == cudaSuccess)
+        e = cudaMemset(ctx->d_counters, 0, sizeof(pt::TraversalCounters));
+    if (e != cudaSuccess)
+    {
+        cudaStreamDestroy(ctx->main_stream);
+        delete ctx;
+        return cuda_fail(e, "cudaMalloc(counters)");
+    }
+    // The megakernel keeps per-thread traversal stacks and a 256-byte material in local memory
+    cudaDeviceSetLimit(cudaLimitStackSize, 8192);
+    *out_ctx = ctx;
+    return B200PT_SUCCESS;
+}
+
+int b200pt_ctx_destroy(b200pt_ctx* ctx)
+{
+    if (!ctx)
+        return B200PT_SUCCESS;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->main_stream);
+    cudaFree(ctx->d_counters);
+    cudaStreamDestroy(ctx->main_stream);
+    delete ctx;
+    return B200PT_SUCCESS;
+}
+
+int b200pt_ctx_make_current(b200pt_ctx* ctx)
+{
+    REQUIRE(ctx != nullptr);
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    return B200PT_SUCCESS;
+}
+
+int b200pt_malloc(b200pt_ctx* ctx, size_t bytes, void** out_dptr)
+{
+    REQUIRE(ctx != nullptr && out_dptr != nullptr);
+    *out_dptr = nullptr;
+    if (bytes == 0)
+        return B200PT_SUCCESS;
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    CUDA_TRY(cudaMalloc(out_dptr, bytes));
+    return B200PT_SUCCESS;
+}
+
+int b200pt_free(b200pt_ctx* ctx, void* dptr)
+{
+    REQUIRE(ctx != nullptr);
+    if (!dptr)
+        return B200PT_SUCCESS;
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    CUDA_TRY(cudaFree(dptr));
+    return B200PT_SUCCESS;
+}
+
+int b200pt_memset(b200pt_ctx* ctx, void* dptr, int value, size_t bytes, b200pt_stream stream)
+{
+    REQUIRE(ctx != nullptr && (dptr != nullptr || bytes == 0));
+    if (bytes == 0)
+        return B200PT_SUCCESS;
+    CUDA_TRY(cudaMemsetAsync(dptr, value, bytes, stream_of(ctx, stream)));
+    return B200PT_SUCCESS;
+}
+
+int b200pt_memcpy_h2d(b200pt_ctx* ctx, void* dst_dptr, const void* src_host, size_t bytes, b200pt_stream stream)
+{
+    REQUIRE(ctx != nullptr && (bytes == 0 || (dst_dptr != nullptr && src_host != nullptr)));
+    if (bytes == 0)
+        return B200PT_SUCCESS;
+    CUDA_TRY(cudaMemcpyAsync(dst_dptr, src_host, bytes, cudaMemcpyHostToDevice, stream_of(ctx, stream)));
+    return B200PT_SUCCESS;
+}
+
+int b200pt_memcpy_d2h(b200pt_ctx* ctx, void* dst_host, const void* src_dptr, size_t bytes, b200pt_stream stream)
+{
+    REQUIRE(ctx != nullptr && (bytes == 0 || (dst_host != nullptr && src_dptr != nullptr)));
+    if (bytes == 0)
+        return B200PT_SUCCESS;
+    CUDA_TRY(cudaMemcpyAsync(dst_host, src_dptr, bytes, cudaMemcpyDeviceToHost, stream_of(ctx, stream)));
+    return B200PT_SUCCESS;
+}
+
+int b200pt_memcpy_d2d(b200pt_ctx* ctx, void* dst_dptr, const void* src_dptr, size_t bytes, b200pt_stream stream)
+{
+    REQUIRE(ctx != nullptr && (bytes == 0 || (dst_dptr != nullptr && src_dptr != nullptr)));
+    if (bytes == 0)
+        return B200PT_SUCCESS;
+    CUDA_TRY(cudaMemcpyAsync(dst_dptr, src_dptr, bytes, cudaMemcpyDeviceToDevice, stream_of(ctx, stream)));
+    return B200PT_SUCCESS;
+}
+
+int b200pt_host_alloc_pinned(b200pt_ctx* ctx, size_t bytes, void** out_host)
+{
+    REQUIRE(ctx != nullptr && out_host != nullptr);
+    CUDA_TRY(cudaMallocHost(out_host, bytes));
+    return B200PT_SUCCESS;
+}
+
+int b200pt_host_free_pinned(b200pt_ctx* ctx, void* host)
+{
+    REQUIRE(ctx != nullptr);
+    if (host)
+        CUDA_TRY(cudaFreeHost(host));
+    return B200PT_SUCCESS;
+}
+
+int b200pt_stream_create(b200pt_ctx* ctx, b200pt_stream* out_stream)
+{
+    REQUIRE(ctx != nullptr && out_stream != nullptr);
+    cudaStream_t s;
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    CUDA_TRY(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    *out_stream = reinterpret_cast<b200pt_stream>(s);
+    return B200PT_SUCCESS;
+}
+
+int b200pt_stream_destroy(b200pt_ctx* ctx, b200pt_stream stream)
+{
+    REQUIRE(ctx != nullptr);
+    if (stream)
+        CUDA_TRY(cudaStreamDestroy(reinterpret_cast<cudaStream_t>(stream)));
+    return B200PT_SUCCESS;
+}
+
+int b200pt_stream_query(b200pt_ctx* ctx, b200pt_stream stream)
+{
+    REQUIRE(ctx != nullptr);
+    cudaError_t e = cudaStreamQuery(stream_of(ctx, stream));
+    if (e == cudaSuccess)
+        return B200PT_SUCCESS;
+    if (e == cudaErrorNotReady)
+        return B200PT_ERROR_NOT_READY;
+    return cuda_fail(e, "cudaStreamQuery");
+}
+
+int b200pt_stream_sync(b200pt_ctx* ctx, b200pt_stream stream)
+{
+    REQUIRE(ctx != nullptr);
+    CUDA_TRY(cudaStreamSynchronize(stream_of(ctx, stream)));
+    return B200PT_SUCCESS;
+}
+
+int b200pt_event_create(b200pt_ctx* ctx, b200pt_event* out_event)
+{
+    REQUIRE(ctx != nullptr && out_event != nullptr);
+    cudaEvent_t ev;
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    CUDA_TRY(cudaEventCreate(&ev));
+    *out_event = reinterpret_cast<b200pt_event>(ev);
+    return B200PT_SUCCESS;
+}
+
+int b200pt_event_destroy(b200pt_ctx* ctx, b200pt_event event)
+{
+    REQUIRE(ctx != nullptr);
+    if (event)
+        CUDA_TRY(cudaEventDestroy(reinterpret_cast<cudaEvent_t>(event)));
+    return B200PT_SUCCESS;
+}
+
+int b200pt_event_record(b200pt_ctx* ctx, b200pt_event event, b200pt_stream stream)
+{
+    REQUIRE(ctx != nullptr && event != nullptr);
+    CUDA_TRY(cudaEventRecord(reinterpret_cast<cudaEvent_t>(event), stream_of(ctx, stream)));
+    return B200PT_SUCCESS;
+}
+
+int b200pt_event_elapsed_ms(b200pt_ctx* ctx, b200pt_event start, b200pt_event stop, float* out_ms)
+{
+    REQUIRE(ctx != nullptr && start != nullptr && stop != nullptr && out_ms != nullptr);
+    CUDA_TRY(cudaEventSynchronize(reinterpret_cast<cudaEvent_t>(stop)));
+    CUDA_TRY(cudaEventElapsedTime(out_ms, reinterpret_cast<cudaEvent_t>(start), reinterpret_cast<cudaEvent_t>(stop)));
+    return B200PT_SUCCESS;
+}
+
+} // extern "C"
+
+#include "b200pt_capi_scene.inl"

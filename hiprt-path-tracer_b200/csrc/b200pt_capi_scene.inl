@@ -1,0 +1,258 @@
+// Second half of the C ABI: textures, acceleration structure, kernel launches, ray batches, counters.
+
+extern "C" {
+
+int b200pt_tex2d_create(b200pt_ctx* ctx, const void* host_texels, int width, int height, int channels, int bytes_per_channel, void** out_descriptor_dptr)
+{
+    REQUIRE(ctx != nullptr && host_texels != nullptr && out_descriptor_dptr != nullptr);
+    REQUIRE(width > 0 && height > 0 && channels >= 1 && channels <= 4 && (bytes_per_channel == 1 || bytes_per_channel == 4));
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    size_t bytes = (size_t)width * height * channels * bytes_per_channel;
+    // descriptor and texels share one allocation: [b200pt_tex2d padded to 64 B][texels]
+    unsigned char* block = nullptr;
+    CUDA_TRY(cudaMalloc(&block, 64 + bytes));
+    b200pt_tex2d desc;
+    desc.texels = block + 64;
+    desc.width = width;
+    desc.height = height;
+    desc.channels = channels;
+    desc.bytes_per_channel = bytes_per_channel;
+    cudaError_t e = cudaMemcpy(block, &desc, sizeof(desc), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess)
+        e = cudaMemcpy(block + 64, host_texels, bytes, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess)
+    {
+        cudaFree(block);
+        return cuda_fail(e, "texture upload");
+    }
+    *out_descriptor_dptr = block;
+    return B200PT_SUCCESS;
+}
+
+int b200pt_tex3d_create(b200pt_ctx* ctx, const float* host_texels, int width, int height, int depth, int channels, void** out_descriptor_dptr)
+{
+    REQUIRE(ctx != nullptr && host_texels != nullptr && out_descriptor_dptr != nullptr);
+    REQUIRE(width > 0 && height > 0 && depth > 0 && channels >= 1 && channels <= 4);
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    size_t bytes = (size_t)width * height * depth * channels * sizeof(float);
+    unsigned char* block = nullptr;
+    CUDA_TRY(cudaMalloc(&block, 64 + bytes));
+    b200pt_tex3d desc;
+    desc.texels = reinterpret_cast<const float*>(block + 64);
+    desc.width = width;
+    desc.height = height;
+    desc.depth = depth;
+    desc.channels = channels;
+    cudaError_t e = cudaMemcpy(block, &desc, sizeof(desc), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess)
+        e = cudaMemcpy(block + 64, host_texels, bytes, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess)
+    {
+        cudaFree(block);
+        return cuda_fail(e, "texture upload");
+    }
+    *out_descriptor_dptr = block;
+    return B200PT_SUCCESS;
+}
+
+int b200pt_tex_destroy(b200pt_ctx* ctx, void* descriptor_dptr) { return b200pt_free(ctx, descriptor_dptr); }
+
+int b200pt_tex2d_array_create(b200pt_ctx* ctx, void* const* descriptor_dptrs, int count, void** out_array_dptr)
+{
+    REQUIRE(ctx != nullptr && out_array_dptr != nullptr && count >= 0 && (count == 0 || descriptor_dptrs != nullptr));
+    *out_array_dptr = nullptr;
+    if (count == 0)
+        return B200PT_SUCCESS;
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    b200pt_tex2d* array = nullptr;
+    CUDA_TRY(cudaMalloc(&array, sizeof(b200pt_tex2d) * (size_t)count));
+    for (int i = 0; i < count; i++)
+    {
+        cudaError_t e = cudaMemcpy(array + i, descriptor_dptrs[i], sizeof(b200pt_tex2d), cudaMemcpyDeviceToDevice);
+        if (e != cudaSuccess)
+        {
+            cudaFree(array);
+            return cuda_fail(e, "texture array upload");
+        }
+    }
+    *out_array_dptr = array;
+    return B200PT_SUCCESS;
+}
+
+int b200pt_bvh_build(b200pt_ctx* ctx, const float* vertices, int vertex_count, const int* triangle_indices, int triangle_count, unsigned flags, b200pt_bvh** out_bvh)
+{
+    (void)flags;
+    REQUIRE(ctx != nullptr && out_bvh != nullptr && triangle_count >= 0 && vertex_count >= 0);
+    REQUIRE(triangle_count == 0 || (vertices != nullptr && triangle_indices != nullptr));
+    *out_bvh = nullptr;
+    CUDA_TRY(cudaSetDevice(ctx->device));
+
+    auto t0 = std::chrono::steady_clock::now();
+    pt::Bvh8Host host = pt::build_bvh8(vertices, vertex_count, triangle_indices, triangle_count);
+    double seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+
+    b200pt_bvh* bvh = new b200pt_bvh();
+    bvh->sah_cost = host.sah_cost;
+    bvh->build_seconds = seconds;
+    size_t node_bytes = host.nodes.size() * sizeof(pt::Bvh8Node);
+    size_t tri_bytes = host.triangles.size() * sizeof(pt::Bvh8Triangle);
+    cudaError_t e = cudaMalloc(&bvh->d_nodes, node_bytes);
+    if (e == cudaSuccess)
+        e = cudaMalloc(&bvh->d_triangles, tri_bytes > 0 ? tri_bytes : 16);
+    if (e == cudaSuccess)
+        e = cudaMalloc(&bvh->d_view, sizeof(pt::Bvh8Device));
+    if (e == cudaSuccess)
+        e = cudaMemcpy(bvh->d_nodes, host.nodes.data(), node_bytes, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && tri_bytes > 0)
+        e = cudaMemcpy(bvh->d_triangles, host.triangles.data(), tri_bytes, cudaMemcpyHostToDevice);
+    bvh->view.nodes = reinterpret_cast<const pt::Bvh8Node*>(bvh->d_nodes);
+    bvh->view.triangles = reinterpret_cast<const pt::Bvh8Triangle*>(bvh->d_triangles);
+    bvh->view.node_count = (uint32_t)host.nodes.size();
+    bvh->view.triangle_count = (uint32_t)host.triangles.size();
+    for (int a = 0; a < 3; a++)
+    {
+        bvh->view.scene_min[a] = host.scene_min[a];
+        bvh->view.scene_max[a] = host.scene_max[a];
+    }
+    if (e == cudaSuccess)
+        e = cudaMemcpy(bvh->d_view, &bvh->view, sizeof(pt::Bvh8Device), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess)
+    {
+        cudaFree(bvh->d_nodes);
+        cudaFree(bvh->d_triangles);
+        cudaFree(bvh->d_view);
+        delete bvh;
+        return cuda_fail(e, "BVH upload");
+    }
+    *out_bvh = bvh;
+    return B200PT_SUCCESS;
+}
+
+int b200pt_bvh_destroy(b200pt_ctx* ctx, b200pt_bvh* bvh)
+{
+    REQUIRE(ctx != nullptr);
+    if (!bvh)
+        return B200PT_SUCCESS;
+    cudaSetDevice(ctx->device);
+    cudaFree(bvh->d_nodes);
+    cudaFree(bvh->d_triangles);
+    cudaFree(bvh->d_view);
+    delete bvh;
+    return B200PT_SUCCESS;
+}
+
+void* b200pt_bvh_device_handle(b200pt_bvh* bvh) { return bvh ? bvh->d_view : nullptr; }
+
+int b200pt_bvh_info(b200pt_bvh* bvh, unsigned* out_node_count, unsigned* out_triangle_count, float* out_sah_cost, double* out_build_seconds)
+{
+    REQUIRE(bvh != nullptr);
+    if (out_node_count) *out_node_count = bvh->view.node_count;
+    if (out_triangle_count) *out_triangle_count = bvh->view.triangle_count;
+    if (out_sah_cost) *out_sah_cost = bvh->sah_cost;
+    if (out_build_seconds) *out_build_seconds = bvh->build_seconds;
+    return B200PT_SUCCESS;
+}
+
+int b200pt_kernel_variant_select(b200pt_ctx* ctx, const b200pt_options* options)
+{
+    REQUIRE(ctx != nullptr && options != nullptr);
+    pt::VariantOptions v = {options->direct_light_sampling_strategy, options->envmap_sampling_strategy, options->restir_di_later_bounces_strategy, options->ggx_sample_function};
+    if (!pt::variant_available_t(v))
+    {
+        char msg[256];
+        snprintf(msg, sizeof(msg), "kernel permutation (LSS=%d, ESS=%d, later=%d, GGX=%d) is not compiled into this build (see csrc/variants.h)", v.lss, v.ess, v.later, v.ggx);
+        return fail(B200PT_ERROR_VARIANT_NOT_COMPILED, msg);
+    }
+    ctx->options = v;
+    return B200PT_SUCCESS;
+}
+
+#define LAUNCH_PIXEL_KERNEL(NAME)                                                                                                  \
+    REQUIRE(ctx != nullptr && render_data != nullptr && res.x > 0 && res.y > 0);                                                   \
+    REQUIRE(render_data->geom != nullptr);                                                                                         \
+    pt::Tile t = tile_of(tile, res);                                                                                               \
+    if (t.x1 <= t.x0 || t.y1 <= t.y0)                                                                                              \
+        return B200PT_SUCCESS;                                                                                                     \
+    cudaError_t e;                                                                                                                 \
+    if (ctx->counting)                                                                                                             \
+    {                                                                                                                              \
+        HIPRTRenderData copy = *render_data;                                                                                       \
+        copy.hiprt_function_table = ctx->d_counters;                                                                               \
+        e = pt::NAME##_c(ctx->options, &copy, make_int2(res.x, res.y), t, stream_of(ctx, stream));                                 \
+    }                                                                                                                              \
+    else                                                                                                                           \
+        e = pt::NAME##_t(ctx->options, render_data, make_int2(res.x, res.y), t, stream_of(ctx, stream));                           \
+    if (e != cudaSuccess)                                                                                                          \
+        return cuda_fail(e, #NAME);                                                                                                \
+    return B200PT_SUCCESS;
+
+int b200pt_launch_CameraRays(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream)
+{
+    LAUNCH_PIXEL_KERNEL(launch_CameraRays)
+}
+
+int b200pt_launch_FullPathTracer(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream)
+{
+    LAUNCH_PIXEL_KERNEL(launch_FullPathTracer)
+}
+
+int b200pt_launch_ReSTIR_DI_LightsPresampling(b200pt_ctx* ctx, const LightPresamplingParameters* parameters, b200pt_stream stream)
+{
+    (void)ctx; (void)parameters; (void)stream;
+    return fail(B200PT_ERROR_VARIANT_NOT_COMPILED, "ReSTIR_DI_LightsPresampling is not built yet");
+}
+
+int b200pt_launch_ReSTIR_DI_InitialCandidates(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream)
+{
+    (void)ctx; (void)render_data; (void)res; (void)tile; (void)stream;
+    return fail(B200PT_ERROR_VARIANT_NOT_COMPILED, "ReSTIR_DI_InitialCandidates is not built yet");
+}
+
+int b200pt_launch_ReSTIR_DI_SpatiotemporalReuse(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream)
+{
+    (void)ctx; (void)render_data; (void)res; (void)tile; (void)stream;
+    return fail(B200PT_ERROR_VARIANT_NOT_COMPILED, "ReSTIR_DI_SpatiotemporalReuse is not built yet");
+}
+
+int b200pt_trace_closest(b200pt_ctx* ctx, b200pt_bvh* bvh, const float* d_rays, const int* d_last_prim, long long n, int* d_out_prim, float* d_out_t, float* d_out_uv, b200pt_stream stream)
+{
+    REQUIRE(ctx != nullptr && bvh != nullptr && n >= 0 && (n == 0 || (d_rays != nullptr && d_out_prim != nullptr && d_out_t != nullptr)));
+    cudaError_t e = ctx->counting ? pt::launch_trace_closest_c(bvh->view, d_rays, d_last_prim, n, d_out_prim, d_out_t, d_out_uv, ctx->d_counters, stream_of(ctx, stream))
+                                  : pt::launch_trace_closest_t(bvh->view, d_rays, d_last_prim, n, d_out_prim, d_out_t, d_out_uv, nullptr, stream_of(ctx, stream));
+    if (e != cudaSuccess)
+        return cuda_fail(e, "trace_closest");
+    return B200PT_SUCCESS;
+}
+
+int b200pt_trace_shadow(b200pt_ctx* ctx, b200pt_bvh* bvh, const float* d_rays, const float* d_t_max, const int* d_last_prim, long long n, unsigned char* d_out_occluded, b200pt_stream stream)
+{
+    REQUIRE(ctx != nullptr && bvh != nullptr && n >= 0 && (n == 0 || (d_rays != nullptr && d_t_max != nullptr && d_out_occluded != nullptr)));
+    cudaError_t e = ctx->counting ? pt::launch_trace_shadow_c(bvh->view, d_rays, d_t_max, d_last_prim, n, d_out_occluded, ctx->d_counters, stream_of(ctx, stream))
+                                  : pt::launch_trace_shadow_t(bvh->view, d_rays, d_t_max, d_last_prim, n, d_out_occluded, nullptr, stream_of(ctx, stream));
+    if (e != cudaSuccess)
+        return cuda_fail(e, "trace_shadow");
+    return B200PT_SUCCESS;
+}
+
+int b200pt_counters_enable(b200pt_ctx* ctx, int enable)
+{
+    REQUIRE(ctx != nullptr);
+    ctx->counting = enable != 0;
+    return B200PT_SUCCESS;
+}
+
+int b200pt_counters_read(b200pt_ctx* ctx, b200pt_counters* out, int reset)
+{
+    REQUIRE(ctx != nullptr && out != nullptr);
+    CUDA_TRY(cudaStreamSynchronize(ctx->main_stream));
+    pt::TraversalCounters c;
+    CUDA_TRY(cudaMemcpy(&c, ctx->d_counters, sizeof(c), cudaMemcpyDeviceToHost));
+    out->rays = c.rays;
+    out->nodes = c.nodes;
+    out->triangles = c.triangles;
+    if (reset)
+        CUDA_TRY(cudaMemset(ctx->d_counters, 0, sizeof(c)));
+    return B200PT_SUCCESS;
+}
+
+} // extern "C"

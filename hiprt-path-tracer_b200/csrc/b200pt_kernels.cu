@@ -1,0 +1,94 @@
+// __global__ entry points and launchers shared by every permutation: CameraRays, ray-batch queries, dispatch of the
+// per-permutation FullPathTracer translation units. Compiled twice: timing build (suffix _t) and, with -DPT_COUNTERS,
+// counting build (suffix _c) that accumulates rays / nodes / triangles for Mrays/s and the node-fetch roofline.
+#include "kernels.cuh"
+#include "launch.h"
+#include "variants.h"
+
+namespace pt
+{
+template <int LSS>
+__global__ void __launch_bounds__(64) PT_SUFFIXED(k_CameraRays)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile)
+{
+    const uint32_t x = tile.x0 + blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t y = tile.y0 + blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= (uint32_t)tile.x1 || y >= (uint32_t)tile.y1)
+        return;
+    camera_rays_pixel<LSS == 5>(rd, res, x, y);
+}
+
+__global__ void PT_SUFFIXED(k_trace_closest)(Bvh8Device bvh, const float* __restrict__ rays, const int* __restrict__ last_prim, long long n, int* out_prim, float* out_t, float* out_uv, TraversalCounters* counters)
+{
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+        return;
+    float3 o = f3(rays[i * 6 + 0], rays[i * 6 + 1], rays[i * 6 + 2]);
+    float3 d = f3(rays[i * 6 + 3], rays[i * 6 + 4], rays[i * 6 + 5]);
+    Hit hit;
+    bvh8_trace<false>(bvh, o, d, INFINITY, last_prim ? last_prim[i] : -1, hit, counters);
+    out_prim[i] = hit.prim;
+    out_t[i] = hit.t;
+    if (out_uv)
+    {
+        out_uv[i * 2 + 0] = hit.u;
+        out_uv[i * 2 + 1] = hit.v;
+    }
+}
+
+__global__ void PT_SUFFIXED(k_trace_shadow)(Bvh8Device bvh, const float* __restrict__ rays, const float* __restrict__ t_max, const int* __restrict__ last_prim, long long n, unsigned char* out_occluded, TraversalCounters* counters)
+{
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+        return;
+    float3 o = f3(rays[i * 6 + 0], rays[i * 6 + 1], rays[i * 6 + 2]);
+    float3 d = f3(rays[i * 6 + 3], rays[i * 6 + 4], rays[i * 6 + 5]);
+    Hit hit;
+    out_occluded[i] = bvh8_trace<true>(bvh, o, d, t_max[i] - 1.0e-4f, last_prim ? last_prim[i] : -1, hit, counters) ? 1 : 0;
+}
+
+static inline dim3 pixel_grid(const Tile& t) { return dim3((t.x1 - t.x0 + 7) / 8, (t.y1 - t.y0 + 7) / 8, 1); }
+
+#define PT_DECLARE_VARIANT(LSS, ESS, LATER, GGX) cudaError_t PT_VARIANT_NAME_OF(launch_FullPathTracer, LSS, ESS, LATER, GGX)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream);
+PT_FOR_EACH_VARIANT(PT_DECLARE_VARIANT)
+
+bool PT_SUFFIXED(variant_available)(const VariantOptions& opt)
+{
+#define PT_CASE_AVAIL(LSS, ESS, LATER, GGX) if (opt.lss == LSS && opt.ess == ESS && (opt.lss != 5 || opt.later == LATER) && opt.ggx == GGX) return true;
+    PT_FOR_EACH_VARIANT(PT_CASE_AVAIL)
+    return false;
+}
+
+cudaError_t PT_SUFFIXED(launch_CameraRays)(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream)
+{
+    if (opt.lss == 5)
+        PT_SUFFIXED(k_CameraRays)<5><<<pixel_grid(tile), dim3(8, 8, 1), 0, stream>>>(*rd, res, tile);
+    else
+        PT_SUFFIXED(k_CameraRays)<0><<<pixel_grid(tile), dim3(8, 8, 1), 0, stream>>>(*rd, res, tile);
+    return cudaGetLastError();
+}
+
+cudaError_t PT_SUFFIXED(launch_FullPathTracer)(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream)
+{
+#define PT_CASE_FPT(LSS, ESS, LATER, GGX) if (opt.lss == LSS && opt.ess == ESS && (opt.lss != 5 || opt.later == LATER) && opt.ggx == GGX) return PT_VARIANT_NAME_OF(launch_FullPathTracer, LSS, ESS, LATER, GGX)(rd, res, tile, stream);
+    PT_FOR_EACH_VARIANT(PT_CASE_FPT)
+    return cudaErrorInvalidDeviceFunction;
+}
+
+cudaError_t PT_SUFFIXED(launch_trace_closest)(const Bvh8Device& bvh, const float* rays, const int* last_prim, long long n, int* out_prim, float* out_t, float* out_uv, TraversalCounters* counters, cudaStream_t stream)
+{
+    if (n <= 0)
+        return cudaSuccess;
+    const int block = 128;
+    PT_SUFFIXED(k_trace_closest)<<<(unsigned)((n + block - 1) / block), block, 0, stream>>>(bvh, rays, last_prim, n, out_prim, out_t, out_uv, counters);
+    return cudaGetLastError();
+}
+
+cudaError_t PT_SUFFIXED(launch_trace_shadow)(const Bvh8Device& bvh, const float* rays, const float* t_max, const int* last_prim, long long n, unsigned char* out_occluded, TraversalCounters* counters, cudaStream_t stream)
+{
+    if (n <= 0)
+        return cudaSuccess;
+    const int block = 128;
+    PT_SUFFIXED(k_trace_shadow)<<<(unsigned)((n + block - 1) / block), block, 0, stream>>>(bvh, rays, t_max, last_prim, n, out_occluded, counters);
+    return cudaGetLastError();
+}
+} // namespace pt

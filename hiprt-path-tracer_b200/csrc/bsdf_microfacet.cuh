@@ -187,7 +187,7 @@ PT_DEV RGB RGB_hue_shift(RGB color, float hue_shift_degrees)
     // double-precision matrix entries rounded to float, as in the reference (ThinFilm.h:87-110)
     float cosA = cosf(hue_shift_degrees / 180.0f * kPi);
     float sinA = sinf(hue_shift_degrees / 180.0f * kPi);
-    double c = cosA, s = sinA, k = sqrt(1. / 3.);
+    double c = cosA, s = sinA, k = ::sqrt(1. / 3.);
     float m00 = (float)(c + (1.0 - c) / 3.0);
     float m01 = (float)(1. / 3. * (1.0 - c) - k * s);
     float m02 = (float)(1. / 3. * (1.0 - c) + k * s);
@@ -201,7 +201,7 @@ PT_DEV RGB RGB_hue_shift(RGB color, float hue_shift_degrees)
 }
 
 // thin_film_fresnel (ThinFilm.h:112-219)
-PT_DEV RGB thin_film_fresnel(const Material& material, float ambient_IOR, float HoL)
+PT_DEV_NOINLINE RGB thin_film_fresnel(const Material& material, float ambient_IOR, float HoL)
 {
     float eta1 = ambient_IOR;
     float eta2 = material.thin_film_ior;

@@ -29,9 +29,10 @@ struct RayPayload
 
 PT_DEV const Bvh8Device& scene_bvh(const HIPRTRenderData& rd) { return *reinterpret_cast<const Bvh8Device*>(rd.geom); }
 
+// Counting build: the launcher stores the device address of the context's counter block in the (otherwise unused)
+// HIPRTRenderData::hiprt_function_table field of its private copy of the struct.
 #ifdef PT_COUNTERS
-__device__ TraversalCounters g_traversal_counters;
-#define PT_COUNTERS_PTR (&g_traversal_counters)
+#define PT_COUNTERS_PTR reinterpret_cast<TraversalCounters*>(rd.hiprt_function_table)
 #else
 #define PT_COUNTERS_PTR nullptr
 #endif
@@ -106,7 +107,7 @@ PT_DEV float3 hit_geometric_normal(const HIPRTRenderData& rd, const Hit& hit)
 }
 
 // trace_ray (Intersect.h:114-219). Returns true if a hit was found.
-PT_DEV bool trace_ray(const HIPRTRenderData& rd, float3 origin, float3 direction, RayPayload& payload, HitInfo& out, int last_hit_primitive_index, Rng& rng)
+PT_DEV_NOINLINE bool trace_ray(const HIPRTRenderData& rd, float3 origin, float3 direction, RayPayload& payload, HitInfo& out, int last_hit_primitive_index, Rng& rng)
 {
     Hit hit;
     bool skipping_volume_boundary = false;
@@ -171,7 +172,7 @@ struct ShadowLightRayHitInfo
 };
 
 // evaluate_shadow_light_ray (Intersect.h:293-410): closest hit, then the emission + shading normal of what was hit
-PT_DEV bool evaluate_shadow_light_ray(const HIPRTRenderData& rd, float3 origin, float3 direction, float t_max, ShadowLightRayHitInfo& out, int last_hit_primitive_index, Rng& rng)
+PT_DEV_NOINLINE bool evaluate_shadow_light_ray(const HIPRTRenderData& rd, float3 origin, float3 direction, float t_max, ShadowLightRayHitInfo& out, int last_hit_primitive_index, Rng& rng)
 {
     (void)rng;
     Hit hit;

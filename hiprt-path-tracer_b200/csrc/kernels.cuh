@@ -4,12 +4,10 @@
 #pragma once
 
 #include "envmap.cuh"
-#include "ris.cuh"
+#include "restir_di.cuh"
 
 namespace pt
 {
-struct Tile { int x0, y0, x1, y1; };
-
 // ---- adaptive sampling (AdaptiveSampling.h) ----------------------------------------------------
 PT_DEV bool has_access_to_adaptive_sampling_buffers(const HIPRTRenderSettings& s)
 {
@@ -246,5 +244,245 @@ PT_DEV void camera_rays_pixel(const HIPRTRenderData& rd, int2 res, uint32_t x, u
 
     if (rd.render_settings.do_update_status_buffers)
         rd.aux_buffers.still_one_ray_active[0] = 1;
+}
+
+// do_russian_roulette (RussianRoulette.h:14-49). Returns false if the path is killed.
+PT_DEV bool do_russian_roulette(const HIPRTRenderSettings& s, int bounce, RGB& throughput, RGB current_weight, Rng& rng)
+{
+    if (bounce >= s.russian_roulette_min_depth && s.use_russian_roulette)
+    {
+        float survive_probability = 0.0f;
+        if (s.path_russian_roulette_method == MAX_THROUGHPUT)
+            survive_probability = throughput.max_component();
+        else if (s.path_russian_roulette_method == ARNOLD_2014)
+        {
+            survive_probability = (throughput * current_weight).max_component() / throughput.max_component();
+            survive_probability = sqrtf(survive_probability);
+        }
+        survive_probability = minf(survive_probability, 1.0f);
+        if (rng() > survive_probability)
+            return false;
+        float throughput_increase = 1.0f / survive_probability;
+        if (s.russian_roulette_throughput_clamp > 0.0f)
+            throughput_increase = minf(throughput_increase, s.russian_roulette_throughput_clamp);
+        throughput *= throughput_increase;
+    }
+    return true;
+}
+
+// sample_one_light (Lights.h:277-321) with sample_many_lights (:222-242) and sample_one_light_ReSTIR_DI (:244-275)
+template <int LSS, int LATER, int GGX_SAMPLER>
+PT_DEV RGB sample_one_light(const HIPRTRenderData& rd, RayPayload& payload, const HitInfo& hit, float3 view_direction, Rng& rng, int2 pixel_coords, int2 res, int bounce)
+{
+    if (rd.buffers.emissive_triangles_count == 0 && !(rd.world_settings.ambient_light_type == AMBIENT_ENVMAP && LSS == 5))
+        return RGB(0.0f);
+    if (rd.bsdfs_data.white_furnace_mode && rd.bsdfs_data.white_furnace_mode_turn_off_emissives)
+        return RGB(0.0f);
+    if (material_is_emissive(payload.material))
+    {
+        if (payload.material.emissive_texture_used && bounce > 0)
+            return material_emission(payload.material);
+        return RGB(0.0f);
+    }
+    if (LSS == 0)
+        return RGB(0.0f);
+
+    RGB direct;
+    if (LSS == 5 && bounce == 0)
+        return sample_light_ReSTIR_DI<GGX_SAMPLER>(rd, payload, hit, view_direction, rng, pixel_coords, res);
+
+    const int strategy = LSS == 5 ? (LATER == 0 ? 1 : LATER == 1 ? 2 : LATER == 2 ? 3 : 4) : LSS;
+    for (int i = 0; i < rd.render_settings.number_of_light_samples; i++)
+    {
+        if (strategy == 1)
+            direct += sample_one_light_no_MIS(rd, payload, hit, view_direction, rng);
+        else if (strategy == 2)
+            direct += sample_one_light_bsdf<GGX_SAMPLER>(rd, payload, hit, view_direction, rng);
+        else if (strategy == 3)
+            direct += sample_one_light_MIS<GGX_SAMPLER>(rd, payload, hit, view_direction, rng);
+        else
+            direct += sample_lights_RIS<GGX_SAMPLER>(rd, payload, hit, view_direction, rng);
+    }
+    return direct / rd.render_settings.number_of_light_samples;
+}
+
+PT_DEV bool sanity_check(const HIPRTRenderData& rd, RayPayload& payload, uint32_t pixel_index)
+{
+    bool invalid = false;
+    if (payload.volume_state.sampled_wavelength == 0.0f)
+        invalid |= payload.ray_color.r < 0 || payload.ray_color.g < 0 || payload.ray_color.b < 0;
+    invalid |= payload.ray_color.has_NaN();
+    if (invalid)
+    {
+        if (rd.render_settings.display_NaNs)
+        {
+            // debug_set_final_color (FullPathTracer.h:27-33)
+            RGB c(1.0e30f, 0.0f, 1.0e30f);
+            if (rd.render_settings.sample_number != 0)
+                c = c * rd.render_settings.sample_number;
+            st3(rd.buffers.pixels, pixel_index, to_f3(c));
+        }
+        else
+            payload.ray_color = RGB(0.0f);
+    }
+    return !invalid;
+}
+
+template <int LSS, int ESS, int LATER, int GGX_SAMPLER>
+PT_DEV void full_path_tracer_pixel(const HIPRTRenderData& rd, int2 res, uint32_t x, uint32_t y)
+{
+    uint32_t pixel_index = x + y * res.x;
+    if (!rd.aux_buffers.pixel_active[pixel_index])
+        return;
+
+    int nb_bounces = rd.render_settings.nb_bounces;
+    if (do_render_low_resolution(rd.render_settings))
+        nb_bounces = mini(3, nb_bounces);
+
+    Rng rng(pixel_seed(rd, pixel_index));
+
+    float squared_luminance_of_samples = 0.0f;
+    RGB denoiser_albedo(0.0f);
+    float3 denoiser_normal = f3(0.0f, 0.0f, 0.0f);
+
+    HitInfo hit;
+    hit.inter_point = ld3_rw(rd.g_buffer.first_hits, pixel_index);
+    hit.geometric_normal = normalize(ld3_rw(rd.g_buffer.geometric_normals, pixel_index));
+    hit.shading_normal = normalize(ld3_rw(rd.g_buffer.shading_normals, pixel_index));
+    hit.primitive_index = rd.g_buffer.first_hit_prim_index[pixel_index];
+
+    float3 origin = f3(0.0f, 0.0f, 0.0f);
+    float3 direction = normalize(-ld3_rw(rd.g_buffer.view_directions, pixel_index));
+    bool intersection_found = rd.g_buffer.camera_ray_hit[pixel_index] == 1;
+
+    RayPayload payload;
+    payload.throughput = RGB(1.0f);
+    payload.ray_color = RGB(0.0f);
+    payload.next_ray_state = 0;
+    load_material(payload.material, rd.g_buffer.materials + pixel_index);
+    copy_volume_state(&payload.volume_state, rd.g_buffer.ray_volume_states + pixel_index);
+
+    for (int bounce = 0; bounce < nb_bounces + 1; bounce++)
+    {
+        if (payload.next_ray_state != 1)
+        {
+            if (bounce > 0)
+                intersection_found = trace_ray(rd, origin, direction, payload, hit, hit.primitive_index, rng);
+
+            if (intersection_found)
+            {
+                if (bounce == 0)
+                {
+                    denoiser_normal += hit.shading_normal;
+                    denoiser_albedo += rgb(payload.material.base_color);
+                }
+
+                if (material_is_emissive(payload.material) && dot(-direction, hit.geometric_normal) < 0)
+                {
+                    hit.geometric_normal = -hit.geometric_normal;
+                    hit.shading_normal = -hit.shading_normal;
+                }
+
+                RGB light_direct = sample_one_light<LSS, LATER, GGX_SAMPLER>(rd, payload, hit, -direction, rng, make_int2(x, y), res, bounce);
+                RGB envmap_direct = sample_environment_map<LSS, ESS, GGX_SAMPLER>(rd, payload, hit, -direction, bounce, rng);
+
+                light_direct = clamp_light_contribution(light_direct, rd.render_settings.direct_contribution_clamp, bounce == 0);
+                envmap_direct = clamp_light_contribution(envmap_direct, rd.render_settings.envmap_contribution_clamp, bounce == 0);
+
+                if (LSS == 0)
+                {
+                    RGB hit_emission = material_emission(payload.material);
+                    hit_emission = clamp_light_contribution(hit_emission, rd.render_settings.indirect_contribution_clamp, bounce > 0);
+                    payload.ray_color += hit_emission * payload.throughput;
+                }
+                else
+                {
+                    if (bounce == 0)
+                        payload.ray_color += material_emission(payload.material);
+                    RGB indirect = (light_direct + envmap_direct) * payload.throughput;
+                    payload.ray_color += clamp_light_contribution(indirect, rd.render_settings.indirect_contribution_clamp, bounce > 0);
+                }
+
+                float bsdf_pdf;
+                float3 bounce_direction;
+                RGB bsdf_color = bsdf_sample<GGX_SAMPLER>(rd, payload.material, payload.volume_state, -direction, hit.shading_normal, hit.geometric_normal, bounce_direction, bsdf_pdf, rng);
+                RGB throughput_attenuation = bsdf_color * fabsf(dot(bounce_direction, hit.shading_normal)) / bsdf_pdf;
+
+                if (bsdf_pdf <= 0.0f)
+                    break;
+                if (!do_russian_roulette(rd.render_settings, bounce, payload.throughput, throughput_attenuation, rng))
+                    break;
+
+                payload.throughput *= get_dispersion_ray_color(payload.volume_state.sampled_wavelength, payload.material.dispersion_scale);
+                payload.throughput *= throughput_attenuation;
+                payload.next_ray_state = 0;
+
+                origin = hit.inter_point;
+                direction = bounce_direction;
+            }
+            else
+            {
+                RGB skysphere_color;
+                if (rd.world_settings.ambient_light_type == AMBIENT_UNIFORM || rd.bsdfs_data.white_furnace_mode)
+                    skysphere_color = rgb(rd.world_settings.uniform_light_color);
+                else if (rd.world_settings.ambient_light_type == AMBIENT_ENVMAP)
+                {
+                    if (ESS == 0 || bounce == 0)
+                    {
+                        skysphere_color = eval_envmap_no_pdf(rd.world_settings, direction);
+                        bool unscale = ESS == 0 ? (!rd.world_settings.envmap_scale_background_intensity && bounce == 0) : !rd.world_settings.envmap_scale_background_intensity;
+                        if (unscale)
+                            skysphere_color /= rd.world_settings.envmap_intensity;
+                    }
+                }
+
+                skysphere_color = clamp_light_contribution(skysphere_color, rd.render_settings.envmap_contribution_clamp, true);
+                RGB indirect = skysphere_color * payload.throughput;
+                payload.ray_color += clamp_light_contribution(indirect, rd.render_settings.indirect_contribution_clamp, bounce > 0);
+                payload.next_ray_state = 1;
+            }
+        }
+        else
+            break;
+    }
+
+    if (!sanity_check(rd, payload, pixel_index))
+        return;
+
+    squared_luminance_of_samples += payload.ray_color.luminance() * payload.ray_color.luminance();
+    rd.aux_buffers.still_one_ray_active[0] = 1;
+
+    if (has_access_to_adaptive_sampling_buffers(rd.render_settings))
+        rd.aux_buffers.pixel_squared_luminance[pixel_index] += squared_luminance_of_samples;
+
+    const int sample_number = rd.render_settings.sample_number;
+    if (sample_number == 0)
+        st3(rd.buffers.pixels, pixel_index, to_f3(payload.ray_color));
+    else
+        st3(rd.buffers.pixels, pixel_index, ld3_rw(rd.buffers.pixels, pixel_index) + to_f3(payload.ray_color));
+
+    const float counter = (float)rd.render_settings.denoiser_AOV_accumulation_counter;
+    if (rd.aux_buffers.denoiser_albedo != nullptr)
+    {
+        if (sample_number == 0)
+            st3(rd.aux_buffers.denoiser_albedo, pixel_index, to_f3(denoiser_albedo));
+        else
+        {
+            RGB prev(ld3_rw(rd.aux_buffers.denoiser_albedo, pixel_index));
+            st3(rd.aux_buffers.denoiser_albedo, pixel_index, to_f3((prev * counter + denoiser_albedo) / (counter + 1.0f)));
+        }
+    }
+    if (rd.aux_buffers.denoiser_normals != nullptr)
+    {
+        if (sample_number == 0)
+            st3(rd.aux_buffers.denoiser_normals, pixel_index, denoiser_normal);
+        else
+        {
+            float3 accumulated = (ld3_rw(rd.aux_buffers.denoiser_normals, pixel_index) * counter + denoiser_normal) / (counter + 1.0f);
+            float normal_length = length(accumulated);
+            if (!is_zero(normal_length))
+                st3(rd.aux_buffers.denoiser_normals, pixel_index, accumulated / normal_length);
+        }
+    }
 }
 } // namespace pt

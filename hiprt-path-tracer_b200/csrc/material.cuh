@@ -92,7 +92,7 @@ PT_DEV float base_color_alpha(const HIPRTRenderData& rd, int material_index, flo
 }
 
 // get_intersection_material (Material.h:47-96)
-PT_DEV void get_intersection_material(const HIPRTRenderData& rd, int material_index, float2 texcoords, Material& out)
+PT_DEV_NOINLINE void get_intersection_material(const HIPRTRenderData& rd, int material_index, float2 texcoords, Material& out)
 {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(material_ptr(rd, material_index));
     uint32_t* dst = reinterpret_cast<uint32_t*>(&out);

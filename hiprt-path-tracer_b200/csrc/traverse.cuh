@@ -14,6 +14,7 @@
 #pragma once
 
 #include "bvh8.h"
+#include "launch.h"
 #include "vec.cuh"
 
 namespace pt
@@ -23,11 +24,6 @@ struct Hit
     int prim;        // scene triangle index, -1 = miss
     int tri_slot;    // index in the BVH triangle array (to re-fetch the vertices)
     float t, u, v;
-};
-
-struct TraversalCounters
-{
-    unsigned long long rays, nodes, triangles;
 };
 
 #ifdef PT_COUNTERS
@@ -70,7 +66,7 @@ PT_DEV bool intersect_triangle_reference(float3 o, float3 d, float3 a, float3 b,
 
 // ANY_HIT = false: closest hit over t in (1e-7, +inf).  ANY_HIT = true: first accepted triangle with t < t_limit.
 template <bool ANY_HIT>
-PT_DEV bool bvh8_trace(const Bvh8Device& bvh, float3 o, float3 d, float t_limit, int last_prim, Hit& hit, TraversalCounters* counters = nullptr)
+PT_DEV_NOINLINE bool bvh8_trace(const Bvh8Device& bvh, float3 o, float3 d, float t_limit, int last_prim, Hit& hit, TraversalCounters* counters = nullptr)
 {
     hit.prim = -1;
     hit.tri_slot = -1;

@@ -12,6 +12,8 @@
 
 #define PT_DEV __device__ __forceinline__
 #define PT_HD __host__ __device__ __forceinline__
+// Large functions called from many sites: a real call keeps the megakernel's code size (and ptxas time) bounded.
+#define PT_DEV_NOINLINE static __device__ __noinline__
 
 namespace pt
 {

@@ -1,0 +1,351 @@
+// See GPURenderer.h. reference: src/Renderer/GPURenderer.cpp:236-267 (update), :408-486 (render + launch points),
+// :980-1039 (update_render_data), :1041-1174 (set_scene / set_envmap); CPU seed schedule: src/Renderer/CPURenderer.cpp:264-296.
+#include "GPURenderer.h"
+
+#include <cstring>
+
+namespace b200pt_host
+{
+void GBufferStorage::set_context(b200pt_ctx* ctx)
+{
+    materials.set_context(ctx); shading_normals.set_context(ctx); geometric_normals.set_context(ctx); view_directions.set_context(ctx);
+    first_hits.set_context(ctx); first_hit_prim_index.set_context(ctx); camera_ray_hit.set_context(ctx); ray_volume_states.set_context(ctx);
+}
+
+void GBufferStorage::resize(size_t n)
+{
+    materials.resize(n); shading_normals.resize(n); geometric_normals.resize(n); view_directions.resize(n);
+    first_hits.resize(n); first_hit_prim_index.resize(n); camera_ray_hit.resize(n); ray_volume_states.resize(n);
+    if (n > 0)
+    {
+        materials.memset_zero(); shading_normals.memset_zero(); geometric_normals.memset_zero(); view_directions.memset_zero();
+        first_hits.memset_zero(); first_hit_prim_index.memset_zero(); camera_ray_hit.memset_zero(); ray_volume_states.memset_zero();
+    }
+}
+
+GBuffer GBufferStorage::view() const
+{
+    GBuffer g;
+    g.materials = materials.get_device_pointer();
+    g.first_hit_prim_index = first_hit_prim_index.get_device_pointer();
+    g.shading_normals = shading_normals.get_device_pointer();
+    g.geometric_normals = geometric_normals.get_device_pointer();
+    g.view_directions = view_directions.get_device_pointer();
+    g.first_hits = first_hits.get_device_pointer();
+    g.camera_ray_hit = camera_ray_hit.get_device_pointer();
+    g.ray_volume_states = ray_volume_states.get_device_pointer();
+    return g;
+}
+
+GPURenderer::GPURenderer(b200pt_ctx* ctx) : m_ctx(ctx)
+{
+    std::memset(&m_camera, 0, sizeof(m_camera));
+    m_camera.do_jittering = 1;
+    DeviceBuffer<unsigned char>* u8[] = {&m_pixel_active, &m_still_one_ray_active, &m_has_vertex_normals};
+    for (auto* b : u8) b->set_context(ctx);
+    DeviceBuffer<int>* i32[] = {&m_pixel_sample_count, &m_pixel_converged_sample_count, &m_triangle_indices, &m_material_indices, &m_emissive_triangles, &m_alias_alias};
+    for (auto* b : i32) b->set_context(ctx);
+    m_pixel_squared_luminance.set_context(ctx); m_alias_probas.set_context(ctx);
+    m_denoiser_albedo.set_context(ctx); m_pixels.set_context(ctx);
+    m_denoiser_normals.set_context(ctx); m_vertices.set_context(ctx); m_normals.set_context(ctx);
+    m_texcoords.set_context(ctx); m_materials.set_context(ctx); m_textures_dims.set_context(ctx);
+    m_stop_noise_threshold_count.set_context(ctx);
+    m_restir_initial.set_context(ctx); m_restir_spatial_1.set_context(ctx); m_restir_spatial_2.set_context(ctx); m_restir_presampled_lights.set_context(ctx);
+    m_g_buffer.set_context(ctx); m_g_buffer_prev.set_context(ctx);
+
+    m_still_one_ray_active.resize(1);
+    m_stop_noise_threshold_count.resize(1);
+    check(b200pt_event_create(ctx, &m_frame_start), "b200pt_event_create");
+    check(b200pt_event_create(ctx, &m_frame_stop), "b200pt_event_create");
+    check(b200pt_kernel_variant_select(ctx, &m_options), "b200pt_kernel_variant_select");
+}
+
+GPURenderer::~GPURenderer()
+{
+    b200pt_stream_sync(m_ctx, nullptr);
+    if (m_bvh) b200pt_bvh_destroy(m_ctx, m_bvh);
+    for (void* d : m_texture_descriptors) b200pt_tex_destroy(m_ctx, d);
+    if (m_texture_array) b200pt_free(m_ctx, m_texture_array);
+    for (void* l : m_luts) if (l) b200pt_tex_destroy(m_ctx, l);
+    if (m_envmap) b200pt_tex_destroy(m_ctx, m_envmap);
+    b200pt_event_destroy(m_ctx, m_frame_start);
+    b200pt_event_destroy(m_ctx, m_frame_stop);
+}
+
+void GPURenderer::set_kernel_options(const b200pt_options& options)
+{
+    check(b200pt_kernel_variant_select(m_ctx, &options), "b200pt_kernel_variant_select");
+    m_options = options;
+}
+
+void GPURenderer::set_brdf_luts(const float* sheen, const float* conductor, const float* glossy, const float* glass, const float* glass_inverse, const float* thin_glass)
+{
+    for (void*& l : m_luts)
+    {
+        if (l) b200pt_tex_destroy(m_ctx, l);
+        l = nullptr;
+    }
+    // dimensions: src/Renderer/Baker/GPUBakerConstants.h:14-31; sheen table: 32x32 RGB (SheenLTCFittedParameters.h)
+    check(b200pt_tex2d_create(m_ctx, sheen, 32, 32, 3, 4, &m_luts[0]), "sheen LTC LUT");
+    check(b200pt_tex2d_create(m_ctx, conductor, 128, 128, 1, 4, &m_luts[1]), "GGX conductor LUT");
+    check(b200pt_tex3d_create(m_ctx, glossy, 128, 64, 128, 1, &m_luts[2]), "glossy dielectric LUT");
+    check(b200pt_tex3d_create(m_ctx, glass, 256, 16, 128, 1, &m_luts[3]), "GGX glass LUT");
+    check(b200pt_tex3d_create(m_ctx, glass_inverse, 256, 16, 128, 1, &m_luts[4]), "GGX glass inverse LUT");
+    check(b200pt_tex3d_create(m_ctx, thin_glass, 32, 32, 96, 1, &m_luts[5]), "GGX thin glass LUT");
+    BRDFsData& b = m_render_data.bsdfs_data;
+    b.sheen_ltc_parameters_texture = m_luts[0];
+    b.GGX_conductor_Ess = m_luts[1];
+    b.glossy_dielectric_Ess = m_luts[2];
+    b.GGX_Ess_glass = m_luts[3];
+    b.GGX_Ess_glass_inverse = m_luts[4];
+    b.GGX_Ess_thin_glass = m_luts[5];
+}
+
+void GPURenderer::set_scene(const Scene& scene)
+{
+    if (m_bvh)
+    {
+        b200pt_bvh_destroy(m_ctx, m_bvh);
+        m_bvh = nullptr;
+    }
+    int ntris = (int)(scene.triangle_indices.size() / 3);
+    check(b200pt_bvh_build(m_ctx, reinterpret_cast<const float*>(scene.vertices_positions.data()), (int)scene.vertices_positions.size(), scene.triangle_indices.data(), ntris, 0, &m_bvh), "b200pt_bvh_build");
+
+    m_triangle_indices.upload_data(scene.triangle_indices);
+    m_vertices.upload_data(scene.vertices_positions);
+    m_normals.upload_data(scene.vertex_normals);
+    m_has_vertex_normals.upload_data(scene.has_vertex_normals);
+    m_texcoords.upload_data(scene.texcoords);
+    m_material_indices.upload_data(scene.material_indices);
+    m_materials.upload_data(scene.materials);
+    m_emissive_triangles.upload_data(scene.emissive_triangle_indices);
+
+    for (void* d : m_texture_descriptors) b200pt_tex_destroy(m_ctx, d);
+    m_texture_descriptors.clear();
+    if (m_texture_array) b200pt_free(m_ctx, m_texture_array);
+    m_texture_array = nullptr;
+    std::vector<b200pt_int2> dims;
+    for (const Scene::Texture8& t : scene.textures)
+    {
+        void* d = nullptr;
+        check(b200pt_tex2d_create(m_ctx, t.texels.data(), t.width, t.height, t.channels, 1, &d), "b200pt_tex2d_create");
+        m_texture_descriptors.push_back(d);
+        dims.push_back({t.width, t.height});
+    }
+    check(b200pt_tex2d_array_create(m_ctx, m_texture_descriptors.data(), (int)m_texture_descriptors.size(), &m_texture_array), "b200pt_tex2d_array_create");
+    m_textures_dims.upload_data(dims);
+
+    RenderBuffers& b = m_render_data.buffers;
+    m_render_data.geom = b200pt_bvh_device_handle(m_bvh);
+    b.triangles_indices = m_triangle_indices.get_device_pointer();
+    b.vertices_positions = m_vertices.get_device_pointer();
+    b.has_vertex_normals = m_has_vertex_normals.get_device_pointer();
+    b.vertex_normals = m_normals.get_device_pointer();
+    b.texcoords = m_texcoords.get_device_pointer();
+    b.material_indices = m_material_indices.get_device_pointer();
+    b.materials_buffer = m_materials.get_device_pointer();
+    b.emissive_triangles_count = (int)scene.emissive_triangle_indices.size();
+    b.emissive_triangles_indices = m_emissive_triangles.get_device_pointer();
+    b.material_textures = m_texture_array;
+    b.textures_dims = m_textures_dims.get_device_pointer();
+}
+
+void GPURenderer::set_envmap(const float* texels, int width, int height, int channels, const float* alias_probas, const int* alias_alias, float total_sum)
+{
+    WorldSettings& w = m_render_data.world_settings;
+    if (m_envmap) b200pt_tex_destroy(m_ctx, m_envmap);
+    m_envmap = nullptr;
+    if (width == 0 || height == 0 || texels == nullptr)
+    {
+        // GPURenderer::set_envmap with an empty image: uniform ambient light (GPURenderer.cpp:1142-1150)
+        w.ambient_light_type = AMBIENT_UNIFORM;
+        w.uniform_light_color = {0.5f, 0.5f, 0.5f};
+        return;
+    }
+    check(b200pt_tex2d_create(m_ctx, texels, width, height, channels, 4, &m_envmap), "envmap upload");
+    size_t n = (size_t)width * height;
+    m_alias_probas.resize(n);
+    m_alias_alias.resize(n);
+    m_alias_probas.upload_data(alias_probas);
+    m_alias_alias.upload_data(alias_alias);
+    w.envmap = m_envmap;
+    w.envmap_width = (unsigned)width;
+    w.envmap_height = (unsigned)height;
+    w.envmap_total_sum = total_sum;
+    w.alias_table_probas = m_alias_probas.get_device_pointer();
+    w.alias_table_alias = m_alias_alias.get_device_pointer();
+    w.ambient_light_type = AMBIENT_ENVMAP;
+}
+
+void GPURenderer::set_camera(const HIPRTCamera& camera)
+{
+    m_camera = camera;
+    m_render_data.current_camera = camera;
+    m_render_data.prev_camera = camera;
+}
+
+void GPURenderer::set_tile(const b200pt_tile* tile)
+{
+    m_has_tile = tile != nullptr;
+    if (tile) m_tile = *tile;
+}
+
+void GPURenderer::resize(int width, int height)
+{
+    synchronize_kernel();
+    m_res = {width, height};
+    size_t n = (size_t)width * height;
+    m_pixels.resize(n); m_pixels.memset_zero();
+    m_pixel_active.resize(n); m_pixel_active.memset_zero();
+    m_denoiser_albedo.resize(n); m_denoiser_albedo.memset_zero();
+    m_denoiser_normals.resize(n); m_denoiser_normals.memset_zero();
+    m_g_buffer.resize(n);
+    reset();
+}
+
+void GPURenderer::reset()
+{
+    m_render_data.render_settings.sample_number = 0;
+    m_render_data.render_settings.denoiser_AOV_accumulation_counter = 0;
+    m_render_data.render_settings.need_to_reset = 1;
+    m_render_data.random_seed = 42;
+    m_rng = Xorshift32Generator();
+    m_restir_odd_frame = false;
+}
+
+void GPURenderer::synchronize_kernel() { check(b200pt_stream_sync(m_ctx, nullptr), "b200pt_stream_sync"); }
+
+void GPURenderer::update()
+{
+    HIPRTRenderSettings& s = m_render_data.render_settings;
+    size_t n = (size_t)m_res.x * m_res.y;
+
+    // ReSTIRDIRenderPass::update (ReSTIRDIRenderPass.cpp:266-304): reservoirs exist only while ReSTIR DI is the strategy
+    bool restir = m_options.direct_light_sampling_strategy == 5;
+    if (restir && m_restir_initial.get_element_count() != n)
+    {
+        std::vector<ReSTIRDIReservoir> empty(n);
+        m_restir_initial.upload_data(empty);
+        m_restir_spatial_1.upload_data(empty);
+        m_restir_spatial_2.upload_data(empty);
+        size_t presampled = (size_t)s.restir_di_settings.light_presampling.number_of_subsets * s.restir_di_settings.light_presampling.subset_size;
+        m_restir_presampled_lights.resize(presampled);
+        m_restir_presampled_lights.memset_zero();
+    }
+    else if (!restir && m_restir_initial.get_element_count() != 0)
+    {
+        m_restir_initial.free(); m_restir_spatial_1.free(); m_restir_spatial_2.free(); m_restir_presampled_lights.free();
+    }
+
+    // internal_update_clear_device_status_buffers (GPURenderer.cpp:275-283)
+    m_still_one_ray_active.memset_zero();
+    m_stop_noise_threshold_count.memset_zero();
+
+    // internal_update_prev_frame_g_buffer (:291-317)
+    bool need_prev = restir && s.restir_di_settings.temporal_pass.do_temporal_reuse_pass;
+    if (need_prev && m_g_buffer_prev.camera_ray_hit.get_element_count() != n)
+        m_g_buffer_prev.resize(n);
+    else if (!need_prev && m_g_buffer_prev.camera_ray_hit.get_element_count() != 0)
+        m_g_buffer_prev.resize(0);
+
+    // internal_update_adaptive_sampling_buffers (:319-354)
+    bool adaptive = (s.stop_pixel_noise_threshold > 0.0f || s.enable_adaptive_sampling) && s.accumulate;
+    if (adaptive && m_pixel_sample_count.get_element_count() != n)
+    {
+        m_pixel_sample_count.resize(n); m_pixel_sample_count.memset_zero();
+        m_pixel_converged_sample_count.resize(n); m_pixel_converged_sample_count.memset_zero();
+        m_pixel_squared_luminance.resize(n); m_pixel_squared_luminance.memset_zero();
+    }
+    else if (!adaptive && m_pixel_sample_count.get_element_count() != 0)
+    {
+        m_pixel_sample_count.free(); m_pixel_converged_sample_count.free(); m_pixel_squared_luminance.free();
+    }
+
+    update_render_data();
+
+    s.do_update_status_buffers = 0;
+    if (!s.accumulate)
+        s.sample_number = 0;
+}
+
+void GPURenderer::update_render_data()
+{
+    // GPURenderer::update_render_data (GPURenderer.cpp:980-1039): re-point every device pointer
+    HIPRTRenderData& rd = m_render_data;
+    rd.buffers.pixels = m_pixels.get_device_pointer();
+    rd.aux_buffers.pixel_active = m_pixel_active.get_device_pointer();
+    rd.aux_buffers.denoiser_albedo = m_denoiser_albedo.get_device_pointer();
+    rd.aux_buffers.denoiser_normals = m_denoiser_normals.get_device_pointer();
+    rd.aux_buffers.pixel_sample_count = m_pixel_sample_count.get_device_pointer();
+    rd.aux_buffers.pixel_converged_sample_count = m_pixel_converged_sample_count.get_device_pointer();
+    rd.aux_buffers.pixel_squared_luminance = m_pixel_squared_luminance.get_device_pointer();
+    rd.aux_buffers.still_one_ray_active = m_still_one_ray_active.get_device_pointer();
+    rd.aux_buffers.stop_noise_threshold_converged_count = m_stop_noise_threshold_count.get_device_pointer();
+    rd.aux_buffers.restir_reservoir_buffer_1 = m_restir_initial.get_device_pointer();
+    rd.aux_buffers.restir_reservoir_buffer_2 = m_restir_spatial_1.get_device_pointer();
+    rd.aux_buffers.restir_reservoir_buffer_3 = m_restir_spatial_2.get_device_pointer();
+    rd.g_buffer = m_g_buffer.view();
+    rd.g_buffer_prev_frame = m_g_buffer_prev.view();
+    ReSTIRDISettings& rs = rd.render_settings.restir_di_settings;
+    rs.light_presampling.light_samples = m_restir_presampled_lights.get_device_pointer();
+    rs.initial_candidates.output_reservoirs = m_restir_initial.get_device_pointer();
+    if (rs.restir_output_reservoirs == nullptr)
+        rs.restir_output_reservoirs = m_restir_spatial_1.get_device_pointer();
+}
+
+void GPURenderer::render()
+{
+    HIPRTRenderSettings& s = m_render_data.render_settings;
+    check(b200pt_event_record(m_ctx, m_frame_start, nullptr), "b200pt_event_record");
+    for (int i = 1; i <= s.samples_per_frame; i++)
+    {
+        m_render_data.prev_camera = m_render_data.current_camera;
+        m_render_data.current_camera = m_camera;
+
+        if (seed_schedule == SeedSchedule::CPU)
+            s.do_update_status_buffers = 1;                         // CPURenderer.cpp:273
+        else if (i == s.samples_per_frame)
+            s.do_update_status_buffers = 1;                         // GPURenderer.cpp:430-434
+
+        launch_camera_rays();
+        launch_ReSTIR_DI();
+        launch_path_tracing();
+
+        if (seed_schedule == SeedSchedule::CPU)
+        {
+            if (s.accumulate)
+                s.sample_number++;
+            m_render_data.random_seed = m_rng.xorshift32();          // CPURenderer.cpp:284-286
+        }
+        else
+        {
+            s.sample_number++;
+            s.denoiser_AOV_accumulation_counter++;
+        }
+        s.need_to_reset = 0;
+        s.restir_di_settings.temporal_pass.temporal_buffer_clear_requested = 0;
+    }
+    check(b200pt_event_record(m_ctx, m_frame_stop, nullptr), "b200pt_event_record");
+}
+
+void GPURenderer::launch_camera_rays()
+{
+    if (seed_schedule == SeedSchedule::GPU)
+        m_render_data.random_seed = m_rng.xorshift32();
+    check(b200pt_launch_CameraRays(m_ctx, &m_render_data, m_res, m_has_tile ? &m_tile : nullptr, nullptr), "b200pt_launch_CameraRays");
+}
+
+void GPURenderer::launch_path_tracing()
+{
+    if (seed_schedule == SeedSchedule::GPU)
+        m_render_data.random_seed = m_rng.xorshift32();
+    check(b200pt_launch_FullPathTracer(m_ctx, &m_render_data, m_res, m_has_tile ? &m_tile : nullptr, nullptr), "b200pt_launch_FullPathTracer");
+}
+
+void GPURenderer::launch_ReSTIR_DI()
+{
+    if (m_options.direct_light_sampling_strategy != 5)
+        return;
+    throw std::runtime_error("ReSTIR DI render pass is not built yet");
+}
+} // namespace b200pt_host

@@ -1,0 +1,59 @@
+/*
+ * b200pt_host.h -- C handle API over b200pt_host::GPURenderer (hiprt-path-tracer_b200/host/GPURenderer.h), the C++
+ * re-hosting of the reference's GPURenderer launch loop (src/Renderer/GPURenderer.cpp:236-486) on top of b200pt.h.
+ * It exists so that non-C++ callers (the Python parity tests, bench.py) drive exactly the same host code a C++
+ * integrator would; it adds no functionality of its own. Every function returns 0 or a negative b200pt_error and
+ * sets b200pt_host_last_error().
+ */
+#ifndef B200PT_HOST_H
+#define B200PT_HOST_H
+
+#include "b200pt.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200pt_renderer b200pt_renderer;
+
+B200PT_API const char* b200pt_host_last_error(void);
+B200PT_API int b200pt_renderer_create(b200pt_ctx* ctx, b200pt_renderer** out);
+B200PT_API int b200pt_renderer_destroy(b200pt_renderer* r);
+/* seed_schedule: 0 = GPU (fresh seed per launch, GPURenderer.cpp:466-486), 1 = CPU (CPURenderer.cpp:264-296) */
+B200PT_API int b200pt_renderer_set_seed_schedule(b200pt_renderer* r, int seed_schedule);
+B200PT_API int b200pt_renderer_set_kernel_options(b200pt_renderer* r, const b200pt_options* options);
+B200PT_API int b200pt_renderer_set_brdf_luts(b200pt_renderer* r, const float* sheen_ltc, const float* conductor, const float* glossy,
+                                             const float* glass, const float* glass_inverse, const float* thin_glass);
+B200PT_API int b200pt_renderer_add_texture(b200pt_renderer* r, const unsigned char* texels, int width, int height, int channels);
+B200PT_API int b200pt_renderer_set_scene(b200pt_renderer* r, const float* vertices, int vertex_count, const int* triangle_indices, int triangle_count,
+                                         const float* vertex_normals, const unsigned char* has_vertex_normals, const float* texcoords,
+                                         const int* material_indices, const RendererMaterial* materials, int material_count,
+                                         const int* emissive_triangle_indices, int emissive_triangle_count);
+B200PT_API int b200pt_renderer_set_envmap(b200pt_renderer* r, const float* texels, int width, int height, int channels,
+                                          const float* alias_probas, const int* alias_alias, float total_sum);
+B200PT_API int b200pt_renderer_set_camera(b200pt_renderer* r, const HIPRTCamera* camera);
+B200PT_API int b200pt_renderer_resize(b200pt_renderer* r, int width, int height);
+B200PT_API int b200pt_renderer_set_tile(b200pt_renderer* r, const b200pt_tile* tile);
+B200PT_API int b200pt_renderer_reset(b200pt_renderer* r);
+/* Host-side structs the caller may edit between frames (copied by value into each launch) */
+B200PT_API HIPRTRenderSettings* b200pt_renderer_render_settings(b200pt_renderer* r);
+B200PT_API WorldSettings* b200pt_renderer_world_settings(b200pt_renderer* r);
+B200PT_API BRDFsData* b200pt_renderer_bsdfs_data(b200pt_renderer* r);
+B200PT_API HIPRTRenderData* b200pt_renderer_render_data(b200pt_renderer* r);
+B200PT_API b200pt_bvh* b200pt_renderer_bvh(b200pt_renderer* r);
+/* update() + render() of one frame = render_settings.samples_per_frame samples; asynchronous */
+B200PT_API int b200pt_renderer_render_frame(b200pt_renderer* r);
+B200PT_API int b200pt_renderer_synchronize(b200pt_renderer* r);
+B200PT_API int b200pt_renderer_last_frame_ms(b200pt_renderer* r, float* out_ms);
+/* which: 0 pixels(3 f32) 1 first_hit_prim_index(i32) 2 shading_normals 3 geometric_normals 4 view_directions 5 first_hits
+ *        6 camera_ray_hit(u8) 7 materials(256 B) 8 ray_volume_states(36 B) 9 pixel_active(u8) 10 pixel_sample_count(i32)
+ *        11 pixel_squared_luminance(f32) 12 pixel_converged_sample_count(i32) 13 denoiser_albedo 14 denoiser_normals
+ *        15 restir output reservoirs(36 B) 16 restir initial candidates 17 presampled lights(48 B)
+ * Returns the number of bytes copied, or the required size negated if capacity is too small. */
+B200PT_API long long b200pt_renderer_download(b200pt_renderer* r, int which, void* out_host, long long capacity_bytes);
+B200PT_API void* b200pt_renderer_device_pointer(b200pt_renderer* r, int which);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200PT_HOST_H */
