@@ -1,0 +1,88 @@
+"""ctypes binding of libb200pt.so (include/b200pt.h) and libb200pt_host.so (include/b200pt_host.h).
+
+There is no fallback of any kind: if the libraries are missing, or no CUDA device is present when a context is
+created, an exception is raised."""
+import ctypes as C
+import os
+
+from . import structs as S
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libb200pt.so")
+HOST_LIB_PATH = os.path.join(HERE, "libb200pt_host.so")
+
+
+class B200ptError(RuntimeError):
+    pass
+
+
+_lib = None
+_host = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise B200ptError(f"{LIB_PATH} is missing: run `python __graft_entry__.py build` (no CPU fallback exists)")
+        _lib = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
+        _lib.b200pt_last_error.restype = C.c_char_p
+        _lib.b200pt_version.restype = C.c_char_p
+        _lib.b200pt_bvh_device_handle.restype = C.c_void_p
+        _lib.b200pt_bvh_device_handle.argtypes = [C.c_void_p]
+    return _lib
+
+
+def host():
+    global _host
+    if _host is None:
+        lib()
+        if not os.path.exists(HOST_LIB_PATH):
+            raise B200ptError(f"{HOST_LIB_PATH} is missing: run `python __graft_entry__.py build`")
+        _host = C.CDLL(HOST_LIB_PATH)
+        _host.b200pt_host_last_error.restype = C.c_char_p
+        for name, res in (("b200pt_renderer_render_settings", S.HIPRTRenderSettings), ("b200pt_renderer_world_settings", S.WorldSettings),
+                          ("b200pt_renderer_bsdfs_data", S.BRDFsData), ("b200pt_renderer_render_data", S.HIPRTRenderData)):
+            getattr(_host, name).restype = C.POINTER(res)
+            getattr(_host, name).argtypes = [C.c_void_p]
+        _host.b200pt_renderer_bvh.restype = C.c_void_p
+        _host.b200pt_renderer_bvh.argtypes = [C.c_void_p]
+        _host.b200pt_renderer_device_pointer.restype = C.c_void_p
+        _host.b200pt_renderer_device_pointer.argtypes = [C.c_void_p, C.c_int]
+        _host.b200pt_renderer_download.restype = C.c_longlong
+        _host.b200pt_renderer_download.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_longlong]
+    return _host
+
+
+def check(code, what=""):
+    if code != 0:
+        msg = lib().b200pt_last_error().decode(errors="replace")
+        raise B200ptError(f"{what} failed ({code}): {msg}")
+
+
+def check_host(code, what=""):
+    if code != 0:
+        msg = host().b200pt_host_last_error().decode(errors="replace")
+        raise B200ptError(f"{what} failed ({code}): {msg}")
+
+
+# Every symbol include/b200pt.h and include/b200pt_host.h declare (checked by tests/test_capi_symbols.py)
+API_SYMBOLS = [
+    "b200pt_device_count", "b200pt_ctx_create", "b200pt_ctx_destroy", "b200pt_ctx_make_current", "b200pt_last_error", "b200pt_version",
+    "b200pt_malloc", "b200pt_free", "b200pt_memset", "b200pt_memcpy_h2d", "b200pt_memcpy_d2h", "b200pt_memcpy_d2d",
+    "b200pt_host_alloc_pinned", "b200pt_host_free_pinned", "b200pt_stream_create", "b200pt_stream_destroy", "b200pt_stream_query",
+    "b200pt_stream_sync", "b200pt_event_create", "b200pt_event_destroy", "b200pt_event_record", "b200pt_event_elapsed_ms",
+    "b200pt_tex2d_create", "b200pt_tex3d_create", "b200pt_tex_destroy", "b200pt_tex2d_array_create", "b200pt_bvh_build",
+    "b200pt_bvh_destroy", "b200pt_bvh_device_handle", "b200pt_bvh_info", "b200pt_kernel_variant_select", "b200pt_launch_CameraRays",
+    "b200pt_launch_FullPathTracer", "b200pt_launch_ReSTIR_DI_LightsPresampling", "b200pt_launch_ReSTIR_DI_InitialCandidates",
+    "b200pt_launch_ReSTIR_DI_SpatiotemporalReuse", "b200pt_trace_closest", "b200pt_trace_shadow", "b200pt_counters_enable",
+    "b200pt_counters_read",
+]
+HOST_API_SYMBOLS = [
+    "b200pt_host_last_error", "b200pt_renderer_create", "b200pt_renderer_destroy", "b200pt_renderer_set_seed_schedule",
+    "b200pt_renderer_set_kernel_options", "b200pt_renderer_set_brdf_luts", "b200pt_renderer_add_texture", "b200pt_renderer_set_scene",
+    "b200pt_renderer_set_envmap", "b200pt_renderer_set_camera", "b200pt_renderer_resize", "b200pt_renderer_set_tile",
+    "b200pt_renderer_reset", "b200pt_renderer_render_settings", "b200pt_renderer_world_settings", "b200pt_renderer_bsdfs_data",
+    "b200pt_renderer_render_data", "b200pt_renderer_bvh", "b200pt_renderer_render_frame", "b200pt_renderer_synchronize",
+    "b200pt_renderer_last_frame_ms", "b200pt_renderer_download", "b200pt_renderer_device_pointer",
+]
