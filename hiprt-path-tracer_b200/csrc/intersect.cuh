@@ -23,7 +23,7 @@ struct RayPayload
     RGB throughput;
     RGB ray_color;
     int next_ray_state;   // 0 BOUNCE, 1 MISSED
-    Material material;
+    alignas(16) Material material;   // moved with 16-byte vector loads/stores to and from the G-buffer
     RayVolumeState volume_state;
 };
 

@@ -164,7 +164,7 @@ PT_DEV void camera_rays_pixel(const HIPRTRenderData& rd, int2 res, uint32_t x, u
         st3(rd.g_buffer_prev_frame.geometric_normals, pixel_index, ld3_rw(rd.g_buffer.geometric_normals, pixel_index));
         st3(rd.g_buffer_prev_frame.shading_normals, pixel_index, ld3_rw(rd.g_buffer.shading_normals, pixel_index));
         {
-            Material m;
+            alignas(16) Material m;
             load_material(m, rd.g_buffer.materials + pixel_index);
             store_material(rd.g_buffer_prev_frame.materials + pixel_index, m);
         }

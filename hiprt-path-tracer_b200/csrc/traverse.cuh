@@ -32,7 +32,18 @@ struct Hit
 #define PT_COUNT(x)
 #endif
 
-PT_DEV uint32_t sign_extend_s8x4(uint32_t x) { return __byte_perm(x, 0, 0xba98); }
+// Replicates the sign bit of each byte over the byte. PRMT with selector nibbles 8..b (bit 3 = "replicate sign");
+// __byte_perm() masks its selector to 3 bits, hence the inline PTX.
+PT_DEV uint32_t sign_extend_s8x4(uint32_t x)
+{
+#ifdef __CUDA_ARCH__
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(x), "r"(0u), "r"(0x0000ba98u));
+    return r;
+#else
+    return ((x & 0x80u) ? 0xFFu : 0u) | ((x & 0x8000u) ? 0xFF00u : 0u) | ((x & 0x800000u) ? 0xFF0000u : 0u) | ((x & 0x80000000u) ? 0xFF000000u : 0u);
+#endif
+}
 PT_DEV float byte_to_float(uint32_t word, int byte) { return (float)((word >> (8 * byte)) & 0xFFu); }
 
 // Triangle::intersect of the reference, bit for bit. Returns true when the reference would report a hit.
