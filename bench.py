@@ -1,0 +1,289 @@
+#!/usr/bin/env python3
+"""Benchmark of the render hot path (CameraRays -> FullPathTracer) on N B200s of one node.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cornell]
+
+A "step" is one sample pass of the whole 1080p frame per GPU (two kernel launches: CameraRays, FullPathTracer).
+Metric (BASELINE.json): Mrays/s = BVH queries (trace_ray iterations + shadow rays + shadow-light rays)
+per second, whole job. Rays are counted by the counting build of the SAME kernels on the SAME seeds in an untimed
+pass; the timed passes run the timing build. N > 1: every rank renders its own sample passes of the full frame
+(sample-pass sharding, weak scaling) and the accumulation buffers are summed with one NCCL all-reduce per K steps
+inside the timed region. `--impl reference` times the reference's own CPU kernels (oracle/_ref) on the host cores.
+Prints ONE JSON line."""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clocks and throttle reasons with nvidia-smi DURING the timed region."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu_index):
+        super().__init__(daemon=True)
+        self.gpu_index, self.samples, self.stop_flag = gpu_index, [], threading.Event()
+
+    def run(self):
+        while not self.stop_flag.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.gpu_index)],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self.stop_flag.wait(0.2)
+
+    def summary(self):
+        self.stop_flag.set()
+        self.join(timeout=6)
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = sorted(int(s[0]) for s in self.samples if s[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for s in self.samples for n, v in zip(names, s[2:6]) if v.lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": int(self.samples[0][1]) if self.samples[0][1].isdigit() else None, "reasons": reasons}
+
+
+def measured_hbm_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json, copy bandwidth)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def run_reference(args, cfg, pt):
+    """Reference arm: the reference's own CPU implementation of the path (oracle/_ref = its unmodified kernels)."""
+    from oracle import ref
+    wl = importlib.import_module("hiprt-path-tracer_b200.workloads")
+    r = wl.setup_oracle(ref, pt.structs, cfg)
+    cores = r.lib.ref_num_threads()
+    for _ in range(args.warmup):
+        r.render(1)
+    r.ray_count(reset=True)
+    t0 = time.time()
+    for _ in range(args.steps):
+        r.render(1)
+    dt = time.time() - t0
+    rays = r.ray_count()
+    value = rays / dt / 1e6
+    sample = f"{args.steps} full sample passes of {cfg['name']} (one step = 1 spp of the whole frame), OpenMP over rows"
+    return {
+        "impl": "reference", "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": cfg["name"]}, "samples_per_px_per_s": args.steps / dt,
+        "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": "reference", "sample": sample},
+        "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+
+
+def run_ours(args, cfg, pt):
+    import ctypes as C
+    import numpy as np
+    import torch
+
+    wl = importlib.import_module("hiprt-path-tracer_b200.workloads")
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    W, H = cfg["width"], cfg["height"]
+    ctx = pt.Context(local_rank)
+    g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="gpu")
+    lib = ctx.lib
+    bvh_info = ctx.bvh_info(g.bvh)
+
+    def restart():
+        # Sample-pass sharding: rank r owns the sample numbers r*2^20 + k; the per-pixel streams are seeded by
+        # (pixel, sample_number, random_seed) (FullPathTracer.h:124-129), so the ranks' samples are independent.
+        g.reset()
+        g.resize(W, H)
+        wl.apply_settings(g.render_settings, cfg["settings"])
+        if rank > 0:
+            g.render_settings.sample_number = rank << 20
+            g.render_settings.need_to_reset = 0
+
+    # ---- 1. counting pass: the same frames as the timed pass, counting build ----
+    restart()
+    ctx.counters_enable(True)
+    for _ in range(args.warmup):
+        g.render_frame()
+    g.synchronize()
+    ctx.counters_read(True)
+    for _ in range(args.steps):
+        g.render_frame()
+    g.synchronize()
+    total = ctx.counters_read(True)
+    res = pt.structs.Int2(W, H)
+    pt._capi.check(lib.b200pt_launch_CameraRays(ctx.handle, C.byref(g.render_data), res, None, None), "b200pt_launch_CameraRays")
+    ctx.sync()
+    cam = ctx.counters_read(True)
+    ctx.counters_enable(False)
+    rays_per_step = total["rays"] / args.steps
+    fpt = {k: total[k] / args.steps - cam[k] for k in total}
+
+    # ---- 2. timed pass: timing build, CUDA events on the launching stream ----
+    restart()
+    for _ in range(max(args.warmup, 3)):
+        g.render_frame()
+    g.synchronize()
+    ev0, ev1 = C.c_void_p(), C.c_void_p()
+    lib.b200pt_event_create(ctx.handle, C.byref(ev0))
+    lib.b200pt_event_create(ctx.handle, C.byref(ev1))
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    if dist:
+        dist.barrier()
+    torch.cuda.synchronize()
+    kernel_ms = {"CameraRays": 0.0, "FullPathTracer": 0.0}
+    lib.b200pt_event_record(ctx.handle, ev0, None)
+    for _ in range(args.steps):
+        g.render_frame()
+        g.synchronize()
+        for k in kernel_ms:
+            kernel_ms[k] += g.last_kernel_ms(k)
+    lib.b200pt_event_record(ctx.handle, ev1, None)
+    ctx.sync()
+    ms = C.c_float()
+    lib.b200pt_event_elapsed_ms(ctx.handle, ev0, ev1, C.byref(ms))
+    elapsed_ms = ms.value
+    reduce_ms = 0.0
+    if dist:
+        # accumulation buffer (sum of samples, RenderData.h:34-36) summed over ranks: one NCCL all-reduce per K steps
+        class _Dev:
+            __cuda_array_interface__ = {"shape": (H, W, 3), "typestr": "<f4", "data": (g.device_pointer("pixels"), False), "version": 3}
+        pixels = torch.as_tensor(_Dev(), device=torch.device("cuda", local_rank))
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record()
+        dist.all_reduce(pixels)
+        t1.record()
+        torch.cuda.synchronize()
+        reduce_ms = t0.elapsed_time(t1)
+        elapsed_ms += reduce_ms
+        dist.barrier()
+    torch.cuda.synchronize()
+    clocks = sampler.summary() if sampler else None
+
+    stats = torch.tensor([elapsed_ms, rays_per_step * args.steps], dtype=torch.float64, device=torch.device("cuda", local_rank))
+    if dist:
+        tmax = stats.clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = stats.clone()
+        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        elapsed_ms, total_rays = float(tmax[0]), float(tsum[1])
+    else:
+        total_rays = rays_per_step * args.steps
+
+    # ---- 3. end to end through the host API with HOST buffers: camera in, accumulated frame out, every step ----
+    restart()
+    pinned = C.c_void_p()
+    lib.b200pt_host_alloc_pinned(ctx.handle, C.c_size_t(W * H * 12), C.byref(pinned))
+    for _ in range(3):
+        g.render_frame()
+    g.synchronize()
+    lib.b200pt_event_record(ctx.handle, ev0, None)
+    for _ in range(args.steps):
+        g.set_camera(cfg["camera"])                       # host struct -> kernel arguments (H2D with each launch)
+        g.render_frame()
+        lib.b200pt_memcpy_d2h(ctx.handle, pinned, C.c_void_p(g.device_pointer("pixels")), C.c_size_t(W * H * 12), None)
+        g.synchronize()
+    lib.b200pt_event_record(ctx.handle, ev1, None)
+    ctx.sync()
+    lib.b200pt_event_elapsed_ms(ctx.handle, ev0, ev1, C.byref(ms))
+    e2e_ms = ms.value
+    e2e_stats = torch.tensor([e2e_ms], dtype=torch.float64, device=torch.device("cuda", local_rank))
+    if dist:
+        dist.all_reduce(e2e_stats, op=dist.ReduceOp.MAX)
+    e2e_ms = float(e2e_stats[0])
+    lib.b200pt_host_free_pinned(ctx.handle, pinned)
+
+    if rank != 0:
+        if dist:
+            dist.destroy_process_group()
+        return None
+
+    value = total_rays / (elapsed_ms * 1e-3) / 1e6
+    peak, peak_kind = measured_hbm_peak()
+    fpt_ms = kernel_ms["FullPathTracer"] / args.steps
+    # algorithmic bytes per ray (SURVEY.md 8d / DESIGN.md): 32 B ray in + 16 B hit out + 80 B per node + 48 B per triangle
+    fpt_bytes = 48.0 * fpt["rays"] + 80.0 * fpt["nodes"] + 48.0 * fpt["triangles"]
+    achieved = fpt_bytes / (fpt_ms * 1e-3) / 1e9
+    out = {
+        "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": cfg["name"], "parallelism": f"sample-pass sharding x{world}, scene+BVH replicated" if world > 1 else "single GPU",
+                   "l2": "inputs larger than L2: the per-step G-buffer round trip is 345 B/px = 715 MB at 1080p (L2 = 126 MB)",
+                   "bvh": bvh_info, "rays_per_step_per_gpu": rays_per_step, "allreduce_ms": reduce_ms},
+        "samples_per_px_per_s": world * args.steps / (elapsed_ms * 1e-3),
+        "gpu_launches": 2 * args.steps,
+        "clocks": clocks,
+        "e2e": {"value": total_rays / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 2 * 1328 + 196, "d2h_bytes_per_step": W * H * 12},
+        "roofline": {"bound": "hbm", "kernel": "FullPathTracer", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "peak_source": peak_kind, "ms_per_launch": fpt_ms, "camera_rays_ms_per_launch": kernel_ms["CameraRays"] / args.steps,
+                     "rays_per_launch": fpt["rays"], "nodes_per_ray": fpt["nodes"] / max(1.0, fpt["rays"]), "triangles_per_ray": fpt["triangles"] / max(1.0, fpt["rays"])},
+    }
+
+    # ---- 4. CPU baseline: the reference's own CPU kernels on a bounded sample of the same workload (rank 0, N = 1) ----
+    if world == 1 and not args.no_cpu_baseline:
+        from oracle import ref
+        r = wl.setup_oracle(ref, pt.structs, cfg)
+        r.render(1)
+        r.ray_count(reset=True)
+        t0 = time.time()
+        r.render(1)
+        t1 = time.time() - t0
+        n = int(min(16, max(1, 12.0 / max(t1, 1e-3))))
+        r.ray_count(reset=True)
+        t0 = time.time()
+        r.render(n)
+        dt = time.time() - t0
+        out["cpu_baseline"] = {"value": r.ray_count() / dt / 1e6, "unit": "Mrays/s", "cores": r.lib.ref_num_threads(), "kind": "reference",
+                               "sample": f"{n} sample passes of {cfg['name']} with the reference's CPU kernels (oracle/_ref), OpenMP over rows", "samples_per_px_per_s": n / dt}
+    if dist:
+        dist.destroy_process_group()
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=16)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cornell")
+    ap.add_argument("--width", type=int, default=1920)
+    ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    pt = importlib.import_module("hiprt-path-tracer_b200")
+    wl = importlib.import_module("hiprt-path-tracer_b200.workloads")
+    cfg = getattr(wl, args.workload)(args.width, args.height)
+
+    if args.impl == "reference":
+        if int(os.environ.get("RANK", 0)) != 0:
+            return
+        args.steps = min(args.steps, 8)
+        print(json.dumps(run_reference(args, cfg, pt)))
+        return
+    out = run_ours(args, cfg, pt)
+    if out is not None:
+        print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()

@@ -84,5 +84,5 @@ HOST_API_SYMBOLS = [
     "b200pt_renderer_set_envmap", "b200pt_renderer_set_camera", "b200pt_renderer_resize", "b200pt_renderer_set_tile",
     "b200pt_renderer_reset", "b200pt_renderer_render_settings", "b200pt_renderer_world_settings", "b200pt_renderer_bsdfs_data",
     "b200pt_renderer_render_data", "b200pt_renderer_bvh", "b200pt_renderer_render_frame", "b200pt_renderer_synchronize",
-    "b200pt_renderer_last_frame_ms", "b200pt_renderer_download", "b200pt_renderer_device_pointer",
+    "b200pt_renderer_last_frame_ms", "b200pt_renderer_last_kernel_ms", "b200pt_renderer_download", "b200pt_renderer_device_pointer",
 ]

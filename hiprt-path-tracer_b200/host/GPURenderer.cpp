@@ -57,6 +57,8 @@ GPURenderer::GPURenderer(b200pt_ctx* ctx) : m_ctx(ctx)
     m_stop_noise_threshold_count.resize(1);
     check(b200pt_event_create(ctx, &m_frame_start), "b200pt_event_create");
     check(b200pt_event_create(ctx, &m_frame_stop), "b200pt_event_create");
+    for (b200pt_event& e : m_kernel_events)
+        check(b200pt_event_create(ctx, &e), "b200pt_event_create");
     check(b200pt_kernel_variant_select(ctx, &m_options), "b200pt_kernel_variant_select");
 }
 
@@ -70,6 +72,7 @@ GPURenderer::~GPURenderer()
     if (m_envmap) b200pt_tex_destroy(m_ctx, m_envmap);
     b200pt_event_destroy(m_ctx, m_frame_start);
     b200pt_event_destroy(m_ctx, m_frame_stop);
+    for (b200pt_event e : m_kernel_events) b200pt_event_destroy(m_ctx, e);
 }
 
 void GPURenderer::set_kernel_options(const b200pt_options& options)
@@ -307,9 +310,16 @@ void GPURenderer::render()
         else if (i == s.samples_per_frame)
             s.do_update_status_buffers = 1;                         // GPURenderer.cpp:430-434
 
+        m_time_kernels = i == s.samples_per_frame;
+        if (m_time_kernels) check(b200pt_event_record(m_ctx, m_kernel_events[0], nullptr), "b200pt_event_record");
         launch_camera_rays();
+        if (m_time_kernels) check(b200pt_event_record(m_ctx, m_kernel_events[1], nullptr), "b200pt_event_record");
+        if (m_time_kernels) check(b200pt_event_record(m_ctx, m_kernel_events[4], nullptr), "b200pt_event_record");
         launch_ReSTIR_DI();
+        if (m_time_kernels) check(b200pt_event_record(m_ctx, m_kernel_events[5], nullptr), "b200pt_event_record");
+        if (m_time_kernels) check(b200pt_event_record(m_ctx, m_kernel_events[2], nullptr), "b200pt_event_record");
         launch_path_tracing();
+        if (m_time_kernels) check(b200pt_event_record(m_ctx, m_kernel_events[3], nullptr), "b200pt_event_record");
 
         if (seed_schedule == SeedSchedule::CPU)
         {

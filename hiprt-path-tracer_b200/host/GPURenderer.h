@@ -159,6 +159,14 @@ public:
         check(b200pt_event_elapsed_ms(m_ctx, m_frame_start, m_frame_stop, &m_last_frame_ms), "b200pt_event_elapsed_ms");
         return m_last_frame_ms;
     }
+    // Per-kernel device times of the LAST sample of the last frame (the reference keeps a start/stop event pair per
+    // kernel, src/Compiler/GPUKernel.cpp:202-211,233-245). which: 0 CameraRays, 1 FullPathTracer, 2 ReSTIR DI passes
+    float last_kernel_ms(int which)
+    {
+        float ms = 0.0f;
+        check(b200pt_event_elapsed_ms(m_ctx, m_kernel_events[2 * which], m_kernel_events[2 * which + 1], &ms), "b200pt_event_elapsed_ms");
+        return ms;
+    }
     int width() const { return m_res.x; }
     int height() const { return m_res.y; }
 
@@ -188,6 +196,8 @@ private:
     HIPRTCamera m_camera;
     bool m_restir_odd_frame = false;
     b200pt_event m_frame_start = nullptr, m_frame_stop = nullptr;
+    b200pt_event m_kernel_events[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    bool m_time_kernels = false;
     float m_last_frame_ms = 0.0f;
 
     DeviceBuffer<ColorRGB32F> m_pixels;

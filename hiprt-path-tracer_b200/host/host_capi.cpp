@@ -136,6 +136,12 @@ int b200pt_renderer_synchronize(b200pt_renderer* r) { return guarded([&] { r->re
 
 int b200pt_renderer_last_frame_ms(b200pt_renderer* r, float* out_ms) { return guarded([&] { *out_ms = r->renderer.last_frame_ms(); }); }
 
+int b200pt_renderer_last_kernel_ms(b200pt_renderer* r, int which, float* out_ms)
+{
+    if (which < 0 || which > 2) return B200PT_ERROR_INVALID_ARGUMENT;
+    return guarded([&] { *out_ms = r->renderer.last_kernel_ms(which); });
+}
+
 void* b200pt_renderer_device_pointer(b200pt_renderer* r, int which)
 {
     GPURenderer& g = r->renderer;

@@ -219,6 +219,15 @@ class GPURenderer:
         _capi.check_host(self.host.b200pt_renderer_last_frame_ms(self.handle, C.byref(ms)), "b200pt_renderer_last_frame_ms")
         return ms.value
 
+    def last_kernel_ms(self, which):
+        ms = C.c_float()
+        idx = {"CameraRays": 0, "FullPathTracer": 1, "ReSTIR_DI": 2}[which]
+        _capi.check_host(self.host.b200pt_renderer_last_kernel_ms(self.handle, C.c_int(idx), C.byref(ms)), "b200pt_renderer_last_kernel_ms")
+        return ms.value
+
+    def device_pointer(self, name):
+        return self.host.b200pt_renderer_device_pointer(self.handle, C.c_int(DOWNLOAD[name][0]))
+
     def download(self, name):
         which, dtype, comps = DOWNLOAD[name]
         n = self.width * self.height

@@ -45,6 +45,8 @@ B200PT_API b200pt_bvh* b200pt_renderer_bvh(b200pt_renderer* r);
 B200PT_API int b200pt_renderer_render_frame(b200pt_renderer* r);
 B200PT_API int b200pt_renderer_synchronize(b200pt_renderer* r);
 B200PT_API int b200pt_renderer_last_frame_ms(b200pt_renderer* r, float* out_ms);
+/* device time of one kernel in the last sample of the last frame; which: 0 CameraRays, 1 FullPathTracer, 2 ReSTIR DI passes */
+B200PT_API int b200pt_renderer_last_kernel_ms(b200pt_renderer* r, int which, float* out_ms);
 /* which: 0 pixels(3 f32) 1 first_hit_prim_index(i32) 2 shading_normals 3 geometric_normals 4 view_directions 5 first_hits
  *        6 camera_ray_hit(u8) 7 materials(256 B) 8 ray_volume_states(36 B) 9 pixel_active(u8) 10 pixel_sample_count(i32)
  *        11 pixel_squared_luminance(f32) 12 pixel_converged_sample_count(i32) 13 denoiser_albedo 14 denoiser_normals

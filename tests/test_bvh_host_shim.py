@@ -1,0 +1,27 @@
+"""BVH8 builder + traversal logic against brute force, compiled for the host with an intrinsics shim (no GPU needed)."""
+import os
+import subprocess
+
+import pytest
+
+ROOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..")
+CSRC = os.path.join(ROOT, "hiprt-path-tracer_b200", "csrc")
+
+
+@pytest.fixture(scope="module")
+def shim_binary(tmp_path_factory):
+    cuda_inc = "/usr/local/cuda/include"
+    if not os.path.exists(os.path.join(cuda_inc, "cuda_runtime.h")):
+        pytest.skip("CUDA headers not installed")
+    out = str(tmp_path_factory.mktemp("shim") / "traverse_host_test")
+    cmd = ["g++", "-std=c++17", "-O1", "-fopenmp", "-I", cuda_inc, "-I", CSRC, "-I", os.path.join(ROOT, "include"),
+           os.path.join(ROOT, "tests", "host_shim", "traverse_host_test.cpp"), os.path.join(CSRC, "bvh8_build.cpp"), "-o", out]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+    return out
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2, 3])
+def test_traversal_equals_brute_force(shim_binary, mode):
+    r = subprocess.run([shim_binary, str(mode)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
