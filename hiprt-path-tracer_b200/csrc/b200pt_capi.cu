@@ -5,6 +5,7 @@
 
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -16,6 +17,9 @@ struct b200pt_ctx
     pt::VariantOptions options = {3, 0, 3, 0};
     bool counting = false;
     pt::TraversalCounters* d_counters = nullptr;
+    int path_mode = pt::WF_SPLIT;
+    pt::WavefrontState wf = {};
+    std::vector<void*> wf_allocations;
 };
 
 struct b200pt_bvh
@@ -123,6 +127,9 @@ int b200pt_ctx_create(int device_index, b200pt_ctx** out_ctx)
     }
     // The megakernel keeps per-thread traversal stacks and a 256-byte material in local memory
     cudaDeviceSetLimit(cudaLimitStackSize, 8192);
+    // B200PT_PATH_MODE=megakernel|fused|split overrides the default shape of FullPathTracer (A/B measurements)
+    if (const char* m = getenv("B200PT_PATH_MODE"))
+        ctx->path_mode = !strcmp(m, "megakernel") ? pt::WF_MEGAKERNEL : !strcmp(m, "fused") ? pt::WF_FUSED : pt::WF_SPLIT;
     *out_ctx = ctx;
     return B200PT_SUCCESS;
 }
@@ -134,6 +141,8 @@ int b200pt_ctx_destroy(b200pt_ctx* ctx)
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->main_stream);
     cudaFree(ctx->d_counters);
+    for (void* p : ctx->wf_allocations)
+        cudaFree(p);
     cudaStreamDestroy(ctx->main_stream);
     delete ctx;
     return B200PT_SUCCESS;

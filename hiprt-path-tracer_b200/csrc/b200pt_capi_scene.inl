@@ -167,7 +167,54 @@ int b200pt_kernel_variant_select(b200pt_ctx* ctx, const b200pt_options* options)
     return B200PT_SUCCESS;
 }
 
-#define LAUNCH_PIXEL_KERNEL(NAME)                                                                                                  \
+// Grows the context's wavefront scratch (wavefront.cuh) to `paths` paths and `bounces` bounces. Reallocation waits for
+// the stream: launches in flight may still use the old arrays.
+static int ensure_wavefront(b200pt_ctx* ctx, uint32_t paths, uint32_t bounces)
+{
+    pt::WavefrontState& wf = ctx->wf;
+    if (paths <= wf.capacity && bounces <= wf.max_bounces)
+        return B200PT_SUCCESS;
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    CUDA_TRY(cudaStreamSynchronize(ctx->main_stream));
+    for (void* p : ctx->wf_allocations)
+        cudaFree(p);
+    ctx->wf_allocations.clear();
+    uint32_t capacity = paths > wf.capacity ? paths : wf.capacity;
+    uint32_t max_bounces = bounces > wf.max_bounces ? bounces : wf.max_bounces;
+    wf = pt::WavefrontState{};
+    auto alloc = [&](size_t bytes) -> void* {
+        void* p = nullptr;
+        if (cudaMalloc(&p, bytes) != cudaSuccess)
+            return nullptr;
+        ctx->wf_allocations.push_back(p);
+        return p;
+    };
+    const size_t n = capacity;
+    float4** f4[] = {&wf.origin_rng, &wf.dir_prim, &wf.throughput, &wf.color, &wf.hit_point, &wf.hit_ns, &wf.hit_ng};
+    bool ok = true;
+    for (float4** a : f4)
+        ok &= (*a = static_cast<float4*>(alloc(n * sizeof(float4)))) != nullptr;
+    ok &= (wf.volume = static_cast<uint32_t*>(alloc(n * 36))) != nullptr;
+    ok &= (wf.materials = alloc(n * 256)) != nullptr;
+    ok &= (wf.ray_queue[0] = static_cast<uint32_t*>(alloc(n * 4))) != nullptr;
+    ok &= (wf.ray_queue[1] = static_cast<uint32_t*>(alloc(n * 4))) != nullptr;
+    ok &= (wf.shade_queue = static_cast<uint32_t*>(alloc(n * 4))) != nullptr;
+    ok &= (wf.counts = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * 2 * (max_bounces + 2)))) != nullptr;
+    if (!ok)
+    {
+        cudaError_t e = cudaGetLastError();
+        for (void* p : ctx->wf_allocations)
+            cudaFree(p);
+        ctx->wf_allocations.clear();
+        wf = pt::WavefrontState{};
+        return cuda_fail(e == cudaSuccess ? cudaErrorMemoryAllocation : e, "wavefront scratch allocation");
+    }
+    wf.capacity = capacity;
+    wf.max_bounces = max_bounces;
+    return B200PT_SUCCESS;
+}
+
+#define LAUNCH_PIXEL_KERNEL(NAME, ...)                                                                                             \
     REQUIRE(ctx != nullptr && render_data != nullptr && res.x > 0 && res.y > 0);                                                   \
     REQUIRE(render_data->geom != nullptr);                                                                                         \
     pt::Tile t = tile_of(tile, res);                                                                                               \
@@ -178,10 +225,10 @@ int b200pt_kernel_variant_select(b200pt_ctx* ctx, const b200pt_options* options)
     {                                                                                                                              \
         HIPRTRenderData copy = *render_data;                                                                                       \
         copy.hiprt_function_table = ctx->d_counters;                                                                               \
-        e = pt::NAME##_c(ctx->options, &copy, make_int2(res.x, res.y), t, stream_of(ctx, stream));                                 \
+        e = pt::NAME##_c(ctx->options, &copy, make_int2(res.x, res.y), t, stream_of(ctx, stream) __VA_ARGS__);                     \
     }                                                                                                                              \
     else                                                                                                                           \
-        e = pt::NAME##_t(ctx->options, render_data, make_int2(res.x, res.y), t, stream_of(ctx, stream));                           \
+        e = pt::NAME##_t(ctx->options, render_data, make_int2(res.x, res.y), t, stream_of(ctx, stream) __VA_ARGS__);               \
     if (e != cudaSuccess)                                                                                                          \
         return cuda_fail(e, #NAME);                                                                                                \
     return B200PT_SUCCESS;
@@ -191,9 +238,28 @@ int b200pt_launch_CameraRays(b200pt_ctx* ctx, const HIPRTRenderData* render_data
     LAUNCH_PIXEL_KERNEL(launch_CameraRays)
 }
 
+int b200pt_set_path_mode(b200pt_ctx* ctx, int mode)
+{
+    REQUIRE(ctx != nullptr && mode >= pt::WF_MEGAKERNEL && mode <= pt::WF_SPLIT);
+    ctx->path_mode = mode;
+    return B200PT_SUCCESS;
+}
+
 int b200pt_launch_FullPathTracer(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream)
 {
-    LAUNCH_PIXEL_KERNEL(launch_FullPathTracer)
+    REQUIRE(ctx != nullptr && render_data != nullptr && res.x > 0 && res.y > 0);
+    if (ctx->path_mode != pt::WF_MEGAKERNEL)
+    {
+        pt::Tile wt = tile_of(tile, res);
+        if (wt.x1 > wt.x0 && wt.y1 > wt.y0)
+        {
+            REQUIRE(render_data->render_settings.nb_bounces >= 0);
+            int rc = ensure_wavefront(ctx, (uint32_t)(wt.x1 - wt.x0) * (uint32_t)(wt.y1 - wt.y0), (uint32_t)render_data->render_settings.nb_bounces);
+            if (rc != B200PT_SUCCESS)
+                return rc;
+        }
+    }
+    LAUNCH_PIXEL_KERNEL(launch_FullPathTracer, , &ctx->wf, ctx->path_mode)
 }
 
 int b200pt_launch_ReSTIR_DI_LightsPresampling(b200pt_ctx* ctx, const LightPresamplingParameters* parameters, b200pt_stream stream)

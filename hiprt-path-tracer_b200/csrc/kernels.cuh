@@ -306,12 +306,12 @@ PT_DEV RGB sample_one_light(const HIPRTRenderData& rd, RayPayload& payload, cons
     return direct / rd.render_settings.number_of_light_samples;
 }
 
-PT_DEV bool sanity_check(const HIPRTRenderData& rd, RayPayload& payload, uint32_t pixel_index)
+PT_DEV bool sanity_check(const HIPRTRenderData& rd, RGB& ray_color, float sampled_wavelength, uint32_t pixel_index)
 {
     bool invalid = false;
-    if (payload.volume_state.sampled_wavelength == 0.0f)
-        invalid |= payload.ray_color.r < 0 || payload.ray_color.g < 0 || payload.ray_color.b < 0;
-    invalid |= payload.ray_color.has_NaN();
+    if (sampled_wavelength == 0.0f)
+        invalid |= ray_color.r < 0 || ray_color.g < 0 || ray_color.b < 0;
+    invalid |= ray_color.has_NaN();
     if (invalid)
     {
         if (rd.render_settings.display_NaNs)
@@ -323,133 +323,95 @@ PT_DEV bool sanity_check(const HIPRTRenderData& rd, RayPayload& payload, uint32_
             st3(rd.buffers.pixels, pixel_index, to_f3(c));
         }
         else
-            payload.ray_color = RGB(0.0f);
+            ray_color = RGB(0.0f);
     }
     return !invalid;
 }
 
+// One path vertex with an intersection (FullPathTracer.h:165-241): NEE + envmap sampling, emission, BSDF sample,
+// russian roulette, throughput update. Returns false when the path ends here. Shared by the megakernel and the
+// wavefront kernels so that both evaluate exactly the same arithmetic in the same RNG order.
 template <int LSS, int ESS, int LATER, int GGX_SAMPLER>
-PT_DEV void full_path_tracer_pixel(const HIPRTRenderData& rd, int2 res, uint32_t x, uint32_t y)
+PT_DEV bool shade_vertex(const HIPRTRenderData& rd, RayPayload& payload, HitInfo& hit, float3& origin, float3& direction, Rng& rng, int2 pixel_coords, int2 res, int bounce)
 {
-    uint32_t pixel_index = x + y * res.x;
-    if (!rd.aux_buffers.pixel_active[pixel_index])
-        return;
-
-    int nb_bounces = rd.render_settings.nb_bounces;
-    if (do_render_low_resolution(rd.render_settings))
-        nb_bounces = mini(3, nb_bounces);
-
-    Rng rng(pixel_seed(rd, pixel_index));
-
-    float squared_luminance_of_samples = 0.0f;
-    RGB denoiser_albedo(0.0f);
-    float3 denoiser_normal = f3(0.0f, 0.0f, 0.0f);
-
-    HitInfo hit;
-    hit.inter_point = ld3_rw(rd.g_buffer.first_hits, pixel_index);
-    hit.geometric_normal = normalize(ld3_rw(rd.g_buffer.geometric_normals, pixel_index));
-    hit.shading_normal = normalize(ld3_rw(rd.g_buffer.shading_normals, pixel_index));
-    hit.primitive_index = rd.g_buffer.first_hit_prim_index[pixel_index];
-
-    float3 origin = f3(0.0f, 0.0f, 0.0f);
-    float3 direction = normalize(-ld3_rw(rd.g_buffer.view_directions, pixel_index));
-    bool intersection_found = rd.g_buffer.camera_ray_hit[pixel_index] == 1;
-
-    RayPayload payload;
-    payload.throughput = RGB(1.0f);
-    payload.ray_color = RGB(0.0f);
-    payload.next_ray_state = 0;
-    load_material(payload.material, rd.g_buffer.materials + pixel_index);
-    copy_volume_state(&payload.volume_state, rd.g_buffer.ray_volume_states + pixel_index);
-
-    for (int bounce = 0; bounce < nb_bounces + 1; bounce++)
+    if (material_is_emissive(payload.material) && dot(-direction, hit.geometric_normal) < 0)
     {
-        if (payload.next_ray_state != 1)
-        {
-            if (bounce > 0)
-                intersection_found = trace_ray(rd, origin, direction, payload, hit, hit.primitive_index, rng);
-
-            if (intersection_found)
-            {
-                if (bounce == 0)
-                {
-                    denoiser_normal += hit.shading_normal;
-                    denoiser_albedo += rgb(payload.material.base_color);
-                }
-
-                if (material_is_emissive(payload.material) && dot(-direction, hit.geometric_normal) < 0)
-                {
-                    hit.geometric_normal = -hit.geometric_normal;
-                    hit.shading_normal = -hit.shading_normal;
-                }
-
-                RGB light_direct = sample_one_light<LSS, LATER, GGX_SAMPLER>(rd, payload, hit, -direction, rng, make_int2(x, y), res, bounce);
-                RGB envmap_direct = sample_environment_map<LSS, ESS, GGX_SAMPLER>(rd, payload, hit, -direction, bounce, rng);
-
-                light_direct = clamp_light_contribution(light_direct, rd.render_settings.direct_contribution_clamp, bounce == 0);
-                envmap_direct = clamp_light_contribution(envmap_direct, rd.render_settings.envmap_contribution_clamp, bounce == 0);
-
-                if (LSS == 0)
-                {
-                    RGB hit_emission = material_emission(payload.material);
-                    hit_emission = clamp_light_contribution(hit_emission, rd.render_settings.indirect_contribution_clamp, bounce > 0);
-                    payload.ray_color += hit_emission * payload.throughput;
-                }
-                else
-                {
-                    if (bounce == 0)
-                        payload.ray_color += material_emission(payload.material);
-                    RGB indirect = (light_direct + envmap_direct) * payload.throughput;
-                    payload.ray_color += clamp_light_contribution(indirect, rd.render_settings.indirect_contribution_clamp, bounce > 0);
-                }
-
-                float bsdf_pdf;
-                float3 bounce_direction;
-                RGB bsdf_color = bsdf_sample<GGX_SAMPLER>(rd, payload.material, payload.volume_state, -direction, hit.shading_normal, hit.geometric_normal, bounce_direction, bsdf_pdf, rng);
-                RGB throughput_attenuation = bsdf_color * fabsf(dot(bounce_direction, hit.shading_normal)) / bsdf_pdf;
-
-                if (bsdf_pdf <= 0.0f)
-                    break;
-                if (!do_russian_roulette(rd.render_settings, bounce, payload.throughput, throughput_attenuation, rng))
-                    break;
-
-                payload.throughput *= get_dispersion_ray_color(payload.volume_state.sampled_wavelength, payload.material.dispersion_scale);
-                payload.throughput *= throughput_attenuation;
-                payload.next_ray_state = 0;
-
-                origin = hit.inter_point;
-                direction = bounce_direction;
-            }
-            else
-            {
-                RGB skysphere_color;
-                if (rd.world_settings.ambient_light_type == AMBIENT_UNIFORM || rd.bsdfs_data.white_furnace_mode)
-                    skysphere_color = rgb(rd.world_settings.uniform_light_color);
-                else if (rd.world_settings.ambient_light_type == AMBIENT_ENVMAP)
-                {
-                    if (ESS == 0 || bounce == 0)
-                    {
-                        skysphere_color = eval_envmap_no_pdf(rd.world_settings, direction);
-                        bool unscale = ESS == 0 ? (!rd.world_settings.envmap_scale_background_intensity && bounce == 0) : !rd.world_settings.envmap_scale_background_intensity;
-                        if (unscale)
-                            skysphere_color /= rd.world_settings.envmap_intensity;
-                    }
-                }
-
-                skysphere_color = clamp_light_contribution(skysphere_color, rd.render_settings.envmap_contribution_clamp, true);
-                RGB indirect = skysphere_color * payload.throughput;
-                payload.ray_color += clamp_light_contribution(indirect, rd.render_settings.indirect_contribution_clamp, bounce > 0);
-                payload.next_ray_state = 1;
-            }
-        }
-        else
-            break;
+        hit.geometric_normal = -hit.geometric_normal;
+        hit.shading_normal = -hit.shading_normal;
     }
 
-    if (!sanity_check(rd, payload, pixel_index))
+    RGB light_direct = sample_one_light<LSS, LATER, GGX_SAMPLER>(rd, payload, hit, -direction, rng, pixel_coords, res, bounce);
+    RGB envmap_direct = sample_environment_map<LSS, ESS, GGX_SAMPLER>(rd, payload, hit, -direction, bounce, rng);
+
+    light_direct = clamp_light_contribution(light_direct, rd.render_settings.direct_contribution_clamp, bounce == 0);
+    envmap_direct = clamp_light_contribution(envmap_direct, rd.render_settings.envmap_contribution_clamp, bounce == 0);
+
+    if (LSS == 0)
+    {
+        RGB hit_emission = material_emission(payload.material);
+        hit_emission = clamp_light_contribution(hit_emission, rd.render_settings.indirect_contribution_clamp, bounce > 0);
+        payload.ray_color += hit_emission * payload.throughput;
+    }
+    else
+    {
+        if (bounce == 0)
+            payload.ray_color += material_emission(payload.material);
+        RGB indirect = (light_direct + envmap_direct) * payload.throughput;
+        payload.ray_color += clamp_light_contribution(indirect, rd.render_settings.indirect_contribution_clamp, bounce > 0);
+    }
+
+    float bsdf_pdf;
+    float3 bounce_direction;
+    RGB bsdf_color = bsdf_sample<GGX_SAMPLER>(rd, payload.material, payload.volume_state, -direction, hit.shading_normal, hit.geometric_normal, bounce_direction, bsdf_pdf, rng);
+    RGB throughput_attenuation = bsdf_color * fabsf(dot(bounce_direction, hit.shading_normal)) / bsdf_pdf;
+
+    if (bsdf_pdf <= 0.0f)
+        return false;
+    if (!do_russian_roulette(rd.render_settings, bounce, payload.throughput, throughput_attenuation, rng))
+        return false;
+
+    payload.throughput *= get_dispersion_ray_color(payload.volume_state.sampled_wavelength, payload.material.dispersion_scale);
+    payload.throughput *= throughput_attenuation;
+    payload.next_ray_state = 0;
+
+    origin = hit.inter_point;
+    direction = bounce_direction;
+    return true;
+}
+
+// The ray left the scene (FullPathTracer.h:243-286): sky / envmap radiance
+template <int ESS>
+PT_DEV void miss_vertex(const HIPRTRenderData& rd, RayPayload& payload, float3 direction, int bounce)
+{
+    RGB skysphere_color;
+    if (rd.world_settings.ambient_light_type == AMBIENT_UNIFORM || rd.bsdfs_data.white_furnace_mode)
+        skysphere_color = rgb(rd.world_settings.uniform_light_color);
+    else if (rd.world_settings.ambient_light_type == AMBIENT_ENVMAP)
+    {
+        if (ESS == 0 || bounce == 0)
+        {
+            skysphere_color = eval_envmap_no_pdf(rd.world_settings, direction);
+            bool unscale = ESS == 0 ? (!rd.world_settings.envmap_scale_background_intensity && bounce == 0) : !rd.world_settings.envmap_scale_background_intensity;
+            if (unscale)
+                skysphere_color /= rd.world_settings.envmap_intensity;
+        }
+    }
+
+    skysphere_color = clamp_light_contribution(skysphere_color, rd.render_settings.envmap_contribution_clamp, true);
+    RGB indirect = skysphere_color * payload.throughput;
+    payload.ray_color += clamp_light_contribution(indirect, rd.render_settings.indirect_contribution_clamp, bounce > 0);
+    payload.next_ray_state = 1;
+}
+
+// End of a path (FullPathTracer.h:288-326): sanity check, then accumulation of the sample into the frame buffers.
+// The denoiser AOVs only depend on the camera hit, so they are re-read from the G-buffer here.
+PT_DEV void accumulate_sample(const HIPRTRenderData& rd, uint32_t pixel_index, RGB ray_color, float sampled_wavelength, float3 denoiser_normal, RGB denoiser_albedo)
+{
+    if (!sanity_check(rd, ray_color, sampled_wavelength, pixel_index))
         return;
 
-    squared_luminance_of_samples += payload.ray_color.luminance() * payload.ray_color.luminance();
+    float squared_luminance_of_samples = 0.0f;
+    squared_luminance_of_samples += ray_color.luminance() * ray_color.luminance();
     rd.aux_buffers.still_one_ray_active[0] = 1;
 
     if (has_access_to_adaptive_sampling_buffers(rd.render_settings))
@@ -457,9 +419,9 @@ PT_DEV void full_path_tracer_pixel(const HIPRTRenderData& rd, int2 res, uint32_t
 
     const int sample_number = rd.render_settings.sample_number;
     if (sample_number == 0)
-        st3(rd.buffers.pixels, pixel_index, to_f3(payload.ray_color));
+        st3(rd.buffers.pixels, pixel_index, to_f3(ray_color));
     else
-        st3(rd.buffers.pixels, pixel_index, ld3_rw(rd.buffers.pixels, pixel_index) + to_f3(payload.ray_color));
+        st3(rd.buffers.pixels, pixel_index, ld3_rw(rd.buffers.pixels, pixel_index) + to_f3(ray_color));
 
     const float counter = (float)rd.render_settings.denoiser_AOV_accumulation_counter;
     if (rd.aux_buffers.denoiser_albedo != nullptr)
@@ -484,5 +446,77 @@ PT_DEV void full_path_tracer_pixel(const HIPRTRenderData& rd, int2 res, uint32_t
                 st3(rd.aux_buffers.denoiser_normals, pixel_index, accumulated / normal_length);
         }
     }
+}
+
+// Denoiser AOVs of a pixel from its G-buffer entry (FullPathTracer.h:167-171: first hit's shading normal + base colour)
+PT_DEV void denoiser_aovs_from_g_buffer(const HIPRTRenderData& rd, uint32_t pixel_index, float3& denoiser_normal, RGB& denoiser_albedo)
+{
+    denoiser_normal = f3(0.0f, 0.0f, 0.0f);
+    denoiser_albedo = RGB(0.0f);
+    if (rd.g_buffer.camera_ray_hit[pixel_index] == 1)
+    {
+        denoiser_normal += normalize(ld3_rw(rd.g_buffer.shading_normals, pixel_index));
+        const ColorRGB32F& bc = rd.g_buffer.materials[pixel_index].base_color;
+        denoiser_albedo += RGB(bc.r, bc.g, bc.b);
+    }
+}
+
+// Megakernel form: one thread walks the whole path of its pixel.
+template <int LSS, int ESS, int LATER, int GGX_SAMPLER>
+PT_DEV void full_path_tracer_pixel(const HIPRTRenderData& rd, int2 res, uint32_t x, uint32_t y)
+{
+    uint32_t pixel_index = x + y * res.x;
+    if (!rd.aux_buffers.pixel_active[pixel_index])
+        return;
+
+    int nb_bounces = rd.render_settings.nb_bounces;
+    if (do_render_low_resolution(rd.render_settings))
+        nb_bounces = mini(3, nb_bounces);
+
+    Rng rng(pixel_seed(rd, pixel_index));
+
+    RGB denoiser_albedo(0.0f);
+    float3 denoiser_normal = f3(0.0f, 0.0f, 0.0f);
+
+    HitInfo hit;
+    hit.inter_point = ld3_rw(rd.g_buffer.first_hits, pixel_index);
+    hit.geometric_normal = normalize(ld3_rw(rd.g_buffer.geometric_normals, pixel_index));
+    hit.shading_normal = normalize(ld3_rw(rd.g_buffer.shading_normals, pixel_index));
+    hit.primitive_index = rd.g_buffer.first_hit_prim_index[pixel_index];
+
+    float3 origin = f3(0.0f, 0.0f, 0.0f);
+    float3 direction = normalize(-ld3_rw(rd.g_buffer.view_directions, pixel_index));
+    bool intersection_found = rd.g_buffer.camera_ray_hit[pixel_index] == 1;
+
+    RayPayload payload;
+    payload.throughput = RGB(1.0f);
+    payload.ray_color = RGB(0.0f);
+    payload.next_ray_state = 0;
+    load_material(payload.material, rd.g_buffer.materials + pixel_index);
+    copy_volume_state(&payload.volume_state, rd.g_buffer.ray_volume_states + pixel_index);
+
+    for (int bounce = 0; bounce < nb_bounces + 1; bounce++)
+    {
+        if (bounce > 0)
+            intersection_found = trace_ray(rd, origin, direction, payload, hit, hit.primitive_index, rng);
+
+        if (intersection_found)
+        {
+            if (bounce == 0)
+            {
+                denoiser_normal += hit.shading_normal;
+                denoiser_albedo += rgb(payload.material.base_color);
+            }
+            if (!shade_vertex<LSS, ESS, LATER, GGX_SAMPLER>(rd, payload, hit, origin, direction, rng, make_int2(x, y), res, bounce))
+                break;
+        }
+        else
+        {
+            miss_vertex<ESS>(rd, payload, direction, bounce);
+            break;
+        }
+    }
+
+    accumulate_sample(rd, pixel_index, payload.ray_color, payload.volume_state.sampled_wavelength, denoiser_normal, denoiser_albedo);
 }
 } // namespace pt

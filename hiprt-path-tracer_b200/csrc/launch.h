@@ -12,6 +12,28 @@ struct VariantOptions { int lss, ess, later, ggx; };
 struct Tile { int x0, y0, x1, y1; };
 struct TraversalCounters { unsigned long long rays, nodes, triangles; };
 
+// How b200pt_launch_FullPathTracer runs the path (wavefront.cuh). Selected per context (b200pt_set_path_mode).
+enum WavefrontMode { WF_MEGAKERNEL = 0, WF_FUSED = 1, WF_SPLIT = 2 };
+
+// Scratch of the wavefront path tracer, owned by the context, sized for the pixels of the largest tile launched so far.
+struct WavefrontState
+{
+    float4* origin_rng;      // ray origin xyz | Xorshift32 state
+    float4* dir_prim;        // ray direction xyz | primitive the ray leaves from
+    float4* throughput;
+    float4* color;
+    float4* hit_point;       // SPLIT only: intersection point | hit primitive
+    float4* hit_ns;          // SPLIT only: shading normal
+    float4* hit_ng;          // SPLIT only: geometric normal
+    uint32_t* volume;        // RayVolumeState, 9 words per path
+    void* materials;         // SPLIT only: 256-byte SimplifiedRendererMaterial per path
+    uint32_t* ray_queue[2];  // slot ids of the paths to extend at the next bounce (ping-pong)
+    uint32_t* shade_queue;   // SPLIT only: slot ids of the paths that hit something at this bounce
+    uint32_t* counts;        // [2*b]: rays queued for bounce b, [2*b+1]: hits queued for shading at bounce b
+    uint32_t capacity;       // paths
+    uint32_t max_bounces;    // counts holds 2 * (max_bounces + 2) entries
+};
+
 #ifdef PT_COUNTERS
 #define PT_SUFFIXED(name) name##_c
 #define PT_VARIANT_NAME_OF(name, L, E, A, G) name##_##L##_##E##_##A##_##G##_c
@@ -25,7 +47,7 @@ struct TraversalCounters { unsigned long long rays, nodes, triangles; };
 #define PT_DECLARE_LAUNCHERS(S)                                                                                                        \
     bool variant_available##S(const VariantOptions& opt);                                                                              \
     cudaError_t launch_CameraRays##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream);   \
-    cudaError_t launch_FullPathTracer##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream); \
+    cudaError_t launch_FullPathTracer##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const WavefrontState* wf, int mode); \
     cudaError_t launch_trace_closest##S(const Bvh8Device& bvh, const float* rays, const int* last_prim, long long n, int* out_prim, float* out_t, float* out_uv, TraversalCounters* counters, cudaStream_t stream); \
     cudaError_t launch_trace_shadow##S(const Bvh8Device& bvh, const float* rays, const float* t_max, const int* last_prim, long long n, unsigned char* out_occluded, TraversalCounters* counters, cudaStream_t stream);
 

@@ -111,6 +111,11 @@ class Context:
         return out
 
     # ---- counters ---------------------------------------------------------------------------
+    def set_path_mode(self, mode):
+        """'megakernel' | 'fused' | 'split' (b200pt_set_path_mode): the shape FullPathTracer runs in."""
+        m = {"megakernel": 0, "fused": 1, "split": 2}[mode] if isinstance(mode, str) else int(mode)
+        _capi.check(self.lib.b200pt_set_path_mode(self.handle, C.c_int(m)), "b200pt_set_path_mode")
+
     def counters_enable(self, enable=True):
         _capi.check(self.lib.b200pt_counters_enable(self.handle, C.c_int(1 if enable else 0)), "b200pt_counters_enable")
 
