@@ -199,6 +199,11 @@ static int ensure_wavefront(b200pt_ctx* ctx, uint32_t paths, uint32_t bounces)
     ok &= (wf.ray_queue[0] = static_cast<uint32_t*>(alloc(n * 4))) != nullptr;
     ok &= (wf.ray_queue[1] = static_cast<uint32_t*>(alloc(n * 4))) != nullptr;
     ok &= (wf.shade_queue = static_cast<uint32_t*>(alloc(n * 4))) != nullptr;
+    ok &= (wf.sorted_queue = static_cast<uint32_t*>(alloc(n * 4))) != nullptr;
+    ok &= (wf.sort_key = static_cast<uint8_t*>(alloc(n))) != nullptr;
+    ok &= (wf.bucket_count = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * pt::kSortBuckets))) != nullptr;
+    if (ok)
+        ok &= cudaMemset(wf.bucket_count, 0, sizeof(uint32_t) * pt::kSortBuckets) == cudaSuccess;
     ok &= (wf.counts = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * 2 * (max_bounces + 2)))) != nullptr;
     if (!ok)
     {

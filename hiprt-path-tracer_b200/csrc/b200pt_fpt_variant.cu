@@ -30,12 +30,35 @@ __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_bounce)(const __grid_
     wf_bounce_path<PT_LSS, PT_ESS, PT_LATER, PT_GGX>(rd, res, tile, wf, bounce, i);
 }
 
+__global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_gen)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf)
+{
+    const uint32_t x = tile.x0 + blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t y = tile.y0 + blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= (uint32_t)tile.x1 || y >= (uint32_t)tile.y1)
+        return;
+    wf_gen_pixel<PT_ESS>(rd, res, tile, wf, x, y);
+}
+
 __global__ void __launch_bounds__(128) PT_VARIANT_NAME(k_wf_extend)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= wf.counts[2 * bounce])
         return;
     wf_extend_path<PT_ESS>(rd, res, tile, wf, bounce, i);
+}
+
+__global__ void __launch_bounds__(kSortBuckets) PT_VARIANT_NAME(k_wf_scan)(const __grid_constant__ WavefrontState wf)
+{
+    __shared__ uint32_t smem[kSortBuckets];
+    wf_scan_buckets(wf, smem);
+}
+
+__global__ void __launch_bounds__(256) PT_VARIANT_NAME(k_wf_scatter)(const __grid_constant__ WavefrontState wf, int bounce)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= wf.counts[2 * bounce + 1])
+        return;
+    wf_scatter_path(wf, i);
 }
 
 __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_shade)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce)
@@ -65,16 +88,26 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
     cudaError_t e = cudaMemsetAsync(wf->counts, 0, sizeof(uint32_t) * 2 * (wf->max_bounces + 2), stream);
     if (e != cudaSuccess)
         return e;
-    PT_VARIANT_NAME(k_wf_bounce0)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile, *wf);
-    for (int bounce = 1; bounce <= nb_bounces; bounce++)
+    if (mode == WF_FUSED)
     {
-        if (mode == WF_FUSED)
+        PT_VARIANT_NAME(k_wf_bounce0)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile, *wf);
+        for (int bounce = 1; bounce <= nb_bounces; bounce++)
             PT_VARIANT_NAME(k_wf_bounce)<<<(paths + 63) / 64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
+        return cudaGetLastError();
+    }
+    for (int bounce = 0; bounce <= nb_bounces; bounce++)
+    {
+        if (bounce == 0)
+            PT_VARIANT_NAME(k_wf_gen)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile, *wf);
         else
-        {
             PT_VARIANT_NAME(k_wf_extend)<<<(paths + 127) / 128, 128, 0, stream>>>(*rd, res, tile, *wf, bounce);
-            PT_VARIANT_NAME(k_wf_shade)<<<(paths + 63) / 64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
-        }
+        PT_VARIANT_NAME(k_wf_scan)<<<1, kSortBuckets, 0, stream>>>(*wf);
+        PT_VARIANT_NAME(k_wf_scatter)<<<(paths + 255) / 256, 256, 0, stream>>>(*wf, bounce);
+        // the scatter cursors become the next histogram: zero them again
+        e = cudaMemsetAsync(wf->bucket_count, 0, sizeof(uint32_t) * kSortBuckets, stream);
+        if (e != cudaSuccess)
+            return e;
+        PT_VARIANT_NAME(k_wf_shade)<<<(paths + 63) / 64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
     }
     return cudaGetLastError();
 }

@@ -13,6 +13,7 @@ struct Tile { int x0, y0, x1, y1; };
 struct TraversalCounters { unsigned long long rays, nodes, triangles; };
 
 // How b200pt_launch_FullPathTracer runs the path (wavefront.cuh). Selected per context (b200pt_set_path_mode).
+constexpr int kSortBuckets = 128;
 enum WavefrontMode { WF_MEGAKERNEL = 0, WF_FUSED = 1, WF_SPLIT = 2 };
 
 // Scratch of the wavefront path tracer, owned by the context, sized for the pixels of the largest tile launched so far.
@@ -28,7 +29,10 @@ struct WavefrontState
     uint32_t* volume;        // RayVolumeState, 9 words per path
     void* materials;         // SPLIT only: 256-byte SimplifiedRendererMaterial per path
     uint32_t* ray_queue[2];  // slot ids of the paths to extend at the next bounce (ping-pong)
-    uint32_t* shade_queue;   // SPLIT only: slot ids of the paths that hit something at this bounce
+    uint32_t* shade_queue;   // SPLIT only: slot ids of the paths that hit something at this bounce (arrival order)
+    uint32_t* sorted_queue;  // SPLIT only: the same ids, grouped by material signature (coherent BSDF branches per warp)
+    uint8_t* sort_key;       // SPLIT only: material signature of the slot's current hit (kSortBuckets values)
+    uint32_t* bucket_count;  // SPLIT only: kSortBuckets histogram of the current shade queue, then scatter cursors
     uint32_t* counts;        // [2*b]: rays queued for bounce b, [2*b+1]: hits queued for shading at bounce b
     uint32_t capacity;       // paths
     uint32_t max_bounces;    // counts holds 2 * (max_bounces + 2) entries

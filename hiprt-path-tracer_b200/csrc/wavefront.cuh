@@ -1,16 +1,19 @@
-// Wavefront form of FullPathTracer: one launch per bounce over a compacted queue of the paths that are still alive.
+// Wavefront form of FullPathTracer: launches per bounce over compacted queues of the paths that are still alive.
 //
 // Why: ncu on the megakernel (profiles/r01_fullpathtracer_megakernel_cornell1080p.txt) shows 8.5 of 32 threads active per
-// instruction -- a warp waits for its longest path. Here every bounce is its own launch; surviving paths are appended to
-// the next bounce's queue with one warp-aggregated atomic, so warps stay full. The per-path arithmetic and RNG order are
-// the shared device functions of kernels.cuh (shade_vertex / miss_vertex / accumulate_sample): results are bit-identical
-// to the megakernel and therefore to the reference (src/Device/kernels/FullPathTracer.h:99-327).
+// instruction -- a warp waits for its longest path -- and the dominant stall is `no_instruction`: ~330 KB of SASS against a
+// 32 KB L1.5 instruction cache, with every warp of an SM at a different place in it. Here every bounce is its own set of
+// launches; surviving paths are appended to the next queue with one warp-aggregated atomic, so warps stay full, and the
+// shade queue is grouped by a material signature so that the lanes of a warp (and the warps of an SM) walk the same
+// BSDF branches. The per-path arithmetic and RNG order are the shared device functions of kernels.cuh (shade_vertex /
+// miss_vertex / accumulate_sample): results are bit-identical to the megakernel and therefore to the reference
+// (src/Device/kernels/FullPathTracer.h:99-327).
 //
 // Path state lives in HBM, indexed by the path's slot = its pixel's index inside the launch tile; queues only carry slot
-// ids (4 B). Two shapes, selected at run time (launch.h: WavefrontMode):
+// ids (4 B). Shapes, selected at run time (launch.h: WavefrontMode):
 //   FUSED: bounce 0 shade kernel, then per bounce ONE kernel = trace_ray + shade_vertex (state: ray, throughput, colour, volume)
-//   SPLIT: per bounce an EXTEND kernel (trace_ray only: low register count, traversal-bound) that writes hit + material,
-//          and a SHADE kernel that consumes them.
+//   SPLIT: GEN (bounce 0: ray state from the G-buffer) or EXTEND (bounce > 0: trace_ray only, low register count) produce the
+//          hit + material and its signature; SCAN + SCATTER group the queue by signature; SHADE consumes it.
 #pragma once
 
 #include "kernels.cuh"
@@ -39,6 +42,31 @@ PT_DEV void queue_push(uint32_t* queue, uint32_t* count, bool pred, uint32_t val
         base = atomicAdd(count, (uint32_t)__popc(mask));
     base = __shfl_sync(mask, base, leader);
     queue[base + (uint32_t)__popc(mask & ((1u << lane) - 1u))] = value;
+}
+
+// Which branches of the principled BSDF a material takes (lobe weights that are zero skip their layer:
+// reference Principled.h:863-972). Paths are grouped by this value before shading.
+PT_DEV uint32_t material_signature(const Material& m)
+{
+    uint32_t s = 0;
+    s |= material_is_emissive(m) ? 1u : 0u;
+    s |= m.coat > 0.0f ? 2u : 0u;
+    s |= m.sheen > 0.0f ? 4u : 0u;
+    s |= m.metallic > 0.0f ? 8u : 0u;
+    s |= m.metallic < 1.0f ? 16u : 0u;
+    s |= m.specular_transmission > 0.0f ? 32u : 0u;
+    s |= m.thin_film > 0.0f ? 64u : 0u;
+    return s;   // < kSortBuckets
+}
+
+// Records the slot's signature and counts it in the histogram of the current shade queue (one atomic per distinct key per warp)
+PT_DEV void wf_classify(const WavefrontState& wf, uint32_t slot, const Material& m)
+{
+    const uint32_t key = material_signature(m);
+    wf.sort_key[slot] = (uint8_t)key;
+    const unsigned peers = __match_any_sync(__activemask(), key);
+    if ((int)lane_id() == __ffs((int)peers) - 1)
+        atomicAdd(wf.bucket_count + key, (uint32_t)__popc(peers));
 }
 
 struct PathRegs
@@ -83,8 +111,19 @@ PT_DEV void wf_store_hit(const WavefrontState& wf, uint32_t slot, const PathRegs
     store_material(reinterpret_cast<SimplifiedRendererMaterial*>(wf.materials) + slot, p.payload.material);
 }
 
-PT_DEV void wf_load_hit(const WavefrontState& wf, uint32_t slot, PathRegs& p)
+// The surface a path is shaded at: bounce 0 reads the camera hit straight from the G-buffer (FullPathTracer.h:136-151,
+// the normals are re-normalised there), later bounces read what EXTEND stored.
+PT_DEV void wf_load_hit(const HIPRTRenderData& rd, const WavefrontState& wf, uint32_t slot, uint32_t pixel_index, int bounce, PathRegs& p)
 {
+    if (bounce == 0)
+    {
+        p.hit.inter_point = ld3_rw(rd.g_buffer.first_hits, pixel_index);
+        p.hit.geometric_normal = normalize(ld3_rw(rd.g_buffer.geometric_normals, pixel_index));
+        p.hit.shading_normal = normalize(ld3_rw(rd.g_buffer.shading_normals, pixel_index));
+        p.hit.primitive_index = rd.g_buffer.first_hit_prim_index[pixel_index];
+        load_material(p.payload.material, rd.g_buffer.materials + pixel_index);
+        return;
+    }
     const float4 hp = wf.hit_point[slot], ns = wf.hit_ns[slot], ng = wf.hit_ng[slot];
     p.hit.inter_point = f3(hp.x, hp.y, hp.z);
     p.hit.primitive_index = __float_as_int(hp.w);
@@ -117,30 +156,31 @@ PT_DEV void wf_slot_to_pixel(const Tile& tile, int2 res, uint32_t slot, uint32_t
     pixel_index = x + y * (uint32_t)res.x;
 }
 
-// ---- bounce 0: the camera hit comes from the G-buffer (FullPathTracer.h:136-151) ------------------------------
+// Ray state of a fresh path at its camera hit (FullPathTracer.h:124-151)
+PT_DEV void wf_init_path(const HIPRTRenderData& rd, uint32_t pixel_index, PathRegs& p)
+{
+    p.rng = Rng(pixel_seed(rd, pixel_index));
+    p.hit.primitive_index = rd.g_buffer.first_hit_prim_index[pixel_index];
+    p.origin = f3(0.0f, 0.0f, 0.0f);
+    p.direction = normalize(-ld3_rw(rd.g_buffer.view_directions, pixel_index));
+    p.payload.throughput = RGB(1.0f);
+    p.payload.ray_color = RGB(0.0f);
+    p.payload.next_ray_state = 0;
+    copy_volume_state(&p.payload.volume_state, rd.g_buffer.ray_volume_states + pixel_index);
+}
+
+// ---- FUSED, bounce 0: the camera hit comes from the G-buffer ------------------------------------------------------
 template <int LSS, int ESS, int LATER, int GGX_SAMPLER>
 PT_DEV void wf_bounce0_pixel(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, uint32_t x, uint32_t y)
 {
     const uint32_t pixel_index = x + y * res.x;
     const uint32_t slot = (x - tile.x0) + (y - tile.y0) * (uint32_t)(tile.x1 - tile.x0);
     bool alive = false;
-    PathRegs p;
-    const bool active = rd.aux_buffers.pixel_active[pixel_index];
-    if (active)
+    if (rd.aux_buffers.pixel_active[pixel_index])
     {
-        p.rng = Rng(pixel_seed(rd, pixel_index));
-        p.hit.inter_point = ld3_rw(rd.g_buffer.first_hits, pixel_index);
-        p.hit.geometric_normal = normalize(ld3_rw(rd.g_buffer.geometric_normals, pixel_index));
-        p.hit.shading_normal = normalize(ld3_rw(rd.g_buffer.shading_normals, pixel_index));
-        p.hit.primitive_index = rd.g_buffer.first_hit_prim_index[pixel_index];
-        p.origin = f3(0.0f, 0.0f, 0.0f);
-        p.direction = normalize(-ld3_rw(rd.g_buffer.view_directions, pixel_index));
-        p.payload.throughput = RGB(1.0f);
-        p.payload.ray_color = RGB(0.0f);
-        p.payload.next_ray_state = 0;
-        load_material(p.payload.material, rd.g_buffer.materials + pixel_index);
-        copy_volume_state(&p.payload.volume_state, rd.g_buffer.ray_volume_states + pixel_index);
-
+        PathRegs p;
+        wf_init_path(rd, pixel_index, p);
+        wf_load_hit(rd, wf, slot, pixel_index, 0, p);
         if (rd.g_buffer.camera_ray_hit[pixel_index] == 1)
             alive = shade_vertex<LSS, ESS, LATER, GGX_SAMPLER>(rd, p.payload, p.hit, p.origin, p.direction, p.rng, make_int2(x, y), res, 0);
         else
@@ -176,7 +216,34 @@ PT_DEV void wf_bounce_path(const HIPRTRenderData& rd, int2 res, const Tile& tile
     queue_push(wf.ray_queue[bounce & 1], wf.counts + 2 * (bounce + 1), alive, slot);
 }
 
-// ---- SPLIT: extend (closest hit + material) and shade as two kernels --------------------------------------------
+// ---- SPLIT, bounce 0: GEN writes the ray state of every active pixel and queues the camera hits for shading -------------
+template <int ESS>
+PT_DEV void wf_gen_pixel(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, uint32_t x, uint32_t y)
+{
+    const uint32_t pixel_index = x + y * res.x;
+    const uint32_t slot = (x - tile.x0) + (y - tile.y0) * (uint32_t)(tile.x1 - tile.x0);
+    bool found = false;
+    if (rd.aux_buffers.pixel_active[pixel_index])
+    {
+        PathRegs p;
+        wf_init_path(rd, pixel_index, p);
+        found = rd.g_buffer.camera_ray_hit[pixel_index] == 1;
+        if (found)
+        {
+            wf_store_ray(wf, slot, p);
+            load_material(p.payload.material, rd.g_buffer.materials + pixel_index);
+            wf_classify(wf, slot, p.payload.material);
+        }
+        else
+        {
+            miss_vertex<ESS>(rd, p.payload, p.direction, 0);
+            wf_finish_path(rd, pixel_index, p);
+        }
+    }
+    queue_push(wf.shade_queue, wf.counts + 1, found, slot);
+}
+
+// ---- SPLIT, bounce >= 1: EXTEND = closest hit + material ----------------------------------------------------------------
 template <int ESS>
 PT_DEV void wf_extend_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
 {
@@ -185,7 +252,10 @@ PT_DEV void wf_extend_path(const HIPRTRenderData& rd, int2 res, const Tile& tile
     wf_load_ray(wf, slot, p);
     const bool found = trace_ray(rd, p.origin, p.direction, p.payload, p.hit, p.hit.primitive_index, p.rng);
     if (found)
+    {
         wf_store_hit(wf, slot, p);
+        wf_classify(wf, slot, p.payload.material);
+    }
     else
     {
         uint32_t x, y, pixel_index;
@@ -196,15 +266,48 @@ PT_DEV void wf_extend_path(const HIPRTRenderData& rd, int2 res, const Tile& tile
     queue_push(wf.shade_queue, wf.counts + 2 * bounce + 1, found, slot);
 }
 
+// ---- SPLIT: group the shade queue by material signature (counting sort: histogram came from wf_classify) ----------------
+// One block of kSortBuckets threads: exclusive scan of the histogram in place -> scatter cursors.
+PT_DEV void wf_scan_buckets(const WavefrontState& wf, uint32_t* smem)
+{
+    const uint32_t t = threadIdx.x;
+    const uint32_t v = wf.bucket_count[t];
+    smem[t] = v;
+    __syncthreads();
+    for (uint32_t offset = 1; offset < (uint32_t)kSortBuckets; offset <<= 1)
+    {
+        const uint32_t add = t >= offset ? smem[t - offset] : 0u;
+        __syncthreads();
+        smem[t] += add;
+        __syncthreads();
+    }
+    wf.bucket_count[t] = smem[t] - v;
+}
+
+PT_DEV void wf_scatter_path(const WavefrontState& wf, uint32_t i)
+{
+    const uint32_t slot = wf.shade_queue[i];
+    const uint32_t key = wf.sort_key[slot];
+    const unsigned peers = __match_any_sync(__activemask(), key);
+    const uint32_t lane = lane_id();
+    const int leader = __ffs((int)peers) - 1;
+    uint32_t base = 0;
+    if ((int)lane == leader)
+        base = atomicAdd(wf.bucket_count + key, (uint32_t)__popc(peers));
+    base = __shfl_sync(peers, base, leader);
+    wf.sorted_queue[base + (uint32_t)__popc(peers & ((1u << lane) - 1u))] = slot;
+}
+
+// ---- SPLIT: SHADE one vertex of every queued path -------------------------------------------------------------------------
 template <int LSS, int ESS, int LATER, int GGX_SAMPLER>
 PT_DEV void wf_shade_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
 {
-    const uint32_t slot = wf.shade_queue[i];
+    const uint32_t slot = wf.sorted_queue[i];
     uint32_t x, y, pixel_index;
     wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
     PathRegs p;
     wf_load_ray(wf, slot, p);
-    wf_load_hit(wf, slot, p);
+    wf_load_hit(rd, wf, slot, pixel_index, bounce, p);
     bool alive = shade_vertex<LSS, ESS, LATER, GGX_SAMPLER>(rd, p.payload, p.hit, p.origin, p.direction, p.rng, make_int2(x, y), res, bounce);
     alive = alive && bounce < wf_nb_bounces(rd);
     if (alive)
