@@ -17,7 +17,7 @@ struct b200pt_ctx
     pt::VariantOptions options = {3, 0, 3, 0};
     bool counting = false;
     pt::TraversalCounters* d_counters = nullptr;
-    int path_mode = pt::WF_SPLIT;
+    int path_mode = pt::WF_PHASED;
     pt::WavefrontState wf = {};
     std::vector<void*> wf_allocations;
 };
@@ -129,7 +129,7 @@ int b200pt_ctx_create(int device_index, b200pt_ctx** out_ctx)
     cudaDeviceSetLimit(cudaLimitStackSize, 8192);
     // B200PT_PATH_MODE=megakernel|fused|split overrides the default shape of FullPathTracer (A/B measurements)
     if (const char* m = getenv("B200PT_PATH_MODE"))
-        ctx->path_mode = !strcmp(m, "megakernel") ? pt::WF_MEGAKERNEL : !strcmp(m, "fused") ? pt::WF_FUSED : pt::WF_SPLIT;
+        ctx->path_mode = !strcmp(m, "megakernel") ? pt::WF_MEGAKERNEL : !strcmp(m, "fused") ? pt::WF_FUSED : !strcmp(m, "split") ? pt::WF_SPLIT : pt::WF_PHASED;
     *out_ctx = ctx;
     return B200PT_SUCCESS;
 }

@@ -194,6 +194,9 @@ static int ensure_wavefront(b200pt_ctx* ctx, uint32_t paths, uint32_t bounces)
     bool ok = true;
     for (float4** a : f4)
         ok &= (*a = static_cast<float4*>(alloc(n * sizeof(float4)))) != nullptr;
+    float4** nee[] = {&wf.nee_ray_o, &wf.nee_ray_d, &wf.nee_pending};
+    for (float4** a : nee)
+        ok &= (*a = static_cast<float4*>(alloc(4 * n * sizeof(float4)))) != nullptr;
     ok &= (wf.volume = static_cast<uint32_t*>(alloc(n * 36))) != nullptr;
     ok &= (wf.materials = alloc(n * 256)) != nullptr;
     ok &= (wf.ray_queue[0] = static_cast<uint32_t*>(alloc(n * 4))) != nullptr;
@@ -204,7 +207,7 @@ static int ensure_wavefront(b200pt_ctx* ctx, uint32_t paths, uint32_t bounces)
     ok &= (wf.bucket_count = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * pt::kSortBuckets))) != nullptr;
     if (ok)
         ok &= cudaMemset(wf.bucket_count, 0, sizeof(uint32_t) * pt::kSortBuckets) == cudaSuccess;
-    ok &= (wf.counts = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * 2 * (max_bounces + 2)))) != nullptr;
+    ok &= (wf.counts = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * (2 + pt::kCursorsPerBounce) * (max_bounces + 2)))) != nullptr;
     if (!ok)
     {
         cudaError_t e = cudaGetLastError();
@@ -214,6 +217,10 @@ static int ensure_wavefront(b200pt_ctx* ctx, uint32_t paths, uint32_t bounces)
         wf = pt::WavefrontState{};
         return cuda_fail(e == cudaSuccess ? cudaErrorMemoryAllocation : e, "wavefront scratch allocation");
     }
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+    wf.sm_count = (uint32_t)sms;
+    wf.cursors = wf.counts + 2 * (max_bounces + 2);
     wf.capacity = capacity;
     wf.max_bounces = max_bounces;
     return B200PT_SUCCESS;
@@ -245,7 +252,7 @@ int b200pt_launch_CameraRays(b200pt_ctx* ctx, const HIPRTRenderData* render_data
 
 int b200pt_set_path_mode(b200pt_ctx* ctx, int mode)
 {
-    REQUIRE(ctx != nullptr && mode >= pt::WF_MEGAKERNEL && mode <= pt::WF_SPLIT);
+    REQUIRE(ctx != nullptr && mode >= pt::WF_MEGAKERNEL && mode <= pt::WF_PHASED);
     ctx->path_mode = mode;
     return B200PT_SUCCESS;
 }

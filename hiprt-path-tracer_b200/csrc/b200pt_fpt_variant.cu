@@ -1,9 +1,18 @@
 // One FullPathTracer permutation per translation unit: compile with -DPT_LSS= -DPT_ESS= -DPT_LATER= -DPT_GGX=
 // Holds the megakernel and the wavefront kernels (wavefront.cuh) of the permutation plus their launcher.
-#include "wavefront.cuh"
+#include "wavefront_mis.cuh"
 
 namespace pt
 {
+// Queue kernels: the queue length is only known on the device. Every warp of a grid sized to the SMs pulls the next 32
+// queue entries with one atomic on a per-launch cursor (dynamic balance, and no mostly-empty 32k-block grids:
+// those cost ~1.5 ns per empty block, 50 us per launch at 1080p). KID = cursor of this kernel within its bounce.
+#define PT_FOR_EACH_QUEUED(I, COUNT, KID)                                                                           \
+    const uint32_t n_queued_ = (COUNT);                                                                             \
+    uint32_t* const cursor_ = wf.cursors + (uint32_t)bounce * kCursorsPerBounce + (KID);                            \
+    for (uint32_t I = wf_next_entry(cursor_); __any_sync(0xFFFFFFFFu, I < n_queued_); I = wf_next_entry(cursor_))   \
+        if (I < n_queued_)
+
 __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_FullPathTracer)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile)
 {
     const uint32_t x = tile.x0 + blockIdx.x * blockDim.x + threadIdx.x;
@@ -24,10 +33,8 @@ __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_bounce0)(const __grid
 
 __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_bounce)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce)
 {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= wf.counts[2 * bounce])
-        return;
-    wf_bounce_path<PT_LSS, PT_ESS, PT_LATER, PT_GGX>(rd, res, tile, wf, bounce, i);
+    PT_FOR_EACH_QUEUED(i, wf.counts[2 * bounce], 0)
+        wf_bounce_path<PT_LSS, PT_ESS, PT_LATER, PT_GGX>(rd, res, tile, wf, bounce, i);
 }
 
 __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_gen)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf)
@@ -41,10 +48,8 @@ __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_gen)(const __grid_con
 
 __global__ void __launch_bounds__(128) PT_VARIANT_NAME(k_wf_extend)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce)
 {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= wf.counts[2 * bounce])
-        return;
-    wf_extend_path<PT_ESS>(rd, res, tile, wf, bounce, i);
+    PT_FOR_EACH_QUEUED(i, wf.counts[2 * bounce], 0)
+        wf_extend_path<PT_ESS>(rd, res, tile, wf, bounce, i);
 }
 
 __global__ void __launch_bounds__(kSortBuckets) PT_VARIANT_NAME(k_wf_scan)(const __grid_constant__ WavefrontState wf)
@@ -55,19 +60,41 @@ __global__ void __launch_bounds__(kSortBuckets) PT_VARIANT_NAME(k_wf_scan)(const
 
 __global__ void __launch_bounds__(256) PT_VARIANT_NAME(k_wf_scatter)(const __grid_constant__ WavefrontState wf, int bounce)
 {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= wf.counts[2 * bounce + 1])
-        return;
-    wf_scatter_path(wf, i);
+    PT_FOR_EACH_QUEUED(i, wf.counts[2 * bounce + 1], 1)
+        wf_scatter_path(wf, i);
 }
 
 __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_shade)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce)
 {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= wf.counts[2 * bounce + 1])
-        return;
-    wf_shade_path<PT_LSS, PT_ESS, PT_LATER, PT_GGX>(rd, res, tile, wf, bounce, i);
+    PT_FOR_EACH_QUEUED(i, wf.counts[2 * bounce + 1], 2)
+        wf_shade_path<PT_LSS, PT_ESS, PT_LATER, PT_GGX>(rd, res, tile, wf, bounce, i);
 }
+
+__global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_direct)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce)
+{
+    PT_FOR_EACH_QUEUED(i, wf.counts[2 * bounce + 1], 2)
+        wf_direct_path<PT_LSS, PT_ESS, PT_LATER, PT_GGX>(rd, res, tile, wf, bounce, i);
+}
+
+__global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_bsdf)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce)
+{
+    PT_FOR_EACH_QUEUED(i, wf.counts[2 * bounce + 1], 7)
+        wf_bsdf_path<PT_GGX>(rd, res, tile, wf, bounce, i);
+}
+
+#if PT_LSS == 3
+#define PT_QUEUE_KERNEL(NAME, BOUNDS, KID, CALL)                                                                                                                            \
+    __global__ void __launch_bounds__(BOUNDS) PT_VARIANT_NAME(NAME)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce) \
+    {                                                                                                                                                                  \
+        PT_FOR_EACH_QUEUED(i, wf.counts[2 * bounce + 1], KID)                                                                                                          \
+            CALL(rd, res, tile, wf, bounce, i);                                                                                                                        \
+    }
+PT_QUEUE_KERNEL(k_wf_nee_light_eval, 64, 2, nee_light_eval_path)
+PT_QUEUE_KERNEL(k_wf_nee_bsdf_sample, 64, 3, nee_bsdf_sample_path<PT_GGX>)
+PT_QUEUE_KERNEL(k_wf_env_light_eval, 64, 4, env_light_eval_path<PT_ESS>)
+PT_QUEUE_KERNEL(k_wf_env_bsdf_sample, 64, 5, env_bsdf_sample_path<PT_GGX>)
+PT_QUEUE_KERNEL(k_wf_nee_trace, 128, 6, nee_trace_path<PT_ESS>)
+#endif
 
 cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const WavefrontState* wf, int mode)
 {
@@ -85,14 +112,18 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
     if (paths > wf->capacity || (uint32_t)nb_bounces > wf->max_bounces)
         return cudaErrorInvalidValue;
 
-    cudaError_t e = cudaMemsetAsync(wf->counts, 0, sizeof(uint32_t) * 2 * (wf->max_bounces + 2), stream);
+    // Queue lengths are only known on the device: queue kernels run grid-stride loops on a grid capped at a few blocks per
+    // SM (an uncapped grid of mostly empty blocks costs ~1.5 ns per block: 50 us per launch at 1080p)
+    const unsigned cap = wf->sm_count * 16u;
+    auto blocks = [&](unsigned block) { unsigned g = (paths + block - 1) / block, c = cap * 64u / block; return g < c ? g : c; };
+    cudaError_t e = cudaMemsetAsync(wf->counts, 0, sizeof(uint32_t) * (2 + kCursorsPerBounce) * (wf->max_bounces + 2), stream);
     if (e != cudaSuccess)
         return e;
     if (mode == WF_FUSED)
     {
         PT_VARIANT_NAME(k_wf_bounce0)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile, *wf);
         for (int bounce = 1; bounce <= nb_bounces; bounce++)
-            PT_VARIANT_NAME(k_wf_bounce)<<<(paths + 63) / 64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
+            PT_VARIANT_NAME(k_wf_bounce)<<<blocks(64), 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
         return cudaGetLastError();
     }
     for (int bounce = 0; bounce <= nb_bounces; bounce++)
@@ -100,14 +131,37 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
         if (bounce == 0)
             PT_VARIANT_NAME(k_wf_gen)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile, *wf);
         else
-            PT_VARIANT_NAME(k_wf_extend)<<<(paths + 127) / 128, 128, 0, stream>>>(*rd, res, tile, *wf, bounce);
+            PT_VARIANT_NAME(k_wf_extend)<<<blocks(128), 128, 0, stream>>>(*rd, res, tile, *wf, bounce);
         PT_VARIANT_NAME(k_wf_scan)<<<1, kSortBuckets, 0, stream>>>(*wf);
-        PT_VARIANT_NAME(k_wf_scatter)<<<(paths + 255) / 256, 256, 0, stream>>>(*wf, bounce);
+        PT_VARIANT_NAME(k_wf_scatter)<<<blocks(256), 256, 0, stream>>>(*wf, bounce);
         // the scatter cursors become the next histogram: zero them again
         e = cudaMemsetAsync(wf->bucket_count, 0, sizeof(uint32_t) * kSortBuckets, stream);
         if (e != cudaSuccess)
             return e;
-        PT_VARIANT_NAME(k_wf_shade)<<<(paths + 63) / 64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
+#if PT_LSS == 3
+        // alpha testing would make shadow rays draw random numbers (FilterFunction.h:42): then the phases cannot be reordered
+        if (mode == WF_PHASED && rd->render_settings.number_of_light_samples == 1 && !rd->render_settings.do_alpha_testing)
+        {
+            const unsigned g64 = blocks(64), g128 = blocks(128);
+            PT_VARIANT_NAME(k_wf_nee_light_eval)<<<g64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
+            PT_VARIANT_NAME(k_wf_nee_bsdf_sample)<<<g64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
+            if (PT_ESS != 0 && rd->world_settings.ambient_light_type == AMBIENT_ENVMAP)
+            {
+                PT_VARIANT_NAME(k_wf_env_light_eval)<<<g64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
+                PT_VARIANT_NAME(k_wf_env_bsdf_sample)<<<g64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
+            }
+            PT_VARIANT_NAME(k_wf_nee_trace)<<<g128, 128, 0, stream>>>(*rd, res, tile, *wf, bounce);
+            PT_VARIANT_NAME(k_wf_bsdf)<<<g64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
+        }
+        else
+#endif
+        if (mode == WF_PHASED)
+        {
+            PT_VARIANT_NAME(k_wf_direct)<<<blocks(64), 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
+            PT_VARIANT_NAME(k_wf_bsdf)<<<blocks(64), 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
+        }
+        else
+            PT_VARIANT_NAME(k_wf_shade)<<<blocks(64), 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
     }
     return cudaGetLastError();
 }

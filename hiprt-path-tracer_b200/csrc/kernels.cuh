@@ -331,8 +331,9 @@ PT_DEV bool sanity_check(const HIPRTRenderData& rd, RGB& ray_color, float sample
 // One path vertex with an intersection (FullPathTracer.h:165-241): NEE + envmap sampling, emission, BSDF sample,
 // russian roulette, throughput update. Returns false when the path ends here. Shared by the megakernel and the
 // wavefront kernels so that both evaluate exactly the same arithmetic in the same RNG order.
+// First half of a vertex: direct lighting (NEE + envmap sampling with their MIS rays), emission, the three clamps.
 template <int LSS, int ESS, int LATER, int GGX_SAMPLER>
-PT_DEV bool shade_vertex(const HIPRTRenderData& rd, RayPayload& payload, HitInfo& hit, float3& origin, float3& direction, Rng& rng, int2 pixel_coords, int2 res, int bounce)
+PT_DEV void shade_vertex_direct(const HIPRTRenderData& rd, RayPayload& payload, HitInfo& hit, float3 direction, Rng& rng, int2 pixel_coords, int2 res, int bounce)
 {
     if (material_is_emissive(payload.material) && dot(-direction, hit.geometric_normal) < 0)
     {
@@ -359,7 +360,13 @@ PT_DEV bool shade_vertex(const HIPRTRenderData& rd, RayPayload& payload, HitInfo
         RGB indirect = (light_direct + envmap_direct) * payload.throughput;
         payload.ray_color += clamp_light_contribution(indirect, rd.render_settings.indirect_contribution_clamp, bounce > 0);
     }
+}
 
+// Second half: BSDF sample, russian roulette, throughput update. `hit` carries the normals as shade_vertex_direct left
+// them (flipped towards the viewer on emissive back faces). Returns false when the path ends here.
+template <int GGX_SAMPLER>
+PT_DEV bool shade_vertex_bounce(const HIPRTRenderData& rd, RayPayload& payload, const HitInfo& hit, float3& origin, float3& direction, Rng& rng, int bounce)
+{
     float bsdf_pdf;
     float3 bounce_direction;
     RGB bsdf_color = bsdf_sample<GGX_SAMPLER>(rd, payload.material, payload.volume_state, -direction, hit.shading_normal, hit.geometric_normal, bounce_direction, bsdf_pdf, rng);
@@ -377,6 +384,13 @@ PT_DEV bool shade_vertex(const HIPRTRenderData& rd, RayPayload& payload, HitInfo
     origin = hit.inter_point;
     direction = bounce_direction;
     return true;
+}
+
+template <int LSS, int ESS, int LATER, int GGX_SAMPLER>
+PT_DEV bool shade_vertex(const HIPRTRenderData& rd, RayPayload& payload, HitInfo& hit, float3& origin, float3& direction, Rng& rng, int2 pixel_coords, int2 res, int bounce)
+{
+    shade_vertex_direct<LSS, ESS, LATER, GGX_SAMPLER>(rd, payload, hit, direction, rng, pixel_coords, res, bounce);
+    return shade_vertex_bounce<GGX_SAMPLER>(rd, payload, hit, origin, direction, rng, bounce);
 }
 
 // The ray left the scene (FullPathTracer.h:243-286): sky / envmap radiance

@@ -14,7 +14,8 @@ struct TraversalCounters { unsigned long long rays, nodes, triangles; };
 
 // How b200pt_launch_FullPathTracer runs the path (wavefront.cuh). Selected per context (b200pt_set_path_mode).
 constexpr int kSortBuckets = 128;
-enum WavefrontMode { WF_MEGAKERNEL = 0, WF_FUSED = 1, WF_SPLIT = 2 };
+constexpr int kCursorsPerBounce = 8;
+enum WavefrontMode { WF_MEGAKERNEL = 0, WF_FUSED = 1, WF_SPLIT = 2, WF_PHASED = 3 };
 
 // Scratch of the wavefront path tracer, owned by the context, sized for the pixels of the largest tile launched so far.
 struct WavefrontState
@@ -33,7 +34,12 @@ struct WavefrontState
     uint32_t* sorted_queue;  // SPLIT only: the same ids, grouped by material signature (coherent BSDF branches per warp)
     uint8_t* sort_key;       // SPLIT only: material signature of the slot's current hit (kSortBuckets values)
     uint32_t* bucket_count;  // SPLIT only: kSortBuckets histogram of the current shade queue, then scatter cursors
+    float4* nee_ray_o;       // PHASED only: 4 NEE rays per path (wavefront_mis.cuh), [which * capacity + slot]: origin | t_max (<0: none)
+    float4* nee_ray_d;       //   direction | cosine term (ray 1)
+    float4* nee_pending;     //   contribution if unoccluded (rays 0,2,3) or BSDF value | pdf (ray 1)
     uint32_t* counts;        // [2*b]: rays queued for bounce b, [2*b+1]: hits queued for shading at bounce b
+    uint32_t* cursors;       // kCursorsPerBounce work cursors per bounce (dynamic fetch of the queue kernels); follows `counts`
+    uint32_t sm_count;       // SMs of the device (grid sizing of the queue kernels)
     uint32_t capacity;       // paths
     uint32_t max_bounces;    // counts holds 2 * (max_bounces + 2) entries
 };

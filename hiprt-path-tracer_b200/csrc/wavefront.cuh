@@ -44,6 +44,16 @@ PT_DEV void queue_push(uint32_t* queue, uint32_t* count, bool pred, uint32_t val
     queue[base + (uint32_t)__popc(mask & ((1u << lane) - 1u))] = value;
 }
 
+// Next queue index of this lane: the warp advances the launch's cursor by 32 (lane 0) and shares the base.
+PT_DEV uint32_t wf_next_entry(uint32_t* cursor)
+{
+    __syncwarp();
+    uint32_t base = 0;
+    if (lane_id() == 0)
+        base = atomicAdd(cursor, 32u);
+    return __shfl_sync(0xFFFFFFFFu, base, 0) + lane_id();
+}
+
 // Which branches of the principled BSDF a material takes (lobe weights that are zero skip their layer:
 // reference Principled.h:863-972). Paths are grouped by this value before shading.
 PT_DEV uint32_t material_signature(const Material& m)
@@ -309,6 +319,45 @@ PT_DEV void wf_shade_path(const HIPRTRenderData& rd, int2 res, const Tile& tile,
     wf_load_ray(wf, slot, p);
     wf_load_hit(rd, wf, slot, pixel_index, bounce, p);
     bool alive = shade_vertex<LSS, ESS, LATER, GGX_SAMPLER>(rd, p.payload, p.hit, p.origin, p.direction, p.rng, make_int2(x, y), res, bounce);
+    alive = alive && bounce < wf_nb_bounces(rd);
+    if (alive)
+        wf_store_ray(wf, slot, p);
+    else
+        wf_finish_path(rd, pixel_index, p);
+    queue_push(wf.ray_queue[bounce & 1], wf.counts + 2 * (bounce + 1), alive, slot);
+}
+
+// ---- PHASED: SHADE split into its two halves, so that all warps of an SM run the same part of the BSDF code ---------------
+template <int LSS, int ESS, int LATER, int GGX_SAMPLER>
+PT_DEV void wf_direct_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
+{
+    const uint32_t slot = wf.sorted_queue[i];
+    uint32_t x, y, pixel_index;
+    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    PathRegs p;
+    wf_load_ray(wf, slot, p);
+    wf_load_hit(rd, wf, slot, pixel_index, bounce, p);
+    shade_vertex_direct<LSS, ESS, LATER, GGX_SAMPLER>(rd, p.payload, p.hit, p.direction, p.rng, make_int2(x, y), res, bounce);
+    wf.origin_rng[slot].w = __uint_as_float(p.rng.state);
+    wf.color[slot] = make_float4(p.payload.ray_color.r, p.payload.ray_color.g, p.payload.ray_color.b, 0.0f);
+}
+
+template <int GGX_SAMPLER>
+PT_DEV void wf_bsdf_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
+{
+    const uint32_t slot = wf.sorted_queue[i];
+    uint32_t x, y, pixel_index;
+    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    PathRegs p;
+    wf_load_ray(wf, slot, p);
+    wf_load_hit(rd, wf, slot, pixel_index, bounce, p);
+    // the flip shade_vertex_direct applied to its copy of the normals (FullPathTracer.h:173-177)
+    if (material_is_emissive(p.payload.material) && dot(-p.direction, p.hit.geometric_normal) < 0)
+    {
+        p.hit.geometric_normal = -p.hit.geometric_normal;
+        p.hit.shading_normal = -p.hit.shading_normal;
+    }
+    bool alive = shade_vertex_bounce<GGX_SAMPLER>(rd, p.payload, p.hit, p.origin, p.direction, p.rng, bounce);
     alive = alive && bounce < wf_nb_bounces(rd);
     if (alive)
         wf_store_ray(wf, slot, p);

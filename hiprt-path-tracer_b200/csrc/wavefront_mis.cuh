@@ -1,0 +1,319 @@
+// PHASED wavefront, LSS_MIS_LIGHT_BSDF: the direct-lighting half of a vertex (shade_vertex_direct) cut into phases, one kernel
+// each, so that every warp of an SM is inside the same few KB of code (ncu: `no_instruction` was the top stall of the
+// monolithic shade kernel -- its hot path does not fit the 32 KB L1.5 instruction cache) and rays are traced by a small
+// low-register kernel instead of from inside the BSDF code:
+//
+//   P1 nee_light_eval   pick an emissive triangle + point (3 draws), BSDF eval          -> shadow ray 0 + its contribution
+//   P2 nee_bsdf_sample  BSDF sample of the light MIS pair                               -> closest-hit ray 1 + BSDF value
+//   P3 env_light_eval   envmap texel by alias table / CDF (2 draws), BSDF eval          -> shadow ray 2 + its contribution
+//   P4 env_bsdf_sample  BSDF sample of the envmap MIS pair, envmap_eval                 -> shadow ray 3 + its contribution
+//   T  nee_trace        traces rays 0-3, resolves ray 1 (emission + light pdf of what was hit), the three clamps, ray_color
+//   P5 bsdf             wf_bsdf_path: BSDF sample, russian roulette, next ray (wavefront.cuh)
+//
+// The phases run in the reference's program order per path and hand the Xorshift32 state on, so the random numbers each
+// sampler sees are the ones it sees in the reference (src/Device/includes/Lights.h:115-220,277-321, Envmap.h:151-246,
+// FullPathTracer.h:173-214); rays draw nothing (alpha testing is off on this path). The reference evaluates the BSDF of
+// a light sample only when its shadow ray is unoccluded; here it is evaluated first and multiplied by the visibility:
+// the same value whenever it is used.
+#pragma once
+
+#include "wavefront.cuh"
+
+namespace pt
+{
+enum NeeSlot { NEE_LIGHT = 0, NEE_LIGHT_BSDF = 1, NEE_ENV = 2, NEE_ENV_BSDF = 3 };
+
+PT_DEV size_t nee_index(const WavefrontState& wf, int which, uint32_t slot) { return (size_t)which * wf.capacity + slot; }
+
+PT_DEV void nee_store_none(const WavefrontState& wf, int which, uint32_t slot)
+{
+    wf.nee_ray_o[nee_index(wf, which, slot)] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
+}
+
+PT_DEV void nee_store(const WavefrontState& wf, int which, uint32_t slot, float3 origin, float t_max, float3 direction, float dir_w, RGB pending, float pending_w)
+{
+    const size_t k = nee_index(wf, which, slot);
+    wf.nee_ray_o[k] = make_float4(origin.x, origin.y, origin.z, t_max);
+    wf.nee_ray_d[k] = make_float4(direction.x, direction.y, direction.z, dir_w);
+    wf.nee_pending[k] = make_float4(pending.r, pending.g, pending.b, pending_w);
+}
+
+// What sample_one_light does before it samples (Lights.h:277-300)
+enum LightsPrelude { LIGHTS_NONE = 0, LIGHTS_EMISSION = 1, LIGHTS_SAMPLE = 2 };
+PT_DEV int lights_prelude(const HIPRTRenderData& rd, const Material& material, int bounce)
+{
+    if (rd.buffers.emissive_triangles_count == 0)
+        return LIGHTS_NONE;
+    if (rd.bsdfs_data.white_furnace_mode && rd.bsdfs_data.white_furnace_mode_turn_off_emissives)
+        return LIGHTS_NONE;
+    if (material_is_emissive(material))
+        return (material.emissive_texture_used && bounce > 0) ? LIGHTS_EMISSION : LIGHTS_NONE;
+    return LIGHTS_SAMPLE;
+}
+
+// The early-outs of sample_environment_map (Envmap.h:220-246) for LSS_MIS_LIGHT_BSDF
+template <int ESS>
+PT_DEV bool envmap_prelude(const HIPRTRenderData& rd, const Material& material)
+{
+    const WorldSettings& ws = rd.world_settings;
+    if (ESS == 0)
+        return false;
+    if (ws.ambient_light_type != AMBIENT_ENVMAP || rd.bsdfs_data.white_furnace_mode)
+        return false;
+    if (material_is_emissive(material))
+        return false;
+    return ws.envmap_intensity > 0.0f;
+}
+
+// Loads the vertex the way shade_vertex_direct sees it: ray state, hit, material, normals flipped on emissive back faces
+PT_DEV void nee_load_vertex(const HIPRTRenderData& rd, const WavefrontState& wf, uint32_t slot, uint32_t pixel_index, int bounce, PathRegs& p)
+{
+    wf_load_ray(wf, slot, p);
+    wf_load_hit(rd, wf, slot, pixel_index, bounce, p);
+    if (material_is_emissive(p.payload.material) && dot(-p.direction, p.hit.geometric_normal) < 0)
+    {
+        p.hit.geometric_normal = -p.hit.geometric_normal;
+        p.hit.shading_normal = -p.hit.shading_normal;
+    }
+}
+
+PT_DEV void nee_store_rng(const WavefrontState& wf, uint32_t slot, const Rng& rng) { wf.origin_rng[slot].w = __uint_as_float(rng.state); }
+
+// ---- P1: light sample + BSDF eval (sample_one_light_MIS, first half: Lights.h:115-170) ------------------------------------
+PT_DEV void nee_light_eval_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
+{
+    const uint32_t slot = wf.sorted_queue[i];
+    uint32_t x, y, pixel_index;
+    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    PathRegs p;
+    nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
+    nee_store_none(wf, NEE_LIGHT, slot);
+    // ray 1 doubles as the "P2 has work" flag: t_max = -2 tells P2 to skip its BSDF sample (light pdf <= 0: the
+    // reference returns before sampling the BSDF, Lights.h:127-128)
+    wf.nee_ray_o[nee_index(wf, NEE_LIGHT_BSDF, slot)] = make_float4(0.0f, 0.0f, 0.0f, -2.0f);
+    if (lights_prelude(rd, p.payload.material, bounce) != LIGHTS_SAMPLE)
+        return;
+
+    const float3 view_direction = -p.direction;
+    const HitInfo& hit = p.hit;
+    bool inside_surface = dot(view_direction, hit.geometric_normal) < 0;
+    float inside_surface_multiplier = inside_surface ? -1.0f : 1.0f;
+    float3 evaluated_point = hit.inter_point + hit.shading_normal * 1.0e-4f * inside_surface_multiplier;
+
+    float light_sample_pdf;
+    LightSourceInformation light_info;
+    float3 random_light_point = uniform_sample_one_emissive_triangle(rd, p.rng, light_sample_pdf, light_info);
+    nee_store_rng(wf, slot, p.rng);
+    if (light_sample_pdf <= 0.0f)
+        return;
+    wf.nee_ray_o[nee_index(wf, NEE_LIGHT_BSDF, slot)].w = -1.0f;   // P2 runs
+
+    float3 shadow_ray_direction = random_light_point - evaluated_point;
+    float distance_to_light = length(shadow_ray_direction);
+    float3 dir = shadow_ray_direction / distance_to_light;
+
+    float dot_light_source = fabsf(dot(light_info.light_source_normal, -dir));
+    if (dot_light_source > 0.0f)
+    {
+        float bsdf_pdf;
+        RayVolumeState trash = p.payload.volume_state;
+        RGB bsdf_color = bsdf_eval(rd, p.payload.material, trash, view_direction, hit.shading_normal, dir, bsdf_pdf);
+        if (bsdf_pdf != 0.0f)
+        {
+            light_sample_pdf *= distance_to_light * distance_to_light;
+            light_sample_pdf /= dot_light_source;
+            float mis_weight = balance_heuristic(light_sample_pdf, bsdf_pdf);
+            float cosine_term = maxf(dot(hit.shading_normal, dir), 0.0f);
+            RGB light_source_radiance_mis = bsdf_color * cosine_term * light_info.emission * mis_weight / light_sample_pdf;
+            nee_store(wf, NEE_LIGHT, slot, evaluated_point, distance_to_light, dir, 0.0f, light_source_radiance_mis, 0.0f);
+        }
+    }
+}
+
+// ---- P2: BSDF sample of the light MIS pair (Lights.h:172-190) ----------------------------------------------------------------
+template <int GGX_SAMPLER>
+PT_DEV void nee_bsdf_sample_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
+{
+    const uint32_t slot = wf.sorted_queue[i];
+    if (wf.nee_ray_o[nee_index(wf, NEE_LIGHT_BSDF, slot)].w != -1.0f)
+        return;
+    uint32_t x, y, pixel_index;
+    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    PathRegs p;
+    nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
+
+    const float3 view_direction = -p.direction;
+    const HitInfo& hit = p.hit;
+    bool inside_surface = dot(view_direction, hit.geometric_normal) < 0;
+    float inside_surface_multiplier = inside_surface ? -1.0f : 1.0f;
+    float3 evaluated_point = hit.inter_point + hit.shading_normal * 1.0e-4f * inside_surface_multiplier;
+
+    float direction_pdf;
+    float3 sampled_bsdf_direction;
+    float3 bsdf_shadow_ray_origin = evaluated_point;
+    RayVolumeState trash = p.payload.volume_state;
+    RGB bsdf_color = bsdf_sample<GGX_SAMPLER>(rd, p.payload.material, trash, view_direction, hit.shading_normal, hit.geometric_normal, sampled_bsdf_direction, direction_pdf, p.rng);
+    nee_store_rng(wf, slot, p.rng);
+    bool refraction_sampled = dot(sampled_bsdf_direction, hit.shading_normal * inside_surface_multiplier) < 0;
+    if (refraction_sampled)
+        bsdf_shadow_ray_origin = hit.inter_point + hit.shading_normal * 1.0e-4f * inside_surface_multiplier * -1.0f;
+
+    if (direction_pdf > 0)
+    {
+        float cosine_term = fabsf(dot(hit.shading_normal, sampled_bsdf_direction));
+        nee_store(wf, NEE_LIGHT_BSDF, slot, bsdf_shadow_ray_origin, 1.0e35f, sampled_bsdf_direction, cosine_term, bsdf_color, direction_pdf);
+    }
+}
+
+// ---- P3: envmap sample + BSDF eval (sample_environment_map_with_mis, first half: Envmap.h:151-185) ---------------------------
+template <int ESS>
+PT_DEV void env_light_eval_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
+{
+    const uint32_t slot = wf.sorted_queue[i];
+    uint32_t x, y, pixel_index;
+    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    PathRegs p;
+    nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
+    nee_store_none(wf, NEE_ENV, slot);
+    wf.nee_ray_o[nee_index(wf, NEE_ENV_BSDF, slot)] = make_float4(0.0f, 0.0f, 0.0f, -2.0f);
+    if (!envmap_prelude<ESS>(rd, p.payload.material))
+        return;
+    wf.nee_ray_o[nee_index(wf, NEE_ENV_BSDF, slot)].w = -1.0f;   // P4 runs
+
+    const float3 view_direction = -p.direction;
+    const HitInfo& hit = p.hit;
+    float envmap_pdf;
+    float3 sampled_direction;
+    RGB envmap_color = envmap_sample<ESS == 0 ? 2 : ESS>(rd.world_settings, sampled_direction, envmap_pdf, p.rng);
+    nee_store_rng(wf, slot, p.rng);
+
+    float cosine_term = dot(hit.shading_normal, sampled_direction);
+    if (envmap_pdf > 0.0f && cosine_term > 0.0f)
+    {
+        float bsdf_pdf;
+        RayVolumeState trash = p.payload.volume_state;
+        RGB bsdf_color = bsdf_eval(rd, p.payload.material, trash, view_direction, hit.shading_normal, sampled_direction, bsdf_pdf);
+        float mis_weight = balance_heuristic(envmap_pdf, bsdf_pdf);
+        RGB envmap_mis_contribution = bsdf_color * cosine_term * mis_weight * envmap_color / envmap_pdf;
+        nee_store(wf, NEE_ENV, slot, hit.inter_point, 1.0e35f, sampled_direction, 0.0f, envmap_mis_contribution, 0.0f);
+    }
+}
+
+// ---- P4: BSDF sample of the envmap MIS pair (Envmap.h:187-215) ----------------------------------------------------------------
+template <int GGX_SAMPLER>
+PT_DEV void env_bsdf_sample_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
+{
+    const uint32_t slot = wf.sorted_queue[i];
+    if (wf.nee_ray_o[nee_index(wf, NEE_ENV_BSDF, slot)].w != -1.0f)
+        return;
+    uint32_t x, y, pixel_index;
+    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    PathRegs p;
+    nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
+
+    const float3 view_direction = -p.direction;
+    const HitInfo& hit = p.hit;
+    float bsdf_sample_pdf;
+    float3 bsdf_sampled_dir;
+    RayVolumeState trash = p.payload.volume_state;
+    RGB bsdf_color = bsdf_sample<GGX_SAMPLER>(rd, p.payload.material, trash, view_direction, hit.shading_normal, hit.geometric_normal, bsdf_sampled_dir, bsdf_sample_pdf, p.rng);
+    nee_store_rng(wf, slot, p.rng);
+
+    float cosine_term = fabsf(dot(hit.shading_normal, bsdf_sampled_dir));
+    if (bsdf_sample_pdf > 0.0f)
+    {
+        float envmap_eval_pdf;
+        RGB envmap_radiance = envmap_eval(rd, bsdf_sampled_dir, envmap_eval_pdf);
+        if (envmap_eval_pdf > 0.0f)
+        {
+            float mis_weight = balance_heuristic(bsdf_sample_pdf, envmap_eval_pdf);
+            RGB bsdf_mis_contribution = envmap_radiance * mis_weight * cosine_term * bsdf_color / bsdf_sample_pdf;
+            nee_store(wf, NEE_ENV_BSDF, slot, hit.inter_point, 1.0e35f, bsdf_sampled_dir, 0.0f, bsdf_mis_contribution, 0.0f);
+        }
+    }
+}
+
+// ---- T: trace the NEE rays of a vertex, finish shade_vertex_direct (FullPathTracer.h:195-214) ---------------------------------
+PT_DEV RGB nee_shadowed_contribution(const HIPRTRenderData& rd, const WavefrontState& wf, int which, uint32_t slot, int last_prim, Rng& rng)
+{
+    const size_t k = nee_index(wf, which, slot);
+    const float4 o = wf.nee_ray_o[k];
+    if (!(o.w > 0.0f))
+        return RGB(0.0f);
+    const float4 d = wf.nee_ray_d[k];
+    if (evaluate_shadow_ray(rd, f3(o.x, o.y, o.z), f3(d.x, d.y, d.z), o.w, last_prim, rng))
+        return RGB(0.0f);
+    const float4 c = wf.nee_pending[k];
+    return RGB(c.x, c.y, c.z);
+}
+
+template <int ESS>
+PT_DEV void nee_trace_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
+{
+    const uint32_t slot = wf.sorted_queue[i];
+    uint32_t x, y, pixel_index;
+    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    const SimplifiedRendererMaterial* mp = bounce == 0 ? rd.g_buffer.materials + pixel_index : reinterpret_cast<const SimplifiedRendererMaterial*>(wf.materials) + slot;
+    // only the emission fields of the material matter here
+    Material m;
+    m.emissive_texture_used = mp->emissive_texture_used;
+    m.emission_strength = mp->emission_strength;
+    m.emission = mp->emission;
+    const int last_prim = bounce == 0 ? rd.g_buffer.first_hit_prim_index[pixel_index] : __float_as_int(wf.hit_point[slot].w);
+    Rng rng(0u);   // shadow rays draw nothing with alpha testing off
+
+    RGB light_direct(0.0f);
+    const int prelude = lights_prelude(rd, m, bounce);
+    if (prelude == LIGHTS_EMISSION)
+        light_direct = material_emission(m);
+    else if (prelude == LIGHTS_SAMPLE)
+    {
+        RGB light_source_radiance_mis = nee_shadowed_contribution(rd, wf, NEE_LIGHT, slot, last_prim, rng);
+        RGB bsdf_radiance_mis;
+        const size_t k = nee_index(wf, NEE_LIGHT_BSDF, slot);
+        const float4 o = wf.nee_ray_o[k];
+        bool sampled = o.w != -2.0f;
+        if (o.w > 0.0f)
+        {
+            const float4 d = wf.nee_ray_d[k];
+            const float3 sampled_bsdf_direction = f3(d.x, d.y, d.z);
+            ShadowLightRayHitInfo light_hit;
+            bool inter_found = evaluate_shadow_light_ray(rd, f3(o.x, o.y, o.z), sampled_bsdf_direction, 1.0e35f, light_hit, last_prim, rng);
+            if (inter_found && !light_hit.hit_emission.is_black())
+            {
+                const float4 c = wf.nee_pending[k];
+                const RGB bsdf_color(c.x, c.y, c.z);
+                const float direction_pdf = c.w, cosine_term = d.w;
+                float light_pdf = pdf_of_emissive_triangle_hit(rd, light_hit, sampled_bsdf_direction);
+                float mis_weight = balance_heuristic(direction_pdf, light_pdf);
+                bsdf_radiance_mis = bsdf_color * cosine_term * light_hit.hit_emission * mis_weight / direction_pdf;
+            }
+        }
+        RGB direct;
+        if (sampled)
+            direct += light_source_radiance_mis + bsdf_radiance_mis;
+        else
+            direct += RGB(0.0f);
+        light_direct = direct / rd.render_settings.number_of_light_samples;
+    }
+
+    RGB envmap_direct(0.0f);
+    if (envmap_prelude<ESS>(rd, m))
+    {
+        RGB envmap_mis_contribution = nee_shadowed_contribution(rd, wf, NEE_ENV, slot, last_prim, rng);
+        RGB bsdf_mis_contribution = nee_shadowed_contribution(rd, wf, NEE_ENV_BSDF, slot, last_prim, rng);
+        envmap_direct = bsdf_mis_contribution + envmap_mis_contribution;
+    }
+
+    light_direct = clamp_light_contribution(light_direct, rd.render_settings.direct_contribution_clamp, bounce == 0);
+    envmap_direct = clamp_light_contribution(envmap_direct, rd.render_settings.envmap_contribution_clamp, bounce == 0);
+
+    const float4 t = wf.throughput[slot], c = wf.color[slot];
+    RGB ray_color(c.x, c.y, c.z);
+    if (bounce == 0)
+        ray_color += material_emission(m);
+    RGB indirect = (light_direct + envmap_direct) * RGB(t.x, t.y, t.z);
+    ray_color += clamp_light_contribution(indirect, rd.render_settings.indirect_contribution_clamp, bounce > 0);
+    wf.color[slot] = make_float4(ray_color.r, ray_color.g, ray_color.b, 0.0f);
+}
+} // namespace pt

@@ -113,7 +113,7 @@ class Context:
     # ---- counters ---------------------------------------------------------------------------
     def set_path_mode(self, mode):
         """'megakernel' | 'fused' | 'split' (b200pt_set_path_mode): the shape FullPathTracer runs in."""
-        m = {"megakernel": 0, "fused": 1, "split": 2}[mode] if isinstance(mode, str) else int(mode)
+        m = {"megakernel": 0, "fused": 1, "split": 2, "phased": 3}[mode] if isinstance(mode, str) else int(mode)
         _capi.check(self.lib.b200pt_set_path_mode(self.handle, C.c_int(m)), "b200pt_set_path_mode")
 
     def counters_enable(self, enable=True):

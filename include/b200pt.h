@@ -137,7 +137,9 @@ B200PT_API int b200pt_bvh_info(b200pt_bvh* bvh, unsigned* out_node_count, unsign
 B200PT_API int b200pt_kernel_variant_select(b200pt_ctx* ctx, const b200pt_options* options);
 /* Shape of FullPathTracer: 0 = megakernel (one launch, one thread per pixel, as the reference), 1 = wavefront with one
  * fused trace+shade launch per bounce over a compacted queue of live paths, 2 = wavefront with separate extend and
- * shade launches per bounce (default). Same per-path arithmetic and RNG order in all three: same bits. */
+ * shade launches per bounce and the shade queue grouped by material signature, 3 = (default) as 2 with the shade step
+ * cut into phases (light eval / BSDF samples / NEE rays / bounce), one small kernel each.
+ * Same per-path arithmetic and RNG order in all four: same bits. */
 B200PT_API int b200pt_set_path_mode(b200pt_ctx* ctx, int mode);
 B200PT_API int b200pt_launch_CameraRays(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream);
 B200PT_API int b200pt_launch_FullPathTracer(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream);

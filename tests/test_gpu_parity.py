@@ -155,6 +155,31 @@ def test_tile_sharding_is_bit_identical_and_deterministic(pt, wl, ctx):
     g.close()
 
 
+@pytest.mark.parametrize("variant", [dict(lss="mis", ess="none"), dict(lss="ris", ess="alias_table")])
+def test_path_modes_are_bit_identical(pt, wl, ctx, variant):
+    """megakernel / fused / split / phased wavefront shapes of FullPathTracer run the same per-path arithmetic in the same
+    RNG order: the accumulated frames must be equal bit for bit (so parity with the oracle carries over to every shape)."""
+    cfg = wl.cornell(320, 200)
+    cfg["options"] = dict(ggx=0, later=3, **variant)
+    g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="cpu")
+    frames = {}
+    try:
+        for mode in ("megakernel", "fused", "split", "phased"):
+            ctx.set_path_mode(mode)
+            g.reset()
+            g.resize(320, 200)
+            wl.apply_settings(g.render_settings, cfg["settings"])
+            for _ in range(3):
+                g.render_frame()
+            g.synchronize()
+            frames[mode] = g.download("pixels").copy()
+    finally:
+        ctx.set_path_mode("phased")
+        g.close()
+    for mode in ("fused", "split", "phased"):
+        assert np.array_equal(frames["megakernel"], frames[mode]), mode
+
+
 def test_edge_cases_empty_scene_and_misses(pt, ctx):
     """Empty scene (0 triangles): every query misses; rays pointing away from the geometry miss; zero-length batches work."""
     bvh = ctx.build_bvh(np.zeros((0, 3), np.float32), np.zeros((0,), np.int32))

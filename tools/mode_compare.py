@@ -19,7 +19,8 @@ cfg = getattr(wl, name)(W, H)
 ctx = pt.Context(0)
 g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="cpu")
 frames = {}
-for mode in ("megakernel", "fused", "split"):
+MODES = os.environ.get("MODES", "megakernel,fused,split,phased").split(",")
+for mode in MODES:
     ctx.set_path_mode(mode)
     g.reset()
     g.resize(W, H)
@@ -31,9 +32,9 @@ for mode in ("megakernel", "fused", "split"):
         ms.append(g.last_kernel_ms("FullPathTracer"))
     frames[mode] = g.download("pixels").copy()
     print(f"{mode:10s} FullPathTracer ms/pass: first {ms[0]:.3f}  median {sorted(ms)[len(ms)//2]:.3f}  mean/px {frames[mode].mean()/spp:.6f}")
-for mode in ("fused", "split"):
-    same = np.array_equal(frames["megakernel"], frames[mode])
-    print(f"{mode} == megakernel bit for bit: {same}")
+for mode in MODES[1:]:
+    same = np.array_equal(frames[MODES[0]], frames[mode])
+    print(f"{mode} == {MODES[0]} bit for bit: {same}")
     if not same:
-        d = np.abs(frames["megakernel"] - frames[mode])
+        d = np.abs(frames[MODES[0]] - frames[mode])
         print("  max abs diff", d.max(), "pixels differing", int((d.max(axis=2) > 0).sum()))
