@@ -153,8 +153,74 @@ void GPURenderer::set_scene(const Scene& scene)
     b.textures_dims = m_textures_dims.get_device_pointer();
 }
 
+// Alias table of the envmap's luminance distribution (Vose's method, double precision, FIFO work lists), the table
+// envmap_sample draws texels from. Same construction rule as the reference's Image32Bit::compute_alias_table
+// (src/Image/Image.cpp:579-659) -- per-texel luminance in float over at most 3 channels (:454-474), normalised to
+// mean 1, "< 1" goes to the small list, a large entry is re-queued as large only while it stays > 1 -- so the
+// tables are identical entry for entry.
+void compute_envmap_alias_table(const float* texels, int width, int height, int channels, std::vector<float>& probas, std::vector<int>& alias, float& luminance_total_sum)
+{
+    const size_t n = (size_t)width * height;
+    std::vector<double> scaled(n);
+    const float weights[3] = {0.3086f, 0.6094f, 0.0820f};
+    double sum = 0.0;
+    for (size_t i = 0; i < n; i++)
+    {
+        float luminance = 0.0f;
+        for (int c = 0; c < (channels < 3 ? channels : 3); c++)
+            luminance += texels[i * channels + c] * weights[c];
+        scaled[i] = (double)luminance;
+        sum += (double)luminance;
+    }
+    luminance_total_sum = (float)sum;
+    for (double& v : scaled)
+    {
+        v /= sum;
+        v *= (double)(width * height);
+    }
+
+    probas.assign(n, 0.0f);
+    alias.assign(n, 0);
+    // FIFO lists as index rings: an entry is pushed at most once per pop, so n + 1 slots suffice for each
+    std::vector<int> small_list(n + 1), large_list(n + 1);
+    size_t small_head = 0, small_tail = 0, large_head = 0, large_tail = 0;
+    auto push = [&](std::vector<int>& list, size_t& tail, int v) { list[tail] = v; tail = tail == n ? 0 : tail + 1; };
+    auto pop = [&](std::vector<int>& list, size_t& head) { int v = list[head]; head = head == n ? 0 : head + 1; return v; };
+    for (size_t i = 0; i < n; i++)
+    {
+        if (scaled[i] < 1.0)
+            push(small_list, small_tail, (int)i);
+        else
+            push(large_list, large_tail, (int)i);
+    }
+    while (small_head != small_tail && large_head != large_tail)
+    {
+        const int s = pop(small_list, small_head);
+        const int l = pop(large_list, large_head);
+        probas[s] = (float)scaled[s];
+        alias[s] = l;
+        scaled[l] = (scaled[l] + scaled[s]) - 1.0;
+        if (scaled[l] > 1.0)
+            push(large_list, large_tail, l);
+        else
+            push(small_list, small_tail, l);
+    }
+    while (large_head != large_tail)
+        probas[pop(large_list, large_head)] = 1.0f;
+    while (small_head != small_tail)
+        probas[pop(small_list, small_head)] = 1.0f;
+}
+
 void GPURenderer::set_envmap(const float* texels, int width, int height, int channels, const float* alias_probas, const int* alias_alias, float total_sum)
 {
+    std::vector<float> own_probas;
+    std::vector<int> own_alias;
+    if (texels != nullptr && width > 0 && height > 0 && (alias_probas == nullptr || alias_alias == nullptr))
+    {
+        compute_envmap_alias_table(texels, width, height, channels, own_probas, own_alias, total_sum);
+        alias_probas = own_probas.data();
+        alias_alias = own_alias.data();
+    }
     WorldSettings& w = m_render_data.world_settings;
     if (m_envmap) b200pt_tex_destroy(m_ctx, m_envmap);
     m_envmap = nullptr;

@@ -122,6 +122,8 @@ enum class SeedSchedule
            // (src/Renderer/CPURenderer.cpp:264-296) -- the mode parity runs use
 };
 
+void compute_envmap_alias_table(const float* texels, int width, int height, int channels, std::vector<float>& probas, std::vector<int>& alias, float& luminance_total_sum);
+
 class GPURenderer
 {
 public:

@@ -109,6 +109,19 @@ int b200pt_renderer_set_envmap(b200pt_renderer* r, const float* texels, int widt
     return guarded([&] { r->renderer.set_envmap(texels, width, height, channels, alias_probas, alias_alias, total_sum); });
 }
 
+int b200pt_host_compute_alias_table(const float* texels, int width, int height, int channels, float* out_probas, int* out_alias, float* out_total_sum)
+{
+    return guarded([&] {
+        if (!texels || width <= 0 || height <= 0 || channels < 1 || !out_probas || !out_alias || !out_total_sum)
+            throw std::runtime_error("b200pt_host_compute_alias_table: invalid argument");
+        std::vector<float> probas;
+        std::vector<int> alias;
+        b200pt_host::compute_envmap_alias_table(texels, width, height, channels, probas, alias, *out_total_sum);
+        std::copy(probas.begin(), probas.end(), out_probas);
+        std::copy(alias.begin(), alias.end(), out_alias);
+    });
+}
+
 int b200pt_renderer_set_camera(b200pt_renderer* r, const HIPRTCamera* camera)
 {
     r->renderer.set_camera(*camera);

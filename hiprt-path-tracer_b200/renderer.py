@@ -169,12 +169,14 @@ class GPURenderer:
             _ptr(a["normals"]), _ptr(a["has_normals"]), _ptr(a["texcoords"]), _ptr(a["material_indices"]), _ptr(a["materials"]),
             C.c_int(scene.material_count), _ptr(a["emissive"]), C.c_int(len(a["emissive"]))), "b200pt_renderer_set_scene")
 
-    def set_envmap(self, texels, alias_probas, alias_alias, total_sum):
+    def set_envmap(self, texels, alias_probas=None, alias_alias=None, total_sum=0.0):
+        """Without an alias table the host layer builds it (GPURenderer.cpp: compute_envmap_alias_table)."""
         texels = np.ascontiguousarray(texels, dtype=np.float32)
         h, w, ch = texels.shape
+        probas = None if alias_probas is None else np.ascontiguousarray(alias_probas, dtype=np.float32)
+        alias = None if alias_alias is None else np.ascontiguousarray(alias_alias, dtype=np.int32)
         _capi.check_host(self.host.b200pt_renderer_set_envmap(self.handle, _ptr(texels), C.c_int(w), C.c_int(h), C.c_int(ch),
-                                                              _ptr(np.ascontiguousarray(alias_probas, dtype=np.float32)),
-                                                              _ptr(np.ascontiguousarray(alias_alias, dtype=np.int32)), C.c_float(total_sum)), "b200pt_renderer_set_envmap")
+                                                              _ptr(probas), _ptr(alias), C.c_float(total_sum)), "b200pt_renderer_set_envmap")
 
     def set_camera(self, camera):
         self.host.b200pt_renderer_set_camera(self.handle, C.byref(camera))

@@ -2,6 +2,7 @@
 kernel options and run-time settings. The same description is applied to the CUDA renderer and to the oracle."""
 import os
 
+from . import procedural
 from . import scene as sc
 from .luts import load_brdf_luts
 
@@ -16,6 +17,46 @@ def cornell(width, height):
         "name": f"cornell_pbr {width}x{height}, 8 bounces, LSS_MIS_LIGHT_BSDF, uniform sky",
         "scene": scene, "camera": sc.scene_camera(scene, width, height), "width": width, "height": height,
         "options": dict(lss="mis", ess="none", ggx=0, later=3), "oracle_variant": "mis", "envmap": None,
+        "settings": dict(nb_bounces=8, do_alpha_testing=0, enable_adaptive_sampling=0, samples_per_frame=1),
+    }
+
+
+_CACHE = {}
+
+
+def synthetic(width, height, quads=1581, spheres=3906, subdivisions=3, ggx=0, envmap_size=(2048, 1024)):
+    """C3: procedural ~10 M-triangle terrain + spheres (9 998 802 triangles at the defaults), 64 random principled materials,
+    procedural HDR envmap sampled through its alias table with BSDF MIS, no emissive geometry."""
+    key = ("synthetic", quads, spheres, subdivisions, envmap_size)
+    if key not in _CACHE:
+        _CACHE[key] = (procedural.terrain_and_spheres(quads, spheres, subdivisions), procedural.procedural_envmap(*envmap_size))
+    scene, env = _CACHE[key]
+    return {
+        "name": f"synthetic terrain+spheres {scene.triangle_count} triangles {width}x{height}, 8 bounces, LSS_MIS_LIGHT_BSDF, envmap {envmap_size[0]}x{envmap_size[1]} alias table + BSDF MIS",
+        "scene": scene, "camera": sc.scene_camera(scene, width, height), "width": width, "height": height,
+        "options": dict(lss="mis", ess="alias_table", ggx=ggx, later=3), "oracle_variant": "mis" if ggx == 0 else "mis_caps",
+        "envmap": {"texels": env, "alias_probas": None, "alias_alias": None, "total_sum": 0.0},
+        "settings": dict(nb_bounces=8, do_alpha_testing=0, enable_adaptive_sampling=0, samples_per_frame=1),
+    }
+
+
+def synthetic_small(width, height, ggx=0):
+    """A parity-sized cut of C3 (~37 k triangles, 256x128 envmap) that the CPU oracle renders in seconds."""
+    cfg = synthetic(width, height, quads=96, spheres=60, subdivisions=2, ggx=ggx, envmap_size=(256, 128))
+    return cfg
+
+
+def many_lights(width, height, boxes=2000, lights=100_000):
+    """C4: closed room + diffuse boxes + 100 000 small emissive triangles; ReSTIR DI with light presampling and the fused
+    spatiotemporal pass, RIS on later bounces."""
+    key = ("many_lights", boxes, lights)
+    if key not in _CACHE:
+        _CACHE[key] = procedural.many_lights_room(boxes, lights)
+    scene = _CACHE[key]
+    return {
+        "name": f"many-light room {scene.triangle_count} triangles ({len(scene.emissive)} emissive) {width}x{height}, 8 bounces, LSS_RESTIR_DI (presampled lights, fused spatiotemporal), later bounces RIS",
+        "scene": scene, "camera": sc.scene_camera(scene, width, height), "width": width, "height": height,
+        "options": dict(lss="restir_di", ess="none", ggx=0, later=3), "oracle_variant": "restir", "envmap": None,
         "settings": dict(nb_bounces=8, do_alpha_testing=0, enable_adaptive_sampling=0, samples_per_frame=1),
     }
 

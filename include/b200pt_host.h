@@ -31,6 +31,9 @@ B200PT_API int b200pt_renderer_set_scene(b200pt_renderer* r, const float* vertic
                                          const int* emissive_triangle_indices, int emissive_triangle_count);
 B200PT_API int b200pt_renderer_set_envmap(b200pt_renderer* r, const float* texels, int width, int height, int channels,
                                           const float* alias_probas, const int* alias_alias, float total_sum);
+/* The alias table set_envmap builds when none is passed (replaces Image32Bit::compute_alias_table, src/Image/Image.cpp:579-659,
+ * called from GPURenderer::set_envmap, src/Renderer/GPURenderer.cpp:1136-1174). Host-only: needs no device. */
+B200PT_API int b200pt_host_compute_alias_table(const float* texels, int width, int height, int channels, float* out_probas, int* out_alias, float* out_total_sum);
 B200PT_API int b200pt_renderer_set_camera(b200pt_renderer* r, const HIPRTCamera* camera);
 B200PT_API int b200pt_renderer_resize(b200pt_renderer* r, int width, int height);
 B200PT_API int b200pt_renderer_set_tile(b200pt_renderer* r, const b200pt_tile* tile);
