@@ -207,7 +207,11 @@ static int ensure_wavefront(b200pt_ctx* ctx, uint32_t paths, uint32_t bounces)
     ok &= (wf.bucket_count = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * pt::kSortBuckets))) != nullptr;
     if (ok)
         ok &= cudaMemset(wf.bucket_count, 0, sizeof(uint32_t) * pt::kSortBuckets) == cudaSuccess;
-    ok &= (wf.counts = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * (2 + pt::kCursorsPerBounce) * (max_bounces + 2)))) != nullptr;
+    ok &= (wf.hit_tuvp = static_cast<float4*>(alloc(2 * n * sizeof(float4)))) != nullptr;
+    ok &= (wf.hit_tri_slot = static_cast<uint32_t*>(alloc(2 * n * 4))) != nullptr;
+    ok &= (wf.any_queue = static_cast<uint32_t*>(alloc(3 * n * 4))) != nullptr;
+    ok &= (wf.closest_queue = static_cast<uint32_t*>(alloc(n * 4))) != nullptr;
+    ok &= (wf.counts = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * (pt::kCountsPerBounce + pt::kCursorsPerBounce) * (max_bounces + 2)))) != nullptr;
     if (!ok)
     {
         cudaError_t e = cudaGetLastError();
@@ -220,7 +224,7 @@ static int ensure_wavefront(b200pt_ctx* ctx, uint32_t paths, uint32_t bounces)
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
     wf.sm_count = (uint32_t)sms;
-    wf.cursors = wf.counts + 2 * (max_bounces + 2);
+    wf.cursors = wf.counts + pt::kCountsPerBounce * (max_bounces + 2);
     wf.capacity = capacity;
     wf.max_bounces = max_bounces;
     return B200PT_SUCCESS;

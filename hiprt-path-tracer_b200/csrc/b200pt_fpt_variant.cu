@@ -33,7 +33,7 @@ __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_bounce0)(const __grid
 
 __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_bounce)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce)
 {
-    PT_FOR_EACH_QUEUED(i, wf.counts[2 * bounce], 0)
+    PT_FOR_EACH_QUEUED(i, wf.counts[kCountsPerBounce * bounce], 0)
         wf_bounce_path<PT_LSS, PT_ESS, PT_LATER, PT_GGX>(rd, res, tile, wf, bounce, i);
 }
 
@@ -48,7 +48,7 @@ __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_gen)(const __grid_con
 
 __global__ void __launch_bounds__(128) PT_VARIANT_NAME(k_wf_extend)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce)
 {
-    PT_FOR_EACH_QUEUED(i, wf.counts[2 * bounce], 0)
+    PT_FOR_EACH_QUEUED(i, wf.counts[kCountsPerBounce * bounce], 0)
         wf_extend_path<PT_ESS>(rd, res, tile, wf, bounce, i);
 }
 
@@ -60,25 +60,25 @@ __global__ void __launch_bounds__(kSortBuckets) PT_VARIANT_NAME(k_wf_scan)(const
 
 __global__ void __launch_bounds__(256) PT_VARIANT_NAME(k_wf_scatter)(const __grid_constant__ WavefrontState wf, int bounce)
 {
-    PT_FOR_EACH_QUEUED(i, wf.counts[2 * bounce + 1], 1)
+    PT_FOR_EACH_QUEUED(i, wf.counts[kCountsPerBounce * bounce + 1], 1)
         wf_scatter_path(wf, i);
 }
 
 __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_shade)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce)
 {
-    PT_FOR_EACH_QUEUED(i, wf.counts[2 * bounce + 1], 2)
+    PT_FOR_EACH_QUEUED(i, wf.counts[kCountsPerBounce * bounce + 1], 2)
         wf_shade_path<PT_LSS, PT_ESS, PT_LATER, PT_GGX>(rd, res, tile, wf, bounce, i);
 }
 
 __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_direct)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce)
 {
-    PT_FOR_EACH_QUEUED(i, wf.counts[2 * bounce + 1], 2)
+    PT_FOR_EACH_QUEUED(i, wf.counts[kCountsPerBounce * bounce + 1], 2)
         wf_direct_path<PT_LSS, PT_ESS, PT_LATER, PT_GGX>(rd, res, tile, wf, bounce, i);
 }
 
 __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_bsdf)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce)
 {
-    PT_FOR_EACH_QUEUED(i, wf.counts[2 * bounce + 1], 7)
+    PT_FOR_EACH_QUEUED(i, wf.counts[kCountsPerBounce * bounce + 1], 7)
         wf_bsdf_path<PT_GGX>(rd, res, tile, wf, bounce, i);
 }
 
@@ -86,14 +86,25 @@ __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_bsdf)(const __grid_co
 #define PT_QUEUE_KERNEL(NAME, BOUNDS, KID, CALL)                                                                                                                            \
     __global__ void __launch_bounds__(BOUNDS) PT_VARIANT_NAME(NAME)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce) \
     {                                                                                                                                                                  \
-        PT_FOR_EACH_QUEUED(i, wf.counts[2 * bounce + 1], KID)                                                                                                          \
+        PT_FOR_EACH_QUEUED(i, wf.counts[kCountsPerBounce * bounce + 1], KID)                                                                                                          \
             CALL(rd, res, tile, wf, bounce, i);                                                                                                                        \
     }
 PT_QUEUE_KERNEL(k_wf_nee_light_eval, 64, 2, nee_light_eval_path)
 PT_QUEUE_KERNEL(k_wf_nee_bsdf_sample, 64, 3, nee_bsdf_sample_path<PT_GGX>)
 PT_QUEUE_KERNEL(k_wf_env_light_eval, 64, 4, env_light_eval_path<PT_ESS>)
 PT_QUEUE_KERNEL(k_wf_env_bsdf_sample, 64, 5, env_bsdf_sample_path<PT_GGX>)
-PT_QUEUE_KERNEL(k_wf_nee_trace, 128, 6, nee_trace_path<PT_ESS>)
+
+__global__ void __launch_bounds__(128) PT_VARIANT_NAME(k_wf_surface)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce)
+{
+    PT_FOR_EACH_QUEUED(i, wf.counts[kCountsPerBounce * bounce], 8)
+        wf_surface_path<PT_ESS>(rd, res, tile, wf, bounce, i);
+}
+
+__global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_bsdf_resolved)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce, bool lights_sampled, bool envmap_sampled)
+{
+    PT_FOR_EACH_QUEUED(i, wf.counts[kCountsPerBounce * bounce + 1], 7)
+        wf_bsdf_resolved_path<PT_ESS, PT_GGX>(rd, res, tile, wf, bounce, i, lights_sampled, envmap_sampled);
+}
 #endif
 
 cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const WavefrontState* wf, int mode)
@@ -116,7 +127,7 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
     // SM (an uncapped grid of mostly empty blocks costs ~1.5 ns per block: 50 us per launch at 1080p)
     const unsigned cap = wf->sm_count * 16u;
     auto blocks = [&](unsigned block) { unsigned g = (paths + block - 1) / block, c = cap * 64u / block; return g < c ? g : c; };
-    cudaError_t e = cudaMemsetAsync(wf->counts, 0, sizeof(uint32_t) * (2 + kCursorsPerBounce) * (wf->max_bounces + 2), stream);
+    cudaError_t e = cudaMemsetAsync(wf->counts, 0, sizeof(uint32_t) * (kCountsPerBounce + kCursorsPerBounce) * (wf->max_bounces + 2), stream);
     if (e != cudaSuccess)
         return e;
     if (mode == WF_FUSED)
@@ -126,10 +137,36 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
             PT_VARIANT_NAME(k_wf_bounce)<<<blocks(64), 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
         return cudaGetLastError();
     }
+#if PT_LSS == 3
+    // alpha testing would make shadow rays draw random numbers (FilterFunction.h:42): then the phases cannot be reordered
+    const bool phased_mis = mode == WF_PHASED && rd->render_settings.number_of_light_samples == 1 && !rd->render_settings.do_alpha_testing;
+#else
+    const bool phased_mis = false;
+#endif
+#ifdef PT_COUNTERS
+    TraversalCounters* const counters = reinterpret_cast<TraversalCounters*>(rd->hiprt_function_table);
+#else
+    TraversalCounters* const counters = nullptr;
+#endif
+    const unsigned trace_blocks = wf->sm_count * 8u;   // persistent: 8 resident blocks of 128 threads per SM
+    (void)counters; (void)trace_blocks;
     for (int bounce = 0; bounce <= nb_bounces; bounce++)
     {
+        uint32_t* const counts = wf->counts + kCountsPerBounce * bounce;
+        uint32_t* const cursors = wf->cursors + kCursorsPerBounce * bounce;
+        (void)counts; (void)cursors;
         if (bounce == 0)
             PT_VARIANT_NAME(k_wf_gen)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile, *wf);
+#if PT_LSS == 3
+        else if (phased_mis)
+        {
+            RayQueueView q = {wf->ray_queue[(bounce - 1) & 1], counts + 0, cursors + 0, wf->origin_rng, wf->dir_prim, wf->hit_tuvp, wf->hit_tri_slot, nullptr};
+            e = PT_SUFFIXED(launch_trace_queue)(rd->geom, q, false, trace_blocks, counters, stream);
+            if (e != cudaSuccess)
+                return e;
+            PT_VARIANT_NAME(k_wf_surface)<<<blocks(128), 128, 0, stream>>>(*rd, res, tile, *wf, bounce);
+        }
+#endif
         else
             PT_VARIANT_NAME(k_wf_extend)<<<blocks(128), 128, 0, stream>>>(*rd, res, tile, *wf, bounce);
         PT_VARIANT_NAME(k_wf_scan)<<<1, kSortBuckets, 0, stream>>>(*wf);
@@ -139,19 +176,36 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
         if (e != cudaSuccess)
             return e;
 #if PT_LSS == 3
-        // alpha testing would make shadow rays draw random numbers (FilterFunction.h:42): then the phases cannot be reordered
-        if (mode == WF_PHASED && rd->render_settings.number_of_light_samples == 1 && !rd->render_settings.do_alpha_testing)
+        if (phased_mis)
         {
-            const unsigned g64 = blocks(64), g128 = blocks(128);
-            PT_VARIANT_NAME(k_wf_nee_light_eval)<<<g64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
-            PT_VARIANT_NAME(k_wf_nee_bsdf_sample)<<<g64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
-            if (PT_ESS != 0 && rd->world_settings.ambient_light_type == AMBIENT_ENVMAP)
+            const unsigned g64 = blocks(64);
+            const bool lights = rd->buffers.emissive_triangles_count > 0;
+            const bool envmap = PT_ESS != 0 && rd->world_settings.ambient_light_type == AMBIENT_ENVMAP;
+            if (lights)
+            {
+                PT_VARIANT_NAME(k_wf_nee_light_eval)<<<g64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
+                PT_VARIANT_NAME(k_wf_nee_bsdf_sample)<<<g64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
+            }
+            if (envmap)
             {
                 PT_VARIANT_NAME(k_wf_env_light_eval)<<<g64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
                 PT_VARIANT_NAME(k_wf_env_bsdf_sample)<<<g64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
             }
-            PT_VARIANT_NAME(k_wf_nee_trace)<<<g128, 128, 0, stream>>>(*rd, res, tile, *wf, bounce);
-            PT_VARIANT_NAME(k_wf_bsdf)<<<g64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
+            if (lights || envmap)
+            {
+                RayQueueView qa = {wf->any_queue, counts + 2, cursors + 6, wf->nee_ray_o, wf->nee_ray_d, nullptr, nullptr, wf->nee_ray_o};
+                e = PT_SUFFIXED(launch_trace_queue)(rd->geom, qa, true, trace_blocks, counters, stream);
+                if (e != cudaSuccess)
+                    return e;
+            }
+            if (lights)
+            {
+                RayQueueView qc = {wf->closest_queue, counts + 3, cursors + 9, wf->nee_ray_o, wf->nee_ray_d, wf->hit_tuvp, wf->hit_tri_slot, nullptr};
+                e = PT_SUFFIXED(launch_trace_queue)(rd->geom, qc, false, trace_blocks, counters, stream);
+                if (e != cudaSuccess)
+                    return e;
+            }
+            PT_VARIANT_NAME(k_wf_bsdf_resolved)<<<g64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce, lights, envmap);
         }
         else
 #endif

@@ -2,6 +2,7 @@
 // per-permutation FullPathTracer translation units. Compiled twice: timing build (suffix _t) and, with -DPT_COUNTERS,
 // counting build (suffix _c) that accumulates rays / nodes / triangles for Mrays/s and the node-fetch roofline.
 #include "kernels.cuh"
+#include "trace_queue.cuh"
 #include "launch.h"
 #include "variants.h"
 
@@ -44,6 +45,24 @@ __global__ void PT_SUFFIXED(k_trace_shadow)(Bvh8Device bvh, const float* __restr
     float3 d = f3(rays[i * 6 + 3], rays[i * 6 + 4], rays[i * 6 + 5]);
     Hit hit;
     out_occluded[i] = bvh8_trace<true>(bvh, o, d, t_max[i] - 1.0e-4f, last_prim ? last_prim[i] : -1, hit, counters) ? 1 : 0;
+}
+
+template <bool ANY_HIT>
+__global__ void __launch_bounds__(kTraceBlock) PT_SUFFIXED(k_trace_queue)(const Bvh8Device* __restrict__ bvh, const __grid_constant__ RayQueueView q, TraversalCounters* counters)
+{
+    __shared__ uint2 shared_stack[kSharedStackEntries * kTraceBlock];
+    const Bvh8Device b = *bvh;
+    trace_queue_body<ANY_HIT>(b, q, shared_stack, counters);
+}
+
+cudaError_t PT_SUFFIXED(launch_trace_queue)(const void* bvh_device_handle, const RayQueueView& q, bool any_hit, unsigned blocks, TraversalCounters* counters, cudaStream_t stream)
+{
+    const Bvh8Device* bvh = reinterpret_cast<const Bvh8Device*>(bvh_device_handle);
+    if (any_hit)
+        PT_SUFFIXED(k_trace_queue)<true><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters);
+    else
+        PT_SUFFIXED(k_trace_queue)<false><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters);
+    return cudaGetLastError();
 }
 
 static inline dim3 pixel_grid(const Tile& t) { return dim3((t.x1 - t.x0 + 7) / 8, (t.y1 - t.y0 + 7) / 8, 1); }

@@ -106,15 +106,22 @@ PT_DEV float3 hit_geometric_normal(const HIPRTRenderData& rd, const Hit& hit)
     return normalize(normalize(bvh8_triangle_normal(scene_bvh(rd), hit.tri_slot)));
 }
 
-// trace_ray (Intersect.h:114-219). Returns true if a hit was found.
-PT_DEV_NOINLINE bool trace_ray(const HIPRTRenderData& rd, float3 origin, float3 direction, RayPayload& payload, HitInfo& out, int last_hit_primitive_index, Rng& rng)
+// trace_ray (Intersect.h:114-219). Returns true if a hit was found. `first`: when have_first is set, the closest hit of
+// (origin, direction) was already found by the ray-queue kernel (trace_queue.cuh) and is passed in instead of traced here;
+// volume boundaries that are skipped (nested dielectrics) are re-traced in place either way.
+PT_DEV_NOINLINE bool trace_ray_from(const HIPRTRenderData& rd, float3 origin, float3 direction, RayPayload& payload, HitInfo& out, int last_hit_primitive_index, Rng& rng, Hit hit, bool have_first)
 {
-    Hit hit;
     bool skipping_volume_boundary = false;
     do
     {
-        if (!bvh8_trace<false>(scene_bvh(rd), origin, direction, INFINITY, last_hit_primitive_index, hit, PT_COUNTERS_PTR))
+        if (have_first)
+        {
+            if (hit.prim < 0)
+                return false;
+        }
+        else if (!bvh8_trace<false>(scene_bvh(rd), origin, direction, INFINITY, last_hit_primitive_index, hit, PT_COUNTERS_PTR))
             return false;
+        have_first = false;
 
         int3 vi = triangle_vertex_indices(rd, hit.prim);
         float2 uv = make_float2(hit.u, hit.v);
@@ -155,6 +162,13 @@ PT_DEV_NOINLINE bool trace_ray(const HIPRTRenderData& rd, float3 origin, float3 
     return true;
 }
 
+PT_DEV bool trace_ray(const HIPRTRenderData& rd, float3 origin, float3 direction, RayPayload& payload, HitInfo& out, int last_hit_primitive_index, Rng& rng)
+{
+    Hit none;
+    none.prim = -1; none.tri_slot = -1; none.t = -1.0f; none.u = 0.0f; none.v = 0.0f;
+    return trace_ray_from(rd, origin, direction, payload, out, last_hit_primitive_index, rng, none, false);
+}
+
 // evaluate_shadow_ray (Intersect.h:224-286): true if occluded. Alpha testing off: one any-hit query.
 PT_DEV bool evaluate_shadow_ray(const HIPRTRenderData& rd, float3 origin, float3 direction, float t_max, int last_hit_primitive_index, Rng& rng)
 {
@@ -172,11 +186,10 @@ struct ShadowLightRayHitInfo
 };
 
 // evaluate_shadow_light_ray (Intersect.h:293-410): closest hit, then the emission + shading normal of what was hit
-PT_DEV_NOINLINE bool evaluate_shadow_light_ray(const HIPRTRenderData& rd, float3 origin, float3 direction, float t_max, ShadowLightRayHitInfo& out, int last_hit_primitive_index, Rng& rng)
+// Second half of evaluate_shadow_light_ray: what the closest hit `hit` of the ray emits (Intersect.h:377-409)
+PT_DEV_NOINLINE bool shadow_light_ray_resolve(const HIPRTRenderData& rd, float t_max, ShadowLightRayHitInfo& out, const Hit& hit)
 {
-    (void)rng;
-    Hit hit;
-    if (!bvh8_trace<false>(scene_bvh(rd), origin, direction, INFINITY, last_hit_primitive_index, hit, PT_COUNTERS_PTR))
+    if (hit.prim < 0)
         return false;
     if (!(hit.t < t_max - 1.0e-4f))
         return false;
@@ -204,5 +217,13 @@ PT_DEV_NOINLINE bool evaluate_shadow_light_ray(const HIPRTRenderData& rd, float3
     out.hit_distance = hit.t;
     out.hit_prim_index = hit.prim;
     return true;
+}
+
+PT_DEV bool evaluate_shadow_light_ray(const HIPRTRenderData& rd, float3 origin, float3 direction, float t_max, ShadowLightRayHitInfo& out, int last_hit_primitive_index, Rng& rng)
+{
+    (void)rng;
+    Hit hit;
+    bvh8_trace<false>(scene_bvh(rd), origin, direction, INFINITY, last_hit_primitive_index, hit, PT_COUNTERS_PTR);
+    return shadow_light_ray_resolve(rd, t_max, out, hit);
 }
 } // namespace pt

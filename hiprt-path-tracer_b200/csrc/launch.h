@@ -14,7 +14,8 @@ struct TraversalCounters { unsigned long long rays, nodes, triangles; };
 
 // How b200pt_launch_FullPathTracer runs the path (wavefront.cuh). Selected per context (b200pt_set_path_mode).
 constexpr int kSortBuckets = 128;
-constexpr int kCursorsPerBounce = 8;
+constexpr int kCursorsPerBounce = 12;
+constexpr int kCountsPerBounce = 4;    // rays to extend, hits to shade, NEE any-hit rays, NEE closest-hit rays
 enum WavefrontMode { WF_MEGAKERNEL = 0, WF_FUSED = 1, WF_SPLIT = 2, WF_PHASED = 3 };
 
 // Scratch of the wavefront path tracer, owned by the context, sized for the pixels of the largest tile launched so far.
@@ -35,9 +36,13 @@ struct WavefrontState
     uint8_t* sort_key;       // SPLIT only: material signature of the slot's current hit (kSortBuckets values)
     uint32_t* bucket_count;  // SPLIT only: kSortBuckets histogram of the current shade queue, then scatter cursors
     float4* nee_ray_o;       // PHASED only: 4 NEE rays per path (wavefront_mis.cuh), [which * capacity + slot]: origin | t_max (<0: none)
-    float4* nee_ray_d;       //   direction | cosine term (ray 1)
-    float4* nee_pending;     //   contribution if unoccluded (rays 0,2,3) or BSDF value | pdf (ray 1)
-    uint32_t* counts;        // [2*b]: rays queued for bounce b, [2*b+1]: hits queued for shading at bounce b
+    float4* nee_ray_d;       //   direction | primitive the ray leaves from
+    float4* nee_pending;     //   contribution if unoccluded (rays 0,2,3) or BSDF value * cosine | pdf (ray 1)
+    float4* hit_tuvp;        // PHASED only: hit records of the ray-queue kernel, [slot] extension rays, [capacity + slot] NEE light rays
+    uint32_t* hit_tri_slot;  //   BVH triangle slot of the hit
+    uint32_t* any_queue;     // PHASED only: ids (which * capacity + slot) of the NEE shadow rays of this bounce
+    uint32_t* closest_queue; // PHASED only: ids (capacity + slot) of the NEE light rays (closest hit + emission) of this bounce
+    uint32_t* counts;        // [4*b + k]: k = 0 rays queued for bounce b, 1 hits queued for shading, 2 NEE any-hit rays, 3 NEE closest-hit rays
     uint32_t* cursors;       // kCursorsPerBounce work cursors per bounce (dynamic fetch of the queue kernels); follows `counts`
     uint32_t sm_count;       // SMs of the device (grid sizing of the queue kernels)
     uint32_t capacity;       // paths
@@ -54,10 +59,24 @@ struct WavefrontState
 #define PT_VARIANT_NAME_EXPAND(name, L, E, A, G) PT_VARIANT_NAME_OF(name, L, E, A, G)
 #define PT_VARIANT_NAME(name) PT_VARIANT_NAME_EXPAND(name, PT_LSS, PT_ESS, PT_LATER, PT_GGX)
 
+// Input/output arrays of one launch of the ray-queue traversal kernel (trace_queue.cuh)
+struct RayQueueView
+{
+    const uint32_t* ids;        // ray ids to trace
+    const uint32_t* count;      // number of ids (device)
+    uint32_t* cursor;           // work cursor of this launch (zeroed beforehand)
+    const float4* ray_o;        // [id]: origin xyz | t_max (any-hit only)
+    const float4* ray_d;        // [id]: direction xyz | primitive the ray leaves from (int bits)
+    float4* hit_tuvp;           // closest: [id] t, u, v, primitive (int bits; -1 = miss)
+    uint32_t* hit_tri_slot;     // closest: [id] index of the triangle in the BVH triangle array
+    float4* occluded_flag;      // any-hit: the ray_o array; .w is set to -1 when the ray is occluded
+};
+
 #define PT_DECLARE_LAUNCHERS(S)                                                                                                        \
     bool variant_available##S(const VariantOptions& opt);                                                                              \
     cudaError_t launch_CameraRays##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream);   \
     cudaError_t launch_FullPathTracer##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const WavefrontState* wf, int mode); \
+    cudaError_t launch_trace_queue##S(const void* bvh_device_handle, const RayQueueView& q, bool any_hit, unsigned blocks, TraversalCounters* counters, cudaStream_t stream); \
     cudaError_t launch_trace_closest##S(const Bvh8Device& bvh, const float* rays, const int* last_prim, long long n, int* out_prim, float* out_t, float* out_uv, TraversalCounters* counters, cudaStream_t stream); \
     cudaError_t launch_trace_shadow##S(const Bvh8Device& bvh, const float* rays, const float* t_max, const int* last_prim, long long n, unsigned char* out_occluded, TraversalCounters* counters, cudaStream_t stream);
 

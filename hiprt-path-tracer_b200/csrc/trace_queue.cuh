@@ -1,0 +1,211 @@
+// Ray-queue traversal kernel of the wavefront path tracer: persistent warps, per-lane ray replacement.
+//
+// ncu on the 10 M-triangle scene (profiles/r01_launches_c3_phased_before_tracequeue.txt): the kernels that traced rays as
+// one-ray-per-thread batches issued instructions for 6.5 of 32 lanes on average -- incoherent rays have very different
+// lengths (a sky ray leaves after 3 nodes, a grazing ray visits 100) and a warp waited for its longest ray -- and every
+// node visit paid 48 I2F.U8 conversions on the quarter-rate XU pipe. Here
+//   * a lane whose ray ends takes the next ray of the queue at once (one warp-aggregated atomic per refill round), so the
+//     lanes of a warp stay busy until the queue is empty (after Aila & Laine, HPG 2009, "persistent threads");
+//   * quantised bounds become floats with PRMT + FADD (0x4B000000 | byte is 2^23 + byte), both full-rate;
+//   * the first kSharedStackEntries stack entries of each lane live in shared memory (lane-interleaved), the rest spills to local memory;
+//   * the kernel only traverses: 16-byte ray records in, 16+4-byte hit records (or an occlusion flag) out; shading data is
+//     fetched by the kernels that consume the hits.
+// Per-ray arithmetic (slab test, visiting order, triangle routine, strict '<' closest rule, last-primitive filter) is the same
+// as bvh8_trace (traverse.cuh), so the hits are identical and parity with the reference (src/Renderer/BVH.h:132-227,
+// Triangle.h:20-63, FilterFunction.h:19-48) is unchanged.
+#pragma once
+
+#include "launch.h"
+#include "traverse.cuh"
+
+namespace pt
+{
+constexpr int kSharedStackEntries = 8;
+constexpr int kTraceBlock = 128;
+constexpr unsigned kRefillIdleLanes = 8;   // refill as soon as this many lanes of a warp have no ray
+
+PT_DEV float quantised_byte_to_float(uint32_t word, int byte)
+{
+    // bytes of (word, 0x4B000000): result = [byte j of word, 0x00, 0x00, 0x4B] = 2^23 + byte
+    return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7540u + (uint32_t)byte)) - 8388608.0f;
+}
+
+template <bool ANY_HIT>
+__device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const RayQueueView& q, uint2* shared_stack, TraversalCounters* counters)
+{
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t n = *q.count;
+    uint2* const my_shared = shared_stack + threadIdx.x;          // entry k at my_shared[k * blockDim.x]
+    uint2 local_stack[kTraversalStackSize - kSharedStackEntries];
+
+    bool active = false, exhausted = false;
+    uint32_t ray_id = 0;
+    float3 o = f3(0.0f), d = f3(0.0f);
+    float idx = 0.0f, idy = 0.0f, idz = 0.0f, t_best = 0.0f;
+    int last_prim = -1;
+    uint32_t oct_inv = 0;
+    Hit hit;
+    hit.prim = -1; hit.tri_slot = -1; hit.t = -1.0f; hit.u = 0.0f; hit.v = 0.0f;
+    uint2 ngroup = make_uint2(0u, 0u);
+    int stack_size = 0;
+    PT_COUNT(unsigned int n_nodes = 0; unsigned int n_tris = 0; unsigned int n_rays = 0;)
+
+    while (true)
+    {
+        // ---- refill: lanes without a ray take the next queue entries -------------------------------------------------
+        const unsigned idle_mask = __ballot_sync(0xFFFFFFFFu, !active);
+        if (!exhausted && (__popc(idle_mask) >= kRefillIdleLanes || idle_mask == 0xFFFFFFFFu))
+        {
+            uint32_t base = 0;
+            if (lane == (uint32_t)(__ffs((int)idle_mask) - 1))
+                base = atomicAdd(q.cursor, (uint32_t)__popc(idle_mask));
+            base = __shfl_sync(0xFFFFFFFFu, base, __ffs((int)idle_mask) - 1);
+            exhausted = base + (uint32_t)__popc(idle_mask) >= n;
+            if (!active)
+            {
+                const uint32_t i = base + (uint32_t)__popc(idle_mask & ((1u << lane) - 1u));
+                if (i < n)
+                {
+                    ray_id = q.ids[i];
+                    const float4 ro = q.ray_o[ray_id], rdir = q.ray_d[ray_id];
+                    o = f3(ro.x, ro.y, ro.z);
+                    d = f3(rdir.x, rdir.y, rdir.z);
+                    last_prim = __float_as_int(rdir.w);
+                    t_best = ANY_HIT ? ro.w - 1.0e-4f : INFINITY;    // evaluate_shadow_ray: occluded iff t < t_max - 1e-4 (Intersect.h:229)
+                    const float kTiny = 1.0e-20f;
+                    idx = 1.0f / (fabsf(d.x) > kTiny ? d.x : copysignf(kTiny, d.x));
+                    idy = 1.0f / (fabsf(d.y) > kTiny ? d.y : copysignf(kTiny, d.y));
+                    idz = 1.0f / (fabsf(d.z) > kTiny ? d.z : copysignf(kTiny, d.z));
+                    oct_inv = (d.x > 0.0f ? 1u : 0u) | (d.y > 0.0f ? 2u : 0u) | (d.z > 0.0f ? 4u : 0u);
+                    hit.prim = -1; hit.tri_slot = -1; hit.t = -1.0f; hit.u = 0.0f; hit.v = 0.0f;
+                    ngroup = make_uint2(0u, 0x80000000u);
+                    stack_size = 0;
+                    active = true;
+                    PT_COUNT(n_rays++;)
+                }
+            }
+        }
+        if (__ballot_sync(0xFFFFFFFFu, active) == 0u)
+            break;
+        if (!active)
+            continue;
+
+        // ---- one traversal iteration of this lane's ray: a node, then the triangles the node handed out ---------------------
+        bool finished = false;
+        uint2 tgroup = make_uint2(0u, 0u);
+        if (ngroup.y > 0x00FFFFFFu)
+        {
+            const uint32_t hits = ngroup.y;
+            const uint32_t imask = hits & 0xFFu;
+            const uint32_t bit = 31u - (uint32_t)__clz((int)hits);
+            ngroup.y &= ~(1u << bit);
+            if (ngroup.y > 0x00FFFFFFu)
+            {
+                if (stack_size < kSharedStackEntries)
+                    my_shared[stack_size * blockDim.x] = ngroup;
+                else if (stack_size < kTraversalStackSize)
+                    local_stack[stack_size - kSharedStackEntries] = ngroup;
+                if (stack_size < kTraversalStackSize)
+                    stack_size++;
+            }
+            const uint32_t slot = (bit - 24u) ^ oct_inv;
+            const uint32_t rank = (uint32_t)__popc(imask & ~(0xFFFFFFFFu << slot));
+            const uint4* np = reinterpret_cast<const uint4*>(bvh.nodes + (ngroup.x + rank));
+            const uint4 n0 = __ldg(np + 0), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+            PT_COUNT(n_nodes++;)
+
+            const float adx = __uint_as_float((n0.w & 0xFFu) << 23) * idx;
+            const float ady = __uint_as_float(((n0.w >> 8) & 0xFFu) << 23) * idy;
+            const float adz = __uint_as_float(((n0.w >> 16) & 0xFFu) << 23) * idz;
+            const float ox = (__uint_as_float(n0.x) - o.x) * idx, oy = (__uint_as_float(n0.y) - o.y) * idy, oz = (__uint_as_float(n0.z) - o.z) * idz;
+            const bool neg_x = d.x < 0.0f, neg_y = d.y < 0.0f, neg_z = d.z < 0.0f;
+            const uint32_t oct_inv4 = oct_inv * 0x01010101u;
+
+            uint32_t hitmask = 0;
+#pragma unroll
+            for (int half = 0; half < 2; half++)
+            {
+                const uint32_t meta4 = half ? n1.w : n1.z;
+                const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+                const uint32_t inner_mask4 = sign_extend_s8x4(is_inner4 << 3);
+                const uint32_t bit_index4 = (meta4 ^ (oct_inv4 & inner_mask4)) & 0x1F1F1F1Fu;
+                const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+                const uint32_t lox = half ? n2.y : n2.x, loy = half ? n2.w : n2.z, loz = half ? n3.y : n3.x;
+                const uint32_t hix = half ? n3.w : n3.z, hiy = half ? n4.y : n4.x, hiz = half ? n4.w : n4.z;
+                const uint32_t nearx = neg_x ? hix : lox, farx = neg_x ? lox : hix;
+                const uint32_t neary = neg_y ? hiy : loy, fary = neg_y ? loy : hiy;
+                const uint32_t nearz = neg_z ? hiz : loz, farz = neg_z ? loz : hiz;
+#pragma unroll
+                for (int j = 0; j < 4; j++)
+                {
+                    const float tnx = __fmaf_rn(quantised_byte_to_float(nearx, j), adx, ox);
+                    const float tny = __fmaf_rn(quantised_byte_to_float(neary, j), ady, oy);
+                    const float tnz = __fmaf_rn(quantised_byte_to_float(nearz, j), adz, oz);
+                    const float tfx = __fmaf_rn(quantised_byte_to_float(farx, j), adx, ox);
+                    const float tfy = __fmaf_rn(quantised_byte_to_float(fary, j), ady, oy);
+                    const float tfz = __fmaf_rn(quantised_byte_to_float(farz, j), adz, oz);
+                    const float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f)) * 0.999999f;
+                    const float cmax = fminf(fminf(fminf(tfx, tfy), tfz) * 1.000001f, t_best);
+                    if (cmin <= cmax)
+                        hitmask |= ((child_bits4 >> (8 * j)) & 0xFFu) << ((bit_index4 >> (8 * j)) & 0xFFu);
+                }
+            }
+            ngroup.x = n1.x;
+            ngroup.y = (hitmask & 0xFF000000u) | (n0.w >> 24);
+            tgroup.x = n1.y;
+            tgroup.y = hitmask & 0x00FFFFFFu;
+        }
+
+        while (tgroup.y != 0u)
+        {
+            const uint32_t tbit = (uint32_t)__ffs((int)tgroup.y) - 1u;
+            tgroup.y &= tgroup.y - 1u;
+            const uint32_t tri_index = tgroup.x + tbit;
+            const float4* tp = reinterpret_cast<const float4*>(bvh.triangles + tri_index);
+            const float4 v0 = __ldg(tp + 0), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+            PT_COUNT(n_tris++;)
+            const int prim = __float_as_int(v0.w);
+            if (prim == last_prim)
+                continue;
+            float t, u, v;
+            if (intersect_triangle_reference(o, d, f3(v0.x, v0.y, v0.z), f3(v1.x, v1.y, v1.z), f3(v2.x, v2.y, v2.z), t, u, v) && t < t_best)
+            {
+                t_best = t;
+                hit.prim = prim; hit.tri_slot = (int)tri_index; hit.t = t; hit.u = u; hit.v = v;
+                if (ANY_HIT)
+                {
+                    finished = true;
+                    break;
+                }
+            }
+        }
+
+        if (!finished && ngroup.y <= 0x00FFFFFFu)
+        {
+            if (stack_size == 0)
+                finished = true;
+            else
+            {
+                stack_size--;
+                ngroup = stack_size < kSharedStackEntries ? my_shared[stack_size * blockDim.x] : local_stack[stack_size - kSharedStackEntries];
+            }
+        }
+
+        if (finished)
+        {
+            if (ANY_HIT)
+            {
+                if (hit.prim >= 0)
+                    q.occluded_flag[ray_id].w = -1.0f;
+            }
+            else
+            {
+                q.hit_tuvp[ray_id] = make_float4(hit.t, hit.u, hit.v, __int_as_float(hit.prim));
+                q.hit_tri_slot[ray_id] = (uint32_t)hit.tri_slot;
+            }
+            active = false;
+        }
+    }
+    PT_COUNT(if (counters && n_rays) { atomicAdd(&counters->rays, (unsigned long long)n_rays); atomicAdd(&counters->nodes, (unsigned long long)n_nodes); atomicAdd(&counters->triangles, (unsigned long long)n_tris); })
+}
+} // namespace pt

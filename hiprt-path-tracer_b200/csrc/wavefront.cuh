@@ -201,7 +201,7 @@ PT_DEV void wf_bounce0_pixel(const HIPRTRenderData& rd, int2 res, const Tile& ti
         else
             wf_finish_path(rd, pixel_index, p);
     }
-    queue_push(wf.ray_queue[0], wf.counts + 2 * 1, alive, slot);
+    queue_push(wf.ray_queue[0], wf.counts + kCountsPerBounce * 1, alive, slot);
 }
 
 // ---- FUSED: bounce >= 1, trace + shade in one kernel ------------------------------------------------------------
@@ -223,7 +223,7 @@ PT_DEV void wf_bounce_path(const HIPRTRenderData& rd, int2 res, const Tile& tile
         wf_store_ray(wf, slot, p);
     else
         wf_finish_path(rd, pixel_index, p);
-    queue_push(wf.ray_queue[bounce & 1], wf.counts + 2 * (bounce + 1), alive, slot);
+    queue_push(wf.ray_queue[bounce & 1], wf.counts + kCountsPerBounce * (bounce + 1), alive, slot);
 }
 
 // ---- SPLIT, bounce 0: GEN writes the ray state of every active pixel and queues the camera hits for shading -------------
@@ -273,7 +273,7 @@ PT_DEV void wf_extend_path(const HIPRTRenderData& rd, int2 res, const Tile& tile
         miss_vertex<ESS>(rd, p.payload, p.direction, bounce);
         wf_finish_path(rd, pixel_index, p);
     }
-    queue_push(wf.shade_queue, wf.counts + 2 * bounce + 1, found, slot);
+    queue_push(wf.shade_queue, wf.counts + kCountsPerBounce * bounce + 1, found, slot);
 }
 
 // ---- SPLIT: group the shade queue by material signature (counting sort: histogram came from wf_classify) ----------------
@@ -324,7 +324,7 @@ PT_DEV void wf_shade_path(const HIPRTRenderData& rd, int2 res, const Tile& tile,
         wf_store_ray(wf, slot, p);
     else
         wf_finish_path(rd, pixel_index, p);
-    queue_push(wf.ray_queue[bounce & 1], wf.counts + 2 * (bounce + 1), alive, slot);
+    queue_push(wf.ray_queue[bounce & 1], wf.counts + kCountsPerBounce * (bounce + 1), alive, slot);
 }
 
 // ---- PHASED: SHADE split into its two halves, so that all warps of an SM run the same part of the BSDF code ---------------
@@ -363,6 +363,34 @@ PT_DEV void wf_bsdf_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, 
         wf_store_ray(wf, slot, p);
     else
         wf_finish_path(rd, pixel_index, p);
-    queue_push(wf.ray_queue[bounce & 1], wf.counts + 2 * (bounce + 1), alive, slot);
+    queue_push(wf.ray_queue[bounce & 1], wf.counts + kCountsPerBounce * (bounce + 1), alive, slot);
+}
+
+// ---- PHASED, bounce >= 1: SURFACE = what trace_ray does with the closest hit the ray-queue kernel found --------------------
+template <int ESS>
+PT_DEV void wf_surface_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
+{
+    const uint32_t slot = wf.ray_queue[(bounce - 1) & 1][i];
+    PathRegs p;
+    wf_load_ray(wf, slot, p);
+    const float4 h = wf.hit_tuvp[slot];
+    Hit first;
+    first.t = h.x; first.u = h.y; first.v = h.z;
+    first.prim = __float_as_int(h.w);
+    first.tri_slot = (int)wf.hit_tri_slot[slot];
+    const bool found = trace_ray_from(rd, p.origin, p.direction, p.payload, p.hit, p.hit.primitive_index, p.rng, first, true);
+    if (found)
+    {
+        wf_store_hit(wf, slot, p);
+        wf_classify(wf, slot, p.payload.material);
+    }
+    else
+    {
+        uint32_t x, y, pixel_index;
+        wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+        miss_vertex<ESS>(rd, p.payload, p.direction, bounce);
+        wf_finish_path(rd, pixel_index, p);
+    }
+    queue_push(wf.shade_queue, wf.counts + kCountsPerBounce * bounce + 1, found, slot);
 }
 } // namespace pt

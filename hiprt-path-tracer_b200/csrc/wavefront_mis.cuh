@@ -7,8 +7,9 @@
 //   P2 nee_bsdf_sample  BSDF sample of the light MIS pair                               -> closest-hit ray 1 + BSDF value
 //   P3 env_light_eval   envmap texel by alias table / CDF (2 draws), BSDF eval          -> shadow ray 2 + its contribution
 //   P4 env_bsdf_sample  BSDF sample of the envmap MIS pair, envmap_eval                 -> shadow ray 3 + its contribution
-//   T  nee_trace        traces rays 0-3, resolves ray 1 (emission + light pdf of what was hit), the three clamps, ray_color
-//   P5 bsdf             wf_bsdf_path: BSDF sample, russian roulette, next ray (wavefront.cuh)
+//   T  ray-queue kernel (trace_queue.cuh) over the compact id lists P1-P4 appended to: any-hit for rays 0,2,3, closest for ray 1
+//   P5 bsdf             resolves ray 1 (emission + light pdf of what was hit), the three clamps, ray_color; then the BSDF
+//                       sample, russian roulette and next ray of shade_vertex_bounce
 //
 // The phases run in the reference's program order per path and hand the Xorshift32 state on, so the random numbers each
 // sampler sees are the ones it sees in the reference (src/Device/includes/Lights.h:115-220,277-321, Envmap.h:151-246,
@@ -30,12 +31,17 @@ PT_DEV void nee_store_none(const WavefrontState& wf, int which, uint32_t slot)
     wf.nee_ray_o[nee_index(wf, which, slot)] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
 }
 
-PT_DEV void nee_store(const WavefrontState& wf, int which, uint32_t slot, float3 origin, float t_max, float3 direction, float dir_w, RGB pending, float pending_w)
+// Records NEE ray `which` of the path and appends it to the bounce's any-hit (rays 0, 2, 3) or closest-hit (ray 1) id list
+PT_DEV void nee_store(const WavefrontState& wf, int bounce, int which, uint32_t slot, float3 origin, float t_max, float3 direction, int last_prim, RGB pending, float pending_w)
 {
     const size_t k = nee_index(wf, which, slot);
     wf.nee_ray_o[k] = make_float4(origin.x, origin.y, origin.z, t_max);
-    wf.nee_ray_d[k] = make_float4(direction.x, direction.y, direction.z, dir_w);
+    wf.nee_ray_d[k] = make_float4(direction.x, direction.y, direction.z, __int_as_float(last_prim));
     wf.nee_pending[k] = make_float4(pending.r, pending.g, pending.b, pending_w);
+    if (which == NEE_LIGHT_BSDF)
+        queue_push(wf.closest_queue, wf.counts + kCountsPerBounce * bounce + 3, true, (uint32_t)k);
+    else
+        queue_push(wf.any_queue, wf.counts + kCountsPerBounce * bounce + 2, true, (uint32_t)k);
 }
 
 // What sample_one_light does before it samples (Lights.h:277-300)
@@ -125,7 +131,7 @@ PT_DEV void nee_light_eval_path(const HIPRTRenderData& rd, int2 res, const Tile&
             float mis_weight = balance_heuristic(light_sample_pdf, bsdf_pdf);
             float cosine_term = maxf(dot(hit.shading_normal, dir), 0.0f);
             RGB light_source_radiance_mis = bsdf_color * cosine_term * light_info.emission * mis_weight / light_sample_pdf;
-            nee_store(wf, NEE_LIGHT, slot, evaluated_point, distance_to_light, dir, 0.0f, light_source_radiance_mis, 0.0f);
+            nee_store(wf, bounce, NEE_LIGHT, slot, evaluated_point, distance_to_light, dir, hit.primitive_index, light_source_radiance_mis, 0.0f);
         }
     }
 }
@@ -161,7 +167,7 @@ PT_DEV void nee_bsdf_sample_path(const HIPRTRenderData& rd, int2 res, const Tile
     if (direction_pdf > 0)
     {
         float cosine_term = fabsf(dot(hit.shading_normal, sampled_bsdf_direction));
-        nee_store(wf, NEE_LIGHT_BSDF, slot, bsdf_shadow_ray_origin, 1.0e35f, sampled_bsdf_direction, cosine_term, bsdf_color, direction_pdf);
+        nee_store(wf, bounce, NEE_LIGHT_BSDF, slot, bsdf_shadow_ray_origin, 1.0e35f, sampled_bsdf_direction, hit.primitive_index, bsdf_color * cosine_term, direction_pdf);
     }
 }
 
@@ -195,7 +201,7 @@ PT_DEV void env_light_eval_path(const HIPRTRenderData& rd, int2 res, const Tile&
         RGB bsdf_color = bsdf_eval(rd, p.payload.material, trash, view_direction, hit.shading_normal, sampled_direction, bsdf_pdf);
         float mis_weight = balance_heuristic(envmap_pdf, bsdf_pdf);
         RGB envmap_mis_contribution = bsdf_color * cosine_term * mis_weight * envmap_color / envmap_pdf;
-        nee_store(wf, NEE_ENV, slot, hit.inter_point, 1.0e35f, sampled_direction, 0.0f, envmap_mis_contribution, 0.0f);
+        nee_store(wf, bounce, NEE_ENV, slot, hit.inter_point, 1.0e35f, sampled_direction, hit.primitive_index, envmap_mis_contribution, 0.0f);
     }
 }
 
@@ -228,47 +234,33 @@ PT_DEV void env_bsdf_sample_path(const HIPRTRenderData& rd, int2 res, const Tile
         {
             float mis_weight = balance_heuristic(bsdf_sample_pdf, envmap_eval_pdf);
             RGB bsdf_mis_contribution = envmap_radiance * mis_weight * cosine_term * bsdf_color / bsdf_sample_pdf;
-            nee_store(wf, NEE_ENV_BSDF, slot, hit.inter_point, 1.0e35f, bsdf_sampled_dir, 0.0f, bsdf_mis_contribution, 0.0f);
+            nee_store(wf, bounce, NEE_ENV_BSDF, slot, hit.inter_point, 1.0e35f, bsdf_sampled_dir, hit.primitive_index, bsdf_mis_contribution, 0.0f);
         }
     }
 }
 
-// ---- T: trace the NEE rays of a vertex, finish shade_vertex_direct (FullPathTracer.h:195-214) ---------------------------------
-PT_DEV RGB nee_shadowed_contribution(const HIPRTRenderData& rd, const WavefrontState& wf, int which, uint32_t slot, int last_prim, Rng& rng)
+// ---- P5: finish shade_vertex_direct from the traced NEE rays (FullPathTracer.h:195-214), then shade_vertex_bounce --------------
+// The any-hit kernel has set t_max = -1 on the occluded rays; ray 1's closest hit is in the hit records at [capacity + slot].
+PT_DEV RGB nee_unoccluded_contribution(const WavefrontState& wf, int which, uint32_t slot)
 {
     const size_t k = nee_index(wf, which, slot);
-    const float4 o = wf.nee_ray_o[k];
-    if (!(o.w > 0.0f))
-        return RGB(0.0f);
-    const float4 d = wf.nee_ray_d[k];
-    if (evaluate_shadow_ray(rd, f3(o.x, o.y, o.z), f3(d.x, d.y, d.z), o.w, last_prim, rng))
+    if (!(wf.nee_ray_o[k].w > 0.0f))
         return RGB(0.0f);
     const float4 c = wf.nee_pending[k];
     return RGB(c.x, c.y, c.z);
 }
 
 template <int ESS>
-PT_DEV void nee_trace_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
+PT_DEV void nee_resolve(const HIPRTRenderData& rd, const WavefrontState& wf, uint32_t slot, int bounce, PathRegs& p, bool lights_sampled, bool envmap_sampled)
 {
-    const uint32_t slot = wf.sorted_queue[i];
-    uint32_t x, y, pixel_index;
-    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
-    const SimplifiedRendererMaterial* mp = bounce == 0 ? rd.g_buffer.materials + pixel_index : reinterpret_cast<const SimplifiedRendererMaterial*>(wf.materials) + slot;
-    // only the emission fields of the material matter here
-    Material m;
-    m.emissive_texture_used = mp->emissive_texture_used;
-    m.emission_strength = mp->emission_strength;
-    m.emission = mp->emission;
-    const int last_prim = bounce == 0 ? rd.g_buffer.first_hit_prim_index[pixel_index] : __float_as_int(wf.hit_point[slot].w);
-    Rng rng(0u);   // shadow rays draw nothing with alpha testing off
-
+    const Material& m = p.payload.material;
     RGB light_direct(0.0f);
     const int prelude = lights_prelude(rd, m, bounce);
     if (prelude == LIGHTS_EMISSION)
         light_direct = material_emission(m);
-    else if (prelude == LIGHTS_SAMPLE)
+    else if (prelude == LIGHTS_SAMPLE && lights_sampled)
     {
-        RGB light_source_radiance_mis = nee_shadowed_contribution(rd, wf, NEE_LIGHT, slot, last_prim, rng);
+        RGB light_source_radiance_mis = nee_unoccluded_contribution(wf, NEE_LIGHT, slot);
         RGB bsdf_radiance_mis;
         const size_t k = nee_index(wf, NEE_LIGHT_BSDF, slot);
         const float4 o = wf.nee_ray_o[k];
@@ -277,16 +269,21 @@ PT_DEV void nee_trace_path(const HIPRTRenderData& rd, int2 res, const Tile& tile
         {
             const float4 d = wf.nee_ray_d[k];
             const float3 sampled_bsdf_direction = f3(d.x, d.y, d.z);
+            const float4 h = wf.hit_tuvp[k];
+            Hit light_ray_hit;
+            light_ray_hit.t = h.x; light_ray_hit.u = h.y; light_ray_hit.v = h.z;
+            light_ray_hit.prim = __float_as_int(h.w);
+            light_ray_hit.tri_slot = (int)wf.hit_tri_slot[k];
             ShadowLightRayHitInfo light_hit;
-            bool inter_found = evaluate_shadow_light_ray(rd, f3(o.x, o.y, o.z), sampled_bsdf_direction, 1.0e35f, light_hit, last_prim, rng);
+            bool inter_found = shadow_light_ray_resolve(rd, 1.0e35f, light_hit, light_ray_hit);
             if (inter_found && !light_hit.hit_emission.is_black())
             {
                 const float4 c = wf.nee_pending[k];
-                const RGB bsdf_color(c.x, c.y, c.z);
-                const float direction_pdf = c.w, cosine_term = d.w;
+                const RGB bsdf_color_cosine(c.x, c.y, c.z);      // bsdf_color * cosine_term, the expression's first product
+                const float direction_pdf = c.w;
                 float light_pdf = pdf_of_emissive_triangle_hit(rd, light_hit, sampled_bsdf_direction);
                 float mis_weight = balance_heuristic(direction_pdf, light_pdf);
-                bsdf_radiance_mis = bsdf_color * cosine_term * light_hit.hit_emission * mis_weight / direction_pdf;
+                bsdf_radiance_mis = bsdf_color_cosine * light_hit.hit_emission * mis_weight / direction_pdf;
             }
         }
         RGB direct;
@@ -298,22 +295,37 @@ PT_DEV void nee_trace_path(const HIPRTRenderData& rd, int2 res, const Tile& tile
     }
 
     RGB envmap_direct(0.0f);
-    if (envmap_prelude<ESS>(rd, m))
+    if (envmap_sampled && envmap_prelude<ESS>(rd, m))
     {
-        RGB envmap_mis_contribution = nee_shadowed_contribution(rd, wf, NEE_ENV, slot, last_prim, rng);
-        RGB bsdf_mis_contribution = nee_shadowed_contribution(rd, wf, NEE_ENV_BSDF, slot, last_prim, rng);
+        RGB envmap_mis_contribution = nee_unoccluded_contribution(wf, NEE_ENV, slot);
+        RGB bsdf_mis_contribution = nee_unoccluded_contribution(wf, NEE_ENV_BSDF, slot);
         envmap_direct = bsdf_mis_contribution + envmap_mis_contribution;
     }
 
     light_direct = clamp_light_contribution(light_direct, rd.render_settings.direct_contribution_clamp, bounce == 0);
     envmap_direct = clamp_light_contribution(envmap_direct, rd.render_settings.envmap_contribution_clamp, bounce == 0);
 
-    const float4 t = wf.throughput[slot], c = wf.color[slot];
-    RGB ray_color(c.x, c.y, c.z);
     if (bounce == 0)
-        ray_color += material_emission(m);
-    RGB indirect = (light_direct + envmap_direct) * RGB(t.x, t.y, t.z);
-    ray_color += clamp_light_contribution(indirect, rd.render_settings.indirect_contribution_clamp, bounce > 0);
-    wf.color[slot] = make_float4(ray_color.r, ray_color.g, ray_color.b, 0.0f);
+        p.payload.ray_color += material_emission(m);
+    RGB indirect = (light_direct + envmap_direct) * p.payload.throughput;
+    p.payload.ray_color += clamp_light_contribution(indirect, rd.render_settings.indirect_contribution_clamp, bounce > 0);
+}
+
+template <int ESS, int GGX_SAMPLER>
+PT_DEV void wf_bsdf_resolved_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i, bool lights_sampled, bool envmap_sampled)
+{
+    const uint32_t slot = wf.sorted_queue[i];
+    uint32_t x, y, pixel_index;
+    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    PathRegs p;
+    nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
+    nee_resolve<ESS>(rd, wf, slot, bounce, p, lights_sampled, envmap_sampled);
+    bool alive = shade_vertex_bounce<GGX_SAMPLER>(rd, p.payload, p.hit, p.origin, p.direction, p.rng, bounce);
+    alive = alive && bounce < wf_nb_bounces(rd);
+    if (alive)
+        wf_store_ray(wf, slot, p);
+    else
+        wf_finish_path(rd, pixel_index, p);
+    queue_push(wf.ray_queue[bounce & 1], wf.counts + kCountsPerBounce * (bounce + 1), alive, slot);
 }
 } // namespace pt
