@@ -6,7 +6,9 @@
 // node visit paid 48 I2F.U8 conversions on the quarter-rate XU pipe. Here
 //   * a lane whose ray ends takes the next ray of the queue at once (one warp-aggregated atomic per refill round), so the
 //     lanes of a warp stay busy until the queue is empty (after Aila & Laine, HPG 2009, "persistent threads");
-//   * quantised bounds become floats with PRMT + FADD (0x4B000000 | byte is 2^23 + byte), both full-rate;
+//   * quantised bounds become floats with one PRMT each (byte into the mantissa of 1.0f, bias folded into the per-node offsets);
+//   * a lane tests at most one triangle per iteration, and only when at least kTrianglePostponeBelow lanes of the warp have
+//     one pending (its node work goes on meanwhile), so the triangle code runs with fuller warps (after Ylitie et al., HPG 2017);
 //   * the first kSharedStackEntries stack entries of each lane live in shared memory (lane-interleaved), the rest spills to local memory;
 //   * the kernel only traverses: 16-byte ray records in, 16+4-byte hit records (or an occlusion flag) out; shading data is
 //     fetched by the kernels that consume the hits.
@@ -22,12 +24,16 @@ namespace pt
 {
 constexpr int kSharedStackEntries = 8;
 constexpr int kTraceBlock = 128;
-constexpr unsigned kRefillIdleLanes = 8;   // refill as soon as this many lanes of a warp have no ray
+constexpr unsigned kRefillIdleLanes = 4;     // refill as soon as this many lanes of a warp have no ray
+constexpr int kTrianglePostponeBelow = 8;    // triangles are tested when at least this many lanes of the warp have one pending
 
-PT_DEV float quantised_byte_to_float(uint32_t word, int byte)
+// 1 + byte * 2^-15, exactly: the byte lands in mantissa bits 8..15 of 1.0f with one PRMT (result bytes, low to high:
+// 0x00, byte j of word, 0x80, 0x3F). The slab test then evaluates plane = (1 + q 2^-15) * (2^15 a) + (o - 2^15 a), the same
+// value as q * a + o up to the rounding of the folded offset (<= 2^-9 of a grid cell), which the per-node offsets below
+// absorb on the conservative side -- no I2F (quarter-rate XU pipe) and no separate bias subtraction per plane.
+PT_DEV float quantised_byte_to_unit_float(uint32_t word, int byte)
 {
-    // bytes of (word, 0x4B000000): result = [byte j of word, 0x00, 0x00, 0x4B] = 2^23 + byte
-    return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7540u + (uint32_t)byte)) - 8388608.0f;
+    return __uint_as_float(__byte_perm(word, 0x3F800000u, 0x7604u + ((uint32_t)byte << 4)));
 }
 
 template <bool ANY_HIT>
@@ -46,7 +52,8 @@ __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const Ra
     uint32_t oct_inv = 0;
     Hit hit;
     hit.prim = -1; hit.tri_slot = -1; hit.t = -1.0f; hit.u = 0.0f; hit.v = 0.0f;
-    uint2 ngroup = make_uint2(0u, 0u);
+    uint2 ngroup = make_uint2(0u, 0u);   // (first child node, hit internal children << 24 | imask): node work of this lane
+    uint2 tgroup = make_uint2(0u, 0u);   // (first triangle, hit-leaf triangle bits): triangle work of this lane
     int stack_size = 0;
     PT_COUNT(unsigned int n_nodes = 0; unsigned int n_tris = 0; unsigned int n_rays = 0;)
 
@@ -79,20 +86,21 @@ __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const Ra
                     oct_inv = (d.x > 0.0f ? 1u : 0u) | (d.y > 0.0f ? 2u : 0u) | (d.z > 0.0f ? 4u : 0u);
                     hit.prim = -1; hit.tri_slot = -1; hit.t = -1.0f; hit.u = 0.0f; hit.v = 0.0f;
                     ngroup = make_uint2(0u, 0x80000000u);
+                    tgroup = make_uint2(0u, 0u);
                     stack_size = 0;
                     active = true;
                     PT_COUNT(n_rays++;)
                 }
             }
         }
-        if (__ballot_sync(0xFFFFFFFFu, active) == 0u)
+        const unsigned active_mask = __ballot_sync(0xFFFFFFFFu, active);
+        if (active_mask == 0u)
             break;
         if (!active)
             continue;
 
-        // ---- one traversal iteration of this lane's ray: a node, then the triangles the node handed out ---------------------
+        // ---- one iteration: at most one node and at most one triangle of this lane's ray ------------------------------------
         bool finished = false;
-        uint2 tgroup = make_uint2(0u, 0u);
         if (ngroup.y > 0x00FFFFFFu)
         {
             const uint32_t hits = ngroup.y;
@@ -114,10 +122,13 @@ __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const Ra
             const uint4 n0 = __ldg(np + 0), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
             PT_COUNT(n_nodes++;)
 
-            const float adx = __uint_as_float((n0.w & 0xFFu) << 23) * idx;
-            const float ady = __uint_as_float(((n0.w >> 8) & 0xFFu) << 23) * idy;
-            const float adz = __uint_as_float(((n0.w >> 16) & 0xFFu) << 23) * idz;
-            const float ox = (__uint_as_float(n0.x) - o.x) * idx, oy = (__uint_as_float(n0.y) - o.y) * idy, oz = (__uint_as_float(n0.z) - o.z) * idz;
+            // cell size * 2^15 / direction, per axis; near / far offsets pushed 2^-7 of a cell outwards (see above)
+            const float adx = __uint_as_float((n0.w & 0xFFu) << 23) * idx * 32768.0f;
+            const float ady = __uint_as_float(((n0.w >> 8) & 0xFFu) << 23) * idy * 32768.0f;
+            const float adz = __uint_as_float(((n0.w >> 16) & 0xFFu) << 23) * idz * 32768.0f;
+            const float ox = (__uint_as_float(n0.x) - o.x) * idx - adx, oy = (__uint_as_float(n0.y) - o.y) * idy - ady, oz = (__uint_as_float(n0.z) - o.z) * idz - adz;
+            const float ex = fabsf(adx) * 2.3841858e-7f, ey = fabsf(ady) * 2.3841858e-7f, ez = fabsf(adz) * 2.3841858e-7f;   // 2^-22 * 2^15 a = 2^-7 cell
+            const float oxn = ox - ex, oyn = oy - ey, ozn = oz - ez, oxf = ox + ex, oyf = oy + ey, ozf = oz + ez;
             const bool neg_x = d.x < 0.0f, neg_y = d.y < 0.0f, neg_z = d.z < 0.0f;
             const uint32_t oct_inv4 = oct_inv * 0x01010101u;
 
@@ -138,12 +149,12 @@ __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const Ra
 #pragma unroll
                 for (int j = 0; j < 4; j++)
                 {
-                    const float tnx = __fmaf_rn(quantised_byte_to_float(nearx, j), adx, ox);
-                    const float tny = __fmaf_rn(quantised_byte_to_float(neary, j), ady, oy);
-                    const float tnz = __fmaf_rn(quantised_byte_to_float(nearz, j), adz, oz);
-                    const float tfx = __fmaf_rn(quantised_byte_to_float(farx, j), adx, ox);
-                    const float tfy = __fmaf_rn(quantised_byte_to_float(fary, j), ady, oy);
-                    const float tfz = __fmaf_rn(quantised_byte_to_float(farz, j), adz, oz);
+                    const float tnx = __fmaf_rn(quantised_byte_to_unit_float(nearx, j), adx, oxn);
+                    const float tny = __fmaf_rn(quantised_byte_to_unit_float(neary, j), ady, oyn);
+                    const float tnz = __fmaf_rn(quantised_byte_to_unit_float(nearz, j), adz, ozn);
+                    const float tfx = __fmaf_rn(quantised_byte_to_unit_float(farx, j), adx, oxf);
+                    const float tfy = __fmaf_rn(quantised_byte_to_unit_float(fary, j), ady, oyf);
+                    const float tfz = __fmaf_rn(quantised_byte_to_unit_float(farz, j), adz, ozf);
                     const float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f)) * 0.999999f;
                     const float cmax = fminf(fminf(fminf(tfx, tfy), tfz) * 1.000001f, t_best);
                     if (cmin <= cmax)
@@ -152,11 +163,26 @@ __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const Ra
             }
             ngroup.x = n1.x;
             ngroup.y = (hitmask & 0xFF000000u) | (n0.w >> 24);
-            tgroup.x = n1.y;
-            tgroup.y = hitmask & 0x00FFFFFFu;
+            if ((hitmask & 0x00FFFFFFu) != 0u)
+            {
+                // the node handed out triangles: they become the lane's triangle work, older triangle work waits on the stack
+                if (tgroup.y != 0u)
+                {
+                    if (stack_size < kSharedStackEntries)
+                        my_shared[stack_size * blockDim.x] = tgroup;
+                    else if (stack_size < kTraversalStackSize)
+                        local_stack[stack_size - kSharedStackEntries] = tgroup;
+                    if (stack_size < kTraversalStackSize)
+                        stack_size++;
+                }
+                tgroup = make_uint2(n1.y, hitmask & 0x00FFFFFFu);
+            }
         }
 
-        while (tgroup.y != 0u)
+        // One triangle per lane, and only when enough lanes of the warp have one: the triangle code runs with fuller warps
+        // while the other lanes' triangle work waits (their node work goes on).
+        const unsigned triangle_lanes = __ballot_sync(active_mask, tgroup.y != 0u);
+        if (tgroup.y != 0u && __popc(triangle_lanes) >= min(kTrianglePostponeBelow, __popc(active_mask)))
         {
             const uint32_t tbit = (uint32_t)__ffs((int)tgroup.y) - 1u;
             tgroup.y &= tgroup.y - 1u;
@@ -165,29 +191,29 @@ __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const Ra
             const float4 v0 = __ldg(tp + 0), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
             PT_COUNT(n_tris++;)
             const int prim = __float_as_int(v0.w);
-            if (prim == last_prim)
-                continue;
             float t, u, v;
-            if (intersect_triangle_reference(o, d, f3(v0.x, v0.y, v0.z), f3(v1.x, v1.y, v1.z), f3(v2.x, v2.y, v2.z), t, u, v) && t < t_best)
+            if (prim != last_prim && intersect_triangle_reference(o, d, f3(v0.x, v0.y, v0.z), f3(v1.x, v1.y, v1.z), f3(v2.x, v2.y, v2.z), t, u, v) && t < t_best)
             {
                 t_best = t;
                 hit.prim = prim; hit.tri_slot = (int)tri_index; hit.t = t; hit.u = u; hit.v = v;
                 if (ANY_HIT)
-                {
                     finished = true;
-                    break;
-                }
             }
         }
 
-        if (!finished && ngroup.y <= 0x00FFFFFFu)
+        // Out of node work and of triangle work: next stack entry (a node group, or a triangle group that was set aside)
+        if (!finished && ngroup.y <= 0x00FFFFFFu && tgroup.y == 0u)
         {
             if (stack_size == 0)
                 finished = true;
             else
             {
                 stack_size--;
-                ngroup = stack_size < kSharedStackEntries ? my_shared[stack_size * blockDim.x] : local_stack[stack_size - kSharedStackEntries];
+                const uint2 e = stack_size < kSharedStackEntries ? my_shared[stack_size * blockDim.x] : local_stack[stack_size - kSharedStackEntries];
+                if (e.y > 0x00FFFFFFu)
+                    ngroup = e;
+                else
+                    tgroup = e;
             }
         }
 
