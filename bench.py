@@ -3,7 +3,8 @@
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cornell]
 
-A "step" is one sample pass of the whole 1080p frame per GPU (two kernel launches: CameraRays, FullPathTracer).
+A "step" is one sample pass of the whole 1080p frame per GPU (two launch points: CameraRays, FullPathTracer; the latter
+runs as a wavefront of per-bounce kernels: ray-queue traversal, surface, queue sort, shading phases).
 Metric (BASELINE.json): Mrays/s = BVH queries (trace_ray iterations + shadow rays + shadow-light rays)
 per second, whole job. Rays are counted by the counting build of the SAME kernels on the SAME seeds in an untimed
 pass; the timed passes run the timing build. N > 1: every rank renders its own sample passes of the full frame
@@ -135,6 +136,19 @@ def run_ours(args, cfg, pt):
     rays_per_step = total["rays"] / args.steps
     fpt = {k: total[k] / args.steps - cam[k] for k in total}
 
+    # ---- 1b. stage pass: the same frames with per-stage CUDA events inside FullPathTracer (timing build, untimed otherwise):
+    #          gives the device time of the ray-queue traversal kernels, the kernels the node-fetch roofline is about ----
+    restart()
+    for _ in range(max(args.warmup, 3)):
+        g.render_frame()
+    g.synchronize()
+    ctx.path_profile_enable(True)
+    for _ in range(args.steps):
+        g.render_frame()
+    g.synchronize()
+    stage_ms = {k: v / args.steps for k, v in ctx.path_profile_read(True).items()}
+    ctx.path_profile_enable(False)
+
     # ---- 2. timed pass: timing build, CUDA events on the launching stream ----
     restart()
     for _ in range(max(args.warmup, 3)):
@@ -221,7 +235,14 @@ def run_ours(args, cfg, pt):
     fpt_ms = kernel_ms["FullPathTracer"] / args.steps
     # algorithmic bytes per ray (SURVEY.md 8d / DESIGN.md): 32 B ray in + 16 B hit out + 80 B per node + 48 B per triangle
     fpt_bytes = 48.0 * fpt["rays"] + 80.0 * fpt["nodes"] + 48.0 * fpt["triangles"]
-    achieved = fpt_bytes / (fpt_ms * 1e-3) / 1e9
+    trace_ms = stage_ms["trace"] if stage_ms["trace"] > 0 else fpt_ms    # bounce >= 1 rays + all NEE rays go through the ray-queue kernel
+    achieved = fpt_bytes / (trace_ms * 1e-3) / 1e9
+    # kernels per step (wavefront, phased MIS shape): CameraRays + per bounce {gen | trace + surface} + scan + scatter +
+    # 2 per sampled light kind (eval, BSDF sample) + NEE any-hit trace + NEE closest trace (emissives only) + bsdf
+    nb = cfg["settings"].get("nb_bounces", 8)
+    has_lights, has_env = len(cfg["scene"].emissive) > 0, cfg["envmap"] is not None and cfg["options"]["ess"] != "none"
+    per_bounce = 2 + 2 * has_lights + 2 * has_env + (1 if (has_lights or has_env) else 0) + (1 if has_lights else 0) + 1
+    launches_per_step = 1 + (1 + per_bounce) + nb * (2 + per_bounce)
     out = {
         "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -229,11 +250,13 @@ def run_ours(args, cfg, pt):
                    "l2": "inputs larger than L2: the per-step G-buffer round trip is 345 B/px = 715 MB at 1080p (L2 = 126 MB)",
                    "bvh": bvh_info, "rays_per_step_per_gpu": rays_per_step, "allreduce_ms": reduce_ms},
         "samples_per_px_per_s": world * args.steps / (elapsed_ms * 1e-3),
-        "gpu_launches": 2 * args.steps,
+        "gpu_launches": launches_per_step * args.steps,
         "clocks": clocks,
         "e2e": {"value": total_rays / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 2 * 1328 + 196, "d2h_bytes_per_step": W * H * 12},
-        "roofline": {"bound": "hbm", "kernel": "FullPathTracer", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                     "peak_source": peak_kind, "ms_per_launch": fpt_ms, "camera_rays_ms_per_launch": kernel_ms["CameraRays"] / args.steps,
+        "roofline": {"bound": "hbm", "kernel": "k_trace_queue (ray-queue BVH8 traversal inside FullPathTracer; per step = sum of its launches)", "achieved": achieved, "peak": peak,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "peak_source": peak_kind, "ms_per_launch": trace_ms, "full_path_tracer_ms": fpt_ms, "stage_ms": stage_ms,
+                     "camera_rays_ms_per_launch": kernel_ms["CameraRays"] / args.steps,
                      "rays_per_launch": fpt["rays"], "nodes_per_ray": fpt["nodes"] / max(1.0, fpt["rays"]), "triangles_per_ray": fpt["triangles"] / max(1.0, fpt["rays"])},
     }
 

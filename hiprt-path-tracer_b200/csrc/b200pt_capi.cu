@@ -20,6 +20,12 @@ struct b200pt_ctx
     int path_mode = pt::WF_PHASED;
     pt::WavefrontState wf = {};
     std::vector<void*> wf_allocations;
+    // per-stage timing of FullPathTracer (b200pt_path_profile_enable / _read)
+    bool profiling = false;
+    std::vector<cudaEvent_t> profile_events;
+    std::vector<int> profile_stages;
+    pt::WavefrontProfile profile = {};
+    double stage_ms[4] = {0.0, 0.0, 0.0, 0.0};
 };
 
 struct b200pt_bvh
@@ -143,6 +149,8 @@ int b200pt_ctx_destroy(b200pt_ctx* ctx)
     cudaFree(ctx->d_counters);
     for (void* p : ctx->wf_allocations)
         cudaFree(p);
+    for (cudaEvent_t e : ctx->profile_events)
+        cudaEventDestroy(e);
     cudaStreamDestroy(ctx->main_stream);
     delete ctx;
     return B200PT_SUCCESS;

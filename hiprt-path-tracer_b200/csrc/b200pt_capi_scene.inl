@@ -169,6 +169,8 @@ int b200pt_kernel_variant_select(b200pt_ctx* ctx, const b200pt_options* options)
 
 // Grows the context's wavefront scratch (wavefront.cuh) to `paths` paths and `bounces` bounces. Reallocation waits for
 // the stream: launches in flight may still use the old arrays.
+extern "C" int b200pt_path_profile_read(b200pt_ctx* ctx, double* out_stage_ms, int reset);
+
 static int ensure_wavefront(b200pt_ctx* ctx, uint32_t paths, uint32_t bounces)
 {
     pt::WavefrontState& wf = ctx->wf;
@@ -275,7 +277,62 @@ int b200pt_launch_FullPathTracer(b200pt_ctx* ctx, const HIPRTRenderData* render_
                 return rc;
         }
     }
-    LAUNCH_PIXEL_KERNEL(launch_FullPathTracer, , &ctx->wf, ctx->path_mode)
+    if (ctx->profiling)
+    {
+        // fold the previous launch's intervals in, then hand the event pool to this launch
+        int rc = b200pt_path_profile_read(ctx, nullptr, 0);
+        if (rc != B200PT_SUCCESS)
+            return rc;
+        ctx->profile.count = 0;
+    }
+    pt::WavefrontProfile* profile = ctx->profiling ? &ctx->profile : nullptr;
+    LAUNCH_PIXEL_KERNEL(launch_FullPathTracer, , &ctx->wf, ctx->path_mode, profile)
+}
+
+int b200pt_path_profile_enable(b200pt_ctx* ctx, int enable)
+{
+    REQUIRE(ctx != nullptr);
+    if (enable && ctx->profile_events.empty())
+    {
+        CUDA_TRY(cudaSetDevice(ctx->device));
+        ctx->profile_events.resize(4096);
+        ctx->profile_stages.resize(4096);
+        for (cudaEvent_t& e : ctx->profile_events)
+            CUDA_TRY(cudaEventCreate(&e));
+        ctx->profile.events = ctx->profile_events.data();
+        ctx->profile.stages = ctx->profile_stages.data();
+        ctx->profile.capacity = (int)ctx->profile_events.size();
+    }
+    ctx->profiling = enable != 0;
+    ctx->profile.count = 0;
+    for (double& v : ctx->stage_ms)
+        v = 0.0;
+    return B200PT_SUCCESS;
+}
+
+int b200pt_path_profile_read(b200pt_ctx* ctx, double* out_stage_ms, int reset)
+{
+    REQUIRE(ctx != nullptr);
+    if (ctx->profile.count > 1)
+    {
+        CUDA_TRY(cudaEventSynchronize(ctx->profile.events[ctx->profile.count - 1]));
+        for (int i = 0; i + 1 < ctx->profile.count; i++)
+        {
+            float ms = 0.0f;
+            CUDA_TRY(cudaEventElapsedTime(&ms, ctx->profile.events[i], ctx->profile.events[i + 1]));
+            int s = ctx->profile.stages[i];
+            if (s >= 0 && s < 4)
+                ctx->stage_ms[s] += ms;
+        }
+    }
+    ctx->profile.count = 0;
+    if (out_stage_ms)
+        for (int s = 0; s < 4; s++)
+            out_stage_ms[s] = ctx->stage_ms[s];
+    if (reset)
+        for (double& v : ctx->stage_ms)
+            v = 0.0;
+    return B200PT_SUCCESS;
 }
 
 int b200pt_launch_ReSTIR_DI_LightsPresampling(b200pt_ctx* ctx, const LightPresamplingParameters* parameters, b200pt_stream stream)

@@ -107,8 +107,15 @@ __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_bsdf_resolved)(const 
 }
 #endif
 
-cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const WavefrontState* wf, int mode)
+cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const WavefrontState* wf, int mode, WavefrontProfile* profile)
 {
+    auto stage = [&](int s) {
+        if (profile && profile->count < profile->capacity)
+        {
+            cudaEventRecord(profile->events[profile->count], stream);
+            profile->stages[profile->count++] = s;
+        }
+    };
     dim3 grid((tile.x1 - tile.x0 + 7) / 8, (tile.y1 - tile.y0 + 7) / 8, 1);
     if (mode == WF_MEGAKERNEL || wf == nullptr)
     {
@@ -155,26 +162,31 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
         uint32_t* const counts = wf->counts + kCountsPerBounce * bounce;
         uint32_t* const cursors = wf->cursors + kCursorsPerBounce * bounce;
         (void)counts; (void)cursors;
+        stage(STAGE_SURFACE);
         if (bounce == 0)
             PT_VARIANT_NAME(k_wf_gen)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile, *wf);
 #if PT_LSS == 3
         else if (phased_mis)
         {
+            stage(STAGE_TRACE);
             RayQueueView q = {wf->ray_queue[(bounce - 1) & 1], counts + 0, cursors + 0, wf->origin_rng, wf->dir_prim, wf->hit_tuvp, wf->hit_tri_slot, nullptr};
             e = PT_SUFFIXED(launch_trace_queue)(rd->geom, q, false, trace_blocks, counters, stream);
             if (e != cudaSuccess)
                 return e;
+            stage(STAGE_SURFACE);
             PT_VARIANT_NAME(k_wf_surface)<<<blocks(128), 128, 0, stream>>>(*rd, res, tile, *wf, bounce);
         }
 #endif
         else
             PT_VARIANT_NAME(k_wf_extend)<<<blocks(128), 128, 0, stream>>>(*rd, res, tile, *wf, bounce);
+        stage(STAGE_SORT);
         PT_VARIANT_NAME(k_wf_scan)<<<1, kSortBuckets, 0, stream>>>(*wf);
         PT_VARIANT_NAME(k_wf_scatter)<<<blocks(256), 256, 0, stream>>>(*wf, bounce);
         // the scatter cursors become the next histogram: zero them again
         e = cudaMemsetAsync(wf->bucket_count, 0, sizeof(uint32_t) * kSortBuckets, stream);
         if (e != cudaSuccess)
             return e;
+        stage(STAGE_SHADE);
 #if PT_LSS == 3
         if (phased_mis)
         {
@@ -191,6 +203,7 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
                 PT_VARIANT_NAME(k_wf_env_light_eval)<<<g64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
                 PT_VARIANT_NAME(k_wf_env_bsdf_sample)<<<g64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
             }
+            stage(STAGE_TRACE);
             if (lights || envmap)
             {
                 RayQueueView qa = {wf->any_queue, counts + 2, cursors + 6, wf->nee_ray_o, wf->nee_ray_d, nullptr, nullptr, wf->nee_ray_o};
@@ -205,6 +218,7 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
                 if (e != cudaSuccess)
                     return e;
             }
+            stage(STAGE_SHADE);
             PT_VARIANT_NAME(k_wf_bsdf_resolved)<<<g64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce, lights, envmap);
         }
         else
@@ -217,6 +231,7 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
         else
             PT_VARIANT_NAME(k_wf_shade)<<<blocks(64), 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
     }
+    stage(STAGE_END);
     return cudaGetLastError();
 }
 

@@ -59,6 +59,17 @@ struct WavefrontState
 #define PT_VARIANT_NAME_EXPAND(name, L, E, A, G) PT_VARIANT_NAME_OF(name, L, E, A, G)
 #define PT_VARIANT_NAME(name) PT_VARIANT_NAME_EXPAND(name, PT_LSS, PT_ESS, PT_LATER, PT_GGX)
 
+// Optional per-stage timing of one FullPathTracer launch (b200pt_path_profile_*): the launcher records an event at every
+// change of stage; the context sums the intervals per stage after the stream has drained.
+enum WavefrontStage { STAGE_TRACE = 0, STAGE_SURFACE = 1, STAGE_SORT = 2, STAGE_SHADE = 3, STAGE_END = 4 };
+struct WavefrontProfile
+{
+    cudaEvent_t* events;
+    int* stages;      // stage that starts at events[i]
+    int capacity;
+    int count;
+};
+
 // Input/output arrays of one launch of the ray-queue traversal kernel (trace_queue.cuh)
 struct RayQueueView
 {
@@ -75,7 +86,7 @@ struct RayQueueView
 #define PT_DECLARE_LAUNCHERS(S)                                                                                                        \
     bool variant_available##S(const VariantOptions& opt);                                                                              \
     cudaError_t launch_CameraRays##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream);   \
-    cudaError_t launch_FullPathTracer##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const WavefrontState* wf, int mode); \
+    cudaError_t launch_FullPathTracer##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const WavefrontState* wf, int mode, WavefrontProfile* profile); \
     cudaError_t launch_trace_queue##S(const void* bvh_device_handle, const RayQueueView& q, bool any_hit, unsigned blocks, TraversalCounters* counters, cudaStream_t stream); \
     cudaError_t launch_trace_closest##S(const Bvh8Device& bvh, const float* rays, const int* last_prim, long long n, int* out_prim, float* out_t, float* out_uv, TraversalCounters* counters, cudaStream_t stream); \
     cudaError_t launch_trace_shadow##S(const Bvh8Device& bvh, const float* rays, const float* t_max, const int* last_prim, long long n, unsigned char* out_occluded, TraversalCounters* counters, cudaStream_t stream);

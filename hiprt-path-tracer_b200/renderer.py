@@ -116,6 +116,15 @@ class Context:
         m = {"megakernel": 0, "fused": 1, "split": 2, "phased": 3}[mode] if isinstance(mode, str) else int(mode)
         _capi.check(self.lib.b200pt_set_path_mode(self.handle, C.c_int(m)), "b200pt_set_path_mode")
 
+    def path_profile_enable(self, enable=True):
+        _capi.check(self.lib.b200pt_path_profile_enable(self.handle, C.c_int(1 if enable else 0)), "b200pt_path_profile_enable")
+
+    def path_profile_read(self, reset=True):
+        """ms per stage of the wavefront FullPathTracer since the last reset."""
+        out = (C.c_double * 4)()
+        _capi.check(self.lib.b200pt_path_profile_read(self.handle, out, C.c_int(1 if reset else 0)), "b200pt_path_profile_read")
+        return {"trace": out[0], "surface": out[1], "sort": out[2], "shade": out[3]}
+
     def counters_enable(self, enable=True):
         _capi.check(self.lib.b200pt_counters_enable(self.handle, C.c_int(1 if enable else 0)), "b200pt_counters_enable")
 

@@ -141,6 +141,11 @@ B200PT_API int b200pt_kernel_variant_select(b200pt_ctx* ctx, const b200pt_option
  * cut into phases (light eval / BSDF samples / NEE rays / bounce), one small kernel each.
  * Same per-path arithmetic and RNG order in all four: same bits. */
 B200PT_API int b200pt_set_path_mode(b200pt_ctx* ctx, int mode);
+/* Device time of the stages of the wavefront FullPathTracer, summed over the launches since the last reset:
+ * out_stage_ms[4] = { ray-queue traversal kernels, gen/surface (hit -> shading data), queue sort, shading phases }.
+ * Measured with CUDA events on the launching stream between the stages' kernels. */
+B200PT_API int b200pt_path_profile_enable(b200pt_ctx* ctx, int enable);
+B200PT_API int b200pt_path_profile_read(b200pt_ctx* ctx, double* out_stage_ms, int reset);
 B200PT_API int b200pt_launch_CameraRays(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream);
 B200PT_API int b200pt_launch_FullPathTracer(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream);
 B200PT_API int b200pt_launch_ReSTIR_DI_LightsPresampling(b200pt_ctx* ctx, const LightPresamplingParameters* parameters, b200pt_stream stream);
