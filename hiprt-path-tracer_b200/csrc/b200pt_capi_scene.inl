@@ -337,20 +337,44 @@ int b200pt_path_profile_read(b200pt_ctx* ctx, double* out_stage_ms, int reset)
 
 int b200pt_launch_ReSTIR_DI_LightsPresampling(b200pt_ctx* ctx, const LightPresamplingParameters* parameters, b200pt_stream stream)
 {
-    (void)ctx; (void)parameters; (void)stream;
-    return fail(B200PT_ERROR_VARIANT_NOT_COMPILED, "ReSTIR_DI_LightsPresampling is not built yet");
+    REQUIRE(ctx != nullptr && parameters != nullptr && parameters->out_light_samples != nullptr);
+    cudaError_t e = pt::launch_ReSTIR_DI_LightsPresampling_t(ctx->options, parameters, stream_of(ctx, stream));
+    if (e == cudaErrorInvalidDeviceFunction)
+        return fail(B200PT_ERROR_VARIANT_NOT_COMPILED, "ReSTIR DI passes need a LSS_RESTIR_DI kernel permutation (b200pt_kernel_variant_select)");
+    if (e != cudaSuccess)
+        return cuda_fail(e, "ReSTIR_DI_LightsPresampling");
+    return B200PT_SUCCESS;
 }
+
+#define LAUNCH_RESTIR_PIXEL_KERNEL(NAME)                                                                                           \
+    REQUIRE(ctx != nullptr && render_data != nullptr && res.x > 0 && res.y > 0);                                                   \
+    REQUIRE(render_data->geom != nullptr);                                                                                         \
+    pt::Tile t = tile_of(tile, res);                                                                                               \
+    if (t.x1 <= t.x0 || t.y1 <= t.y0)                                                                                              \
+        return B200PT_SUCCESS;                                                                                                     \
+    cudaError_t e;                                                                                                                 \
+    if (ctx->counting)                                                                                                             \
+    {                                                                                                                              \
+        HIPRTRenderData copy = *render_data;                                                                                       \
+        copy.hiprt_function_table = ctx->d_counters;                                                                               \
+        e = pt::NAME##_c(ctx->options, &copy, make_int2(res.x, res.y), t, stream_of(ctx, stream));                                 \
+    }                                                                                                                              \
+    else                                                                                                                           \
+        e = pt::NAME##_t(ctx->options, render_data, make_int2(res.x, res.y), t, stream_of(ctx, stream));                           \
+    if (e == cudaErrorInvalidDeviceFunction)                                                                                       \
+        return fail(B200PT_ERROR_VARIANT_NOT_COMPILED, "ReSTIR DI passes need a LSS_RESTIR_DI kernel permutation (b200pt_kernel_variant_select)"); \
+    if (e != cudaSuccess)                                                                                                          \
+        return cuda_fail(e, #NAME);                                                                                                \
+    return B200PT_SUCCESS;
 
 int b200pt_launch_ReSTIR_DI_InitialCandidates(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream)
 {
-    (void)ctx; (void)render_data; (void)res; (void)tile; (void)stream;
-    return fail(B200PT_ERROR_VARIANT_NOT_COMPILED, "ReSTIR_DI_InitialCandidates is not built yet");
+    LAUNCH_RESTIR_PIXEL_KERNEL(launch_ReSTIR_DI_InitialCandidates)
 }
 
 int b200pt_launch_ReSTIR_DI_SpatiotemporalReuse(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream)
 {
-    (void)ctx; (void)render_data; (void)res; (void)tile; (void)stream;
-    return fail(B200PT_ERROR_VARIANT_NOT_COMPILED, "ReSTIR_DI_SpatiotemporalReuse is not built yet");
+    LAUNCH_RESTIR_PIXEL_KERNEL(launch_ReSTIR_DI_SpatiotemporalReuse)
 }
 
 int b200pt_trace_closest(b200pt_ctx* ctx, b200pt_bvh* bvh, const float* d_rays, const int* d_last_prim, long long n, int* d_out_prim, float* d_out_t, float* d_out_uv, b200pt_stream stream)

@@ -1,6 +1,9 @@
 // One FullPathTracer permutation per translation unit: compile with -DPT_LSS= -DPT_ESS= -DPT_LATER= -DPT_GGX=
 // Holds the megakernel and the wavefront kernels (wavefront.cuh) of the permutation plus their launcher.
 #include "wavefront_mis.cuh"
+#if PT_LSS == 5
+#include "restir_di_kernels.cuh"
+#endif
 
 namespace pt
 {
@@ -235,4 +238,53 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
     return cudaGetLastError();
 }
 
+
+#if PT_LSS == 5
+// ---- ReSTIR DI passes (restir_di_kernels.cuh); compiled with the LSS_RESTIR_DI permutations only --------------------------------
+__global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_ReSTIR_DI_LightsPresampling)(const __grid_constant__ LightPresamplingParameters p)
+{
+    restir_presample_light<PT_ESS>(p, blockIdx.x * blockDim.x + threadIdx.x);
+}
+
+__global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_ReSTIR_DI_InitialCandidates)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile)
+{
+    const uint32_t x = tile.x0 + blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t y = tile.y0 + blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= (uint32_t)tile.x1 || y >= (uint32_t)tile.y1)
+        return;
+    restir_initial_candidates_pixel<PT_GGX>(rd, res, x, y);
+}
+
+__global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_ReSTIR_DI_SpatiotemporalReuse)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile)
+{
+    const uint32_t x = tile.x0 + blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t y = tile.y0 + blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= (uint32_t)tile.x1 || y >= (uint32_t)tile.y1)
+        return;
+    restir_spatiotemporal_pixel(rd, res, x, y);
+}
+
+cudaError_t PT_VARIANT_NAME(launch_ReSTIR_DI_LightsPresampling)(const LightPresamplingParameters* p, cudaStream_t stream)
+{
+    const long long n = (long long)p->subset_size * p->number_of_subsets;
+    if (n <= 0)
+        return cudaSuccess;
+    PT_VARIANT_NAME(k_ReSTIR_DI_LightsPresampling)<<<(unsigned)((n + 63) / 64), 64, 0, stream>>>(*p);
+    return cudaGetLastError();
+}
+
+cudaError_t PT_VARIANT_NAME(launch_ReSTIR_DI_InitialCandidates)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream)
+{
+    dim3 grid((tile.x1 - tile.x0 + 7) / 8, (tile.y1 - tile.y0 + 7) / 8, 1);
+    PT_VARIANT_NAME(k_ReSTIR_DI_InitialCandidates)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile);
+    return cudaGetLastError();
+}
+
+cudaError_t PT_VARIANT_NAME(launch_ReSTIR_DI_SpatiotemporalReuse)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream)
+{
+    dim3 grid((tile.x1 - tile.x0 + 7) / 8, (tile.y1 - tile.y0 + 7) / 8, 1);
+    PT_VARIANT_NAME(k_ReSTIR_DI_SpatiotemporalReuse)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile);
+    return cudaGetLastError();
+}
+#endif
 } // namespace pt

@@ -70,6 +70,42 @@ static inline dim3 pixel_grid(const Tile& t) { return dim3((t.x1 - t.x0 + 7) / 8
 #define PT_DECLARE_VARIANT(LSS, ESS, LATER, GGX) cudaError_t PT_VARIANT_NAME_OF(launch_FullPathTracer, LSS, ESS, LATER, GGX)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const WavefrontState* wf, int mode, WavefrontProfile* profile);
 PT_FOR_EACH_VARIANT(PT_DECLARE_VARIANT)
 
+#define PT_DECLARE_RESTIR(LSS, ESS, LATER, GGX)                                                                                                                    \
+    cudaError_t PT_VARIANT_NAME_OF(launch_ReSTIR_DI_LightsPresampling, LSS, ESS, LATER, GGX)(const LightPresamplingParameters* p, cudaStream_t stream);              \
+    cudaError_t PT_VARIANT_NAME_OF(launch_ReSTIR_DI_InitialCandidates, LSS, ESS, LATER, GGX)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream);    \
+    cudaError_t PT_VARIANT_NAME_OF(launch_ReSTIR_DI_SpatiotemporalReuse, LSS, ESS, LATER, GGX)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream);
+#define PT_DECLARE_RESTIR_IF_5(LSS, ESS, LATER, GGX) PT_DECLARE_RESTIR_##LSS(LSS, ESS, LATER, GGX)
+#define PT_DECLARE_RESTIR_3(LSS, ESS, LATER, GGX)
+#define PT_DECLARE_RESTIR_4(LSS, ESS, LATER, GGX)
+#define PT_DECLARE_RESTIR_5(LSS, ESS, LATER, GGX) PT_DECLARE_RESTIR(LSS, ESS, LATER, GGX)
+PT_FOR_EACH_VARIANT(PT_DECLARE_RESTIR_IF_5)
+
+// ReSTIR DI passes exist for the LSS_RESTIR_DI permutations only; other options get cudaErrorInvalidDeviceFunction
+#define PT_CASE_RESTIR_3(CALL, LSS, ESS, LATER, GGX)
+#define PT_CASE_RESTIR_4(CALL, LSS, ESS, LATER, GGX)
+#define PT_CASE_RESTIR_5(CALL, LSS, ESS, LATER, GGX) if (opt.lss == LSS && opt.ess == ESS && opt.later == LATER && opt.ggx == GGX) return CALL;
+
+cudaError_t PT_SUFFIXED(launch_ReSTIR_DI_LightsPresampling)(const VariantOptions& opt, const LightPresamplingParameters* p, cudaStream_t stream)
+{
+#define PT_CASE_PRESAMPLE(LSS, ESS, LATER, GGX) PT_CASE_RESTIR_##LSS(PT_VARIANT_NAME_OF(launch_ReSTIR_DI_LightsPresampling, LSS, ESS, LATER, GGX)(p, stream), LSS, ESS, LATER, GGX)
+    PT_FOR_EACH_VARIANT(PT_CASE_PRESAMPLE)
+    return cudaErrorInvalidDeviceFunction;
+}
+
+cudaError_t PT_SUFFIXED(launch_ReSTIR_DI_InitialCandidates)(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream)
+{
+#define PT_CASE_INITIAL(LSS, ESS, LATER, GGX) PT_CASE_RESTIR_##LSS(PT_VARIANT_NAME_OF(launch_ReSTIR_DI_InitialCandidates, LSS, ESS, LATER, GGX)(rd, res, tile, stream), LSS, ESS, LATER, GGX)
+    PT_FOR_EACH_VARIANT(PT_CASE_INITIAL)
+    return cudaErrorInvalidDeviceFunction;
+}
+
+cudaError_t PT_SUFFIXED(launch_ReSTIR_DI_SpatiotemporalReuse)(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream)
+{
+#define PT_CASE_SPATIOTEMPORAL(LSS, ESS, LATER, GGX) PT_CASE_RESTIR_##LSS(PT_VARIANT_NAME_OF(launch_ReSTIR_DI_SpatiotemporalReuse, LSS, ESS, LATER, GGX)(rd, res, tile, stream), LSS, ESS, LATER, GGX)
+    PT_FOR_EACH_VARIANT(PT_CASE_SPATIOTEMPORAL)
+    return cudaErrorInvalidDeviceFunction;
+}
+
 bool PT_SUFFIXED(variant_available)(const VariantOptions& opt)
 {
 #define PT_CASE_AVAIL(LSS, ESS, LATER, GGX) if (opt.lss == LSS && opt.ess == ESS && (opt.lss != 5 || opt.later == LATER) && opt.ggx == GGX) return true;

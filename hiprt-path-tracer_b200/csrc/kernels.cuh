@@ -4,7 +4,6 @@
 #pragma once
 
 #include "envmap.cuh"
-#include "restir_di.cuh"
 
 namespace pt
 {
@@ -95,6 +94,10 @@ PT_DEV void copy_volume_state(RayVolumeState* dst, const RayVolumeState* src)
     for (int i = 0; i < 9; i++)
         d[i] = s[i];
 }
+
+} // namespace pt
+#include "restir_di.cuh"
+namespace pt {
 
 PT_DEV void reset_reservoir(ReSTIRDIReservoir* r)
 {

@@ -422,6 +422,53 @@ void GPURenderer::launch_ReSTIR_DI()
 {
     if (m_options.direct_light_sampling_strategy != 5)
         return;
-    throw std::runtime_error("ReSTIR DI render pass is not built yet");
+
+    // ReSTIRDIRenderPass::launch (ReSTIRDIRenderPass.cpp:306-352) / CPURenderer::ReSTIR_DI (CPURenderer.cpp:401-434):
+    // presampling -> initial candidates -> fused spatiotemporal reuse, each with its own seed draw
+    HIPRTRenderData& rd = m_render_data;
+    ReSTIRDISettings& rs = rd.render_settings.restir_di_settings;
+    if (!rs.do_fused_spatiotemporal || !rs.temporal_pass.do_temporal_reuse_pass || !rs.spatial_pass.do_spatial_reuse_pass)
+        throw std::runtime_error("ReSTIR DI: only the fused spatiotemporal reuse pass is built (do_fused_spatiotemporal with temporal and spatial reuse enabled)");
+    const b200pt_tile* tile = m_has_tile ? &m_tile : nullptr;
+
+    // ReSTIRDIRenderPass::launch_presampling_lights_pass / configure (ReSTIRDIRenderPass.cpp:354-386)
+    LightPresamplingParameters p;
+    std::memset(&p, 0, sizeof(p));
+    p.number_of_subsets = rs.light_presampling.number_of_subsets;
+    p.subset_size = rs.light_presampling.subset_size;
+    p.out_light_samples = m_restir_presampled_lights.get_device_pointer();
+    p.emissive_triangles_count = rd.buffers.emissive_triangles_count;
+    p.emissive_triangles_indices = rd.buffers.emissive_triangles_indices;
+    p.triangles_indices = rd.buffers.triangles_indices;
+    p.vertices_positions = rd.buffers.vertices_positions;
+    p.material_indices = rd.buffers.material_indices;
+    p.materials = rd.buffers.materials_buffer;
+    p.world_settings = rd.world_settings;
+    p.freeze_random = rd.render_settings.freeze_random;
+    p.sample_number = rd.render_settings.sample_number;
+    p.random_seed = m_rng.xorshift32();
+    p.envmap_sampling_probability = rs.initial_candidates.envmap_candidate_probability;
+    check(b200pt_launch_ReSTIR_DI_LightsPresampling(m_ctx, &p, nullptr), "b200pt_launch_ReSTIR_DI_LightsPresampling");
+
+    // initial candidates (ReSTIRDIRenderPass.cpp:388-403)
+    rd.random_seed = m_rng.xorshift32();
+    rs.light_presampling.light_samples = m_restir_presampled_lights.get_device_pointer();
+    rs.initial_candidates.output_reservoirs = m_restir_initial.get_device_pointer();
+    check(b200pt_launch_ReSTIR_DI_InitialCandidates(m_ctx, &rd, m_res, tile, nullptr), "b200pt_launch_ReSTIR_DI_InitialCandidates");
+
+    // fused spatiotemporal reuse (ReSTIRDIRenderPass.cpp:505-548): last frame's output is this frame's temporal input
+    rd.random_seed = m_rng.xorshift32();
+    rs.temporal_pass.permutation_sampling_random_bits = m_rng.xorshift32();
+    ReSTIRDIReservoir* previous = m_restir_odd_frame ? m_restir_spatial_1.get_device_pointer() : m_restir_spatial_2.get_device_pointer();
+    ReSTIRDIReservoir* output = m_restir_odd_frame ? m_restir_spatial_2.get_device_pointer() : m_restir_spatial_1.get_device_pointer();
+    rs.temporal_pass.input_reservoirs = previous;
+    rs.temporal_pass.output_reservoirs = nullptr;
+    rs.spatial_pass.input_reservoirs = previous;
+    rs.spatial_pass.output_reservoirs = output;
+    check(b200pt_launch_ReSTIR_DI_SpatiotemporalReuse(m_ctx, &rd, m_res, tile, nullptr), "b200pt_launch_ReSTIR_DI_SpatiotemporalReuse");
+
+    // configure_output_buffer (ReSTIRDIRenderPass.cpp:550-563)
+    rs.restir_output_reservoirs = output;
+    m_restir_odd_frame = !m_restir_odd_frame;
 }
 } // namespace b200pt_host

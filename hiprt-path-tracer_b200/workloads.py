@@ -62,8 +62,13 @@ def many_lights(width, height, boxes=2000, lights=100_000):
 
 
 def apply_settings(render_settings, settings):
+    """Keys may be dotted to reach nested settings, e.g. "restir_di_settings.spatial_pass.reuse_neighbor_count"."""
     for k, v in settings.items():
-        setattr(render_settings, k, v)
+        target = render_settings
+        *parents, leaf = k.split(".")
+        for name in parents:
+            target = getattr(target, name)
+        setattr(target, leaf, v)
 
 
 def setup_gpu(pt, ctx, cfg, seed_schedule="gpu"):
