@@ -2,6 +2,7 @@
 // :980-1039 (update_render_data), :1041-1174 (set_scene / set_envmap); CPU seed schedule: src/Renderer/CPURenderer.cpp:264-296.
 #include "GPURenderer.h"
 
+#include <algorithm>
 #include <cstring>
 
 namespace b200pt_host
@@ -259,6 +260,8 @@ void GPURenderer::set_tile(const b200pt_tile* tile)
     if (tile) m_tile = *tile;
 }
 
+void GPURenderer::set_tile_halo(int rows) { m_tile_halo = rows > 0 ? rows : 0; }
+
 void GPURenderer::resize(int width, int height)
 {
     synchronize_kernel();
@@ -408,7 +411,15 @@ void GPURenderer::launch_camera_rays()
 {
     if (seed_schedule == SeedSchedule::GPU)
         m_render_data.random_seed = m_rng.xorshift32();
-    check(b200pt_launch_CameraRays(m_ctx, &m_render_data, m_res, m_has_tile ? &m_tile : nullptr, nullptr), "b200pt_launch_CameraRays");
+    // A ReSTIR DI tile also needs the G-buffer (and last frame's) of the halo rows its spatiotemporal pass reads: CameraRays is
+    // deterministic per pixel, so the rank recomputes those rows instead of receiving 344 B/px from the neighbouring rank
+    b200pt_tile camera_tile = m_tile;
+    if (m_has_tile && m_tile_halo > 0 && m_tile.y1 > m_tile.y0)
+    {
+        camera_tile.y0 = std::max(0, m_tile.y0 - m_tile_halo);
+        camera_tile.y1 = std::min(m_res.y, m_tile.y1 + m_tile_halo);
+    }
+    check(b200pt_launch_CameraRays(m_ctx, &m_render_data, m_res, m_has_tile ? &camera_tile : nullptr, nullptr), "b200pt_launch_CameraRays");
 }
 
 void GPURenderer::launch_path_tracing()

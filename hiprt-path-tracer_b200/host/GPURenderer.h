@@ -140,6 +140,7 @@ public:
     void set_kernel_options(const b200pt_options& options);                          // GPUKernelCompilerOptions -> prebuilt permutation
     void resize(int width, int height);                                               // GPURenderer.cpp:resize
     void set_tile(const b200pt_tile* tile);                                           // multi-GPU image shard (new)
+    void set_tile_halo(int rows);                                                     // rows either side of the tile CameraRays also covers (ReSTIR DI)
     void reset();
 
     void update();                                                                    // GPURenderer.cpp:236-267
@@ -194,6 +195,7 @@ private:
     b200pt_int2 m_res = {0, 0};
     bool m_has_tile = false;
     b200pt_tile m_tile = {0, 0, 0, 0};
+    int m_tile_halo = 0;
     Xorshift32Generator m_rng;
     HIPRTCamera m_camera;
     bool m_restir_odd_frame = false;

@@ -1,0 +1,106 @@
+"""Multi-GPU plumbing of the render path: one process per GPU, scene + BVH8 replicated, the image sharded by
+row tiles or by sample passes. The reference has no distributed backend (single device, src/main.cpp:57); this is new.
+
+  * tile sharding      rank r renders rows [y0_r, y1_r) with the global pixel_index = x + y*W, so its pixels are bit-identical to
+                       the 1-GPU render; `gather_rows` assembles the frame once per output (not per sample).
+  * sample-pass        every rank renders the full frame for disjoint sample numbers; `reduce_accumulation` sums the accumulation
+    sharding           buffers (RenderData.h:34-36 pixels, AuxiliaryBuffers pixel_squared_luminance / pixel_sample_count).
+  * ReSTIR DI halo     the fused spatiotemporal pass reads last frame's output reservoirs within reuse_radius of the temporal
+                       position, itself within neighbor_search_radius of the pixel (ReSTIRDISettings.h:42,65; Utils.h:301-366,
+                       426-478): `restir_halo_rows` rows either side of a tile. The G-buffer and this frame's initial candidates
+                       are deterministic per pixel, so each rank recomputes CameraRays over tile + halo itself
+                       (GPURenderer::set_tile_halo) and only the 36-byte reservoirs of the halo rows travel (`exchange_halo`).
+
+The collectives are torch.distributed calls on tensors that alias the renderer's device buffers (`device_rows`): NCCL over NVLink on
+the GPUs, gloo on CPU tensors in tests/test_multigpu_gloo.py. Buffers are viewed as [H, row_bytes] so that a band of rows is one
+contiguous slice.
+"""
+import torch
+
+
+def row_tiles(height, world, align=8):
+    """Contiguous row bands, one per rank, each a multiple of `align` rows (the 8x8 launch blocks) except the last."""
+    if world < 1 or height < 0:
+        raise ValueError("row_tiles: world must be >= 1 and height >= 0")
+    blocks = (height + align - 1) // align
+    bounds = [min(height, align * ((blocks * r) // world)) for r in range(world)] + [height]
+    return [(bounds[r], bounds[r + 1]) for r in range(world)]
+
+
+def restir_halo_rows(reuse_radius=16, neighbor_search_radius=4, camera_motion_rows=0):
+    """Rows of neighbour data the fused ReSTIR DI pass can reach above and below a tile."""
+    return int(reuse_radius) + int(neighbor_search_radius) + int(camera_motion_rows)
+
+
+def halo_plan(tiles, rank, halo):
+    """[(peer, (send_y0, send_y1), (recv_y0, recv_y1))]: what `rank` sends from its own rows and receives into its halo rows.
+    A halo wider than a neighbour's tile reaches the next rank too, so every rank whose rows fall inside the halo is a peer."""
+    y0, y1 = tiles[rank]
+    if y1 <= y0 or halo <= 0:
+        return []
+    height = tiles[-1][1]
+    lo, hi = max(0, y0 - halo), min(height, y1 + halo)
+    plan = []
+    for peer, (p0, p1) in enumerate(tiles):
+        if peer == rank or p1 <= p0:
+            continue
+        # rows of the peer inside my halo: I receive them
+        r0, r1 = max(p0, lo), min(p1, hi)
+        # rows of mine inside the peer's halo: I send them
+        s0, s1 = max(y0, p0 - halo), min(y1, p1 + halo)
+        recv = (r0, r1) if r1 > r0 else None
+        send = (s0, s1) if s1 > s0 else None
+        if recv or send:
+            plan.append((peer, send, recv))
+    return plan
+
+
+def exchange_halo(dist, rows, tiles, rank, halo):
+    """rows: [H, row_bytes] tensor aliasing a per-pixel buffer whose rows tiles[rank] this rank has just written. After the call
+    the rows within `halo` of the tile hold the owners' values. One grouped batch of point-to-point operations."""
+    ops = []
+    for peer, send, recv in halo_plan(tiles, rank, halo):
+        if send:
+            ops.append(dist.P2POp(dist.isend, rows[send[0]:send[1]], peer))
+        if recv:
+            ops.append(dist.P2POp(dist.irecv, rows[recv[0]:recv[1]], peer))
+    if ops:
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+    return len(ops)
+
+
+def gather_rows(dist, rows, tiles):
+    """Every rank ends with the whole [H, row_bytes] buffer: each tile is broadcast by its owner, in place."""
+    for owner, (y0, y1) in enumerate(tiles):
+        if y1 > y0:
+            dist.broadcast(rows[y0:y1], src=owner)
+
+
+def reduce_accumulation(dist, pixels, squared_luminance=None, sample_count=None):
+    """Sample-pass sharding: sum the accumulation buffers over ranks so that adaptive sampling decides on global statistics
+    (AdaptiveSampling.h:30-104). Float summation order changes: statistically, not bitwise, equal to the 1-GPU render."""
+    dist.all_reduce(pixels, op=dist.ReduceOp.SUM)
+    if squared_luminance is not None:
+        dist.all_reduce(squared_luminance, op=dist.ReduceOp.SUM)
+    if sample_count is not None:
+        dist.all_reduce(sample_count, op=dist.ReduceOp.SUM)
+
+
+class _DevicePointer:
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"shape": shape, "typestr": typestr, "data": (int(ptr), False), "version": 3}
+
+
+def device_rows(ptr, height, row_bytes, device):
+    """[H, row_bytes] uint8 tensor aliasing a renderer device buffer (no copy)."""
+    if not ptr:
+        raise ValueError("device_rows: null device pointer")
+    return torch.as_tensor(_DevicePointer(ptr, (int(height), int(row_bytes)), "|u1"), device=device)
+
+
+def device_array(ptr, shape, typestr, device):
+    """Typed tensor aliasing a renderer device buffer, e.g. the float32 [H, W, 3] accumulation buffer."""
+    if not ptr:
+        raise ValueError("device_array: null device pointer")
+    return torch.as_tensor(_DevicePointer(ptr, tuple(int(s) for s in shape), typestr), device=device)

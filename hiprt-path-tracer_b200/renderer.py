@@ -194,12 +194,14 @@ class GPURenderer:
         _capi.check_host(self.host.b200pt_renderer_resize(self.handle, C.c_int(width), C.c_int(height)), "b200pt_renderer_resize")
         self.width, self.height = width, height
 
-    def set_tile(self, tile):
+    def set_tile(self, tile, halo=0):
+        """tile = (x0, y0, x1, y1) or None; halo = rows either side CameraRays also renders (ReSTIR DI tile sharding)."""
         if tile is None:
             self.host.b200pt_renderer_set_tile(self.handle, None)
         else:
             t = S.Tile(*tile)
             self.host.b200pt_renderer_set_tile(self.handle, C.byref(t))
+        self.host.b200pt_renderer_set_tile_halo(self.handle, C.c_int(halo))
 
     def reset(self):
         self.host.b200pt_renderer_reset(self.handle)

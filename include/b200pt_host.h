@@ -37,6 +37,9 @@ B200PT_API int b200pt_host_compute_alias_table(const float* texels, int width, i
 B200PT_API int b200pt_renderer_set_camera(b200pt_renderer* r, const HIPRTCamera* camera);
 B200PT_API int b200pt_renderer_resize(b200pt_renderer* r, int width, int height);
 B200PT_API int b200pt_renderer_set_tile(b200pt_renderer* r, const b200pt_tile* tile);
+/* Tile sharding with ReSTIR DI (new): CameraRays also covers `rows` rows above and below the tile, so that the
+ * G-buffers the fused spatiotemporal pass reads around the tile are computed locally; only reservoirs are exchanged. */
+B200PT_API int b200pt_renderer_set_tile_halo(b200pt_renderer* r, int rows);
 B200PT_API int b200pt_renderer_reset(b200pt_renderer* r);
 /* Host-side structs the caller may edit between frames (copied by value into each launch) */
 B200PT_API HIPRTRenderSettings* b200pt_renderer_render_settings(b200pt_renderer* r);

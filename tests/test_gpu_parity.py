@@ -1,6 +1,7 @@
 """GPU parity tests proper: the CUDA path, called through the C ABI, against the oracle (the reference's own CPU kernels)
 and against the committed golden vectors. Bars (BASELINE.json north_star): hit primitive ids bit-exact on fixed ray
 batches (exact distance ties excluded); radiance within 1e-3 mean relative error with matched RNG streams."""
+import importlib
 import os
 
 import numpy as np
@@ -290,3 +291,47 @@ def test_restir_di_parity(pt, wl, ctx, ref):
     assert err < 1e-3, err
     assert abs(a.mean() - b.mean()) / a.mean() < 1e-3
     g.close()
+
+
+def test_restir_di_tile_sharding_with_halo_is_bit_identical(pt, wl, ctx):
+    """The multi-GPU shard shape of config C4 on one device: two renderers own the two halves of the image, each runs CameraRays
+    over tile + 20 halo rows, and after every frame only the output reservoirs of the halo rows are copied across (what
+    multigpu.exchange_halo does over NCCL). The union of the tiles must equal the unsharded render bit for bit."""
+    import ctypes as C
+    mg = importlib.import_module("hiprt-path-tracer_b200.multigpu")
+    W, H, frames = 128, 96, 4
+    cfg = wl.many_lights(W, H, boxes=150, lights=3000)
+    whole = wl.setup_gpu(pt, ctx, cfg, seed_schedule="cpu")
+    for _ in range(frames):
+        whole.render_frame()
+    whole.synchronize()
+    want = whole.download("pixels").reshape(H, W, 3).copy()
+    want_res = whole.download("restir_output_reservoirs").reshape(H, W, 36).copy()
+    whole.close()
+
+    tiles = mg.row_tiles(H, 2)
+    halo = mg.restir_halo_rows()
+    parts = []
+    for y0, y1 in tiles:
+        g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="cpu")
+        g.set_tile((0, y0, W, y1), halo=halo)
+        parts.append(g)
+    row_bytes = W * 36
+    for _ in range(frames):
+        for g in parts:
+            g.render_frame()
+        for g in parts:
+            g.synchronize()
+        for rank, g in enumerate(parts):
+            for peer, send, recv in mg.halo_plan(tiles, rank, halo):
+                if recv:
+                    src = parts[peer].device_pointer("restir_output_reservoirs") + recv[0] * row_bytes
+                    dst = g.device_pointer("restir_output_reservoirs") + recv[0] * row_bytes
+                    pt._capi.check(ctx.lib.b200pt_memcpy_d2d(ctx.handle, C.c_void_p(dst), C.c_void_p(src), C.c_size_t((recv[1] - recv[0]) * row_bytes), None), "d2d")
+        ctx.sync()
+    for (y0, y1), g in zip(tiles, parts):
+        got = g.download("pixels").reshape(H, W, 3)
+        got_res = g.download("restir_output_reservoirs").reshape(H, W, 36)
+        assert np.array_equal(got_res[y0:y1], want_res[y0:y1]), (y0, y1)
+        assert np.array_equal(got[y0:y1], want[y0:y1]), (y0, y1)
+        g.close()
