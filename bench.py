@@ -79,7 +79,7 @@ def run_reference(args, cfg, pt):
     sample = f"{args.steps} full sample passes of {cfg['name']} (one step = 1 spp of the whole frame), OpenMP over rows"
     return {
         "impl": "reference", "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong" if (world > 1 and sharding == "tiles") else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": cfg["name"]}, "samples_per_px_per_s": args.steps / dt,
         "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": "reference", "sample": sample},
         "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -102,6 +102,14 @@ def run_ours(args, cfg, pt):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     W, H = cfg["width"], cfg["height"]
+    mg = importlib.import_module("hiprt-path-tracer_b200.multigpu")
+    restir = cfg["options"]["lss"] == "restir_di"
+    sharding = args.sharding if args.sharding != "auto" else ("samples" if args.workload == "cornell" else "tiles")
+    if restir:
+        sharding = "tiles"              # reservoirs are per pixel and per frame: ReSTIR DI shards by tiles + halo only
+    tiles = mg.row_tiles(H, world)
+    halo = mg.restir_halo_rows() if restir else 0
+    device = torch.device("cuda", local_rank)
     ctx = pt.Context(local_rank)
     g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="gpu")
     lib = ctx.lib
@@ -113,19 +121,33 @@ def run_ours(args, cfg, pt):
         g.reset()
         g.resize(W, H)
         wl.apply_settings(g.render_settings, cfg["settings"])
-        if rank > 0:
+        if world > 1 and sharding == "tiles":
+            # Tile sharding: rank r owns rows tiles[r]; global pixel indices and the shared seed sequence make its pixels
+            # bit-identical to the 1-GPU render (tests/test_gpu_parity.py::test_tile_sharding_*, test_restir_di_tile_sharding_*)
+            g.set_tile((0, tiles[rank][0], W, tiles[rank][1]), halo=halo)
+        elif rank > 0:
             g.render_settings.sample_number = rank << 20
             g.render_settings.need_to_reset = 0
+
+    def step():
+        g.render_frame()
+        if restir and world > 1:
+            # ReSTIR DI halo: this frame's output reservoirs of the rows within 20 of a tile edge go to the neighbouring ranks
+            # (36 B/px; the G-buffer of those rows is recomputed locally by CameraRays over tile + halo)
+            g.synchronize()
+            rows = mg.device_rows(g.device_pointer("restir_output_reservoirs"), H, W * 36, device)
+            mg.exchange_halo(dist, rows, tiles, rank, halo)
+            torch.cuda.synchronize()
 
     # ---- 1. counting pass: the same frames as the timed pass, counting build ----
     restart()
     ctx.counters_enable(True)
     for _ in range(args.warmup):
-        g.render_frame()
+        step()
     g.synchronize()
     ctx.counters_read(True)
     for _ in range(args.steps):
-        g.render_frame()
+        step()
     g.synchronize()
     total = ctx.counters_read(True)
     res = pt.structs.Int2(W, H)
@@ -140,11 +162,11 @@ def run_ours(args, cfg, pt):
     #          gives the device time of the ray-queue traversal kernels, the kernels the node-fetch roofline is about ----
     restart()
     for _ in range(max(args.warmup, 3)):
-        g.render_frame()
+        step()
     g.synchronize()
     ctx.path_profile_enable(True)
     for _ in range(args.steps):
-        g.render_frame()
+        step()
     g.synchronize()
     stage_ms = {k: v / args.steps for k, v in ctx.path_profile_read(True).items()}
     ctx.path_profile_enable(False)
@@ -152,7 +174,7 @@ def run_ours(args, cfg, pt):
     # ---- 2. timed pass: timing build, CUDA events on the launching stream ----
     restart()
     for _ in range(max(args.warmup, 3)):
-        g.render_frame()
+        step()
     g.synchronize()
     ev0, ev1 = C.c_void_p(), C.c_void_p()
     lib.b200pt_event_create(ctx.handle, C.byref(ev0))
@@ -166,7 +188,7 @@ def run_ours(args, cfg, pt):
     kernel_ms = {"CameraRays": 0.0, "FullPathTracer": 0.0}
     lib.b200pt_event_record(ctx.handle, ev0, None)
     for _ in range(args.steps):
-        g.render_frame()
+        step()
         g.synchronize()
         for k in kernel_ms:
             kernel_ms[k] += g.last_kernel_ms(k)
@@ -183,7 +205,10 @@ def run_ours(args, cfg, pt):
         pixels = torch.as_tensor(_Dev(), device=torch.device("cuda", local_rank))
         t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0.record()
-        dist.all_reduce(pixels)
+        if sharding == "tiles":
+            mg.gather_rows(dist, pixels.view(H, W * 3), tiles)       # once per output frame, not per sample
+        else:
+            mg.reduce_accumulation(dist, pixels)
         t1.record()
         torch.cuda.synchronize()
         reduce_ms = t0.elapsed_time(t1)
@@ -204,16 +229,17 @@ def run_ours(args, cfg, pt):
 
     # ---- 3. end to end through the host API with HOST buffers: camera in, accumulated frame out, every step ----
     restart()
+    own_y0, own_rows = (tiles[rank][0], tiles[rank][1] - tiles[rank][0]) if (world > 1 and sharding == "tiles") else (0, H)
     pinned = C.c_void_p()
     lib.b200pt_host_alloc_pinned(ctx.handle, C.c_size_t(W * H * 12), C.byref(pinned))
     for _ in range(3):
-        g.render_frame()
+        step()
     g.synchronize()
     lib.b200pt_event_record(ctx.handle, ev0, None)
     for _ in range(args.steps):
         g.set_camera(cfg["camera"])                       # host struct -> kernel arguments (H2D with each launch)
-        g.render_frame()
-        lib.b200pt_memcpy_d2h(ctx.handle, pinned, C.c_void_p(g.device_pointer("pixels")), C.c_size_t(W * H * 12), None)
+        step()
+        lib.b200pt_memcpy_d2h(ctx.handle, pinned, C.c_void_p(g.device_pointer("pixels") + own_y0 * W * 12), C.c_size_t(W * own_rows * 12), None)
         g.synchronize()
     lib.b200pt_event_record(ctx.handle, ev1, None)
     ctx.sync()
@@ -242,17 +268,17 @@ def run_ours(args, cfg, pt):
     nb = cfg["settings"].get("nb_bounces", 8)
     has_lights, has_env = len(cfg["scene"].emissive) > 0, cfg["envmap"] is not None and cfg["options"]["ess"] != "none"
     per_bounce = 2 + 2 * has_lights + 2 * has_env + (1 if (has_lights or has_env) else 0) + (1 if has_lights else 0) + 1
-    launches_per_step = 1 + (1 + per_bounce) + nb * (2 + per_bounce)
+    launches_per_step = 1 + (1 + per_bounce) + nb * (2 + per_bounce) + (3 if restir else 0)
     out = {
         "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-        "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": cfg["name"], "parallelism": f"sample-pass sharding x{world}, scene+BVH replicated" if world > 1 else "single GPU",
+        "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "strong" if (world > 1 and sharding == "tiles") else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": cfg["name"], "parallelism": "single GPU" if world == 1 else (f"row-tile sharding x{world}" + (f" + {halo}-row ReSTIR reservoir halo exchange" if restir else "") + ", frame gathered once per output" if sharding == "tiles" else f"sample-pass sharding x{world}, accumulation all-reduce") + ", scene+BVH replicated",
                    "l2": "inputs larger than L2: the per-step G-buffer round trip is 345 B/px = 715 MB at 1080p (L2 = 126 MB)",
                    "bvh": bvh_info, "rays_per_step_per_gpu": rays_per_step, "allreduce_ms": reduce_ms},
-        "samples_per_px_per_s": world * args.steps / (elapsed_ms * 1e-3),
+        "samples_per_px_per_s": (1 if (world > 1 and sharding == "tiles") else world) * args.steps / (elapsed_ms * 1e-3),
         "gpu_launches": launches_per_step * args.steps,
         "clocks": clocks,
-        "e2e": {"value": total_rays / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 2 * 1328 + 196, "d2h_bytes_per_step": W * H * 12},
+        "e2e": {"value": total_rays / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 2 * 1328 + 196, "d2h_bytes_per_step": W * own_rows * 12},
         "roofline": {"bound": "hbm", "kernel": "k_trace_queue (ray-queue BVH8 traversal inside FullPathTracer; per step = sum of its launches)", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                      "peak_source": peak_kind, "ms_per_launch": trace_ms, "full_path_tracer_ms": fpt_ms, "stage_ms": stage_ms,
@@ -290,6 +316,8 @@ def main():
     ap.add_argument("--workload", default="cornell")
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--sharding", default="auto", choices=["auto", "samples", "tiles"],
+                    help="N > 1: sample-pass sharding (weak scaling, default for cornell) or row tiles (strong scaling; always for ReSTIR DI)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
 
