@@ -99,7 +99,7 @@ int b200pt_device_count(void)
 }
 
 const char* b200pt_last_error(void) { return g_last_error.c_str(); }
-const char* b200pt_version(void) { return "b200pt 0.1 (sm_100a; BVH8 software traversal; megakernel path tracer)"; }
+const char* b200pt_version(void) { return "b200pt 0.2 (sm_100a; BVH8 ray-queue traversal; phased wavefront path tracer; ReSTIR DI)"; }
 
 int b200pt_ctx_create(int device_index, b200pt_ctx** out_ctx)
 {
