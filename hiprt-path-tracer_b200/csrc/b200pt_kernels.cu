@@ -48,7 +48,7 @@ __global__ void PT_SUFFIXED(k_trace_shadow)(Bvh8Device bvh, const float* __restr
 }
 
 template <bool ANY_HIT>
-__global__ void __launch_bounds__(kTraceBlock) PT_SUFFIXED(k_trace_queue)(const Bvh8Device* __restrict__ bvh, const __grid_constant__ RayQueueView q, TraversalCounters* counters)
+__global__ void __launch_bounds__(kTraceBlock, kTraceBlocksPerSM) PT_SUFFIXED(k_trace_queue)(const Bvh8Device* __restrict__ bvh, const __grid_constant__ RayQueueView q, TraversalCounters* counters)
 {
     __shared__ uint2 shared_stack[kSharedStackEntries * kTraceBlock];
     const Bvh8Device b = *bvh;

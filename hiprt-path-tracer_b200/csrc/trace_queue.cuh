@@ -24,6 +24,7 @@ namespace pt
 {
 constexpr int kSharedStackEntries = 8;
 constexpr int kTraceBlock = 128;
+constexpr int kTraceBlocksPerSM = 7;         // 72 registers per thread; 64 (8 blocks) measured no faster
 constexpr unsigned kRefillIdleLanes = 4;     // refill as soon as this many lanes of a warp have no ray
 constexpr int kTrianglePostponeBelow = 8;    // triangles are tested when at least this many lanes of the warp have one pending
 
@@ -31,9 +32,24 @@ constexpr int kTrianglePostponeBelow = 8;    // triangles are tested when at lea
 // 0x00, byte j of word, 0x80, 0x3F). The slab test then evaluates plane = (1 + q 2^-15) * (2^15 a) + (o - 2^15 a), the same
 // value as q * a + o up to the rounding of the folded offset (<= 2^-9 of a grid cell), which the per-node offsets below
 // absorb on the conservative side -- no I2F (quarter-rate XU pipe) and no separate bias subtraction per plane.
-PT_DEV float quantised_byte_to_unit_float(uint32_t word, int byte)
+// 'one' is 0x3F800000 held in a register (opaque_one_bits): PRMT has a single immediate slot, and with a literal constant
+// ptxas spends it on the constant and re-materialises the SELECTOR in a register before every PRMT (one extra MOV per plane,
+// 48 per node in the first version of this kernel, see profiles/r01_trace_queue_sass_notes.txt).
+PT_DEV float quantised_byte_to_unit_float(uint32_t word, int byte, uint32_t one)
 {
-    return __uint_as_float(__byte_perm(word, 0x3F800000u, 0x7604u + ((uint32_t)byte << 4)));
+    return __uint_as_float(__byte_perm(word, one, 0x7604u + ((uint32_t)byte << 4)));
+}
+PT_DEV uint32_t opaque_one_bits(uint32_t queue_count)
+{
+    return 0x3F800000u | (queue_count >> 31);    // a queue holds < 2^31 rays: always 0x3F800000, but not a compile-time constant to ptxas
+}
+
+// Non-blocking hint: the line is on its way into L2/L1 while the lane does other work (ncu, profiles/r01_trace_queue_closest_c3_v2.txt:
+// a third of the stall samples of this kernel were long-scoreboard waits on the triangle fetch, which misses L2 -- the 480 MB
+// triangle array of the 10 M-triangle scene does not fit -- and another third on the node fetch).
+PT_DEV void prefetch_global(const void* p)
+{
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
 }
 
 template <bool ANY_HIT>
@@ -43,6 +59,7 @@ __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const Ra
     const uint32_t n = *q.count;
     uint2* const my_shared = shared_stack + threadIdx.x;          // entry k at my_shared[k * blockDim.x]
     uint2 local_stack[kTraversalStackSize - kSharedStackEntries];
+    const uint32_t one = opaque_one_bits(n);
 
     bool active = false, exhausted = false;
     uint32_t ray_id = 0;
@@ -127,7 +144,10 @@ __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const Ra
             const float ady = __uint_as_float(((n0.w >> 8) & 0xFFu) << 23) * idy * 32768.0f;
             const float adz = __uint_as_float(((n0.w >> 16) & 0xFFu) << 23) * idz * 32768.0f;
             const float ox = (__uint_as_float(n0.x) - o.x) * idx - adx, oy = (__uint_as_float(n0.y) - o.y) * idy - ady, oz = (__uint_as_float(n0.z) - o.z) * idz - adz;
-            const float ex = fabsf(adx) * 2.3841858e-7f, ey = fabsf(ady) * 2.3841858e-7f, ez = fabsf(adz) * 2.3841858e-7f;   // 2^-22 * 2^15 a = 2^-7 cell
+            // pad per axis: 2^-7 of a cell (2^-22 * 2^15 a) plus 1e-6 relative to the largest plane distance of the axis
+            // (|t| <= |o| + 2 |2^15 a|), which covers the rounding of the offset, of the product and of the triangle routine's t
+            const float ex = __fmaf_rn(fabsf(adx), 2.2384186e-6f, fabsf(ox) * 1.0e-6f), ey = __fmaf_rn(fabsf(ady), 2.2384186e-6f, fabsf(oy) * 1.0e-6f),
+                        ez = __fmaf_rn(fabsf(adz), 2.2384186e-6f, fabsf(oz) * 1.0e-6f);
             const float oxn = ox - ex, oyn = oy - ey, ozn = oz - ez, oxf = ox + ex, oyf = oy + ey, ozf = oz + ez;
             const bool neg_x = d.x < 0.0f, neg_y = d.y < 0.0f, neg_z = d.z < 0.0f;
             const uint32_t oct_inv4 = oct_inv * 0x01010101u;
@@ -149,14 +169,14 @@ __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const Ra
 #pragma unroll
                 for (int j = 0; j < 4; j++)
                 {
-                    const float tnx = __fmaf_rn(quantised_byte_to_unit_float(nearx, j), adx, oxn);
-                    const float tny = __fmaf_rn(quantised_byte_to_unit_float(neary, j), ady, oyn);
-                    const float tnz = __fmaf_rn(quantised_byte_to_unit_float(nearz, j), adz, ozn);
-                    const float tfx = __fmaf_rn(quantised_byte_to_unit_float(farx, j), adx, oxf);
-                    const float tfy = __fmaf_rn(quantised_byte_to_unit_float(fary, j), ady, oyf);
-                    const float tfz = __fmaf_rn(quantised_byte_to_unit_float(farz, j), adz, ozf);
-                    const float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f)) * 0.999999f;
-                    const float cmax = fminf(fminf(fminf(tfx, tfy), tfz) * 1.000001f, t_best);
+                    const float tnx = __fmaf_rn(quantised_byte_to_unit_float(nearx, j, one), adx, oxn);
+                    const float tny = __fmaf_rn(quantised_byte_to_unit_float(neary, j, one), ady, oyn);
+                    const float tnz = __fmaf_rn(quantised_byte_to_unit_float(nearz, j, one), adz, ozn);
+                    const float tfx = __fmaf_rn(quantised_byte_to_unit_float(farx, j, one), adx, oxf);
+                    const float tfy = __fmaf_rn(quantised_byte_to_unit_float(fary, j, one), ady, oyf);
+                    const float tfz = __fmaf_rn(quantised_byte_to_unit_float(farz, j, one), adz, ozf);
+                    const float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
+                    const float cmax = fminf(fminf(fminf(tfx, tfy), tfz), t_best);
                     if (cmin <= cmax)
                         hitmask |= ((child_bits4 >> (8 * j)) & 0xFFu) << ((bit_index4 >> (8 * j)) & 0xFFu);
                 }
@@ -176,6 +196,20 @@ __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const Ra
                         stack_size++;
                 }
                 tgroup = make_uint2(n1.y, hitmask & 0x00FFFFFFu);
+                // the triangles are tested in later iterations (one per iteration, possibly postponed): start fetching them now
+                const char* first_triangle = reinterpret_cast<const char*>(bvh.triangles + (n1.y + (uint32_t)__ffs((int)tgroup.y) - 1u));
+                prefetch_global(first_triangle);
+                prefetch_global(first_triangle + 128);
+            }
+            if (ngroup.y > 0x00FFFFFFu)
+            {
+                // ... and the node the next iteration visits (the nearest hit child in ray-octant order)
+                const uint32_t next_bit = 31u - (uint32_t)__clz((int)ngroup.y);
+                const uint32_t next_slot = (next_bit - 24u) ^ oct_inv;
+                const uint32_t next_rank = (uint32_t)__popc(ngroup.y & 0xFFu & ~(0xFFFFFFFFu << next_slot));
+                const char* next_node = reinterpret_cast<const char*>(bvh.nodes + (ngroup.x + next_rank));
+                prefetch_global(next_node);
+                prefetch_global(next_node + 64);
             }
         }
 
@@ -192,7 +226,8 @@ __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const Ra
             PT_COUNT(n_tris++;)
             const int prim = __float_as_int(v0.w);
             float t, u, v;
-            if (prim != last_prim && intersect_triangle_reference(o, d, f3(v0.x, v0.y, v0.z), f3(v1.x, v1.y, v1.z), f3(v2.x, v2.y, v2.z), t, u, v) && t < t_best)
+            if (prim != last_prim && intersect_triangle_reference(o, d, f3(v0.x, v0.y, v0.z), f3(v1.x, v1.y, v1.z), f3(v2.x, v2.y, v2.z), t, u, v) &&
+                (t < t_best || (!ANY_HIT && t == t_best && prim < hit.prim)))     // equal distance: lowest primitive id, whatever the visiting order
             {
                 t_best = t;
                 hit.prim = prim; hit.tri_slot = (int)tri_index; hit.t = t; hit.u = u; hit.v = v;
@@ -201,19 +236,27 @@ __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const Ra
             }
         }
 
-        // Out of node work and of triangle work: next stack entry (a node group, or a triangle group that was set aside)
-        if (!finished && ngroup.y <= 0x00FFFFFFu && tgroup.y == 0u)
+        // Out of node work: take the next stack entry. A node group is taken even while triangles are still pending (they are
+        // tested one per iteration, possibly postponed, and the lane would otherwise idle through the node step meanwhile);
+        // a triangle group that was set aside is taken only once the current one is done.
+        if (!finished && ngroup.y <= 0x00FFFFFFu)
         {
             if (stack_size == 0)
-                finished = true;
+                finished = tgroup.y == 0u;
             else
             {
-                stack_size--;
-                const uint2 e = stack_size < kSharedStackEntries ? my_shared[stack_size * blockDim.x] : local_stack[stack_size - kSharedStackEntries];
+                const int top = stack_size - 1;
+                const uint2 e = top < kSharedStackEntries ? my_shared[top * blockDim.x] : local_stack[top - kSharedStackEntries];
                 if (e.y > 0x00FFFFFFu)
+                {
                     ngroup = e;
-                else
+                    stack_size = top;
+                }
+                else if (tgroup.y == 0u)
+                {
                     tgroup = e;
+                    stack_size = top;
+                }
             }
         }
 

@@ -188,7 +188,9 @@ PT_DEV_NOINLINE bool bvh8_trace(const Bvh8Device& bvh, float3 o, float3 d, float
             float t, u, v;
             if (intersect_triangle_reference(o, d, f3(v0.x, v0.y, v0.z), f3(v1.x, v1.y, v1.z), f3(v2.x, v2.y, v2.z), t, u, v))
             {
-                if (t < t_best)
+                // strict '<' as in the reference (BVH.h:132-227); among hits at exactly the same distance (a ray through a shared
+                // edge) the lowest primitive id wins, so the result does not depend on the order the triangles were visited in
+                if (t < t_best || (!ANY_HIT && t == t_best && prim < hit.prim))
                 {
                     t_best = t;
                     hit.prim = prim;

@@ -21,6 +21,27 @@ def cornell(width, height):
     }
 
 
+def golden_scene(name, width, height, lss="mis", adaptive=False, thin_film=False, nb_bounces=8):
+    """C5-shaped parity inputs: the reference's own test scenes (tests/golden/<name>.npz: nested-dielectrics,
+    nested-dielectrics-complex, multi-dispersion, cornell_pbr), optionally with per-pixel adaptive sampling and with a
+    thin-film coating put on every non-emissive material. No emissive geometry -> uniform sky 0.5 lights the scene."""
+    scene = sc.load_scene(os.path.join(ROOT, "tests", "golden", name + ".npz"))
+    if thin_film:
+        for i, m in enumerate(scene.materials):
+            if i not in set(int(scene.material_indices[t]) for t in scene.emissive):
+                m.base.thin_film = 1.0
+                m.base.thin_film_ior = 1.3 + 0.05 * (i % 4)
+                m.base.thin_film_thickness = 300.0 + 90.0 * i
+    settings = dict(nb_bounces=nb_bounces, do_alpha_testing=0, enable_adaptive_sampling=int(adaptive), samples_per_frame=1)
+    if adaptive:
+        settings.update(adaptive_sampling_min_samples=4, adaptive_sampling_noise_threshold=1.0)
+    return {
+        "name": f"{name} {width}x{height}, {nb_bounces} bounces, {lss}" + (", adaptive sampling" if adaptive else "") + (", thin film" if thin_film else ""),
+        "scene": scene, "camera": sc.scene_camera(scene, width, height), "width": width, "height": height,
+        "options": dict(lss=lss, ess="none", ggx=0, later=3), "oracle_variant": lss, "envmap": None, "settings": settings,
+    }
+
+
 _CACHE = {}
 
 
