@@ -164,12 +164,15 @@ def run_ours(args, cfg, pt):
     for _ in range(max(args.warmup, 3)):
         step()
     g.synchronize()
+    lanes = g.path_lanes
+    g.set_path_lanes(1)                  # the stages of concurrent lanes overlap: stage times are taken with a single lane
     ctx.path_profile_enable(True)
     for _ in range(args.steps):
         step()
     g.synchronize()
     stage_ms = {k: v / args.steps for k, v in ctx.path_profile_read(True).items()}
     ctx.path_profile_enable(False)
+    g.set_path_lanes(lanes)
 
     # ---- 2. timed pass: timing build, CUDA events on the launching stream ----
     restart()
@@ -268,13 +271,13 @@ def run_ours(args, cfg, pt):
     nb = cfg["settings"].get("nb_bounces", 8)
     has_lights, has_env = len(cfg["scene"].emissive) > 0, cfg["envmap"] is not None and cfg["options"]["ess"] != "none"
     per_bounce = 2 + 2 * has_lights + 2 * has_env + (1 if (has_lights or has_env) else 0) + (1 if has_lights else 0) + 1
-    launches_per_step = 1 + (1 + per_bounce) + nb * (2 + per_bounce) + (3 if restir else 0)
+    launches_per_step = 1 + lanes * ((1 + per_bounce) + nb * (2 + per_bounce)) + (3 if restir else 0)      # every path lane launches its own band
     out = {
         "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "strong" if (world > 1 and sharding == "tiles") else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": cfg["name"], "parallelism": "single GPU" if world == 1 else (f"row-tile sharding x{world}" + (f" + {halo}-row ReSTIR reservoir halo exchange" if restir else "") + ", frame gathered once per output" if sharding == "tiles" else f"sample-pass sharding x{world}, accumulation all-reduce") + ", scene+BVH replicated",
                    "l2": "inputs larger than L2: the per-step G-buffer round trip is 345 B/px = 715 MB at 1080p (L2 = 126 MB)",
-                   "bvh": bvh_info, "rays_per_step_per_gpu": rays_per_step, "allreduce_ms": reduce_ms},
+                   "bvh": bvh_info, "path_lanes": lanes, "rays_per_step_per_gpu": rays_per_step, "allreduce_ms": reduce_ms},
         "samples_per_px_per_s": (1 if (world > 1 and sharding == "tiles") else world) * args.steps / (elapsed_ms * 1e-3),
         "gpu_launches": launches_per_step * args.steps,
         "clocks": clocks,

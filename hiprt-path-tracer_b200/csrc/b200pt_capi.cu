@@ -18,8 +18,10 @@ struct b200pt_ctx
     bool counting = false;
     pt::TraversalCounters* d_counters = nullptr;
     int path_mode = pt::WF_PHASED;
-    pt::WavefrontState wf = {};
-    std::vector<void*> wf_allocations;
+    // wavefront scratch, one set per path lane (b200pt_launch_FullPathTracer_lane): lane launches run on concurrent streams
+    static constexpr int kMaxPathLanes = 4;
+    pt::WavefrontState wf[kMaxPathLanes] = {};
+    std::vector<void*> wf_allocations[kMaxPathLanes];
     // per-stage timing of FullPathTracer (b200pt_path_profile_enable / _read)
     bool profiling = false;
     std::vector<cudaEvent_t> profile_events;
@@ -147,8 +149,9 @@ int b200pt_ctx_destroy(b200pt_ctx* ctx)
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->main_stream);
     cudaFree(ctx->d_counters);
-    for (void* p : ctx->wf_allocations)
-        cudaFree(p);
+    for (auto& allocations : ctx->wf_allocations)
+        for (void* p : allocations)
+            cudaFree(p);
     for (cudaEvent_t e : ctx->profile_events)
         cudaEventDestroy(e);
     cudaStreamDestroy(ctx->main_stream);
@@ -293,6 +296,13 @@ int b200pt_event_record(b200pt_ctx* ctx, b200pt_event event, b200pt_stream strea
 {
     REQUIRE(ctx != nullptr && event != nullptr);
     CUDA_TRY(cudaEventRecord(reinterpret_cast<cudaEvent_t>(event), stream_of(ctx, stream)));
+    return B200PT_SUCCESS;
+}
+
+int b200pt_stream_wait_event(b200pt_ctx* ctx, b200pt_stream stream, b200pt_event event)
+{
+    REQUIRE(ctx != nullptr && event != nullptr);
+    CUDA_TRY(cudaStreamWaitEvent(stream_of(ctx, stream), reinterpret_cast<cudaEvent_t>(event), 0));
     return B200PT_SUCCESS;
 }
 

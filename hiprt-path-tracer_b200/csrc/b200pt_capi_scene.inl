@@ -171,16 +171,17 @@ int b200pt_kernel_variant_select(b200pt_ctx* ctx, const b200pt_options* options)
 // the stream: launches in flight may still use the old arrays.
 extern "C" int b200pt_path_profile_read(b200pt_ctx* ctx, double* out_stage_ms, int reset);
 
-static int ensure_wavefront(b200pt_ctx* ctx, uint32_t paths, uint32_t bounces)
+static int ensure_wavefront(b200pt_ctx* ctx, int lane, uint32_t paths, uint32_t bounces)
 {
-    pt::WavefrontState& wf = ctx->wf;
+    pt::WavefrontState& wf = ctx->wf[lane];
+    std::vector<void*>& allocations = ctx->wf_allocations[lane];
     if (paths <= wf.capacity && bounces <= wf.max_bounces)
         return B200PT_SUCCESS;
     CUDA_TRY(cudaSetDevice(ctx->device));
-    CUDA_TRY(cudaStreamSynchronize(ctx->main_stream));
-    for (void* p : ctx->wf_allocations)
+    CUDA_TRY(cudaDeviceSynchronize());
+    for (void* p : allocations)
         cudaFree(p);
-    ctx->wf_allocations.clear();
+    allocations.clear();
     uint32_t capacity = paths > wf.capacity ? paths : wf.capacity;
     uint32_t max_bounces = bounces > wf.max_bounces ? bounces : wf.max_bounces;
     wf = pt::WavefrontState{};
@@ -188,7 +189,7 @@ static int ensure_wavefront(b200pt_ctx* ctx, uint32_t paths, uint32_t bounces)
         void* p = nullptr;
         if (cudaMalloc(&p, bytes) != cudaSuccess)
             return nullptr;
-        ctx->wf_allocations.push_back(p);
+        allocations.push_back(p);
         return p;
     };
     const size_t n = capacity;
@@ -217,9 +218,9 @@ static int ensure_wavefront(b200pt_ctx* ctx, uint32_t paths, uint32_t bounces)
     if (!ok)
     {
         cudaError_t e = cudaGetLastError();
-        for (void* p : ctx->wf_allocations)
+        for (void* p : allocations)
             cudaFree(p);
-        ctx->wf_allocations.clear();
+        allocations.clear();
         wf = pt::WavefrontState{};
         return cuda_fail(e == cudaSuccess ? cudaErrorMemoryAllocation : e, "wavefront scratch allocation");
     }
@@ -265,18 +266,27 @@ int b200pt_set_path_mode(b200pt_ctx* ctx, int mode)
 
 int b200pt_launch_FullPathTracer(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream)
 {
+    return b200pt_launch_FullPathTracer_lane(ctx, render_data, res, tile, stream, 0, 1);
+}
+
+int b200pt_launch_FullPathTracer_lane(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream, int lane, int lane_count)
+{
     REQUIRE(ctx != nullptr && render_data != nullptr && res.x > 0 && res.y > 0);
+    REQUIRE(lane_count >= 1 && lane_count <= b200pt_ctx::kMaxPathLanes && lane >= 0 && lane < lane_count);
     if (ctx->path_mode != pt::WF_MEGAKERNEL)
     {
         pt::Tile wt = tile_of(tile, res);
         if (wt.x1 > wt.x0 && wt.y1 > wt.y0)
         {
             REQUIRE(render_data->render_settings.nb_bounces >= 0);
-            int rc = ensure_wavefront(ctx, (uint32_t)(wt.x1 - wt.x0) * (uint32_t)(wt.y1 - wt.y0), (uint32_t)render_data->render_settings.nb_bounces);
+            int rc = ensure_wavefront(ctx, lane, (uint32_t)(wt.x1 - wt.x0) * (uint32_t)(wt.y1 - wt.y0), (uint32_t)render_data->render_settings.nb_bounces);
             if (rc != B200PT_SUCCESS)
                 return rc;
+            ctx->wf[lane].grid_share = (uint32_t)lane_count;
         }
     }
+    if (ctx->profiling && lane_count > 1)
+        return fail(B200PT_ERROR_INVALID_ARGUMENT, "per-stage profiling needs a single path lane (the stages of concurrent lanes overlap)");
     if (ctx->profiling)
     {
         // fold the previous launch's intervals in, then hand the event pool to this launch
@@ -286,7 +296,7 @@ int b200pt_launch_FullPathTracer(b200pt_ctx* ctx, const HIPRTRenderData* render_
         ctx->profile.count = 0;
     }
     pt::WavefrontProfile* profile = ctx->profiling ? &ctx->profile : nullptr;
-    LAUNCH_PIXEL_KERNEL(launch_FullPathTracer, , &ctx->wf, ctx->path_mode, profile)
+    LAUNCH_PIXEL_KERNEL(launch_FullPathTracer, , &ctx->wf[lane], ctx->path_mode, profile)
 }
 
 int b200pt_path_profile_enable(b200pt_ctx* ctx, int enable)

@@ -1,5 +1,6 @@
 // One FullPathTracer permutation per translation unit: compile with -DPT_LSS= -DPT_ESS= -DPT_LATER= -DPT_GGX=
 // Holds the megakernel and the wavefront kernels (wavefront.cuh) of the permutation plus their launcher.
+#include <cstdlib>
 #include "wavefront_mis.cuh"
 #if PT_LSS == 5
 #include "restir_di_kernels.cuh"
@@ -86,8 +87,13 @@ __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_bsdf)(const __grid_co
 }
 
 #if PT_LSS == 3
+// The phase kernels wait on memory (ncu, profiles/r01_shade_phases_c3.txt: issue-active 18-23 %, long-scoreboard 7-12 stalled warps
+// per issue at 114-118 registers = 16 warps per SM): cap the registers so that more warps are resident to cover the latency.
+#ifndef PT_PHASE_BLOCKS_PER_SM
+#define PT_PHASE_BLOCKS_PER_SM 12
+#endif
 #define PT_QUEUE_KERNEL(NAME, BOUNDS, KID, CALL)                                                                                                                            \
-    __global__ void __launch_bounds__(BOUNDS) PT_VARIANT_NAME(NAME)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce) \
+    __global__ void __launch_bounds__(BOUNDS, PT_PHASE_BLOCKS_PER_SM) PT_VARIANT_NAME(NAME)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce) \
     {                                                                                                                                                                  \
         PT_FOR_EACH_QUEUED(i, wf.counts[kCountsPerBounce * bounce + 1], KID)                                                                                                          \
             CALL(rd, res, tile, wf, bounce, i);                                                                                                                        \
@@ -103,7 +109,7 @@ __global__ void __launch_bounds__(128) PT_VARIANT_NAME(k_wf_surface)(const __gri
         wf_surface_path<PT_ESS>(rd, res, tile, wf, bounce, i);
 }
 
-__global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_bsdf_resolved)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce, bool lights_sampled, bool envmap_sampled)
+__global__ void __launch_bounds__(64, PT_PHASE_BLOCKS_PER_SM) PT_VARIANT_NAME(k_wf_bsdf_resolved)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce, bool lights_sampled, bool envmap_sampled)
 {
     PT_FOR_EACH_QUEUED(i, wf.counts[kCountsPerBounce * bounce + 1], 7)
         wf_bsdf_resolved_path<PT_ESS, PT_GGX>(rd, res, tile, wf, bounce, i, lights_sampled, envmap_sampled);
@@ -135,7 +141,12 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
 
     // Queue lengths are only known on the device: queue kernels run grid-stride loops on a grid capped at a few blocks per
     // SM (an uncapped grid of mostly empty blocks costs ~1.5 ns per block: 50 us per launch at 1080p)
-    const unsigned cap = wf->sm_count * 16u;
+    static const unsigned blocks_per_sm = [] { const char* v = getenv("B200PT_QUEUE_BLOCKS_PER_SM"); int n = v ? atoi(v) : 0; return n > 0 ? (unsigned)n : 16u; }();
+    // Path lanes: when the host runs several band launches on concurrent streams (trace of one band under the shade phases of
+    // another), each launch sizes its grids for its share of an SM so that blocks of both are resident together
+    static const unsigned share_override = [] { const char* v = getenv("B200PT_GRID_SHARE"); int n = v ? atoi(v) : 0; return n > 0 ? (unsigned)n : 0u; }();
+    const unsigned share = share_override ? share_override : (wf->grid_share > 0u ? wf->grid_share : 1u);
+    const unsigned cap = wf->sm_count * ((blocks_per_sm + share - 1u) / share);
     auto blocks = [&](unsigned block) { unsigned g = (paths + block - 1) / block, c = cap * 64u / block; return g < c ? g : c; };
     cudaError_t e = cudaMemsetAsync(wf->counts, 0, sizeof(uint32_t) * (kCountsPerBounce + kCursorsPerBounce) * (wf->max_bounces + 2), stream);
     if (e != cudaSuccess)
@@ -158,7 +169,7 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
 #else
     TraversalCounters* const counters = nullptr;
 #endif
-    const unsigned trace_blocks = wf->sm_count * 8u;   // persistent: 8 resident blocks of 128 threads per SM
+    const unsigned trace_blocks = wf->sm_count * ((8u + share - 1u) / share);   // persistent: 8 resident blocks of 128 threads per SM, shared between lanes
     (void)counters; (void)trace_blocks;
     for (int bounce = 0; bounce <= nb_bounces; bounce++)
     {

@@ -45,6 +45,7 @@ struct WavefrontState
     uint32_t* counts;        // [4*b + k]: k = 0 rays queued for bounce b, 1 hits queued for shading, 2 NEE any-hit rays, 3 NEE closest-hit rays
     uint32_t* cursors;       // kCursorsPerBounce work cursors per bounce (dynamic fetch of the queue kernels); follows `counts`
     uint32_t sm_count;       // SMs of the device (grid sizing of the queue kernels)
+    uint32_t grid_share;     // how many FullPathTracer launches share the device at the same time (path lanes, >= 1): grids are sized 1/share
     uint32_t capacity;       // paths
     uint32_t max_bounces;    // counts holds 2 * (max_bounces + 2) entries
 };

@@ -140,7 +140,11 @@ public:
     void set_kernel_options(const b200pt_options& options);                          // GPUKernelCompilerOptions -> prebuilt permutation
     void resize(int width, int height);                                               // GPURenderer.cpp:resize
     void set_tile(const b200pt_tile* tile);                                           // multi-GPU image shard (new)
-    void set_tile_halo(int rows);                                                     // rows either side of the tile CameraRays also covers (ReSTIR DI)
+    void set_tile_halo(int rows);
+    // FullPathTracer as `lanes` (1..4) concurrent band launches on separate streams (b200pt_launch_FullPathTracer_lane): the
+    // traversal kernels of one band run under the DRAM-bound shade phases of another. Bands are row tiles, so pixels are unchanged.
+    void set_path_lanes(int lanes);
+    int path_lanes() const { return m_path_lanes; }                                                     // rows either side of the tile CameraRays also covers (ReSTIR DI)
     void reset();
 
     void update();                                                                    // GPURenderer.cpp:236-267
@@ -196,6 +200,10 @@ private:
     bool m_has_tile = false;
     b200pt_tile m_tile = {0, 0, 0, 0};
     int m_tile_halo = 0;
+    int m_path_lanes = 1;
+    b200pt_stream m_lane_streams[3] = {nullptr, nullptr, nullptr};
+    b200pt_event m_lane_fork = nullptr;
+    b200pt_event m_lane_join[3] = {nullptr, nullptr, nullptr};
     Xorshift32Generator m_rng;
     HIPRTCamera m_camera;
     bool m_restir_odd_frame = false;

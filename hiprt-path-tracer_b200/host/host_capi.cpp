@@ -131,6 +131,8 @@ int b200pt_renderer_set_camera(b200pt_renderer* r, const HIPRTCamera* camera)
 int b200pt_renderer_resize(b200pt_renderer* r, int width, int height) { return guarded([&] { r->renderer.resize(width, height); }); }
 int b200pt_renderer_set_tile(b200pt_renderer* r, const b200pt_tile* tile) { r->renderer.set_tile(tile); return B200PT_SUCCESS; }
 int b200pt_renderer_set_tile_halo(b200pt_renderer* r, int rows) { r->renderer.set_tile_halo(rows); return B200PT_SUCCESS; }
+int b200pt_renderer_set_path_lanes(b200pt_renderer* r, int lanes) { return guarded([&] { r->renderer.set_path_lanes(lanes); }); }
+int b200pt_renderer_path_lanes(b200pt_renderer* r) { return r->renderer.path_lanes(); }
 int b200pt_renderer_reset(b200pt_renderer* r) { r->renderer.reset(); return B200PT_SUCCESS; }
 HIPRTRenderSettings* b200pt_renderer_render_settings(b200pt_renderer* r) { return &r->renderer.get_render_settings(); }
 WorldSettings* b200pt_renderer_world_settings(b200pt_renderer* r) { return &r->renderer.get_world_settings(); }

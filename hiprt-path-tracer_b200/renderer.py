@@ -203,6 +203,14 @@ class GPURenderer:
             self.host.b200pt_renderer_set_tile(self.handle, C.byref(t))
         self.host.b200pt_renderer_set_tile_halo(self.handle, C.c_int(halo))
 
+    def set_path_lanes(self, lanes):
+        """FullPathTracer as 1..4 concurrent band launches (trace of one band under the shade phases of another)."""
+        _capi.check(self.host.b200pt_renderer_set_path_lanes(self.handle, C.c_int(lanes)), "b200pt_renderer_set_path_lanes")
+
+    @property
+    def path_lanes(self):
+        return int(self.host.b200pt_renderer_path_lanes(self.handle))
+
     def reset(self):
         self.host.b200pt_renderer_reset(self.handle)
 

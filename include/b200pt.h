@@ -148,6 +148,13 @@ B200PT_API int b200pt_path_profile_enable(b200pt_ctx* ctx, int enable);
 B200PT_API int b200pt_path_profile_read(b200pt_ctx* ctx, double* out_stage_ms, int reset);
 B200PT_API int b200pt_launch_CameraRays(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream);
 B200PT_API int b200pt_launch_FullPathTracer(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream);
+/* New (no reference counterpart): the same launch as one of `lane_count` (<= 4) concurrent band launches. Each lane has its own
+ * wavefront scratch and sizes its grids for 1/lane_count of an SM, so that launches issued on different streams for different
+ * tiles overlap (the ray-queue traversal of one band is latency-bound, the shade phases of another are DRAM-bound).
+ * b200pt_launch_FullPathTracer is lane 0 of 1. */
+B200PT_API int b200pt_launch_FullPathTracer_lane(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream, int lane, int lane_count);
+/* cudaStreamWaitEvent: work queued on `stream` after this call starts after `event` (replaces oroStreamWaitEvent) */
+B200PT_API int b200pt_stream_wait_event(b200pt_ctx* ctx, b200pt_stream stream, b200pt_event event);
 B200PT_API int b200pt_launch_ReSTIR_DI_LightsPresampling(b200pt_ctx* ctx, const LightPresamplingParameters* parameters, b200pt_stream stream);
 B200PT_API int b200pt_launch_ReSTIR_DI_InitialCandidates(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream);
 B200PT_API int b200pt_launch_ReSTIR_DI_SpatiotemporalReuse(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream);

@@ -40,6 +40,10 @@ B200PT_API int b200pt_renderer_set_tile(b200pt_renderer* r, const b200pt_tile* t
 /* Tile sharding with ReSTIR DI (new): CameraRays also covers `rows` rows above and below the tile, so that the
  * G-buffers the fused spatiotemporal pass reads around the tile are computed locally; only reservoirs are exchanged. */
 B200PT_API int b200pt_renderer_set_tile_halo(b200pt_renderer* r, int rows);
+/* FullPathTracer as 1..4 concurrent band launches on separate streams (new; see b200pt_launch_FullPathTracer_lane). Also read
+ * from the environment variable B200PT_PATH_LANES at construction. Pixels do not change (bands are row tiles). */
+B200PT_API int b200pt_renderer_set_path_lanes(b200pt_renderer* r, int lanes);
+B200PT_API int b200pt_renderer_path_lanes(b200pt_renderer* r);
 B200PT_API int b200pt_renderer_reset(b200pt_renderer* r);
 /* Host-side structs the caller may edit between frames (copied by value into each launch) */
 B200PT_API HIPRTRenderSettings* b200pt_renderer_render_settings(b200pt_renderer* r);

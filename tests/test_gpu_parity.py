@@ -378,3 +378,23 @@ def test_c5_feature_scenes_parity(pt, wl, ctx, ref, name, kwargs):
     assert err < 1e-3, err
     assert abs(a.mean() - b.mean()) / a.mean() < 1e-3
     g.close()
+
+
+def test_path_lanes_are_bit_identical(pt, wl, ctx):
+    """FullPathTracer as 1, 2 or 3 concurrent band launches on separate streams (the default is 2) gives the same frame."""
+    cfg = wl.cornell(1920, 1080)
+    g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="cpu")
+    frames = {}
+    for lanes in (1, 2, 3):
+        g.set_path_lanes(lanes)
+        assert g.path_lanes == lanes
+        g.reset()
+        g.resize(1920, 1080)
+        wl.apply_settings(g.render_settings, cfg["settings"])
+        for _ in range(3):
+            g.render_frame()
+        g.synchronize()
+        frames[lanes] = g.download("pixels").copy()
+    assert np.array_equal(frames[1], frames[2])
+    assert np.array_equal(frames[1], frames[3])
+    g.close()

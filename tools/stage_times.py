@@ -20,13 +20,15 @@ g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="cpu")
 for _ in range(3):
     g.render_frame()
 g.synchronize()
-ctx.path_profile_enable(True)
+lanes = g.path_lanes
+if lanes == 1:
+    ctx.path_profile_enable(True)       # per-stage events need a single lane: the stages of concurrent lanes overlap
 fpt = cam = 0.0
 for _ in range(frames):
     g.render_frame()
     g.synchronize()
     fpt += g.last_kernel_ms("FullPathTracer")
     cam += g.last_kernel_ms("CameraRays")
-stage = {k: round(v / frames, 3) for k, v in ctx.path_profile_read(True).items()}
+stage = {k: round(v / frames, 3) for k, v in ctx.path_profile_read(True).items()} if lanes == 1 else f"(lanes={lanes})"
 digest = hashlib.sha1(g.download("pixels").tobytes()).hexdigest()[:16]
 print(f"{name} {W}x{H}: FullPathTracer {fpt / frames:.3f} ms  CameraRays {cam / frames:.3f} ms  stages {stage}  pixels sha1 {digest}")
