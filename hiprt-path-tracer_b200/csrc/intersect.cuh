@@ -106,6 +106,31 @@ PT_DEV float3 hit_geometric_normal(const HIPRTRenderData& rd, const Hit& hit)
     return normalize(normalize(bvh8_triangle_normal(scene_bvh(rd), hit.tri_slot)));
 }
 
+// filter_function with do_alpha_testing (FilterFunction.h:33-47): a candidate hit is kept iff rng() < alpha_opacity * alpha of
+// the base colour texture at the hit. One number of the path's generator is drawn per candidate, in traversal order (so the
+// stream, unlike the image statistics, depends on the acceleration structure -- also true between the reference's own CPU
+// and GPU paths).
+struct AlphaHitFilter
+{
+    const HIPRTRenderData& rd;
+    Rng& rng;
+    PT_DEV bool reject(int prim, float u, float v) const
+    {
+        const int material_index = __ldg(rd.buffers.material_indices + prim);
+        const float base_alpha = base_color_alpha(rd, material_index, interpolate_texcoords(rd, triangle_vertex_indices(rd, prim), make_float2(u, v)));
+        const float composited_alpha = material_field_f(rd, material_index, offsetof(SimplifiedRendererMaterial, alpha_opacity)) * base_alpha;
+        return !(rng() < composited_alpha);
+    }
+};
+
+template <bool ANY_HIT>
+PT_DEV bool trace_filtered(const HIPRTRenderData& rd, float3 origin, float3 direction, float t_limit, int last_hit_primitive_index, Hit& hit, Rng& rng)
+{
+    if (rd.render_settings.do_alpha_testing)
+        return bvh8_trace<ANY_HIT, AlphaHitFilter>(scene_bvh(rd), origin, direction, t_limit, last_hit_primitive_index, hit, PT_COUNTERS_PTR, AlphaHitFilter{rd, rng});
+    return bvh8_trace<ANY_HIT>(scene_bvh(rd), origin, direction, t_limit, last_hit_primitive_index, hit, PT_COUNTERS_PTR);
+}
+
 // trace_ray (Intersect.h:114-219). Returns true if a hit was found. `first`: when have_first is set, the closest hit of
 // (origin, direction) was already found by the ray-queue kernel (trace_queue.cuh) and is passed in instead of traced here;
 // volume boundaries that are skipped (nested dielectrics) are re-traced in place either way.
@@ -119,7 +144,7 @@ PT_DEV_NOINLINE bool trace_ray_from(const HIPRTRenderData& rd, float3 origin, fl
             if (hit.prim < 0)
                 return false;
         }
-        else if (!bvh8_trace<false>(scene_bvh(rd), origin, direction, INFINITY, last_hit_primitive_index, hit, PT_COUNTERS_PTR))
+        else if (!trace_filtered<false>(rd, origin, direction, INFINITY, last_hit_primitive_index, hit, rng))
             return false;
         have_first = false;
 
@@ -169,12 +194,11 @@ PT_DEV bool trace_ray(const HIPRTRenderData& rd, float3 origin, float3 direction
     return trace_ray_from(rd, origin, direction, payload, out, last_hit_primitive_index, rng, none, false);
 }
 
-// evaluate_shadow_ray (Intersect.h:224-286): true if occluded. Alpha testing off: one any-hit query.
+// evaluate_shadow_ray (Intersect.h:224-254, the device branch): true if occluded; one any-hit query through the filter
 PT_DEV bool evaluate_shadow_ray(const HIPRTRenderData& rd, float3 origin, float3 direction, float t_max, int last_hit_primitive_index, Rng& rng)
 {
-    (void)rng;
     Hit hit;
-    return bvh8_trace<true>(scene_bvh(rd), origin, direction, t_max - 1.0e-4f, last_hit_primitive_index, hit, PT_COUNTERS_PTR);
+    return trace_filtered<true>(rd, origin, direction, t_max - 1.0e-4f, last_hit_primitive_index, hit, rng);
 }
 
 struct ShadowLightRayHitInfo
@@ -221,9 +245,8 @@ PT_DEV_NOINLINE bool shadow_light_ray_resolve(const HIPRTRenderData& rd, float t
 
 PT_DEV bool evaluate_shadow_light_ray(const HIPRTRenderData& rd, float3 origin, float3 direction, float t_max, ShadowLightRayHitInfo& out, int last_hit_primitive_index, Rng& rng)
 {
-    (void)rng;
     Hit hit;
-    bvh8_trace<false>(scene_bvh(rd), origin, direction, INFINITY, last_hit_primitive_index, hit, PT_COUNTERS_PTR);
+    trace_filtered<false>(rd, origin, direction, INFINITY, last_hit_primitive_index, hit, rng);
     return shadow_light_ray_resolve(rd, t_max, out, hit);
 }
 } // namespace pt

@@ -75,9 +75,17 @@ PT_DEV bool intersect_triangle_reference(float3 o, float3 d, float3 a, float3 b,
     return t > EPSILON;
 }
 
+// The any-hit callback of the reference (filter_function, src/Device/functions/FilterFunction.h:19-48) beyond the
+// last-primitive rejection, which every traversal does: a FILTER sees each candidate hit that would otherwise be accepted and
+// may reject it (alpha testing, AlphaHitFilter in intersect.cuh). NoHitFilter compiles away.
+struct NoHitFilter
+{
+    PT_DEV bool reject(int, float, float) const { return false; }
+};
+
 // ANY_HIT = false: closest hit over t in (1e-7, +inf).  ANY_HIT = true: first accepted triangle with t < t_limit.
-template <bool ANY_HIT>
-PT_DEV_NOINLINE bool bvh8_trace(const Bvh8Device& bvh, float3 o, float3 d, float t_limit, int last_prim, Hit& hit, TraversalCounters* counters = nullptr)
+template <bool ANY_HIT, class FILTER = NoHitFilter>
+PT_DEV_NOINLINE bool bvh8_trace(const Bvh8Device& bvh, float3 o, float3 d, float t_limit, int last_prim, Hit& hit, TraversalCounters* counters = nullptr, FILTER filter = FILTER())
 {
     hit.prim = -1;
     hit.tri_slot = -1;
@@ -190,7 +198,7 @@ PT_DEV_NOINLINE bool bvh8_trace(const Bvh8Device& bvh, float3 o, float3 d, float
             {
                 // strict '<' as in the reference (BVH.h:132-227); among hits at exactly the same distance (a ray through a shared
                 // edge) the lowest primitive id wins, so the result does not depend on the order the triangles were visited in
-                if (t < t_best || (!ANY_HIT && t == t_best && prim < hit.prim))
+                if ((t < t_best || (!ANY_HIT && t == t_best && prim < hit.prim)) && !filter.reject(prim, u, v))
                 {
                     t_best = t;
                     hit.prim = prim;

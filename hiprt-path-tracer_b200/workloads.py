@@ -21,7 +21,7 @@ def cornell(width, height):
     }
 
 
-def golden_scene(name, width, height, lss="mis", adaptive=False, thin_film=False, nb_bounces=8):
+def golden_scene(name, width, height, lss="mis", adaptive=False, thin_film=False, nb_bounces=8, alpha_opacity=None):
     """C5-shaped parity inputs: the reference's own test scenes (tests/golden/<name>.npz: nested-dielectrics,
     nested-dielectrics-complex, multi-dispersion, cornell_pbr), optionally with per-pixel adaptive sampling and with a
     thin-film coating put on every non-emissive material. No emissive geometry -> uniform sky 0.5 lights the scene."""
@@ -32,7 +32,13 @@ def golden_scene(name, width, height, lss="mis", adaptive=False, thin_film=False
                 m.base.thin_film = 1.0
                 m.base.thin_film_ior = 1.3 + 0.05 * (i % 4)
                 m.base.thin_film_thickness = 300.0 + 90.0 * i
-    settings = dict(nb_bounces=nb_bounces, do_alpha_testing=0, enable_adaptive_sampling=int(adaptive), samples_per_frame=1)
+    if alpha_opacity is not None:
+        # stochastic alpha testing (filter_function): every second non-emissive material lets part of the rays through
+        emissive_materials = set(int(scene.material_indices[t]) for t in scene.emissive)
+        for i, m in enumerate(scene.materials):
+            if i not in emissive_materials and i % 2 == 0:
+                m.base.alpha_opacity = alpha_opacity
+    settings = dict(nb_bounces=nb_bounces, do_alpha_testing=int(alpha_opacity is not None), enable_adaptive_sampling=int(adaptive), samples_per_frame=1)
     if adaptive:
         settings.update(adaptive_sampling_min_samples=4, adaptive_sampling_noise_threshold=1.0)
     return {
