@@ -61,6 +61,10 @@ def build(force=False, verbose=False):
         for (lss, ess, later, ggx) in variants():
             objects.append(add(f"fpt_{lss}_{ess}_{later}_{ggx}_{suffix}.o", "b200pt_fpt_variant.cu",
                                defs + [f"-DPT_LSS={lss}", f"-DPT_ESS={ess}", f"-DPT_LATER={later}", f"-DPT_GGX={ggx}"]))
+            if lss == 3:
+                # the phase kernels of the phased MIS pipeline, with the BSDF entry points inlined (see b200pt_phase_variant.cu)
+                objects.append(add(f"phase_{lss}_{ess}_{later}_{ggx}_{suffix}.o", "b200pt_phase_variant.cu",
+                                   defs + [f"-DPT_LSS={lss}", f"-DPT_ESS={ess}", f"-DPT_LATER={later}", f"-DPT_GGX={ggx}", "-DPT_BSDF_INLINE"]))
 
     if jobs:
         with ThreadPoolExecutor(max_workers=os.cpu_count() or 4) as ex:

@@ -87,33 +87,17 @@ __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_bsdf)(const __grid_co
 }
 
 #if PT_LSS == 3
-// The phase kernels wait on memory (ncu, profiles/r01_shade_phases_c3.txt: issue-active 18-23 %, long-scoreboard 7-12 stalled warps
-// per issue at 114-118 registers = 16 warps per SM): cap the registers so that more warps are resident to cover the latency.
-#ifndef PT_PHASE_BLOCKS_PER_SM
-#define PT_PHASE_BLOCKS_PER_SM 12
-#endif
-#define PT_QUEUE_KERNEL(NAME, BOUNDS, KID, CALL)                                                                                                                            \
-    __global__ void __launch_bounds__(BOUNDS, PT_PHASE_BLOCKS_PER_SM) PT_VARIANT_NAME(NAME)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce) \
-    {                                                                                                                                                                  \
-        PT_FOR_EACH_QUEUED(i, wf.counts[kCountsPerBounce * bounce + 1], KID)                                                                                                          \
-            CALL(rd, res, tile, wf, bounce, i);                                                                                                                        \
-    }
-PT_QUEUE_KERNEL(k_wf_nee_light_eval, 64, 2, nee_light_eval_path)
-PT_QUEUE_KERNEL(k_wf_nee_bsdf_sample, 64, 3, nee_bsdf_sample_path<PT_GGX>)
-PT_QUEUE_KERNEL(k_wf_env_light_eval, 64, 4, env_light_eval_path<PT_ESS>)
-PT_QUEUE_KERNEL(k_wf_env_bsdf_sample, 64, 5, env_bsdf_sample_path<PT_GGX>)
-
+// The phase kernels P1..P5 of the phased MIS pipeline live in their own translation unit (b200pt_phase_variant.cu), compiled
+// with the BSDF entry points inlined; this one launches them through launch_phase.
+enum PhaseKernel { PHASE_NEE_LIGHT_EVAL, PHASE_NEE_BSDF_SAMPLE, PHASE_ENV_LIGHT_EVAL, PHASE_ENV_BSDF_SAMPLE, PHASE_BSDF_RESOLVED };
+cudaError_t PT_VARIANT_NAME(launch_phase)(int which, unsigned blocks, cudaStream_t stream, const HIPRTRenderData* rd, int2 res, Tile tile, const WavefrontState* wf, int bounce,
+                                          bool lights_sampled, bool envmap_sampled);
 __global__ void __launch_bounds__(128) PT_VARIANT_NAME(k_wf_surface)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce)
 {
     PT_FOR_EACH_QUEUED(i, wf.counts[kCountsPerBounce * bounce], 8)
         wf_surface_path<PT_ESS>(rd, res, tile, wf, bounce, i);
 }
 
-__global__ void __launch_bounds__(64, PT_PHASE_BLOCKS_PER_SM) PT_VARIANT_NAME(k_wf_bsdf_resolved)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce, bool lights_sampled, bool envmap_sampled)
-{
-    PT_FOR_EACH_QUEUED(i, wf.counts[kCountsPerBounce * bounce + 1], 7)
-        wf_bsdf_resolved_path<PT_ESS, PT_GGX>(rd, res, tile, wf, bounce, i, lights_sampled, envmap_sampled);
-}
 #endif
 
 cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const WavefrontState* wf, int mode, WavefrontProfile* profile)
@@ -209,13 +193,13 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
             const bool envmap = PT_ESS != 0 && rd->world_settings.ambient_light_type == AMBIENT_ENVMAP;
             if (lights)
             {
-                PT_VARIANT_NAME(k_wf_nee_light_eval)<<<g64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
-                PT_VARIANT_NAME(k_wf_nee_bsdf_sample)<<<g64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
+                PT_VARIANT_NAME(launch_phase)(PHASE_NEE_LIGHT_EVAL, g64, stream, rd, res, tile, wf, bounce, lights, envmap);
+                PT_VARIANT_NAME(launch_phase)(PHASE_NEE_BSDF_SAMPLE, g64, stream, rd, res, tile, wf, bounce, lights, envmap);
             }
             if (envmap)
             {
-                PT_VARIANT_NAME(k_wf_env_light_eval)<<<g64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
-                PT_VARIANT_NAME(k_wf_env_bsdf_sample)<<<g64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
+                PT_VARIANT_NAME(launch_phase)(PHASE_ENV_LIGHT_EVAL, g64, stream, rd, res, tile, wf, bounce, lights, envmap);
+                PT_VARIANT_NAME(launch_phase)(PHASE_ENV_BSDF_SAMPLE, g64, stream, rd, res, tile, wf, bounce, lights, envmap);
             }
             stage(STAGE_TRACE);
             if (lights || envmap)
@@ -233,7 +217,7 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
                     return e;
             }
             stage(STAGE_SHADE);
-            PT_VARIANT_NAME(k_wf_bsdf_resolved)<<<g64, 64, 0, stream>>>(*rd, res, tile, *wf, bounce, lights, envmap);
+            PT_VARIANT_NAME(launch_phase)(PHASE_BSDF_RESOLVED, g64, stream, rd, res, tile, wf, bounce, lights, envmap);
         }
         else
 #endif

@@ -201,7 +201,7 @@ PT_DEV RGB RGB_hue_shift(RGB color, float hue_shift_degrees)
 }
 
 // thin_film_fresnel (ThinFilm.h:112-219)
-PT_DEV_NOINLINE RGB thin_film_fresnel(const Material& material, float ambient_IOR, float HoL)
+PT_BSDF_FN RGB thin_film_fresnel(const Material& material, float ambient_IOR, float HoL)
 {
     float eta1 = ambient_IOR;
     float eta2 = material.thin_film_ior;

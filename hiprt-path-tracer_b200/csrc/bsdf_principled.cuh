@@ -27,7 +27,7 @@ PT_DEV RGB principled_specular_fresnel(const Material& material, float relative_
 }
 
 // principled_glass_eval (Principled.h:207-388)
-PT_DEV_NOINLINE RGB principled_glass_eval(const HIPRTRenderData& rd, const Material& material, RayVolumeState& vs, float3 wo, float3 wi, float& pdf)
+PT_BSDF_FN RGB principled_glass_eval(const HIPRTRenderData& rd, const Material& material, RayVolumeState& vs, float3 wo, float3 wi, float& pdf)
 {
     pdf = 0.0f;
     float NoV = wo.z;
@@ -395,7 +395,7 @@ PT_DEV LobeWeights principled_lobe_probabilities(const LobeWeights& w)
 }
 
 // principled_bsdf_eval (Principled.h:974-1063)
-PT_DEV_NOINLINE RGB principled_bsdf_eval(const HIPRTRenderData& rd, const Material& material, RayVolumeState& vs, float3 view_direction, float3 shading_normal, float3 to_light_direction, float& pdf)
+PT_BSDF_FN RGB principled_bsdf_eval(const HIPRTRenderData& rd, const Material& material, RayVolumeState& vs, float3 view_direction, float3 shading_normal, float3 to_light_direction, float& pdf)
 {
     pdf = 0.0f;
 
@@ -446,7 +446,7 @@ PT_DEV_NOINLINE RGB principled_bsdf_eval(const HIPRTRenderData& rd, const Materi
 
 // principled_bsdf_sample (Principled.h:1065-1193)
 template <int GGX_SAMPLER>
-PT_DEV_NOINLINE RGB principled_bsdf_sample(const HIPRTRenderData& rd, const Material& material, RayVolumeState& vs, float3 view_direction, float3 shading_normal, float3 geometric_normal, float3& output_direction, float& pdf, Rng& rng)
+PT_BSDF_FN RGB principled_bsdf_sample(const HIPRTRenderData& rd, const Material& material, RayVolumeState& vs, float3 view_direction, float3 shading_normal, float3 geometric_normal, float3& output_direction, float& pdf, Rng& rng)
 {
     pdf = 0.0f;
     float3 normal = shading_normal;

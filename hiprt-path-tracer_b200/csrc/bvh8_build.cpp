@@ -1,4 +1,4 @@
-// Host builder for the compressed BVH8: binned-SAH binary build (OpenMP tasks) -> greedy surface-area collapse to
+// Host builder for the compressed BVH8: binned-SAH binary build (OpenMP tasks) -> SAH-optimal (dynamic programming) collapse to
 // 8-wide nodes -> octant-aware slot assignment -> 8-bit quantisation (layout: bvh8.h).
 //
 // Replaces hiprtBuildGeometry(hiprtBuildFlagBitPreferHighQualityBuild) behind HIPRTGeometry::build_bvh
@@ -11,6 +11,7 @@
 #include <atomic>
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <queue>
 #include <omp.h>
@@ -157,6 +158,15 @@ struct Builder2
 };
 
 uint8_t unary_bits(int count) { return (uint8_t)((1 << count) - 1); }
+
+// Decisions of the collapse DP for one binary node: used[i-1] = slots actually taken when i are granted (1 = the node itself,
+// as a leaf slot or as a wide node: `leaf`); left_slots[j-2] = slots handed to the left child when the node's subtree is split over j
+struct CollapseChoice
+{
+    uint8_t used[7];
+    uint8_t left_slots[7];
+    uint8_t leaf = 0;
+};
 } // namespace
 
 Bvh8Host build_bvh8(const float* vertices, int vertex_count, const int* indices, int triangle_count)
@@ -200,7 +210,62 @@ Bvh8Host build_bvh8(const float* vertices, int vertex_count, const int* indices,
     const std::vector<Node2>& n2 = b2.nodes;
     for (int a = 0; a < 3; a++) { out.scene_min[a] = n2[root2].box.lo[a]; out.scene_max[a] = n2[root2].box.hi[a]; }
 
-    // ---- collapse to 8-wide and emit breadth-first -------------------------------------------
+    // ---- SAH-optimal collapse of the binary tree into 8-wide nodes (Ylitie, Karras, Laine 2017, section 3.2) --------------
+    // cost[n][i-1] = cheapest way to represent the subtree of n as a forest of at most i children of some wide node:
+    //   leaf(n)       = A(n) * count(n) * c_prim                      (count <= 3: one slot addresses at most 3 triangles)
+    //   internal(n)   = A(n) * c_node + distribute(n, 8)              (n becomes a wide node of its own)
+    //   C(n, 1)       = min(leaf, internal);   C(n, i) = min(distribute(n, i), C(n, i-1))
+    //   distribute(n, j) = min over 0 < k < j of C(left, k) + C(right, j - k)
+    // Children are allocated after their parents, so decreasing index order is bottom-up.
+    const int node_total = b2.node_cursor.load();
+    std::vector<CollapseChoice> choice((size_t)node_total);
+    {
+        static const float c_prim = [] { const char* v = std::getenv("B200PT_BVH_PRIMITIVE_COST"); float f = v ? (float)std::atof(v) : 0.0f; return f > 0.0f ? f : 0.4f; }();
+        const float c_node = 1.0f;
+        std::vector<float> cost((size_t)node_total * 7);
+        for (int n_index = node_total - 1; n_index >= 0; n_index--)
+        {
+            const Node2& nd = n2[n_index];
+            float* c = &cost[(size_t)n_index * 7];
+            CollapseChoice& ch = choice[n_index];
+            const float area = nd.box.half_area();
+            const float leaf = nd.count <= kBvh8MaxLeafTriangles ? area * nd.count * c_prim : FLT_MAX;
+            if (nd.left < 0)
+            {
+                for (int i = 0; i < 7; i++) { c[i] = leaf; ch.used[i] = 1; }
+                ch.leaf = 1;
+                continue;
+            }
+            const float* cl = &cost[(size_t)nd.left * 7];
+            const float* cr = &cost[(size_t)nd.right * 7];
+            float distribute[9];
+            for (int j = 2; j <= 8; j++)
+            {
+                float best = FLT_MAX;
+                int best_k = 1;
+                for (int k = 1; k < j; k++)
+                {
+                    if (k > 7 || j - k > 7)
+                        continue;
+                    const float v = cl[k - 1] + cr[j - k - 1];
+                    if (v < best) { best = v; best_k = k; }
+                }
+                distribute[j] = best;
+                ch.left_slots[j - 2] = (uint8_t)best_k;
+            }
+            const float internal = area * c_node + distribute[8];
+            ch.leaf = leaf <= internal;
+            c[0] = ch.leaf ? leaf : internal;
+            ch.used[0] = 1;
+            for (int i = 2; i <= 7; i++)
+            {
+                if (distribute[i] < c[i - 2]) { c[i - 1] = distribute[i]; ch.used[i - 1] = (uint8_t)i; }
+                else { c[i - 1] = c[i - 2]; ch.used[i - 1] = ch.used[i - 2]; }
+            }
+        }
+    }
+
+    // ---- emit breadth-first -------------------------------------------------------------------
     out.nodes.reserve(n / 4 + 16);
     out.triangles.reserve(n);
     out.nodes.emplace_back();
@@ -215,35 +280,39 @@ Bvh8Host build_bvh8(const float* vertices, int vertex_count, const int* indices,
         auto [bin_index, wide_index] = todo.front();
         todo.pop();
 
-        // Children candidates: open the candidate with the largest area until 8 slots are used. Subtrees holding more than
-        // kBvh8MaxLeafTriangles primitives have to be opened first (a leaf slot addresses at most 3 triangles).
+        // Children of this wide node: the forest the SAH-optimal collapse chose for the binary subtree (see collapse_costs)
         int cand[8];
+        bool cand_is_leaf[8];
         int ncand = 0;
-        if (n2[bin_index].count <= kBvh8MaxLeafTriangles)
+        if (n2[bin_index].left < 0 || (bin_index == root2 && n2[bin_index].count <= kBvh8MaxLeafTriangles))
+        {
+            cand_is_leaf[ncand] = true;
             cand[ncand++] = bin_index;
+        }
         else
         {
-            cand[ncand++] = n2[bin_index].left;
-            cand[ncand++] = n2[bin_index].right;
-        }
-        for (int pass = 0; pass < 2; pass++)
-        {
-            while (ncand < 8)
+            // explicit stack of (binary node, slots granted); a grant of 1 ends in the node's own leaf / internal decision
+            std::pair<int, int> work[16];
+            int nwork = 0;
+            work[nwork++] = {bin_index, 8};
+            bool at_root = true;
+            while (nwork > 0)
             {
-                int pick = -1;
-                float pick_area = -1.0f;
-                for (int i = 0; i < ncand; i++)
+                auto [node, slots] = work[--nwork];
+                const CollapseChoice& ch = choice[node];
+                const int used = at_root ? 8 : (n2[node].left < 0 ? 1 : ch.used[slots - 1]);
+                if (used <= 1)
                 {
-                    const Node2& c = n2[cand[i]];
-                    bool openable = pass == 0 ? c.count > kBvh8MaxLeafTriangles : c.count > 1;
-                    float area = c.box.half_area();
-                    if (openable && area > pick_area) { pick = i; pick_area = area; }
+                    cand_is_leaf[ncand] = n2[node].left < 0 || ch.leaf;
+                    cand[ncand++] = node;
                 }
-                if (pick < 0)
-                    break;
-                int opened = cand[pick];
-                cand[pick] = n2[opened].left;
-                cand[ncand++] = n2[opened].right;
+                else
+                {
+                    const int k = ch.left_slots[used - 2];
+                    work[nwork++] = {n2[node].right, used - k};
+                    work[nwork++] = {n2[node].left, k};
+                }
+                at_root = false;
             }
         }
 
@@ -305,8 +374,9 @@ Bvh8Host build_bvh8(const float* vertices, int vertex_count, const int* indices,
             slot_of[bc] = bs;
         }
         int cand_in_slot[8];
+        bool leaf_in_slot[8] = {false};
         for (int s = 0; s < 8; s++) cand_in_slot[s] = -1;
-        for (int i = 0; i < ncand; i++) cand_in_slot[slot_of[i]] = cand[i];
+        for (int i = 0; i < ncand; i++) { cand_in_slot[slot_of[i]] = cand[i]; leaf_in_slot[slot_of[i]] = cand_is_leaf[i]; }
 
         node.child_base = (uint32_t)out.nodes.size();
         node.tri_base = (uint32_t)out.triangles.size();
@@ -318,7 +388,7 @@ Bvh8Host build_bvh8(const float* vertices, int vertex_count, const int* indices,
                 continue;   // meta 0 = empty slot
             const Node2& child = n2[c];
             double area_ratio = child.box.half_area() / root_area;
-            if (child.count > kBvh8MaxLeafTriangles)
+            if (!leaf_in_slot[s])
             {
                 node.imask |= (uint8_t)(1u << s);
                 node.meta[s] = (uint8_t)((1u << 5) | (24u + s));

@@ -14,6 +14,14 @@
 #define PT_HD __host__ __device__ __forceinline__
 // Large functions called from many sites: a real call keeps the megakernel's code size (and ptxas time) bounded.
 #define PT_DEV_NOINLINE static __device__ __noinline__
+// The BSDF entry points (principled eval / sample, glass eval, thin-film Fresnel). Out of line they take the 256-byte material
+// by reference, which pins it (and the spills around the call) in local memory; PT_BSDF_INLINE lets the compiler keep the
+// fields a kernel uses in registers at the price of code size.
+#ifdef PT_BSDF_INLINE
+#define PT_BSDF_FN static __device__ __forceinline__
+#else
+#define PT_BSDF_FN static __device__ __noinline__
+#endif
 
 namespace pt
 {
