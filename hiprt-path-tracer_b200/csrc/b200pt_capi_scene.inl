@@ -387,6 +387,16 @@ int b200pt_launch_ReSTIR_DI_SpatiotemporalReuse(b200pt_ctx* ctx, const HIPRTRend
     LAUNCH_RESTIR_PIXEL_KERNEL(launch_ReSTIR_DI_SpatiotemporalReuse)
 }
 
+int b200pt_launch_ReSTIR_DI_TemporalReuse(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream)
+{
+    LAUNCH_RESTIR_PIXEL_KERNEL(launch_ReSTIR_DI_TemporalReuse)
+}
+
+int b200pt_launch_ReSTIR_DI_SpatialReuse(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream)
+{
+    LAUNCH_RESTIR_PIXEL_KERNEL(launch_ReSTIR_DI_SpatialReuse)
+}
+
 int b200pt_trace_closest(b200pt_ctx* ctx, b200pt_bvh* bvh, const float* d_rays, const int* d_last_prim, long long n, int* d_out_prim, float* d_out_t, float* d_out_uv, b200pt_stream stream)
 {
     REQUIRE(ctx != nullptr && bvh != nullptr && n >= 0 && (n == 0 || (d_rays != nullptr && d_out_prim != nullptr && d_out_t != nullptr)));

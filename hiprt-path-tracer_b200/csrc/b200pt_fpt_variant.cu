@@ -259,6 +259,24 @@ __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_ReSTIR_DI_Spatiotemporal
     restir_spatiotemporal_pixel(rd, res, x, y);
 }
 
+__global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_ReSTIR_DI_TemporalReuse)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile)
+{
+    const uint32_t x = tile.x0 + blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t y = tile.y0 + blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= (uint32_t)tile.x1 || y >= (uint32_t)tile.y1)
+        return;
+    restir_temporal_pixel(rd, res, x, y);
+}
+
+__global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_ReSTIR_DI_SpatialReuse)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile)
+{
+    const uint32_t x = tile.x0 + blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t y = tile.y0 + blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= (uint32_t)tile.x1 || y >= (uint32_t)tile.y1)
+        return;
+    restir_spatial_pixel(rd, res, x, y);
+}
+
 cudaError_t PT_VARIANT_NAME(launch_ReSTIR_DI_LightsPresampling)(const LightPresamplingParameters* p, cudaStream_t stream)
 {
     const long long n = (long long)p->subset_size * p->number_of_subsets;
@@ -279,6 +297,20 @@ cudaError_t PT_VARIANT_NAME(launch_ReSTIR_DI_SpatiotemporalReuse)(const HIPRTRen
 {
     dim3 grid((tile.x1 - tile.x0 + 7) / 8, (tile.y1 - tile.y0 + 7) / 8, 1);
     PT_VARIANT_NAME(k_ReSTIR_DI_SpatiotemporalReuse)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile);
+    return cudaGetLastError();
+}
+
+cudaError_t PT_VARIANT_NAME(launch_ReSTIR_DI_TemporalReuse)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream)
+{
+    dim3 grid((tile.x1 - tile.x0 + 7) / 8, (tile.y1 - tile.y0 + 7) / 8, 1);
+    PT_VARIANT_NAME(k_ReSTIR_DI_TemporalReuse)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile);
+    return cudaGetLastError();
+}
+
+cudaError_t PT_VARIANT_NAME(launch_ReSTIR_DI_SpatialReuse)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream)
+{
+    dim3 grid((tile.x1 - tile.x0 + 7) / 8, (tile.y1 - tile.y0 + 7) / 8, 1);
+    PT_VARIANT_NAME(k_ReSTIR_DI_SpatialReuse)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile);
     return cudaGetLastError();
 }
 #endif

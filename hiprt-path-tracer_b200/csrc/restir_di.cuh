@@ -366,6 +366,9 @@ PT_DEV int3 restir_find_temporal_neighbor_index(const HIPRTRenderData& rd, float
 struct PairwiseDefensiveMISWeight
 {
     float mc = 0.0f;
+    // the stand-alone spatial pass (SpatialMISWeight.h:216) reads the neighbour's surface from THIS frame's G-buffer, the fused
+    // pass (SpatiotemporalMISWeight.h:241) from last frame's when the temporal pass is enabled; the arithmetic is the same
+    bool neighbor_surface_of_current_frame = false;
 
     PT_DEV float get(const HIPRTRenderData& rd, const ReSTIRDIReservoir& reservoir_being_resampled, const ReSTIRDIReservoir& center_pixel_reservoir, float target_function_at_center,
                      int neighbor_pixel_index, int valid_neighbors_count, int valid_neighbors_M_sum, bool update_mc, bool resample_canonical, Rng& rng)
@@ -390,7 +393,7 @@ struct PairwiseDefensiveMISWeight
             if (update_mc)
             {
                 ReSTIRSurface neighbor_pixel_surface;
-                get_pixel_surface(rd, neighbor_pixel_index, use_prev_frame_g_buffer(rd), neighbor_pixel_surface);
+                get_pixel_surface(rd, neighbor_pixel_index, neighbor_surface_of_current_frame ? false : use_prev_frame_g_buffer(rd), neighbor_pixel_surface);
                 float at_neighbor = restir_evaluate_target_function<true>(rd, center_pixel_reservoir.sample, neighbor_pixel_surface, rng);
                 float at_center = center_pixel_reservoir.sample.target_function;
                 float nume_mc = at_center / valid_neighbor_division_term * center_reservoir_M;
@@ -408,6 +411,49 @@ struct PairwiseDefensiveMISWeight
         if (confidence)
             return mc + (float)center_pixel_reservoir.M / (center_pixel_reservoir.M + valid_neighbors_M_sum);
         return (1 + mc) / (valid_neighbors_count + 1);
+    }
+};
+
+// ReSTIRDITemporalResamplingMISWeight<PAIRWISE_MIS_DEFENSIVE> (TemporalMISWeight.h:204-279): the two-sample case of the
+// pairwise weights, temporal neighbour first (accumulates mc), initial candidates second
+struct TemporalPairwiseDefensiveMISWeight
+{
+    float mc = 0.0f;
+
+    PT_DEV float get(const HIPRTRenderData& rd, const ReSTIRDIReservoir& temporal_neighbor_reservoir, const ReSTIRDIReservoir& initial_candidates_reservoir,
+                     const ReSTIRSurface& temporal_neighbor_surface, float neighbor_sample_target_function_at_center, bool resample_initial_candidates, Rng& rng)
+    {
+        const bool confidence = rd.render_settings.restir_di_settings.use_confidence_weights;
+        if (!resample_initial_candidates)
+        {
+            float target_function_at_neighbor = temporal_neighbor_reservoir.sample.target_function;
+            float target_function_at_center = neighbor_sample_target_function_at_center;
+            float temporal_neighbor_M = confidence ? temporal_neighbor_reservoir.M : 1;
+            float center_reservoir_M = confidence ? initial_candidates_reservoir.M : 1;
+            float neighbors_confidence_sum = confidence ? temporal_neighbor_reservoir.M : 1;
+
+            float nume = target_function_at_neighbor * temporal_neighbor_M;
+            float denom = target_function_at_neighbor * neighbors_confidence_sum + target_function_at_center * center_reservoir_M;
+            float mi = denom == 0.0f ? 0.0f : (nume / denom);
+            if (confidence)
+                mi *= neighbors_confidence_sum / (neighbors_confidence_sum + center_reservoir_M);
+
+            float at_neighbor = restir_evaluate_target_function<true>(rd, initial_candidates_reservoir.sample, temporal_neighbor_surface, rng);
+            float at_center = initial_candidates_reservoir.sample.target_function;
+            float nume_mc = at_center * center_reservoir_M;
+            float denom_mc = at_neighbor * neighbors_confidence_sum + at_center * center_reservoir_M;
+            float confidence_multiplier = 1.0f;
+            if (confidence)
+                confidence_multiplier = neighbors_confidence_sum / (neighbors_confidence_sum + center_reservoir_M);
+            if (denom_mc != 0.0f)
+                mc += nume_mc / denom_mc * confidence_multiplier;
+            return confidence ? mi : mi * 0.5f;
+        }
+        if (mc == 0.0f)
+            return 1.0f;
+        if (confidence)
+            return mc + (float)initial_candidates_reservoir.M / (initial_candidates_reservoir.M + temporal_neighbor_reservoir.M);
+        return (1.0f + mc) * 0.5f;
     }
 };
 

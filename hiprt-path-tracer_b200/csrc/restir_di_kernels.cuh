@@ -444,4 +444,192 @@ PT_DEV void restir_spatiotemporal_pixel(const HIPRTRenderData& rd, int2 res, uin
         out.M = mini(out.M, rs.m_cap);
     store_reservoir(rs.spatial_pass.output_reservoirs + center_pixel_index, out);
 }
+
+// ---- ReSTIR_DI_TemporalReuse (TemporalReuse.h:48-306): the non-fused configuration's temporal pass ---------------------------------
+// Combines last frame's reservoir at the back-projected pixel with this frame's initial candidates (pairwise-defensive MIS,
+// bias correction with visibility). Pixels without a usable temporal neighbour copy their initial candidates through.
+PT_DEV void restir_temporal_pixel(const HIPRTRenderData& rd, int2 res, uint32_t x, uint32_t y)
+{
+    const uint32_t center_pixel_index = x + y * res.x;
+    if (!rd.aux_buffers.pixel_active[center_pixel_index] || !rd.g_buffer.camera_ray_hit[center_pixel_index])
+        return;
+
+    const ReSTIRDISettings& rs = rd.render_settings.restir_di_settings;
+    Rng rng(pixel_seed(rd, center_pixel_index));
+
+    if (rs.temporal_pass.temporal_buffer_clear_requested)
+        store_reservoir(rs.temporal_pass.input_reservoirs + center_pixel_index, empty_reservoir());
+
+    ReSTIRSurface center;
+    get_pixel_surface(rd, center_pixel_index, false, center);
+    if (material_is_emissive(center.material))
+        return;
+
+    const ReSTIRDIReservoir initial_candidates_reservoir = load_reservoir(rs.initial_candidates.output_reservoirs + center_pixel_index);
+    ReSTIRDIReservoir* output = rs.temporal_pass.output_reservoirs + center_pixel_index;
+
+    int temporal_neighbor_pixel_index = restir_find_temporal_neighbor_index(rd, ld3_rw(rd.g_buffer.first_hits, center_pixel_index), center.shading_normal, res, center_pixel_index, rng).x;
+    if (temporal_neighbor_pixel_index == -1 || rd.render_settings.freeze_random)
+    {
+        store_reservoir(output, initial_candidates_reservoir);       // :88-97 (disocclusion, or frozen random: same samples every frame)
+        return;
+    }
+    const ReSTIRDIReservoir temporal_neighbor_reservoir = load_reservoir(rs.temporal_pass.input_reservoirs + temporal_neighbor_pixel_index);
+    if (temporal_neighbor_reservoir.M == 0)
+    {
+        store_reservoir(output, initial_candidates_reservoir);       // :100-108
+        return;
+    }
+    ReSTIRSurface temporal_neighbor_surface;
+    get_pixel_surface(rd, temporal_neighbor_pixel_index, use_prev_frame_g_buffer(rd), temporal_neighbor_surface);
+    if (material_is_emissive(temporal_neighbor_surface.material))
+    {
+        store_reservoir(output, initial_candidates_reservoir);       // :113-120
+        return;
+    }
+
+    ReSTIRDIReservoir out = empty_reservoir();
+    TemporalPairwiseDefensiveMISWeight mis_weight_function;
+
+    // temporal neighbour (:136-207)
+    {
+        float target_function_at_center = 0.0f;
+        if (temporal_neighbor_reservoir.UCW > 0.0f)
+            target_function_at_center = restir_evaluate_target_function<true>(rd, temporal_neighbor_reservoir.sample, center, rng);
+
+        float jacobian_determinant = 1.0f;
+        if (target_function_at_center > 0.0f && temporal_neighbor_reservoir.UCW > 0.0f && !(temporal_neighbor_reservoir.sample.flags & RESTIR_DI_FLAGS_ENVMAP_SAMPLE))
+        {
+            jacobian_determinant = restir_jacobian_reconnection_shift(rd, temporal_neighbor_reservoir, center.shading_point, temporal_neighbor_surface.shading_point - temporal_neighbor_surface.shading_normal * 1.0e-4f);
+            if (jacobian_determinant == -1.0f)
+                jacobian_determinant = 0.0f;
+        }
+        float w = mis_weight_function.get(rd, temporal_neighbor_reservoir, initial_candidates_reservoir, temporal_neighbor_surface, target_function_at_center, false, rng);
+        if (reservoir_combine_with(out, temporal_neighbor_reservoir, w, target_function_at_center, jacobian_determinant, rng))
+            out.sample.flags |= RESTIR_DI_FLAGS_UNOCCLUDED;           // ReSTIR_DI_BiasCorrectionUseVisibility == TRUE
+    }
+
+    // initial candidates (:210-247)
+    {
+        float w = mis_weight_function.get(rd, temporal_neighbor_reservoir, initial_candidates_reservoir, temporal_neighbor_surface, 0.0f, true, rng);
+        if (reservoir_combine_with(out, initial_candidates_reservoir, w, initial_candidates_reservoir.sample.target_function, 1.0f, rng))
+            out.sample.flags |= RESTIR_DI_FLAGS_UNOCCLUDED;
+    }
+
+    reservoir_end_with_normalization(out, 1.0f, 1.0f);
+    if (rs.m_cap > 0)
+        out.M = mini(out.M, rs.m_cap);
+    store_reservoir(output, out);
+}
+
+// ---- ReSTIR_DI_SpatialReuse (SpatialReuse.h:64-348): a spatial pass on its own -- the non-fused configuration, and the passes
+// 1..number_of_passes-1 that follow the fused pass on the GPU (ReSTIRDIRenderPass.cpp:492-501). Neighbours on the rotated
+// Hammersley disk around the pixel ITSELF, read from this frame's G-buffer; the centre reservoir is the pass input at the pixel.
+PT_DEV void restir_spatial_pixel(const HIPRTRenderData& rd, int2 res, uint32_t x, uint32_t y)
+{
+    const uint32_t center_pixel_index = x + y * res.x;
+    if (!rd.aux_buffers.pixel_active[center_pixel_index] || !rd.g_buffer.camera_ray_hit[center_pixel_index])
+        return;
+
+    const ReSTIRDISettings& rs = rd.render_settings.restir_di_settings;
+    Rng rng(pixel_seed(rd, center_pixel_index));
+    const ReSTIRDIReservoir* spatial_input = rs.spatial_pass.input_reservoirs;
+    const int2 center_pixel_coords = make_int2(x, y);
+
+    ReSTIRSurface center;
+    get_pixel_surface(rd, center_pixel_index, false, center);
+    if (material_is_emissive(center.material))
+        return;
+
+    float rotation_theta = rs.spatial_pass.do_neighbor_rotation ? kTwoPi * rng() : 0.0f;
+    float2 cos_sin_theta_rotation = make_float2(cosf(rotation_theta), sinf(rotation_theta));
+
+    const ReSTIRDIReservoir center_pixel_reservoir = load_reservoir(spatial_input + center_pixel_index);
+    int reused_neighbors_count = rs.spatial_pass.reuse_neighbor_count;
+    if (center_pixel_reservoir.M <= 1 && rs.spatial_pass.do_disocclusion_reuse_boost)
+        reused_neighbors_count = rs.spatial_pass.disocclusion_reuse_count;
+
+    // count_valid_spatial_neighbors (Utils.h:382-402)
+    int neighbor_heuristics_cache = 0, valid_neighbors_count = 0, valid_neighbors_M_sum = 0;
+    for (int neighbor_index = 0; neighbor_index < reused_neighbors_count; neighbor_index++)
+    {
+        int neighbor_pixel_index = restir_spatial_neighbor_pixel_index(rd, neighbor_index, reused_neighbors_count, rs.spatial_pass.reuse_radius, center_pixel_coords, res, cos_sin_theta_rotation);
+        if (neighbor_pixel_index == -1)
+            continue;
+        if (!restir_check_neighbor_similarity_heuristics(rd, neighbor_pixel_index, center_pixel_index, center.shading_point, center.shading_normal, false))
+            continue;
+        valid_neighbors_M_sum += spatial_input[neighbor_pixel_index].M;
+        valid_neighbors_count++;
+        neighbor_heuristics_cache |= (1 << neighbor_index);
+    }
+
+    ReSTIRDIReservoir out = empty_reservoir();
+    PairwiseDefensiveMISWeight mis_weight_function;
+    mis_weight_function.neighbor_surface_of_current_frame = true;
+    const bool update_mc = center_pixel_reservoir.M > 0 && center_pixel_reservoir.UCW > 0.0f;
+
+    int start_index = valid_neighbors_M_sum == 0 ? reused_neighbors_count : 0;
+    for (int neighbor_index = start_index; neighbor_index < reused_neighbors_count + 1; neighbor_index++)
+    {
+        const bool canonical = neighbor_index == reused_neighbors_count;
+        if (!canonical && reused_neighbors_count <= 32)
+            if ((neighbor_heuristics_cache & (1 << neighbor_index)) == 0)
+                continue;
+
+        int neighbor_pixel_index = restir_spatial_neighbor_pixel_index(rd, neighbor_index, reused_neighbors_count, rs.spatial_pass.reuse_radius, center_pixel_coords, res, cos_sin_theta_rotation);
+        if (neighbor_pixel_index == -1)
+            continue;
+        if (!canonical && reused_neighbors_count > 32)
+            if (!restir_check_neighbor_similarity_heuristics(rd, neighbor_pixel_index, center_pixel_index, center.shading_point, center.shading_normal, false))
+                continue;
+
+        ReSTIRDIReservoir neighbor_reservoir = canonical ? center_pixel_reservoir : load_reservoir(spatial_input + neighbor_pixel_index);
+
+        float target_function_at_center = 0.0f;
+        const bool do_neighbor_target_function_visibility = restir_include_spatial_visibility(rd, neighbor_index, reused_neighbors_count);
+        if (neighbor_reservoir.UCW > 0.0f)
+        {
+            if (canonical)
+                target_function_at_center = neighbor_reservoir.sample.target_function;
+            else if (do_neighbor_target_function_visibility)
+                target_function_at_center = restir_evaluate_target_function<true>(rd, neighbor_reservoir.sample, center, rng);
+            else
+                target_function_at_center = restir_evaluate_target_function<false>(rd, neighbor_reservoir.sample, center, rng);
+        }
+
+        float jacobian_determinant = 1.0f;
+        if (target_function_at_center > 0.0f && neighbor_reservoir.UCW > 0.0f && !canonical && !(neighbor_reservoir.sample.flags & RESTIR_DI_FLAGS_ENVMAP_SAMPLE))
+        {
+            // Utils.h:199-202: the neighbour's first hit WITHOUT the normal offset
+            jacobian_determinant = restir_jacobian_reconnection_shift(rd, neighbor_reservoir, center.shading_point, ld3_rw(rd.g_buffer.first_hits, neighbor_pixel_index));
+            if (jacobian_determinant == -1.0f)
+            {
+                out.M += neighbor_reservoir.M;
+                continue;
+            }
+        }
+
+        float mis_weight = mis_weight_function.get(rd, neighbor_reservoir, center_pixel_reservoir, target_function_at_center, neighbor_pixel_index, valid_neighbors_count, valid_neighbors_M_sum, update_mc, canonical, rng);
+
+        if (reservoir_combine_with(out, neighbor_reservoir, mis_weight, target_function_at_center, jacobian_determinant, rng))
+        {
+            if (do_neighbor_target_function_visibility)
+                out.sample.flags |= RESTIR_DI_FLAGS_UNOCCLUDED;
+            else if (canonical)
+                out.sample.flags |= neighbor_reservoir.sample.flags & RESTIR_DI_FLAGS_UNOCCLUDED;
+            else
+                out.sample.flags &= ~RESTIR_DI_FLAGS_UNOCCLUDED;
+        }
+    }
+
+    reservoir_end_with_normalization(out, 1.0f, 1.0f);
+
+    // end-of-pass visibility reuse (:262-336)
+    if (rs.temporal_pass.do_temporal_reuse_pass || rs.spatial_pass.number_of_passes - 1 != rs.spatial_pass.spatial_pass_index)
+        restir_visibility_reuse(rd, out, center.shading_point, center.last_hit_primitive_index, rng);
+
+    if (rs.m_cap > 0)
+        out.M = mini(out.M, rs.m_cap);
+    store_reservoir(rs.spatial_pass.output_reservoirs + center_pixel_index, out);
+}
 } // namespace pt
