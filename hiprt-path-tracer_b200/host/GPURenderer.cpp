@@ -483,8 +483,8 @@ void GPURenderer::launch_ReSTIR_DI()
     // presampling -> initial candidates -> fused spatiotemporal reuse, each with its own seed draw
     HIPRTRenderData& rd = m_render_data;
     ReSTIRDISettings& rs = rd.render_settings.restir_di_settings;
-    if (!rs.do_fused_spatiotemporal || !rs.temporal_pass.do_temporal_reuse_pass || !rs.spatial_pass.do_spatial_reuse_pass)
-        throw std::runtime_error("ReSTIR DI: only the fused spatiotemporal reuse pass is built (do_fused_spatiotemporal with temporal and spatial reuse enabled)");
+    if (rs.do_fused_spatiotemporal && !(rs.temporal_pass.do_temporal_reuse_pass && rs.spatial_pass.do_spatial_reuse_pass))
+        throw std::runtime_error("ReSTIR DI: do_fused_spatiotemporal needs both the temporal and the spatial reuse pass enabled (ReSTIRDIRenderPass.cpp:268-274)");
     const b200pt_tile* tile = m_has_tile ? &m_tile : nullptr;
 
     // ReSTIRDIRenderPass::launch_presampling_lights_pass / configure (ReSTIRDIRenderPass.cpp:354-386)
@@ -512,19 +512,86 @@ void GPURenderer::launch_ReSTIR_DI()
     rs.initial_candidates.output_reservoirs = m_restir_initial.get_device_pointer();
     check(b200pt_launch_ReSTIR_DI_InitialCandidates(m_ctx, &rd, m_res, tile, nullptr), "b200pt_launch_ReSTIR_DI_InitialCandidates");
 
-    // fused spatiotemporal reuse (ReSTIRDIRenderPass.cpp:505-548): last frame's output is this frame's temporal input
-    rd.random_seed = m_rng.xorshift32();
-    rs.temporal_pass.permutation_sampling_random_bits = m_rng.xorshift32();
-    ReSTIRDIReservoir* previous = m_restir_odd_frame ? m_restir_spatial_1.get_device_pointer() : m_restir_spatial_2.get_device_pointer();
-    ReSTIRDIReservoir* output = m_restir_odd_frame ? m_restir_spatial_2.get_device_pointer() : m_restir_spatial_1.get_device_pointer();
-    rs.temporal_pass.input_reservoirs = previous;
-    rs.temporal_pass.output_reservoirs = nullptr;
-    rs.spatial_pass.input_reservoirs = previous;
-    rs.spatial_pass.output_reservoirs = output;
-    check(b200pt_launch_ReSTIR_DI_SpatiotemporalReuse(m_ctx, &rd, m_res, tile, nullptr), "b200pt_launch_ReSTIR_DI_SpatiotemporalReuse");
+    ReSTIRDIReservoir* const spatial_1 = m_restir_spatial_1.get_device_pointer();
+    ReSTIRDIReservoir* const spatial_2 = m_restir_spatial_2.get_device_pointer();
+    // The CPU seed schedule mirrors CPURenderer::ReSTIR_DI (CPURenderer.cpp:401-434, configure_* :503-633), which never updates
+    // spatial_pass_index and runs no extra spatial pass after the fused one; the GPU schedule mirrors ReSTIRDIRenderPass
+    const bool cpu_schedule = seed_schedule == SeedSchedule::CPU;
+    if (rs.do_fused_spatiotemporal)
+    {
+        // fused spatiotemporal reuse (ReSTIRDIRenderPass.cpp:378-390,433-455,476-503): last frame's output is this frame's temporal input
+        rd.random_seed = m_rng.xorshift32();
+        rs.temporal_pass.permutation_sampling_random_bits = m_rng.xorshift32();
+        ReSTIRDIReservoir* previous = m_restir_odd_frame ? spatial_1 : spatial_2;
+        rs.temporal_pass.input_reservoirs = previous;
+        rs.temporal_pass.output_reservoirs = nullptr;
+        rs.spatial_pass.input_reservoirs = previous;
+        rs.spatial_pass.output_reservoirs = previous == spatial_1 ? spatial_2 : spatial_1;
+        if (!cpu_schedule)
+            rs.spatial_pass.spatial_pass_index = 0;
+        check(b200pt_launch_ReSTIR_DI_SpatiotemporalReuse(m_ctx, &rd, m_res, tile, nullptr), "b200pt_launch_ReSTIR_DI_SpatiotemporalReuse");
 
-    // configure_output_buffer (ReSTIRDIRenderPass.cpp:550-563)
-    rs.restir_output_reservoirs = output;
-    m_restir_odd_frame = !m_restir_odd_frame;
+        // the remaining spatial passes of number_of_passes (:492-501), ping-ponging between the two spatial buffers
+        for (int pass = 1; !cpu_schedule && pass < rs.spatial_pass.number_of_passes; pass++)
+        {
+            if (m_has_tile && m_tile_halo > 0)
+                throw std::runtime_error("ReSTIR DI tile sharding exchanges one halo per frame: number_of_passes > 1 is not supported on a tile with a halo");
+            rs.spatial_pass.spatial_pass_index = pass;
+            rd.random_seed = m_rng.xorshift32();
+            rs.spatial_pass.input_reservoirs = rs.spatial_pass.output_reservoirs;
+            rs.spatial_pass.output_reservoirs = rs.spatial_pass.input_reservoirs == spatial_1 ? spatial_2 : spatial_1;
+            check(b200pt_launch_ReSTIR_DI_SpatialReuse(m_ctx, &rd, m_res, tile, nullptr), "b200pt_launch_ReSTIR_DI_SpatialReuse");
+        }
+        // With an even number of passes the output lands in last frame's buffer: the next frame's temporal input is
+        // restir_output_reservoirs (ReSTIRDIRenderPass.cpp:384), so m_restir_odd_frame follows the buffer, not the frame count
+        m_restir_odd_frame = rs.spatial_pass.output_reservoirs == spatial_1;
+    }
+    else
+    {
+        if (m_has_tile && m_tile_halo > 0)
+            throw std::runtime_error("ReSTIR DI tile sharding with a halo is built for the fused spatiotemporal pass only");
+        if (rs.temporal_pass.do_temporal_reuse_pass)
+        {
+            // configure_temporal_pass (ReSTIRDIRenderPass.cpp:332-366)
+            rd.random_seed = m_rng.xorshift32();
+            rs.temporal_pass.permutation_sampling_random_bits = m_rng.xorshift32();
+            rs.temporal_pass.input_reservoirs = rs.restir_output_reservoirs;
+            if (rs.spatial_pass.do_spatial_reuse_pass)
+                rs.temporal_pass.output_reservoirs = m_restir_initial.get_device_pointer();     // in place: a pixel touches only its own entry
+            else
+                rs.temporal_pass.output_reservoirs = m_restir_odd_frame ? spatial_1 : spatial_2;
+            check(b200pt_launch_ReSTIR_DI_TemporalReuse(m_ctx, &rd, m_res, tile, nullptr), "b200pt_launch_ReSTIR_DI_TemporalReuse");
+        }
+        if (rs.spatial_pass.do_spatial_reuse_pass)
+        {
+            for (int pass = 0; pass < rs.spatial_pass.number_of_passes; pass++)
+            {
+                // configure_spatial_pass (ReSTIRDIRenderPass.cpp:392-431)
+                rd.random_seed = m_rng.xorshift32();
+                if (!cpu_schedule)
+                    rs.spatial_pass.spatial_pass_index = pass;
+                if (pass == 0)
+                {
+                    rs.spatial_pass.input_reservoirs = rs.temporal_pass.do_temporal_reuse_pass ? rs.temporal_pass.output_reservoirs : rs.initial_candidates.output_reservoirs;
+                    rs.spatial_pass.output_reservoirs = spatial_1;
+                }
+                else
+                {
+                    rs.spatial_pass.input_reservoirs = (pass & 1) == 0 ? spatial_2 : spatial_1;
+                    rs.spatial_pass.output_reservoirs = (pass & 1) == 0 ? spatial_1 : spatial_2;
+                }
+                check(b200pt_launch_ReSTIR_DI_SpatialReuse(m_ctx, &rd, m_res, tile, nullptr), "b200pt_launch_ReSTIR_DI_SpatialReuse");
+            }
+        }
+        m_restir_odd_frame = !m_restir_odd_frame;
+    }
+
+    // configure_output_buffer (ReSTIRDIRenderPass.cpp:550-570)
+    if (rs.spatial_pass.do_spatial_reuse_pass || rs.do_fused_spatiotemporal)
+        rs.restir_output_reservoirs = rs.spatial_pass.output_reservoirs;
+    else if (rs.temporal_pass.do_temporal_reuse_pass)
+        rs.restir_output_reservoirs = rs.temporal_pass.output_reservoirs;
+    else
+        rs.restir_output_reservoirs = rs.initial_candidates.output_reservoirs;
 }
 } // namespace b200pt_host

@@ -73,18 +73,23 @@ def synthetic_small(width, height, ggx=0):
     return cfg
 
 
-def many_lights(width, height, boxes=2000, lights=100_000):
+def many_lights(width, height, boxes=2000, lights=100_000, fused=True, temporal=True, spatial=True, spatial_passes=1):
     """C4: closed room + diffuse boxes + 100 000 small emissive triangles; ReSTIR DI with light presampling and the fused
-    spatiotemporal pass, RIS on later bounces."""
+    spatiotemporal pass, RIS on later bounces. fused=False runs the stand-alone TemporalReuse / SpatialReuse passes
+    (ReSTIRDIRenderPass.cpp:332-474); spatial_passes > 1 adds SpatialReuse passes (after the fused pass: GPU seed schedule only)."""
     key = ("many_lights", boxes, lights)
     if key not in _CACHE:
         _CACHE[key] = procedural.many_lights_room(boxes, lights)
     scene = _CACHE[key]
     return {
-        "name": f"many-light room {scene.triangle_count} triangles ({len(scene.emissive)} emissive) {width}x{height}, 8 bounces, LSS_RESTIR_DI (presampled lights, fused spatiotemporal), later bounces RIS",
+        "name": f"many-light room {scene.triangle_count} triangles ({len(scene.emissive)} emissive) {width}x{height}, 8 bounces, LSS_RESTIR_DI (presampled lights, "
+                + ("fused spatiotemporal" if fused else "+".join(n for n, on in (("temporal", temporal), ("spatial", spatial)) if on) + " reuse passes")
+                + (f", {spatial_passes} spatial passes" if spatial_passes > 1 else "") + "), later bounces RIS",
         "scene": scene, "camera": sc.scene_camera(scene, width, height), "width": width, "height": height,
         "options": dict(lss="restir_di", ess="none", ggx=0, later=3), "oracle_variant": "restir", "envmap": None,
-        "settings": dict(nb_bounces=8, do_alpha_testing=0, enable_adaptive_sampling=0, samples_per_frame=1),
+        "settings": {"nb_bounces": 8, "do_alpha_testing": 0, "enable_adaptive_sampling": 0, "samples_per_frame": 1,
+                     "restir_di_settings.do_fused_spatiotemporal": int(fused), "restir_di_settings.temporal_pass.do_temporal_reuse_pass": int(temporal),
+                     "restir_di_settings.spatial_pass.do_spatial_reuse_pass": int(spatial), "restir_di_settings.spatial_pass.number_of_passes": spatial_passes},
     }
 
 

@@ -158,6 +158,13 @@ B200PT_API int b200pt_stream_wait_event(b200pt_ctx* ctx, b200pt_stream stream, b
 B200PT_API int b200pt_launch_ReSTIR_DI_LightsPresampling(b200pt_ctx* ctx, const LightPresamplingParameters* parameters, b200pt_stream stream);
 B200PT_API int b200pt_launch_ReSTIR_DI_InitialCandidates(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream);
 B200PT_API int b200pt_launch_ReSTIR_DI_SpatiotemporalReuse(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream);
+/* The stand-alone reuse passes: replace the launches of ReSTIR_DI_TemporalReuse (src/Device/kernels/ReSTIR/DI/TemporalReuse.h:48,
+ * launched at src/Renderer/RenderPasses/ReSTIRDIRenderPass.cpp:368-376) and ReSTIR_DI_SpatialReuse (SpatialReuse.h:64, launched at
+ * ReSTIRDIRenderPass.cpp:457-474 and, after the fused pass when number_of_passes > 1, :492-501). Buffers are the pointers inside
+ * render_data->render_settings.restir_di_settings.{temporal_pass,spatial_pass}; the temporal pass may write in place over the
+ * initial-candidates buffer (a pixel reads and writes only its own entry of it), a spatial pass must not alias input and output. */
+B200PT_API int b200pt_launch_ReSTIR_DI_TemporalReuse(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream);
+B200PT_API int b200pt_launch_ReSTIR_DI_SpatialReuse(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream);
 
 /* ---- ray batches: the traversal core on its own (parity pins on hit ids; roofline measurement) ------------------ */
 /* rays: n x 6 floats (origin, direction) on the device. last_prim: n ints or NULL (-1). Outputs on the device. */

@@ -293,6 +293,70 @@ def test_restir_di_parity(pt, wl, ctx, ref):
     g.close()
 
 
+@pytest.mark.parametrize("temporal,spatial,passes", [(True, True, 1), (True, True, 2), (False, True, 2), (True, False, 1)])
+def test_restir_di_separate_reuse_passes_parity(pt, wl, ctx, ref, temporal, spatial, passes):
+    """the stand-alone ReSTIR_DI_TemporalReuse / ReSTIR_DI_SpatialReuse kernels (do_fused_spatiotemporal off) and
+    the host ping-pong of their reservoir buffers (temporal pass in place over the initial candidates, spatial passes between the
+    two spatial buffers), against the reference's CPU kernels driven the way CPURenderer::ReSTIR_DI drives them
+    (CPURenderer.cpp:413-429). Same comparison rules as the fused test: integers exact, a small budget for reservoirs where a
+    sinf/cosf ulp moved a disk-sampled neighbour by a pixel."""
+    cfg = wl.many_lights(128, 96, boxes=150, lights=3000, fused=False, temporal=temporal, spatial=spatial, spatial_passes=passes)
+    r = wl.setup_oracle(ref, pt.structs, cfg)
+    g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="cpu")
+    frames = 4
+    import ctypes as C
+    try:
+        for f in range(frames):
+            r.render(1)
+            g.render_frame()
+            g.synchronize()
+            raw = np.ascontiguousarray(r.buffer("restir_output_reservoirs"))
+            oa, ob = _reservoirs(raw), _reservoirs(g.download("restir_output_reservoirs"))
+            same = (oa["tri"] == ob["tri"]) & (oa["M"] == ob["M"])
+            assert same.mean() > 0.998, (f, same.mean())
+            ok = same & np.isfinite(oa["UCW"])
+            close = np.isclose(oa["UCW"][ok], ob["UCW"][ok], rtol=1e-4, atol=1e-12)
+            assert close.mean() > 0.995, (f, close.mean())
+            if f > 0 or spatial:
+                assert (ob["M"] > 1).mean() > 0.3, (f, (ob["M"] > 1).mean())      # the passes did combine reservoirs
+            # A reservoir that differs (a sinf/cosf ulp moved a disk-sampled neighbour by a pixel) spreads over reuse_radius per
+            # spatial pass and per frame; the oracle's output becomes the next frame's temporal input on both sides so that
+            # every frame is checked on its own
+            pt._capi.check(ctx.lib.b200pt_memcpy_h2d(ctx.handle, C.c_void_p(g.device_pointer("restir_output_reservoirs")), raw.ctypes.data_as(C.c_void_p), C.c_size_t(raw.nbytes), None), "h2d")
+            ctx.sync()
+        a, b = r.pixels() / frames, g.download("pixels") / frames
+        err = _rel_err(a, b)
+        assert err < 1e-3, err
+        assert abs(a.mean() - b.mean()) / a.mean() < 1e-3
+    finally:
+        g.close()
+
+
+def test_restir_di_extra_spatial_pass_after_fused(pt, wl, ctx):
+    """GPU schedule of the reference (ReSTIRDIRenderPass.cpp:476-503): number_of_passes = 2 runs one SpatialReuse pass after the
+    fused spatiotemporal pass. The CPU renderer never does (CPURenderer.cpp:405-411), so there is no oracle run for this shape:
+    checked here are the buffer ping-pong (the output of frame k is the temporal input of frame k + 1, M grows to the cap),
+    determinism, and that the estimate agrees with the one-pass render of the same scene (both are unbiased: pairwise MIS)."""
+    W, H, frames = 128, 96, 24
+    means = []
+    for passes in (1, 2):
+        cfg = wl.many_lights(W, H, boxes=150, lights=3000, spatial_passes=passes)
+        runs = []
+        for _ in range(2 if passes == 2 else 1):
+            g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="gpu")
+            for _ in range(frames):
+                g.render_frame()
+            g.synchronize()
+            runs.append((g.download("pixels").copy() / frames, _reservoirs(g.download("restir_output_reservoirs")).copy()))
+            g.close()
+        if passes == 2:
+            assert np.array_equal(runs[0][0], runs[1][0])
+            M, cap = runs[0][1]["M"], 25       # ReSTIRDISettings.h m_cap default
+            assert M.max() == cap and (M == cap).mean() > 0.5, (M.max(), (M == cap).mean())     # m_cap: the history survived every frame
+        means.append(runs[0][0].mean())
+    assert abs(means[0] - means[1]) / means[0] < 0.02, means
+
+
 def test_restir_di_tile_sharding_with_halo_is_bit_identical(pt, wl, ctx):
     """The multi-GPU shard shape of config C4 on one device: two renderers own the two halves of the image, each runs CameraRays
     over tile + 20 halo rows, and after every frame only the output reservoirs of the halo rows are copied across (what
