@@ -61,6 +61,17 @@ def measured_hbm_peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def measured_traffic(workload, width, height):
+    """DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of the k_trace_queue launches of ONE step, from the committed
+    `ncu --set full` capture of `bench.py --profile` (profiles/traffic.json, written by tools/ncu_traffic.py); null if this
+    workload / size was not captured."""
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(path):
+        return None
+    entry = json.load(open(path)).get(f"{workload}_{width}x{height}")
+    return entry["trace_queue_dram_bytes_per_step"] if entry else None
+
+
 def run_reference(args, cfg, pt):
     """Reference arm: the reference's own CPU implementation of the path (oracle/_ref = its unmodified kernels)."""
     from oracle import ref
@@ -138,6 +149,15 @@ def run_ours(args, cfg, pt):
             rows = mg.device_rows(g.device_pointer("restir_output_reservoirs"), H, W * 36, device)
             mg.exchange_halo(dist, rows, tiles, rank, halo)
             torch.cuda.synchronize()
+
+    if args.profile:
+        # under ncu: only what the timed pass launches (3 warm-up frames + K frames), so that the launch list is the step's
+        restart()
+        for _ in range(3 + args.steps):
+            step()
+        g.synchronize()
+        print(json.dumps({"profile": cfg["name"], "frames": 3 + args.steps, "path_lanes": g.path_lanes}))
+        return None
 
     # ---- 1. counting pass: the same frames as the timed pass, counting build ----
     restart()
@@ -283,7 +303,7 @@ def run_ours(args, cfg, pt):
         "clocks": clocks,
         "e2e": {"value": total_rays / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 2 * 1328 + 196, "d2h_bytes_per_step": W * own_rows * 12},
         "roofline": {"bound": "hbm", "kernel": "k_trace_queue (ray-queue BVH8 traversal inside FullPathTracer; per step = sum of its launches)", "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(args.workload, W, H),
                      "peak_source": peak_kind, "ms_per_launch": trace_ms, "full_path_tracer_ms": fpt_ms, "stage_ms": stage_ms,
                      "camera_rays_ms_per_launch": kernel_ms["CameraRays"] / args.steps,
                      "rays_per_launch": fpt["rays"], "nodes_per_ray": fpt["nodes"] / max(1.0, fpt["rays"]), "triangles_per_ray": fpt["triangles"] / max(1.0, fpt["rays"])},
@@ -322,6 +342,7 @@ def main():
     ap.add_argument("--sharding", default="auto", choices=["auto", "samples", "tiles"],
                     help="N > 1: sample-pass sharding (weak scaling, default for cornell) or row tiles (strong scaling; always for ReSTIR DI)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile", action="store_true", help="for ncu: run only 3 warm-up + K frames of the timed pass (no counting / stage / e2e / CPU passes), print no bench line")
     args = ap.parse_args()
 
     pt = importlib.import_module("hiprt-path-tracer_b200")

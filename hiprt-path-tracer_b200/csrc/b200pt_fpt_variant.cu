@@ -86,10 +86,13 @@ __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_bsdf)(const __grid_co
         wf_bsdf_path<PT_GGX>(rd, res, tile, wf, bounce, i);
 }
 
+#ifndef PT_PAIR_PHASES_DEFAULT
+#define PT_PAIR_PHASES_DEFAULT false
+#endif
 #if PT_LSS == 3
 // The phase kernels P1..P5 of the phased MIS pipeline live in their own translation unit (b200pt_phase_variant.cu), compiled
 // with the BSDF entry points inlined; this one launches them through launch_phase.
-enum PhaseKernel { PHASE_NEE_LIGHT_EVAL, PHASE_NEE_BSDF_SAMPLE, PHASE_ENV_LIGHT_EVAL, PHASE_ENV_BSDF_SAMPLE, PHASE_BSDF_RESOLVED };
+enum PhaseKernel { PHASE_NEE_LIGHT_EVAL, PHASE_NEE_BSDF_SAMPLE, PHASE_ENV_LIGHT_EVAL, PHASE_ENV_BSDF_SAMPLE, PHASE_BSDF_RESOLVED, PHASE_NEE_PAIR, PHASE_ENV_PAIR };
 cudaError_t PT_VARIANT_NAME(launch_phase)(int which, unsigned blocks, cudaStream_t stream, const HIPRTRenderData* rd, int2 res, Tile tile, const WavefrontState* wf, int bounce,
                                           bool lights_sampled, bool envmap_sampled);
 __global__ void __launch_bounds__(128) PT_VARIANT_NAME(k_wf_surface)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce)
@@ -191,12 +194,19 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
             const unsigned g64 = blocks(64);
             const bool lights = rd->buffers.emissive_triangles_count > 0;
             const bool envmap = PT_ESS != 0 && rd->world_settings.ambient_light_type == AMBIENT_ENVMAP;
-            if (lights)
+            // B200PT_PAIR_PHASES=1: eval + sample of a MIS pair in one kernel on one loaded vertex (one ~400-byte vertex load
+            // less per pair, twice the code per kernel); same arithmetic and RNG order, same bits
+            static const bool pair_phases = [] { const char* v = getenv("B200PT_PAIR_PHASES"); return v ? atoi(v) != 0 : PT_PAIR_PHASES_DEFAULT; }();
+            if (lights && pair_phases)
+                PT_VARIANT_NAME(launch_phase)(PHASE_NEE_PAIR, g64, stream, rd, res, tile, wf, bounce, lights, envmap);
+            else if (lights)
             {
                 PT_VARIANT_NAME(launch_phase)(PHASE_NEE_LIGHT_EVAL, g64, stream, rd, res, tile, wf, bounce, lights, envmap);
                 PT_VARIANT_NAME(launch_phase)(PHASE_NEE_BSDF_SAMPLE, g64, stream, rd, res, tile, wf, bounce, lights, envmap);
             }
-            if (envmap)
+            if (envmap && pair_phases)
+                PT_VARIANT_NAME(launch_phase)(PHASE_ENV_PAIR, g64, stream, rd, res, tile, wf, bounce, lights, envmap);
+            else if (envmap)
             {
                 PT_VARIANT_NAME(launch_phase)(PHASE_ENV_LIGHT_EVAL, g64, stream, rd, res, tile, wf, bounce, lights, envmap);
                 PT_VARIANT_NAME(launch_phase)(PHASE_ENV_BSDF_SAMPLE, g64, stream, rd, res, tile, wf, bounce, lights, envmap);

@@ -28,6 +28,11 @@ PT_QUEUE_KERNEL(k_wf_nee_light_eval, 64, 2, nee_light_eval_path)
 PT_QUEUE_KERNEL(k_wf_nee_bsdf_sample, 64, 3, nee_bsdf_sample_path<PT_GGX>)
 PT_QUEUE_KERNEL(k_wf_env_light_eval, 64, 4, env_light_eval_path<PT_ESS>)
 PT_QUEUE_KERNEL(k_wf_env_bsdf_sample, 64, 5, env_bsdf_sample_path<PT_GGX>)
+// eval + sample of a MIS pair on one loaded vertex (B200PT_PAIR_PHASES=1); they take the queue cursor of the eval phase
+#define PT_NEE_PAIR nee_pair_path<PT_GGX>
+#define PT_ENV_PAIR env_pair_path<PT_ESS, PT_GGX>
+PT_QUEUE_KERNEL(k_wf_nee_pair, 64, 2, PT_NEE_PAIR)
+PT_QUEUE_KERNEL(k_wf_env_pair, 64, 4, PT_ENV_PAIR)
 
 __global__ void __launch_bounds__(64, PT_PHASE_BLOCKS_PER_SM) PT_VARIANT_NAME(k_wf_bsdf_resolved)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce, bool lights_sampled, bool envmap_sampled)
 {
@@ -35,7 +40,7 @@ __global__ void __launch_bounds__(64, PT_PHASE_BLOCKS_PER_SM) PT_VARIANT_NAME(k_
         wf_bsdf_resolved_path<PT_ESS, PT_GGX>(rd, res, tile, wf, bounce, i, lights_sampled, envmap_sampled);
 }
 
-enum PhaseKernel { PHASE_NEE_LIGHT_EVAL, PHASE_NEE_BSDF_SAMPLE, PHASE_ENV_LIGHT_EVAL, PHASE_ENV_BSDF_SAMPLE, PHASE_BSDF_RESOLVED };
+enum PhaseKernel { PHASE_NEE_LIGHT_EVAL, PHASE_NEE_BSDF_SAMPLE, PHASE_ENV_LIGHT_EVAL, PHASE_ENV_BSDF_SAMPLE, PHASE_BSDF_RESOLVED, PHASE_NEE_PAIR, PHASE_ENV_PAIR };
 
 cudaError_t PT_VARIANT_NAME(launch_phase)(int which, unsigned blocks, cudaStream_t stream, const HIPRTRenderData* rd, int2 res, Tile tile, const WavefrontState* wf, int bounce,
                                           bool lights_sampled, bool envmap_sampled)
@@ -47,6 +52,8 @@ cudaError_t PT_VARIANT_NAME(launch_phase)(int which, unsigned blocks, cudaStream
     case PHASE_ENV_LIGHT_EVAL: PT_VARIANT_NAME(k_wf_env_light_eval)<<<blocks, 64, 0, stream>>>(*rd, res, tile, *wf, bounce); break;
     case PHASE_ENV_BSDF_SAMPLE: PT_VARIANT_NAME(k_wf_env_bsdf_sample)<<<blocks, 64, 0, stream>>>(*rd, res, tile, *wf, bounce); break;
     case PHASE_BSDF_RESOLVED: PT_VARIANT_NAME(k_wf_bsdf_resolved)<<<blocks, 64, 0, stream>>>(*rd, res, tile, *wf, bounce, lights_sampled, envmap_sampled); break;
+    case PHASE_NEE_PAIR: PT_VARIANT_NAME(k_wf_nee_pair)<<<blocks, 64, 0, stream>>>(*rd, res, tile, *wf, bounce); break;
+    case PHASE_ENV_PAIR: PT_VARIANT_NAME(k_wf_env_pair)<<<blocks, 64, 0, stream>>>(*rd, res, tile, *wf, bounce); break;
     default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();

@@ -86,13 +86,8 @@ PT_DEV void nee_load_vertex(const HIPRTRenderData& rd, const WavefrontState& wf,
 PT_DEV void nee_store_rng(const WavefrontState& wf, uint32_t slot, const Rng& rng) { wf.origin_rng[slot].w = __uint_as_float(rng.state); }
 
 // ---- P1: light sample + BSDF eval (sample_one_light_MIS, first half: Lights.h:115-170) ------------------------------------
-PT_DEV void nee_light_eval_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
+PT_DEV void nee_light_eval_body(const HIPRTRenderData& rd, const WavefrontState& wf, int bounce, uint32_t slot, PathRegs& p)
 {
-    const uint32_t slot = wf.sorted_queue[i];
-    uint32_t x, y, pixel_index;
-    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
-    PathRegs p;
-    nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
     nee_store_none(wf, NEE_LIGHT, slot);
     // ray 1 doubles as the "P2 has work" flag: t_max = -2 tells P2 to skip its BSDF sample (light pdf <= 0: the
     // reference returns before sampling the BSDF, Lights.h:127-128)
@@ -138,15 +133,8 @@ PT_DEV void nee_light_eval_path(const HIPRTRenderData& rd, int2 res, const Tile&
 
 // ---- P2: BSDF sample of the light MIS pair (Lights.h:172-190) ----------------------------------------------------------------
 template <int GGX_SAMPLER>
-PT_DEV void nee_bsdf_sample_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
+PT_DEV void nee_bsdf_sample_body(const HIPRTRenderData& rd, const WavefrontState& wf, int bounce, uint32_t slot, PathRegs& p)
 {
-    const uint32_t slot = wf.sorted_queue[i];
-    if (wf.nee_ray_o[nee_index(wf, NEE_LIGHT_BSDF, slot)].w != -1.0f)
-        return;
-    uint32_t x, y, pixel_index;
-    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
-    PathRegs p;
-    nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
 
     const float3 view_direction = -p.direction;
     const HitInfo& hit = p.hit;
@@ -173,13 +161,8 @@ PT_DEV void nee_bsdf_sample_path(const HIPRTRenderData& rd, int2 res, const Tile
 
 // ---- P3: envmap sample + BSDF eval (sample_environment_map_with_mis, first half: Envmap.h:151-185) ---------------------------
 template <int ESS>
-PT_DEV void env_light_eval_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
+PT_DEV void env_light_eval_body(const HIPRTRenderData& rd, const WavefrontState& wf, int bounce, uint32_t slot, PathRegs& p)
 {
-    const uint32_t slot = wf.sorted_queue[i];
-    uint32_t x, y, pixel_index;
-    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
-    PathRegs p;
-    nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
     nee_store_none(wf, NEE_ENV, slot);
     wf.nee_ray_o[nee_index(wf, NEE_ENV_BSDF, slot)] = make_float4(0.0f, 0.0f, 0.0f, -2.0f);
     if (!envmap_prelude<ESS>(rd, p.payload.material))
@@ -207,15 +190,8 @@ PT_DEV void env_light_eval_path(const HIPRTRenderData& rd, int2 res, const Tile&
 
 // ---- P4: BSDF sample of the envmap MIS pair (Envmap.h:187-215) ----------------------------------------------------------------
 template <int GGX_SAMPLER>
-PT_DEV void env_bsdf_sample_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
+PT_DEV void env_bsdf_sample_body(const HIPRTRenderData& rd, const WavefrontState& wf, int bounce, uint32_t slot, PathRegs& p)
 {
-    const uint32_t slot = wf.sorted_queue[i];
-    if (wf.nee_ray_o[nee_index(wf, NEE_ENV_BSDF, slot)].w != -1.0f)
-        return;
-    uint32_t x, y, pixel_index;
-    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
-    PathRegs p;
-    nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
 
     const float3 view_direction = -p.direction;
     const HitInfo& hit = p.hit;
@@ -237,6 +213,83 @@ PT_DEV void env_bsdf_sample_path(const HIPRTRenderData& rd, int2 res, const Tile
             nee_store(wf, bounce, NEE_ENV_BSDF, slot, hit.inter_point, 1.0e35f, bsdf_sampled_dir, hit.primitive_index, bsdf_mis_contribution, 0.0f);
         }
     }
+}
+
+// ---- kernel bodies: one phase per kernel, or an eval + sample pair on one loaded vertex ---------------------------------------------
+// A phase that has work loads the vertex (ray, hit, 256-byte material: ~400 bytes); the paired forms load it once for both halves.
+// The sample half runs only where the eval half left its flag (t_max = -1 in the pair's second ray record); it continues from the
+// Xorshift32 state the eval half stored, which is the state already in p.
+PT_DEV void nee_light_eval_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
+{
+    const uint32_t slot = wf.sorted_queue[i];
+    uint32_t x, y, pixel_index;
+    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    PathRegs p;
+    nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
+    nee_light_eval_body(rd, wf, bounce, slot, p);
+}
+
+template <int GGX_SAMPLER>
+PT_DEV void nee_bsdf_sample_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
+{
+    const uint32_t slot = wf.sorted_queue[i];
+    if (wf.nee_ray_o[nee_index(wf, NEE_LIGHT_BSDF, slot)].w != -1.0f)
+        return;
+    uint32_t x, y, pixel_index;
+    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    PathRegs p;
+    nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
+    nee_bsdf_sample_body<GGX_SAMPLER>(rd, wf, bounce, slot, p);
+}
+
+template <int ESS>
+PT_DEV void env_light_eval_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
+{
+    const uint32_t slot = wf.sorted_queue[i];
+    uint32_t x, y, pixel_index;
+    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    PathRegs p;
+    nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
+    env_light_eval_body<ESS>(rd, wf, bounce, slot, p);
+}
+
+template <int GGX_SAMPLER>
+PT_DEV void env_bsdf_sample_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
+{
+    const uint32_t slot = wf.sorted_queue[i];
+    if (wf.nee_ray_o[nee_index(wf, NEE_ENV_BSDF, slot)].w != -1.0f)
+        return;
+    uint32_t x, y, pixel_index;
+    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    PathRegs p;
+    nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
+    env_bsdf_sample_body<GGX_SAMPLER>(rd, wf, bounce, slot, p);
+}
+
+template <int GGX_SAMPLER>
+PT_DEV void nee_pair_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
+{
+    const uint32_t slot = wf.sorted_queue[i];
+    uint32_t x, y, pixel_index;
+    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    PathRegs p;
+    nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
+    nee_light_eval_body(rd, wf, bounce, slot, p);
+    if (wf.nee_ray_o[nee_index(wf, NEE_LIGHT_BSDF, slot)].w == -1.0f)
+        nee_bsdf_sample_body<GGX_SAMPLER>(rd, wf, bounce, slot, p);
+}
+
+template <int ESS, int GGX_SAMPLER>
+PT_DEV void env_pair_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
+{
+    const uint32_t slot = wf.sorted_queue[i];
+    uint32_t x, y, pixel_index;
+    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    PathRegs p;
+    nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
+    env_light_eval_body<ESS>(rd, wf, bounce, slot, p);
+    if (wf.nee_ray_o[nee_index(wf, NEE_ENV_BSDF, slot)].w == -1.0f)
+        env_bsdf_sample_body<GGX_SAMPLER>(rd, wf, bounce, slot, p);
 }
 
 // ---- P5: finish shade_vertex_direct from the traced NEE rays (FullPathTracer.h:195-214), then shade_vertex_bounce --------------
