@@ -283,6 +283,8 @@ int b200pt_launch_FullPathTracer_lane(b200pt_ctx* ctx, const HIPRTRenderData* re
             if (rc != B200PT_SUCCESS)
                 return rc;
             ctx->wf[lane].grid_share = (uint32_t)lane_count;
+            static const bool slot_materials = [] { const char* v = getenv("B200PT_SLOT_MATERIALS"); return v && atoi(v) != 0; }();
+            ctx->wf[lane].force_slot_materials = slot_materials ? 1u : 0u;
         }
     }
     if (ctx->profiling && lane_count > 1)

@@ -16,6 +16,7 @@ struct HitInfo
     float2 uv;
     float t;
     int primitive_index;
+    int material_ref;       // trace_ray: material index + 1 when the material has no texture override (plain_intersection_material), else 0
 };
 
 struct RayPayload
@@ -162,7 +163,7 @@ PT_DEV_NOINLINE bool trace_ray_from(const HIPRTRenderData& rd, float3 origin, fl
             payload.volume_state.distance_in_volume += hit.t;
 
         int material_index = __ldg(rd.buffers.material_indices + hit.prim);
-        get_intersection_material(rd, material_index, out.texcoords, payload.material);
+        out.material_ref = get_intersection_material(rd, material_index, out.texcoords, payload.material) ? material_index + 1 : 0;
 
         if ((!is_inside_volume(payload.volume_state) || payload.material.specular_transmission == 0.0f) && !payload.material.thin_walled)
         {

@@ -48,6 +48,7 @@ struct WavefrontState
     uint32_t grid_share;     // how many FullPathTracer launches share the device at the same time (path lanes, >= 1): grids are sized 1/share
     uint32_t capacity;       // paths
     uint32_t max_bounces;    // counts holds 2 * (max_bounces + 2) entries
+    uint32_t force_slot_materials;   // debug (B200PT_SLOT_MATERIALS=1): every hit writes its 256-byte material to the slot (wf_store_hit)
 };
 
 #ifdef PT_COUNTERS

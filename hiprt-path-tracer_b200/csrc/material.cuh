@@ -91,14 +91,48 @@ PT_DEV float base_color_alpha(const HIPRTRenderData& rd, int material_index, flo
     return sample_tex2d_rgba(material_texture(rd, tex), texcoords, true).a;
 }
 
-// get_intersection_material (Material.h:47-96)
-PT_DEV_NOINLINE void get_intersection_material(const HIPRTRenderData& rd, int material_index, float2 texcoords, Material& out)
+// Coat roughening of the base and second-metal roughness (Material.h:87-93) and the emissive-texture flag (:82)
+PT_DEV void finish_intersection_material(Material& out, int emission_texture_index)
+{
+    out.emissive_texture_used = emission_texture_index > 0;   // reference quirk: index 0 does not count (Material.h:82)
+
+    float coat = out.coat;
+    float target_base = pow_1_4(minf(1.0f, pow_4(out.roughness) + 2.0f * pow_4(out.coat_roughness)));
+    float roughened_base = lerpf(out.roughness, target_base, coat);
+    out.roughness = lerpf(out.roughness, roughened_base, out.coat_roughening);
+
+    float target_second = pow_1_4(minf(1.0f, pow_4(out.second_roughness) + 2.0f * pow_4(out.coat_roughness)));
+    float roughened_second = lerpf(out.second_roughness, target_second, coat);
+    out.second_roughness = lerpf(out.second_roughness, roughened_second, out.coat_roughening);
+}
+
+// get_intersection_material for a material WITHOUT texture overrides (none of the 18 parameter textures; the normal map is
+// applied to the shading normal elsewhere): a function of the material buffer entry alone -- no texcoords, no hit. The
+// wavefront keeps only the material INDEX of such a vertex in the path state and its kernels call this where they load the
+// vertex (the inlined copy lets the compiler fetch just the fields a kernel reads, from a buffer that lives in L1/L2),
+// instead of writing the 256-byte material to the slot and reading it back in every phase.
+PT_DEV void plain_intersection_material(const HIPRTRenderData& rd, int material_index, Material& out)
 {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(material_ptr(rd, material_index));
     uint32_t* dst = reinterpret_cast<uint32_t*>(&out);
 #pragma unroll
     for (int i = 0; i < (int)(sizeof(Material) / 4); i++)
         dst[i] = __ldg(src + i);
+    const int emission_texture_index = __ldg(reinterpret_cast<const int*>(src) + sizeof(Material) / 4 + 1);
+    // The reference always round-trips the emission through '/ strength' and get_emission() multiplies again;
+    // keep the division so that a zero strength yields the same NaN/Inf pattern as the oracle.
+    RGB emission = material_emission(out) / out.emission_strength;
+    set_rgb(out.emission, emission);
+    if (rd.bsdfs_data.white_furnace_mode)
+        set_rgb(out.base_color, RGB(1.0f));
+    finish_intersection_material(out, emission_texture_index);
+}
+
+// get_intersection_material (Material.h:47-96). Returns true when the material has no texture override (see above).
+PT_DEV_NOINLINE bool get_intersection_material(const HIPRTRenderData& rd, int material_index, float2 texcoords, Material& out)
+{
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(material_ptr(rd, material_index));
+    uint32_t* dst = reinterpret_cast<uint32_t*>(&out);
 
     int tex[19];
 #pragma unroll
@@ -111,8 +145,15 @@ PT_DEV_NOINLINE void get_intersection_material(const HIPRTRenderData& rd, int ma
 #pragma unroll
     for (int i = 1; i < 19; i++)
         any_texture |= has_texture(tex[i]);
+    if (!any_texture)
+    {
+        plain_intersection_material(rd, material_index, out);
+        return true;
+    }
 
-    if (any_texture)
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(Material) / 4); i++)
+        dst[i] = __ldg(src + i);
     {
         // emission = get_emission() / emission_strength, overridden by the emission texture
         RGB emission = material_emission(out) / out.emission_strength;
@@ -121,13 +162,6 @@ PT_DEV_NOINLINE void get_intersection_material(const HIPRTRenderData& rd, int ma
             RGBA c = sample_tex2d_rgba(material_texture(rd, tex[1]), texcoords, false);
             emission = RGB(c.r, c.g, c.b);
         }
-        set_rgb(out.emission, emission);
-    }
-    else
-    {
-        // The reference always round-trips the emission through '/ strength' and get_emission() multiplies again;
-        // keep the division so that a zero strength yields the same NaN/Inf pattern as the oracle.
-        RGB emission = material_emission(out) / out.emission_strength;
         set_rgb(out.emission, emission);
     }
 
@@ -139,7 +173,6 @@ PT_DEV_NOINLINE void get_intersection_material(const HIPRTRenderData& rd, int ma
         set_rgb(out.base_color, RGB(c.r, c.g, c.b));
     }
 
-    if (any_texture)
     {
         if (tex[3] != B200PT_NO_TEXTURE)
         {
@@ -167,17 +200,8 @@ PT_DEV_NOINLINE void get_intersection_material(const HIPRTRenderData& rd, int ma
         texture_override_f(rd, out.specular_transmission, texcoords, tex[18]);
     }
 
-    out.emissive_texture_used = tex[1] > 0;   // reference quirk: index 0 does not count (Material.h:82)
-
-    // Coat roughening of the base and second-metal roughness (Material.h:87-93)
-    float coat = out.coat;
-    float target_base = pow_1_4(minf(1.0f, pow_4(out.roughness) + 2.0f * pow_4(out.coat_roughness)));
-    float roughened_base = lerpf(out.roughness, target_base, coat);
-    out.roughness = lerpf(out.roughness, roughened_base, out.coat_roughening);
-
-    float target_second = pow_1_4(minf(1.0f, pow_4(out.second_roughness) + 2.0f * pow_4(out.coat_roughness)));
-    float roughened_second = lerpf(out.second_roughness, target_second, coat);
-    out.second_roughness = lerpf(out.second_roughness, roughened_second, out.coat_roughening);
+    finish_intersection_material(out, tex[1]);
+    return false;
 }
 
 // ---- interior stack (ISS_WITH_PRIORITIES, stack size 3) ---------------------------------------

@@ -115,10 +115,16 @@ PT_DEV void wf_store_hit(const WavefrontState& wf, uint32_t slot, const PathRegs
 {
     wf.origin_rng[slot].w = __uint_as_float(p.rng.state);          // trace_ray may have drawn a wavelength
     wf.hit_point[slot] = make_float4(p.hit.inter_point.x, p.hit.inter_point.y, p.hit.inter_point.z, __int_as_float(p.hit.primitive_index));
-    wf.hit_ns[slot] = make_float4(p.hit.shading_normal.x, p.hit.shading_normal.y, p.hit.shading_normal.z, 0.0f);
+    // A material without texture overrides is a function of its index alone: the slot keeps the index (in the spare word of
+    // the shading normal) and the shading kernels rebuild it from the material buffer (L1/L2 resident) where they load the
+    // vertex; only textured hits write their 256-byte material to the slot. B200PT_SLOT_MATERIALS=1 (a debug switch read by
+    // the launcher into wf.force_slot_materials) restores the copy for every hit.
+    const int material_ref = wf.force_slot_materials ? 0 : p.hit.material_ref;
+    wf.hit_ns[slot] = make_float4(p.hit.shading_normal.x, p.hit.shading_normal.y, p.hit.shading_normal.z, __int_as_float(material_ref));
     wf.hit_ng[slot] = make_float4(p.hit.geometric_normal.x, p.hit.geometric_normal.y, p.hit.geometric_normal.z, 0.0f);
     copy_volume_state(reinterpret_cast<RayVolumeState*>(wf.volume + (size_t)slot * 9), &p.payload.volume_state);
-    store_material(reinterpret_cast<SimplifiedRendererMaterial*>(wf.materials) + slot, p.payload.material);
+    if (material_ref == 0)
+        store_material(reinterpret_cast<SimplifiedRendererMaterial*>(wf.materials) + slot, p.payload.material);
 }
 
 // The surface a path is shaded at: bounce 0 reads the camera hit straight from the G-buffer (FullPathTracer.h:136-151,
@@ -139,7 +145,11 @@ PT_DEV void wf_load_hit(const HIPRTRenderData& rd, const WavefrontState& wf, uin
     p.hit.primitive_index = __float_as_int(hp.w);
     p.hit.shading_normal = f3(ns.x, ns.y, ns.z);
     p.hit.geometric_normal = f3(ng.x, ng.y, ng.z);
-    load_material(p.payload.material, reinterpret_cast<const SimplifiedRendererMaterial*>(wf.materials) + slot);
+    const int material_ref = __float_as_int(ns.w);
+    if (material_ref > 0)
+        plain_intersection_material(rd, material_ref - 1, p.payload.material);
+    else
+        load_material(p.payload.material, reinterpret_cast<const SimplifiedRendererMaterial*>(wf.materials) + slot);
 }
 
 PT_DEV int wf_nb_bounces(const HIPRTRenderData& rd)
