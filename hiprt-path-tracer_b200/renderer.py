@@ -254,6 +254,21 @@ class GPURenderer:
     def device_pointer(self, name):
         return self.host.b200pt_renderer_device_pointer(self.handle, C.c_int(DOWNLOAD[name][0]))
 
+    def tonemap(self, gamma=2.2, exposure=1.0, flip_y=False):
+        """Headless output (the reference's main.cpp:91-97: cpu_renderer.tonemap(2.2f, 1.0f), then write_image_png): the accumulated
+        frame tone-mapped on the device (b200pt_tonemap). Returns ([H, W, 3] float32, [H, W, 3] uint8)."""
+        self.synchronize()
+        ctx, n = self.ctx, self.width * self.height
+        d_float, d_u8 = ctx.malloc(n * 12), ctx.malloc(n * 3)
+        try:
+            samples = int(self.render_settings.sample_number) if self.render_settings.accumulate else 0
+            _capi.check(ctx.lib.b200pt_tonemap(ctx.handle, C.c_void_p(self.device_pointer("pixels")), C.c_int(self.width), C.c_int(self.height), C.c_int(samples),
+                                               C.c_float(gamma), C.c_float(exposure), C.c_int(int(flip_y)), d_float, d_u8, None), "b200pt_tonemap")
+            return ctx.download(d_float, (self.height, self.width, 3), np.float32), ctx.download(d_u8, (self.height, self.width, 3), np.uint8)
+        finally:
+            ctx.free(d_float)
+            ctx.free(d_u8)
+
     def download(self, name):
         which, dtype, comps = DOWNLOAD[name]
         n = self.width * self.height

@@ -166,6 +166,14 @@ B200PT_API int b200pt_launch_ReSTIR_DI_SpatiotemporalReuse(b200pt_ctx* ctx, cons
 B200PT_API int b200pt_launch_ReSTIR_DI_TemporalReuse(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream);
 B200PT_API int b200pt_launch_ReSTIR_DI_SpatialReuse(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream);
 
+/* ---- headless output (replaces the GL display path) ------------------------------------------------ */
+/* Replaces CPURenderer::tonemap (src/Renderer/CPURenderer.cpp:663-686) / Utils::tonemap_hdr_image (src/Utils/Utils.cpp:35-52):
+ * out = pow(1 - exp(-(hdr / sample_number) * exposure), 1 / gamma) per channel; sample_number <= 0 = no scaling (not accumulating).
+ * d_out_rgb_float (W*H*3 floats; may alias d_hdr_rgb when flip_y is 0) and/or d_out_rgb8 (W*H*3 bytes, quantised like
+ * Image32Bit::write_image_png, src/Image/Image.cpp:427-437: clamp(0, 255, v * 255) truncated); flip_y writes row H-1-y. */
+B200PT_API int b200pt_tonemap(b200pt_ctx* ctx, const float* d_hdr_rgb, int width, int height, int sample_number, float gamma, float exposure, int flip_y,
+                              float* d_out_rgb_float, unsigned char* d_out_rgb8, b200pt_stream stream);
+
 /* ---- ray batches: the traversal core on its own (parity pins on hit ids; roofline measurement) ------------------ */
 /* rays: n x 6 floats (origin, direction) on the device. last_prim: n ints or NULL (-1). Outputs on the device. */
 B200PT_API int b200pt_trace_closest(b200pt_ctx* ctx, b200pt_bvh* bvh, const float* d_rays, const int* d_last_prim, long long n, int* d_out_prim, float* d_out_t, float* d_out_uv, b200pt_stream stream);

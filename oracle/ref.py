@@ -119,6 +119,13 @@ class RefRenderer:
         self.lib.ref_get_pixels(self.h, _p(out))
         return out
 
+    def tonemap(self, gamma=2.2, exposure=1.0):
+        """CPURenderer::tonemap + the 8-bit quantisation of write_image_png (ref_harness_passes.inl: ref_tonemap)."""
+        f = np.empty((self.height, self.width, 3), np.float32)
+        u = np.empty((self.height, self.width, 3), np.uint8)
+        self.lib.ref_tonemap(self.h, C.c_float(gamma), C.c_float(exposure), _p(f), _p(u))
+        return f, u
+
     def buffer(self, name):
         which, dtype, comps = BUFFERS[name]
         n = -self.lib.ref_get_buffer(self.h, C.c_int(which), None, C.c_longlong(0))

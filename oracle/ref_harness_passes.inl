@@ -204,6 +204,29 @@ long long ref_get_buffer(void* h, int which, void* out, long long capacity_bytes
     return (long long)bytes;
 }
 
+// CPURenderer::tonemap (src/Renderer/CPURenderer.cpp:663-686) on a copy of the accumulation buffer, with the reference's own
+// ColorRGB32F exp / pow (HostDeviceCommon/Color.h), then the 8-bit quantisation of Image32Bit::write_image_png
+// (src/Image/Image.cpp:427-437: clamp(0, 255, v * 255) truncated to unsigned char). out_float / out_u8: W*H*3 each, may be null.
+void ref_tonemap(void* h, float gamma, float exposure, float* out_float, unsigned char* out_u8)
+{
+    RefCtx* c = reinterpret_cast<RefCtx*>(h);
+    const size_t n = c->pixels.size();
+    for (size_t index = 0; index < n; index++)
+    {
+        ColorRGB32F hdr_color = c->pixels[index];
+        if (c->rd.render_settings.accumulate)
+            hdr_color = hdr_color / float(c->rd.render_settings.sample_number);
+        ColorRGB32F tone_mapped = ColorRGB32F(1.0f) - exp(-hdr_color * exposure);
+        tone_mapped = pow(tone_mapped, 1.0f / gamma);
+        const float v[3] = {tone_mapped.r, tone_mapped.g, tone_mapped.b};
+        for (int k = 0; k < 3; k++)
+        {
+            if (out_float) out_float[index * 3 + k] = v[k];
+            if (out_u8) out_u8[index * 3 + k] = (unsigned char)hippt::clamp(0.0f, 255.0f, v[k] * 255.0f);
+        }
+    }
+}
+
 unsigned long long ref_ray_count() { return g_ray_count.load(); }
 void ref_ray_count_reset() { g_ray_count.store(0); }
 

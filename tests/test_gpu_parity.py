@@ -357,6 +357,68 @@ def test_restir_di_extra_spatial_pass_after_fused(pt, wl, ctx):
     assert abs(means[0] - means[1]) / means[0] < 0.02, means
 
 
+def test_tonemap_and_headless_png_parity(pt, wl, ctx, ref, tmp_path):
+    """SURVEY 8f rank 3: the headless output path. b200pt_tonemap against CPURenderer::tonemap + write_image_png's quantisation
+    (the reference's own ColorRGB32F exp / pow through the oracle harness) on the same accumulated frame, then the PNG written
+    from it decodes to the same bytes. expf / powf differ by an ulp between glibc and CUDA: floats within 2e-6, and an 8-bit
+    value may land on the other side of a truncation boundary in a handful of pixels (never by more than 1)."""
+    io = importlib.import_module("hiprt-path-tracer_b200.image_io")
+    cfg = wl.cornell(160, 96)
+    r = wl.setup_oracle(ref, pt.structs, cfg)
+    g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="cpu")
+    try:
+        spp = 3
+        r.render(spp)
+        for _ in range(spp):
+            g.render_frame()
+        g.synchronize()
+        want_f, want_u8 = r.tonemap(2.2, 1.0)
+        got_f, got_u8 = g.tonemap(2.2, 1.0)
+        assert np.abs(want_f - got_f).max() < 2e-5            # includes the ~1e-7 relative difference of the frames themselves
+        d = np.abs(want_u8.astype(np.int32) - got_u8.astype(np.int32))
+        assert d.max() <= 1 and (d != 0).mean() < 2e-3, (d.max(), (d != 0).mean())
+        assert got_u8.max() > 200 and got_u8.min() < 30       # a real image, not a constant
+        flipped_f, flipped_u8 = g.tonemap(2.2, 1.0, flip_y=True)
+        assert np.array_equal(flipped_u8, got_u8[::-1]) and np.array_equal(flipped_f, got_f[::-1])
+        path = os.path.join(tmp_path, "cornell.png")
+        io.write_png(path, got_u8)
+        assert np.array_equal(io.read_png(path), got_u8)
+    finally:
+        g.close()
+
+
+def test_column_tile_sharding_is_bit_identical(pt, wl, ctx):
+    """The strong-scaling shard shape of config C3 (bench.py --sharding columns) on one device: three renderers own three column
+    bands of the envmap scene; the union of their accumulation buffers equals the unsharded render bit for bit."""
+    mg = importlib.import_module("hiprt-path-tracer_b200.multigpu")
+    W, H, frames = 200, 96, 3
+    cfg = wl.synthetic_small(W, H)
+    whole = wl.setup_gpu(pt, ctx, cfg, seed_schedule="cpu")
+    try:
+        for _ in range(frames):
+            whole.render_frame()
+        whole.synchronize()
+        want = whole.download("pixels").reshape(H, W, 3).copy()
+    finally:
+        whole.close()
+    tiles = mg.column_tiles(W, 3)
+    assert tiles == [(0, 64), (64, 128), (128, 200)]
+    got = np.zeros_like(want)
+    for x0, x1 in tiles:
+        g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="cpu")
+        try:
+            g.set_tile((x0, 0, x1, H))
+            for _ in range(frames):
+                g.render_frame()
+            g.synchronize()
+            band = g.download("pixels").reshape(H, W, 3)
+            assert not band[:, :x0].any() and not band[:, x1:].any()      # a rank writes only its own columns
+            got[:, x0:x1] = band[:, x0:x1]
+        finally:
+            g.close()
+    assert np.array_equal(got, want)
+
+
 def test_restir_di_tile_sharding_with_halo_is_bit_identical(pt, wl, ctx):
     """The multi-GPU shard shape of config C4 on one device: two renderers own the two halves of the image, each runs CameraRays
     over tile + 20 halo rows, and after every frame only the output reservoirs of the halo rows are copied across (what

@@ -78,6 +78,15 @@ def _worker(rank, world, port, height, width, halo, result_queue):
         mg.gather_rows(dist, torch.from_numpy(frame), tiles)
         ok_gather = bool(np.array_equal(frame, full[:, :width * 12]))
 
+        # --- column tiles: the same through a strided band ---
+        ctiles = mg.column_tiles(width, world)
+        x0, x1 = ctiles[rank]
+        want_image = rng.random((height, width, 3), dtype=np.float32)
+        image = np.zeros_like(want_image)
+        image[:, x0:x1] = want_image[:, x0:x1]
+        mg.gather_columns(dist, torch.from_numpy(image), ctiles)
+        ok_gather = ok_gather and bool(np.array_equal(image, want_image))
+
         # --- sample-pass sharding: accumulation buffers summed ---
         pixels = torch.full((height, width, 3), float(rank + 1))
         lum = torch.full((height, width), 0.5 * (rank + 1))
