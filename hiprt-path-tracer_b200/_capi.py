@@ -8,8 +8,10 @@ import os
 from . import structs as S
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libb200pt.so")
-HOST_LIB_PATH = os.path.join(HERE, "libb200pt_host.so")
+# B200PT_LIB_DIR: a directory holding another build of BOTH libraries (tools/trace_sweep.sh puts tuning variants there)
+LIB_DIR = os.environ.get("B200PT_LIB_DIR") or HERE
+LIB_PATH = os.path.join(LIB_DIR, "libb200pt.so")
+HOST_LIB_PATH = os.path.join(LIB_DIR, "libb200pt_host.so")
 
 
 class B200ptError(RuntimeError):

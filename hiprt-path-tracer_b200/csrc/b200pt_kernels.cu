@@ -48,20 +48,26 @@ __global__ void PT_SUFFIXED(k_trace_shadow)(Bvh8Device bvh, const float* __restr
 }
 
 template <bool ANY_HIT>
-__global__ void __launch_bounds__(kTraceBlock, kTraceBlocksPerSM) PT_SUFFIXED(k_trace_queue)(const Bvh8Device* __restrict__ bvh, const __grid_constant__ RayQueueView q, TraversalCounters* counters)
+__global__ void __launch_bounds__(kTraceBlock, kTraceBlocksPerSM) PT_SUFFIXED(k_trace_queue)(const Bvh8Device* __restrict__ bvh, const __grid_constant__ RayQueueView q, TraversalCounters* counters,
+                                                                                             unsigned refill_idle_lanes, int triangle_postpone_below)
 {
     __shared__ uint2 shared_stack[kSharedStackEntries * kTraceBlock];
     const Bvh8Device b = *bvh;
-    trace_queue_body<ANY_HIT>(b, q, shared_stack, counters);
+    trace_queue_body<ANY_HIT>(b, q, shared_stack, counters, refill_idle_lanes, triangle_postpone_below);
 }
 
 cudaError_t PT_SUFFIXED(launch_trace_queue)(const void* bvh_device_handle, const RayQueueView& q, bool any_hit, unsigned blocks, TraversalCounters* counters, cudaStream_t stream)
 {
     const Bvh8Device* bvh = reinterpret_cast<const Bvh8Device*>(bvh_device_handle);
+    // scheduling knobs of the kernel (trace_queue.cuh), overridable for sweeps (tools/trace_sweep.sh); results do not depend on them
+    static const unsigned refill = [] { const char* v = getenv("B200PT_TRACE_REFILL_IDLE"); int n = v ? atoi(v) : 0; return n > 0 && n <= 32 ? (unsigned)n : kRefillIdleLanes; }();
+    static const int postpone = [] { const char* v = getenv("B200PT_TRACE_TRI_POSTPONE"); int n = v ? atoi(v) : 0; return n > 0 && n <= 32 ? n : kTrianglePostponeBelow; }();
+    static const unsigned block_scale_pct = [] { const char* v = getenv("B200PT_TRACE_GRID_PCT"); int n = v ? atoi(v) : 0; return n > 0 ? (unsigned)n : 100u; }();
+    blocks = blocks * block_scale_pct / 100u > 0u ? blocks * block_scale_pct / 100u : 1u;
     if (any_hit)
-        PT_SUFFIXED(k_trace_queue)<true><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters);
+        PT_SUFFIXED(k_trace_queue)<true><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters, refill, postpone);
     else
-        PT_SUFFIXED(k_trace_queue)<false><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters);
+        PT_SUFFIXED(k_trace_queue)<false><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters, refill, postpone);
     return cudaGetLastError();
 }
 

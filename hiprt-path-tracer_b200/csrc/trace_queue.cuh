@@ -22,11 +22,24 @@
 
 namespace pt
 {
-constexpr int kSharedStackEntries = 8;
+// Tunables (-D overrides exist for the sweeps of tools/trace_sweep.sh; the defaults are the measured best)
+#ifndef PT_TRACE_SHARED_STACK
+#define PT_TRACE_SHARED_STACK 8
+#endif
+#ifndef PT_TRACE_BLOCKS_PER_SM
+#define PT_TRACE_BLOCKS_PER_SM 7
+#endif
+#ifndef PT_TRACE_REFILL_IDLE
+#define PT_TRACE_REFILL_IDLE 4
+#endif
+#ifndef PT_TRACE_TRI_POSTPONE
+#define PT_TRACE_TRI_POSTPONE 8
+#endif
+constexpr int kSharedStackEntries = PT_TRACE_SHARED_STACK;
 constexpr int kTraceBlock = 128;
-constexpr int kTraceBlocksPerSM = 7;         // 72 registers per thread; 64 (8 blocks) measured no faster
-constexpr unsigned kRefillIdleLanes = 4;     // refill as soon as this many lanes of a warp have no ray
-constexpr int kTrianglePostponeBelow = 8;    // triangles are tested when at least this many lanes of the warp have one pending
+constexpr int kTraceBlocksPerSM = PT_TRACE_BLOCKS_PER_SM;         // 72 registers per thread; 64 (8 blocks) measured no faster
+constexpr unsigned kRefillIdleLanes = PT_TRACE_REFILL_IDLE;       // refill as soon as this many lanes of a warp have no ray
+constexpr int kTrianglePostponeBelow = PT_TRACE_TRI_POSTPONE;     // triangles are tested when at least this many lanes of the warp have one pending
 
 // 1 + byte * 2^-15, exactly: the byte lands in mantissa bits 8..15 of 1.0f with one PRMT (result bytes, low to high:
 // 0x00, byte j of word, 0x80, 0x3F). The slab test then evaluates plane = (1 + q 2^-15) * (2^15 a) + (o - 2^15 a), the same
@@ -53,7 +66,8 @@ PT_DEV void prefetch_global(const void* p)
 }
 
 template <bool ANY_HIT>
-__device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const RayQueueView& q, uint2* shared_stack, TraversalCounters* counters)
+__device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const RayQueueView& q, uint2* shared_stack, TraversalCounters* counters,
+                                                 const unsigned refill_idle_lanes = kRefillIdleLanes, const int triangle_postpone_below = kTrianglePostponeBelow)
 {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t n = *q.count;
@@ -78,7 +92,7 @@ __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const Ra
     {
         // ---- refill: lanes without a ray take the next queue entries -------------------------------------------------
         const unsigned idle_mask = __ballot_sync(0xFFFFFFFFu, !active);
-        if (!exhausted && (__popc(idle_mask) >= kRefillIdleLanes || idle_mask == 0xFFFFFFFFu))
+        if (!exhausted && (__popc(idle_mask) >= refill_idle_lanes || idle_mask == 0xFFFFFFFFu))
         {
             uint32_t base = 0;
             if (lane == (uint32_t)(__ffs((int)idle_mask) - 1))
@@ -216,7 +230,7 @@ __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const Ra
         // One triangle per lane, and only when enough lanes of the warp have one: the triangle code runs with fuller warps
         // while the other lanes' triangle work waits (their node work goes on).
         const unsigned triangle_lanes = __ballot_sync(active_mask, tgroup.y != 0u);
-        if (tgroup.y != 0u && __popc(triangle_lanes) >= min(kTrianglePostponeBelow, __popc(active_mask)))
+        if (tgroup.y != 0u && __popc(triangle_lanes) >= min(triangle_postpone_below, __popc(active_mask)))
         {
             const uint32_t tbit = (uint32_t)__ffs((int)tgroup.y) - 1u;
             tgroup.y &= tgroup.y - 1u;
