@@ -115,7 +115,7 @@ def run_ours(args, cfg, pt):
     W, H = cfg["width"], cfg["height"]
     mg = importlib.import_module("hiprt-path-tracer_b200.multigpu")
     restir = cfg["options"]["lss"] == "restir_di"
-    sharding = args.sharding if args.sharding != "auto" else ("samples" if args.workload == "cornell" else "columns")
+    sharding = args.sharding if args.sharding != "auto" else ("samples" if args.workload in ("cornell", "adaptive") else "columns")
     if restir:
         sharding = "tiles"              # reservoirs are per pixel and per frame: ReSTIR DI shards by row tiles + halo only
     tiles = mg.column_tiles(W, world) if sharding == "columns" else mg.row_tiles(H, world)
@@ -246,6 +246,12 @@ def run_ours(args, cfg, pt):
             mg.gather_columns(dist, pixels, tiles)
         else:
             mg.reduce_accumulation(dist, pixels)
+        if sharding == "samples" and cfg["settings"].get("enable_adaptive_sampling"):
+            # adaptive sampling decides on global statistics (AdaptiveSampling.h:30-104): its two buffers are summed as well
+            lum = mg.device_array(g.device_pointer("pixel_squared_luminance"), (H, W), "<f4", device)
+            cnt = mg.device_array(g.device_pointer("pixel_sample_count"), (H, W), "<i4", device)
+            dist.all_reduce(lum, op=dist.ReduceOp.SUM)
+            dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
         t1.record()
         torch.cuda.synchronize()
         reduce_ms = t0.elapsed_time(t1)

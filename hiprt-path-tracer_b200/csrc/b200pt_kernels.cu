@@ -47,13 +47,13 @@ __global__ void PT_SUFFIXED(k_trace_shadow)(Bvh8Device bvh, const float* __restr
     out_occluded[i] = bvh8_trace<true>(bvh, o, d, t_max[i] - 1.0e-4f, last_prim ? last_prim[i] : -1, hit, counters) ? 1 : 0;
 }
 
-template <bool ANY_HIT>
+template <bool ANY_HIT, bool POSTPONE>
 __global__ void __launch_bounds__(kTraceBlock, kTraceBlocksPerSM) PT_SUFFIXED(k_trace_queue)(const Bvh8Device* __restrict__ bvh, const __grid_constant__ RayQueueView q, TraversalCounters* counters,
                                                                                              unsigned refill_idle_lanes, int triangle_postpone_below)
 {
     __shared__ uint2 shared_stack[kSharedStackEntries * kTraceBlock];
     const Bvh8Device b = *bvh;
-    trace_queue_body<ANY_HIT>(b, q, shared_stack, counters, refill_idle_lanes, triangle_postpone_below);
+    trace_queue_body<ANY_HIT, POSTPONE>(b, q, shared_stack, counters, refill_idle_lanes, triangle_postpone_below);
 }
 
 cudaError_t PT_SUFFIXED(launch_trace_queue)(const void* bvh_device_handle, const RayQueueView& q, bool any_hit, unsigned blocks, TraversalCounters* counters, cudaStream_t stream)
@@ -64,10 +64,14 @@ cudaError_t PT_SUFFIXED(launch_trace_queue)(const void* bvh_device_handle, const
     static const int postpone = [] { const char* v = getenv("B200PT_TRACE_TRI_POSTPONE"); int n = v ? atoi(v) : 0; return n > 0 && n <= 32 ? n : kTrianglePostponeBelow; }();
     static const unsigned block_scale_pct = [] { const char* v = getenv("B200PT_TRACE_GRID_PCT"); int n = v ? atoi(v) : 0; return n > 0 ? (unsigned)n : 100u; }();
     blocks = blocks * block_scale_pct / 100u > 0u ? blocks * block_scale_pct / 100u : 1u;
-    if (any_hit)
-        PT_SUFFIXED(k_trace_queue)<true><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters, refill, postpone);
+    if (any_hit && postpone > 1)
+        PT_SUFFIXED(k_trace_queue)<true, true><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters, refill, postpone);
+    else if (any_hit)
+        PT_SUFFIXED(k_trace_queue)<true, false><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters, refill, postpone);
+    else if (postpone > 1)
+        PT_SUFFIXED(k_trace_queue)<false, true><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters, refill, postpone);
     else
-        PT_SUFFIXED(k_trace_queue)<false><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters, refill, postpone);
+        PT_SUFFIXED(k_trace_queue)<false, false><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters, refill, postpone);
     return cudaGetLastError();
 }
 

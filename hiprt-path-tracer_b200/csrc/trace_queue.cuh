@@ -7,8 +7,8 @@
 //   * a lane whose ray ends takes the next ray of the queue at once (one warp-aggregated atomic per refill round), so the
 //     lanes of a warp stay busy until the queue is empty (after Aila & Laine, HPG 2009, "persistent threads");
 //   * quantised bounds become floats with one PRMT each (byte into the mantissa of 1.0f, bias folded into the per-node offsets);
-//   * a lane tests at most one triangle per iteration, and only when at least kTrianglePostponeBelow lanes of the warp have
-//     one pending (its node work goes on meanwhile), so the triangle code runs with fuller warps (after Ylitie et al., HPG 2017);
+//   * a lane tests at most one triangle per iteration, next to its node step (its node work goes on meanwhile); postponing the
+//     triangle until several lanes of the warp have one pending (after Ylitie et al., HPG 2017) is built in but measured slower;
 //   * the first kSharedStackEntries stack entries of each lane live in shared memory (lane-interleaved), the rest spills to local memory;
 //   * the kernel only traverses: 16-byte ray records in, 16+4-byte hit records (or an occlusion flag) out; shading data is
 //     fetched by the kernels that consume the hits.
@@ -30,16 +30,20 @@ namespace pt
 #define PT_TRACE_BLOCKS_PER_SM 7
 #endif
 #ifndef PT_TRACE_REFILL_IDLE
-#define PT_TRACE_REFILL_IDLE 4
+#define PT_TRACE_REFILL_IDLE 8
 #endif
 #ifndef PT_TRACE_TRI_POSTPONE
-#define PT_TRACE_TRI_POSTPONE 8
+#define PT_TRACE_TRI_POSTPONE 1
 #endif
 constexpr int kSharedStackEntries = PT_TRACE_SHARED_STACK;
 constexpr int kTraceBlock = 128;
 constexpr int kTraceBlocksPerSM = PT_TRACE_BLOCKS_PER_SM;         // 72 registers per thread; 64 (8 blocks) measured no faster
+// Sweep on B200 (tools/trace_sweep.sh, profiles/r01_trace_sweep.txt), trace stage of a C3 pass: refill at 1 / 2 / 4 / 8 / 16 idle
+// lanes 7.36 / 7.02 / 6.77 / 6.73 / 7.00 ms; triangle postponement below 1 (= none) / 4 / 8 / 16 / 24 lanes 6.47 / 6.59 / 6.76 /
+// 7.17 / 8.22 ms. With one triangle per iteration and the node step of the other lanes going on in the same iteration, waiting
+// for fuller triangle warps only delays the rays: postponement is off by default (POSTPONE = false compiles the vote out).
 constexpr unsigned kRefillIdleLanes = PT_TRACE_REFILL_IDLE;       // refill as soon as this many lanes of a warp have no ray
-constexpr int kTrianglePostponeBelow = PT_TRACE_TRI_POSTPONE;     // triangles are tested when at least this many lanes of the warp have one pending
+constexpr int kTrianglePostponeBelow = PT_TRACE_TRI_POSTPONE;     // > 1: triangles are tested when at least this many lanes of the warp have one pending
 
 // 1 + byte * 2^-15, exactly: the byte lands in mantissa bits 8..15 of 1.0f with one PRMT (result bytes, low to high:
 // 0x00, byte j of word, 0x80, 0x3F). The slab test then evaluates plane = (1 + q 2^-15) * (2^15 a) + (o - 2^15 a), the same
@@ -65,7 +69,7 @@ PT_DEV void prefetch_global(const void* p)
     asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
 }
 
-template <bool ANY_HIT>
+template <bool ANY_HIT, bool POSTPONE>
 __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const RayQueueView& q, uint2* shared_stack, TraversalCounters* counters,
                                                  const unsigned refill_idle_lanes = kRefillIdleLanes, const int triangle_postpone_below = kTrianglePostponeBelow)
 {
@@ -229,8 +233,13 @@ __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const Ra
 
         // One triangle per lane, and only when enough lanes of the warp have one: the triangle code runs with fuller warps
         // while the other lanes' triangle work waits (their node work goes on).
-        const unsigned triangle_lanes = __ballot_sync(active_mask, tgroup.y != 0u);
-        if (tgroup.y != 0u && __popc(triangle_lanes) >= min(triangle_postpone_below, __popc(active_mask)))
+        bool test_triangle = tgroup.y != 0u;
+        if (POSTPONE)
+        {
+            const unsigned triangle_lanes = __ballot_sync(active_mask, tgroup.y != 0u);
+            test_triangle = test_triangle && __popc(triangle_lanes) >= min(triangle_postpone_below, __popc(active_mask));
+        }
+        if (test_triangle)
         {
             const uint32_t tbit = (uint32_t)__ffs((int)tgroup.y) - 1u;
             tgroup.y &= tgroup.y - 1u;

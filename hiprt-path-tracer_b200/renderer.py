@@ -2,6 +2,8 @@
 reference's GPURenderer). All compute happens in the CUDA library; numpy is only used to carry host arrays."""
 import ctypes as C
 
+import weakref
+
 import numpy as np
 
 from . import _capi
@@ -32,6 +34,10 @@ class Context:
 
     def close(self):
         if self.handle:
+            # renderers hold device buffers of this context: destroy the ones still alive first (a renderer leaked by a failed
+            # test would otherwise be collected after the context and free through a dangling b200pt_ctx)
+            for r in list(getattr(self, "_renderers", ())):
+                r.close()
             self.lib.b200pt_ctx_destroy(self.handle)
             self.handle = C.c_void_p()
 
@@ -142,6 +148,9 @@ class GPURenderer:
         self.host = _capi.host()
         self.handle = C.c_void_p()
         _capi.check_host(self.host.b200pt_renderer_create(ctx.handle, C.byref(self.handle)), "b200pt_renderer_create")
+        if not hasattr(ctx, "_renderers"):
+            ctx._renderers = weakref.WeakSet()
+        ctx._renderers.add(self)
         self.set_seed_schedule(seed_schedule)
         if options is not None:
             self.set_kernel_options(**options)

@@ -48,6 +48,20 @@ def golden_scene(name, width, height, lss="mis", adaptive=False, thin_film=False
     }
 
 
+def adaptive(width, height):
+    """C5: per-pixel adaptive sampling on the reference's nested-dielectrics-complex scene with a thin-film coating on every
+    non-emissive material and spectral dispersion switched on for the transmissive ones (4K in BASELINE.json: bench.py
+    --workload adaptive --width 3840 --height 2160; N GPUs shard sample passes and all-reduce the accumulation, squared-luminance
+    and sample-count buffers)."""
+    cfg = golden_scene("nested-dielectrics-complex", width, height, adaptive=True, thin_film=True)
+    for m in cfg["scene"].materials:
+        if m.base.specular_transmission > 0.0 and m.base.ior > 1.05:     # dispersion around an index of 1 makes the reference produce NaN samples
+            m.base.dispersion_scale = 1.0
+            m.base.dispersion_abbe_number = 20.0
+    cfg["name"] = f"nested-dielectrics-complex {width}x{height}, 8 bounces, LSS_MIS_LIGHT_BSDF, adaptive sampling (min 4 samples, threshold 1.0), thin film + dispersion"
+    return cfg
+
+
 _CACHE = {}
 
 

@@ -397,6 +397,82 @@ def test_tonemap_and_headless_png_parity(pt, wl, ctx, ref, tmp_path):
         g.close()
 
 
+def _textured_cornell(wl, width, height):
+    """Cornell box with 8-bit textures driving the material parameters (get_intersection_material's overrides,
+    Material.h:47-96; sample_texture_rgba, Texture.h:30-76; normal mapping): planar texcoords that leave [0, 1] (wrap), an sRGB
+    RGBA base colour, a packed roughness-metallic map, single-parameter maps and a normal map on different materials."""
+    cfg = wl.cornell(width, height)
+    scene = cfg["scene"]
+    v = scene.vertices
+    scene.texcoords = np.stack([v[:, 0] * 0.37 + 0.5 * v[:, 1], v[:, 2] * 0.41 - 0.3 * v[:, 1]], axis=1).astype(np.float32)
+    rng = np.random.default_rng(11)
+    def tex(h, w, c, lo=0, hi=256):
+        return rng.integers(lo, hi, size=(h, w, c), dtype=np.uint8)
+    normal_map = tex(8, 8, 3, 96, 160)
+    normal_map[..., 2] = 255                                   # mostly +z: a perturbed, not a random, normal
+    scene.textures = [tex(16, 32, 4, 40, 256), tex(16, 16, 3), tex(8, 8, 3, 20, 230), normal_map, tex(4, 4, 3)]
+    emissive_materials = set(int(scene.material_indices[t]) for t in scene.emissive)
+    plain = [i for i in range(len(scene.materials)) if i not in emissive_materials]
+    assert len(plain) >= 5
+    m = scene.materials
+    m[plain[0]].base_color_texture_index = 0
+    m[plain[1]].roughness_metallic_texture_index = 1
+    m[plain[2]].roughness_texture_index = 2
+    m[plain[2]].specular_texture_index = 4
+    m[plain[2]].coat_texture_index = 2
+    m[plain[3]].normal_map_texture_index = 3
+    m[plain[4]].base_color_texture_index = 0
+    m[plain[4]].specular_color_texture_index = 4
+    m[plain[4]].sheen_texture_index = 2
+    m[plain[4]].sheen_color_texture_index = 4
+    cfg["name"] += ", textured"
+    return cfg
+
+
+def test_textured_materials_parity(pt, wl, ctx, ref):
+    """Row M against the reference CPU kernels with matched RNG streams: the G-buffer materials (every overridden parameter) and
+    shading normals (normal map) are compared byte for byte, radiance within the north-star tolerance, and the wavefront (textured
+    hits keep their material in the path-state slot, plain hits keep the index) equals the megakernel bit for bit."""
+    W, H, spp = 160, 96, 4
+    cfg = _textured_cornell(wl, W, H)
+    r = wl.setup_oracle(ref, pt.structs, cfg)
+    g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="cpu")
+    try:
+        r.render(spp)
+        frames = {}
+        for mode in ("megakernel", "phased"):
+            ctx.set_path_mode(mode)
+            g.reset()
+            g.resize(W, H)
+            wl.apply_settings(g.render_settings, cfg["settings"])
+            for _ in range(spp):
+                g.render_frame()
+            g.synchronize()
+            frames[mode] = g.download("pixels").copy()
+        hit = r.buffer("camera_ray_hit") == 1
+        assert np.array_equal(r.buffer("first_hit_prim_index"), g.download("first_hit_prim_index"))
+        ma, mb = r.buffer("materials")[hit][:, 4:244].copy(), g.download("materials")[hit][:, 4:244].copy()
+        # the sRGB base colour goes through powf(texel, 2.2) (Texture.h:72-73): glibc and CUDA differ by one ulp on ~7 % of the
+        # textured pixels; every other parameter (linear texel / 255) is byte-equal
+        o = pt.structs.SimplifiedRendererMaterial.base_color.offset - 4
+        ca, cb = ma[:, o:o + 12].copy().view(np.float32), mb[:, o:o + 12].copy().view(np.float32)
+        assert np.allclose(ca, cb, rtol=1.5e-7, atol=0.0)
+        ma[:, o:o + 12] = 0
+        mb[:, o:o + 12] = 0
+        assert np.array_equal(ma, mb)
+        ma[:, o:o + 12] = ca.view(np.uint8)
+        assert np.array_equal(r.buffer("shading_normals")[hit], g.download("shading_normals")[hit])
+        textured_pixels = (ma.view(np.float32) != ma.view(np.float32)[0]).any(axis=1).mean()
+        assert textured_pixels > 0.5                               # the textures do vary the materials over the image
+        assert np.array_equal(frames["megakernel"], frames["phased"])
+        a, b = r.pixels() / spp, frames["phased"] / spp
+        err = _rel_err(a, b)
+        assert err < 1e-3, err
+    finally:
+        ctx.set_path_mode("phased")
+        g.close()
+
+
 def test_column_tile_sharding_is_bit_identical(pt, wl, ctx):
     """The strong-scaling shard shape of config C3 (bench.py --sharding columns) on one device: three renderers own three column
     bands of the envmap scene; the union of their accumulation buffers equals the unsharded render bit for bit."""
@@ -478,6 +554,7 @@ def test_restir_di_tile_sharding_with_halo_is_bit_identical(pt, wl, ctx):
     ("nested-dielectrics-complex", dict(nb_bounces=12)),
     ("multi-dispersion", dict()),
     ("cornell_pbr", dict(thin_film=True, adaptive=True)),
+    ("C5 bench workload", dict(adaptive=True)),
 ])
 def test_c5_feature_scenes_parity(pt, wl, ctx, ref, name, kwargs):
     """The material features config C5 names, on the reference's own test scenes with matched RNG streams: nested dielectrics
@@ -485,7 +562,8 @@ def test_c5_feature_scenes_parity(pt, wl, ctx, ref, name, kwargs):
     sampling. G-buffer hit ids and the adaptive-sampling counters are integer work -> exact; radiance within the north-star
     tolerance; the phased wavefront equals the megakernel bit for bit on each of them."""
     W, H, spp = 128, 96, 12 if kwargs.get("adaptive") else 4
-    cfg = wl.golden_scene(name, W, H, **kwargs)
+    # "C5 bench workload": all of them at once, as bench.py --workload adaptive runs it (nested dielectrics + thin film + dispersion + adaptive)
+    cfg = wl.adaptive(W, H) if name == "C5 bench workload" else wl.golden_scene(name, W, H, **kwargs)
     r = wl.setup_oracle(ref, pt.structs, cfg)
     g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="cpu")
     r.render(spp)
