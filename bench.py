@@ -127,8 +127,11 @@ def run_ours(args, cfg, pt):
     bvh_info = ctx.bvh_info(g.bvh)
 
     def restart():
-        # Sample-pass sharding: rank r owns the sample numbers r*2^20 + k; the per-pixel streams are seeded by
-        # (pixel, sample_number, random_seed) (FullPathTracer.h:124-129), so the ranks' samples are independent.
+        # Sample-pass sharding: every rank draws its per-launch seeds from its own host stream, so the ranks render independent
+        # samples at the SAME sample_number (the per-pixel streams are seeded by (pixel, sample_number, random_seed),
+        # FullPathTracer.h:124-129; adaptive sampling's thresholds are sample numbers, so the sample number itself is not offset)
+        if world > 1 and sharding == "samples":
+            g.set_rng_seed(42 + 7919 * rank)
         g.reset()
         g.resize(W, H)
         wl.apply_settings(g.render_settings, cfg["settings"])
@@ -139,9 +142,6 @@ def run_ours(args, cfg, pt):
         elif world > 1 and sharding == "columns":
             # the same with column bands: balanced on landscape frames (sky above, geometry below)
             g.set_tile((tiles[rank][0], 0, tiles[rank][1], H))
-        elif rank > 0:
-            g.render_settings.sample_number = rank << 20
-            g.render_settings.need_to_reset = 0
 
     def step():
         g.render_frame()

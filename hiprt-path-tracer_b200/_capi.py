@@ -81,7 +81,7 @@ API_SYMBOLS = [
     "b200pt_counters_read",
 ]
 HOST_API_SYMBOLS = [
-    "b200pt_host_last_error", "b200pt_renderer_create", "b200pt_renderer_destroy", "b200pt_renderer_set_seed_schedule",
+    "b200pt_host_last_error", "b200pt_renderer_create", "b200pt_renderer_destroy", "b200pt_renderer_set_seed_schedule", "b200pt_renderer_set_rng_seed",
     "b200pt_renderer_set_kernel_options", "b200pt_renderer_set_brdf_luts", "b200pt_renderer_add_texture", "b200pt_renderer_set_scene",
     "b200pt_renderer_set_envmap", "b200pt_host_compute_alias_table", "b200pt_renderer_set_camera", "b200pt_renderer_resize", "b200pt_renderer_set_tile", "b200pt_renderer_set_tile_halo", "b200pt_renderer_set_path_lanes", "b200pt_renderer_path_lanes",
     "b200pt_renderer_reset", "b200pt_renderer_render_settings", "b200pt_renderer_world_settings", "b200pt_renderer_bsdfs_data",

@@ -300,6 +300,7 @@ void GPURenderer::reset()
     m_render_data.render_settings.need_to_reset = 1;
     m_render_data.random_seed = 42;
     m_rng = Xorshift32Generator();
+    m_rng.seed = rng_seed != 0u ? rng_seed : 42u;
     m_restir_odd_frame = false;
 }
 

@@ -156,6 +156,10 @@ public:
     BRDFsData& get_bsdfs_data() { return m_render_data.bsdfs_data; }
     HIPRTRenderData& get_render_data() { return m_render_data; }
     SeedSchedule seed_schedule = SeedSchedule::GPU;
+    // Seed of the host generator the per-launch random_seed values are drawn from (the reference's m_rng starts at 42,
+    // src/Renderer/GPURenderer.h). Multi-GPU sample-pass sharding gives every rank its own stream: the ranks then render
+    // independent samples with the SAME sample_number, which adaptive sampling's thresholds are expressed in.
+    unsigned int rng_seed = 42;
 
     std::vector<ColorRGB32F> download_framebuffer() const { return m_pixels.download_data(); }
     const DeviceBuffer<ColorRGB32F>& framebuffer() const { return m_pixels; }

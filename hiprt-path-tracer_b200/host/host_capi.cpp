@@ -62,6 +62,13 @@ int b200pt_renderer_set_seed_schedule(b200pt_renderer* r, int seed_schedule)
     return B200PT_SUCCESS;
 }
 
+int b200pt_renderer_set_rng_seed(b200pt_renderer* r, unsigned int seed)
+{
+    r->renderer.rng_seed = seed;
+    r->renderer.reset();
+    return B200PT_SUCCESS;
+}
+
 int b200pt_renderer_set_kernel_options(b200pt_renderer* r, const b200pt_options* options)
 {
     return guarded([&] { r->renderer.set_kernel_options(*options); });

@@ -166,6 +166,10 @@ class GPURenderer:
         except Exception:
             pass
 
+    def set_rng_seed(self, seed):
+        """Host generator seed (42 = the reference's); resets the accumulation. One per rank under sample-pass sharding."""
+        _capi.check_host(self.host.b200pt_renderer_set_rng_seed(self.handle, C.c_uint(seed)), "b200pt_renderer_set_rng_seed")
+
     def set_seed_schedule(self, schedule):
         self.host.b200pt_renderer_set_seed_schedule(self.handle, C.c_int(1 if schedule == "cpu" else 0))
 

@@ -21,6 +21,9 @@ B200PT_API int b200pt_renderer_create(b200pt_ctx* ctx, b200pt_renderer** out);
 B200PT_API int b200pt_renderer_destroy(b200pt_renderer* r);
 /* seed_schedule: 0 = GPU (fresh seed per launch, GPURenderer.cpp:466-486), 1 = CPU (CPURenderer.cpp:264-296) */
 B200PT_API int b200pt_renderer_set_seed_schedule(b200pt_renderer* r, int seed_schedule);
+/* Seed of the host xorshift32 generator the per-launch random_seed values come from (42 in the reference, nonzero); resets the
+ * accumulation. One value per rank under sample-pass sharding: independent samples at equal sample_number on every rank. */
+B200PT_API int b200pt_renderer_set_rng_seed(b200pt_renderer* r, unsigned int seed);
 B200PT_API int b200pt_renderer_set_kernel_options(b200pt_renderer* r, const b200pt_options* options);
 B200PT_API int b200pt_renderer_set_brdf_luts(b200pt_renderer* r, const float* sheen_ltc, const float* conductor, const float* glossy,
                                              const float* glass, const float* glass_inverse, const float* thin_glass);
