@@ -310,7 +310,8 @@ def run_ours(args, cfg, pt):
     # 2 per sampled light kind (eval, BSDF sample) + NEE any-hit trace + NEE closest trace (emissives only) + bsdf
     nb = cfg["settings"].get("nb_bounces", 8)
     has_lights, has_env = len(cfg["scene"].emissive) > 0, cfg["envmap"] is not None and cfg["options"]["ess"] != "none"
-    per_bounce = 2 + 2 * has_lights + 2 * has_env + (1 if (has_lights or has_env) else 0) + (1 if has_lights else 0) + 1
+    # (shadow rays and NEE light rays of a bounce share one launch: k_trace_queue_pair)
+    per_bounce = 2 + 2 * has_lights + 2 * has_env + (1 if (has_lights or has_env) else 0) + 1
     launches_per_step = 1 + lanes * ((1 + per_bounce) + nb * (2 + per_bounce)) + (3 if restir else 0)      # every path lane launches its own band
     out = {
         "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),

@@ -212,19 +212,30 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
                 PT_VARIANT_NAME(launch_phase)(PHASE_ENV_BSDF_SAMPLE, g64, stream, rd, res, tile, wf, bounce, lights, envmap);
             }
             stage(STAGE_TRACE);
-            if (lights || envmap)
+            static const bool pair_trace = [] { const char* v = getenv("B200PT_PAIR_TRACE"); return v ? atoi(v) != 0 : true; }();
+            RayQueueView qa = {wf->any_queue, counts + 2, cursors + 6, wf->nee_ray_o, wf->nee_ray_d, nullptr, nullptr, wf->nee_ray_o};
+            RayQueueView qc = {wf->closest_queue, counts + 3, cursors + 9, wf->nee_ray_o, wf->nee_ray_d, wf->hit_tuvp, wf->hit_tri_slot, nullptr};
+            if (lights && pair_trace)
             {
-                RayQueueView qa = {wf->any_queue, counts + 2, cursors + 6, wf->nee_ray_o, wf->nee_ray_d, nullptr, nullptr, wf->nee_ray_o};
-                e = PT_SUFFIXED(launch_trace_queue)(rd->geom, qa, true, trace_blocks, counters, stream);
+                // shadow rays (any hit) and light rays (closest hit) of the bounce in ONE launch: see k_trace_queue_pair
+                e = PT_SUFFIXED(launch_trace_queue_pair)(rd->geom, qa, qc, trace_blocks, counters, stream);
                 if (e != cudaSuccess)
                     return e;
             }
-            if (lights)
+            else
             {
-                RayQueueView qc = {wf->closest_queue, counts + 3, cursors + 9, wf->nee_ray_o, wf->nee_ray_d, wf->hit_tuvp, wf->hit_tri_slot, nullptr};
-                e = PT_SUFFIXED(launch_trace_queue)(rd->geom, qc, false, trace_blocks, counters, stream);
-                if (e != cudaSuccess)
-                    return e;
+                if (lights || envmap)
+                {
+                    e = PT_SUFFIXED(launch_trace_queue)(rd->geom, qa, true, trace_blocks, counters, stream);
+                    if (e != cudaSuccess)
+                        return e;
+                }
+                if (lights)
+                {
+                    e = PT_SUFFIXED(launch_trace_queue)(rd->geom, qc, false, trace_blocks, counters, stream);
+                    if (e != cudaSuccess)
+                        return e;
+                }
             }
             stage(STAGE_SHADE);
             PT_VARIANT_NAME(launch_phase)(PHASE_BSDF_RESOLVED, g64, stream, rd, res, tile, wf, bounce, lights, envmap);

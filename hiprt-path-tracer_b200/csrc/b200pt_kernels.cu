@@ -56,6 +56,34 @@ __global__ void __launch_bounds__(kTraceBlock, kTraceBlocksPerSM) PT_SUFFIXED(k_
     trace_queue_body<ANY_HIT, POSTPONE>(b, q, shared_stack, counters, refill_idle_lanes, triangle_postpone_below);
 }
 
+// Two independent queues in one launch: every warp drains the any-hit queue, then the closest-hit queue. A launch of this kernel
+// cannot end before its longest ray has walked its dependent node fetches (~40 us on B200 whatever the queue length,
+// profiles/r01_launches_c2_bench_profile.txt): the NEE shadow rays and the NEE light rays of a bounce do not depend on each
+// other, so the second queue's rays fill the lanes the first queue's stragglers leave idle instead of paying that tail twice.
+template <bool POSTPONE>
+__global__ void __launch_bounds__(kTraceBlock, kTraceBlocksPerSM) PT_SUFFIXED(k_trace_queue_pair)(const Bvh8Device* __restrict__ bvh, const __grid_constant__ RayQueueView q_any,
+                                                                                                  const __grid_constant__ RayQueueView q_closest, TraversalCounters* counters,
+                                                                                                  unsigned refill_idle_lanes, int triangle_postpone_below)
+{
+    __shared__ uint2 shared_stack[kSharedStackEntries * kTraceBlock];
+    const Bvh8Device b = *bvh;
+    trace_queue_body<true, POSTPONE>(b, q_any, shared_stack, counters, refill_idle_lanes, triangle_postpone_below);
+    trace_queue_body<false, POSTPONE>(b, q_closest, shared_stack, counters, refill_idle_lanes, triangle_postpone_below);
+}
+
+static unsigned trace_knob_refill() { static const unsigned v = [] { const char* e = getenv("B200PT_TRACE_REFILL_IDLE"); int n = e ? atoi(e) : 0; return n > 0 && n <= 32 ? (unsigned)n : kRefillIdleLanes; }(); return v; }
+static int trace_knob_postpone() { static const int v = [] { const char* e = getenv("B200PT_TRACE_TRI_POSTPONE"); int n = e ? atoi(e) : 0; return n > 0 && n <= 32 ? n : kTrianglePostponeBelow; }(); return v; }
+
+cudaError_t PT_SUFFIXED(launch_trace_queue_pair)(const void* bvh_device_handle, const RayQueueView& q_any, const RayQueueView& q_closest, unsigned blocks, TraversalCounters* counters, cudaStream_t stream)
+{
+    const Bvh8Device* bvh = reinterpret_cast<const Bvh8Device*>(bvh_device_handle);
+    if (trace_knob_postpone() > 1)
+        PT_SUFFIXED(k_trace_queue_pair)<true><<<blocks, kTraceBlock, 0, stream>>>(bvh, q_any, q_closest, counters, trace_knob_refill(), trace_knob_postpone());
+    else
+        PT_SUFFIXED(k_trace_queue_pair)<false><<<blocks, kTraceBlock, 0, stream>>>(bvh, q_any, q_closest, counters, trace_knob_refill(), trace_knob_postpone());
+    return cudaGetLastError();
+}
+
 cudaError_t PT_SUFFIXED(launch_trace_queue)(const void* bvh_device_handle, const RayQueueView& q, bool any_hit, unsigned blocks, TraversalCounters* counters, cudaStream_t stream)
 {
     const Bvh8Device* bvh = reinterpret_cast<const Bvh8Device*>(bvh_device_handle);
