@@ -12,7 +12,7 @@ python bench.py --profile --steps 2 --workload synthetic > $O/prof_c3_plain.log 
 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file $O/launches_c3.csv python bench.py --profile --steps 2 --workload synthetic > $O/ncu_c3.log 2>&1
 python tools/ncu_launches.py $O/launches_c3.csv --sum > $O/launches_c3_summary.txt 2>&1
 if [ "$1" == "full" ]; then
-ncu --set full --clock-control none -k regex:k_trace_queue --launch-skip 156 -c 52 -f -o /tmp/trace_full_c2 python bench.py --profile --steps 2 > $O/ncu_full_c2.log 2>&1
+ncu --set full --clock-control none -k regex:k_trace_queue --launch-skip 102 -c 34 -f -o /tmp/trace_full_c2 python bench.py --profile --steps 2 > $O/ncu_full_c2.log 2>&1
 python tools/ncu_traffic.py /tmp/trace_full_c2.ncu-rep cornell_1920x1080 1 > $O/traffic_c2.log 2>&1
 python tools/ncu_summary.py /tmp/trace_full_c2.ncu-rep > $O/trace_full_c2_summary.txt 2>&1
 ncu --set full --clock-control none -k regex:k_trace_queue --launch-skip 102 -c 34 -f -o /tmp/trace_full_c3 python bench.py --profile --steps 2 --workload synthetic > $O/ncu_full_c3.log 2>&1
