@@ -72,13 +72,55 @@ def measured_traffic(workload, width, height):
     return entry["trace_queue_dram_bytes_per_step"] if entry else None
 
 
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def bounded_oracle(ref, wl, pt, cfg, seconds_per_pass=4.0):
+    """The reference's CPU renderer on a BOUNDED sample of the workload: the whole frame when one sample pass takes under
+    `seconds_per_pass`, else a quarter-size frame of the same scene and camera (1/16 of the pixels; rays per pixel, hence
+    Mrays/s, do not depend on it). The OpenMP team is set to every host core explicitly: torch.distributed.run exports
+    OMP_NUM_THREADS=1, which the reference's `#pragma omp parallel for` (CPURenderer.cpp:378-389) would otherwise inherit."""
+    r = wl.setup_oracle(ref, pt.structs, cfg)
+    cores = host_cores()
+    r.lib.ref_set_num_threads(C_int(cores))
+    W, H = cfg["width"], cfg["height"]
+    r.resize(max(W // 4, 8), max(H // 4, 8))
+    r.render(1)
+    t0 = time.time()
+    r.render(1)
+    t_small = time.time() - t0
+    small = t_small * 16.0 > seconds_per_pass
+    if not small:
+        r.resize(W, H)
+        r.render(1)
+    frame = f"{max(W // 4, 8)}x{max(H // 4, 8)} frame (1/16 of the pixels, same scene and camera)" if small else "whole frame"
+    return r, r.lib.ref_num_threads(), (t_small if small else t_small * 16.0), frame, (16.0 if small else 1.0)
+
+
+def C_int(v):
+    import ctypes
+    return ctypes.c_int(v)
+
+
+def workload_config(cfg, args, extra=None):
+    """`config` of the JSON line: the same keys on the GPU arm and on the reference arm."""
+    out = {"workload": cfg["name"], "width": cfg["width"], "height": cfg["height"], "nb_bounces": cfg["settings"].get("nb_bounces", 8),
+           "kernel_options": cfg["options"], "step": "one sample pass (1 spp) of the frame"}
+    out.update(extra or {})
+    return out
+
+
 def run_reference(args, cfg, pt):
-    """Reference arm: the reference's own CPU implementation of the path (oracle/_ref = its unmodified kernels)."""
+    """Reference arm: the reference's own CPU implementation of the path (oracle/_ref = its unmodified kernels) on every host
+    core, each step a bounded sample of the workload (see bounded_oracle)."""
     from oracle import ref
     wl = importlib.import_module("hiprt-path-tracer_b200.workloads")
-    r = wl.setup_oracle(ref, pt.structs, cfg)
-    cores = r.lib.ref_num_threads()
-    for _ in range(args.warmup):
+    r, cores, t_pass, frame, shrink = bounded_oracle(ref, wl, pt, cfg)
+    for _ in range(max(0, args.warmup - 2)):
         r.render(1)
     r.ray_count(reset=True)
     t0 = time.time()
@@ -87,11 +129,11 @@ def run_reference(args, cfg, pt):
     dt = time.time() - t0
     rays = r.ray_count()
     value = rays / dt / 1e6
-    sample = f"{args.steps} full sample passes of {cfg['name']} (one step = 1 spp of the whole frame), OpenMP over rows"
+    sample = f"{args.steps} sample passes of the {frame} of {cfg['name']} (one step = 1 spp), OpenMP over rows on {cores} threads"
     return {
         "impl": "reference", "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": cfg["name"]}, "samples_per_px_per_s": args.steps / dt,
+        "ms_per_step": dt / args.steps * 1e3 * shrink, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(cfg, args), "samples_per_px_per_s": args.steps / dt / shrink,
         "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": "reference", "sample": sample},
         "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
@@ -180,6 +222,7 @@ def run_ours(args, cfg, pt):
     ctx.counters_enable(False)
     rays_per_step = total["rays"] / args.steps
     fpt = {k: total[k] / args.steps - cam[k] for k in total}
+    assert total["stack_overflows"] == 0, "traversal stack overflow"
 
     # ---- 1b. stage pass: the same frames with per-stage CUDA events inside FullPathTracer (timing build, untimed otherwise):
     #          gives the device time of the ray-queue traversal kernels, the kernels the node-fetch roofline is about ----
@@ -302,8 +345,12 @@ def run_ours(args, cfg, pt):
     value = total_rays / (elapsed_ms * 1e-3) / 1e6
     peak, peak_kind = measured_hbm_peak()
     fpt_ms = kernel_ms["FullPathTracer"] / args.steps
-    # algorithmic bytes per ray (SURVEY.md 8d / DESIGN.md): 32 B ray in + 16 B hit out + 80 B per node + 48 B per triangle
-    fpt_bytes = 48.0 * fpt["rays"] + 80.0 * fpt["nodes"] + 48.0 * fpt["triangles"]
+    # algorithmic bytes per ray (SURVEY.md 8d / DESIGN.md): 32 B ray in + 16 B hit out + 80 B per node + 48 B per triangle,
+    # over the rays / nodes / triangles of the ray-queue kernel ALONE (per-thread traversals inside other kernels are not credited to it)
+    queue = {k: fpt["queue_" + k] for k in ("rays", "nodes", "triangles")}
+    if queue["rays"] <= 0:
+        queue = {k: fpt[k] for k in ("rays", "nodes", "triangles")}     # shapes without the ray-queue kernel: every traversal of FullPathTracer
+    fpt_bytes = 48.0 * queue["rays"] + 80.0 * queue["nodes"] + 48.0 * queue["triangles"]
     trace_ms = stage_ms["trace"] if stage_ms["trace"] > 0 else fpt_ms    # bounce >= 1 rays + all NEE rays go through the ray-queue kernel
     achieved = fpt_bytes / (trace_ms * 1e-3) / 1e9
     # kernels per step (wavefront, phased MIS shape): CameraRays + per bounce {gen | trace + surface} + scan + scatter +
@@ -316,7 +363,7 @@ def run_ours(args, cfg, pt):
     out = {
         "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "strong" if (world > 1 and sharding in ("tiles", "columns")) else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": cfg["name"], "parallelism": "single GPU" if world == 1 else ((f"row-tile sharding x{world}" + (f" + {halo}-row ReSTIR reservoir halo exchange" if restir else "") + ", frame gathered once per output") if sharding == "tiles"
+        "config": {**workload_config(cfg, args), "parallelism": "single GPU" if world == 1 else ((f"row-tile sharding x{world}" + (f" + {halo}-row ReSTIR reservoir halo exchange" if restir else "") + ", frame gathered once per output") if sharding == "tiles"
                                                                       else (f"column-tile sharding x{world}, frame gathered once per output; e2e reads the whole accumulation buffer back (a column band is strided)") if sharding == "columns"
                                                                       else f"sample-pass sharding x{world}, accumulation all-reduce") + ", scene+BVH replicated",
                    "l2": "inputs larger than L2: the per-step G-buffer round trip is 345 B/px = 715 MB at 1080p (L2 = 126 MB)",
@@ -325,38 +372,28 @@ def run_ours(args, cfg, pt):
         "gpu_launches": launches_per_step * args.steps,
         "clocks": clocks,
         "e2e": {"value": total_rays / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 2 * 1328 + 196, "d2h_bytes_per_step": W * own_rows * 12},
-        "roofline": {"bound": "hbm", "kernel": "k_trace_queue (ray-queue BVH8 traversal inside FullPathTracer; per step = sum of its launches)", "achieved": achieved, "peak": peak,
+        "roofline": {"bound": "hbm", "frac_of": "HBM copy peak (the contract's denominator; the kernel is L2-latency-bound, not HBM-bound)", "kernel": "k_trace_queue (ray-queue BVH8 traversal inside FullPathTracer; per step = sum of its launches)", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(args.workload, W, H),
                      "peak_source": peak_kind, "ms_per_launch": trace_ms, "full_path_tracer_ms": fpt_ms, "stage_ms": stage_ms,
                      "camera_rays_ms_per_launch": kernel_ms["CameraRays"] / args.steps,
-                     "rays_per_launch": fpt["rays"], "nodes_per_ray": fpt["nodes"] / max(1.0, fpt["rays"]), "triangles_per_ray": fpt["triangles"] / max(1.0, fpt["rays"])},
+                     "stage_ms_lanes": 1, "rays_per_launch": queue["rays"], "nodes_per_ray": queue["nodes"] / max(1.0, queue["rays"]),
+                     "triangles_per_ray": queue["triangles"] / max(1.0, queue["rays"]), "algorithmic_bytes_per_step": fpt_bytes,
+                     "limiter": "latency of dependent node / triangle fetches served by L1/L2 (ncu: long_scoreboard; DRAM traffic is several times below the algorithmic bytes), see DESIGN.md 4.2"},
     }
 
     # ---- 4. CPU baseline: the reference's own CPU kernels on a bounded sample of the same workload (rank 0, N = 1) ----
     if world == 1 and not args.no_cpu_baseline:
         from oracle import ref
-        r = wl.setup_oracle(ref, pt.structs, cfg)
-        # Bounded sample (~10-30 s of CPU work): whole sample passes of the frame when one takes under ~4 s, else passes of a
-        # quarter-size frame of the same scene and camera (1/16 of the pixels; rays per pixel, hence Mrays/s, do not depend on it)
-        r.resize(max(W // 4, 8), max(H // 4, 8))
-        r.render(1)
-        t0 = time.time()
-        r.render(1)
-        t_small = time.time() - t0
-        small = t_small * 16.0 > 4.0
-        if not small:
-            r.resize(W, H)
-            r.render(1)
-        t_pass = t_small if small else t_small * 16.0
+        # Bounded sample (~10-30 s of CPU work), every host core (bounded_oracle)
+        r, cores, t_pass, frame, shrink = bounded_oracle(ref, wl, pt, cfg)
         n = int(min(16, max(1, 12.0 / max(t_pass, 1e-3))))
         r.ray_count(reset=True)
         t0 = time.time()
         r.render(n)
         dt = time.time() - t0
-        frame = f"{max(W // 4, 8)}x{max(H // 4, 8)} frame (1/16 of the pixels)" if small else "whole frame"
-        out["cpu_baseline"] = {"value": r.ray_count() / dt / 1e6, "unit": "Mrays/s", "cores": r.lib.ref_num_threads(), "kind": "reference",
+        out["cpu_baseline"] = {"value": r.ray_count() / dt / 1e6, "unit": "Mrays/s", "cores": cores, "kind": "reference",
                                "sample": f"{n} sample passes of the {frame} of {cfg['name']} with the reference's CPU kernels (oracle/_ref), OpenMP over rows",
-                               "samples_per_px_per_s": n / dt / (16.0 if small else 1.0)}
+                               "samples_per_px_per_s": n / dt / shrink}
     if dist:
         dist.destroy_process_group()
     return out
@@ -368,7 +405,7 @@ def main():
     ap.add_argument("--steps", type=int, default=16)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cornell")
+    ap.add_argument("--workload", default="synthetic", help="synthetic = C3 (10 M triangles + envmap, the config the target is quoted on; default), cornell = C2, many_lights = C4, adaptive = C5")
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--sharding", default="auto", choices=["auto", "samples", "tiles", "columns"],

@@ -36,6 +36,22 @@ def sources_mtime():
     return newest
 
 
+def stale(obj):
+    """An object is rebuilt when it, or its dependency file (nvcc -MD), is missing, or when a file it includes is newer."""
+    dep = obj[:-2] + ".d"
+    if not (os.path.exists(obj) and os.path.exists(dep)):
+        return True
+    built = os.path.getmtime(obj)
+    text = open(dep).read().replace("\\\n", " ")
+    deps = text.split(":", 1)[1].split() if ":" in text else []
+    for d in deps:
+        if d.startswith(("/usr/", "/opt/")):
+            continue
+        if not os.path.exists(d) or os.path.getmtime(d) > built:
+            return True
+    return False
+
+
 def run(cmd):
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
@@ -51,8 +67,8 @@ def build(force=False, verbose=False):
 
     def add(obj, src, extra=()):
         o = os.path.join(OBJ, obj)
-        if force or not os.path.exists(o) or os.path.getmtime(o) < newest:
-            jobs.append((o, [NVCC, *NVCC_FLAGS, *extra, "-c", os.path.join(CSRC, src), "-o", o]))
+        if force or stale(o):
+            jobs.append((o, [NVCC, *NVCC_FLAGS, *extra, "-MD", "-MF", o[:-2] + ".d", "-c", os.path.join(CSRC, src), "-o", o]))
         return o
 
     objects = [add("bvh8_build.o", "bvh8_build.cpp", ["-x", "cu"]), add("capi.o", "b200pt_capi.cu")]
@@ -66,6 +82,8 @@ def build(force=False, verbose=False):
                 objects.append(add(f"phase_{lss}_{ess}_{later}_{ggx}_{suffix}.o", "b200pt_phase_variant.cu",
                                    defs + [f"-DPT_LSS={lss}", f"-DPT_ESS={ess}", f"-DPT_LATER={later}", f"-DPT_GGX={ggx}", "-DPT_BSDF_INLINE"]))
 
+    # slowest translation units first (the phase kernels take ~2 minutes each)
+    jobs.sort(key=lambda j: (0 if "/phase_" in j[0] else 1 if "/fpt_" in j[0] else 2))
     if jobs:
         with ThreadPoolExecutor(max_workers=os.cpu_count() or 4) as ex:
             for out in ex.map(lambda j: run(j[1]), jobs):

@@ -38,7 +38,12 @@ struct b200pt_bvh
     void* d_triangles = nullptr;
     float sah_cost = 0.0f;
     double build_seconds = 0.0;
+    int max_depth = 0;
+    float node_fill = 0.0f;
+    bool built_on_device = false;
 };
+
+namespace pt { int g_trace_flavour = -1; }
 
 namespace
 {

@@ -91,9 +91,19 @@ int b200pt_bvh_build(b200pt_ctx* ctx, const float* vertices, int vertex_count, c
     pt::Bvh8Host host = pt::build_bvh8(vertices, vertex_count, triangle_indices, triangle_count);
     double seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 
+    // The traversal stacks hold kTraversalStackSize entries: a ray of the ray-queue kernel defers at most one node group and one
+    // triangle group per level. A deeper tree would drop subtrees silently, so it is refused here instead.
+    if (2 * host.max_depth + 1 > pt::kTraversalStackSize)
+    {
+        char msg[160];
+        snprintf(msg, sizeof(msg), "BVH8 depth %d needs %d traversal-stack entries, kTraversalStackSize is %d", host.max_depth, 2 * host.max_depth + 1, pt::kTraversalStackSize);
+        return fail(B200PT_ERROR_INVALID_ARGUMENT, msg);
+    }
     b200pt_bvh* bvh = new b200pt_bvh();
     bvh->sah_cost = host.sah_cost;
     bvh->build_seconds = seconds;
+    bvh->max_depth = host.max_depth;
+    bvh->node_fill = host.nodes.empty() ? 0.0f : (float)((double)host.child_slots_used / (8.0 * (double)host.nodes.size()));
     size_t node_bytes = host.nodes.size() * sizeof(pt::Bvh8Node);
     size_t tri_bytes = host.triangles.size() * sizeof(pt::Bvh8Triangle);
     cudaError_t e = cudaMalloc(&bvh->d_nodes, node_bytes);
@@ -150,6 +160,19 @@ int b200pt_bvh_info(b200pt_bvh* bvh, unsigned* out_node_count, unsigned* out_tri
     if (out_triangle_count) *out_triangle_count = bvh->view.triangle_count;
     if (out_sah_cost) *out_sah_cost = bvh->sah_cost;
     if (out_build_seconds) *out_build_seconds = bvh->build_seconds;
+    return B200PT_SUCCESS;
+}
+
+int b200pt_bvh_get_stats(b200pt_bvh* bvh, b200pt_bvh_stats* out_stats)
+{
+    REQUIRE(bvh != nullptr && out_stats != nullptr);
+    out_stats->node_count = bvh->view.node_count;
+    out_stats->triangle_count = bvh->view.triangle_count;
+    out_stats->max_depth = bvh->max_depth;
+    out_stats->built_on_device = bvh->built_on_device ? 1 : 0;
+    out_stats->sah_cost = bvh->sah_cost;
+    out_stats->node_fill = bvh->node_fill;
+    out_stats->build_seconds = bvh->build_seconds;
     return B200PT_SUCCESS;
 }
 
@@ -419,6 +442,31 @@ int b200pt_trace_shadow(b200pt_ctx* ctx, b200pt_bvh* bvh, const float* d_rays, c
     return B200PT_SUCCESS;
 }
 
+int b200pt_trace_queue(b200pt_ctx* ctx, b200pt_bvh* bvh, const float* d_rays, const float* d_t_max, const int* d_last_prim, long long n, int* d_out_prim, float* d_out_t, float* d_out_uv,
+                       unsigned char* d_out_occluded, b200pt_stream stream)
+{
+    REQUIRE(ctx != nullptr && bvh != nullptr && n >= 0 && n < (1ll << 31));
+    const bool any_hit = d_t_max != nullptr;
+    REQUIRE(n == 0 || (d_rays != nullptr && (any_hit ? d_out_occluded != nullptr : (d_out_prim != nullptr && d_out_t != nullptr))));
+    if (n == 0)
+        return B200PT_SUCCESS;
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+    cudaError_t e = ctx->counting ? pt::launch_trace_batch_queue_c(bvh->d_view, d_rays, d_t_max, d_last_prim, n, d_out_prim, d_out_t, d_out_uv, d_out_occluded, (unsigned)sms, ctx->d_counters, stream_of(ctx, stream))
+                                  : pt::launch_trace_batch_queue_t(bvh->d_view, d_rays, d_t_max, d_last_prim, n, d_out_prim, d_out_t, d_out_uv, d_out_occluded, (unsigned)sms, nullptr, stream_of(ctx, stream));
+    if (e != cudaSuccess)
+        return cuda_fail(e, "trace_queue");
+    return B200PT_SUCCESS;
+}
+
+int b200pt_set_trace_flavour(b200pt_ctx* ctx, int flavour)
+{
+    REQUIRE(ctx != nullptr && (flavour == -1 || flavour == 0 || flavour == 1 || (flavour >= 5 && flavour <= 7)));
+    pt::g_trace_flavour = flavour;
+    return B200PT_SUCCESS;
+}
+
 int b200pt_counters_enable(b200pt_ctx* ctx, int enable)
 {
     REQUIRE(ctx != nullptr);
@@ -435,6 +483,10 @@ int b200pt_counters_read(b200pt_ctx* ctx, b200pt_counters* out, int reset)
     out->rays = c.rays;
     out->nodes = c.nodes;
     out->triangles = c.triangles;
+    out->stack_overflows = c.overflows;
+    out->queue_rays = c.queue_rays;
+    out->queue_nodes = c.queue_nodes;
+    out->queue_triangles = c.queue_triangles;
     if (reset)
         CUDA_TRY(cudaMemset(ctx->d_counters, 0, sizeof(c)));
     return B200PT_SUCCESS;

@@ -156,7 +156,7 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
 #else
     TraversalCounters* const counters = nullptr;
 #endif
-    const unsigned trace_blocks = wf->sm_count * ((8u + share - 1u) / share);   // persistent: 8 resident blocks of 128 threads per SM, shared between lanes
+    const unsigned trace_blocks = wf->sm_count * (((unsigned)kTraceGridBlocksPerSM + share - 1u) / share);   // persistent: the resident blocks of 128 threads per SM (trace_queue.cuh), shared between lanes
     (void)counters; (void)trace_blocks;
     for (int bounce = 0; bounce <= nb_bounces; bounce++)
     {

@@ -47,60 +47,169 @@ __global__ void PT_SUFFIXED(k_trace_shadow)(Bvh8Device bvh, const float* __restr
     out_occluded[i] = bvh8_trace<true>(bvh, o, d, t_max[i] - 1.0e-4f, last_prim ? last_prim[i] : -1, hit, counters) ? 1 : 0;
 }
 
-template <bool ANY_HIT, bool POSTPONE>
-__global__ void __launch_bounds__(kTraceBlock, kTraceBlocksPerSM) PT_SUFFIXED(k_trace_queue)(const Bvh8Device* __restrict__ bvh, const __grid_constant__ RayQueueView q, TraversalCounters* counters,
-                                                                                             unsigned refill_idle_lanes, int triangle_postpone_below)
+// FLAVOUR 0: the classic loop (load, wait, test) at kTraceBlocksPerSM resident blocks; FLAVOUR 5 / 6 / 7: the pipelined loop
+// (trace_queue_body_pipelined) compiled for that many resident blocks per SM (95 / 80 / 72 registers: the loads in flight stay
+// live across the box tests, so fewer warps fit, each with more memory-level parallelism). B200PT_TRACE_PIPELINE selects at run time.
+template <bool ANY_HIT, int FLAVOUR>
+__global__ void __launch_bounds__(kTraceBlock, FLAVOUR ? FLAVOUR : kTraceBlocksPerSM) PT_SUFFIXED(k_trace_queue)(const Bvh8Device* __restrict__ bvh, const __grid_constant__ RayQueueView q,
+                                                                                                              TraversalCounters* counters, unsigned refill_idle_lanes)
 {
     __shared__ uint2 shared_stack[kSharedStackEntries * kTraceBlock];
     const Bvh8Device b = *bvh;
-    trace_queue_body<ANY_HIT, POSTPONE>(b, q, shared_stack, counters, refill_idle_lanes, triangle_postpone_below);
+    if (FLAVOUR)
+        trace_queue_body_pipelined<ANY_HIT>(b, q, shared_stack, counters, refill_idle_lanes);
+    else
+        trace_queue_body<ANY_HIT>(b, q, shared_stack, counters, refill_idle_lanes);
 }
 
 // Two independent queues in one launch: every warp drains the any-hit queue, then the closest-hit queue. A launch of this kernel
 // cannot end before its longest ray has walked its dependent node fetches (~40 us on B200 whatever the queue length,
 // profiles/r01_launches_c2_bench_profile.txt): the NEE shadow rays and the NEE light rays of a bounce do not depend on each
 // other, so the second queue's rays fill the lanes the first queue's stragglers leave idle instead of paying that tail twice.
-template <bool POSTPONE>
-__global__ void __launch_bounds__(kTraceBlock, kTraceBlocksPerSM) PT_SUFFIXED(k_trace_queue_pair)(const Bvh8Device* __restrict__ bvh, const __grid_constant__ RayQueueView q_any,
-                                                                                                  const __grid_constant__ RayQueueView q_closest, TraversalCounters* counters,
-                                                                                                  unsigned refill_idle_lanes, int triangle_postpone_below)
+template <int FLAVOUR>
+__global__ void __launch_bounds__(kTraceBlock, FLAVOUR ? FLAVOUR : kTraceBlocksPerSM) PT_SUFFIXED(k_trace_queue_pair)(const Bvh8Device* __restrict__ bvh, const __grid_constant__ RayQueueView q_any,
+                                                                                                                   const __grid_constant__ RayQueueView q_closest, TraversalCounters* counters,
+                                                                                                                   unsigned refill_idle_lanes)
 {
     __shared__ uint2 shared_stack[kSharedStackEntries * kTraceBlock];
     const Bvh8Device b = *bvh;
-    trace_queue_body<true, POSTPONE>(b, q_any, shared_stack, counters, refill_idle_lanes, triangle_postpone_below);
-    trace_queue_body<false, POSTPONE>(b, q_closest, shared_stack, counters, refill_idle_lanes, triangle_postpone_below);
+    if (FLAVOUR)
+    {
+        trace_queue_body_pipelined<true>(b, q_any, shared_stack, counters, refill_idle_lanes);
+        trace_queue_body_pipelined<false>(b, q_closest, shared_stack, counters, refill_idle_lanes);
+    }
+    else
+    {
+        trace_queue_body<true>(b, q_any, shared_stack, counters, refill_idle_lanes);
+        trace_queue_body<false>(b, q_closest, shared_stack, counters, refill_idle_lanes);
+    }
 }
 
+// scheduling knobs of the kernel (trace_queue.cuh), overridable for sweeps (tools/trace_sweep.sh); results do not depend on them
 static unsigned trace_knob_refill() { static const unsigned v = [] { const char* e = getenv("B200PT_TRACE_REFILL_IDLE"); int n = e ? atoi(e) : 0; return n > 0 && n <= 32 ? (unsigned)n : kRefillIdleLanes; }(); return v; }
-static int trace_knob_postpone() { static const int v = [] { const char* e = getenv("B200PT_TRACE_TRI_POSTPONE"); int n = e ? atoi(e) : 0; return n > 0 && n <= 32 ? n : kTrianglePostponeBelow; }(); return v; }
+static int trace_knob_flavour()
+{
+    static const int from_env = [] { const char* e = getenv("B200PT_TRACE_PIPELINE"); return e ? atoi(e) : PT_TRACE_PIPELINED_DEFAULT; }();
+    const int n = g_trace_flavour >= 0 ? g_trace_flavour : from_env;
+    return n == 5 || n == 6 || n == 7 ? n : (n == 1 ? 6 : 0);
+}
+static unsigned trace_knob_grid(unsigned blocks)
+{
+    static const unsigned pct = [] { const char* v = getenv("B200PT_TRACE_GRID_PCT"); int n = v ? atoi(v) : 0; return n > 0 ? (unsigned)n : 100u; }();
+    // `blocks` is sized for kTraceBlocksPerSM resident blocks per SM: a flavour with fewer resident blocks starts fewer
+    const int flavour = trace_knob_flavour();
+    const unsigned resident = flavour ? blocks * (unsigned)flavour / (unsigned)kTraceBlocksPerSM : blocks;
+    const unsigned scaled = resident * pct / 100u;
+    return scaled > 0u ? scaled : 1u;
+}
 
 cudaError_t PT_SUFFIXED(launch_trace_queue_pair)(const void* bvh_device_handle, const RayQueueView& q_any, const RayQueueView& q_closest, unsigned blocks, TraversalCounters* counters, cudaStream_t stream)
 {
     const Bvh8Device* bvh = reinterpret_cast<const Bvh8Device*>(bvh_device_handle);
-    if (trace_knob_postpone() > 1)
-        PT_SUFFIXED(k_trace_queue_pair)<true><<<blocks, kTraceBlock, 0, stream>>>(bvh, q_any, q_closest, counters, trace_knob_refill(), trace_knob_postpone());
-    else
-        PT_SUFFIXED(k_trace_queue_pair)<false><<<blocks, kTraceBlock, 0, stream>>>(bvh, q_any, q_closest, counters, trace_knob_refill(), trace_knob_postpone());
+    blocks = trace_knob_grid(blocks);
+    const unsigned refill = trace_knob_refill();
+    switch (trace_knob_flavour())
+    {
+    case 5: PT_SUFFIXED(k_trace_queue_pair)<5><<<blocks, kTraceBlock, 0, stream>>>(bvh, q_any, q_closest, counters, refill); break;
+    case 6: PT_SUFFIXED(k_trace_queue_pair)<6><<<blocks, kTraceBlock, 0, stream>>>(bvh, q_any, q_closest, counters, refill); break;
+    case 7: PT_SUFFIXED(k_trace_queue_pair)<7><<<blocks, kTraceBlock, 0, stream>>>(bvh, q_any, q_closest, counters, refill); break;
+    default: PT_SUFFIXED(k_trace_queue_pair)<0><<<blocks, kTraceBlock, 0, stream>>>(bvh, q_any, q_closest, counters, refill); break;
+    }
     return cudaGetLastError();
+}
+
+template <bool ANY_HIT>
+static void launch_trace_queue_flavour(const Bvh8Device* bvh, const RayQueueView& q, unsigned blocks, TraversalCounters* counters, unsigned refill, cudaStream_t stream)
+{
+    switch (trace_knob_flavour())
+    {
+    case 5: PT_SUFFIXED(k_trace_queue)<ANY_HIT, 5><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters, refill); break;
+    case 6: PT_SUFFIXED(k_trace_queue)<ANY_HIT, 6><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters, refill); break;
+    case 7: PT_SUFFIXED(k_trace_queue)<ANY_HIT, 7><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters, refill); break;
+    default: PT_SUFFIXED(k_trace_queue)<ANY_HIT, 0><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters, refill); break;
+    }
 }
 
 cudaError_t PT_SUFFIXED(launch_trace_queue)(const void* bvh_device_handle, const RayQueueView& q, bool any_hit, unsigned blocks, TraversalCounters* counters, cudaStream_t stream)
 {
     const Bvh8Device* bvh = reinterpret_cast<const Bvh8Device*>(bvh_device_handle);
-    // scheduling knobs of the kernel (trace_queue.cuh), overridable for sweeps (tools/trace_sweep.sh); results do not depend on them
-    static const unsigned refill = [] { const char* v = getenv("B200PT_TRACE_REFILL_IDLE"); int n = v ? atoi(v) : 0; return n > 0 && n <= 32 ? (unsigned)n : kRefillIdleLanes; }();
-    static const int postpone = [] { const char* v = getenv("B200PT_TRACE_TRI_POSTPONE"); int n = v ? atoi(v) : 0; return n > 0 && n <= 32 ? n : kTrianglePostponeBelow; }();
-    static const unsigned block_scale_pct = [] { const char* v = getenv("B200PT_TRACE_GRID_PCT"); int n = v ? atoi(v) : 0; return n > 0 ? (unsigned)n : 100u; }();
-    blocks = blocks * block_scale_pct / 100u > 0u ? blocks * block_scale_pct / 100u : 1u;
-    if (any_hit && postpone > 1)
-        PT_SUFFIXED(k_trace_queue)<true, true><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters, refill, postpone);
-    else if (any_hit)
-        PT_SUFFIXED(k_trace_queue)<true, false><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters, refill, postpone);
-    else if (postpone > 1)
-        PT_SUFFIXED(k_trace_queue)<false, true><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters, refill, postpone);
+    blocks = trace_knob_grid(blocks);
+    if (any_hit)
+        launch_trace_queue_flavour<true>(bvh, q, blocks, counters, trace_knob_refill(), stream);
     else
-        PT_SUFFIXED(k_trace_queue)<false, false><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters, refill, postpone);
+        launch_trace_queue_flavour<false>(bvh, q, blocks, counters, trace_knob_refill(), stream);
     return cudaGetLastError();
+}
+
+// ---- a ray batch through the ray-queue kernel (b200pt_trace_queue): pack -> k_trace_queue -> unpack -------------------------------
+__global__ void __launch_bounds__(256) PT_SUFFIXED(k_batch_pack)(const float* __restrict__ rays, const float* __restrict__ t_max, const int* __restrict__ last_prim, uint32_t n,
+                                                                float4* ray_o, float4* ray_d, uint32_t* ids, float4* hit_tuvp, uint32_t* count_and_cursor)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0)
+    {
+        count_and_cursor[0] = n;
+        count_and_cursor[1] = 0u;
+    }
+    if (i >= n)
+        return;
+    ray_o[i] = make_float4(rays[i * 6 + 0], rays[i * 6 + 1], rays[i * 6 + 2], t_max ? t_max[i] : 0.0f);
+    ray_d[i] = make_float4(rays[i * 6 + 3], rays[i * 6 + 4], rays[i * 6 + 5], __int_as_float(last_prim ? last_prim[i] : -1));
+    ids[i] = i;
+    if (hit_tuvp)
+        hit_tuvp[i] = make_float4(-1.0f, 0.0f, 0.0f, __int_as_float(-1));
+}
+
+__global__ void __launch_bounds__(256) PT_SUFFIXED(k_batch_unpack)(const float4* __restrict__ ray_o, const float4* __restrict__ hit_tuvp, uint32_t n, int* out_prim, float* out_t, float* out_uv,
+                                                                  unsigned char* out_occluded)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+        return;
+    if (out_occluded)
+        out_occluded[i] = ray_o[i].w == -1.0f ? 1 : 0;      // the any-hit kernel's flag (trace_queue_store_hit)
+    else
+    {
+        const float4 h = hit_tuvp[i];
+        out_prim[i] = __float_as_int(h.w);
+        out_t[i] = h.x;
+        if (out_uv)
+        {
+            out_uv[i * 2 + 0] = h.y;
+            out_uv[i * 2 + 1] = h.z;
+        }
+    }
+}
+
+cudaError_t PT_SUFFIXED(launch_trace_batch_queue)(const void* bvh_device_handle, const float* rays, const float* t_max, const int* last_prim, long long n, int* out_prim, float* out_t, float* out_uv,
+                                                  unsigned char* out_occluded, unsigned sm_count, TraversalCounters* counters, cudaStream_t stream)
+{
+    const bool any_hit = t_max != nullptr;
+    const uint32_t count = (uint32_t)n;
+    float4 *ray_o = nullptr, *ray_d = nullptr, *hit_tuvp = nullptr;
+    uint32_t *ids = nullptr, *tri_slot = nullptr, *count_and_cursor = nullptr;
+    cudaError_t e = cudaMalloc(&ray_o, sizeof(float4) * n);
+    if (e == cudaSuccess) e = cudaMalloc(&ray_d, sizeof(float4) * n);
+    if (e == cudaSuccess) e = cudaMalloc(&ids, sizeof(uint32_t) * n);
+    if (e == cudaSuccess) e = cudaMalloc(&count_and_cursor, sizeof(uint32_t) * 2);
+    if (e == cudaSuccess && !any_hit) e = cudaMalloc(&hit_tuvp, sizeof(float4) * n);
+    if (e == cudaSuccess && !any_hit) e = cudaMalloc(&tri_slot, sizeof(uint32_t) * n);
+    if (e == cudaSuccess)
+    {
+        const unsigned grid = (count + 255u) / 256u;
+        PT_SUFFIXED(k_batch_pack)<<<grid, 256, 0, stream>>>(rays, t_max, last_prim, count, ray_o, ray_d, ids, hit_tuvp, count_and_cursor);
+        RayQueueView q = {ids, count_and_cursor, count_and_cursor + 1, ray_o, ray_d, hit_tuvp, tri_slot, any_hit ? ray_o : nullptr};
+        e = PT_SUFFIXED(launch_trace_queue)(bvh_device_handle, q, any_hit, sm_count * (unsigned)kTraceGridBlocksPerSM, counters, stream);
+        if (e == cudaSuccess)
+        {
+            PT_SUFFIXED(k_batch_unpack)<<<grid, 256, 0, stream>>>(ray_o, hit_tuvp, count, out_prim, out_t, out_uv, any_hit ? out_occluded : nullptr);
+            e = cudaGetLastError();
+        }
+        if (e == cudaSuccess)
+            e = cudaStreamSynchronize(stream);
+    }
+    cudaFree(ray_o); cudaFree(ray_d); cudaFree(ids); cudaFree(count_and_cursor); cudaFree(hit_tuvp); cudaFree(tri_slot);
+    return e;
 }
 
 static inline dim3 pixel_grid(const Tile& t) { return dim3((t.x1 - t.x0 + 7) / 8, (t.y1 - t.y0 + 7) / 8, 1); }

@@ -270,7 +270,9 @@ Bvh8Host build_bvh8(const float* vertices, int vertex_count, const int* indices,
     out.triangles.reserve(n);
     out.nodes.emplace_back();
     std::queue<std::pair<int, uint32_t>> todo;   // (binary node, wide node index)
+    std::queue<int> todo_depth;
     todo.push({root2, 0u});
+    todo_depth.push(1);
 
     double sah_internal = 0.0, sah_leaf = 0.0;
     const double root_area = std::max(1e-30f, n2[root2].box.half_area());
@@ -279,6 +281,9 @@ Bvh8Host build_bvh8(const float* vertices, int vertex_count, const int* indices,
     {
         auto [bin_index, wide_index] = todo.front();
         todo.pop();
+        const int depth = todo_depth.front();
+        todo_depth.pop();
+        out.max_depth = std::max(out.max_depth, depth);
 
         // Children of this wide node: the forest the SAH-optimal collapse chose for the binary subtree (see collapse_costs)
         int cand[8];
@@ -387,12 +392,14 @@ Bvh8Host build_bvh8(const float* vertices, int vertex_count, const int* indices,
             if (c < 0)
                 continue;   // meta 0 = empty slot
             const Node2& child = n2[c];
+            out.child_slots_used++;
             double area_ratio = child.box.half_area() / root_area;
             if (!leaf_in_slot[s])
             {
                 node.imask |= (uint8_t)(1u << s);
                 node.meta[s] = (uint8_t)((1u << 5) | (24u + s));
                 todo.push({c, (uint32_t)out.nodes.size()});
+                todo_depth.push(depth + 1);
                 out.nodes.emplace_back();
                 sah_internal += area_ratio;
             }

@@ -10,10 +10,16 @@ namespace pt
 {
 struct VariantOptions { int lss, ess, later, ggx; };
 struct Tile { int x0, y0, x1, y1; };
-struct TraversalCounters { unsigned long long rays, nodes, triangles; };
+// rays / nodes / triangles: every BVH query of the launch (per-thread traversals and the ray-queue kernel); queue_*: the ray-queue kernel's
+// share (the kernel the node-fetch roofline is about); overflows: traversal-stack pushes that found the stack full (must stay 0).
+struct TraversalCounters { unsigned long long rays, nodes, triangles, overflows, queue_rays, queue_nodes, queue_triangles; };
 
 // How b200pt_launch_FullPathTracer runs the path (wavefront.cuh). Selected per context (b200pt_set_path_mode).
 constexpr int kSortBuckets = 128;
+// Loop flavour of the ray-queue traversal kernel (b200pt_set_trace_flavour): -1 = B200PT_TRACE_PIPELINE / the built-in default,
+// 0 = classic, 5 / 6 / 7 = pipelined at that many resident blocks per SM. Process-wide; the hits do not depend on it.
+extern int g_trace_flavour;
+constexpr int kTraceGridBlocksPerSM = 7;   // resident blocks per SM of the ray-queue traversal kernel (= kTraceBlocksPerSM, trace_queue.cuh): its persistent grid
 constexpr int kCursorsPerBounce = 12;
 constexpr int kCountsPerBounce = 4;    // rays to extend, hits to shade, NEE any-hit rays, NEE closest-hit rays
 enum WavefrontMode { WF_MEGAKERNEL = 0, WF_FUSED = 1, WF_SPLIT = 2, WF_PHASED = 3 };
@@ -96,6 +102,7 @@ struct RayQueueView
     cudaError_t launch_ReSTIR_DI_SpatialReuse##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream); \
     cudaError_t launch_trace_queue##S(const void* bvh_device_handle, const RayQueueView& q, bool any_hit, unsigned blocks, TraversalCounters* counters, cudaStream_t stream); \
     cudaError_t launch_trace_queue_pair##S(const void* bvh_device_handle, const RayQueueView& q_any, const RayQueueView& q_closest, unsigned blocks, TraversalCounters* counters, cudaStream_t stream); \
+    cudaError_t launch_trace_batch_queue##S(const void* bvh_device_handle, const float* rays, const float* t_max, const int* last_prim, long long n, int* out_prim, float* out_t, float* out_uv, unsigned char* out_occluded, unsigned sm_count, TraversalCounters* counters, cudaStream_t stream); \
     cudaError_t launch_trace_closest##S(const Bvh8Device& bvh, const float* rays, const int* last_prim, long long n, int* out_prim, float* out_t, float* out_uv, TraversalCounters* counters, cudaStream_t stream); \
     cudaError_t launch_trace_shadow##S(const Bvh8Device& bvh, const float* rays, const float* t_max, const int* last_prim, long long n, unsigned char* out_occluded, TraversalCounters* counters, cudaStream_t stream);
 

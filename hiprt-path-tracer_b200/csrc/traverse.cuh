@@ -108,7 +108,7 @@ PT_DEV_NOINLINE bool bvh8_trace(const Bvh8Device& bvh, float3 o, float3 d, float
     int stack_size = 0;
     uint2 ngroup = make_uint2(0u, 0x80000000u);   // the root plays "internal child in the top-priority slot"
 
-    PT_COUNT(unsigned int n_nodes = 0; unsigned int n_tris = 0;)
+    PT_COUNT(unsigned int n_nodes = 0; unsigned int n_tris = 0; unsigned int n_overflows = 0;)
 
     while (true)
     {
@@ -121,8 +121,11 @@ PT_DEV_NOINLINE bool bvh8_trace(const Bvh8Device& bvh, float3 o, float3 d, float
             ngroup.y &= ~(1u << bit);
             if (ngroup.y > 0x00FFFFFFu)
             {
+                // A full stack cannot happen on a tree whose wide depth d satisfies d <= kTraversalStackSize (one deferred group per
+                // level; the builder reports d and b200pt_bvh_build refuses deeper trees). The counting build still counts it.
                 if (stack_size < kTraversalStackSize)
                     stack[stack_size++] = ngroup;
+                else { PT_COUNT(n_overflows++;) }
             }
             const uint32_t slot = (bit - 24u) ^ oct_inv;
             const uint32_t rank = (uint32_t)__popc(imask & ~(0xFFFFFFFFu << slot));
@@ -137,6 +140,13 @@ PT_DEV_NOINLINE bool bvh8_trace(const Bvh8Device& bvh, float3 o, float3 d, float
             const float ady = __uint_as_float(((n0.w >> 8) & 0xFFu) << 23) * idy;
             const float adz = __uint_as_float(((n0.w >> 16) & 0xFFu) << 23) * idz;
             const float ox = (px - o.x) * idx, oy = (py - o.y) * idy, oz = (pz - o.z) * idz;
+            // Additive pad per axis, the rule of the ray-queue kernel (trace_queue.cuh): the rounding error of a plane distance
+            // fma(q, a, o) scales with |o| and with the cell size |a|, not with the distance itself, so a purely relative slack
+            // is not conservative for short rays that start far from the node origin. 2.55e-4 |a| + 1e-6 |o| = 1e-6 of the largest
+            // plane distance of the axis (|t| <= |o| + 255 |a|).
+            const float ex = __fmaf_rn(fabsf(adx), 2.55e-4f, fabsf(ox) * 1.0e-6f), ey = __fmaf_rn(fabsf(ady), 2.55e-4f, fabsf(oy) * 1.0e-6f),
+                        ez = __fmaf_rn(fabsf(adz), 2.55e-4f, fabsf(oz) * 1.0e-6f);
+            const float oxn = ox - ex, oyn = oy - ey, ozn = oz - ez, oxf = ox + ex, oyf = oy + ey, ozf = oz + ez;
 
             uint32_t hitmask = 0;
 #pragma unroll
@@ -156,14 +166,14 @@ PT_DEV_NOINLINE bool bvh8_trace(const Bvh8Device& bvh, float3 o, float3 d, float
 #pragma unroll
                 for (int j = 0; j < 4; j++)
                 {
-                    const float tnx = __fmaf_rn(byte_to_float(nearx, j), adx, ox);
-                    const float tny = __fmaf_rn(byte_to_float(neary, j), ady, oy);
-                    const float tnz = __fmaf_rn(byte_to_float(nearz, j), adz, oz);
-                    const float tfx = __fmaf_rn(byte_to_float(farx, j), adx, ox);
-                    const float tfy = __fmaf_rn(byte_to_float(fary, j), ady, oy);
-                    const float tfz = __fmaf_rn(byte_to_float(farz, j), adz, oz);
-                    const float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f)) * 0.999999f;
-                    const float cmax = fminf(fminf(fminf(tfx, tfy), tfz) * 1.000001f, t_best);
+                    const float tnx = __fmaf_rn(byte_to_float(nearx, j), adx, oxn);
+                    const float tny = __fmaf_rn(byte_to_float(neary, j), ady, oyn);
+                    const float tnz = __fmaf_rn(byte_to_float(nearz, j), adz, ozn);
+                    const float tfx = __fmaf_rn(byte_to_float(farx, j), adx, oxf);
+                    const float tfy = __fmaf_rn(byte_to_float(fary, j), ady, oyf);
+                    const float tfz = __fmaf_rn(byte_to_float(farz, j), adz, ozf);
+                    const float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
+                    const float cmax = fminf(fminf(fminf(tfx, tfy), tfz), t_best);
                     if (cmin <= cmax)
                     {
                         const uint32_t child_bits = (child_bits4 >> (8 * j)) & 0xFFu;
@@ -208,7 +218,7 @@ PT_DEV_NOINLINE bool bvh8_trace(const Bvh8Device& bvh, float3 o, float3 d, float
                     hit.v = v;
                     if (ANY_HIT)
                     {
-                        PT_COUNT(if (counters) { atomicAdd(&counters->rays, 1ull); atomicAdd(&counters->nodes, (unsigned long long)n_nodes); atomicAdd(&counters->triangles, (unsigned long long)n_tris); })
+                        PT_COUNT(if (counters) { atomicAdd(&counters->rays, 1ull); atomicAdd(&counters->nodes, (unsigned long long)n_nodes); atomicAdd(&counters->triangles, (unsigned long long)n_tris); if (n_overflows) atomicAdd(&counters->overflows, (unsigned long long)n_overflows); })
                         return true;
                     }
                 }
@@ -223,7 +233,7 @@ PT_DEV_NOINLINE bool bvh8_trace(const Bvh8Device& bvh, float3 o, float3 d, float
         }
     }
 
-    PT_COUNT(if (counters) { atomicAdd(&counters->rays, 1ull); atomicAdd(&counters->nodes, (unsigned long long)n_nodes); atomicAdd(&counters->triangles, (unsigned long long)n_tris); })
+    PT_COUNT(if (counters) { atomicAdd(&counters->rays, 1ull); atomicAdd(&counters->nodes, (unsigned long long)n_nodes); atomicAdd(&counters->triangles, (unsigned long long)n_tris); if (n_overflows) atomicAdd(&counters->overflows, (unsigned long long)n_overflows); })
     return hit.prim >= 0;
 }
 

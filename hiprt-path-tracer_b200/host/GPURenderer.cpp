@@ -322,10 +322,17 @@ void GPURenderer::update()
         size_t presampled = (size_t)s.restir_di_settings.light_presampling.number_of_subsets * s.restir_di_settings.light_presampling.subset_size;
         m_restir_presampled_lights.resize(presampled);
         m_restir_presampled_lights.memset_zero();
+        // The buffers were reallocated (resolution change, or ReSTIR DI switched back on): the output pointer of the previous
+        // frame refers to freed memory. Re-point it to the (empty) first spatial buffer, as the reference does whenever it
+        // invalidates the reservoirs (ReSTIRDIRenderPass.cpp:195-207), and restart the ping-pong.
+        s.restir_di_settings.restir_output_reservoirs = m_restir_spatial_1.get_device_pointer();
+        m_restir_odd_frame = false;
     }
     else if (!restir && m_restir_initial.get_element_count() != 0)
     {
         m_restir_initial.free(); m_restir_spatial_1.free(); m_restir_spatial_2.free(); m_restir_presampled_lights.free();
+        s.restir_di_settings.restir_output_reservoirs = nullptr;
+        m_restir_odd_frame = false;
     }
 
     // internal_update_clear_device_status_buffers (GPURenderer.cpp:275-283)

@@ -84,7 +84,10 @@ class Context:
     def bvh_info(self, bvh):
         nodes, tris, sah, secs = C.c_uint(), C.c_uint(), C.c_float(), C.c_double()
         _capi.check(self.lib.b200pt_bvh_info(bvh, C.byref(nodes), C.byref(tris), C.byref(sah), C.byref(secs)), "b200pt_bvh_info")
-        return {"nodes": nodes.value, "triangles": tris.value, "sah_cost": sah.value, "build_seconds": secs.value}
+        st = S.BvhStats()
+        _capi.check(self.lib.b200pt_bvh_get_stats(bvh, C.byref(st)), "b200pt_bvh_get_stats")
+        return {"nodes": nodes.value, "triangles": tris.value, "sah_cost": sah.value, "build_seconds": secs.value, "max_depth": st.max_depth,
+                "node_fill": st.node_fill, "built_on_device": bool(st.built_on_device)}
 
     def destroy_bvh(self, bvh):
         self.lib.b200pt_bvh_destroy(self.handle, bvh)
@@ -99,6 +102,28 @@ class Context:
         _capi.check(self.lib.b200pt_trace_closest(self.handle, bvh, d_rays, d_last, C.c_longlong(n), d_prim, d_t, d_uv, None), "b200pt_trace_closest")
         out = self.download(d_prim, (n,), np.int32), self.download(d_t, (n,), np.float32), self.download(d_uv, (n, 2), np.float32)
         for p in (d_rays, d_last, d_prim, d_t, d_uv):
+            if p is not None:
+                self.free(p)
+        return out
+
+    def trace_queue(self, bvh, rays, t_max=None, last_prim=None):
+        """The same queries through the ray-queue traversal kernel FullPathTracer uses (b200pt_trace_queue). t_max None: closest hit,
+        returns (prim, t, uv); else any-hit, returns the occlusion flags."""
+        rays = np.ascontiguousarray(rays, dtype=np.float32)
+        n = len(rays)
+        d_rays = self.upload(rays)
+        d_tmax = self.upload(np.ascontiguousarray(t_max, dtype=np.float32)) if t_max is not None else None
+        d_last = self.upload(np.ascontiguousarray(last_prim, dtype=np.int32)) if last_prim is not None else None
+        if t_max is None:
+            d_prim, d_t, d_uv, d_occ = self.malloc(4 * n), self.malloc(4 * n), self.malloc(8 * n), None
+        else:
+            d_prim, d_t, d_uv, d_occ = None, None, None, self.malloc(n)
+        _capi.check(self.lib.b200pt_trace_queue(self.handle, bvh, d_rays, d_tmax, d_last, C.c_longlong(n), d_prim, d_t, d_uv, d_occ, None), "b200pt_trace_queue")
+        if t_max is None:
+            out = self.download(d_prim, (n,), np.int32), self.download(d_t, (n,), np.float32), self.download(d_uv, (n, 2), np.float32)
+        else:
+            out = self.download(d_occ, (n,), np.uint8)
+        for p in (d_rays, d_tmax, d_last, d_prim, d_t, d_uv, d_occ):
             if p is not None:
                 self.free(p)
         return out
@@ -131,13 +156,18 @@ class Context:
         _capi.check(self.lib.b200pt_path_profile_read(self.handle, out, C.c_int(1 if reset else 0)), "b200pt_path_profile_read")
         return {"trace": out[0], "surface": out[1], "sort": out[2], "shade": out[3]}
 
+    def set_trace_flavour(self, flavour):
+        """0 classic, 5 / 6 / 7 pipelined at that many blocks per SM, 1 pipelined default, -1 environment / built-in default."""
+        _capi.check(self.lib.b200pt_set_trace_flavour(self.handle, C.c_int(flavour)), "b200pt_set_trace_flavour")
+
     def counters_enable(self, enable=True):
         _capi.check(self.lib.b200pt_counters_enable(self.handle, C.c_int(1 if enable else 0)), "b200pt_counters_enable")
 
     def counters_read(self, reset=True):
         c = S.Counters()
         _capi.check(self.lib.b200pt_counters_read(self.handle, C.byref(c), C.c_int(1 if reset else 0)), "b200pt_counters_read")
-        return {"rays": c.rays, "nodes": c.nodes, "triangles": c.triangles}
+        return {"rays": c.rays, "nodes": c.nodes, "triangles": c.triangles, "stack_overflows": c.stack_overflows,
+                "queue_rays": c.queue_rays, "queue_nodes": c.queue_nodes, "queue_triangles": c.queue_triangles}
 
 
 class GPURenderer:

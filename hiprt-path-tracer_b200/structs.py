@@ -184,7 +184,13 @@ class Tile(C.Structure):
 
 
 class Counters(C.Structure):
-    _fields_ = [("rays", C.c_uint64), ("nodes", C.c_uint64), ("triangles", C.c_uint64)]
+    _fields_ = [("rays", C.c_uint64), ("nodes", C.c_uint64), ("triangles", C.c_uint64), ("stack_overflows", C.c_uint64),
+                ("queue_rays", C.c_uint64), ("queue_nodes", C.c_uint64), ("queue_triangles", C.c_uint64)]
+
+
+class BvhStats(C.Structure):
+    _fields_ = [("node_count", C.c_uint), ("triangle_count", C.c_uint), ("max_depth", i32), ("built_on_device", i32), ("sah_cost", C.c_float),
+                ("node_fill", C.c_float), ("build_seconds", C.c_double)]
 
 
 LSS = {"none": 0, "uniform": 1, "bsdf": 2, "mis": 3, "ris": 4, "restir_di": 5}

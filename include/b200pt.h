@@ -88,7 +88,23 @@ typedef struct b200pt_counters
     unsigned long long rays;        /* BVH queries: trace_ray iterations + shadow rays + shadow-light rays */
     unsigned long long nodes;       /* 80-byte BVH8 nodes fetched */
     unsigned long long triangles;   /* 48-byte triangles fetched */
+    unsigned long long stack_overflows;   /* traversal-stack pushes that found the stack full (a lost subtree): must be 0 */
+    unsigned long long queue_rays;        /* the share of the ray-queue traversal kernel (k_trace_queue), the kernel the */
+    unsigned long long queue_nodes;       /*   node-fetch roofline is reported for */
+    unsigned long long queue_triangles;
 } b200pt_counters;
+
+/* Shape of a built acceleration structure. max_depth bounds the traversal stacks: the ray-queue kernel needs at most
+ * 2 * max_depth entries of its 48; b200pt_bvh_build fails with B200PT_ERROR_INVALID_ARGUMENT for a deeper tree. */
+typedef struct b200pt_bvh_stats
+{
+    unsigned node_count, triangle_count;
+    int max_depth;
+    int built_on_device;            /* 1: the device builder (B200PT_BVH_BUILD_DEVICE), 0: the host SAH builder */
+    float sah_cost;
+    float node_fill;                /* occupied child slots / (8 * node_count) */
+    double build_seconds;
+} b200pt_bvh_stats;
 
 /* ---- context, memory, streams, events ------------------------------------------------------------------------ */
 B200PT_API int b200pt_device_count(void);
@@ -132,6 +148,7 @@ B200PT_API int b200pt_bvh_build(b200pt_ctx* ctx, const float* vertices, int vert
 B200PT_API int b200pt_bvh_destroy(b200pt_ctx* ctx, b200pt_bvh* bvh);
 B200PT_API void* b200pt_bvh_device_handle(b200pt_bvh* bvh);             /* value for HIPRTRenderData::geom */
 B200PT_API int b200pt_bvh_info(b200pt_bvh* bvh, unsigned* out_node_count, unsigned* out_triangle_count, float* out_sah_cost, double* out_build_seconds);
+B200PT_API int b200pt_bvh_get_stats(b200pt_bvh* bvh, b200pt_bvh_stats* out_stats);
 
 /* ---- kernels (names of the reference's kernels kept; src/Device/kernels) --------------------------------------- */
 B200PT_API int b200pt_kernel_variant_select(b200pt_ctx* ctx, const b200pt_options* options);
@@ -178,6 +195,16 @@ B200PT_API int b200pt_tonemap(b200pt_ctx* ctx, const float* d_hdr_rgb, int width
 /* rays: n x 6 floats (origin, direction) on the device. last_prim: n ints or NULL (-1). Outputs on the device. */
 B200PT_API int b200pt_trace_closest(b200pt_ctx* ctx, b200pt_bvh* bvh, const float* d_rays, const int* d_last_prim, long long n, int* d_out_prim, float* d_out_t, float* d_out_uv, b200pt_stream stream);
 B200PT_API int b200pt_trace_shadow(b200pt_ctx* ctx, b200pt_bvh* bvh, const float* d_rays, const float* d_t_max, const int* d_last_prim, long long n, unsigned char* d_out_occluded, b200pt_stream stream);
+/* The same queries through the ray-queue traversal kernel FullPathTracer uses (persistent warps, per-lane ray replacement), so that
+ * hit-id parity is pinned on the kernel the render runs. d_t_max == NULL: closest hit (d_out_prim / d_out_t / d_out_uv); else any-hit
+ * (d_out_occluded). Synchronises the stream before it returns (it owns temporary queue buffers). */
+B200PT_API int b200pt_trace_queue(b200pt_ctx* ctx, b200pt_bvh* bvh, const float* d_rays, const float* d_t_max, const int* d_last_prim, long long n, int* d_out_prim, float* d_out_t,
+                                  float* d_out_uv, unsigned char* d_out_occluded, b200pt_stream stream);
+
+/* Loop flavour of the ray-queue traversal kernel: 0 = classic (load, wait, test), 5 / 6 / 7 = software-pipelined (every load issued one
+ * iteration ahead) compiled for that many resident blocks per SM, 1 = the pipelined default, -1 = B200PT_TRACE_PIPELINE / built-in default.
+ * A scheduling choice only: hit records are identical in every flavour. Process-wide. */
+B200PT_API int b200pt_set_trace_flavour(b200pt_ctx* ctx, int flavour);
 
 /* ---- counters (counting build of the same kernels; the timing build has them compiled out) --------------------- */
 B200PT_API int b200pt_counters_enable(b200pt_ctx* ctx, int enable);

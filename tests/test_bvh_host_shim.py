@@ -25,3 +25,24 @@ def shim_binary(tmp_path_factory):
 def test_traversal_equals_brute_force(shim_binary, mode):
     r = subprocess.run([shim_binary, str(mode)], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout + r.stderr
+
+
+@pytest.fixture(scope="module")
+def queue_shim_binary(tmp_path_factory):
+    cuda_inc = "/usr/local/cuda/include"
+    if not os.path.exists(os.path.join(cuda_inc, "cuda_runtime.h")):
+        pytest.skip("CUDA headers not installed")
+    out = str(tmp_path_factory.mktemp("shim") / "trace_queue_host_test")
+    cmd = ["g++", "-std=c++17", "-O1", "-fopenmp", "-I", cuda_inc, "-I", CSRC, "-I", os.path.join(ROOT, "include"),
+           os.path.join(ROOT, "tests", "host_shim", "trace_queue_host_test.cpp"), os.path.join(CSRC, "bvh8_build.cpp"), "-o", out]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+    return out
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2, 3])
+def test_ray_queue_loop_flavours_equal_brute_force(queue_shim_binary, mode):
+    """Both loops of the ray-queue traversal kernel (classic and software-pipelined, csrc/trace_queue.cuh) as a warp of one lane on
+    the host: closest hits (id, t bit-equal, triangle slot) and occlusion flags against a brute-force loop over all triangles."""
+    r = subprocess.run([queue_shim_binary, str(mode)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr

@@ -78,6 +78,110 @@ def test_oracle_ray_batches_closest_and_shadow(pt, wl, ctx, ref):
     g.close()
 
 
+def _assert_hits_equal(prim, t, log, what):
+    ties = (prim != log["hit_prim"]) & (t == log["t"])
+    bad = ~((prim == log["hit_prim"]) | ties)
+    assert not bad.any(), f"{what}: {int(bad.sum())} hit-id mismatches of {len(prim)} rays ({int(ties.sum())} exact-distance ties excluded)"
+    same = prim == log["hit_prim"]
+    assert np.array_equal(t[same], log["t"][same]), f"{what}: hit distances differ in their bits"
+
+
+def test_trace_queue_flavours_agree(pt, wl, ctx, ref):
+    """The ray-queue traversal kernel (the kernel FullPathTracer traces with) in each loop flavour -- classic, pipelined at 5 / 6 / 7
+    resident blocks per SM -- against the oracle's logged rays: same ids, same bits of t and uv as the per-thread traversal."""
+    cfg = wl.cornell(256, 192)
+    r = wl.setup_oracle(ref, pt.structs, cfg)
+    g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="cpu")
+    r.ray_log_begin(1_000_000, 1)
+    r.render(1)
+    log = r.ray_log_end(1_000_000)
+    prim0, t0, uv0 = ctx.trace_closest(g.bvh, log["rays"], log["last_prim"])
+    rng = np.random.default_rng(5)
+    n = len(log["rays"])
+    t_max = np.where(log["t"] > 0, log["t"] * rng.uniform(0.5, 1.5, n).astype(np.float32), rng.uniform(0.1, 10.0, n).astype(np.float32)).astype(np.float32)
+    occ0 = ctx.trace_shadow(g.bvh, log["rays"], t_max, log["last_prim"])
+    ctx.counters_enable(True)
+    ctx.counters_read(True)
+    try:
+        for flavour in (0, 5, 6, 7):
+            ctx.set_trace_flavour(flavour)
+            prim, t, uv = ctx.trace_queue(g.bvh, log["rays"], None, log["last_prim"])
+            _assert_hits_equal(prim, t, log, f"flavour {flavour}")
+            assert np.array_equal(prim, prim0) and np.array_equal(t, t0) and np.array_equal(uv, uv0), f"flavour {flavour} differs from the per-thread traversal"
+            occ = ctx.trace_queue(g.bvh, log["rays"], t_max, log["last_prim"])
+            assert np.array_equal(occ, occ0), f"flavour {flavour}: occlusion flags differ"
+        c = ctx.counters_read(True)
+        assert c["stack_overflows"] == 0 and c["queue_rays"] == 8 * n
+    finally:
+        ctx.set_trace_flavour(-1)
+        ctx.counters_enable(False)
+    g.close()
+
+
+def test_c3_hit_ids_on_the_10m_triangle_bvh(pt, wl, ctx, ref):
+    """SURVEY 8(d) C3 at its stated size: the 9 998 802-triangle scene's own BVH8 (about a million nodes: the deepest tree, the stack
+    spill path and the SAH collapse are only stressed here). >= 2e6 primary + bounce + shadow rays logged from the reference's CPU
+    render of that scene are traced through the per-thread traversal and through the ray-queue kernel: ids and t bit-exact,
+    occlusion predicates equal, no traversal-stack overflow."""
+    cfg = wl.synthetic(480, 270)
+    r = wl.setup_oracle(ref, pt.structs, cfg)
+    bvh = ctx.build_bvh(cfg["scene"].vertices, cfg["scene"].indices)
+    info = ctx.bvh_info(bvh)
+    assert info["triangles"] == 9_998_802 and 2 * info["max_depth"] + 1 <= 48, info
+    r.ray_log_begin(3_000_000, 1)
+    r.render(3)
+    log = r.ray_log_end(3_000_000)
+    n = len(log["rays"])
+    assert n >= 2_000_000, n
+    ctx.counters_enable(True)
+    ctx.counters_read(True)
+    try:
+        prim, t, _ = ctx.trace_closest(bvh, log["rays"], log["last_prim"])
+        _assert_hits_equal(prim, t, log, "per-thread traversal")
+        for flavour in (0, 6):
+            ctx.set_trace_flavour(flavour)
+            qprim, qt, _ = ctx.trace_queue(bvh, log["rays"], None, log["last_prim"])
+            _assert_hits_equal(qprim, qt, log, f"ray-queue kernel, flavour {flavour}")
+            assert np.array_equal(qprim, prim) and np.array_equal(qt, t)
+        rng = np.random.default_rng(11)
+        m = 500_000
+        rays, last = log["rays"][:m], log["last_prim"][:m]
+        t_max = np.where(log["t"][:m] > 0, log["t"][:m] * rng.uniform(0.5, 1.5, m).astype(np.float32), rng.uniform(0.1, 50.0, m).astype(np.float32)).astype(np.float32)
+        occ_ref = r.trace_shadow(rays, t_max, last)
+        assert np.array_equal(ctx.trace_shadow(bvh, rays, t_max, last), occ_ref)
+        assert np.array_equal(ctx.trace_queue(bvh, rays, t_max, last), occ_ref)
+        c = ctx.counters_read(True)
+        assert c["stack_overflows"] == 0, c
+    finally:
+        ctx.set_trace_flavour(-1)
+        ctx.counters_enable(False)
+        ctx.destroy_bvh(bvh)
+
+
+def test_c2_size_ray_batches(pt, wl, ctx, ref):
+    """SURVEY 8(d) C2 check (i) at its stated size: the 2 073 600 primary rays of the 1920x1080 Cornell frame and >= 1e7 bounce /
+    shadow rays the reference's CPU render traces for it, hit ids bit-compared (exact-distance ties excluded)."""
+    cfg = wl.cornell(1920, 1080)
+    r = wl.setup_oracle(ref, pt.structs, cfg)
+    g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="cpu")
+    cap = 16_000_000
+    r.ray_log_begin(cap, 1)
+    r.render(3)
+    log = r.ray_log_end(cap)
+    n = len(log["rays"])
+    assert n >= 2_073_600 + 10_000_000, n
+    assert int((log["last_prim"] == -1).sum()) >= 2_073_600          # camera rays leave from no primitive
+    ctx.counters_enable(True)
+    ctx.counters_read(True)
+    try:
+        prim, t, _ = ctx.trace_queue(g.bvh, log["rays"], None, log["last_prim"])
+        _assert_hits_equal(prim, t, log, "ray-queue kernel")
+        assert ctx.counters_read(True)["stack_overflows"] == 0
+    finally:
+        ctx.counters_enable(False)
+    g.close()
+
+
 def test_frame_parity_per_sample(pt, wl, ctx, ref):
     """Matched RNG streams (CPU seed schedule): G-buffer identical, radiance within the north-star tolerance."""
     cfg = wl.cornell(256, 192)
