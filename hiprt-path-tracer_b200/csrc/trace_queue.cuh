@@ -96,7 +96,7 @@ PT_DEV uint32_t node_hitmask(const uint4 n0, const uint4 n1, const uint4 n2, con
     const float ex = __fmaf_rn(fabsf(adx), 2.2384186e-6f, fabsf(ox) * 1.0e-6f), ey = __fmaf_rn(fabsf(ady), 2.2384186e-6f, fabsf(oy) * 1.0e-6f),
                 ez = __fmaf_rn(fabsf(adz), 2.2384186e-6f, fabsf(oz) * 1.0e-6f);
     const float oxn = ox - ex, oyn = oy - ey, ozn = oz - ez, oxf = ox + ex, oyf = oy + ey, ozf = oz + ez;
-    const bool neg_x = r.d.x < 0.0f, neg_y = r.d.y < 0.0f, neg_z = r.d.z < 0.0f;
+    const bool neg_x = r.idx < 0.0f, neg_y = r.idy < 0.0f, neg_z = r.idz < 0.0f;     // signs of the reciprocals: -0.0 counts as negative (traverse.cuh)
     const uint32_t oct_inv4 = r.oct_inv * 0x01010101u;
 
     uint32_t hitmask = 0;
@@ -172,7 +172,7 @@ PT_DEV void trace_queue_load_ray(const RayQueueView& q, const uint32_t ray_id, c
     r.idx = 1.0f / (fabsf(r.d.x) > kTiny ? r.d.x : copysignf(kTiny, r.d.x));
     r.idy = 1.0f / (fabsf(r.d.y) > kTiny ? r.d.y : copysignf(kTiny, r.d.y));
     r.idz = 1.0f / (fabsf(r.d.z) > kTiny ? r.d.z : copysignf(kTiny, r.d.z));
-    r.oct_inv = (r.d.x > 0.0f ? 1u : 0u) | (r.d.y > 0.0f ? 2u : 0u) | (r.d.z > 0.0f ? 4u : 0u);
+    r.oct_inv = (r.idx > 0.0f ? 1u : 0u) | (r.idy > 0.0f ? 2u : 0u) | (r.idz > 0.0f ? 4u : 0u);
 }
 
 template <bool ANY_HIT>

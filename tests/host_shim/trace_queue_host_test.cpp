@@ -110,6 +110,8 @@ int main(int argc, char** argv)
         float3 dir = make_float3(frand() - 0.5f, (frand() - 0.5f) * (mode == 1 ? 0.3f : 1.0f), frand() - 0.5f);
         if (r % 7 == 0) dir.x = 0.0f;
         if (r % 11 == 0) dir.z = 0.0f;
+        if (r % 13 == 0) dir.z = -0.0f;     // negative zero: its reciprocal is negative although it does not compare below zero
+        if (r % 17 == 0) dir.x = -0.0f;
         float l = sqrtf(dir.x * dir.x + dir.y * dir.y + dir.z * dir.z);
         if (l == 0.0f) { dir = make_float3(0, -1, 0); l = 1.0f; }
         dir.x /= l; dir.y /= l; dir.z /= l;
