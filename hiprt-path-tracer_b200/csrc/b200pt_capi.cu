@@ -361,3 +361,4 @@ int b200pt_event_elapsed_ms(b200pt_ctx* ctx, b200pt_event start, b200pt_event st
 } // extern "C"
 
 #include "b200pt_capi_scene.inl"
+#include "b200pt_capi_noalloc.inl"

@@ -128,6 +128,12 @@ class Context:
                 self.free(p)
         return out
 
+    STATIC_MAX_RAYS = 262144     # B200PT_TRACE_QUEUE_STATIC_MAX_RAYS (include/b200pt.h)
+
+    def trace_queue_static(self, bvh, d_rays, d_t_max, d_last_prim, n, d_prim, d_t, d_uv, d_occluded):
+        """b200pt_trace_queue_static on DEVICE buffers the caller owns (the entry point itself allocates nothing). Asynchronous."""
+        _capi.check(self.lib.b200pt_trace_queue_static(self.handle, bvh, d_rays, d_t_max, d_last_prim, C.c_longlong(n), d_prim, d_t, d_uv, d_occluded, None), "b200pt_trace_queue_static")
+
     def trace_shadow(self, bvh, rays, t_max, last_prim=None):
         rays = np.ascontiguousarray(rays, dtype=np.float32)
         n = len(rays)

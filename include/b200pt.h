@@ -201,6 +201,16 @@ B200PT_API int b200pt_trace_shadow(b200pt_ctx* ctx, b200pt_bvh* bvh, const float
 B200PT_API int b200pt_trace_queue(b200pt_ctx* ctx, b200pt_bvh* bvh, const float* d_rays, const float* d_t_max, const int* d_last_prim, long long n, int* d_out_prim, float* d_out_t,
                                   float* d_out_uv, unsigned char* d_out_occluded, b200pt_stream stream);
 
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc (CUDA graph
+ * capture, tight serving loops, harnesses that forbid it). The same query as b200pt_trace_queue, same outputs bit for bit, but it allocates
+ * NOTHING (no cudaMalloc / cudaFree / allocating library call): its queue scratch is one file-scope static __device__ array sized for
+ * B200PT_TRACE_QUEUE_STATIC_MAX_RAYS rays (56 B per ray, about 14 MiB, held by every GPU that loads the library until exit). n beyond that
+ * maximum is rejected with B200PT_ERROR_INVALID_ARGUMENT and a message naming the limit. Asynchronous on `stream`. Every call shares the array
+ * (each call rewrites all it reads and zeroes its work cursor): calls that overlap on the GPU race -- serialise them. */
+#define B200PT_TRACE_QUEUE_STATIC_MAX_RAYS 262144
+B200PT_API int b200pt_trace_queue_static(b200pt_ctx* ctx, b200pt_bvh* bvh, const float* d_rays, const float* d_t_max, const int* d_last_prim, long long n, int* d_out_prim, float* d_out_t,
+                                         float* d_out_uv, unsigned char* d_out_occluded, b200pt_stream stream);
+
 /* Loop flavour of the ray-queue traversal kernel: 0 = classic (load, wait, test), 5 / 6 / 7 = software-pipelined (every load issued one
  * iteration ahead) compiled for that many resident blocks per SM, 1 = the pipelined default, -1 = B200PT_TRACE_PIPELINE / built-in default.
  * A scheduling choice only: hit records are identical in every flavour. Process-wide. */
