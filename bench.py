@@ -3,7 +3,9 @@
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cornell]
 
-A "step" is one sample pass of the whole 1080p frame per GPU (two launch points: CameraRays, FullPathTracer; the latter
+A "step" is one frame = one call of the renderer's render() = `--samples-per-frame` (default 8) sample passes of the whole
+1080p frame per GPU, the reference's samples_per_frame setting (GPURenderer::render, src/Renderer/GPURenderer.cpp:408-464; per pass
+two launch points: CameraRays, FullPathTracer; here a frame's passes run as fused sample batches where the options allow it; the path tracer
 runs as a wavefront of per-bounce kernels: ray-queue traversal, surface, queue sort, shading phases).
 Metric (BASELINE.json): Mrays/s = BVH queries (trace_ray iterations + shadow rays + shadow-light rays)
 per second, whole job. Rays are counted by the counting build of the SAME kernels on the SAME seeds in an untimed
@@ -109,7 +111,8 @@ def C_int(v):
 def workload_config(cfg, args, extra=None):
     """`config` of the JSON line: the same keys on the GPU arm and on the reference arm."""
     out = {"workload": cfg["name"], "width": cfg["width"], "height": cfg["height"], "nb_bounces": cfg["settings"].get("nb_bounces", 8),
-           "kernel_options": cfg["options"], "step": "one sample pass (1 spp) of the frame"}
+           "kernel_options": cfg["options"], "samples_per_frame": cfg["settings"].get("samples_per_frame", 1),
+           "step": "one frame = samples_per_frame sample passes (1 spp each) of the whole image"}
     out.update(extra or {})
     return out
 
@@ -132,7 +135,8 @@ def run_reference(args, cfg, pt):
     sample = f"{args.steps} sample passes of the {frame} of {cfg['name']} (one step = 1 spp), OpenMP over rows on {cores} threads"
     return {
         "impl": "reference", "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": dt / args.steps * 1e3 * shrink, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        # a step of the GPU arm is a frame of samples_per_frame passes of the whole image: the bounded sample's time, scaled to that size
+        "ms_per_step": dt / args.steps * 1e3 * shrink * cfg["settings"].get("samples_per_frame", 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(cfg, args), "samples_per_px_per_s": args.steps / dt / shrink,
         "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": "reference", "sample": sample},
         "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -167,6 +171,8 @@ def run_ours(args, cfg, pt):
     g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="gpu")
     lib = ctx.lib
     bvh_info = ctx.bvh_info(g.bvh)
+    in_flight = int(os.environ.get("B200PT_SAMPLES_IN_FLIGHT", "8"))
+    batched = g.renders_sample_batches
 
     def restart():
         # Sample-pass sharding: every rank draws its per-launch seeds from its own host stream, so the ranks render independent
@@ -359,7 +365,13 @@ def run_ours(args, cfg, pt):
     has_lights, has_env = len(cfg["scene"].emissive) > 0, cfg["envmap"] is not None and cfg["options"]["ess"] != "none"
     # (shadow rays and NEE light rays of a bounce share one launch: k_trace_queue_pair)
     per_bounce = 2 + 2 * has_lights + 2 * has_env + (1 if (has_lights or has_env) else 0) + 1
-    launches_per_step = 1 + lanes * ((1 + per_bounce) + nb * (2 + per_bounce)) + (3 if restir else 0)      # every path lane launches its own band
+    spf = cfg["settings"].get("samples_per_frame", 1)
+    if batched:
+        # fused sample batches: per lane and batch camera + trace + camera-surface, the bounce chain once for all passes in flight, accumulate
+        batches = -(-spf // max(1, in_flight))
+        launches_per_step = batches * lanes * (3 + per_bounce + nb * (2 + per_bounce) + 1)
+    else:
+        launches_per_step = spf * (1 + lanes * ((1 + per_bounce) + nb * (2 + per_bounce)) + (3 if restir else 0))      # every path lane launches its own band
     out = {
         "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "strong" if (world > 1 and sharding in ("tiles", "columns")) else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -367,8 +379,8 @@ def run_ours(args, cfg, pt):
                                                                       else (f"column-tile sharding x{world}, frame gathered once per output; e2e reads the whole accumulation buffer back (a column band is strided)") if sharding == "columns"
                                                                       else f"sample-pass sharding x{world}, accumulation all-reduce") + ", scene+BVH replicated",
                    "l2": "inputs larger than L2: the per-step G-buffer round trip is 345 B/px = 715 MB at 1080p (L2 = 126 MB)",
-                   "bvh": bvh_info, "path_lanes": lanes, "rays_per_step_per_gpu": rays_per_step, "allreduce_ms": reduce_ms},
-        "samples_per_px_per_s": (1 if (world > 1 and sharding in ("tiles", "columns")) else world) * args.steps / (elapsed_ms * 1e-3),
+                   "bvh": bvh_info, "path_lanes": lanes, "samples_in_flight": in_flight if batched else 0, "rays_per_step_per_gpu": rays_per_step, "allreduce_ms": reduce_ms},
+        "samples_per_px_per_s": (1 if (world > 1 and sharding in ("tiles", "columns")) else world) * spf * args.steps / (elapsed_ms * 1e-3),
         "gpu_launches": launches_per_step * args.steps,
         "clocks": clocks,
         "e2e": {"value": total_rays / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 2 * 1328 + 196, "d2h_bytes_per_step": W * own_rows * 12},
@@ -410,6 +422,7 @@ def main():
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--sharding", default="auto", choices=["auto", "samples", "tiles", "columns"],
                     help="N > 1: sample-pass sharding (weak scaling, default for cornell), column tiles (strong scaling, default otherwise) or row tiles (strong scaling; always for ReSTIR DI)")
+    ap.add_argument("--samples-per-frame", type=int, default=8, help="sample passes per step (= per render() call): the reference's samples_per_frame render setting")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile", action="store_true", help="for ncu: run only 3 warm-up + K frames of the timed pass (no counting / stage / e2e / CPU passes), print no bench line")
     args = ap.parse_args()
@@ -417,6 +430,7 @@ def main():
     pt = importlib.import_module("hiprt-path-tracer_b200")
     wl = importlib.import_module("hiprt-path-tracer_b200.workloads")
     cfg = getattr(wl, args.workload)(args.width, args.height)
+    cfg["settings"]["samples_per_frame"] = args.samples_per_frame
 
     if args.impl == "reference":
         if int(os.environ.get("RANK", 0)) != 0:

@@ -75,15 +75,15 @@ API_SYMBOLS = [
     "b200pt_host_alloc_pinned", "b200pt_host_free_pinned", "b200pt_stream_create", "b200pt_stream_destroy", "b200pt_stream_query",
     "b200pt_stream_sync", "b200pt_event_create", "b200pt_event_destroy", "b200pt_event_record", "b200pt_event_elapsed_ms",
     "b200pt_tex2d_create", "b200pt_tex3d_create", "b200pt_tex_destroy", "b200pt_tex2d_array_create", "b200pt_bvh_build",
-    "b200pt_bvh_destroy", "b200pt_bvh_device_handle", "b200pt_bvh_info", "b200pt_bvh_get_stats", "b200pt_kernel_variant_select", "b200pt_set_path_mode", "b200pt_path_profile_enable", "b200pt_path_profile_read", "b200pt_launch_CameraRays",
-    "b200pt_launch_FullPathTracer", "b200pt_launch_FullPathTracer_lane", "b200pt_stream_wait_event", "b200pt_launch_ReSTIR_DI_LightsPresampling", "b200pt_launch_ReSTIR_DI_InitialCandidates",
+    "b200pt_bvh_destroy", "b200pt_bvh_device_handle", "b200pt_bvh_info", "b200pt_bvh_get_stats", "b200pt_kernel_variant_select", "b200pt_set_path_mode", "b200pt_get_path_mode", "b200pt_path_profile_enable", "b200pt_path_profile_read", "b200pt_launch_CameraRays",
+    "b200pt_launch_FullPathTracer", "b200pt_launch_FullPathTracer_lane", "b200pt_launch_PathTraceSamples", "b200pt_stream_wait_event", "b200pt_launch_ReSTIR_DI_LightsPresampling", "b200pt_launch_ReSTIR_DI_InitialCandidates",
     "b200pt_launch_ReSTIR_DI_SpatiotemporalReuse", "b200pt_launch_ReSTIR_DI_TemporalReuse", "b200pt_launch_ReSTIR_DI_SpatialReuse", "b200pt_tonemap", "b200pt_trace_closest", "b200pt_trace_shadow", "b200pt_trace_queue", "b200pt_trace_queue_static", "b200pt_set_trace_flavour", "b200pt_counters_enable",
     "b200pt_counters_read",
 ]
 HOST_API_SYMBOLS = [
     "b200pt_host_last_error", "b200pt_renderer_create", "b200pt_renderer_destroy", "b200pt_renderer_set_seed_schedule", "b200pt_renderer_set_rng_seed",
     "b200pt_renderer_set_kernel_options", "b200pt_renderer_set_brdf_luts", "b200pt_renderer_add_texture", "b200pt_renderer_set_scene",
-    "b200pt_renderer_set_envmap", "b200pt_host_compute_alias_table", "b200pt_renderer_set_camera", "b200pt_renderer_resize", "b200pt_renderer_set_tile", "b200pt_renderer_set_tile_halo", "b200pt_renderer_set_path_lanes", "b200pt_renderer_path_lanes",
+    "b200pt_renderer_set_envmap", "b200pt_host_compute_alias_table", "b200pt_renderer_set_camera", "b200pt_renderer_resize", "b200pt_renderer_set_tile", "b200pt_renderer_set_tile_halo", "b200pt_renderer_set_path_lanes", "b200pt_renderer_path_lanes", "b200pt_renderer_set_samples_in_flight", "b200pt_renderer_renders_sample_batches",
     "b200pt_renderer_reset", "b200pt_renderer_render_settings", "b200pt_renderer_world_settings", "b200pt_renderer_bsdfs_data",
     "b200pt_renderer_render_data", "b200pt_renderer_bvh", "b200pt_renderer_render_frame", "b200pt_renderer_synchronize",
     "b200pt_renderer_last_frame_ms", "b200pt_renderer_last_kernel_ms", "b200pt_renderer_download", "b200pt_renderer_device_pointer",

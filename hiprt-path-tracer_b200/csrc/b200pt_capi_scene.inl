@@ -216,7 +216,7 @@ static int ensure_wavefront(b200pt_ctx* ctx, int lane, uint32_t paths, uint32_t 
         return p;
     };
     const size_t n = capacity;
-    float4** f4[] = {&wf.origin_rng, &wf.dir_prim, &wf.throughput, &wf.color, &wf.hit_point, &wf.hit_ns, &wf.hit_ng};
+    float4** f4[] = {&wf.origin_rng, &wf.dir_prim, &wf.throughput, &wf.color, &wf.hit_point, &wf.hit_ns, &wf.hit_ng, &wf.final_color, &wf.aov_normal, &wf.aov_albedo};
     bool ok = true;
     for (float4** a : f4)
         ok &= (*a = static_cast<float4*>(alloc(n * sizeof(float4)))) != nullptr;
@@ -287,6 +287,13 @@ int b200pt_set_path_mode(b200pt_ctx* ctx, int mode)
     return B200PT_SUCCESS;
 }
 
+int b200pt_get_path_mode(b200pt_ctx* ctx, int* out_mode)
+{
+    REQUIRE(ctx != nullptr && out_mode != nullptr);
+    *out_mode = ctx->path_mode;
+    return B200PT_SUCCESS;
+}
+
 int b200pt_launch_FullPathTracer(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream)
 {
     return b200pt_launch_FullPathTracer_lane(ctx, render_data, res, tile, stream, 0, 1);
@@ -308,6 +315,9 @@ int b200pt_launch_FullPathTracer_lane(b200pt_ctx* ctx, const HIPRTRenderData* re
             ctx->wf[lane].grid_share = (uint32_t)lane_count;
             static const bool slot_materials = [] { const char* v = getenv("B200PT_SLOT_MATERIALS"); return v && atoi(v) != 0; }();
             ctx->wf[lane].force_slot_materials = slot_materials ? 1u : 0u;
+            ctx->wf[lane].fused_camera = 0u;
+            ctx->wf[lane].samples = 1u;
+            ctx->wf[lane].tile_pixels = (uint32_t)(wt.x1 - wt.x0) * (uint32_t)(wt.y1 - wt.y0);
         }
     }
     if (ctx->profiling && lane_count > 1)
@@ -322,6 +332,70 @@ int b200pt_launch_FullPathTracer_lane(b200pt_ctx* ctx, const HIPRTRenderData* re
     }
     pt::WavefrontProfile* profile = ctx->profiling ? &ctx->profile : nullptr;
     LAUNCH_PIXEL_KERNEL(launch_FullPathTracer, , &ctx->wf[lane], ctx->path_mode, profile)
+}
+
+int b200pt_launch_PathTraceSamples(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream, const b200pt_sample_batch* batch, int lane,
+                                   int lane_count)
+{
+    REQUIRE(ctx != nullptr && render_data != nullptr && batch != nullptr && res.x > 0 && res.y > 0);
+    REQUIRE(render_data->geom != nullptr);
+    REQUIRE(lane_count >= 1 && lane_count <= b200pt_ctx::kMaxPathLanes && lane >= 0 && lane < lane_count);
+    REQUIRE(batch->count >= 1 && batch->count <= pt::kMaxSamplesInFlight);
+    const HIPRTRenderSettings& rs = render_data->render_settings;
+    REQUIRE(rs.nb_bounces >= 0);
+    // A pass of the batch must not depend on the previous pass' result, and the phased MIS pipeline must be the one that runs
+    const bool adaptive_buffers = (rs.stop_pixel_noise_threshold > 0.0f || rs.enable_adaptive_sampling) && rs.accumulate;
+    const bool low_resolution = rs.wants_render_low_resolution && rs.allow_render_low_resolution && rs.accumulate;
+    if (ctx->options.lss != 3 || ctx->path_mode != pt::WF_PHASED || rs.number_of_light_samples != 1 || rs.do_alpha_testing || adaptive_buffers || low_resolution)
+        return fail(B200PT_ERROR_VARIANT_NOT_COMPILED, "b200pt_launch_PathTraceSamples: fused sample batches need LSS_MIS_LIGHT_BSDF in the phased wavefront shape with one light sample, "
+                                                        "no alpha testing, no adaptive sampling / pixel noise threshold and no low-resolution rendering; launch CameraRays and FullPathTracer separately");
+    pt::Tile t = tile_of(tile, res);
+    if (t.x1 <= t.x0 || t.y1 <= t.y0)
+        return B200PT_SUCCESS;
+    const uint32_t tile_pixels = (uint32_t)(t.x1 - t.x0) * (uint32_t)(t.y1 - t.y0);
+    REQUIRE((unsigned long long)tile_pixels * (unsigned)batch->count < (1ull << 30));     // NEE ray ids are 3 * capacity + slot in 32 bits
+    int rc = ensure_wavefront(ctx, lane, tile_pixels * (uint32_t)batch->count, (uint32_t)rs.nb_bounces);
+    if (rc != B200PT_SUCCESS)
+        return rc;
+    pt::WavefrontState& wf = ctx->wf[lane];
+    wf.grid_share = (uint32_t)lane_count;
+    wf.force_slot_materials = 0u;
+    wf.fused_camera = 1u;
+    wf.samples = (uint32_t)batch->count;
+    wf.tile_pixels = tile_pixels;
+    pt::SampleBatch b;
+    memset(&b, 0, sizeof(b));
+    b.count = (uint32_t)batch->count;
+    for (int i = 0; i < batch->count; i++)
+    {
+        b.camera_seed[i] = batch->camera_seeds[i];
+        b.path_seed[i] = batch->path_seeds[i];
+        b.sample_number[i] = batch->sample_numbers[i];
+        b.aov_counter[i] = batch->aov_counters[i];
+    }
+    b.write_g_buffer = batch->write_g_buffer ? 1u : 0u;
+    if (ctx->profiling && lane_count > 1)
+        return fail(B200PT_ERROR_INVALID_ARGUMENT, "per-stage profiling needs a single path lane (the stages of concurrent lanes overlap)");
+    if (ctx->profiling)
+    {
+        rc = b200pt_path_profile_read(ctx, nullptr, 0);
+        if (rc != B200PT_SUCCESS)
+            return rc;
+        ctx->profile.count = 0;
+    }
+    pt::WavefrontProfile* profile = ctx->profiling ? &ctx->profile : nullptr;
+    cudaError_t e;
+    if (ctx->counting)
+    {
+        HIPRTRenderData copy = *render_data;
+        copy.hiprt_function_table = ctx->d_counters;
+        e = pt::launch_PathTraceSamples_c(ctx->options, &copy, make_int2(res.x, res.y), t, stream_of(ctx, stream), &wf, &b, profile);
+    }
+    else
+        e = pt::launch_PathTraceSamples_t(ctx->options, render_data, make_int2(res.x, res.y), t, stream_of(ctx, stream), &wf, &b, profile);
+    if (e != cudaSuccess)
+        return cuda_fail(e, "launch_PathTraceSamples");
+    return B200PT_SUCCESS;
 }
 
 int b200pt_path_profile_enable(b200pt_ctx* ctx, int enable)

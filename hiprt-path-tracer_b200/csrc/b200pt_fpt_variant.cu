@@ -101,9 +101,38 @@ __global__ void __launch_bounds__(128) PT_VARIANT_NAME(k_wf_surface)(const __gri
         wf_surface_path<PT_ESS>(rd, res, tile, wf, bounce, i);
 }
 
+// ---- sample batches (wavefront.cuh): camera rays of every pass in flight, camera hits, accumulation in pass order --------------------
+__global__ void __launch_bounds__(128) PT_VARIANT_NAME(k_wf_camera)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf,
+                                                                   const __grid_constant__ SampleBatch batch)
+{
+    const uint32_t total = wf.tile_pixels * batch.count;
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+        wf.counts[0] = total;             // length of the primary-ray queue (identity), read by the ray-queue kernel and CAMERA_SURFACE
+    for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < total; slot += gridDim.x * blockDim.x)
+        wf_camera_slot(rd, res, tile, wf, batch, slot);
+}
+
+__global__ void __launch_bounds__(128) PT_VARIANT_NAME(k_wf_camera_surface)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf,
+                                                                           const __grid_constant__ SampleBatch batch)
+{
+    const int bounce = 0;
+    PT_FOR_EACH_QUEUED(i, wf.counts[0], 8)
+        wf_camera_surface_path<PT_ESS>(rd, res, tile, wf, batch, i);
+}
+
+__global__ void __launch_bounds__(128) PT_VARIANT_NAME(k_wf_accumulate)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf,
+                                                                       const __grid_constant__ SampleBatch batch)
+{
+    for (uint32_t local = blockIdx.x * blockDim.x + threadIdx.x; local < wf.tile_pixels; local += gridDim.x * blockDim.x)
+        wf_accumulate_pixel(rd, res, tile, wf, batch, local);
+}
+
 #endif
 
-cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const WavefrontState* wf, int mode, WavefrontProfile* profile)
+// batch == nullptr: FullPathTracer alone, on the G-buffer a CameraRays launch left (the reference's two launch points).
+// batch != nullptr: b200pt_launch_PathTraceSamples, `batch->count` passes of CameraRays + FullPathTracer as one wavefront (phased MIS only).
+cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const WavefrontState* wf, int mode, WavefrontProfile* profile,
+                                                   const SampleBatch* batch)
 {
     auto stage = [&](int s) {
         if (profile && profile->count < profile->capacity)
@@ -122,8 +151,10 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
     int nb_bounces = rd->render_settings.nb_bounces;
     if (rd->render_settings.wants_render_low_resolution && rd->render_settings.allow_render_low_resolution && rd->render_settings.accumulate)
         nb_bounces = nb_bounces < 3 ? nb_bounces : 3;
-    const uint32_t paths = (uint32_t)(tile.x1 - tile.x0) * (uint32_t)(tile.y1 - tile.y0);
+    const uint32_t paths = (uint32_t)(tile.x1 - tile.x0) * (uint32_t)(tile.y1 - tile.y0) * (batch ? batch->count : 1u);
     if (paths > wf->capacity || (uint32_t)nb_bounces > wf->max_bounces)
+        return cudaErrorInvalidValue;
+    if (batch && (mode != WF_PHASED || PT_LSS != 3 || wf->fused_camera == 0u || wf->samples != batch->count))
         return cudaErrorInvalidValue;
 
     // Queue lengths are only known on the device: queue kernels run grid-stride loops on a grid capped at a few blocks per
@@ -151,6 +182,8 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
 #else
     const bool phased_mis = false;
 #endif
+    if (batch && !phased_mis)
+        return cudaErrorInvalidValue;
 #ifdef PT_COUNTERS
     TraversalCounters* const counters = reinterpret_cast<TraversalCounters*>(rd->hiprt_function_table);
 #else
@@ -164,6 +197,20 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
         uint32_t* const cursors = wf->cursors + kCursorsPerBounce * bounce;
         (void)counts; (void)cursors;
         stage(STAGE_SURFACE);
+#if PT_LSS == 3
+        if (bounce == 0 && batch)
+        {
+            PT_VARIANT_NAME(k_wf_camera)<<<blocks(128), 128, 0, stream>>>(*rd, res, tile, *wf, *batch);
+            stage(STAGE_TRACE);
+            RayQueueView q = {wf->ray_queue[1], counts + 0, cursors + 0, wf->origin_rng, wf->dir_prim, wf->hit_tuvp, wf->hit_tri_slot, nullptr};
+            e = PT_SUFFIXED(launch_trace_queue)(rd->geom, q, false, trace_blocks, counters, stream);
+            if (e != cudaSuccess)
+                return e;
+            stage(STAGE_SURFACE);
+            PT_VARIANT_NAME(k_wf_camera_surface)<<<blocks(128), 128, 0, stream>>>(*rd, res, tile, *wf, *batch);
+        }
+        else
+#endif
         if (bounce == 0)
             PT_VARIANT_NAME(k_wf_gen)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile, *wf);
 #if PT_LSS == 3
@@ -250,6 +297,13 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
         else
             PT_VARIANT_NAME(k_wf_shade)<<<blocks(64), 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
     }
+#if PT_LSS == 3
+    if (batch)
+    {
+        stage(STAGE_SHADE);
+        PT_VARIANT_NAME(k_wf_accumulate)<<<blocks(128), 128, 0, stream>>>(*rd, res, tile, *wf, *batch);
+    }
+#endif
     stage(STAGE_END);
     return cudaGetLastError();
 }

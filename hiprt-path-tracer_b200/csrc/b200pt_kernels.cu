@@ -214,7 +214,7 @@ cudaError_t PT_SUFFIXED(launch_trace_batch_queue)(const void* bvh_device_handle,
 
 static inline dim3 pixel_grid(const Tile& t) { return dim3((t.x1 - t.x0 + 7) / 8, (t.y1 - t.y0 + 7) / 8, 1); }
 
-#define PT_DECLARE_VARIANT(LSS, ESS, LATER, GGX) cudaError_t PT_VARIANT_NAME_OF(launch_FullPathTracer, LSS, ESS, LATER, GGX)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const WavefrontState* wf, int mode, WavefrontProfile* profile);
+#define PT_DECLARE_VARIANT(LSS, ESS, LATER, GGX) cudaError_t PT_VARIANT_NAME_OF(launch_FullPathTracer, LSS, ESS, LATER, GGX)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const WavefrontState* wf, int mode, WavefrontProfile* profile, const SampleBatch* batch);
 PT_FOR_EACH_VARIANT(PT_DECLARE_VARIANT)
 
 #define PT_DECLARE_RESTIR(LSS, ESS, LATER, GGX)                                                                                                                    \
@@ -287,8 +287,15 @@ cudaError_t PT_SUFFIXED(launch_CameraRays)(const VariantOptions& opt, const HIPR
 
 cudaError_t PT_SUFFIXED(launch_FullPathTracer)(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const WavefrontState* wf, int mode, WavefrontProfile* profile)
 {
-#define PT_CASE_FPT(LSS, ESS, LATER, GGX) if (opt.lss == LSS && opt.ess == ESS && (opt.lss != 5 || opt.later == LATER) && opt.ggx == GGX) return PT_VARIANT_NAME_OF(launch_FullPathTracer, LSS, ESS, LATER, GGX)(rd, res, tile, stream, wf, mode, profile);
+#define PT_CASE_FPT(LSS, ESS, LATER, GGX) if (opt.lss == LSS && opt.ess == ESS && (opt.lss != 5 || opt.later == LATER) && opt.ggx == GGX) return PT_VARIANT_NAME_OF(launch_FullPathTracer, LSS, ESS, LATER, GGX)(rd, res, tile, stream, wf, mode, profile, nullptr);
     PT_FOR_EACH_VARIANT(PT_CASE_FPT)
+    return cudaErrorInvalidDeviceFunction;
+}
+
+cudaError_t PT_SUFFIXED(launch_PathTraceSamples)(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const WavefrontState* wf, const SampleBatch* batch, WavefrontProfile* profile)
+{
+#define PT_CASE_BATCH(LSS, ESS, LATER, GGX) if (opt.lss == LSS && opt.ess == ESS && (opt.lss != 5 || opt.later == LATER) && opt.ggx == GGX) return PT_VARIANT_NAME_OF(launch_FullPathTracer, LSS, ESS, LATER, GGX)(rd, res, tile, stream, wf, WF_PHASED, profile, batch);
+    PT_FOR_EACH_VARIANT(PT_CASE_BATCH)
     return cudaErrorInvalidDeviceFunction;
 }
 

@@ -138,11 +138,17 @@ PT_DEV void get_camera_ray(const HIPRTCamera& cam, float x, float y, int2 res, f
     direction = normalize(p_ws - ray_origin);
 }
 
-PT_DEV unsigned int pixel_seed(const HIPRTRenderData& rd, uint32_t pixel_index)
+// Seed of a pixel's generator in the sample pass (sample_number, random_seed): CameraRays.h:127-132, FullPathTracer.h:124-129
+PT_DEV unsigned int pixel_seed_of_pass(const HIPRTRenderData& rd, uint32_t pixel_index, int sample_number, unsigned int random_seed)
 {
     if (rd.render_settings.freeze_random)
         return wang_hash(pixel_index + 1);
-    return wang_hash((pixel_index + 1) * (rd.render_settings.sample_number + 1) * rd.random_seed);
+    return wang_hash((pixel_index + 1) * (sample_number + 1) * random_seed);
+}
+
+PT_DEV unsigned int pixel_seed(const HIPRTRenderData& rd, uint32_t pixel_index)
+{
+    return pixel_seed_of_pass(rd, pixel_index, rd.render_settings.sample_number, rd.random_seed);
 }
 
 template <bool USE_PREV_GBUFFER>
@@ -309,7 +315,7 @@ PT_DEV RGB sample_one_light(const HIPRTRenderData& rd, RayPayload& payload, cons
     return direct / rd.render_settings.number_of_light_samples;
 }
 
-PT_DEV bool sanity_check(const HIPRTRenderData& rd, RGB& ray_color, float sampled_wavelength, uint32_t pixel_index)
+PT_DEV bool sanity_check(const HIPRTRenderData& rd, RGB& ray_color, float sampled_wavelength, uint32_t pixel_index, int sample_number)
 {
     bool invalid = false;
     if (sampled_wavelength == 0.0f)
@@ -321,8 +327,8 @@ PT_DEV bool sanity_check(const HIPRTRenderData& rd, RGB& ray_color, float sample
         {
             // debug_set_final_color (FullPathTracer.h:27-33)
             RGB c(1.0e30f, 0.0f, 1.0e30f);
-            if (rd.render_settings.sample_number != 0)
-                c = c * rd.render_settings.sample_number;
+            if (sample_number != 0)
+                c = c * sample_number;
             st3(rd.buffers.pixels, pixel_index, to_f3(c));
         }
         else
@@ -422,9 +428,12 @@ PT_DEV void miss_vertex(const HIPRTRenderData& rd, RayPayload& payload, float3 d
 
 // End of a path (FullPathTracer.h:288-326): sanity check, then accumulation of the sample into the frame buffers.
 // The denoiser AOVs only depend on the camera hit, so they are re-read from the G-buffer here.
-PT_DEV void accumulate_sample(const HIPRTRenderData& rd, uint32_t pixel_index, RGB ray_color, float sampled_wavelength, float3 denoiser_normal, RGB denoiser_albedo)
+// `sample_number` / `aov_counter` are the render settings' values of the sample pass the colour belongs to (a sample batch
+// accumulates several passes in one kernel, in pass order: wf_accumulate_pixel).
+PT_DEV void accumulate_sample_at(const HIPRTRenderData& rd, uint32_t pixel_index, RGB ray_color, float sampled_wavelength, float3 denoiser_normal, RGB denoiser_albedo,
+                                 const int sample_number, const int aov_counter)
 {
-    if (!sanity_check(rd, ray_color, sampled_wavelength, pixel_index))
+    if (!sanity_check(rd, ray_color, sampled_wavelength, pixel_index, sample_number))
         return;
 
     float squared_luminance_of_samples = 0.0f;
@@ -434,13 +443,12 @@ PT_DEV void accumulate_sample(const HIPRTRenderData& rd, uint32_t pixel_index, R
     if (has_access_to_adaptive_sampling_buffers(rd.render_settings))
         rd.aux_buffers.pixel_squared_luminance[pixel_index] += squared_luminance_of_samples;
 
-    const int sample_number = rd.render_settings.sample_number;
     if (sample_number == 0)
         st3(rd.buffers.pixels, pixel_index, to_f3(ray_color));
     else
         st3(rd.buffers.pixels, pixel_index, ld3_rw(rd.buffers.pixels, pixel_index) + to_f3(ray_color));
 
-    const float counter = (float)rd.render_settings.denoiser_AOV_accumulation_counter;
+    const float counter = (float)aov_counter;
     if (rd.aux_buffers.denoiser_albedo != nullptr)
     {
         if (sample_number == 0)
@@ -463,6 +471,12 @@ PT_DEV void accumulate_sample(const HIPRTRenderData& rd, uint32_t pixel_index, R
                 st3(rd.aux_buffers.denoiser_normals, pixel_index, accumulated / normal_length);
         }
     }
+}
+
+PT_DEV void accumulate_sample(const HIPRTRenderData& rd, uint32_t pixel_index, RGB ray_color, float sampled_wavelength, float3 denoiser_normal, RGB denoiser_albedo)
+{
+    accumulate_sample_at(rd, pixel_index, ray_color, sampled_wavelength, denoiser_normal, denoiser_albedo, rd.render_settings.sample_number,
+                         rd.render_settings.denoiser_AOV_accumulation_counter);
 }
 
 // Denoiser AOVs of a pixel from its G-buffer entry (FullPathTracer.h:167-171: first hit's shading normal + base colour)

@@ -55,6 +55,26 @@ struct WavefrontState
     uint32_t capacity;       // paths
     uint32_t max_bounces;    // counts holds 2 * (max_bounces + 2) entries
     uint32_t force_slot_materials;   // debug (B200PT_SLOT_MATERIALS=1): every hit writes its 256-byte material to the slot (wf_store_hit)
+    // ---- sample batches (b200pt_launch_PathTraceSamples): CameraRays fused in, `samples` sample passes in flight together ----
+    uint32_t fused_camera;   // 1: bounce 0 comes from the camera kernel + ray-queue traversal of this launch, not from the G-buffer
+    uint32_t samples;        // sample passes in flight (>= 1); slot = sample * tile_pixels + index of the pixel inside the tile
+    uint32_t tile_pixels;    // pixels of the launch tile
+    float4* final_color;     // fused: [slot] final ray colour | sampled wavelength, accumulated in sample order by k_wf_accumulate
+    float4* aov_normal;      // fused: [slot] denoiser normal of the camera hit | 1 if the camera ray hit something
+    float4* aov_albedo;      // fused: [slot] denoiser albedo of the camera hit
+};
+
+// The sample passes one b200pt_launch_PathTraceSamples call renders: pass s is CameraRays with random_seed = camera_seed[s] followed by
+// FullPathTracer with random_seed = path_seed[s], both at sample_number[s] (GPURenderer::render: src/Renderer/GPURenderer.cpp:408-464).
+constexpr int kMaxSamplesInFlight = 16;
+struct SampleBatch
+{
+    uint32_t count;
+    uint32_t camera_seed[kMaxSamplesInFlight];
+    uint32_t path_seed[kMaxSamplesInFlight];
+    int sample_number[kMaxSamplesInFlight];
+    int aov_counter[kMaxSamplesInFlight];      // denoiser_AOV_accumulation_counter of the pass
+    uint32_t write_g_buffer;                   // the last pass of the batch leaves its camera hits in the G-buffer, as CameraRays would
 };
 
 #ifdef PT_COUNTERS
@@ -95,6 +115,7 @@ struct RayQueueView
     bool variant_available##S(const VariantOptions& opt);                                                                              \
     cudaError_t launch_CameraRays##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream);   \
     cudaError_t launch_FullPathTracer##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const WavefrontState* wf, int mode, WavefrontProfile* profile); \
+    cudaError_t launch_PathTraceSamples##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const WavefrontState* wf, const SampleBatch* batch, WavefrontProfile* profile); \
     cudaError_t launch_ReSTIR_DI_LightsPresampling##S(const VariantOptions& opt, const LightPresamplingParameters* p, cudaStream_t stream);            \
     cudaError_t launch_ReSTIR_DI_InitialCandidates##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream); \
     cudaError_t launch_ReSTIR_DI_SpatiotemporalReuse##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream); \

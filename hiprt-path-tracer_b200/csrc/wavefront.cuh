@@ -131,7 +131,7 @@ PT_DEV void wf_store_hit(const WavefrontState& wf, uint32_t slot, const PathRegs
 // the normals are re-normalised there), later bounces read what EXTEND stored.
 PT_DEV void wf_load_hit(const HIPRTRenderData& rd, const WavefrontState& wf, uint32_t slot, uint32_t pixel_index, int bounce, PathRegs& p)
 {
-    if (bounce == 0)
+    if (bounce == 0 && !wf.fused_camera)      // fused: the camera hit went through SURFACE like any later hit (wf_camera_surface_path)
     {
         p.hit.inter_point = ld3_rw(rd.g_buffer.first_hits, pixel_index);
         p.hit.geometric_normal = normalize(ld3_rw(rd.g_buffer.geometric_normals, pixel_index));
@@ -160,19 +160,26 @@ PT_DEV int wf_nb_bounces(const HIPRTRenderData& rd)
     return nb_bounces;
 }
 
-PT_DEV void wf_finish_path(const HIPRTRenderData& rd, uint32_t pixel_index, const PathRegs& p)
+PT_DEV void wf_finish_path(const HIPRTRenderData& rd, const WavefrontState& wf, uint32_t slot, uint32_t pixel_index, const PathRegs& p)
 {
+    if (wf.fused_camera)
+    {
+        // sample batch: the samples of a pixel are accumulated in sample order by k_wf_accumulate once every path has ended
+        wf.final_color[slot] = make_float4(p.payload.ray_color.r, p.payload.ray_color.g, p.payload.ray_color.b, p.payload.volume_state.sampled_wavelength);
+        return;
+    }
     float3 denoiser_normal;
     RGB denoiser_albedo;
     denoiser_aovs_from_g_buffer(rd, pixel_index, denoiser_normal, denoiser_albedo);
     accumulate_sample(rd, pixel_index, p.payload.ray_color, p.payload.volume_state.sampled_wavelength, denoiser_normal, denoiser_albedo);
 }
 
-PT_DEV void wf_slot_to_pixel(const Tile& tile, int2 res, uint32_t slot, uint32_t& x, uint32_t& y, uint32_t& pixel_index)
+PT_DEV void wf_slot_to_pixel(const WavefrontState& wf, const Tile& tile, int2 res, uint32_t slot, uint32_t& x, uint32_t& y, uint32_t& pixel_index)
 {
     const uint32_t tw = (uint32_t)(tile.x1 - tile.x0);
-    x = (uint32_t)tile.x0 + slot % tw;
-    y = (uint32_t)tile.y0 + slot / tw;
+    const uint32_t local = wf.samples > 1u ? slot % wf.tile_pixels : slot;     // slot = sample * tile_pixels + pixel inside the tile
+    x = (uint32_t)tile.x0 + local % tw;
+    y = (uint32_t)tile.y0 + local / tw;
     pixel_index = x + y * (uint32_t)res.x;
 }
 
@@ -209,7 +216,7 @@ PT_DEV void wf_bounce0_pixel(const HIPRTRenderData& rd, int2 res, const Tile& ti
         if (alive)
             wf_store_ray(wf, slot, p);
         else
-            wf_finish_path(rd, pixel_index, p);
+            wf_finish_path(rd, wf, slot, pixel_index, p);
     }
     queue_push(wf.ray_queue[0], wf.counts + kCountsPerBounce * 1, alive, slot);
 }
@@ -220,7 +227,7 @@ PT_DEV void wf_bounce_path(const HIPRTRenderData& rd, int2 res, const Tile& tile
 {
     const uint32_t slot = wf.ray_queue[(bounce - 1) & 1][i];
     uint32_t x, y, pixel_index;
-    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    wf_slot_to_pixel(wf, tile, res, slot, x, y, pixel_index);
     PathRegs p;
     wf_load_ray(wf, slot, p);
     bool alive = false;
@@ -232,7 +239,7 @@ PT_DEV void wf_bounce_path(const HIPRTRenderData& rd, int2 res, const Tile& tile
     if (alive)
         wf_store_ray(wf, slot, p);
     else
-        wf_finish_path(rd, pixel_index, p);
+        wf_finish_path(rd, wf, slot, pixel_index, p);
     queue_push(wf.ray_queue[bounce & 1], wf.counts + kCountsPerBounce * (bounce + 1), alive, slot);
 }
 
@@ -257,10 +264,127 @@ PT_DEV void wf_gen_pixel(const HIPRTRenderData& rd, int2 res, const Tile& tile, 
         else
         {
             miss_vertex<ESS>(rd, p.payload, p.direction, 0);
-            wf_finish_path(rd, pixel_index, p);
+            wf_finish_path(rd, wf, slot, pixel_index, p);
         }
     }
     queue_push(wf.shade_queue, wf.counts + 1, found, slot);
+}
+
+// ---- sample batches (b200pt_launch_PathTraceSamples): CameraRays fused into the wavefront, several sample passes in flight ---------
+// What the reference runs as  for s in passes: CameraRays(seed_c[s]); FullPathTracer(seed_p[s])  (GPURenderer::render,
+// src/Renderer/GPURenderer.cpp:408-464) runs here as ONE wavefront over slots = (pass, pixel): CAMERA generates every pass's primary
+// rays (CameraRays.h:127-150), the ray-queue kernel traces them, CAMERA_SURFACE finishes CameraRays (hit -> surface, emissive flip,
+// G-buffer of the last pass: CameraRays.h:152-170) and starts FullPathTracer on the same registers (FullPathTracer.h:124-151: fresh
+// generator from the path seed, normals and direction re-normalised as when they are read back from the G-buffer), so the 345 B/px
+// G-buffer round trip is not paid per pass; paths end in final_color[slot] and ACCUMULATE adds a pixel's passes in pass order
+// (FullPathTracer.h:296-326). Same arithmetic, same generators, same order of additions: same bits as the separate launches.
+// Only for options under which a pass does not depend on the previous one's result: no adaptive sampling / pixel noise threshold
+// (CameraRays reads the accumulated statistics), no ReSTIR DI (temporal reuse), no low-resolution rendering.
+PT_DEV void wf_camera_slot(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, const SampleBatch& batch, uint32_t slot)
+{
+    uint32_t x, y, pixel_index;
+    wf_slot_to_pixel(wf, tile, res, slot, x, y, pixel_index);
+    const uint32_t pass = slot / wf.tile_pixels;
+
+    Rng rng(pixel_seed_of_pass(rd, pixel_index, batch.sample_number[pass], batch.camera_seed[pass]));
+    float x_dir = (x + 0.5f);
+    float y_dir = (y + 0.5f);
+    if (rd.current_camera.do_jittering)
+    {
+        x_dir += rng() - 0.5f;
+        y_dir += rng() - 0.5f;
+    }
+    PathRegs p;
+    get_camera_ray(rd.current_camera, x_dir, y_dir, res, p.origin, p.direction);
+    p.rng = rng;
+    p.hit.primitive_index = -1;             // the camera ray leaves from no primitive
+    p.payload.throughput = RGB(1.0f);
+    p.payload.ray_color = RGB(0.0f);
+    p.payload.next_ray_state = 0;
+    volume_state_init(p.payload.volume_state);
+    wf_store_ray(wf, slot, p);
+    wf.ray_queue[1][slot] = slot;           // every slot has a primary ray: the queue is the identity, its length is written by the launcher
+    if (pass + 1 == batch.count)
+    {
+        rd.aux_buffers.pixel_active[pixel_index] = true;
+        if (rd.render_settings.do_update_status_buffers)
+            rd.aux_buffers.still_one_ray_active[0] = 1;
+    }
+}
+
+template <int ESS>
+PT_DEV void wf_camera_surface_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, const SampleBatch& batch, uint32_t i)
+{
+    const uint32_t slot = wf.ray_queue[1][i];
+    uint32_t x, y, pixel_index;
+    wf_slot_to_pixel(wf, tile, res, slot, x, y, pixel_index);
+    const uint32_t pass = slot / wf.tile_pixels;
+    PathRegs p;
+    wf_load_ray(wf, slot, p);
+    const float4 h = wf.hit_tuvp[slot];
+    Hit first;
+    first.t = h.x; first.u = h.y; first.v = h.z;
+    first.prim = __float_as_int(h.w);
+    first.tri_slot = (int)wf.hit_tri_slot[slot];
+    // ---- the rest of CameraRays (CameraRays.h:150-170)
+    const bool found = trace_ray_from(rd, p.origin, p.direction, p.payload, p.hit, -1, p.rng, first, true);
+    if (found && material_is_emissive(p.payload.material) && dot(-p.direction, p.hit.geometric_normal) < 0)
+    {
+        p.hit.geometric_normal = -p.hit.geometric_normal;
+        p.hit.shading_normal = -p.hit.shading_normal;
+    }
+    if (batch.write_g_buffer && pass + 1 == batch.count)
+    {
+        if (found)
+        {
+            st3(rd.g_buffer.geometric_normals, pixel_index, p.hit.geometric_normal);
+            st3(rd.g_buffer.shading_normals, pixel_index, p.hit.shading_normal);
+            store_material(rd.g_buffer.materials + pixel_index, p.payload.material);
+            st3(rd.g_buffer.first_hits, pixel_index, p.hit.inter_point);
+            copy_volume_state(rd.g_buffer.ray_volume_states + pixel_index, &p.payload.volume_state);
+        }
+        rd.g_buffer.first_hit_prim_index[pixel_index] = found ? p.hit.primitive_index : -1;
+        st3(rd.g_buffer.view_directions, pixel_index, -p.direction);
+        rd.g_buffer.camera_ray_hit[pixel_index] = found;
+    }
+    // ---- the head of FullPathTracer (FullPathTracer.h:124-151): its own generator; what it reads back from the G-buffer it normalises
+    p.rng = Rng(pixel_seed_of_pass(rd, pixel_index, batch.sample_number[pass], batch.path_seed[pass]));
+    p.origin = f3(0.0f, 0.0f, 0.0f);
+    p.direction = normalize(-(-p.direction));
+    if (found)
+    {
+        p.hit.geometric_normal = normalize(p.hit.geometric_normal);
+        p.hit.shading_normal = normalize(p.hit.shading_normal);
+        wf.aov_normal[slot] = make_float4(p.hit.shading_normal.x, p.hit.shading_normal.y, p.hit.shading_normal.z, 1.0f);
+        wf.aov_albedo[slot] = make_float4(p.payload.material.base_color.r, p.payload.material.base_color.g, p.payload.material.base_color.b, 0.0f);
+        wf_store_ray(wf, slot, p);
+        wf_store_hit(wf, slot, p);
+        wf_classify(wf, slot, p.payload.material);
+    }
+    else
+    {
+        wf.aov_normal[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        wf.aov_albedo[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        miss_vertex<ESS>(rd, p.payload, p.direction, 0);
+        wf_finish_path(rd, wf, slot, pixel_index, p);
+    }
+    queue_push(wf.shade_queue, wf.counts + 1, found, slot);
+}
+
+// The end of FullPathTracer for every pass of the batch, in pass order (FullPathTracer.h:288-326); one thread per pixel of the tile
+PT_DEV void wf_accumulate_pixel(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, const SampleBatch& batch, uint32_t local)
+{
+    uint32_t x, y, pixel_index;
+    wf_slot_to_pixel(wf, tile, res, local, x, y, pixel_index);
+    for (uint32_t pass = 0; pass < batch.count; pass++)
+    {
+        const uint32_t slot = pass * wf.tile_pixels + local;
+        const float4 c = wf.final_color[slot], n = wf.aov_normal[slot], a = wf.aov_albedo[slot];
+        // aov_normal holds normalize(G-buffer shading normal), the value denoiser_aovs_from_g_buffer adds to zero
+        const float3 denoiser_normal = n.w != 0.0f ? f3(0.0f, 0.0f, 0.0f) + f3(n.x, n.y, n.z) : f3(0.0f, 0.0f, 0.0f);
+        const RGB denoiser_albedo = n.w != 0.0f ? RGB(0.0f) + RGB(a.x, a.y, a.z) : RGB(0.0f);
+        accumulate_sample_at(rd, pixel_index, RGB(c.x, c.y, c.z), c.w, denoiser_normal, denoiser_albedo, batch.sample_number[pass], batch.aov_counter[pass]);
+    }
 }
 
 // ---- SPLIT, bounce >= 1: EXTEND = closest hit + material ----------------------------------------------------------------
@@ -279,9 +403,9 @@ PT_DEV void wf_extend_path(const HIPRTRenderData& rd, int2 res, const Tile& tile
     else
     {
         uint32_t x, y, pixel_index;
-        wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+        wf_slot_to_pixel(wf, tile, res, slot, x, y, pixel_index);
         miss_vertex<ESS>(rd, p.payload, p.direction, bounce);
-        wf_finish_path(rd, pixel_index, p);
+        wf_finish_path(rd, wf, slot, pixel_index, p);
     }
     queue_push(wf.shade_queue, wf.counts + kCountsPerBounce * bounce + 1, found, slot);
 }
@@ -324,7 +448,7 @@ PT_DEV void wf_shade_path(const HIPRTRenderData& rd, int2 res, const Tile& tile,
 {
     const uint32_t slot = wf.sorted_queue[i];
     uint32_t x, y, pixel_index;
-    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    wf_slot_to_pixel(wf, tile, res, slot, x, y, pixel_index);
     PathRegs p;
     wf_load_ray(wf, slot, p);
     wf_load_hit(rd, wf, slot, pixel_index, bounce, p);
@@ -333,7 +457,7 @@ PT_DEV void wf_shade_path(const HIPRTRenderData& rd, int2 res, const Tile& tile,
     if (alive)
         wf_store_ray(wf, slot, p);
     else
-        wf_finish_path(rd, pixel_index, p);
+        wf_finish_path(rd, wf, slot, pixel_index, p);
     queue_push(wf.ray_queue[bounce & 1], wf.counts + kCountsPerBounce * (bounce + 1), alive, slot);
 }
 
@@ -343,7 +467,7 @@ PT_DEV void wf_direct_path(const HIPRTRenderData& rd, int2 res, const Tile& tile
 {
     const uint32_t slot = wf.sorted_queue[i];
     uint32_t x, y, pixel_index;
-    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    wf_slot_to_pixel(wf, tile, res, slot, x, y, pixel_index);
     PathRegs p;
     wf_load_ray(wf, slot, p);
     wf_load_hit(rd, wf, slot, pixel_index, bounce, p);
@@ -357,7 +481,7 @@ PT_DEV void wf_bsdf_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, 
 {
     const uint32_t slot = wf.sorted_queue[i];
     uint32_t x, y, pixel_index;
-    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    wf_slot_to_pixel(wf, tile, res, slot, x, y, pixel_index);
     PathRegs p;
     wf_load_ray(wf, slot, p);
     wf_load_hit(rd, wf, slot, pixel_index, bounce, p);
@@ -372,7 +496,7 @@ PT_DEV void wf_bsdf_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, 
     if (alive)
         wf_store_ray(wf, slot, p);
     else
-        wf_finish_path(rd, pixel_index, p);
+        wf_finish_path(rd, wf, slot, pixel_index, p);
     queue_push(wf.ray_queue[bounce & 1], wf.counts + kCountsPerBounce * (bounce + 1), alive, slot);
 }
 
@@ -397,9 +521,9 @@ PT_DEV void wf_surface_path(const HIPRTRenderData& rd, int2 res, const Tile& til
     else
     {
         uint32_t x, y, pixel_index;
-        wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+        wf_slot_to_pixel(wf, tile, res, slot, x, y, pixel_index);
         miss_vertex<ESS>(rd, p.payload, p.direction, bounce);
-        wf_finish_path(rd, pixel_index, p);
+        wf_finish_path(rd, wf, slot, pixel_index, p);
     }
     queue_push(wf.shade_queue, wf.counts + kCountsPerBounce * bounce + 1, found, slot);
 }

@@ -223,7 +223,7 @@ PT_DEV void nee_light_eval_path(const HIPRTRenderData& rd, int2 res, const Tile&
 {
     const uint32_t slot = wf.sorted_queue[i];
     uint32_t x, y, pixel_index;
-    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    wf_slot_to_pixel(wf, tile, res, slot, x, y, pixel_index);
     PathRegs p;
     nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
     nee_light_eval_body(rd, wf, bounce, slot, p);
@@ -236,7 +236,7 @@ PT_DEV void nee_bsdf_sample_path(const HIPRTRenderData& rd, int2 res, const Tile
     if (wf.nee_ray_o[nee_index(wf, NEE_LIGHT_BSDF, slot)].w != -1.0f)
         return;
     uint32_t x, y, pixel_index;
-    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    wf_slot_to_pixel(wf, tile, res, slot, x, y, pixel_index);
     PathRegs p;
     nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
     nee_bsdf_sample_body<GGX_SAMPLER>(rd, wf, bounce, slot, p);
@@ -247,7 +247,7 @@ PT_DEV void env_light_eval_path(const HIPRTRenderData& rd, int2 res, const Tile&
 {
     const uint32_t slot = wf.sorted_queue[i];
     uint32_t x, y, pixel_index;
-    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    wf_slot_to_pixel(wf, tile, res, slot, x, y, pixel_index);
     PathRegs p;
     nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
     env_light_eval_body<ESS>(rd, wf, bounce, slot, p);
@@ -260,7 +260,7 @@ PT_DEV void env_bsdf_sample_path(const HIPRTRenderData& rd, int2 res, const Tile
     if (wf.nee_ray_o[nee_index(wf, NEE_ENV_BSDF, slot)].w != -1.0f)
         return;
     uint32_t x, y, pixel_index;
-    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    wf_slot_to_pixel(wf, tile, res, slot, x, y, pixel_index);
     PathRegs p;
     nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
     env_bsdf_sample_body<GGX_SAMPLER>(rd, wf, bounce, slot, p);
@@ -271,7 +271,7 @@ PT_DEV void nee_pair_path(const HIPRTRenderData& rd, int2 res, const Tile& tile,
 {
     const uint32_t slot = wf.sorted_queue[i];
     uint32_t x, y, pixel_index;
-    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    wf_slot_to_pixel(wf, tile, res, slot, x, y, pixel_index);
     PathRegs p;
     nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
     nee_light_eval_body(rd, wf, bounce, slot, p);
@@ -284,7 +284,7 @@ PT_DEV void env_pair_path(const HIPRTRenderData& rd, int2 res, const Tile& tile,
 {
     const uint32_t slot = wf.sorted_queue[i];
     uint32_t x, y, pixel_index;
-    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    wf_slot_to_pixel(wf, tile, res, slot, x, y, pixel_index);
     PathRegs p;
     nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
     env_light_eval_body<ESS>(rd, wf, bounce, slot, p);
@@ -369,7 +369,7 @@ PT_DEV void wf_bsdf_resolved_path(const HIPRTRenderData& rd, int2 res, const Til
 {
     const uint32_t slot = wf.sorted_queue[i];
     uint32_t x, y, pixel_index;
-    wf_slot_to_pixel(tile, res, slot, x, y, pixel_index);
+    wf_slot_to_pixel(wf, tile, res, slot, x, y, pixel_index);
     PathRegs p;
     nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
     nee_resolve<ESS>(rd, wf, slot, bounce, p, lights_sampled, envmap_sampled);
@@ -378,7 +378,7 @@ PT_DEV void wf_bsdf_resolved_path(const HIPRTRenderData& rd, int2 res, const Til
     if (alive)
         wf_store_ray(wf, slot, p);
     else
-        wf_finish_path(rd, pixel_index, p);
+        wf_finish_path(rd, wf, slot, pixel_index, p);
     queue_push(wf.ray_queue[bounce & 1], wf.counts + kCountsPerBounce * (bounce + 1), alive, slot);
 }
 } // namespace pt

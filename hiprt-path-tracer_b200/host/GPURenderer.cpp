@@ -65,6 +65,8 @@ GPURenderer::GPURenderer(b200pt_ctx* ctx) : m_ctx(ctx)
     // two concurrent band launches by default: measured -13 % (Cornell) / -4.5 % (10 M triangles) of FullPathTracer time at 1080p
     const char* lanes = std::getenv("B200PT_PATH_LANES");
     set_path_lanes(lanes ? std::atoi(lanes) : 2);
+    if (const char* v = std::getenv("B200PT_SAMPLES_IN_FLIGHT"))
+        samples_in_flight = std::min(16, std::max(0, std::atoi(v)));
 }
 
 GPURenderer::~GPURenderer()
@@ -391,10 +393,104 @@ void GPURenderer::update_render_data()
         rs.restir_output_reservoirs = m_restir_spatial_1.get_device_pointer();
 }
 
+// Fused sample batches need options under which a pass does not read what the previous pass accumulated (b200pt.h)
+bool GPURenderer::can_render_sample_batches() const
+{
+    const HIPRTRenderSettings& s = m_render_data.render_settings;
+    if (samples_in_flight <= 0 || m_options.direct_light_sampling_strategy != 3)
+        return false;
+    int mode = -1;
+    if (b200pt_get_path_mode(m_ctx, &mode) != 0 || mode != 3)
+        return false;
+    if (s.number_of_light_samples != 1 || s.do_alpha_testing || !s.accumulate)
+        return false;
+    if ((s.stop_pixel_noise_threshold > 0.0f || s.enable_adaptive_sampling) && s.accumulate)
+        return false;
+    if (s.wants_render_low_resolution && s.allow_render_low_resolution && s.accumulate)
+        return false;
+    return true;
+}
+
+// The sample loop of render() below with CameraRays fused into FullPathTracer and up to samples_in_flight passes per wavefront.
+// Seeds, sample numbers and counters of every pass are drawn exactly as the per-pass loop draws them.
+void GPURenderer::render_sample_batches()
+{
+    HIPRTRenderSettings& s = m_render_data.render_settings;
+    int done = 0;
+    while (done < s.samples_per_frame)
+    {
+        const int n = std::min(std::min(samples_in_flight, 16), s.samples_per_frame - done);
+        b200pt_sample_batch batch;
+        std::memset(&batch, 0, sizeof(batch));
+        batch.count = n;
+        batch.write_g_buffer = keep_g_buffer ? 1 : 0;
+        m_render_data.prev_camera = m_render_data.current_camera;
+        m_render_data.current_camera = m_camera;
+        const bool last_batch = done + n == s.samples_per_frame;
+        s.do_update_status_buffers = (seed_schedule == SeedSchedule::CPU || last_batch) ? 1 : s.do_update_status_buffers;
+        // the render data snapshot of the launch carries the FIRST pass' sample number; every pass' own values travel in the batch
+        const int first_sample_number = s.sample_number;
+        const int first_aov_counter = s.denoiser_AOV_accumulation_counter;
+        const unsigned int first_seed = m_render_data.random_seed;
+        for (int i = 0; i < n; i++)
+        {
+            batch.sample_numbers[i] = s.sample_number;
+            batch.aov_counters[i] = s.denoiser_AOV_accumulation_counter;
+            if (seed_schedule == SeedSchedule::GPU)
+            {
+                batch.camera_seeds[i] = m_rng.xorshift32();      // launch_camera_rays
+                batch.path_seeds[i] = m_rng.xorshift32();        // launch_path_tracing
+                s.sample_number++;
+                s.denoiser_AOV_accumulation_counter++;
+            }
+            else
+            {
+                batch.camera_seeds[i] = m_render_data.random_seed;
+                batch.path_seeds[i] = m_render_data.random_seed;
+                if (s.accumulate)
+                    s.sample_number++;
+                m_render_data.random_seed = m_rng.xorshift32();  // CPURenderer.cpp:284-286
+            }
+        }
+        const int next_sample_number = s.sample_number;
+        const int next_aov_counter = s.denoiser_AOV_accumulation_counter;
+        const unsigned int next_seed = m_render_data.random_seed;
+        s.sample_number = first_sample_number;
+        s.denoiser_AOV_accumulation_counter = first_aov_counter;
+        m_render_data.random_seed = seed_schedule == SeedSchedule::GPU ? batch.path_seeds[0] : first_seed;
+
+        m_time_kernels = last_batch;
+        if (m_time_kernels)
+        {
+            // CameraRays has no launch of its own here: its interval is empty, the fused wavefront is timed as FullPathTracer
+            check(b200pt_event_record(m_ctx, m_kernel_events[0], nullptr), "b200pt_event_record");
+            check(b200pt_event_record(m_ctx, m_kernel_events[1], nullptr), "b200pt_event_record");
+            check(b200pt_event_record(m_ctx, m_kernel_events[4], nullptr), "b200pt_event_record");
+            check(b200pt_event_record(m_ctx, m_kernel_events[5], nullptr), "b200pt_event_record");
+            check(b200pt_event_record(m_ctx, m_kernel_events[2], nullptr), "b200pt_event_record");
+        }
+        launch_path_tracing(&batch);
+        if (m_time_kernels)
+            check(b200pt_event_record(m_ctx, m_kernel_events[3], nullptr), "b200pt_event_record");
+
+        s.sample_number = next_sample_number;
+        s.denoiser_AOV_accumulation_counter = next_aov_counter;
+        m_render_data.random_seed = next_seed;
+        s.need_to_reset = 0;
+        done += n;
+    }
+}
+
 void GPURenderer::render()
 {
     HIPRTRenderSettings& s = m_render_data.render_settings;
     check(b200pt_event_record(m_ctx, m_frame_start, nullptr), "b200pt_event_record");
+    if (can_render_sample_batches())
+    {
+        render_sample_batches();
+        check(b200pt_event_record(m_ctx, m_frame_stop, nullptr), "b200pt_event_record");
+        return;
+    }
     for (int i = 1; i <= s.samples_per_frame; i++)
     {
         m_render_data.prev_camera = m_render_data.current_camera;
@@ -448,9 +544,9 @@ void GPURenderer::launch_camera_rays()
     check(b200pt_launch_CameraRays(m_ctx, &m_render_data, m_res, m_has_tile ? &camera_tile : nullptr, nullptr), "b200pt_launch_CameraRays");
 }
 
-void GPURenderer::launch_path_tracing()
+void GPURenderer::launch_path_tracing(const b200pt_sample_batch* batch)
 {
-    if (seed_schedule == SeedSchedule::GPU)
+    if (seed_schedule == SeedSchedule::GPU && batch == nullptr)
         m_render_data.random_seed = m_rng.xorshift32();
     b200pt_tile whole = m_has_tile ? m_tile : b200pt_tile{0, 0, m_res.x, m_res.y};
     const int columns = whole.x1 - whole.x0;
@@ -459,7 +555,10 @@ void GPURenderer::launch_path_tracing()
         lanes--;
     if (lanes <= 1)
     {
-        check(b200pt_launch_FullPathTracer(m_ctx, &m_render_data, m_res, m_has_tile ? &m_tile : nullptr, nullptr), "b200pt_launch_FullPathTracer");
+        if (batch)
+            check(b200pt_launch_PathTraceSamples(m_ctx, &m_render_data, m_res, m_has_tile ? &m_tile : nullptr, nullptr, batch, 0, 1), "b200pt_launch_PathTraceSamples");
+        else
+            check(b200pt_launch_FullPathTracer(m_ctx, &m_render_data, m_res, m_has_tile ? &m_tile : nullptr, nullptr), "b200pt_launch_FullPathTracer");
         return;
     }
     // Bands are COLUMN ranges of whole 8-pixel blocks (a landscape frame is sky above and geometry below: row bands would
@@ -474,7 +573,10 @@ void GPURenderer::launch_path_tracing()
         b200pt_stream st = lane == 0 ? nullptr : m_lane_streams[lane - 1];
         if (lane > 0)
             check(b200pt_stream_wait_event(m_ctx, st, m_lane_fork), "b200pt_stream_wait_event");
-        check(b200pt_launch_FullPathTracer_lane(m_ctx, &m_render_data, m_res, &band, st, lane, lanes), "b200pt_launch_FullPathTracer_lane");
+        if (batch)
+            check(b200pt_launch_PathTraceSamples(m_ctx, &m_render_data, m_res, &band, st, batch, lane, lanes), "b200pt_launch_PathTraceSamples");
+        else
+            check(b200pt_launch_FullPathTracer_lane(m_ctx, &m_render_data, m_res, &band, st, lane, lanes), "b200pt_launch_FullPathTracer_lane");
         if (lane > 0)
             check(b200pt_event_record(m_ctx, m_lane_join[lane - 1], st), "b200pt_event_record");
     }

@@ -144,6 +144,11 @@ public:
     // FullPathTracer as `lanes` (1..4) concurrent band launches on separate streams (b200pt_launch_FullPathTracer_lane): the
     // traversal kernels of one band run under the DRAM-bound shade phases of another. Bands are row tiles, so pixels are unchanged.
     void set_path_lanes(int lanes);
+    // Sample batches (b200pt_launch_PathTraceSamples): render() runs the samples_per_frame passes of a frame as fused wavefronts of up
+    // to `samples_in_flight` passes (CameraRays fused in) whenever the options allow it; 0 keeps the two launch points per pass.
+    int samples_in_flight = 8;
+    bool renders_sample_batches() const { return can_render_sample_batches(); }
+    bool keep_g_buffer = true;      // the last pass of a batch leaves its camera hits in the G-buffer, as CameraRays would
     int path_lanes() const { return m_path_lanes; }                                                     // rows either side of the tile CameraRays also covers (ReSTIR DI)
     void reset();
 
@@ -194,7 +199,9 @@ private:
     void update_render_data();
     void launch_camera_rays();
     void launch_ReSTIR_DI();
-    void launch_path_tracing();
+    void launch_path_tracing(const b200pt_sample_batch* batch = nullptr);
+    bool can_render_sample_batches() const;
+    void render_sample_batches();
 
     b200pt_ctx* m_ctx;
     b200pt_bvh* m_bvh = nullptr;

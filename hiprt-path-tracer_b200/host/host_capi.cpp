@@ -140,6 +140,13 @@ int b200pt_renderer_set_tile(b200pt_renderer* r, const b200pt_tile* tile) { r->r
 int b200pt_renderer_set_tile_halo(b200pt_renderer* r, int rows) { r->renderer.set_tile_halo(rows); return B200PT_SUCCESS; }
 int b200pt_renderer_set_path_lanes(b200pt_renderer* r, int lanes) { return guarded([&] { r->renderer.set_path_lanes(lanes); }); }
 int b200pt_renderer_path_lanes(b200pt_renderer* r) { return r->renderer.path_lanes(); }
+int b200pt_renderer_set_samples_in_flight(b200pt_renderer* r, int samples, int keep_g_buffer)
+{
+    r->renderer.samples_in_flight = samples < 0 ? 0 : (samples > 16 ? 16 : samples);
+    r->renderer.keep_g_buffer = keep_g_buffer != 0;
+    return B200PT_SUCCESS;
+}
+int b200pt_renderer_renders_sample_batches(b200pt_renderer* r) { return r->renderer.renders_sample_batches() ? 1 : 0; }
 int b200pt_renderer_reset(b200pt_renderer* r) { r->renderer.reset(); return B200PT_SUCCESS; }
 HIPRTRenderSettings* b200pt_renderer_render_settings(b200pt_renderer* r) { return &r->renderer.get_render_settings(); }
 WorldSettings* b200pt_renderer_world_settings(b200pt_renderer* r) { return &r->renderer.get_world_settings(); }

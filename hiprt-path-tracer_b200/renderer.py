@@ -252,6 +252,14 @@ class GPURenderer:
             self.host.b200pt_renderer_set_tile(self.handle, C.byref(t))
         self.host.b200pt_renderer_set_tile_halo(self.handle, C.c_int(halo))
 
+    def set_samples_in_flight(self, samples, keep_g_buffer=True):
+        """Fused sample batches (b200pt_renderer_set_samples_in_flight): 0 = the two launch points per pass."""
+        _capi.check(self.host.b200pt_renderer_set_samples_in_flight(self.handle, C.c_int(samples), C.c_int(1 if keep_g_buffer else 0)), "b200pt_renderer_set_samples_in_flight")
+
+    @property
+    def renders_sample_batches(self):
+        return bool(self.host.b200pt_renderer_renders_sample_batches(self.handle))
+
     def set_path_lanes(self, lanes):
         """FullPathTracer as 1..4 concurrent band launches (trace of one band under the shade phases of another)."""
         _capi.check(self.host.b200pt_renderer_set_path_lanes(self.handle, C.c_int(lanes)), "b200pt_renderer_set_path_lanes")

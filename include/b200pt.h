@@ -158,6 +158,7 @@ B200PT_API int b200pt_kernel_variant_select(b200pt_ctx* ctx, const b200pt_option
  * cut into phases (light eval / BSDF samples / NEE rays / bounce), one small kernel each.
  * Same per-path arithmetic and RNG order in all four: same bits. */
 B200PT_API int b200pt_set_path_mode(b200pt_ctx* ctx, int mode);
+B200PT_API int b200pt_get_path_mode(b200pt_ctx* ctx, int* out_mode);
 /* Device time of the stages of the wavefront FullPathTracer, summed over the launches since the last reset:
  * out_stage_ms[4] = { ray-queue traversal kernels, gen/surface (hit -> shading data), queue sort, shading phases }.
  * Measured with CUDA events on the launching stream between the stages' kernels. */
@@ -170,6 +171,27 @@ B200PT_API int b200pt_launch_FullPathTracer(b200pt_ctx* ctx, const HIPRTRenderDa
  * tiles overlap (the ray-queue traversal of one band is latency-bound, the shade phases of another are DRAM-bound).
  * b200pt_launch_FullPathTracer is lane 0 of 1. */
 B200PT_API int b200pt_launch_FullPathTracer_lane(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream, int lane, int lane_count);
+/* New (no reference counterpart; replaces the LOOP around the two launch points, src/Renderer/GPURenderer.cpp:408-464, when samples_per_frame
+ * sample passes are rendered per frame): `count` consecutive sample passes -- pass i = CameraRays with random_seed = camera_seeds[i], then
+ * FullPathTracer with random_seed = path_seeds[i], both at render_settings.sample_number = sample_numbers[i] and
+ * denoiser_AOV_accumulation_counter = aov_counters[i] -- as ONE wavefront: CameraRays is fused in (the primary rays go through the ray-queue
+ * traversal kernel; the 345 B/px G-buffer round trip per pass disappears) and all passes' paths are in flight together, so the per-launch
+ * costs of the bounce chain are paid once per batch and a small tile (multi-GPU tile sharding) still fills the GPU. The frame buffers
+ * receive the passes in pass order: same bits as `count` iterations of the two separate launches. With write_g_buffer the last pass
+ * leaves its camera hits in the G-buffer as CameraRays would. Restrictions (B200PT_ERROR_VARIANT_NOT_COMPILED otherwise; use the separate
+ * launches then): LSS_MIS_LIGHT_BSDF, one light sample, no alpha testing, no adaptive sampling / pixel noise threshold, no ReSTIR DI, no
+ * low-resolution rendering -- the options under which a pass does not read what the previous pass accumulated. */
+typedef struct b200pt_sample_batch
+{
+    int count;                       /* 1..16 */
+    unsigned camera_seeds[16];
+    unsigned path_seeds[16];
+    int sample_numbers[16];
+    int aov_counters[16];
+    int write_g_buffer;
+} b200pt_sample_batch;
+B200PT_API int b200pt_launch_PathTraceSamples(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream,
+                                              const b200pt_sample_batch* batch, int lane, int lane_count);
 /* cudaStreamWaitEvent: work queued on `stream` after this call starts after `event` (replaces oroStreamWaitEvent) */
 B200PT_API int b200pt_stream_wait_event(b200pt_ctx* ctx, b200pt_stream stream, b200pt_event event);
 B200PT_API int b200pt_launch_ReSTIR_DI_LightsPresampling(b200pt_ctx* ctx, const LightPresamplingParameters* parameters, b200pt_stream stream);

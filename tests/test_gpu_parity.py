@@ -759,6 +759,42 @@ def test_path_lanes_are_bit_identical(pt, wl, ctx):
     g.close()
 
 
+@pytest.mark.parametrize("workload,schedule", [("cornell", "gpu"), ("cornell", "cpu"), ("synthetic_small", "gpu")])
+def test_sample_batches_are_bit_identical(pt, wl, ctx, workload, schedule):
+    """b200pt_launch_PathTraceSamples: a frame of samples_per_frame = 5 passes as fused wavefronts of 1, 2, 4 or 5 passes in flight
+    (CameraRays fused in, 1 or 2 path lanes) against the reference's loop of two launches per pass: accumulation buffer, denoiser
+    AOVs and the G-buffer the last pass leaves are the same bits; two frames, so that batches start at a non-zero sample number."""
+    W, H = (320, 200) if workload == "cornell" else (256, 160)
+    cfg = getattr(wl, workload)(W, H)
+    g = wl.setup_gpu(pt, ctx, cfg, seed_schedule=schedule)
+    names = ("pixels", "denoiser_albedo", "denoiser_normals", "first_hit_prim_index", "shading_normals", "geometric_normals", "view_directions", "first_hits",
+             "camera_ray_hit", "materials", "ray_volume_states", "pixel_active")
+    results = {}
+    for in_flight, lanes in ((0, 1), (1, 1), (2, 2), (4, 1), (5, 2)):
+        g.set_samples_in_flight(in_flight)
+        g.set_path_lanes(lanes)
+        g.reset()
+        g.resize(W, H)
+        wl.apply_settings(g.render_settings, cfg["settings"])
+        g.render_settings.samples_per_frame = 5
+        assert g.renders_sample_batches == (in_flight > 0)
+        for _ in range(2):
+            g.render_frame()
+        g.synchronize()
+        assert g.render_settings.sample_number == 10
+        results[(in_flight, lanes)] = {n: g.download(n).copy() for n in names}
+    base = results[(0, 1)]
+    assert base["camera_ray_hit"].any() and np.isfinite(base["pixels"]).all() and base["pixels"].sum() > 0
+    hit = base["camera_ray_hit"].astype(bool)
+    for key, r in results.items():
+        for n in names:
+            a, b = base[n], r[n]
+            if n in ("shading_normals", "geometric_normals", "first_hits", "materials", "ray_volume_states"):
+                a, b = a[hit], b[hit]          # CameraRays leaves these untouched where the camera ray missed
+            assert np.array_equal(a.view(np.uint8), b.view(np.uint8)), f"{n} differs with {key[0]} passes in flight, {key[1]} lanes"
+    g.close()
+
+
 def test_alpha_testing_statistical_parity(pt, wl, ctx, ref):
     """Row F, the any-hit filter with do_alpha_testing: a candidate hit survives iff rng() < alpha_opacity * texture alpha.
     The number drawn per candidate depends on the traversal order of the acceleration structure, so the streams of the two
