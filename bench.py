@@ -63,14 +63,14 @@ def measured_hbm_peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def measured_traffic(workload, width, height):
+def measured_traffic(workload, width, height, spf):
     """DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of the k_trace_queue launches of ONE step, from the committed
     `ncu --set full` capture of `bench.py --profile` (profiles/traffic.json, written by tools/ncu_traffic.py); null if this
     workload / size was not captured."""
     path = os.path.join(ROOT, "profiles", "traffic.json")
     if not os.path.exists(path):
         return None
-    entry = json.load(open(path)).get(f"{workload}_{width}x{height}")
+    entry = json.load(open(path)).get(f"{workload}_{width}x{height}_spf{spf}")
     return entry["trace_queue_dram_bytes_per_step"] if entry else None
 
 
@@ -170,6 +170,15 @@ def run_ours(args, cfg, pt):
     ctx = pt.Context(local_rank)
     g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="gpu")
     lib = ctx.lib
+    # The data-path collectives (frame gather, ReSTIR halo, accumulation all-reduce) are the C ABI's (include/b200pt_comm.h: NCCL bound
+    # by libb200pt.so, enqueued on the render stream); torch.distributed is only the launcher's rendezvous for the 128-byte NCCL id
+    comm = None
+    if dist:
+        ident = [mg.Comm.unique_id(lib) if rank == 0 else None]
+        dist.broadcast_object_list(ident, src=0, device=device)
+        comm = mg.Comm(ctx, rank, world, ident[0])
+        shard_kind = mg.Comm.COLUMNS if sharding == "columns" else mg.Comm.ROWS
+        assert mg.Comm.tile(lib, shard_kind, W, H, world, rank) == ((tiles[rank][0], 0, tiles[rank][1], H) if sharding == "columns" else (0, tiles[rank][0], W, tiles[rank][1]))
     bvh_info = ctx.bvh_info(g.bvh)
     in_flight = int(os.environ.get("B200PT_SAMPLES_IN_FLIGHT", "8"))
     batched = g.renders_sample_batches
@@ -196,10 +205,7 @@ def run_ours(args, cfg, pt):
         if restir and world > 1:
             # ReSTIR DI halo: this frame's output reservoirs of the rows within 20 of a tile edge go to the neighbouring ranks
             # (36 B/px; the G-buffer of those rows is recomputed locally by CameraRays over tile + halo)
-            g.synchronize()
-            rows = mg.device_rows(g.device_pointer("restir_output_reservoirs"), H, W * 36, device)
-            mg.exchange_halo(dist, rows, tiles, rank, halo)
-            torch.cuda.synchronize()
+            comm.exchange_halo(g.device_pointer("restir_output_reservoirs"), H, W * 36, halo)     # on the render stream: ordered after the frame
 
     if args.profile:
         # under ncu: only what the timed pass launches (3 warm-up frames + K frames), so that the launch list is the step's
@@ -274,48 +280,42 @@ def run_ours(args, cfg, pt):
     elapsed_ms = ms.value
     reduce_ms = 0.0
     if dist:
-        # accumulation buffer (sum of samples, RenderData.h:34-36) summed over ranks: one NCCL all-reduce per K steps
-        class _Dev:
-            __cuda_array_interface__ = {"shape": (H, W, 3), "typestr": "<f4", "data": (g.device_pointer("pixels"), False), "version": 3}
-        pixels = torch.as_tensor(_Dev(), device=torch.device("cuda", local_rank))
-        # one untimed round first (communicator set-up, staging allocations): the gathers are idempotent, the reduce runs on a copy
-        if sharding == "tiles":
-            mg.gather_rows(dist, pixels.view(H, W * 3), tiles)
-        elif sharding == "columns":
-            mg.gather_columns(dist, pixels, tiles)
-        else:
-            mg.reduce_accumulation(dist, pixels.clone())
-        torch.cuda.synchronize()
-        dist.barrier()
-        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        t0.record()
-        if sharding == "tiles":
-            mg.gather_rows(dist, pixels.view(H, W * 3), tiles)       # once per output frame, not per sample
-        elif sharding == "columns":
-            mg.gather_columns(dist, pixels, tiles)
-        else:
-            mg.reduce_accumulation(dist, pixels)
-        if sharding == "samples" and cfg["settings"].get("enable_adaptive_sampling"):
-            # adaptive sampling decides on global statistics (AdaptiveSampling.h:30-104): its two buffers are summed as well
-            lum = mg.device_array(g.device_pointer("pixel_squared_luminance"), (H, W), "<f4", device)
-            cnt = mg.device_array(g.device_pointer("pixel_sample_count"), (H, W), "<i4", device)
-            dist.all_reduce(lum, op=dist.ReduceOp.SUM)
-            dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
-        t1.record()
-        torch.cuda.synchronize()
-        reduce_ms = t0.elapsed_time(t1)
+        # once per OUTPUT, not per sample: the frame assembled on every rank (tile sharding) or the accumulation buffers summed into a
+        # separate buffer (sample-pass sharding; multigpu.reduce_accumulation explains why not in place)
+        d_pixels = g.device_pointer("pixels")
+        d_sum = ctx.malloc(W * H * 12) if sharding == "samples" else None
+        adaptive = sharding == "samples" and bool(cfg["settings"].get("enable_adaptive_sampling"))
+        d_lum, d_cnt = (ctx.malloc(W * H * 4), ctx.malloc(W * H * 4)) if adaptive else (None, None)
+
+        def collective():
+            if sharding == "samples":
+                comm.allreduce_sum(d_pixels, d_sum.value, W * H * 3, "f32")
+                if adaptive:
+                    comm.allreduce_sum(g.device_pointer("pixel_squared_luminance"), d_lum.value, W * H, "f32")
+                    comm.allreduce_sum(g.device_pointer("pixel_sample_count"), d_cnt.value, W * H, "i32")
+            else:
+                comm.gather_tiles(d_pixels, W, H, 12, shard_kind)
+
+        collective()                 # one untimed round first (NCCL channel set-up, staging allocation); the gathers are idempotent
+        ctx.sync()
+        comm.barrier()
+        lib.b200pt_event_record(ctx.handle, ev0, None)
+        collective()
+        lib.b200pt_event_record(ctx.handle, ev1, None)
+        ctx.sync()
+        lib.b200pt_event_elapsed_ms(ctx.handle, ev0, ev1, C.byref(ms))
+        reduce_ms = ms.value
         elapsed_ms += reduce_ms
-        dist.barrier()
+        for p in (d_sum, d_lum, d_cnt):
+            if p is not None:
+                ctx.free(p)
+        comm.barrier()
     torch.cuda.synchronize()
     clocks = sampler.summary() if sampler else None
 
-    stats = torch.tensor([elapsed_ms, rays_per_step * args.steps], dtype=torch.float64, device=torch.device("cuda", local_rank))
     if dist:
-        tmax = stats.clone()
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        tsum = stats.clone()
-        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        elapsed_ms, total_rays = float(tmax[0]), float(tsum[1])
+        elapsed_ms = comm.allreduce_host([elapsed_ms], "max")[0]                      # device-timed, max over ranks
+        total_rays = comm.allreduce_host([rays_per_step * args.steps], "sum")[0]
     else:
         total_rays = rays_per_step * args.steps
 
@@ -337,12 +337,12 @@ def run_ours(args, cfg, pt):
     ctx.sync()
     lib.b200pt_event_elapsed_ms(ctx.handle, ev0, ev1, C.byref(ms))
     e2e_ms = ms.value
-    e2e_stats = torch.tensor([e2e_ms], dtype=torch.float64, device=torch.device("cuda", local_rank))
     if dist:
-        dist.all_reduce(e2e_stats, op=dist.ReduceOp.MAX)
-    e2e_ms = float(e2e_stats[0])
+        e2e_ms = comm.allreduce_host([e2e_ms], "max")[0]
     lib.b200pt_host_free_pinned(ctx.handle, pinned)
 
+    if comm:
+        comm.close()
     if rank != 0:
         if dist:
             dist.destroy_process_group()
@@ -385,7 +385,7 @@ def run_ours(args, cfg, pt):
         "clocks": clocks,
         "e2e": {"value": total_rays / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 2 * 1328 + 196, "d2h_bytes_per_step": W * own_rows * 12},
         "roofline": {"bound": "hbm", "frac_of": "HBM copy peak (the contract's denominator; the kernel is L2-latency-bound, not HBM-bound)", "kernel": "k_trace_queue (ray-queue BVH8 traversal inside FullPathTracer; per step = sum of its launches)", "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(args.workload, W, H),
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(args.workload, W, H, cfg["settings"].get("samples_per_frame", 1)),
                      "peak_source": peak_kind, "ms_per_launch": trace_ms, "full_path_tracer_ms": fpt_ms, "stage_ms": stage_ms,
                      "camera_rays_ms_per_launch": kernel_ms["CameraRays"] / args.steps,
                      "stage_ms_lanes": 1, "rays_per_launch": queue["rays"], "nodes_per_ray": queue["nodes"] / max(1.0, queue["rays"]),

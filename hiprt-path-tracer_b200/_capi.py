@@ -77,8 +77,13 @@ API_SYMBOLS = [
     "b200pt_tex2d_create", "b200pt_tex3d_create", "b200pt_tex_destroy", "b200pt_tex2d_array_create", "b200pt_bvh_build",
     "b200pt_bvh_destroy", "b200pt_bvh_device_handle", "b200pt_bvh_info", "b200pt_bvh_get_stats", "b200pt_kernel_variant_select", "b200pt_set_path_mode", "b200pt_get_path_mode", "b200pt_path_profile_enable", "b200pt_path_profile_read", "b200pt_launch_CameraRays",
     "b200pt_launch_FullPathTracer", "b200pt_launch_FullPathTracer_lane", "b200pt_launch_PathTraceSamples", "b200pt_stream_wait_event", "b200pt_launch_ReSTIR_DI_LightsPresampling", "b200pt_launch_ReSTIR_DI_InitialCandidates",
-    "b200pt_launch_ReSTIR_DI_SpatiotemporalReuse", "b200pt_launch_ReSTIR_DI_TemporalReuse", "b200pt_launch_ReSTIR_DI_SpatialReuse", "b200pt_tonemap", "b200pt_trace_closest", "b200pt_trace_shadow", "b200pt_trace_queue", "b200pt_trace_queue_static", "b200pt_set_trace_flavour", "b200pt_counters_enable",
+    "b200pt_launch_ReSTIR_DI_SpatiotemporalReuse", "b200pt_launch_ReSTIR_DI_TemporalReuse", "b200pt_launch_ReSTIR_DI_SpatialReuse", "b200pt_tonemap", "b200pt_trace_closest", "b200pt_trace_shadow", "b200pt_trace_queue", "b200pt_trace_queue_static", "b200pt_set_trace_flavour", "b200pt_set_ray_bin_bits", "b200pt_counters_enable",
     "b200pt_counters_read",
+]
+# include/b200pt_comm.h (multi-GPU plumbing; part of libb200pt.so)
+COMM_API_SYMBOLS = [
+    "b200pt_comm_tile", "b200pt_comm_restir_halo_rows", "b200pt_comm_get_unique_id", "b200pt_comm_create", "b200pt_comm_destroy", "b200pt_comm_rank", "b200pt_comm_world",
+    "b200pt_comm_gather_tiles", "b200pt_comm_exchange_halo", "b200pt_comm_allreduce_sum", "b200pt_comm_allreduce_host_f64", "b200pt_comm_barrier",
 ]
 HOST_API_SYMBOLS = [
     "b200pt_host_last_error", "b200pt_renderer_create", "b200pt_renderer_destroy", "b200pt_renderer_set_seed_schedule", "b200pt_renderer_set_rng_seed",

@@ -43,7 +43,7 @@ struct b200pt_bvh
     bool built_on_device = false;
 };
 
-namespace pt { int g_trace_flavour = -1; }
+namespace pt { int g_trace_flavour = -1; int g_ray_bin_bits = -1; }
 
 namespace
 {
@@ -362,3 +362,4 @@ int b200pt_event_elapsed_ms(b200pt_ctx* ctx, b200pt_event start, b200pt_event st
 
 #include "b200pt_capi_scene.inl"
 #include "b200pt_capi_noalloc.inl"
+#include "b200pt_capi_comm.inl"

@@ -237,6 +237,10 @@ static int ensure_wavefront(b200pt_ctx* ctx, int lane, uint32_t paths, uint32_t 
     ok &= (wf.hit_tri_slot = static_cast<uint32_t*>(alloc(2 * n * 4))) != nullptr;
     ok &= (wf.any_queue = static_cast<uint32_t*>(alloc(3 * n * 4))) != nullptr;
     ok &= (wf.closest_queue = static_cast<uint32_t*>(alloc(n * 4))) != nullptr;
+    ok &= (wf.bin_hist = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * (pt::kRayBinsMax + 1u)))) != nullptr;
+    ok &= (wf.binned_any = static_cast<uint32_t*>(alloc(3 * n * 4))) != nullptr;
+    ok &= (wf.binned_ext = static_cast<uint32_t*>(alloc(n * 4))) != nullptr;
+    ok &= (wf.bin_keys = static_cast<uint32_t*>(alloc(3 * n * 4))) != nullptr;
     ok &= (wf.counts = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * (pt::kCountsPerBounce + pt::kCursorsPerBounce) * (max_bounces + 2)))) != nullptr;
     if (!ok)
     {
@@ -538,6 +542,13 @@ int b200pt_set_trace_flavour(b200pt_ctx* ctx, int flavour)
 {
     REQUIRE(ctx != nullptr && (flavour == -1 || flavour == 0 || flavour == 1 || (flavour >= 5 && flavour <= 7)));
     pt::g_trace_flavour = flavour;
+    return B200PT_SUCCESS;
+}
+
+int b200pt_set_ray_bin_bits(b200pt_ctx* ctx, int bits)
+{
+    REQUIRE(ctx != nullptr && bits >= -1 && bits <= pt::kRayBinBitsMax);
+    pt::g_ray_bin_bits = bits;
     return B200PT_SUCCESS;
 }
 

@@ -191,6 +191,17 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
 #endif
     const unsigned trace_blocks = wf->sm_count * (((unsigned)kTraceGridBlocksPerSM + share - 1u) / share);   // persistent: the resident blocks of 128 threads per SM (trace_queue.cuh), shared between lanes
     (void)counters; (void)trace_blocks;
+    // Ray binning (launch_bin_rays): cells per axis = 2^bits, 0 = off. B200PT_RAY_BIN_BITS for both kinds of queue, or
+    // B200PT_RAY_BIN_BITS_EXT / _NEE separately (sweeps: profiles/r02_ray_binning.txt)
+#ifndef PT_RAY_BIN_BITS_DEFAULT
+#define PT_RAY_BIN_BITS_DEFAULT 0
+#endif
+    static const int bin_bits_both = [] { const char* v = getenv("B200PT_RAY_BIN_BITS"); return v ? atoi(v) : PT_RAY_BIN_BITS_DEFAULT; }();
+    static const int bin_bits_ext_env = [] { const char* v = getenv("B200PT_RAY_BIN_BITS_EXT"); return v ? atoi(v) : bin_bits_both; }();
+    static const int bin_bits_nee_env = [] { const char* v = getenv("B200PT_RAY_BIN_BITS_NEE"); return v ? atoi(v) : bin_bits_both; }();
+    const int bin_bits_ext = g_ray_bin_bits >= 0 ? g_ray_bin_bits : bin_bits_ext_env;
+    const int bin_bits_nee = g_ray_bin_bits >= 0 ? g_ray_bin_bits : bin_bits_nee_env;
+    (void)bin_bits_ext; (void)bin_bits_nee;
     for (int bounce = 0; bounce <= nb_bounces; bounce++)
     {
         uint32_t* const counts = wf->counts + kCountsPerBounce * bounce;
@@ -216,13 +227,21 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
 #if PT_LSS == 3
         else if (phased_mis)
         {
-            stage(STAGE_TRACE);
+            stage(bin_bits_ext > 0 ? STAGE_SORT : STAGE_TRACE);
             RayQueueView q = {wf->ray_queue[(bounce - 1) & 1], counts + 0, cursors + 0, wf->origin_rng, wf->dir_prim, wf->hit_tuvp, wf->hit_tri_slot, nullptr};
+            // rays regrouped by origin cell and direction octant (launch_bin_rays); SURFACE then walks the same order: the rays of a
+            // cell hit neighbouring triangles, so its vertex / normal gathers share cache lines too
+            e = PT_SUFFIXED(launch_bin_rays)(rd->geom, q, wf->bin_hist, wf->bin_keys, wf->binned_ext, bin_bits_ext, wf->sm_count, stream);
+            if (e != cudaSuccess)
+                return e;
+            stage(STAGE_TRACE);
             e = PT_SUFFIXED(launch_trace_queue)(rd->geom, q, false, trace_blocks, counters, stream);
             if (e != cudaSuccess)
                 return e;
             stage(STAGE_SURFACE);
-            PT_VARIANT_NAME(k_wf_surface)<<<blocks(128), 128, 0, stream>>>(*rd, res, tile, *wf, bounce);
+            WavefrontState wf_binned = *wf;
+            wf_binned.ray_queue[(bounce - 1) & 1] = const_cast<uint32_t*>(q.ids);
+            PT_VARIANT_NAME(k_wf_surface)<<<blocks(128), 128, 0, stream>>>(*rd, res, tile, wf_binned, bounce);
         }
 #endif
         else
@@ -258,10 +277,23 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
                 PT_VARIANT_NAME(launch_phase)(PHASE_ENV_LIGHT_EVAL, g64, stream, rd, res, tile, wf, bounce, lights, envmap);
                 PT_VARIANT_NAME(launch_phase)(PHASE_ENV_BSDF_SAMPLE, g64, stream, rd, res, tile, wf, bounce, lights, envmap);
             }
-            stage(STAGE_TRACE);
+            stage(bin_bits_nee > 0 ? STAGE_SORT : STAGE_TRACE);
             static const bool pair_trace = [] { const char* v = getenv("B200PT_PAIR_TRACE"); return v ? atoi(v) != 0 : true; }();
             RayQueueView qa = {wf->any_queue, counts + 2, cursors + 6, wf->nee_ray_o, wf->nee_ray_d, nullptr, nullptr, wf->nee_ray_o};
             RayQueueView qc = {wf->closest_queue, counts + 3, cursors + 9, wf->nee_ray_o, wf->nee_ray_d, wf->hit_tuvp, wf->hit_tri_slot, nullptr};
+            if (lights || envmap)
+            {
+                e = PT_SUFFIXED(launch_bin_rays)(rd->geom, qa, wf->bin_hist, wf->bin_keys, wf->binned_any, bin_bits_nee, wf->sm_count, stream);
+                if (e != cudaSuccess)
+                    return e;
+            }
+            if (lights)
+            {
+                e = PT_SUFFIXED(launch_bin_rays)(rd->geom, qc, wf->bin_hist, wf->bin_keys, wf->binned_ext, bin_bits_nee, wf->sm_count, stream);
+                if (e != cudaSuccess)
+                    return e;
+            }
+            stage(STAGE_TRACE);
             if (lights && pair_trace)
             {
                 // shadow rays (any hit) and light rays (closest hit) of the bounce in ONE launch: see k_trace_queue_pair

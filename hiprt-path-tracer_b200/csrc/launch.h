@@ -19,6 +19,8 @@ constexpr int kSortBuckets = 128;
 // Loop flavour of the ray-queue traversal kernel (b200pt_set_trace_flavour): -1 = B200PT_TRACE_PIPELINE / the built-in default,
 // 0 = classic, 5 / 6 / 7 = pipelined at that many resident blocks per SM. Process-wide; the hits do not depend on it.
 extern int g_trace_flavour;
+// Ray binning before traversal (b200pt_set_ray_bin_bits): -1 = B200PT_RAY_BIN_BITS / the built-in default, 0 = off, 1..6 = cells per axis 2^bits
+extern int g_ray_bin_bits;
 constexpr int kTraceGridBlocksPerSM = 7;   // resident blocks per SM of the ray-queue traversal kernel (= kTraceBlocksPerSM, trace_queue.cuh): its persistent grid
 constexpr int kCursorsPerBounce = 12;
 constexpr int kCountsPerBounce = 4;    // rays to extend, hits to shade, NEE any-hit rays, NEE closest-hit rays
@@ -62,7 +64,14 @@ struct WavefrontState
     float4* final_color;     // fused: [slot] final ray colour | sampled wavelength, accumulated in sample order by k_wf_accumulate
     float4* aov_normal;      // fused: [slot] denoiser normal of the camera hit | 1 if the camera ray hit something
     float4* aov_albedo;      // fused: [slot] denoiser albedo of the camera hit
+    // ---- ray binning (launch_bin_rays): a queue's ids regrouped by origin cell and direction octant before it is traced ----
+    uint32_t* bin_hist;      // kRayBinsMax + 1 counters / scatter cursors
+    uint32_t* binned_any;    // 3 * capacity ids: the NEE any-hit queue in bin order
+    uint32_t* binned_ext;    // capacity ids: the extension-ray queue (or the NEE closest-hit queue) in bin order
+    uint32_t* bin_keys;      // 3 * capacity: bin of queue entry i (histogram pass -> scatter pass)
 };
+constexpr int kRayBinBitsMax = 6;                                   // cells per axis = 2^bits
+constexpr uint32_t kRayBinsMax = 1u << (3 * kRayBinBitsMax + 3);    // cells x 8 direction octants
 
 // The sample passes one b200pt_launch_PathTraceSamples call renders: pass s is CameraRays with random_seed = camera_seed[s] followed by
 // FullPathTracer with random_seed = path_seed[s], both at sample_number[s] (GPURenderer::render: src/Renderer/GPURenderer.cpp:408-464).
@@ -122,6 +131,7 @@ struct RayQueueView
     cudaError_t launch_ReSTIR_DI_TemporalReuse##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream); \
     cudaError_t launch_ReSTIR_DI_SpatialReuse##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream); \
     cudaError_t launch_trace_queue##S(const void* bvh_device_handle, const RayQueueView& q, bool any_hit, unsigned blocks, TraversalCounters* counters, cudaStream_t stream); \
+    cudaError_t launch_bin_rays##S(const void* bvh_device_handle, RayQueueView& q, uint32_t* hist, uint32_t* keys, uint32_t* out_ids, int bits, unsigned sm_count, cudaStream_t stream); \
     cudaError_t launch_trace_queue_pair##S(const void* bvh_device_handle, const RayQueueView& q_any, const RayQueueView& q_closest, unsigned blocks, TraversalCounters* counters, cudaStream_t stream); \
     cudaError_t launch_trace_batch_queue##S(const void* bvh_device_handle, const float* rays, const float* t_max, const int* last_prim, long long n, int* out_prim, float* out_t, float* out_uv, unsigned char* out_occluded, unsigned sm_count, TraversalCounters* counters, cudaStream_t stream); \
     cudaError_t launch_trace_closest##S(const Bvh8Device& bvh, const float* rays, const int* last_prim, long long n, int* out_prim, float* out_t, float* out_uv, TraversalCounters* counters, cudaStream_t stream); \

@@ -89,20 +89,35 @@ def exchange_halo(dist, rows, tiles, rank, halo):
 
 
 def gather_rows(dist, rows, tiles):
-    """Every rank ends with the whole [H, row_bytes] buffer: each tile is broadcast by its owner, in place."""
+    """Every rank ends with the whole [H, row_bytes] buffer. Equal bands: ONE all_gather (in place: the output list aliases the bands
+    of `rows`); ragged bands (the last one is shorter when H is not a multiple of 8 * world): one broadcast per band."""
+    sizes = {y1 - y0 for y0, y1 in tiles}
+    if len(sizes) == 1 and next(iter(sizes)) > 0:
+        rank = dist.get_rank()
+        y0, y1 = tiles[rank]
+        dist.all_gather([rows[a:b] for a, b in tiles], rows[y0:y1].clone())
+        return
     for owner, (y0, y1) in enumerate(tiles):
         if y1 > y0:
             dist.broadcast(rows[y0:y1], src=owner)
 
 
 def reduce_accumulation(dist, pixels, squared_luminance=None, sample_count=None):
-    """Sample-pass sharding: sum the accumulation buffers over ranks so that adaptive sampling decides on global statistics
-    (AdaptiveSampling.h:30-104). Float summation order changes: statistically, not bitwise, equal to the 1-GPU render."""
-    dist.all_reduce(pixels, op=dist.ReduceOp.SUM)
-    if squared_luminance is not None:
-        dist.all_reduce(squared_luminance, op=dist.ReduceOp.SUM)
-    if sample_count is not None:
-        dist.all_reduce(sample_count, op=dist.ReduceOp.SUM)
+    """Sample-pass sharding: the sum over ranks of the accumulation buffers (RenderData.h:34-36 `pixels`, and optionally
+    pixel_squared_luminance / pixel_sample_count), returned as NEW tensors. The ranks' own buffers are left untouched, so the call can be
+    repeated at any time (every K passes, or once per output) and rendering can go on afterwards: an in-place reduce would make every
+    rank hold the global sum and count it again at the next reduce. Consequence, stated plainly: each rank's adaptive-sampling
+    decisions (AdaptiveSampling.h:30-104) are taken on ITS OWN statistics, not on the global ones; the reduced image divided by the
+    reduced sample count is the global estimate. Float summation order changes: statistically, not bitwise, equal to one GPU."""
+    out = []
+    for t in (pixels, squared_luminance, sample_count):
+        if t is None:
+            out.append(None)
+            continue
+        total = t.clone()
+        dist.all_reduce(total, op=dist.ReduceOp.SUM)
+        out.append(total)
+    return tuple(out)
 
 
 class _DevicePointer:
@@ -122,3 +137,63 @@ def device_array(ptr, shape, typestr, device):
     if not ptr:
         raise ValueError("device_array: null device pointer")
     return torch.as_tensor(_DevicePointer(ptr, tuple(int(s) for s in shape), typestr), device=device)
+
+
+class Comm:
+    """b200pt_comm (include/b200pt_comm.h): the same plumbing behind the C ABI, over NCCL bound by libb200pt.so itself -- what a C/C++
+    host links against. Python is only the launcher here: `unique_id` is made on rank 0 and handed to the other ranks by the caller
+    (bench.py broadcasts it with torch.distributed, a C++ host would use a file or MPI)."""
+    ROWS, COLUMNS = 0, 1
+
+    def __init__(self, ctx, rank, world, unique_id):
+        import ctypes as C
+        from . import _capi
+        self._C, self._capi, self.ctx, self.lib = C, _capi, ctx, ctx.lib
+        self.handle = C.c_void_p()
+        ident = (C.c_ubyte * 128).from_buffer_copy(bytes(unique_id))
+        _capi.check(self.lib.b200pt_comm_create(ctx.handle, C.c_int(rank), C.c_int(world), ident, C.byref(self.handle)), "b200pt_comm_create")
+        self.rank, self.world = rank, world
+
+    @staticmethod
+    def unique_id(lib):
+        import ctypes as C
+        from . import _capi
+        ident = (C.c_ubyte * 128)()
+        _capi.check(lib.b200pt_comm_get_unique_id(ident), "b200pt_comm_get_unique_id")
+        return bytes(ident)
+
+    @staticmethod
+    def tile(lib, sharding, width, height, world, rank):
+        """(x0, y0, x1, y1) of the rank's band (b200pt_comm_tile)."""
+        import ctypes as C
+        from . import _capi, structs
+        t = structs.Tile()
+        _capi.check(lib.b200pt_comm_tile(C.c_int(sharding), C.c_int(width), C.c_int(height), C.c_int(world), C.c_int(rank), C.byref(t)), "b200pt_comm_tile")
+        return (t.x0, t.y0, t.x1, t.y1)
+
+    def close(self):
+        if self.handle:
+            self.lib.b200pt_comm_destroy(self.handle)
+            self.handle = self._C.c_void_p()
+
+    def gather_tiles(self, dptr, width, height, bytes_per_pixel, sharding):
+        C = self._C
+        self._capi.check(self.lib.b200pt_comm_gather_tiles(self.handle, C.c_void_p(dptr), C.c_int(width), C.c_int(height), C.c_int(bytes_per_pixel), C.c_int(sharding), None), "b200pt_comm_gather_tiles")
+
+    def exchange_halo(self, dptr, height, row_bytes, halo):
+        C = self._C
+        self._capi.check(self.lib.b200pt_comm_exchange_halo(self.handle, C.c_void_p(dptr), C.c_int(height), C.c_size_t(row_bytes), C.c_int(halo), None), "b200pt_comm_exchange_halo")
+
+    def allreduce_sum(self, d_in, d_out, count, dtype="f32"):
+        C = self._C
+        self._capi.check(self.lib.b200pt_comm_allreduce_sum(self.handle, C.c_void_p(d_in), C.c_void_p(d_out), C.c_size_t(count), C.c_int(0 if dtype == "f32" else 1), None), "b200pt_comm_allreduce_sum")
+
+    def allreduce_host(self, values, op="sum"):
+        C = self._C
+        arr = (C.c_double * len(values))(*[float(v) for v in values])
+        self._capi.check(self.lib.b200pt_comm_allreduce_host_f64(self.handle, arr, C.c_int(len(values)), C.c_int(0 if op == "sum" else 1)), "b200pt_comm_allreduce_host_f64")
+        return list(arr)
+
+    def barrier(self):
+        self._capi.check(self.lib.b200pt_comm_barrier(self.handle), "b200pt_comm_barrier")
+

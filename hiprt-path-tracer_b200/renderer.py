@@ -166,6 +166,10 @@ class Context:
         """0 classic, 5 / 6 / 7 pipelined at that many blocks per SM, 1 pipelined default, -1 environment / built-in default."""
         _capi.check(self.lib.b200pt_set_trace_flavour(self.handle, C.c_int(flavour)), "b200pt_set_trace_flavour")
 
+    def set_ray_bin_bits(self, bits):
+        """Ray binning before traversal: 2^bits cells per axis, 0 off, -1 environment / built-in default (b200pt_set_ray_bin_bits)."""
+        _capi.check(self.lib.b200pt_set_ray_bin_bits(self.handle, C.c_int(bits)), "b200pt_set_ray_bin_bits")
+
     def counters_enable(self, enable=True):
         _capi.check(self.lib.b200pt_counters_enable(self.handle, C.c_int(1 if enable else 0)), "b200pt_counters_enable")
 

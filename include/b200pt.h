@@ -238,6 +238,11 @@ B200PT_API int b200pt_trace_queue_static(b200pt_ctx* ctx, b200pt_bvh* bvh, const
  * A scheduling choice only: hit records are identical in every flavour. Process-wide. */
 B200PT_API int b200pt_set_trace_flavour(b200pt_ctx* ctx, int flavour);
 
+/* Ray binning (new): before a queue of bounce / NEE rays is traced, its ids are regrouped by (origin cell in the scene's bounding box,
+ * direction octant), 2^bits cells per axis (0 = off, max 6, -1 = B200PT_RAY_BIN_BITS / built-in default), so that the rays of a warp walk
+ * the same part of the BVH. A scheduling choice only: every ray's hit record, hence the frame, is the same bits. Process-wide. */
+B200PT_API int b200pt_set_ray_bin_bits(b200pt_ctx* ctx, int bits);
+
 /* ---- counters (counting build of the same kernels; the timing build has them compiled out) --------------------- */
 B200PT_API int b200pt_counters_enable(b200pt_ctx* ctx, int enable);
 B200PT_API int b200pt_counters_read(b200pt_ctx* ctx, b200pt_counters* out, int reset);

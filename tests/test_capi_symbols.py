@@ -24,6 +24,10 @@ def test_every_declared_symbol_is_exported(pt):
     capi = __import__("importlib").import_module("hiprt-path-tracer_b200._capi")
     assert sorted(capi.API_SYMBOLS) == core
     assert sorted(capi.HOST_API_SYMBOLS) == hostsyms
+    commsyms = _declared("b200pt_comm.h")            # the multi-GPU plumbing is part of libb200pt.so (NCCL itself is bound at run time)
+    assert len(commsyms) == 12 and sorted(capi.COMM_API_SYMBOLS) == commsyms
+    for s in commsyms:
+        assert hasattr(lib, s), s
 
 
 def test_no_cpu_fallback(pt):
@@ -40,3 +44,18 @@ def test_variant_list_matches_header(pt):
     text = open(os.path.join(ROOT, "hiprt-path-tracer_b200", "csrc", "variants.h")).read()
     variants = re.findall(r"M\((\d+),\s*(\d+),\s*(\d+),\s*(\d+)\)", text.split("PT_FOR_EACH_VARIANT(M)")[1])
     assert ("3", "0", "3", "0") in variants and ("3", "2", "3", "0") in variants
+
+
+def test_comm_tile_plan_matches_the_python_plan(pt):
+    """b200pt_comm_tile (C ABI, needs neither GPU nor NCCL) against multigpu.row_tiles / column_tiles, which the gloo tests cover."""
+    mg = __import__("importlib").import_module("hiprt-path-tracer_b200.multigpu")
+    lib = pt.lib()
+    for width, height in ((1920, 1080), (3840, 2160), (96, 64), (17, 9), (8, 8)):
+        for world in (1, 2, 3, 4, 8):
+            rows, cols = mg.row_tiles(height, world), mg.column_tiles(width, world)
+            for rank in range(world):
+                assert mg.Comm.tile(lib, mg.Comm.ROWS, width, height, world, rank) == (0, rows[rank][0], width, rows[rank][1])
+                assert mg.Comm.tile(lib, mg.Comm.COLUMNS, width, height, world, rank) == (cols[rank][0], 0, cols[rank][1], height)
+    t = pt.structs.Tile()
+    assert lib.b200pt_comm_tile(0, 64, 64, 2, 2, ctypes.byref(t)) == -1          # rank out of range
+    assert lib.b200pt_comm_restir_halo_rows(16, 4, 0) == 20

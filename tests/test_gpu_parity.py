@@ -770,7 +770,8 @@ def test_sample_batches_are_bit_identical(pt, wl, ctx, workload, schedule):
     names = ("pixels", "denoiser_albedo", "denoiser_normals", "first_hit_prim_index", "shading_normals", "geometric_normals", "view_directions", "first_hits",
              "camera_ray_hit", "materials", "ray_volume_states", "pixel_active")
     results = {}
-    for in_flight, lanes in ((0, 1), (1, 1), (2, 2), (4, 1), (5, 2)):
+    for in_flight, lanes, bin_bits in ((0, 1, 0), (1, 1, 0), (2, 2, 3), (4, 1, 0), (5, 2, 5), (0, 2, 4)):
+        ctx.set_ray_bin_bits(bin_bits)         # ray binning before traversal only reorders the queues: same bits
         g.set_samples_in_flight(in_flight)
         g.set_path_lanes(lanes)
         g.reset()
@@ -782,8 +783,9 @@ def test_sample_batches_are_bit_identical(pt, wl, ctx, workload, schedule):
             g.render_frame()
         g.synchronize()
         assert g.render_settings.sample_number == 10
-        results[(in_flight, lanes)] = {n: g.download(n).copy() for n in names}
-    base = results[(0, 1)]
+        results[(in_flight, lanes, bin_bits)] = {n: g.download(n).copy() for n in names}
+    ctx.set_ray_bin_bits(-1)
+    base = results[(0, 1, 0)]
     assert base["camera_ray_hit"].any() and np.isfinite(base["pixels"]).all() and base["pixels"].sum() > 0
     hit = base["camera_ray_hit"].astype(bool)
     for key, r in results.items():
@@ -791,7 +793,7 @@ def test_sample_batches_are_bit_identical(pt, wl, ctx, workload, schedule):
             a, b = base[n], r[n]
             if n in ("shading_normals", "geometric_normals", "first_hits", "materials", "ray_volume_states"):
                 a, b = a[hit], b[hit]          # CameraRays leaves these untouched where the camera ray missed
-            assert np.array_equal(a.view(np.uint8), b.view(np.uint8)), f"{n} differs with {key[0]} passes in flight, {key[1]} lanes"
+            assert np.array_equal(a.view(np.uint8), b.view(np.uint8)), f"{n} differs with {key[0]} passes in flight, {key[1]} lanes, ray bin bits {key[2]}"
     g.close()
 
 

@@ -91,9 +91,15 @@ def _worker(rank, world, port, height, width, halo, result_queue):
         pixels = torch.full((height, width, 3), float(rank + 1))
         lum = torch.full((height, width), 0.5 * (rank + 1))
         count = torch.full((height, width), rank + 1, dtype=torch.int32)
-        mg.reduce_accumulation(dist, pixels, lum, count)
         total = world * (world + 1) / 2
-        ok_reduce = bool((pixels == total).all() and (lum == 0.5 * total).all() and (count == int(total)).all())
+        ok_reduce = True
+        for round_ in range(2):
+            # out of place: the rank's own buffers keep their values, so a second reduce (after more rendering) is again the plain sum
+            gp, gl, gc = mg.reduce_accumulation(dist, pixels, lum, count)
+            scale = round_ + 1
+            ok_reduce = ok_reduce and bool((gp == total * scale).all() and (gl == 0.5 * total * scale).all() and (gc == int(total) * scale).all())
+            ok_reduce = ok_reduce and bool((pixels == float(rank + 1) * scale).all() and (count == (rank + 1) * scale).all())
+            pixels += float(rank + 1); lum += 0.5 * (rank + 1); count += rank + 1          # "another pass rendered"
         result_queue.put((rank, ok_halo, untouched, ok_gather, ok_reduce))
     finally:
         dist.destroy_process_group()
