@@ -1,6 +1,7 @@
 // Implementation of the C ABI declared in include/b200pt.h (see that header for the reference call sites each
 // entry point replaces). No CPU fallback: every compute entry point needs a CUDA device.
 #include "bvh8_build.h"
+#include "bvh8_build_device.h"
 #include "launch.h"
 
 #include <chrono>
@@ -41,6 +42,7 @@ struct b200pt_bvh
     int max_depth = 0;
     float node_fill = 0.0f;
     bool built_on_device = false;
+    double device_build_seconds = 0.0;
 };
 
 namespace pt { int g_trace_flavour = -1; int g_ray_bin_bits = -1; }

@@ -81,11 +81,61 @@ int b200pt_tex2d_array_create(b200pt_ctx* ctx, void* const* descriptor_dptrs, in
 
 int b200pt_bvh_build(b200pt_ctx* ctx, const float* vertices, int vertex_count, const int* triangle_indices, int triangle_count, unsigned flags, b200pt_bvh** out_bvh)
 {
-    (void)flags;
     REQUIRE(ctx != nullptr && out_bvh != nullptr && triangle_count >= 0 && vertex_count >= 0);
     REQUIRE(triangle_count == 0 || (vertices != nullptr && triangle_indices != nullptr));
     *out_bvh = nullptr;
     CUDA_TRY(cudaSetDevice(ctx->device));
+
+    // B200PT_BVH_BUILD_DEVICE (flag, or the environment variable of the same name set to 1): Morton LBVH + SAH-optimal collapse on the GPU
+    // (bvh8_build_device.cu) instead of the host's binned-SAH builder, which stays the quality baseline and the default
+    static const bool device_by_env = [] { const char* v = getenv("B200PT_BVH_BUILD_DEVICE"); return v && atoi(v) != 0; }();
+    if (((flags & B200PT_BVH_BUILD_DEVICE) || device_by_env) && triangle_count > 0)
+    {
+        auto t0 = std::chrono::steady_clock::now();
+        pt::Bvh8DeviceBuild built;
+        cudaError_t e = pt::build_bvh8_device(vertices, vertex_count, triangle_indices, triangle_count, ctx->main_stream, &built);
+        if (e != cudaSuccess)
+            return cuda_fail(e, "device BVH8 build");
+        if (2 * built.max_depth + 1 > pt::kTraversalStackSize)
+        {
+            cudaFree(built.nodes);
+            cudaFree(built.triangles);
+            char msg[160];
+            snprintf(msg, sizeof(msg), "BVH8 depth %d needs %d traversal-stack entries, kTraversalStackSize is %d", built.max_depth, 2 * built.max_depth + 1, pt::kTraversalStackSize);
+            return fail(B200PT_ERROR_INVALID_ARGUMENT, msg);
+        }
+        b200pt_bvh* bvh = new b200pt_bvh();
+        bvh->d_nodes = built.nodes;
+        bvh->d_triangles = built.triangles;
+        bvh->sah_cost = built.sah_cost;
+        bvh->max_depth = built.max_depth;
+        bvh->node_fill = built.node_count ? (float)((double)built.child_slots_used / (8.0 * (double)built.node_count)) : 0.0f;
+        bvh->built_on_device = true;
+        bvh->device_build_seconds = built.device_seconds;
+        bvh->view.nodes = built.nodes;
+        bvh->view.triangles = built.triangles;
+        bvh->view.node_count = built.node_count;
+        bvh->view.triangle_count = built.triangle_count;
+        for (int a = 0; a < 3; a++)
+        {
+            bvh->view.scene_min[a] = built.scene_min[a];
+            bvh->view.scene_max[a] = built.scene_max[a];
+        }
+        e = cudaMalloc(&bvh->d_view, sizeof(pt::Bvh8Device));
+        if (e == cudaSuccess)
+            e = cudaMemcpy(bvh->d_view, &bvh->view, sizeof(pt::Bvh8Device), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess)
+        {
+            cudaFree(bvh->d_nodes);
+            cudaFree(bvh->d_triangles);
+            cudaFree(bvh->d_view);
+            delete bvh;
+            return cuda_fail(e, "BVH descriptor upload");
+        }
+        bvh->build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        *out_bvh = bvh;
+        return B200PT_SUCCESS;
+    }
 
     auto t0 = std::chrono::steady_clock::now();
     pt::Bvh8Host host = pt::build_bvh8(vertices, vertex_count, triangle_indices, triangle_count);
@@ -173,6 +223,7 @@ int b200pt_bvh_get_stats(b200pt_bvh* bvh, b200pt_bvh_stats* out_stats)
     out_stats->sah_cost = bvh->sah_cost;
     out_stats->node_fill = bvh->node_fill;
     out_stats->build_seconds = bvh->build_seconds;
+    out_stats->device_build_seconds = bvh->device_build_seconds;
     return B200PT_SUCCESS;
 }
 

@@ -80,10 +80,13 @@ LBVH_HD uint64_t triangle_box_and_code(uint32_t t, const float* vertices, const 
         box_lo[a] = lo[a];
         box_hi[a] = hi[a];
     }
+    // ONE cell size for the three axes (the largest extent): a Morton split then halves a cube, and a flat scene (a terrain: y extent
+    // of a few percent of x and z) is split along x and z until its cells are as thin as it is, instead of being sliced into layers
+    // (per-axis normalisation: SAH 58.5 on the 10 M-triangle scene against 43.5 of the host's binned-SAH tree)
+    const float extent = fmaxf(scene_max[0] - scene_min[0], fmaxf(scene_max[1] - scene_min[1], scene_max[2] - scene_min[2]));
     uint64_t code = 0;
     for (int a = 0; a < 3; a++)
     {
-        const float extent = scene_max[a] - scene_min[a];
         float u = extent > 0.0f ? (0.5f * (lo[a] + hi[a]) - scene_min[a]) / extent : 0.0f;
         u = fminf(fmaxf(u, 0.0f), 1.0f);
         const uint64_t q = (uint64_t)fminf(u * 2097152.0f, 2097151.0f);

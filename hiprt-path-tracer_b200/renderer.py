@@ -73,12 +73,12 @@ class Context:
         _capi.check(self.lib.b200pt_stream_sync(self.handle, None), "b200pt_stream_sync")
 
     # ---- acceleration structure + ray batches ------------------------------------------------
-    def build_bvh(self, vertices, indices):
+    def build_bvh(self, vertices, indices, device=False):
         vertices = np.ascontiguousarray(vertices, dtype=np.float32)
         indices = np.ascontiguousarray(indices, dtype=np.int32)
         bvh = C.c_void_p()
         _capi.check(self.lib.b200pt_bvh_build(self.handle, _ptr(vertices), C.c_int(len(vertices)), _ptr(indices), C.c_int(len(indices) // 3 if indices.ndim == 1 else len(indices)),
-                                              C.c_uint(0), C.byref(bvh)), "b200pt_bvh_build")
+                                              C.c_uint(1 if device else 0), C.byref(bvh)), "b200pt_bvh_build")
         return bvh
 
     def bvh_info(self, bvh):
@@ -87,7 +87,7 @@ class Context:
         st = S.BvhStats()
         _capi.check(self.lib.b200pt_bvh_get_stats(bvh, C.byref(st)), "b200pt_bvh_get_stats")
         return {"nodes": nodes.value, "triangles": tris.value, "sah_cost": sah.value, "build_seconds": secs.value, "max_depth": st.max_depth,
-                "node_fill": st.node_fill, "built_on_device": bool(st.built_on_device)}
+                "node_fill": st.node_fill, "built_on_device": bool(st.built_on_device), "device_build_seconds": st.device_build_seconds}
 
     def destroy_bvh(self, bvh):
         self.lib.b200pt_bvh_destroy(self.handle, bvh)

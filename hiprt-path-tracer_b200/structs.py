@@ -190,7 +190,7 @@ class Counters(C.Structure):
 
 class BvhStats(C.Structure):
     _fields_ = [("node_count", C.c_uint), ("triangle_count", C.c_uint), ("max_depth", i32), ("built_on_device", i32), ("sah_cost", C.c_float),
-                ("node_fill", C.c_float), ("build_seconds", C.c_double)]
+                ("node_fill", C.c_float), ("build_seconds", C.c_double), ("device_build_seconds", C.c_double)]
 
 
 LSS = {"none": 0, "uniform": 1, "bsdf": 2, "mis": 3, "ris": 4, "restir_di": 5}

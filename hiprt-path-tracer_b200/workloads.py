@@ -62,6 +62,74 @@ def adaptive(width, height):
     return cfg
 
 
+def merge_scenes(a, b, offset_b=(0.0, 0.0, 0.0)):
+    """a UNION b (b translated by offset_b): vertex, material and emissive indices of b shifted; a's camera kept."""
+    import numpy as np
+    out = sc.Scene()
+    nv, nm = len(a.vertices), len(a.materials)
+    out.vertices = np.concatenate([a.vertices, (b.vertices + np.asarray(offset_b, np.float32)[None, :]).astype(np.float32)])
+    out.indices = np.concatenate([a.indices, (b.indices + nv).astype(np.int32)])
+    out.normals = np.concatenate([a.normals, b.normals])
+    out.has_normals = np.concatenate([a.has_normals, b.has_normals])
+    out.texcoords = np.concatenate([a.texcoords, b.texcoords])
+    out.material_indices = np.concatenate([a.material_indices, (b.material_indices + nm).astype(np.int32)])
+    out.materials = list(a.materials) + list(b.materials)
+    out.textures = list(a.textures) + list(b.textures)
+    out.camera = a.camera
+    out.name = f"{a.name}+{b.name}"
+    out.compute_emissive_triangles()
+    return out
+
+
+# C5's fixed table of the material fields a glTF cannot carry (SURVEY.md 8d): per transmissive material, in scene order, cycling
+C5_PRIORITIES = (1, 2, 3)
+C5_ABSORPTION = ((0.9, 0.3, 0.3), (0.3, 0.9, 0.4), (0.35, 0.45, 0.95), (0.95, 0.85, 0.3))
+
+
+def adaptive_full(width, height, envmap_size=(2048, 1024), thin_film_on_glass=True):
+    """C5 as SURVEY.md 8(d) specifies it: nested-dielectrics-complex (3088 triangles) UNION multi-dispersion (9002 triangles, set beside it),
+    the procedural HDR envmap of C3 sampled through its alias table with BSDF MIS, and on the transmissive materials the fields the glTF
+    cannot carry, from a fixed table: dielectric_priority 1..3 (ISS_WITH_PRIORITIES, stack size 3), absorption colour at distance 1,
+    thin film (thickness 500 nm, ior 1.3), dispersion (scale 1, Abbe number 20); per-pixel adaptive sampling at the reference's defaults
+    (min 64 samples, noise threshold 0.3, RenderSettings.h:126-133). 4K in BASELINE.json: bench.py --workload adaptive_full --width 3840
+    --height 2160. thin_film_on_glass=False leaves the coating off the transmissive materials: thin film on glass under total internal
+    reflection is undefined behaviour in the reference, so parity is pinned without it and bounded with it."""
+    key = ("adaptive_full", envmap_size)
+    if key not in _CACHE:
+        a = sc.load_scene(os.path.join(ROOT, "tests", "golden", "nested-dielectrics-complex.npz"))
+        b = sc.load_scene(os.path.join(ROOT, "tests", "golden", "multi-dispersion.npz"))
+        extent = a.vertices.max(axis=0) - a.vertices.min(axis=0)
+        shift = (float(a.vertices.max(axis=0)[0] - b.vertices.min(axis=0)[0] + 0.05 * extent[0]), float(a.vertices.min(axis=0)[1] - b.vertices.min(axis=0)[1]), 0.0)
+        _CACHE[key] = (merge_scenes(a, b, shift), procedural.procedural_envmap(*envmap_size))
+    scene, env = _CACHE[key]
+    import copy
+    scene = copy.copy(scene)
+    scene.materials = [copy.deepcopy(m) for m in scene.materials]
+    k = 0
+    for m in scene.materials:
+        if m.base.specular_transmission > 0.0:
+            m.base.dielectric_priority = C5_PRIORITIES[k % len(C5_PRIORITIES)]
+            c = C5_ABSORPTION[k % len(C5_ABSORPTION)]
+            m.base.absorption_color.r, m.base.absorption_color.g, m.base.absorption_color.b = c
+            m.base.absorption_at_distance = 1.0
+            if m.base.ior > 1.05:            # dispersion around an index of 1 makes the reference produce NaN samples
+                m.base.dispersion_scale = 1.0
+                m.base.dispersion_abbe_number = 20.0
+            if thin_film_on_glass:
+                m.base.thin_film, m.base.thin_film_thickness, m.base.thin_film_ior = 1.0, 500.0, 1.3
+            k += 1
+        elif not sc.material_is_emissive(m):
+            m.base.thin_film, m.base.thin_film_thickness, m.base.thin_film_ior = 1.0, 500.0, 1.3
+    return {
+        "name": f"nested-dielectrics-complex + multi-dispersion ({scene.triangle_count} triangles) {width}x{height}, 8 bounces, LSS_MIS_LIGHT_BSDF, envmap {envmap_size[0]}x{envmap_size[1]} alias table + BSDF MIS, "
+                f"priorities 1..3 + absorption + dispersion + thin film{'' if thin_film_on_glass else ' (not on glass)'}, adaptive sampling (min 64 samples, threshold 0.3)",
+        "scene": scene, "camera": sc.scene_camera(scene, width, height), "width": width, "height": height,
+        "options": dict(lss="mis", ess="alias_table", ggx=0, later=3), "oracle_variant": "mis",
+        "envmap": {"texels": env, "alias_probas": None, "alias_alias": None, "total_sum": 0.0},
+        "settings": dict(nb_bounces=8, do_alpha_testing=0, enable_adaptive_sampling=1, adaptive_sampling_min_samples=64, adaptive_sampling_noise_threshold=0.3, samples_per_frame=1),
+    }
+
+
 _CACHE = {}
 
 

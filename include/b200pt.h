@@ -103,7 +103,8 @@ typedef struct b200pt_bvh_stats
     int built_on_device;            /* 1: the device builder (B200PT_BVH_BUILD_DEVICE), 0: the host SAH builder */
     float sah_cost;
     float node_fill;                /* occupied child slots / (8 * node_count) */
-    double build_seconds;
+    double build_seconds;           /* wall clock of b200pt_bvh_build (host build + upload, or upload + device build) */
+    double device_build_seconds;    /* device builder only: CUDA-event time of the build with the geometry already on the device */
 } b200pt_bvh_stats;
 
 /* ---- context, memory, streams, events ------------------------------------------------------------------------ */
@@ -143,7 +144,8 @@ B200PT_API int b200pt_tex2d_array_create(b200pt_ctx* ctx, void* const* descripto
 
 /* ---- acceleration structure ---------------------------------------------------------------------------------- */
 /* vertices: 3 floats per vertex; triangle_indices: 3 ints per triangle (host pointers). The primitive index reported
- * by the kernels is the index into triangle_indices / 3, as in the reference. flags: reserved, pass 0. */
+ * by the kernels is the index into triangle_indices / 3, as in the reference. flags: 0 or B200PT_BVH_BUILD_DEVICE. */
+#define B200PT_BVH_BUILD_DEVICE 1u   /* flags: build on the GPU (Morton LBVH + SAH-optimal collapse) instead of the host's binned-SAH builder */
 B200PT_API int b200pt_bvh_build(b200pt_ctx* ctx, const float* vertices, int vertex_count, const int* triangle_indices, int triangle_count, unsigned flags, b200pt_bvh** out_bvh);
 B200PT_API int b200pt_bvh_destroy(b200pt_ctx* ctx, b200pt_bvh* bvh);
 B200PT_API void* b200pt_bvh_device_handle(b200pt_bvh* bvh);             /* value for HIPRTRenderData::geom */

@@ -33,6 +33,14 @@ VARIANTS = {
     "ris": {"DirectLightSamplingStrategy": "LSS_RIS_BSDF_AND_LIGHT", "EnvmapSamplingStrategy": "ESS_ALIAS_TABLE"},
     # config C4
     "restir": {"DirectLightSamplingStrategy": "LSS_RESTIR_DI", "EnvmapSamplingStrategy": "ESS_NO_SAMPLING"},
+    # the rest of the permutation matrix of SURVEY.md 8(b): spherical-cap GGX sampling under RIS / ReSTIR DI, ReSTIR DI with the alias table
+    "ris_caps": {"DirectLightSamplingStrategy": "LSS_RIS_BSDF_AND_LIGHT", "EnvmapSamplingStrategy": "ESS_ALIAS_TABLE",
+                 "PrincipledBSDFAnisotropicGGXSampleFunction": "GGX_VNDF_SPHERICAL_CAPS"},
+    "restir_caps": {"DirectLightSamplingStrategy": "LSS_RESTIR_DI", "EnvmapSamplingStrategy": "ESS_NO_SAMPLING",
+                    "PrincipledBSDFAnisotropicGGXSampleFunction": "GGX_VNDF_SPHERICAL_CAPS"},
+    "restir_alias": {"DirectLightSamplingStrategy": "LSS_RESTIR_DI", "EnvmapSamplingStrategy": "ESS_ALIAS_TABLE"},
+    "restir_alias_caps": {"DirectLightSamplingStrategy": "LSS_RESTIR_DI", "EnvmapSamplingStrategy": "ESS_ALIAS_TABLE",
+                          "PrincipledBSDFAnisotropicGGXSampleFunction": "GGX_VNDF_SPHERICAL_CAPS"},
 }
 
 CXXFLAGS = ["-std=c++20", "-O2", "-fopenmp", "-ffp-contract=off", "-fPIC", "-w"]

@@ -46,3 +46,25 @@ def test_ray_queue_loop_flavours_equal_brute_force(queue_shim_binary, mode):
     the host: closest hits (id, t bit-equal, triangle slot) and occlusion flags against a brute-force loop over all triangles."""
     r = subprocess.run([queue_shim_binary, str(mode)], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout + r.stderr
+
+
+@pytest.fixture(scope="module")
+def lbvh_shim_binary(tmp_path_factory):
+    cuda_inc = "/usr/local/cuda/include"
+    if not os.path.exists(os.path.join(cuda_inc, "cuda_runtime.h")):
+        pytest.skip("CUDA headers not installed")
+    out = str(tmp_path_factory.mktemp("shim") / "lbvh_host_test")
+    cmd = ["g++", "-std=c++17", "-O1", "-I", cuda_inc, "-I", CSRC, "-I", os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "host_shim", "lbvh_host_test.cpp"), "-o", out]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+    return out
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2, 3, 4])
+def test_device_builder_steps_equal_brute_force(lbvh_shim_binary, mode):
+    """The per-element functions of the DEVICE BVH8 builder (Morton codes, Karras radix tree, bottom-up boxes + collapse costs, emission;
+    csrc/bvh8_build_device.cuh) in serial loops on the host: every triangle emitted once, traversal equals brute force, depth fits the stack.
+    Modes: soup, height field, one triangle, duplicated axis-aligned triangles (equal Morton codes, flat boxes), two triangles."""
+    r = subprocess.run([lbvh_shim_binary, str(mode)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+

@@ -152,10 +152,66 @@ def test_c3_hit_ids_on_the_10m_triangle_bvh(pt, wl, ctx, ref):
         assert np.array_equal(ctx.trace_queue(bvh, rays, t_max, last), occ_ref)
         c = ctx.counters_read(True)
         assert c["stack_overflows"] == 0, c
+        # the same rays on the tree the DEVICE builder makes of the scene: hit ids are a property of the triangles, not
+        # of the tree, so they must again equal the reference's
+        bvh_d = ctx.build_bvh(cfg["scene"].vertices, cfg["scene"].indices, device=True)
+        try:
+            info_d = ctx.bvh_info(bvh_d)
+            print("host build:", info, "\ndevice build:", info_d)
+            assert info_d["built_on_device"] and info_d["triangles"] == 9_998_802 and 2 * info_d["max_depth"] + 1 <= 48, info_d
+            assert info_d["device_build_seconds"] < 1.0, info_d
+            dprim, dt, _ = ctx.trace_queue(bvh_d, log["rays"], None, log["last_prim"])
+            _assert_hits_equal(dprim, dt, log, "ray-queue kernel on the device-built tree")
+            assert np.array_equal(ctx.trace_queue(bvh_d, rays, t_max, last), occ_ref)
+            assert ctx.counters_read(True)["stack_overflows"] == 0
+        finally:
+            ctx.destroy_bvh(bvh_d)
     finally:
         ctx.set_trace_flavour(-1)
         ctx.counters_enable(False)
         ctx.destroy_bvh(bvh)
+
+
+@pytest.mark.parametrize("scene_name", ["cornell", "synthetic_small", "tiny"])
+def test_device_built_bvh_gives_the_same_hits(pt, wl, ctx, scene_name):
+    """b200pt_bvh_build with B200PT_BVH_BUILD_DEVICE (Morton LBVH + SAH-optimal collapse on the GPU) against the host builder's tree:
+    closest hits (id, t, uv bits; exact-distance ties excluded) and occlusion flags of random + axis-parallel rays, per-thread traversal and
+    ray-queue kernel; edge cases: one and two triangles."""
+    rng = np.random.default_rng(17)
+    if scene_name == "tiny":
+        cases = [(np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32), np.array([0, 1, 2], np.int32)),
+                 (np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 1], [1, 0, 1], [0, 1, 1]], np.float32), np.array([0, 1, 2, 3, 4, 5], np.int32))]
+    else:
+        scene = getattr(wl, scene_name)(64, 48)["scene"]
+        cases = [(scene.vertices, scene.indices)]
+    for vertices, indices in cases:
+        host, dev = ctx.build_bvh(vertices, indices), ctx.build_bvh(vertices, indices, device=True)
+        try:
+            ih, idv = ctx.bvh_info(host), ctx.bvh_info(dev)
+            assert idv["built_on_device"] and not ih["built_on_device"] and idv["triangles"] == ih["triangles"] == len(indices) // 3
+            lo, hi = vertices.min(axis=0), vertices.max(axis=0)
+            n = 200_000
+            o = rng.uniform(lo - 0.3 * (hi - lo) - 0.1, hi + 0.3 * (hi - lo) + 0.1, (n, 3)).astype(np.float32)
+            d = rng.normal(size=(n, 3)).astype(np.float32)
+            d[::11, 1] = 0.0
+            d[::13, 2] = -0.0
+            d /= np.linalg.norm(d, axis=1, keepdims=True)
+            rays = np.ascontiguousarray(np.concatenate([o, d], axis=1), np.float32)
+            last = rng.integers(-1, len(indices) // 3, n).astype(np.int32)
+            t_max = rng.uniform(0.05, float(np.linalg.norm(hi - lo)) + 1.0, n).astype(np.float32)
+            ph, th, uh = ctx.trace_closest(host, rays, last)
+            for fn in (ctx.trace_closest, lambda b, r, l: ctx.trace_queue(b, r, None, l)):
+                pd, td, ud = fn(dev, rays, last)
+                ties = (pd != ph) & (td == th)
+                assert ((pd == ph) | ties).all(), f"{int(((pd != ph) & ~ties).sum())} hit ids differ between the device-built and the host-built tree"
+                same = pd == ph
+                assert np.array_equal(td[same], th[same]) and np.array_equal(ud[same], uh[same])
+            assert (ph >= 0).any()
+            assert np.array_equal(ctx.trace_shadow(dev, rays, t_max, last), ctx.trace_shadow(host, rays, t_max, last))
+            assert np.array_equal(ctx.trace_queue(dev, rays, t_max, last), ctx.trace_shadow(host, rays, t_max, last))
+        finally:
+            ctx.destroy_bvh(host)
+            ctx.destroy_bvh(dev)
 
 
 def test_c2_size_ray_batches(pt, wl, ctx, ref):
@@ -391,6 +447,42 @@ def test_restir_di_parity(pt, wl, ctx, ref):
         assert close.mean() > 0.995, (f, close.mean())
     assert ia.shape[0] == n
     a, b = r.pixels() / frames, g.download("pixels") / frames
+    err = _rel_err(a, b)
+    assert err < 1e-3, err
+    assert abs(a.mean() - b.mean()) / a.mean() < 1e-3
+    g.close()
+
+
+@pytest.mark.parametrize("lss,ess,ggx,oracle_variant", [
+    ("mis", "none", 1, "mis_caps"), ("ris", "none", 1, "ris_caps"), ("ris", "alias_table", 1, "ris_caps"),
+    ("restir_di", "none", 1, "restir_caps"), ("restir_di", "alias_table", 0, "restir_alias"), ("restir_di", "alias_table", 1, "restir_alias_caps")])
+def test_kernel_permutation_matrix_parity(pt, wl, ctx, ref, lss, ess, ggx, oracle_variant):
+    """{MIS, RIS, ReSTIR DI} x {no envmap sampling, alias table} x {VNDF, spherical caps}. The permutations the configs do
+    not use, each against the reference's CPU kernels compiled with the same KernelOptions (oracle/build_ref.py), matched RNG streams,
+    3 frames, mean relative radiance error <= 1e-3 (north-star tolerance) and G-buffer hit ids identical."""
+    if not ref.available(oracle_variant):
+        pytest.skip(f"oracle variant {oracle_variant} is not built")
+    procedural = importlib.import_module("hiprt-path-tracer_b200.procedural")
+    if lss == "restir_di":
+        cfg = wl.many_lights(112, 80, boxes=120, lights=2000)
+    elif ess == "alias_table":
+        cfg = wl.synthetic_small(112, 80, ggx=ggx)
+    else:
+        cfg = wl.cornell(112, 80)
+    if ess == "alias_table" and cfg["envmap"] is None:
+        cfg["envmap"] = {"texels": procedural.procedural_envmap(256, 128), "alias_probas": None, "alias_alias": None, "total_sum": 0.0}
+    cfg["options"] = dict(lss=lss, ess=ess, ggx=ggx, later=3)
+    cfg["oracle_variant"] = oracle_variant
+    r = wl.setup_oracle(ref, pt.structs, cfg)
+    g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="cpu")
+    frames = 3
+    for _ in range(frames):
+        r.render(1)
+        g.render_frame()
+    g.synchronize()
+    assert np.array_equal(g.download("first_hit_prim_index"), r.buffer("first_hit_prim_index"))
+    a, b = r.pixels() / frames, g.download("pixels") / frames
+    assert np.isfinite(b).all() and a.mean() > 0
     err = _rel_err(a, b)
     assert err < 1e-3, err
     assert abs(a.mean() - b.mean()) / a.mean() < 1e-3
