@@ -74,6 +74,20 @@ def measured_traffic(workload, width, height, spf):
     return entry["trace_queue_dram_bytes_per_step"] if entry else None
 
 
+class oracle_prints_to_stderr:
+    """The reference's CPU kernels print diagnostics ('NaN at [x, y], sample n') on stdout from C++; this process must print ONE JSON line
+    there. While the oracle runs, file descriptor 1 points at stderr."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+
+    def __exit__(self, *exc):
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
+
+
 def host_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -122,14 +136,15 @@ def run_reference(args, cfg, pt):
     core, each step a bounded sample of the workload (see bounded_oracle)."""
     from oracle import ref
     wl = importlib.import_module("hiprt-path-tracer_b200.workloads")
-    r, cores, t_pass, frame, shrink = bounded_oracle(ref, wl, pt, cfg)
-    for _ in range(max(0, args.warmup - 2)):
-        r.render(1)
-    r.ray_count(reset=True)
-    t0 = time.time()
-    for _ in range(args.steps):
-        r.render(1)
-    dt = time.time() - t0
+    with oracle_prints_to_stderr():
+        r, cores, t_pass, frame, shrink = bounded_oracle(ref, wl, pt, cfg)
+        for _ in range(max(0, args.warmup - 2)):
+            r.render(1)
+        r.ray_count(reset=True)
+        t0 = time.time()
+        for _ in range(args.steps):
+            r.render(1)
+        dt = time.time() - t0
     rays = r.ray_count()
     value = rays / dt / 1e6
     sample = f"{args.steps} sample passes of the {frame} of {cfg['name']} (one step = 1 spp), OpenMP over rows on {cores} threads"
@@ -397,12 +412,13 @@ def run_ours(args, cfg, pt):
     if world == 1 and not args.no_cpu_baseline:
         from oracle import ref
         # Bounded sample (~10-30 s of CPU work), every host core (bounded_oracle)
-        r, cores, t_pass, frame, shrink = bounded_oracle(ref, wl, pt, cfg)
-        n = int(min(16, max(1, 12.0 / max(t_pass, 1e-3))))
-        r.ray_count(reset=True)
-        t0 = time.time()
-        r.render(n)
-        dt = time.time() - t0
+        with oracle_prints_to_stderr():
+            r, cores, t_pass, frame, shrink = bounded_oracle(ref, wl, pt, cfg)
+            n = int(min(16, max(1, 12.0 / max(t_pass, 1e-3))))
+            r.ray_count(reset=True)
+            t0 = time.time()
+            r.render(n)
+            dt = time.time() - t0
         out["cpu_baseline"] = {"value": r.ray_count() / dt / 1e6, "unit": "Mrays/s", "cores": cores, "kind": "reference",
                                "sample": f"{n} sample passes of the {frame} of {cfg['name']} with the reference's CPU kernels (oracle/_ref), OpenMP over rows",
                                "samples_per_px_per_s": n / dt / shrink}

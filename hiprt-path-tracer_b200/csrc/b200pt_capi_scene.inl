@@ -596,6 +596,43 @@ int b200pt_set_trace_flavour(b200pt_ctx* ctx, int flavour)
     return B200PT_SUCCESS;
 }
 
+static int debug_function(b200pt_ctx* ctx, int which, const HIPRTRenderData* rd, const void* materials, void* volume_states, const float* vecs, unsigned int* seeds, long long n, int ggx, float* out,
+                          const char* what)
+{
+    REQUIRE(ctx != nullptr && n >= 0 && (n == 0 || out != nullptr));
+    HIPRTRenderData none;
+    memset(&none, 0, sizeof(none));
+    cudaError_t e = pt::launch_debug_function(which, rd ? rd : &none, materials, volume_states, vecs, seeds, n, ggx, out, ctx->main_stream);
+    if (e != cudaSuccess)
+        return cuda_fail(e, what);
+    return B200PT_SUCCESS;
+}
+
+int b200pt_debug_bsdf_eval(b200pt_ctx* ctx, const HIPRTRenderData* render_data, const void* d_materials, void* d_volume_states, const float* d_vecs, long long n, float* d_out)
+{
+    REQUIRE(render_data != nullptr && (n == 0 || (d_materials != nullptr && d_volume_states != nullptr && d_vecs != nullptr)));
+    return debug_function(ctx, 0, render_data, d_materials, d_volume_states, d_vecs, nullptr, n, 0, d_out, "debug_bsdf_eval");
+}
+
+int b200pt_debug_bsdf_sample(b200pt_ctx* ctx, const HIPRTRenderData* render_data, const void* d_materials, void* d_volume_states, const float* d_vecs, unsigned int* d_seeds, long long n, int ggx_sampler,
+                             float* d_out)
+{
+    REQUIRE(render_data != nullptr && (ggx_sampler == 0 || ggx_sampler == 1) && (n == 0 || (d_materials != nullptr && d_volume_states != nullptr && d_vecs != nullptr && d_seeds != nullptr)));
+    return debug_function(ctx, 1, render_data, d_materials, d_volume_states, d_vecs, d_seeds, n, ggx_sampler, d_out, "debug_bsdf_sample");
+}
+
+int b200pt_debug_envmap_sample(b200pt_ctx* ctx, const HIPRTRenderData* render_data, unsigned int* d_seeds, long long n, float* d_out)
+{
+    REQUIRE(render_data != nullptr && render_data->world_settings.alias_table_probas != nullptr && (n == 0 || d_seeds != nullptr));
+    return debug_function(ctx, 2, render_data, nullptr, nullptr, nullptr, d_seeds, n, 0, d_out, "debug_envmap_sample");
+}
+
+int b200pt_debug_thin_film_fresnel(b200pt_ctx* ctx, const void* d_materials, const float* d_ambient_ior_and_cosine, long long n, float* d_out)
+{
+    REQUIRE(n == 0 || (d_materials != nullptr && d_ambient_ior_and_cosine != nullptr));
+    return debug_function(ctx, 3, nullptr, d_materials, nullptr, d_ambient_ior_and_cosine, nullptr, n, 0, d_out, "debug_thin_film_fresnel");
+}
+
 int b200pt_set_ray_bin_bits(b200pt_ctx* ctx, int bits)
 {
     REQUIRE(ctx != nullptr && bits >= -1 && bits <= pt::kRayBinBitsMax);

@@ -427,4 +427,98 @@ cudaError_t PT_SUFFIXED(launch_trace_shadow)(const Bvh8Device& bvh, const float*
     PT_SUFFIXED(k_trace_shadow)<<<(unsigned)((n + block - 1) / block), block, 0, stream>>>(bvh, rays, t_max, last_prim, n, out_occluded, counters);
     return cudaGetLastError();
 }
+
+#ifndef PT_COUNTERS
+// ---- per-function known-answer entry points (b200pt_debug_*): the device functions of the shading path on
+// caller-provided inputs, one thread per item, so that a failing image test can be bisected to a function. Layouts follow the oracle's
+// ref_bsdf_eval / ref_bsdf_sample / ref_envmap_sample / ref_thin_film_fresnel (oracle/ref_harness_passes.inl).
+__global__ void __launch_bounds__(64) k_debug_bsdf_eval(const __grid_constant__ HIPRTRenderData rd, const SimplifiedRendererMaterial* materials, RayVolumeState* volume_states, const float* vecs,
+                                                        long long n, float* out)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+        return;
+    alignas(16) Material m;
+    load_material(m, materials + i);
+    RayVolumeState vs;
+    copy_volume_state(&vs, volume_states + i);
+    const float* v = vecs + i * 9;
+    float pdf;
+    const RGB f = bsdf_eval(rd, m, vs, f3(v[0], v[1], v[2]), f3(v[3], v[4], v[5]), f3(v[6], v[7], v[8]), pdf);
+    copy_volume_state(volume_states + i, &vs);
+    out[i * 4 + 0] = f.r; out[i * 4 + 1] = f.g; out[i * 4 + 2] = f.b; out[i * 4 + 3] = pdf;
+}
+
+template <int GGX_SAMPLER>
+__global__ void __launch_bounds__(64) k_debug_bsdf_sample(const __grid_constant__ HIPRTRenderData rd, const SimplifiedRendererMaterial* materials, RayVolumeState* volume_states, const float* vecs,
+                                                          unsigned int* seeds, long long n, float* out)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+        return;
+    alignas(16) Material m;
+    load_material(m, materials + i);
+    RayVolumeState vs;
+    copy_volume_state(&vs, volume_states + i);
+    const float* v = vecs + i * 9;
+    float pdf;
+    float3 dir = f3(0.0f, 0.0f, 0.0f);
+    Rng rng(seeds[i]);
+    const RGB f = bsdf_sample<GGX_SAMPLER>(rd, m, vs, f3(v[0], v[1], v[2]), f3(v[3], v[4], v[5]), f3(v[6], v[7], v[8]), dir, pdf, rng);
+    seeds[i] = rng.state;
+    copy_volume_state(volume_states + i, &vs);
+    out[i * 7 + 0] = f.r; out[i * 7 + 1] = f.g; out[i * 7 + 2] = f.b; out[i * 7 + 3] = pdf;
+    out[i * 7 + 4] = dir.x; out[i * 7 + 5] = dir.y; out[i * 7 + 6] = dir.z;
+}
+
+__global__ void __launch_bounds__(64) k_debug_envmap_sample(const __grid_constant__ HIPRTRenderData rd, unsigned int* seeds, long long n, float* out)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+        return;
+    Rng rng(seeds[i]);
+    float3 dir;
+    float pdf, pdf2;
+    const RGB r = envmap_sample<2>(rd.world_settings, dir, pdf, rng);      // ESS_ALIAS_TABLE
+    envmap_eval(rd, dir, pdf2);
+    seeds[i] = rng.state;
+    out[i * 8 + 0] = r.r; out[i * 8 + 1] = r.g; out[i * 8 + 2] = r.b; out[i * 8 + 3] = pdf;
+    out[i * 8 + 4] = dir.x; out[i * 8 + 5] = dir.y; out[i * 8 + 6] = dir.z; out[i * 8 + 7] = pdf2;
+}
+
+__global__ void __launch_bounds__(64) k_debug_thin_film_fresnel(const SimplifiedRendererMaterial* materials, const float* ior_and_cosine, long long n, float* out)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+        return;
+    alignas(16) Material m;
+    load_material(m, materials + i);
+    const RGB f = thin_film_fresnel(m, ior_and_cosine[i * 2 + 0], ior_and_cosine[i * 2 + 1]);
+    out[i * 3 + 0] = f.r; out[i * 3 + 1] = f.g; out[i * 3 + 2] = f.b;
+}
+
+cudaError_t launch_debug_function(int which, const HIPRTRenderData* rd, const void* materials, void* volume_states, const float* vecs, unsigned int* seeds, long long n, int ggx_sampler, float* out,
+                                  cudaStream_t stream)
+{
+    if (n <= 0)
+        return cudaSuccess;
+    const unsigned grid = (unsigned)((n + 63) / 64);
+    const SimplifiedRendererMaterial* mats = reinterpret_cast<const SimplifiedRendererMaterial*>(materials);
+    RayVolumeState* vs = reinterpret_cast<RayVolumeState*>(volume_states);
+    switch (which)
+    {
+    case 0: k_debug_bsdf_eval<<<grid, 64, 0, stream>>>(*rd, mats, vs, vecs, n, out); break;
+    case 1:
+        if (ggx_sampler == 1)
+            k_debug_bsdf_sample<1><<<grid, 64, 0, stream>>>(*rd, mats, vs, vecs, seeds, n, out);
+        else
+            k_debug_bsdf_sample<0><<<grid, 64, 0, stream>>>(*rd, mats, vs, vecs, seeds, n, out);
+        break;
+    case 2: k_debug_envmap_sample<<<grid, 64, 0, stream>>>(*rd, seeds, n, out); break;
+    case 3: k_debug_thin_film_fresnel<<<grid, 64, 0, stream>>>(mats, vecs, n, out); break;
+    default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+#endif
 } // namespace pt

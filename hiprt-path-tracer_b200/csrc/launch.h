@@ -137,6 +137,9 @@ struct RayQueueView
     cudaError_t launch_trace_closest##S(const Bvh8Device& bvh, const float* rays, const int* last_prim, long long n, int* out_prim, float* out_t, float* out_uv, TraversalCounters* counters, cudaStream_t stream); \
     cudaError_t launch_trace_shadow##S(const Bvh8Device& bvh, const float* rays, const float* t_max, const int* last_prim, long long n, unsigned char* out_occluded, TraversalCounters* counters, cudaStream_t stream);
 
+// b200pt_debug_*: which = 0 bsdf_eval, 1 bsdf_sample, 2 envmap_sample (alias table), 3 thin_film_fresnel (timing build only)
+cudaError_t launch_debug_function(int which, const HIPRTRenderData* rd, const void* materials, void* volume_states, const float* vecs, unsigned int* seeds, long long n, int ggx_sampler, float* out,
+                                  cudaStream_t stream);
 PT_DECLARE_LAUNCHERS(_t)
 PT_DECLARE_LAUNCHERS(_c)
 } // namespace pt

@@ -245,6 +245,22 @@ B200PT_API int b200pt_set_trace_flavour(b200pt_ctx* ctx, int flavour);
  * the same part of the BVH. A scheduling choice only: every ray's hit record, hence the frame, is the same bits. Process-wide. */
 B200PT_API int b200pt_set_ray_bin_bits(b200pt_ctx* ctx, int bits);
 
+/* ---- per-function known-answer entry points (the parity pins of SURVEY.md 8c item 3; not used by the render path) -------------------
+ * The device functions of the shading path on caller-provided inputs, one item per thread, so that an image difference can be bisected to
+ * a function. render_data supplies the LUT / envmap pointers (take it from a renderer that has rendered a frame). Device pointers; layouts
+ * as the oracle's ref_bsdf_eval / ref_bsdf_sample / ref_envmap_sample / ref_thin_film_fresnel:
+ *   bsdf_eval     bsdf_dispatcher_eval   (src/Device/includes/Dispatcher.h:18-44): materials n x 256 B (SimplifiedRendererMaterial), volume states
+ *                 n x 36 B (in/out), vecs n x 9 floats (view, shading normal, to-light direction) -> out n x 4 floats (rgb, pdf)
+ *   bsdf_sample   bsdf_dispatcher_sample (Dispatcher.h:46-68): vecs n x 9 (view, shading normal, geometric normal), seeds n (Xorshift32 state,
+ *                 in/out), ggx_sampler 0 VNDF / 1 spherical caps (BSDFs/Microfacet.h:162-218) -> out n x 7 (rgb, pdf, sampled direction)
+ *   envmap_sample envmap_sample + envmap_eval (Envmap.h:77-149), alias table: seeds n (in/out) -> out n x 8 (radiance rgb, pdf, direction, eval pdf)
+ *   thin_film_fresnel (BSDFs/ThinFilm.h:112-219): materials n x 256 B, n x 2 floats (ambient ior, cosine) -> out n x 3 (rgb) */
+B200PT_API int b200pt_debug_bsdf_eval(b200pt_ctx* ctx, const HIPRTRenderData* render_data, const void* d_materials, void* d_volume_states, const float* d_vecs, long long n, float* d_out);
+B200PT_API int b200pt_debug_bsdf_sample(b200pt_ctx* ctx, const HIPRTRenderData* render_data, const void* d_materials, void* d_volume_states, const float* d_vecs, unsigned int* d_seeds, long long n,
+                                        int ggx_sampler, float* d_out);
+B200PT_API int b200pt_debug_envmap_sample(b200pt_ctx* ctx, const HIPRTRenderData* render_data, unsigned int* d_seeds, long long n, float* d_out);
+B200PT_API int b200pt_debug_thin_film_fresnel(b200pt_ctx* ctx, const void* d_materials, const float* d_ambient_ior_and_cosine, long long n, float* d_out);
+
 /* ---- counters (counting build of the same kernels; the timing build has them compiled out) --------------------- */
 B200PT_API int b200pt_counters_enable(b200pt_ctx* ctx, int enable);
 B200PT_API int b200pt_counters_read(b200pt_ctx* ctx, b200pt_counters* out, int reset);
