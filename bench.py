@@ -3,7 +3,7 @@
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cornell]
 
-A "step" is one frame = one call of the renderer's render() = `--samples-per-frame` (default 8) sample passes of the whole
+A "step" is one frame = one call of the renderer's render() = `--samples-per-frame` (default 16) sample passes of the whole
 1080p frame per GPU, the reference's samples_per_frame setting (GPURenderer::render, src/Renderer/GPURenderer.cpp:408-464; per pass
 two launch points: CameraRays, FullPathTracer; here a frame's passes run as fused sample batches where the options allow it; the path tracer
 runs as a wavefront of per-bounce kernels: ray-queue traversal, surface, queue sort, shading phases).
@@ -195,7 +195,7 @@ def run_ours(args, cfg, pt):
         shard_kind = mg.Comm.COLUMNS if sharding == "columns" else mg.Comm.ROWS
         assert mg.Comm.tile(lib, shard_kind, W, H, world, rank) == ((tiles[rank][0], 0, tiles[rank][1], H) if sharding == "columns" else (0, tiles[rank][0], W, tiles[rank][1]))
     bvh_info = ctx.bvh_info(g.bvh)
-    in_flight = int(os.environ.get("B200PT_SAMPLES_IN_FLIGHT", "8"))
+    in_flight = int(os.environ.get("B200PT_SAMPLES_IN_FLIGHT", "16"))
     batched = g.renders_sample_batches
 
     def restart():
@@ -438,7 +438,7 @@ def main():
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--sharding", default="auto", choices=["auto", "samples", "tiles", "columns"],
                     help="N > 1: sample-pass sharding (weak scaling, default for cornell), column tiles (strong scaling, default otherwise) or row tiles (strong scaling; always for ReSTIR DI)")
-    ap.add_argument("--samples-per-frame", type=int, default=8, help="sample passes per step (= per render() call): the reference's samples_per_frame render setting")
+    ap.add_argument("--samples-per-frame", type=int, default=16, help="sample passes per step (= per render() call): the reference's samples_per_frame render setting")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile", action="store_true", help="for ncu: run only 3 warm-up + K frames of the timed pass (no counting / stage / e2e / CPU passes), print no bench line")
     args = ap.parse_args()

@@ -19,7 +19,7 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 
 # -fmad=false: shading arithmetic is evaluated exactly like the CPU oracle (g++ -ffp-contract=off); the traversal's
 # box tests use explicit fused multiply-adds, its triangle test explicit unfused ones.
-NVCC_FLAGS = ["-std=c++17", "-O3", "-lineinfo", "-gencode", "arch=compute_100a,code=sm_100a", "-fmad=false",
+NVCC_FLAGS = ["-std=c++17", "-O3", "-lineinfo", "-gencode", "arch=compute_100a,code=sm_100a", "-fmad=false", "-Xfatbin", "-compress-all",
               "-Xcompiler", "-fPIC,-fopenmp,-fvisibility=hidden", "-I", os.path.join(HERE, "..", "include")]
 
 
@@ -77,7 +77,7 @@ def build(force=False, verbose=False):
         for (lss, ess, later, ggx) in variants():
             objects.append(add(f"fpt_{lss}_{ess}_{later}_{ggx}_{suffix}.o", "b200pt_fpt_variant.cu",
                                defs + [f"-DPT_LSS={lss}", f"-DPT_ESS={ess}", f"-DPT_LATER={later}", f"-DPT_GGX={ggx}"]))
-            if lss == 3:
+            if lss in (3, 4, 5):
                 # the phase kernels of the phased MIS pipeline, with the BSDF entry points inlined (see b200pt_phase_variant.cu)
                 objects.append(add(f"phase_{lss}_{ess}_{later}_{ggx}_{suffix}.o", "b200pt_phase_variant.cu",
                                    defs + [f"-DPT_LSS={lss}", f"-DPT_ESS={ess}", f"-DPT_LATER={later}", f"-DPT_GGX={ggx}", "-DPT_BSDF_INLINE"]))

@@ -267,7 +267,7 @@ static int ensure_wavefront(b200pt_ctx* ctx, int lane, uint32_t paths, uint32_t 
         return p;
     };
     const size_t n = capacity;
-    float4** f4[] = {&wf.origin_rng, &wf.dir_prim, &wf.throughput, &wf.color, &wf.hit_point, &wf.hit_ns, &wf.hit_ng, &wf.final_color, &wf.aov_normal, &wf.aov_albedo};
+    float4** f4[] = {&wf.origin_rng, &wf.dir_prim, &wf.throughput, &wf.color, &wf.hit_point, &wf.hit_ns, &wf.hit_ng, &wf.final_color, &wf.aov_normal, &wf.aov_albedo, &wf.ris_a, &wf.ris_b};
     bool ok = true;
     for (float4** a : f4)
         ok &= (*a = static_cast<float4*>(alloc(n * sizeof(float4)))) != nullptr;
@@ -401,8 +401,9 @@ int b200pt_launch_PathTraceSamples(b200pt_ctx* ctx, const HIPRTRenderData* rende
     // A pass of the batch must not depend on the previous pass' result, and the phased MIS pipeline must be the one that runs
     const bool adaptive_buffers = (rs.stop_pixel_noise_threshold > 0.0f || rs.enable_adaptive_sampling) && rs.accumulate;
     const bool low_resolution = rs.wants_render_low_resolution && rs.allow_render_low_resolution && rs.accumulate;
-    if (ctx->options.lss != 3 || ctx->path_mode != pt::WF_PHASED || rs.number_of_light_samples != 1 || rs.do_alpha_testing || adaptive_buffers || low_resolution)
-        return fail(B200PT_ERROR_VARIANT_NOT_COMPILED, "b200pt_launch_PathTraceSamples: fused sample batches need LSS_MIS_LIGHT_BSDF in the phased wavefront shape with one light sample, "
+    const bool strategy_ok = ctx->options.lss == 3 || (ctx->options.lss == 4 && rs.ris_settings.number_of_bsdf_candidates == 1);
+    if (!strategy_ok || ctx->path_mode != pt::WF_PHASED || rs.number_of_light_samples != 1 || rs.do_alpha_testing || adaptive_buffers || low_resolution)
+        return fail(B200PT_ERROR_VARIANT_NOT_COMPILED, "b200pt_launch_PathTraceSamples: fused sample batches need LSS_MIS_LIGHT_BSDF or LSS_RIS_BSDF_AND_LIGHT (one BSDF candidate) in the phased wavefront shape with one light sample, "
                                                         "no alpha testing, no adaptive sampling / pixel noise threshold and no low-resolution rendering; launch CameraRays and FullPathTracer separately");
     pt::Tile t = tile_of(tile, res);
     if (t.x1 <= t.x0 || t.y1 <= t.y0)

@@ -89,10 +89,9 @@ __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_bsdf)(const __grid_co
 #ifndef PT_PAIR_PHASES_DEFAULT
 #define PT_PAIR_PHASES_DEFAULT false
 #endif
-#if PT_LSS == 3
-// The phase kernels P1..P5 of the phased MIS pipeline live in their own translation unit (b200pt_phase_variant.cu), compiled
-// with the BSDF entry points inlined; this one launches them through launch_phase.
-enum PhaseKernel { PHASE_NEE_LIGHT_EVAL, PHASE_NEE_BSDF_SAMPLE, PHASE_ENV_LIGHT_EVAL, PHASE_ENV_BSDF_SAMPLE, PHASE_BSDF_RESOLVED, PHASE_NEE_PAIR, PHASE_ENV_PAIR };
+// The phase kernels of the phased pipelines (MIS: P1..P5; RIS: R1, R2, P3..P5) live in their own translation unit
+// (b200pt_phase_variant.cu), compiled with the BSDF entry points inlined; this one launches them through launch_phase.
+enum PhaseKernel { PHASE_NEE_LIGHT_EVAL, PHASE_NEE_BSDF_SAMPLE, PHASE_ENV_LIGHT_EVAL, PHASE_ENV_BSDF_SAMPLE, PHASE_BSDF_RESOLVED, PHASE_NEE_PAIR, PHASE_ENV_PAIR, PHASE_RIS_CANDIDATES, PHASE_RIS_SELECT };
 cudaError_t PT_VARIANT_NAME(launch_phase)(int which, unsigned blocks, cudaStream_t stream, const HIPRTRenderData* rd, int2 res, Tile tile, const WavefrontState* wf, int bounce,
                                           bool lights_sampled, bool envmap_sampled);
 __global__ void __launch_bounds__(128) PT_VARIANT_NAME(k_wf_surface)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce)
@@ -101,6 +100,7 @@ __global__ void __launch_bounds__(128) PT_VARIANT_NAME(k_wf_surface)(const __gri
         wf_surface_path<PT_ESS>(rd, res, tile, wf, bounce, i);
 }
 
+#if PT_LSS == 3 || PT_LSS == 4
 // ---- sample batches (wavefront.cuh): camera rays of every pass in flight, camera hits, accumulation in pass order --------------------
 __global__ void __launch_bounds__(128) PT_VARIANT_NAME(k_wf_camera)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf,
                                                                    const __grid_constant__ SampleBatch batch)
@@ -154,7 +154,7 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
     const uint32_t paths = (uint32_t)(tile.x1 - tile.x0) * (uint32_t)(tile.y1 - tile.y0) * (batch ? batch->count : 1u);
     if (paths > wf->capacity || (uint32_t)nb_bounces > wf->max_bounces)
         return cudaErrorInvalidValue;
-    if (batch && (mode != WF_PHASED || PT_LSS != 3 || wf->fused_camera == 0u || wf->samples != batch->count))
+    if (batch && (mode != WF_PHASED || (PT_LSS != 3 && PT_LSS != 4) || wf->fused_camera == 0u || wf->samples != batch->count))
         return cudaErrorInvalidValue;
 
     // Queue lengths are only known on the device: queue kernels run grid-stride loops on a grid capped at a few blocks per
@@ -176,13 +176,17 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
             PT_VARIANT_NAME(k_wf_bounce)<<<blocks(64), 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
         return cudaGetLastError();
     }
-#if PT_LSS == 3
-    // alpha testing would make shadow rays draw random numbers (FilterFunction.h:42): then the phases cannot be reordered
-    const bool phased_mis = mode == WF_PHASED && rd->render_settings.number_of_light_samples == 1 && !rd->render_settings.do_alpha_testing;
-#else
-    const bool phased_mis = false;
-#endif
-    if (batch && !phased_mis)
+    // Which strategy the phases run: MIS light + BSDF (LSS 3), or RIS (LSS 4; LSS 5 with RIS on the later bounces, from bounce 1 on: bounce 0
+    // shades from the ReSTIR DI reservoirs in the unphased kernels). Alpha testing would make shadow rays draw random numbers
+    // (FilterFunction.h:42): then the phases cannot be reordered. RIS runs phased with one BSDF candidate (the default) only.
+    constexpr bool kPhasesMis = PT_LSS == 3;
+    constexpr bool kPhasesRis = PT_LSS == 4 || (PT_LSS == 5 && PT_LATER == 3);
+    const HIPRTRenderSettings& rs = rd->render_settings;
+    const bool low_resolution = rs.wants_render_low_resolution && rs.allow_render_low_resolution && rs.accumulate;
+    static const bool ris_phases_enabled = [] { const char* v = getenv("B200PT_RIS_PHASES"); return v ? atoi(v) != 0 : true; }();
+    const bool phased = mode == WF_PHASED && rs.number_of_light_samples == 1 && !rs.do_alpha_testing &&
+                        (kPhasesMis || (kPhasesRis && ris_phases_enabled && !low_resolution && rs.ris_settings.number_of_bsdf_candidates == 1));
+    if (batch && !(phased && (kPhasesMis || PT_LSS == 4)))
         return cudaErrorInvalidValue;
 #ifdef PT_COUNTERS
     TraversalCounters* const counters = reinterpret_cast<TraversalCounters*>(rd->hiprt_function_table);
@@ -208,7 +212,7 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
         uint32_t* const cursors = wf->cursors + kCursorsPerBounce * bounce;
         (void)counts; (void)cursors;
         stage(STAGE_SURFACE);
-#if PT_LSS == 3
+#if PT_LSS == 3 || PT_LSS == 4
         if (bounce == 0 && batch)
         {
             PT_VARIANT_NAME(k_wf_camera)<<<blocks(128), 128, 0, stream>>>(*rd, res, tile, *wf, *batch);
@@ -224,8 +228,7 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
 #endif
         if (bounce == 0)
             PT_VARIANT_NAME(k_wf_gen)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile, *wf);
-#if PT_LSS == 3
-        else if (phased_mis)
+        else if (phased)
         {
             stage(bin_bits_ext > 0 ? STAGE_SORT : STAGE_TRACE);
             RayQueueView q = {wf->ray_queue[(bounce - 1) & 1], counts + 0, cursors + 0, wf->origin_rng, wf->dir_prim, wf->hit_tuvp, wf->hit_tri_slot, nullptr};
@@ -243,7 +246,6 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
             wf_binned.ray_queue[(bounce - 1) & 1] = const_cast<uint32_t*>(q.ids);
             PT_VARIANT_NAME(k_wf_surface)<<<blocks(128), 128, 0, stream>>>(*rd, res, tile, wf_binned, bounce);
         }
-#endif
         else
             PT_VARIANT_NAME(k_wf_extend)<<<blocks(128), 128, 0, stream>>>(*rd, res, tile, *wf, bounce);
         stage(STAGE_SORT);
@@ -254,12 +256,43 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
         if (e != cudaSuccess)
             return e;
         stage(STAGE_SHADE);
-#if PT_LSS == 3
-        if (phased_mis)
+        if (phased && !(PT_LSS == 5 && bounce == 0))
         {
             const unsigned g64 = blocks(64);
             const bool lights = rd->buffers.emissive_triangles_count > 0;
             const bool envmap = PT_ESS != 0 && rd->world_settings.ambient_light_type == AMBIENT_ENVMAP;
+            RayQueueView qa = {wf->any_queue, counts + 2, cursors + 6, wf->nee_ray_o, wf->nee_ray_d, nullptr, nullptr, wf->nee_ray_o};
+            RayQueueView qc = {wf->closest_queue, counts + 3, cursors + 9, wf->nee_ray_o, wf->nee_ray_d, wf->hit_tuvp, wf->hit_tri_slot, nullptr};
+            if (kPhasesRis)
+            {
+                // R1 -> closest trace of the BSDF candidates' rays -> R2 -> envmap phases -> any-hit trace of the winners' shadow rays (+ the
+                // envmap rays) -> resolve
+                if (lights)
+                {
+                    PT_VARIANT_NAME(launch_phase)(PHASE_RIS_CANDIDATES, g64, stream, rd, res, tile, wf, bounce, lights, envmap);
+                    stage(STAGE_TRACE);
+                    e = PT_SUFFIXED(launch_trace_queue)(rd->geom, qc, false, trace_blocks, counters, stream);
+                    if (e != cudaSuccess)
+                        return e;
+                    stage(STAGE_SHADE);
+                    PT_VARIANT_NAME(launch_phase)(PHASE_RIS_SELECT, g64, stream, rd, res, tile, wf, bounce, lights, envmap);
+                }
+                if (envmap)
+                {
+                    PT_VARIANT_NAME(launch_phase)(PHASE_ENV_LIGHT_EVAL, g64, stream, rd, res, tile, wf, bounce, lights, envmap);
+                    PT_VARIANT_NAME(launch_phase)(PHASE_ENV_BSDF_SAMPLE, g64, stream, rd, res, tile, wf, bounce, lights, envmap);
+                }
+                if (lights || envmap)
+                {
+                    stage(STAGE_TRACE);
+                    e = PT_SUFFIXED(launch_trace_queue)(rd->geom, qa, true, trace_blocks, counters, stream);
+                    if (e != cudaSuccess)
+                        return e;
+                    stage(STAGE_SHADE);
+                }
+                PT_VARIANT_NAME(launch_phase)(PHASE_BSDF_RESOLVED, g64, stream, rd, res, tile, wf, bounce, lights, envmap);
+                continue;
+            }
             // B200PT_PAIR_PHASES=1: eval + sample of a MIS pair in one kernel on one loaded vertex (one ~400-byte vertex load
             // less per pair, twice the code per kernel); same arithmetic and RNG order, same bits
             static const bool pair_phases = [] { const char* v = getenv("B200PT_PAIR_PHASES"); return v ? atoi(v) != 0 : PT_PAIR_PHASES_DEFAULT; }();
@@ -279,8 +312,6 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
             }
             stage(bin_bits_nee > 0 ? STAGE_SORT : STAGE_TRACE);
             static const bool pair_trace = [] { const char* v = getenv("B200PT_PAIR_TRACE"); return v ? atoi(v) != 0 : true; }();
-            RayQueueView qa = {wf->any_queue, counts + 2, cursors + 6, wf->nee_ray_o, wf->nee_ray_d, nullptr, nullptr, wf->nee_ray_o};
-            RayQueueView qc = {wf->closest_queue, counts + 3, cursors + 9, wf->nee_ray_o, wf->nee_ray_d, wf->hit_tuvp, wf->hit_tri_slot, nullptr};
             if (lights || envmap)
             {
                 e = PT_SUFFIXED(launch_bin_rays)(rd->geom, qa, wf->bin_hist, wf->bin_keys, wf->binned_any, bin_bits_nee, wf->sm_count, stream);
@@ -319,9 +350,7 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
             stage(STAGE_SHADE);
             PT_VARIANT_NAME(launch_phase)(PHASE_BSDF_RESOLVED, g64, stream, rd, res, tile, wf, bounce, lights, envmap);
         }
-        else
-#endif
-        if (mode == WF_PHASED)
+        else if (mode == WF_PHASED)
         {
             PT_VARIANT_NAME(k_wf_direct)<<<blocks(64), 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
             PT_VARIANT_NAME(k_wf_bsdf)<<<blocks(64), 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
@@ -329,7 +358,7 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
         else
             PT_VARIANT_NAME(k_wf_shade)<<<blocks(64), 64, 0, stream>>>(*rd, res, tile, *wf, bounce);
     }
-#if PT_LSS == 3
+#if PT_LSS == 3 || PT_LSS == 4
     if (batch)
     {
         stage(STAGE_SHADE);

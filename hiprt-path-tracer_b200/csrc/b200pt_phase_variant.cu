@@ -24,36 +24,51 @@ namespace pt
         PT_FOR_EACH_QUEUED(i, wf.counts[kCountsPerBounce * bounce + 1], KID)                                                                                                          \
             CALL(rd, res, tile, wf, bounce, i);                                                                                                                        \
     }
+#if PT_LSS == 3
 PT_QUEUE_KERNEL(k_wf_nee_light_eval, 64, 2, nee_light_eval_path)
 PT_QUEUE_KERNEL(k_wf_nee_bsdf_sample, 64, 3, nee_bsdf_sample_path<PT_GGX>)
+#endif
 PT_QUEUE_KERNEL(k_wf_env_light_eval, 64, 4, env_light_eval_path<PT_ESS>)
 PT_QUEUE_KERNEL(k_wf_env_bsdf_sample, 64, 5, env_bsdf_sample_path<PT_GGX>)
 // eval + sample of a MIS pair on one loaded vertex (B200PT_PAIR_PHASES=1); they take the queue cursor of the eval phase
 #define PT_NEE_PAIR nee_pair_path<PT_GGX>
 #define PT_ENV_PAIR env_pair_path<PT_ESS, PT_GGX>
+#if PT_LSS == 3
 PT_QUEUE_KERNEL(k_wf_nee_pair, 64, 2, PT_NEE_PAIR)
 PT_QUEUE_KERNEL(k_wf_env_pair, 64, 4, PT_ENV_PAIR)
+#endif
+// phased RIS (LSS_RIS_BSDF_AND_LIGHT, later bounces of LSS_RESTIR_DI): R1 / R2 of wavefront_mis.cuh
+PT_QUEUE_KERNEL(k_wf_ris_candidates, 64, 2, ris_candidates_path<PT_GGX>)
+PT_QUEUE_KERNEL(k_wf_ris_select, 64, 3, ris_select_path)
 
+// the strategy sample_one_light runs at bounces the phases handle: RIS for LSS 4, and for LSS 5 with RESTIR_DI_LATER_BOUNCES_RIS (bounce >= 1)
+#define PT_PHASED_RIS (PT_LSS == 4 || (PT_LSS == 5 && PT_LATER == 3))
 __global__ void __launch_bounds__(64, PT_PHASE_BLOCKS_PER_SM) PT_VARIANT_NAME(k_wf_bsdf_resolved)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce, bool lights_sampled, bool envmap_sampled)
 {
     PT_FOR_EACH_QUEUED(i, wf.counts[kCountsPerBounce * bounce + 1], 7)
-        wf_bsdf_resolved_path<PT_ESS, PT_GGX>(rd, res, tile, wf, bounce, i, lights_sampled, envmap_sampled);
+        wf_bsdf_resolved_path<PT_ESS, PT_GGX, PT_PHASED_RIS>(rd, res, tile, wf, bounce, i, lights_sampled, envmap_sampled);
 }
 
-enum PhaseKernel { PHASE_NEE_LIGHT_EVAL, PHASE_NEE_BSDF_SAMPLE, PHASE_ENV_LIGHT_EVAL, PHASE_ENV_BSDF_SAMPLE, PHASE_BSDF_RESOLVED, PHASE_NEE_PAIR, PHASE_ENV_PAIR };
+enum PhaseKernel { PHASE_NEE_LIGHT_EVAL, PHASE_NEE_BSDF_SAMPLE, PHASE_ENV_LIGHT_EVAL, PHASE_ENV_BSDF_SAMPLE, PHASE_BSDF_RESOLVED, PHASE_NEE_PAIR, PHASE_ENV_PAIR, PHASE_RIS_CANDIDATES, PHASE_RIS_SELECT };
 
 cudaError_t PT_VARIANT_NAME(launch_phase)(int which, unsigned blocks, cudaStream_t stream, const HIPRTRenderData* rd, int2 res, Tile tile, const WavefrontState* wf, int bounce,
                                           bool lights_sampled, bool envmap_sampled)
 {
     switch (which)
     {
+#if PT_LSS == 3
     case PHASE_NEE_LIGHT_EVAL: PT_VARIANT_NAME(k_wf_nee_light_eval)<<<blocks, 64, 0, stream>>>(*rd, res, tile, *wf, bounce); break;
     case PHASE_NEE_BSDF_SAMPLE: PT_VARIANT_NAME(k_wf_nee_bsdf_sample)<<<blocks, 64, 0, stream>>>(*rd, res, tile, *wf, bounce); break;
+#endif
     case PHASE_ENV_LIGHT_EVAL: PT_VARIANT_NAME(k_wf_env_light_eval)<<<blocks, 64, 0, stream>>>(*rd, res, tile, *wf, bounce); break;
     case PHASE_ENV_BSDF_SAMPLE: PT_VARIANT_NAME(k_wf_env_bsdf_sample)<<<blocks, 64, 0, stream>>>(*rd, res, tile, *wf, bounce); break;
     case PHASE_BSDF_RESOLVED: PT_VARIANT_NAME(k_wf_bsdf_resolved)<<<blocks, 64, 0, stream>>>(*rd, res, tile, *wf, bounce, lights_sampled, envmap_sampled); break;
+#if PT_LSS == 3
     case PHASE_NEE_PAIR: PT_VARIANT_NAME(k_wf_nee_pair)<<<blocks, 64, 0, stream>>>(*rd, res, tile, *wf, bounce); break;
     case PHASE_ENV_PAIR: PT_VARIANT_NAME(k_wf_env_pair)<<<blocks, 64, 0, stream>>>(*rd, res, tile, *wf, bounce); break;
+#endif
+    case PHASE_RIS_CANDIDATES: PT_VARIANT_NAME(k_wf_ris_candidates)<<<blocks, 64, 0, stream>>>(*rd, res, tile, *wf, bounce); break;
+    case PHASE_RIS_SELECT: PT_VARIANT_NAME(k_wf_ris_select)<<<blocks, 64, 0, stream>>>(*rd, res, tile, *wf, bounce); break;
     default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();

@@ -69,6 +69,8 @@ struct WavefrontState
     uint32_t* binned_any;    // 3 * capacity ids: the NEE any-hit queue in bin order
     uint32_t* binned_ext;    // capacity ids: the extension-ray queue (or the NEE closest-hit queue) in bin order
     uint32_t* bin_keys;      // 3 * capacity: bin of queue entry i (histogram pass -> scatter pass)
+    float4* ris_a;           // phased RIS (wavefront_mis.cuh): the reservoir between R1, R2 and the resolve, 2 x float4 per slot
+    float4* ris_b;
 };
 constexpr int kRayBinBitsMax = 6;                                   // cells per axis = 2^bits
 constexpr uint32_t kRayBinsMax = 1u << (3 * kRayBinBitsMax + 3);    // cells x 8 direction octants

@@ -87,20 +87,23 @@ PT_DEV RGB evaluate_reservoir_sample(const HIPRTRenderData& rd, const RayPayload
     return final_color;
 }
 
-// sample_bsdf_and_lights_RIS_reservoir (RIS.h:82-290), RISUseVisiblityTargetFunction = FALSE
-template <int GGX_SAMPLER>
-PT_DEV RISReservoir sample_bsdf_and_lights_RIS_reservoir(const HIPRTRenderData& rd, const RayPayload& payload, const HitInfo& hit, float3 view_direction, Rng& rng)
+// sample_bsdf_and_lights_RIS_reservoir (RIS.h:82-290), RISUseVisiblityTargetFunction = FALSE, cut at the points where it traces a ray, so
+// that the per-thread form below and the phased wavefront (wavefront_mis.cuh: R1 / R2) run the SAME pieces in the same order:
+//   ris_light_candidates        the light-candidate loop (RIS.h:101-190)
+//   ris_bsdf_candidate_sample   BSDF sample of one BSDF candidate and its ray (RIS.h:192-215)       -> closest-hit ray
+//   ris_bsdf_candidate_finish   what the ray hit -> candidate sample + weight (RIS.h:217-280)
+struct RISBsdfCandidate
 {
-    bool inside_surface = dot(view_direction, hit.geometric_normal) < 0;
-    float inside_surface_multiplier = inside_surface ? -1.0f : 1.0f;
-    float3 evaluated_point = hit.inter_point + hit.shading_normal * 1.0e-4f * inside_surface_multiplier;
+    float pdf;
+    float3 direction, origin;
+    RGB color;
+    bool refraction;
+};
 
+PT_DEV void ris_light_candidates(const HIPRTRenderData& rd, const RayPayload& payload, const HitInfo& hit, float3 view_direction, float3 evaluated_point, float inside_surface_multiplier,
+                                 int nb_light_candidates, int nb_bsdf_candidates, Rng& rng, RISReservoir& reservoir)
+{
     const HIPRTRenderSettings& s = rd.render_settings;
-    bool low_res = s.wants_render_low_resolution && s.allow_render_low_resolution && s.accumulate;
-    int nb_light_candidates = low_res ? 1 : s.ris_settings.number_of_light_candidates;
-    int nb_bsdf_candidates = low_res ? 1 : s.ris_settings.number_of_bsdf_candidates;
-
-    RISReservoir reservoir;
     for (int i = 0; i < nb_light_candidates; i++)
     {
         float light_sample_pdf;
@@ -150,50 +153,83 @@ PT_DEV RISReservoir sample_bsdf_and_lights_RIS_reservoir(const HIPRTRenderData& 
         light_sample.emissive_triangle_index = light_info.emissive_triangle_index;
         reservoir.add_one_candidate(light_sample, candidate_weight, rng);
     }
+}
+
+template <int GGX_SAMPLER>
+PT_DEV RISBsdfCandidate ris_bsdf_candidate_sample(const HIPRTRenderData& rd, const RayPayload& payload, const HitInfo& hit, float3 view_direction, float3 evaluated_point,
+                                                  float inside_surface_multiplier, Rng& rng)
+{
+    RISBsdfCandidate c;
+    c.pdf = 0.0f;
+    c.origin = evaluated_point;
+    RayVolumeState trash = payload.volume_state;
+    c.color = bsdf_sample<GGX_SAMPLER>(rd, payload.material, trash, view_direction, hit.shading_normal, hit.geometric_normal, c.direction, c.pdf, rng);
+    c.refraction = dot(c.direction, hit.shading_normal * inside_surface_multiplier) < 0;
+    if (c.refraction)
+        c.origin = hit.inter_point + hit.shading_normal * 1.0e-4f * inside_surface_multiplier * -1.0f;
+    return c;
+}
+
+PT_DEV void ris_bsdf_candidate_finish(const HIPRTRenderData& rd, const HitInfo& hit, const RISBsdfCandidate& c, bool hit_found, const ShadowLightRayHitInfo& light_hit, int nb_light_candidates,
+                                      int nb_bsdf_candidates, RISSample& bsdf_RIS_sample, float& candidate_weight)
+{
+    const HIPRTRenderSettings& s = rd.render_settings;
+    if (hit_found && !light_hit.hit_emission.is_black())
+    {
+        float cosine_at_evaluated_point = fabsf(dot(hit.shading_normal, c.direction));
+        RGB light_contribution = c.color * light_hit.hit_emission * cosine_at_evaluated_point;
+        float target_function = light_contribution.luminance();
+
+        float light_pdf = pdf_of_emissive_triangle_hit(rd, light_hit, c.direction);
+        light_pdf *= c.refraction ? 0.0f : 1.0f;
+
+        bool contributes_enough = check_minimum_light_contribution(s.minimum_light_contribution, light_contribution / light_pdf / c.pdf);
+        if (!contributes_enough)
+            target_function = 0.0f;
+
+        float mis_weight = balance_heuristic(c.pdf, (float)nb_bsdf_candidates, light_pdf, (float)nb_light_candidates);
+        candidate_weight = mis_weight * target_function / c.pdf;
+
+        bsdf_RIS_sample.emissive_triangle_index = light_hit.hit_prim_index;
+        bsdf_RIS_sample.point_on_light_source = c.origin + c.direction * light_hit.hit_distance;
+        bsdf_RIS_sample.is_bsdf_sample = true;
+        bsdf_RIS_sample.bsdf_sample_contribution = c.color;
+        bsdf_RIS_sample.bsdf_sample_cosine_term = cosine_at_evaluated_point;
+        bsdf_RIS_sample.target_function = target_function;
+    }
+}
+
+PT_DEV void ris_candidate_counts(const HIPRTRenderData& rd, int& nb_light_candidates, int& nb_bsdf_candidates)
+{
+    const HIPRTRenderSettings& s = rd.render_settings;
+    bool low_res = s.wants_render_low_resolution && s.allow_render_low_resolution && s.accumulate;
+    nb_light_candidates = low_res ? 1 : s.ris_settings.number_of_light_candidates;
+    nb_bsdf_candidates = low_res ? 1 : s.ris_settings.number_of_bsdf_candidates;
+}
+
+template <int GGX_SAMPLER>
+PT_DEV RISReservoir sample_bsdf_and_lights_RIS_reservoir(const HIPRTRenderData& rd, const RayPayload& payload, const HitInfo& hit, float3 view_direction, Rng& rng)
+{
+    bool inside_surface = dot(view_direction, hit.geometric_normal) < 0;
+    float inside_surface_multiplier = inside_surface ? -1.0f : 1.0f;
+    float3 evaluated_point = hit.inter_point + hit.shading_normal * 1.0e-4f * inside_surface_multiplier;
+
+    int nb_light_candidates, nb_bsdf_candidates;
+    ris_candidate_counts(rd, nb_light_candidates, nb_bsdf_candidates);
+
+    RISReservoir reservoir;
+    ris_light_candidates(rd, payload, hit, view_direction, evaluated_point, inside_surface_multiplier, nb_light_candidates, nb_bsdf_candidates, rng, reservoir);
 
     for (int i = 0; i < nb_bsdf_candidates; i++)
     {
-        float bsdf_sample_pdf = 0.0f;
-        float target_function = 0.0f;
         float candidate_weight = 0.0f;
-        float3 sampled_direction;
-        float3 shadow_ray_origin = evaluated_point;
-        RayVolumeState trash = payload.volume_state;
-
-        RGB bsdf_color = bsdf_sample<GGX_SAMPLER>(rd, payload.material, trash, view_direction, hit.shading_normal, hit.geometric_normal, sampled_direction, bsdf_sample_pdf, rng);
-
-        bool refraction_sampled = dot(sampled_direction, hit.shading_normal * inside_surface_multiplier) < 0;
-        if (refraction_sampled)
-            shadow_ray_origin = hit.inter_point + hit.shading_normal * 1.0e-4f * inside_surface_multiplier * -1.0f;
-
+        RISBsdfCandidate c = ris_bsdf_candidate_sample<GGX_SAMPLER>(rd, payload, hit, view_direction, evaluated_point, inside_surface_multiplier, rng);
         RISSample bsdf_RIS_sample;
-        if (bsdf_sample_pdf > 0.0f)
+        if (c.pdf > 0.0f)
         {
             ShadowLightRayHitInfo light_hit;
-            bool hit_found = evaluate_shadow_light_ray(rd, shadow_ray_origin, sampled_direction, 1.0e35f, light_hit, hit.primitive_index, rng);
-            if (hit_found && !light_hit.hit_emission.is_black())
-            {
-                float cosine_at_evaluated_point = fabsf(dot(hit.shading_normal, sampled_direction));
-                RGB light_contribution = bsdf_color * light_hit.hit_emission * cosine_at_evaluated_point;
-                target_function = light_contribution.luminance();
-
-                float light_pdf = pdf_of_emissive_triangle_hit(rd, light_hit, sampled_direction);
-                light_pdf *= refraction_sampled ? 0.0f : 1.0f;
-
-                bool contributes_enough = check_minimum_light_contribution(s.minimum_light_contribution, light_contribution / light_pdf / bsdf_sample_pdf);
-                if (!contributes_enough)
-                    target_function = 0.0f;
-
-                float mis_weight = balance_heuristic(bsdf_sample_pdf, (float)nb_bsdf_candidates, light_pdf, (float)nb_light_candidates);
-                candidate_weight = mis_weight * target_function / bsdf_sample_pdf;
-
-                bsdf_RIS_sample.emissive_triangle_index = light_hit.hit_prim_index;
-                bsdf_RIS_sample.point_on_light_source = shadow_ray_origin + sampled_direction * light_hit.hit_distance;
-                bsdf_RIS_sample.is_bsdf_sample = true;
-                bsdf_RIS_sample.bsdf_sample_contribution = bsdf_color;
-                bsdf_RIS_sample.bsdf_sample_cosine_term = cosine_at_evaluated_point;
-                bsdf_RIS_sample.target_function = target_function;
-            }
+            bool hit_found = evaluate_shadow_light_ray(rd, c.origin, c.direction, 1.0e35f, light_hit, hit.primitive_index, rng);
+            ris_bsdf_candidate_finish(rd, hit, c, hit_found, light_hit, nb_light_candidates, nb_bsdf_candidates, bsdf_RIS_sample, candidate_weight);
         }
         reservoir.add_one_candidate(bsdf_RIS_sample, candidate_weight, rng);
     }

@@ -292,6 +292,161 @@ PT_DEV void env_pair_path(const HIPRTRenderData& rd, int2 res, const Tile& tile,
         env_bsdf_sample_body<GGX_SAMPLER>(rd, wf, bounce, slot, p);
 }
 
+// ---- PHASED RIS (LSS_RIS_BSDF_AND_LIGHT, and the later bounces of LSS_RESTIR_DI with RESTIR_DI_LATER_BOUNCES_RIS) ------------------------
+// sample_lights_RIS (RIS.h:292-302) traces twice in the middle of its random-number sequence: the BSDF candidate's ray (closest hit, then
+// one more draw for the reservoir update) and the winner's shadow ray. Cut there:
+//   R1 ris_candidates  light candidates (draws + BSDF evals), BSDF candidate sample                    -> closest-hit ray (NEE_LIGHT_BSDF record)
+//   T  ray-queue kernel, closest
+//   R2 ris_select      what the candidate hit -> reservoir update (1 draw), UCW, the winner's shadow ray -> any-hit ray (NEE_LIGHT record)
+//   [P3 / P4 envmap phases], T any-hit, P5 resolves (ris_resolve_light)
+// The pieces are the ones of the per-thread form (ris.cuh), in its order, on the same generator state handed from phase to phase: same bits.
+// Only number_of_bsdf_candidates == 1 (the reference's default) runs phased; other counts keep the split shape.
+// Reservoir between the phases: ris_a[slot] = weight_sum | target_function | M | emissive triangle, ris_b[slot] = point on the light | 0;
+// after R2: ris_a = UCW | cosine of a BSDF sample | is-BSDF-sample flag | emissive triangle, ris_b = BSDF sample contribution.
+template <int GGX_SAMPLER>
+PT_DEV void ris_candidates_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
+{
+    const uint32_t slot = wf.sorted_queue[i];
+    uint32_t x, y, pixel_index;
+    wf_slot_to_pixel(wf, tile, res, slot, x, y, pixel_index);
+    PathRegs p;
+    nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
+    nee_store_none(wf, NEE_LIGHT, slot);
+    const size_t kb = nee_index(wf, NEE_LIGHT_BSDF, slot);
+    wf.nee_ray_o[kb] = make_float4(0.0f, 0.0f, 0.0f, -2.0f);          // -2: RIS does not run at this vertex (R2 and the resolve skip it)
+    if (lights_prelude(rd, p.payload.material, bounce) != LIGHTS_SAMPLE)
+        return;
+
+    const float3 view_direction = -p.direction;
+    const HitInfo& hit = p.hit;
+    bool inside_surface = dot(view_direction, hit.geometric_normal) < 0;
+    float inside_surface_multiplier = inside_surface ? -1.0f : 1.0f;
+    float3 evaluated_point = hit.inter_point + hit.shading_normal * 1.0e-4f * inside_surface_multiplier;
+    int nb_light_candidates, nb_bsdf_candidates;
+    ris_candidate_counts(rd, nb_light_candidates, nb_bsdf_candidates);
+
+    RISReservoir reservoir;
+    ris_light_candidates(rd, p.payload, hit, view_direction, evaluated_point, inside_surface_multiplier, nb_light_candidates, nb_bsdf_candidates, p.rng, reservoir);
+    RISBsdfCandidate c = ris_bsdf_candidate_sample<GGX_SAMPLER>(rd, p.payload, hit, view_direction, evaluated_point, inside_surface_multiplier, p.rng);
+    nee_store_rng(wf, slot, p.rng);
+    wf.ris_a[slot] = make_float4(reservoir.weight_sum, reservoir.sample.target_function, __uint_as_float(reservoir.M), __int_as_float(reservoir.sample.emissive_triangle_index));
+    wf.ris_b[slot] = make_float4(reservoir.sample.point_on_light_source.x, reservoir.sample.point_on_light_source.y, reservoir.sample.point_on_light_source.z, 0.0f);
+    wf.nee_ray_o[kb].w = -1.0f;                                       // R2 runs; no candidate ray unless the sample has a pdf
+    // the candidate's direction and colour travel in its ray record even when no ray is traced (pdf <= 0): R2 rebuilds the candidate from it
+    wf.nee_ray_d[kb] = make_float4(c.direction.x, c.direction.y, c.direction.z, __int_as_float(hit.primitive_index));
+    wf.nee_pending[kb] = make_float4(c.color.r, c.color.g, c.color.b, c.pdf);
+    if (c.pdf > 0.0f)
+        nee_store(wf, bounce, NEE_LIGHT_BSDF, slot, c.origin, 1.0e35f, c.direction, hit.primitive_index, c.color, c.pdf);
+}
+
+PT_DEV void ris_select_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
+{
+    const uint32_t slot = wf.sorted_queue[i];
+    const size_t kb = nee_index(wf, NEE_LIGHT_BSDF, slot);
+    const float4 o = wf.nee_ray_o[kb];
+    if (o.w == -2.0f)
+        return;
+    uint32_t x, y, pixel_index;
+    wf_slot_to_pixel(wf, tile, res, slot, x, y, pixel_index);
+    PathRegs p;
+    nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
+    const HitInfo& hit = p.hit;
+    const float3 view_direction = -p.direction;
+    bool inside_surface = dot(view_direction, hit.geometric_normal) < 0;
+    float inside_surface_multiplier = inside_surface ? -1.0f : 1.0f;
+    int nb_light_candidates, nb_bsdf_candidates;
+    ris_candidate_counts(rd, nb_light_candidates, nb_bsdf_candidates);
+
+    const float4 a = wf.ris_a[slot], b = wf.ris_b[slot];
+    RISReservoir reservoir;
+    reservoir.weight_sum = a.x;
+    reservoir.sample.target_function = a.y;
+    reservoir.M = __float_as_uint(a.z);
+    reservoir.sample.emissive_triangle_index = __float_as_int(a.w);
+    reservoir.sample.point_on_light_source = f3(b.x, b.y, b.z);
+    reservoir.sample.is_bsdf_sample = false;
+
+    const float4 d = wf.nee_ray_d[kb], pc = wf.nee_pending[kb];
+    RISBsdfCandidate c;
+    c.direction = f3(d.x, d.y, d.z);
+    c.color = RGB(pc.x, pc.y, pc.z);
+    c.pdf = pc.w;
+    c.refraction = dot(c.direction, hit.shading_normal * inside_surface_multiplier) < 0;
+    c.origin = c.refraction ? hit.inter_point + hit.shading_normal * 1.0e-4f * inside_surface_multiplier * -1.0f
+                            : hit.inter_point + hit.shading_normal * 1.0e-4f * inside_surface_multiplier;
+    float candidate_weight = 0.0f;
+    RISSample bsdf_RIS_sample;
+    if (c.pdf > 0.0f)
+    {
+        const float4 h = wf.hit_tuvp[kb];
+        Hit light_ray_hit;
+        light_ray_hit.t = h.x; light_ray_hit.u = h.y; light_ray_hit.v = h.z;
+        light_ray_hit.prim = __float_as_int(h.w);
+        light_ray_hit.tri_slot = (int)wf.hit_tri_slot[kb];
+        ShadowLightRayHitInfo light_hit;
+        bool hit_found = shadow_light_ray_resolve(rd, 1.0e35f, light_hit, light_ray_hit);
+        ris_bsdf_candidate_finish(rd, hit, c, hit_found, light_hit, nb_light_candidates, nb_bsdf_candidates, bsdf_RIS_sample, candidate_weight);
+    }
+    reservoir.add_one_candidate(bsdf_RIS_sample, candidate_weight, p.rng);
+    reservoir.end();
+    nee_store_rng(wf, slot, p.rng);
+
+    // first half of evaluate_reservoir_sample (RIS.h:18-48): the winner's shadow ray
+    wf.ris_a[slot] = make_float4(reservoir.UCW, reservoir.sample.bsdf_sample_cosine_term, reservoir.sample.is_bsdf_sample ? 1.0f : 0.0f, __int_as_float(reservoir.sample.emissive_triangle_index));
+    wf.ris_b[slot] = make_float4(reservoir.sample.bsdf_sample_contribution.r, reservoir.sample.bsdf_sample_contribution.g, reservoir.sample.bsdf_sample_contribution.b, 0.0f);
+    if (reservoir.UCW <= 0.0f || reservoir.sample.is_bsdf_sample)
+        return;
+    float3 evaluated_point = hit.inter_point + hit.shading_normal * 1.0e-4f;
+    float3 shadow_ray_direction = reservoir.sample.point_on_light_source - evaluated_point;
+    float distance_to_light = length(shadow_ray_direction);
+    float3 dir = shadow_ray_direction / distance_to_light;
+    nee_store(wf, bounce, NEE_LIGHT, slot, evaluated_point, distance_to_light, dir, hit.primitive_index, RGB(0.0f), 0.0f);
+}
+
+// second half of evaluate_reservoir_sample (RIS.h:50-80), from the traced shadow ray
+PT_DEV RGB ris_resolve_light(const HIPRTRenderData& rd, const WavefrontState& wf, uint32_t slot, PathRegs& p)
+{
+    if (wf.nee_ray_o[nee_index(wf, NEE_LIGHT_BSDF, slot)].w == -2.0f)
+        return RGB(0.0f);
+    const float4 a = wf.ris_a[slot];
+    const float UCW = a.x;
+    RGB final_color;
+    if (UCW <= 0.0f)
+        return RGB(0.0f);
+    const bool is_bsdf_sample = a.z != 0.0f;
+    bool in_shadow = false;
+    const size_t k = nee_index(wf, NEE_LIGHT, slot);
+    if (!is_bsdf_sample)
+        in_shadow = !(wf.nee_ray_o[k].w > 0.0f);          // the any-hit kernel set t_max = -1 on occluded rays
+    if (!in_shadow)
+    {
+        float bsdf_pdf;
+        float cosine_at_evaluated_point;
+        RGB bsdf_color;
+        RayVolumeState trash = p.payload.volume_state;
+        if (is_bsdf_sample)
+        {
+            const float4 b = wf.ris_b[slot];
+            bsdf_color = RGB(b.x, b.y, b.z);
+            cosine_at_evaluated_point = a.y;
+        }
+        else
+        {
+            const float4 d = wf.nee_ray_d[k];
+            const float3 dir = f3(d.x, d.y, d.z);
+            bsdf_color = bsdf_eval(rd, p.payload.material, trash, -p.direction, p.hit.shading_normal, dir, bsdf_pdf);
+            cosine_at_evaluated_point = maxf(0.0f, dot(p.hit.shading_normal, dir));
+        }
+        if (cosine_at_evaluated_point > 0.0f)
+        {
+            int material_index = __ldg(rd.buffers.material_indices + __float_as_int(a.w));
+            RGB sample_emission = material_buffer_emission(rd, material_index);
+            final_color = bsdf_color * UCW * sample_emission * cosine_at_evaluated_point;
+        }
+    }
+    return final_color;
+}
+
 // ---- P5: finish shade_vertex_direct from the traced NEE rays (FullPathTracer.h:195-214), then shade_vertex_bounce --------------
 // The any-hit kernel has set t_max = -1 on the occluded rays; ray 1's closest hit is in the hit records at [capacity + slot].
 PT_DEV RGB nee_unoccluded_contribution(const WavefrontState& wf, int which, uint32_t slot)
@@ -303,7 +458,7 @@ PT_DEV RGB nee_unoccluded_contribution(const WavefrontState& wf, int which, uint
     return RGB(c.x, c.y, c.z);
 }
 
-template <int ESS>
+template <int ESS, bool RIS>
 PT_DEV void nee_resolve(const HIPRTRenderData& rd, const WavefrontState& wf, uint32_t slot, int bounce, PathRegs& p, bool lights_sampled, bool envmap_sampled)
 {
     const Material& m = p.payload.material;
@@ -311,6 +466,12 @@ PT_DEV void nee_resolve(const HIPRTRenderData& rd, const WavefrontState& wf, uin
     const int prelude = lights_prelude(rd, m, bounce);
     if (prelude == LIGHTS_EMISSION)
         light_direct = material_emission(m);
+    else if (RIS && prelude == LIGHTS_SAMPLE && lights_sampled)
+    {
+        RGB direct;
+        direct += ris_resolve_light(rd, wf, slot, p);
+        light_direct = direct / rd.render_settings.number_of_light_samples;
+    }
     else if (prelude == LIGHTS_SAMPLE && lights_sampled)
     {
         RGB light_source_radiance_mis = nee_unoccluded_contribution(wf, NEE_LIGHT, slot);
@@ -364,7 +525,7 @@ PT_DEV void nee_resolve(const HIPRTRenderData& rd, const WavefrontState& wf, uin
     p.payload.ray_color += clamp_light_contribution(indirect, rd.render_settings.indirect_contribution_clamp, bounce > 0);
 }
 
-template <int ESS, int GGX_SAMPLER>
+template <int ESS, int GGX_SAMPLER, bool RIS>
 PT_DEV void wf_bsdf_resolved_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i, bool lights_sampled, bool envmap_sampled)
 {
     const uint32_t slot = wf.sorted_queue[i];
@@ -372,7 +533,7 @@ PT_DEV void wf_bsdf_resolved_path(const HIPRTRenderData& rd, int2 res, const Til
     wf_slot_to_pixel(wf, tile, res, slot, x, y, pixel_index);
     PathRegs p;
     nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
-    nee_resolve<ESS>(rd, wf, slot, bounce, p, lights_sampled, envmap_sampled);
+    nee_resolve<ESS, RIS>(rd, wf, slot, bounce, p, lights_sampled, envmap_sampled);
     bool alive = shade_vertex_bounce<GGX_SAMPLER>(rd, p.payload, p.hit, p.origin, p.direction, p.rng, bounce);
     alive = alive && bounce < wf_nb_bounces(rd);
     if (alive)

@@ -397,7 +397,8 @@ void GPURenderer::update_render_data()
 bool GPURenderer::can_render_sample_batches() const
 {
     const HIPRTRenderSettings& s = m_render_data.render_settings;
-    if (samples_in_flight <= 0 || m_options.direct_light_sampling_strategy != 3)
+    const int lss = m_options.direct_light_sampling_strategy;
+    if (samples_in_flight <= 0 || !(lss == 3 || (lss == 4 && s.ris_settings.number_of_bsdf_candidates == 1)))
         return false;
     int mode = -1;
     if (b200pt_get_path_mode(m_ctx, &mode) != 0 || mode != 3)

@@ -146,7 +146,7 @@ public:
     void set_path_lanes(int lanes);
     // Sample batches (b200pt_launch_PathTraceSamples): render() runs the samples_per_frame passes of a frame as fused wavefronts of up
     // to `samples_in_flight` passes (CameraRays fused in) whenever the options allow it; 0 keeps the two launch points per pass.
-    int samples_in_flight = 8;
+    int samples_in_flight = 16;
     bool renders_sample_batches() const { return can_render_sample_batches(); }
     bool keep_g_buffer = true;      // the last pass of a batch leaves its camera hits in the G-buffer, as CameraRays would
     int path_lanes() const { return m_path_lanes; }                                                     // rows either side of the tile CameraRays also covers (ReSTIR DI)

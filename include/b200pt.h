@@ -181,7 +181,7 @@ B200PT_API int b200pt_launch_FullPathTracer_lane(b200pt_ctx* ctx, const HIPRTRen
  * costs of the bounce chain are paid once per batch and a small tile (multi-GPU tile sharding) still fills the GPU. The frame buffers
  * receive the passes in pass order: same bits as `count` iterations of the two separate launches. With write_g_buffer the last pass
  * leaves its camera hits in the G-buffer as CameraRays would. Restrictions (B200PT_ERROR_VARIANT_NOT_COMPILED otherwise; use the separate
- * launches then): LSS_MIS_LIGHT_BSDF, one light sample, no alpha testing, no adaptive sampling / pixel noise threshold, no ReSTIR DI, no
+ * launches then): LSS_MIS_LIGHT_BSDF or LSS_RIS_BSDF_AND_LIGHT (with one BSDF candidate, the default), one light sample, no alpha testing, no adaptive sampling / pixel noise threshold, no ReSTIR DI, no
  * low-resolution rendering -- the options under which a pass does not read what the previous pass accumulated. */
 typedef struct b200pt_sample_batch
 {

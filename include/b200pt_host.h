@@ -48,7 +48,7 @@ B200PT_API int b200pt_renderer_set_tile_halo(b200pt_renderer* r, int rows);
 B200PT_API int b200pt_renderer_set_path_lanes(b200pt_renderer* r, int lanes);
 B200PT_API int b200pt_renderer_path_lanes(b200pt_renderer* r);
 /* Fused sample batches (new; see b200pt_launch_PathTraceSamples): a frame's samples_per_frame passes run as wavefronts of up to `samples`
- * (0..16; 0 = off, default 8, environment B200PT_SAMPLES_IN_FLIGHT) passes with CameraRays fused in, whenever the options allow it
+ * (0..16; 0 = off, default 16, environment B200PT_SAMPLES_IN_FLIGHT) passes with CameraRays fused in, whenever the options allow it
  * (b200pt_renderer_renders_sample_batches tells); same bits as the per-pass launches. keep_g_buffer: the last pass of a batch leaves its
  * camera hits in the G-buffer as CameraRays would (345 B/px of stores; switch off when nothing reads the G-buffer). */
 B200PT_API int b200pt_renderer_set_samples_in_flight(b200pt_renderer* r, int samples, int keep_g_buffer);

@@ -374,6 +374,37 @@ def test_path_modes_are_bit_identical(pt, wl, ctx, variant):
         assert np.array_equal(frames["megakernel"], frames[mode]), mode
 
 
+@pytest.mark.parametrize("lss,ess", [("ris", "none"), ("ris", "alias_table"), ("restir_di", "none"), ("restir_di", "alias_table")])
+def test_ris_phases_are_bit_identical(pt, wl, ctx, lss, ess):
+    """Phased RIS (R1 candidates -> closest trace -> R2 select -> [envmap phases] -> any-hit trace -> resolve; under ReSTIR DI from bounce 1
+    on) against the megakernel and the split shape on a many-light scene (with a procedural envmap for the alias-table permutations, so that
+    emissive triangles AND the envmap are sampled): the per-thread pieces run in the same order on the same generator states, same bits."""
+    procedural = importlib.import_module("hiprt-path-tracer_b200.procedural")
+    W, H = 160, 112
+    cfg = wl.many_lights(W, H, boxes=100, lights=1500)
+    cfg["options"] = dict(lss=lss, ess=ess, ggx=0, later=3)
+    if ess == "alias_table":
+        cfg["envmap"] = {"texels": procedural.procedural_envmap(256, 128), "alias_probas": None, "alias_alias": None, "total_sum": 0.0}
+    g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="cpu")
+    frames = {}
+    try:
+        for mode in ("megakernel", "split", "phased"):
+            ctx.set_path_mode(mode)
+            g.reset()
+            g.resize(W, H)
+            wl.apply_settings(g.render_settings, cfg["settings"])
+            for _ in range(3):
+                g.render_frame()
+            g.synchronize()
+            frames[mode] = g.download("pixels").copy()
+    finally:
+        ctx.set_path_mode("phased")
+        g.close()
+    assert np.isfinite(frames["phased"]).all() and frames["phased"].sum() > 0
+    for mode in ("split", "phased"):
+        assert np.array_equal(frames["megakernel"], frames[mode]), mode
+
+
 def test_edge_cases_empty_scene_and_misses(pt, ctx):
     """Empty scene (0 triangles): every query misses; rays pointing away from the geometry miss; zero-length batches work."""
     bvh = ctx.build_bvh(np.zeros((0, 3), np.float32), np.zeros((0,), np.int32))
@@ -883,13 +914,15 @@ def test_path_lanes_are_bit_identical(pt, wl, ctx):
     g.close()
 
 
-@pytest.mark.parametrize("workload,schedule", [("cornell", "gpu"), ("cornell", "cpu"), ("synthetic_small", "gpu")])
+@pytest.mark.parametrize("workload,schedule", [("cornell", "gpu"), ("cornell", "cpu"), ("synthetic_small", "gpu"), ("cornell_ris", "gpu")])
 def test_sample_batches_are_bit_identical(pt, wl, ctx, workload, schedule):
     """b200pt_launch_PathTraceSamples: a frame of samples_per_frame = 5 passes as fused wavefronts of 1, 2, 4 or 5 passes in flight
     (CameraRays fused in, 1 or 2 path lanes) against the reference's loop of two launches per pass: accumulation buffer, denoiser
     AOVs and the G-buffer the last pass leaves are the same bits; two frames, so that batches start at a non-zero sample number."""
     W, H = (320, 200) if workload == "cornell" else (256, 160)
-    cfg = getattr(wl, workload)(W, H)
+    cfg = getattr(wl, workload.replace("_ris", ""))(W, H)
+    if workload.endswith("_ris"):
+        cfg["options"] = dict(lss="ris", ess="none", ggx=0, later=3)       # RIS (the reference's default strategy) batches as well
     g = wl.setup_gpu(pt, ctx, cfg, seed_schedule=schedule)
     names = ("pixels", "denoiser_albedo", "denoiser_normals", "first_hit_prim_index", "shading_normals", "geometric_normals", "view_directions", "first_hits",
              "camera_ray_hit", "materials", "ray_volume_states", "pixel_active")
