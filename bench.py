@@ -71,7 +71,7 @@ def measured_traffic(workload, width, height, spf):
     if not os.path.exists(path):
         return None
     entry = json.load(open(path)).get(f"{workload}_{width}x{height}_spf{spf}")
-    return entry["trace_queue_dram_bytes_per_step"] if entry else None
+    return (entry["trace_queue_dram_bytes_per_step"], entry.get("ncu_time_weighted")) if entry else (None, None)
 
 
 class oracle_prints_to_stderr:
@@ -387,6 +387,9 @@ def run_ours(args, cfg, pt):
         launches_per_step = batches * lanes * (3 + per_bounce + nb * (2 + per_bounce) + 1)
     else:
         launches_per_step = spf * (1 + lanes * ((1 + per_bounce) + nb * (2 + per_bounce)) + (3 if restir else 0))      # every path lane launches its own band
+    # DRAM bytes of the kernel per step and its time-weighted ncu counters (L2 throughput as a fraction of the L2 peak, hit rates, issue rate, lanes
+    # per instruction), from the committed `ncu --set full` capture of the same command (profiles/traffic.json); null when not captured
+    traffic, ncu_weighted = measured_traffic(args.workload, W, H, cfg["settings"].get("samples_per_frame", 1))
     out = {
         "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "strong" if (world > 1 and sharding in ("tiles", "columns")) else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -400,7 +403,7 @@ def run_ours(args, cfg, pt):
         "clocks": clocks,
         "e2e": {"value": total_rays / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 2 * 1328 + 196, "d2h_bytes_per_step": W * own_rows * 12},
         "roofline": {"bound": "hbm", "frac_of": "HBM copy peak (the contract's denominator; the kernel is L2-latency-bound, not HBM-bound)", "kernel": "k_trace_queue (ray-queue BVH8 traversal inside FullPathTracer; per step = sum of its launches)", "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(args.workload, W, H, cfg["settings"].get("samples_per_frame", 1)),
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "ncu": ncu_weighted, "l2_frac": (ncu_weighted["l2_throughput_pct"] / 100.0) if ncu_weighted else None,
                      "peak_source": peak_kind, "ms_per_launch": trace_ms, "full_path_tracer_ms": fpt_ms, "stage_ms": stage_ms,
                      "camera_rays_ms_per_launch": kernel_ms["CameraRays"] / args.steps,
                      "stage_ms_lanes": 1, "rays_per_launch": queue["rays"], "nodes_per_ray": queue["nodes"] / max(1.0, queue["rays"]),

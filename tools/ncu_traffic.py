@@ -22,16 +22,27 @@ def scale(name):
     return {"byte": 1.0, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9, "ns": 1e-9, "us": 1e-6, "usecond": 1e-6, "ms": 1e-3, "msecond": 1e-3, "nsecond": 1e-9, "second": 1.0, "s": 1.0}.get(u, 1.0)
 
 
+# time-weighted means over the kernel's launches: what bounds it (L2 / L1 hit rates, issue rate, lanes per instruction, memory stalls)
+WEIGHTED = {"lts__throughput.avg.pct_of_peak_sustained_elapsed": "l2_throughput_pct", "lts__t_sector_hit_rate.pct": "l2_hit_pct", "l1tex__t_sector_hit_rate.pct": "l1_hit_pct",
+            "smsp__issue_active.avg.pct_of_peak_sustained_active": "issue_active_pct", "smsp__thread_inst_executed_per_inst_executed.ratio": "threads_per_inst",
+            "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio": "long_scoreboard_per_issue",
+            "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed": "dram_throughput_pct", "sm__warps_active.avg.pct_of_peak_sustained_active": "warps_active_pct"}
+weighted = {v: 0.0 for v in WEIGHTED.values()}
 tot = {"read": 0.0, "write": 0.0, "seconds": 0.0, "launches": 0}
 for r in rows[2:]:
     if "k_trace_queue" not in r[col["Kernel Name"]]:
         continue
+    seconds = float(r[col["gpu__time_duration.sum"]].replace(",", "")) * scale("gpu__time_duration.sum")
+    for name, key in WEIGHTED.items():
+        if name in col and r[col[name]] not in ("", "n/a"):
+            weighted[key] += float(r[col[name]].replace(",", "")) * seconds
     tot["read"] += float(r[col["dram__bytes_read.sum"]].replace(",", "")) * scale("dram__bytes_read.sum")
     tot["write"] += float(r[col["dram__bytes_write.sum"]].replace(",", "")) * scale("dram__bytes_write.sum")
     tot["seconds"] += float(r[col["gpu__time_duration.sum"]].replace(",", "")) * scale("gpu__time_duration.sum")
     tot["launches"] += 1
 entry = {"trace_queue_dram_bytes_per_step": (tot["read"] + tot["write"]) / steps, "dram_read_bytes_per_step": tot["read"] / steps, "dram_write_bytes_per_step": tot["write"] / steps,
-         "trace_queue_launches_per_step": tot["launches"] / steps, "ncu_serialised_ms_per_step": tot["seconds"] / steps * 1e3, "source": os.path.basename(rep)}
+         "trace_queue_launches_per_step": tot["launches"] / steps, "ncu_serialised_ms_per_step": tot["seconds"] / steps * 1e3, "source": os.path.basename(rep),
+         "ncu_time_weighted": {k: round(v / max(tot["seconds"], 1e-12), 3) for k, v in weighted.items()}}
 path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "profiles", "traffic.json")
 data = json.load(open(path)) if os.path.exists(path) else {}
 data[key] = entry

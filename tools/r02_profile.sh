@@ -11,7 +11,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file $O/p_
 python tools/ncu_launches.py $O/p_${W}_launches.csv --sum > $O/p_${W}_launches_summary.txt 2>&1
 tail -25 $O/p_${W}_launches_summary.txt
 ncu --set full --clock-control none --import-source on -k regex:k_trace_queue --launch-skip 108 -c 36 -f -o /tmp/p_trace python bench.py --profile --steps 1 --workload $W > $O/p_${W}_ncu_trace.log 2>&1
-python tools/ncu_traffic.py /tmp/p_trace.ncu-rep ${W}_1920x1080_spf8 1 > $O/p_${W}_traffic.log 2>&1
+python tools/ncu_traffic.py /tmp/p_trace.ncu-rep ${W}_1920x1080_spf16 1 > $O/p_${W}_traffic.log 2>&1
 python tools/ncu_summary.py /tmp/p_trace.ncu-rep > $O/p_${W}_trace_full.txt 2>&1
 cp profiles/traffic.json $O/traffic.json
 ncu --set full --clock-control none --import-source on -k regex:"k_wf_(bsdf_resolved|env_bsdf_sample|env_light_eval|nee_light_eval|nee_bsdf_sample|surface|camera_surface|camera_|accumulate)" --launch-skip 222 -c 12 -f -o /tmp/p_shade python bench.py --profile --steps 1 --workload $W > $O/p_${W}_ncu_shade.log 2>&1
