@@ -52,7 +52,7 @@ constexpr unsigned kRefillIdleLanes = PT_TRACE_REFILL_IDLE;       // refill as s
 // absorb on the conservative side -- no I2F (quarter-rate XU pipe) and no separate bias subtraction per plane.
 // 'one' is 0x3F800000 held in a register (opaque_one_bits): PRMT has a single immediate slot, and with a literal constant
 // ptxas spends it on the constant and re-materialises the SELECTOR in a register before every PRMT (one extra MOV per plane,
-// 48 per node in the first version of this kernel, see profiles/r01_trace_queue_sass_notes.txt).
+// 48 per node in the first version of this kernel; the census of the current SASS is profiles/r02_trace_queue_sass_notes.txt, tools/sass_notes.py).
 PT_DEV float quantised_byte_to_unit_float(uint32_t word, int byte, uint32_t one)
 {
     return __uint_as_float(__byte_perm(word, one, 0x7604u + ((uint32_t)byte << 4)));
@@ -142,15 +142,34 @@ PT_DEV uint32_t group_next_node(const uint2 group, const uint32_t oct_inv, uint3
 // Per-lane traversal stack: the first kSharedStackEntries entries in shared memory (lane-interleaved), the rest in local memory.
 // A wide tree of depth d needs at most 2 d entries (per level one deferred node group and one set-aside triangle group); the builder
 // reports d and b200pt_bvh_build refuses trees with 2 d + 1 > kTraversalStackSize, so `full` cannot happen; the counting build counts it.
+// On the device the shared part is addressed in the shared state space (32-bit window address, st.shared / ld.shared): through the
+// generic pointer of the first version ptxas could not prove the address space and emitted generic ST.E.64 / LD.E.64 with 64-bit
+// address arithmetic for every push and pop (profiles/r02_trace_queue_sass_notes.txt).
 struct LaneStack
 {
-    uint2* shared_base;        // entry k at shared_base[k * blockDim.x]
+#ifdef __CUDA_ARCH__
+    uint32_t shared_addr;      // shared-window byte address of this lane's entry 0; entry k is kTraceBlock * 8 bytes further per k
+    PT_DEV void bind(uint2* lane_entry0) { shared_addr = (uint32_t)__cvta_generic_to_shared(lane_entry0); }
+    // volatile, no memory clobber: the stack's own stores and loads keep their order, global loads may still move across them
+    PT_DEV void shared_store(const int k, const uint2 e) { asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(shared_addr + (uint32_t)k * (kTraceBlock * 8u)), "r"(e.x), "r"(e.y)); }
+    PT_DEV uint2 shared_load(const int k) const
+    {
+        uint2 e;
+        asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(e.x), "=r"(e.y) : "r"(shared_addr + (uint32_t)k * (kTraceBlock * 8u)));
+        return e;
+    }
+#else
+    uint2* shared_base;        // host emulation (tests/host_shim): entry k at shared_base[k * blockDim.x]
+    PT_DEV void bind(uint2* lane_entry0) { shared_base = lane_entry0; }
+    PT_DEV void shared_store(const int k, const uint2 e) { shared_base[k * blockDim.x] = e; }
+    PT_DEV uint2 shared_load(const int k) const { return shared_base[k * blockDim.x]; }
+#endif
     uint2 local[kTraversalStackSize - kSharedStackEntries];
     int size;
     PT_DEV bool push(const uint2 e)
     {
         if (size < kSharedStackEntries)
-            shared_base[size * blockDim.x] = e;
+            shared_store(size, e);
         else if (size < kTraversalStackSize)
             local[size - kSharedStackEntries] = e;
         else
@@ -158,7 +177,7 @@ struct LaneStack
         size++;
         return true;
     }
-    PT_DEV uint2 top() const { return size - 1 < kSharedStackEntries ? shared_base[(size - 1) * blockDim.x] : local[size - 1 - kSharedStackEntries]; }
+    PT_DEV uint2 top() const { return size - 1 < kSharedStackEntries ? shared_load(size - 1) : local[size - 1 - kSharedStackEntries]; }
 };
 
 PT_DEV void trace_queue_load_ray(const RayQueueView& q, const uint32_t ray_id, const bool any_hit, RaySlabs& r, int& last_prim, float& t_best)
@@ -205,7 +224,7 @@ __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const Ra
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t n = *q.count;
     LaneStack stack;
-    stack.shared_base = shared_stack + threadIdx.x;
+    stack.bind(shared_stack + threadIdx.x);
     stack.size = 0;
     const uint32_t one = opaque_one_bits(n);
 
@@ -358,7 +377,7 @@ __device__ __forceinline__ void trace_queue_body_pipelined(const Bvh8Device& bvh
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t n = *q.count;
     LaneStack stack;
-    stack.shared_base = shared_stack + threadIdx.x;
+    stack.bind(shared_stack + threadIdx.x);
     stack.size = 0;
     const uint32_t one = opaque_one_bits(n);
 
