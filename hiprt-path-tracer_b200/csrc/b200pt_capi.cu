@@ -23,6 +23,10 @@ struct b200pt_ctx
     static constexpr int kMaxPathLanes = 4;
     pt::WavefrontState wf[kMaxPathLanes] = {};
     std::vector<void*> wf_allocations[kMaxPathLanes];
+    // scratch of the phased ReSTIR DI passes (launch.h: RestirScratch), sized for the largest tile launched so far
+    pt::RestirScratch restir_scratch{};
+    bool restir_phases = true;          // b200pt_set_restir_phases
+    std::vector<void*> restir_allocations;
     // per-stage timing of FullPathTracer (b200pt_path_profile_enable / _read)
     bool profiling = false;
     std::vector<cudaEvent_t> profile_events;
@@ -159,6 +163,8 @@ int b200pt_ctx_destroy(b200pt_ctx* ctx)
     for (auto& allocations : ctx->wf_allocations)
         for (void* p : allocations)
             cudaFree(p);
+    for (void* p : ctx->restir_allocations)
+        cudaFree(p);
     for (cudaEvent_t e : ctx->profile_events)
         cudaEventDestroy(e);
     cudaStreamDestroy(ctx->main_stream);

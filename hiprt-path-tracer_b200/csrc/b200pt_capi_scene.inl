@@ -511,7 +511,65 @@ int b200pt_launch_ReSTIR_DI_LightsPresampling(b200pt_ctx* ctx, const LightPresam
     return B200PT_SUCCESS;
 }
 
-#define LAUNCH_RESTIR_PIXEL_KERNEL(NAME)                                                                                           \
+// Grows the scratch of the phased ReSTIR DI passes to `pixels` pixels (same discipline as ensure_wavefront). A failed allocation is not an
+// error: the passes then run as single kernels with per-thread traversal (scratch capacity 0).
+static const pt::RestirScratch* ensure_restir_scratch(b200pt_ctx* ctx, uint32_t pixels)
+{
+    pt::RestirScratch& rs = ctx->restir_scratch;
+    if (!ctx->restir_phases)
+        return nullptr;
+    if (pixels <= rs.capacity)
+        return &rs;
+    if (cudaSetDevice(ctx->device) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess)
+        return nullptr;
+    for (void* p : ctx->restir_allocations)
+        cudaFree(p);
+    ctx->restir_allocations.clear();
+    rs = pt::RestirScratch{};
+    bool ok = true;
+    auto alloc = [&](size_t bytes) -> void* {
+        void* p = nullptr;
+        if (!ok || cudaMalloc(&p, bytes) != cudaSuccess)
+        {
+            ok = false;
+            return nullptr;
+        }
+        ctx->restir_allocations.push_back(p);
+        return p;
+    };
+    const size_t n = pixels, rays = n * (size_t)pt::kRestirSites;
+    rs.ray_o = static_cast<float4*>(alloc(rays * sizeof(float4)));
+    rs.ray_d = static_cast<float4*>(alloc(rays * sizeof(float4)));
+    rs.target = static_cast<float*>(alloc(rays * sizeof(float)));
+    rs.hit_tuvp = static_cast<float4*>(alloc(n * sizeof(float4)));
+    rs.hit_tri_slot = static_cast<uint32_t*>(alloc(n * sizeof(uint32_t)));
+    rs.ic_state = static_cast<float4*>(alloc(4 * n * sizeof(float4)));
+    rs.status = static_cast<uint32_t*>(alloc(n * sizeof(uint32_t)));
+    rs.queue = static_cast<uint32_t*>(alloc(rays * sizeof(uint32_t)));
+    rs.counts = static_cast<uint32_t*>(alloc(4 * sizeof(uint32_t)));
+    if (!ok)
+    {
+        cudaGetLastError();
+        for (void* p : ctx->restir_allocations)
+            cudaFree(p);
+        ctx->restir_allocations.clear();
+        rs = pt::RestirScratch{};
+        return nullptr;
+    }
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+    rs.sm_count = (uint32_t)sms;
+    rs.capacity = pixels;
+    return &rs;
+}
+
+static uint32_t restir_tile_pixels(const b200pt_tile* tile, b200pt_int2 res)
+{
+    const pt::Tile t = tile_of(tile, res);
+    return t.x1 > t.x0 && t.y1 > t.y0 ? (uint32_t)(t.x1 - t.x0) * (uint32_t)(t.y1 - t.y0) : 0u;
+}
+
+#define LAUNCH_RESTIR_PIXEL_KERNEL(NAME, ...)                                                                                      \
     REQUIRE(ctx != nullptr && render_data != nullptr && res.x > 0 && res.y > 0);                                                   \
     REQUIRE(render_data->geom != nullptr);                                                                                         \
     pt::Tile t = tile_of(tile, res);                                                                                               \
@@ -522,10 +580,10 @@ int b200pt_launch_ReSTIR_DI_LightsPresampling(b200pt_ctx* ctx, const LightPresam
     {                                                                                                                              \
         HIPRTRenderData copy = *render_data;                                                                                       \
         copy.hiprt_function_table = ctx->d_counters;                                                                               \
-        e = pt::NAME##_c(ctx->options, &copy, make_int2(res.x, res.y), t, stream_of(ctx, stream));                                 \
+        e = pt::NAME##_c(ctx->options, &copy, make_int2(res.x, res.y), t, stream_of(ctx, stream) __VA_ARGS__);                     \
     }                                                                                                                              \
     else                                                                                                                           \
-        e = pt::NAME##_t(ctx->options, render_data, make_int2(res.x, res.y), t, stream_of(ctx, stream));                           \
+        e = pt::NAME##_t(ctx->options, render_data, make_int2(res.x, res.y), t, stream_of(ctx, stream) __VA_ARGS__);               \
     if (e == cudaErrorInvalidDeviceFunction)                                                                                       \
         return fail(B200PT_ERROR_VARIANT_NOT_COMPILED, "ReSTIR DI passes need a LSS_RESTIR_DI kernel permutation (b200pt_kernel_variant_select)"); \
     if (e != cudaSuccess)                                                                                                          \
@@ -534,12 +592,14 @@ int b200pt_launch_ReSTIR_DI_LightsPresampling(b200pt_ctx* ctx, const LightPresam
 
 int b200pt_launch_ReSTIR_DI_InitialCandidates(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream)
 {
-    LAUNCH_RESTIR_PIXEL_KERNEL(launch_ReSTIR_DI_InitialCandidates)
+    const pt::RestirScratch* scratch = ctx != nullptr && res.x > 0 && res.y > 0 ? ensure_restir_scratch(ctx, restir_tile_pixels(tile, res)) : nullptr;
+    LAUNCH_RESTIR_PIXEL_KERNEL(launch_ReSTIR_DI_InitialCandidates, , scratch)
 }
 
 int b200pt_launch_ReSTIR_DI_SpatiotemporalReuse(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream)
 {
-    LAUNCH_RESTIR_PIXEL_KERNEL(launch_ReSTIR_DI_SpatiotemporalReuse)
+    const pt::RestirScratch* scratch = ctx != nullptr && res.x > 0 && res.y > 0 ? ensure_restir_scratch(ctx, restir_tile_pixels(tile, res)) : nullptr;
+    LAUNCH_RESTIR_PIXEL_KERNEL(launch_ReSTIR_DI_SpatiotemporalReuse, , scratch)
 }
 
 int b200pt_launch_ReSTIR_DI_TemporalReuse(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream)
@@ -632,6 +692,13 @@ int b200pt_debug_thin_film_fresnel(b200pt_ctx* ctx, const void* d_materials, con
 {
     REQUIRE(n == 0 || (d_materials != nullptr && d_ambient_ior_and_cosine != nullptr));
     return debug_function(ctx, 3, nullptr, d_materials, nullptr, d_ambient_ior_and_cosine, nullptr, n, 0, d_out, "debug_thin_film_fresnel");
+}
+
+int b200pt_set_restir_phases(b200pt_ctx* ctx, int enable)
+{
+    REQUIRE(ctx != nullptr);
+    ctx->restir_phases = enable != 0;
+    return B200PT_SUCCESS;
 }
 
 int b200pt_set_ray_bin_bits(b200pt_ctx* ctx, int bits)

@@ -395,6 +395,27 @@ __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_ReSTIR_DI_Spatiotemporal
     restir_spatiotemporal_pixel(rd, res, x, y);
 }
 
+// Phased passes (restir_di_kernels.cuh): COLLECT / RESOLVE kernels around launches of the ray-queue traversal kernel
+#define PT_RESTIR_PHASE_KERNEL(NAME, CALL)                                                                                                       \
+    __global__ void __launch_bounds__(64) PT_VARIANT_NAME(NAME)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ RestirScratch scratch) \
+    {                                                                                                                                            \
+        const uint32_t x = tile.x0 + blockIdx.x * blockDim.x + threadIdx.x;                                                                      \
+        const uint32_t y = tile.y0 + blockIdx.y * blockDim.y + threadIdx.y;                                                                      \
+        if (x >= (uint32_t)tile.x1 || y >= (uint32_t)tile.y1)                                                                                    \
+            return;                                                                                                                              \
+        RestirSites sites;                                                                                                                       \
+        sites.scratch = &scratch;                                                                                                                \
+        sites.pixel = (x - (uint32_t)tile.x0) + (y - (uint32_t)tile.y0) * (uint32_t)(tile.x1 - tile.x0);                                         \
+        CALL(rd, res, x, y, sites);                                                                                                              \
+    }
+#define PT_IC_COLLECT restir_initial_candidates_pixel<PT_GGX, RESTIR_COLLECT>
+#define PT_IC_RESOLVE restir_initial_candidates_pixel<PT_GGX, RESTIR_RESOLVE>
+PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_InitialCandidates_collect, PT_IC_COLLECT)
+PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_InitialCandidates_resolve, PT_IC_RESOLVE)
+PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_InitialCandidates_visibility, restir_initial_candidates_visibility)
+PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_SpatiotemporalReuse_collect, restir_spatiotemporal_pixel<RESTIR_COLLECT>)
+PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_SpatiotemporalReuse_resolve, restir_spatiotemporal_pixel<RESTIR_RESOLVE>)
+
 __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_ReSTIR_DI_TemporalReuse)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile)
 {
     const uint32_t x = tile.x0 + blockIdx.x * blockDim.x + threadIdx.x;
@@ -422,17 +443,66 @@ cudaError_t PT_VARIANT_NAME(launch_ReSTIR_DI_LightsPresampling)(const LightPresa
     return cudaGetLastError();
 }
 
-cudaError_t PT_VARIANT_NAME(launch_ReSTIR_DI_InitialCandidates)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream)
+// Whether a ReSTIR DI pass runs phased (its rays through the ray-queue kernel): scratch large enough for the tile, no alpha testing
+// (a shadow ray would draw random numbers: FilterFunction.h:42), full-resolution rendering; B200PT_RESTIR_PHASES=0 keeps the one-kernel passes
+static bool restir_phased(const HIPRTRenderData* rd, Tile tile, const RestirScratch* scratch)
+{
+    static const bool enabled = [] { const char* v = getenv("B200PT_RESTIR_PHASES"); return v ? atoi(v) != 0 : true; }();
+    const HIPRTRenderSettings& rs = rd->render_settings;
+    const bool low_resolution = rs.wants_render_low_resolution && rs.allow_render_low_resolution && rs.accumulate;
+    return enabled && scratch != nullptr && scratch->capacity >= (uint32_t)(tile.x1 - tile.x0) * (uint32_t)(tile.y1 - tile.y0) && !rs.do_alpha_testing && !low_resolution;
+}
+
+static cudaError_t restir_trace(const HIPRTRenderData* rd, const RestirScratch* scratch, bool any_hit, cudaStream_t stream)
+{
+#ifdef PT_COUNTERS
+    TraversalCounters* const counters = reinterpret_cast<TraversalCounters*>(rd->hiprt_function_table);
+#else
+    TraversalCounters* const counters = nullptr;
+#endif
+    uint32_t* const counts = scratch->counts + (any_hit ? 2 : 0);
+    RayQueueView q{scratch->queue, counts, counts + 1, scratch->ray_o, scratch->ray_d, scratch->hit_tuvp, scratch->hit_tri_slot, scratch->ray_o};
+    return PT_SUFFIXED(launch_trace_queue)(rd->geom, q, any_hit, scratch->sm_count * (unsigned)kTraceGridBlocksPerSM, counters, stream);
+}
+
+cudaError_t PT_VARIANT_NAME(launch_ReSTIR_DI_InitialCandidates)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const RestirScratch* scratch)
 {
     dim3 grid((tile.x1 - tile.x0 + 7) / 8, (tile.y1 - tile.y0 + 7) / 8, 1);
-    PT_VARIANT_NAME(k_ReSTIR_DI_InitialCandidates)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile);
+    if (!restir_phased(rd, tile, scratch) || rd->render_settings.restir_di_settings.initial_candidates.number_of_initial_bsdf_candidates > 1)
+    {
+        PT_VARIANT_NAME(k_ReSTIR_DI_InitialCandidates)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile);
+        return cudaGetLastError();
+    }
+    cudaError_t e = cudaMemsetAsync(scratch->counts, 0, 4 * sizeof(uint32_t), stream);
+    if (e != cudaSuccess)
+        return e;
+    PT_VARIANT_NAME(k_ReSTIR_DI_InitialCandidates_collect)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile, *scratch);
+    if ((e = restir_trace(rd, scratch, false, stream)) != cudaSuccess)
+        return e;
+    PT_VARIANT_NAME(k_ReSTIR_DI_InitialCandidates_resolve)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile, *scratch);
+    if ((e = restir_trace(rd, scratch, true, stream)) != cudaSuccess)
+        return e;
+    PT_VARIANT_NAME(k_ReSTIR_DI_InitialCandidates_visibility)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile, *scratch);
     return cudaGetLastError();
 }
 
-cudaError_t PT_VARIANT_NAME(launch_ReSTIR_DI_SpatiotemporalReuse)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream)
+cudaError_t PT_VARIANT_NAME(launch_ReSTIR_DI_SpatiotemporalReuse)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const RestirScratch* scratch)
 {
     dim3 grid((tile.x1 - tile.x0 + 7) / 8, (tile.y1 - tile.y0 + 7) / 8, 1);
-    PT_VARIANT_NAME(k_ReSTIR_DI_SpatiotemporalReuse)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile);
+    const SpatialPassSettings& sp = rd->render_settings.restir_di_settings.spatial_pass;
+    const int neighbors = sp.do_disocclusion_reuse_boost && sp.disocclusion_reuse_count > sp.reuse_neighbor_count ? sp.disocclusion_reuse_count : sp.reuse_neighbor_count;
+    if (!restir_phased(rd, tile, scratch) || neighbors > kRestirMaxNeighbors)
+    {
+        PT_VARIANT_NAME(k_ReSTIR_DI_SpatiotemporalReuse)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile);
+        return cudaGetLastError();
+    }
+    cudaError_t e = cudaMemsetAsync(scratch->counts, 0, 4 * sizeof(uint32_t), stream);
+    if (e != cudaSuccess)
+        return e;
+    PT_VARIANT_NAME(k_ReSTIR_DI_SpatiotemporalReuse_collect)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile, *scratch);
+    if ((e = restir_trace(rd, scratch, true, stream)) != cudaSuccess)
+        return e;
+    PT_VARIANT_NAME(k_ReSTIR_DI_SpatiotemporalReuse_resolve)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile, *scratch);
     return cudaGetLastError();
 }
 

@@ -330,8 +330,8 @@ PT_FOR_EACH_VARIANT(PT_DECLARE_VARIANT)
 
 #define PT_DECLARE_RESTIR(LSS, ESS, LATER, GGX)                                                                                                                    \
     cudaError_t PT_VARIANT_NAME_OF(launch_ReSTIR_DI_LightsPresampling, LSS, ESS, LATER, GGX)(const LightPresamplingParameters* p, cudaStream_t stream);              \
-    cudaError_t PT_VARIANT_NAME_OF(launch_ReSTIR_DI_InitialCandidates, LSS, ESS, LATER, GGX)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream);    \
-    cudaError_t PT_VARIANT_NAME_OF(launch_ReSTIR_DI_SpatiotemporalReuse, LSS, ESS, LATER, GGX)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream); \
+    cudaError_t PT_VARIANT_NAME_OF(launch_ReSTIR_DI_InitialCandidates, LSS, ESS, LATER, GGX)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const RestirScratch* scratch);    \
+    cudaError_t PT_VARIANT_NAME_OF(launch_ReSTIR_DI_SpatiotemporalReuse, LSS, ESS, LATER, GGX)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const RestirScratch* scratch); \
     cudaError_t PT_VARIANT_NAME_OF(launch_ReSTIR_DI_TemporalReuse, LSS, ESS, LATER, GGX)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream);        \
     cudaError_t PT_VARIANT_NAME_OF(launch_ReSTIR_DI_SpatialReuse, LSS, ESS, LATER, GGX)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream);
 #define PT_DECLARE_RESTIR_IF_5(LSS, ESS, LATER, GGX) PT_DECLARE_RESTIR_##LSS(LSS, ESS, LATER, GGX)
@@ -352,16 +352,16 @@ cudaError_t PT_SUFFIXED(launch_ReSTIR_DI_LightsPresampling)(const VariantOptions
     return cudaErrorInvalidDeviceFunction;
 }
 
-cudaError_t PT_SUFFIXED(launch_ReSTIR_DI_InitialCandidates)(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream)
+cudaError_t PT_SUFFIXED(launch_ReSTIR_DI_InitialCandidates)(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const RestirScratch* scratch)
 {
-#define PT_CASE_INITIAL(LSS, ESS, LATER, GGX) PT_CASE_RESTIR_##LSS(PT_VARIANT_NAME_OF(launch_ReSTIR_DI_InitialCandidates, LSS, ESS, LATER, GGX)(rd, res, tile, stream), LSS, ESS, LATER, GGX)
+#define PT_CASE_INITIAL(LSS, ESS, LATER, GGX) PT_CASE_RESTIR_##LSS(PT_VARIANT_NAME_OF(launch_ReSTIR_DI_InitialCandidates, LSS, ESS, LATER, GGX)(rd, res, tile, stream, scratch), LSS, ESS, LATER, GGX)
     PT_FOR_EACH_VARIANT(PT_CASE_INITIAL)
     return cudaErrorInvalidDeviceFunction;
 }
 
-cudaError_t PT_SUFFIXED(launch_ReSTIR_DI_SpatiotemporalReuse)(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream)
+cudaError_t PT_SUFFIXED(launch_ReSTIR_DI_SpatiotemporalReuse)(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const RestirScratch* scratch)
 {
-#define PT_CASE_SPATIOTEMPORAL(LSS, ESS, LATER, GGX) PT_CASE_RESTIR_##LSS(PT_VARIANT_NAME_OF(launch_ReSTIR_DI_SpatiotemporalReuse, LSS, ESS, LATER, GGX)(rd, res, tile, stream), LSS, ESS, LATER, GGX)
+#define PT_CASE_SPATIOTEMPORAL(LSS, ESS, LATER, GGX) PT_CASE_RESTIR_##LSS(PT_VARIANT_NAME_OF(launch_ReSTIR_DI_SpatiotemporalReuse, LSS, ESS, LATER, GGX)(rd, res, tile, stream, scratch), LSS, ESS, LATER, GGX)
     PT_FOR_EACH_VARIANT(PT_CASE_SPATIOTEMPORAL)
     return cudaErrorInvalidDeviceFunction;
 }

@@ -109,6 +109,29 @@ struct WavefrontProfile
     int count;
 };
 
+// Scratch of the PHASED ReSTIR DI passes (restir_di_kernels.cuh): a pass is cut at its rays, which go through the ray-queue traversal
+// kernel instead of a per-thread traversal inside the pass. A ray of a pixel belongs to a SITE of the pass (which evaluation of the
+// pass it serves); ray id = site * capacity + pixel inside the tile.
+//   InitialCandidates:     site 0 = the BSDF candidate's ray (closest hit), site 1 = visibility of the chosen candidate
+//   SpatiotemporalReuse:   site 0 = temporal neighbour's sample seen from the pixel, site 1 = the pixel's sample seen from the temporal
+//                          neighbour's surface, sites 2 + 2 i / 3 + 2 i = the same pair for spatial neighbour i
+constexpr int kRestirMaxNeighbors = 5;                       // spatial neighbours per pixel the phased pass has sites for (more: unphased kernel)
+constexpr int kRestirSites = 2 + 2 * kRestirMaxNeighbors;
+struct RestirScratch
+{
+    float4* ray_o;           // [ray id] origin | t_max; the any-hit trace sets .w = -1 when the ray is occluded
+    float4* ray_d;           // [ray id] direction | primitive the ray leaves from (int bits)
+    float* target;           // [ray id] target function of the site before visibility (0: nothing to trace)
+    float4* hit_tuvp;        // [pixel] closest hit of the initial-candidates BSDF ray
+    uint32_t* hit_tri_slot;
+    float4* ic_state;        // [k * capacity + pixel], k < 4: initial candidates between their phases (reservoir, generator, BSDF sample)
+    uint32_t* status;        // [pixel] 0: the pass has nothing to do for the pixel (COLLECT's early returns), else what the next phase continues with
+    uint32_t* queue;         // ray ids of the trace launch in flight (kRestirSites * capacity)
+    uint32_t* counts;        // 2 x (queue length, work cursor)
+    uint32_t capacity;       // pixels
+    uint32_t sm_count;
+};
+
 // Input/output arrays of one launch of the ray-queue traversal kernel (trace_queue.cuh)
 struct RayQueueView
 {
@@ -128,8 +151,8 @@ struct RayQueueView
     cudaError_t launch_FullPathTracer##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const WavefrontState* wf, int mode, WavefrontProfile* profile); \
     cudaError_t launch_PathTraceSamples##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const WavefrontState* wf, const SampleBatch* batch, WavefrontProfile* profile); \
     cudaError_t launch_ReSTIR_DI_LightsPresampling##S(const VariantOptions& opt, const LightPresamplingParameters* p, cudaStream_t stream);            \
-    cudaError_t launch_ReSTIR_DI_InitialCandidates##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream); \
-    cudaError_t launch_ReSTIR_DI_SpatiotemporalReuse##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream); \
+    cudaError_t launch_ReSTIR_DI_InitialCandidates##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const RestirScratch* scratch); \
+    cudaError_t launch_ReSTIR_DI_SpatiotemporalReuse##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const RestirScratch* scratch); \
     cudaError_t launch_ReSTIR_DI_TemporalReuse##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream); \
     cudaError_t launch_ReSTIR_DI_SpatialReuse##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream); \
     cudaError_t launch_trace_queue##S(const void* bvh_device_handle, const RayQueueView& q, bool any_hit, unsigned blocks, TraversalCounters* counters, cudaStream_t stream); \

@@ -8,6 +8,7 @@
 #pragma once
 
 #include "ris.cuh"
+#include "launch.h"
 
 namespace pt
 {
@@ -120,13 +121,18 @@ struct ReSTIRSurface
 
 PT_DEV bool use_prev_frame_g_buffer(const HIPRTRenderData& rd) { return rd.render_settings.restir_di_settings.temporal_pass.do_temporal_reuse_pass; }
 
+// FULL = false: only what the resolve phase of a phased pass reads (points, normals, primitive), not the 256-byte material
+template <bool FULL = true>
 PT_DEV void get_pixel_surface(const HIPRTRenderData& rd, int pixel_index, bool previous_frame, ReSTIRSurface& s)
 {
     const GBuffer& g = previous_frame ? rd.g_buffer_prev_frame : rd.g_buffer;
-    load_material(s.material, g.materials + pixel_index);
-    copy_volume_state(&s.ray_volume_state, g.ray_volume_states + pixel_index);
+    if (FULL)
+    {
+        load_material(s.material, g.materials + pixel_index);
+        copy_volume_state(&s.ray_volume_state, g.ray_volume_states + pixel_index);
+        s.view_direction = ld3_rw(g.view_directions, pixel_index);
+    }
     s.last_hit_primitive_index = g.first_hit_prim_index[pixel_index];
-    s.view_direction = ld3_rw(g.view_directions, pixel_index);
     s.shading_normal = ld3_rw(g.shading_normals, pixel_index);
     s.geometric_normal = ld3_rw(g.geometric_normals, pixel_index);
     s.shading_point = ld3_rw(g.first_hits, pixel_index) + s.shading_normal * 1.0e-4f;
@@ -142,10 +148,54 @@ PT_DEV RGB restir_sample_emission(const HIPRTRenderData& rd, const ReSTIRDISampl
     return material_buffer_emission(rd, __ldg(rd.buffers.material_indices + sample.emissive_triangle_index));
 }
 
-// ReSTIR_DI_evaluate_target_function<withVisibility> (Utils.h:17-132)
-template <bool WITH_VISIBILITY>
-PT_DEV_NOINLINE float restir_evaluate_target_function(const HIPRTRenderData& rd, const ReSTIRDISample& sample, const ReSTIRSurface& surface, Rng& rng)
+// ---- phased passes (launch.h: RestirScratch): a pass runs as COLLECT (everything up to its visibility rays, which are queued) ->
+// ray-queue traversal -> RESOLVE (the resampling itself, with the traced answers). INLINE is the unphased pass: one kernel that
+// traces per thread. Which rays a pass needs does not depend on the answers of earlier ones (the samples and surfaces are inputs,
+// no random number is drawn between the neighbour search and the resampling), so COLLECT can queue them all.
+enum { RESTIR_INLINE = 0, RESTIR_COLLECT = 1, RESTIR_RESOLVE = 2 };
+struct RestirSites
 {
+    const RestirScratch* scratch = nullptr;
+    uint32_t pixel = 0;        // pixel inside the launch tile
+    PT_DEV uint32_t ray_id(int site) const { return (uint32_t)site * scratch->capacity + pixel; }
+    PT_DEV void emit(int site, float3 origin, float3 direction, float t_max, int last_prim, int counts_index) const
+    {
+        const uint32_t id = ray_id(site);
+        scratch->ray_o[id] = make_float4(origin.x, origin.y, origin.z, t_max);
+        scratch->ray_d[id] = make_float4(direction.x, direction.y, direction.z, __int_as_float(last_prim));
+        // warp-aggregated append (the lanes of the warp that are here together take consecutive entries)
+        const unsigned mask = __activemask();
+        uint32_t lane;
+        asm("mov.u32 %0, %%laneid;" : "=r"(lane));
+        const int leader = __ffs((int)mask) - 1;
+        uint32_t base = 0;
+        if ((int)lane == leader)
+            base = atomicAdd(scratch->counts + counts_index, (uint32_t)__popc(mask));
+        base = __shfl_sync(mask, base, leader);
+        scratch->queue[base + (uint32_t)__popc(mask & ((1u << lane) - 1u))] = id;
+    }
+    PT_DEV void emit_any_hit(int site, float3 origin, float3 direction, float t_max, int last_prim) const { emit(site, origin, direction, t_max, last_prim, 2); }
+    PT_DEV bool occluded(int site) const { return scratch->ray_o[ray_id(site)].w == -1.0f; }
+};
+
+// ReSTIR_DI_evaluate_target_function<withVisibility> (Utils.h:17-132)
+template <bool WITH_VISIBILITY, int MODE = RESTIR_INLINE>
+PT_DEV_NOINLINE float restir_evaluate_target_function(const HIPRTRenderData& rd, const ReSTIRDISample& sample, const ReSTIRSurface& surface, Rng& rng, const RestirSites sites = RestirSites(),
+                                                      int site = 0)
+{
+    if (MODE == RESTIR_RESOLVE)
+    {
+        // the value COLLECT stored for this site, times the traced visibility
+        float target_function = sites.scratch->target[sites.ray_id(site)];
+        if (WITH_VISIBILITY && target_function != 0.0f)
+        {
+            bool visible = !sites.occluded(site);
+            target_function *= visible;
+        }
+        return target_function;
+    }
+    if (MODE == RESTIR_COLLECT)
+        sites.scratch->target[sites.ray_id(site)] = 0.0f;
     if (sample.emissive_triangle_index == -1 && !(sample.flags & RESTIR_DI_FLAGS_ENVMAP_SAMPLE))
         return 0.0f;
 
@@ -173,6 +223,13 @@ PT_DEV_NOINLINE float restir_evaluate_target_function(const HIPRTRenderData& rd,
     float target_function = (bsdf_color * sample_emission * cosine_term).luminance();
     if (target_function == 0.0f)
         return 0.0f;
+    if (MODE == RESTIR_COLLECT)
+    {
+        sites.scratch->target[sites.ray_id(site)] = target_function;
+        if (WITH_VISIBILITY)
+            sites.emit_any_hit(site, surface.shading_point, sample_direction, distance_to_light, surface.last_hit_primitive_index);
+        return target_function;
+    }
     if (WITH_VISIBILITY)
     {
         bool visible = !evaluate_shadow_ray(rd, surface.shading_point, sample_direction, distance_to_light, surface.last_hit_primitive_index, rng);
@@ -182,26 +239,46 @@ PT_DEV_NOINLINE float restir_evaluate_target_function(const HIPRTRenderData& rd,
 }
 
 // ReSTIR_DI_visibility_reuse (Utils.h:138-170)
-PT_DEV void restir_visibility_reuse(const HIPRTRenderData& rd, ReSTIRDIReservoir& reservoir, float3 shading_point, int last_primitive_hit_index, Rng& rng)
+// The shadow ray ReSTIR_DI_visibility_reuse traces for a sample seen from shading_point
+PT_DEV void restir_visibility_reuse_ray(const HIPRTRenderData& rd, const ReSTIRDISample& sample, float3 shading_point, float3& sample_direction, float& distance_to_light)
+{
+    if (sample.flags & RESTIR_DI_FLAGS_ENVMAP_SAMPLE)
+    {
+        sample_direction = matrix_X_vec(as_mat4(rd.world_settings.envmap_to_world_matrix), to_f3(sample.point_on_light_source));
+        distance_to_light = 1.0e35f;
+    }
+    else
+    {
+        sample_direction = to_f3(sample.point_on_light_source) - shading_point;
+        sample_direction /= (distance_to_light = length(sample_direction));
+    }
+}
+
+// COLLECT queues the ray at `site` and leaves the reservoir alone (the answer is applied by a later phase); RESOLVE applies the answer
+template <int MODE = RESTIR_INLINE>
+PT_DEV void restir_visibility_reuse(const HIPRTRenderData& rd, ReSTIRDIReservoir& reservoir, float3 shading_point, int last_primitive_hit_index, Rng& rng, const RestirSites sites = RestirSites(),
+                                    int site = 0)
 {
     if (reservoir.UCW <= 0.0f)
         return;
     else if (reservoir.sample.flags & RESTIR_DI_FLAGS_UNOCCLUDED)
         return;
 
-    float distance_to_light;
-    float3 sample_direction;
-    if (reservoir.sample.flags & RESTIR_DI_FLAGS_ENVMAP_SAMPLE)
-    {
-        sample_direction = matrix_X_vec(as_mat4(rd.world_settings.envmap_to_world_matrix), to_f3(reservoir.sample.point_on_light_source));
-        distance_to_light = 1.0e35f;
-    }
+    bool visible;
+    if (MODE == RESTIR_RESOLVE)
+        visible = !sites.occluded(site);
     else
     {
-        sample_direction = to_f3(reservoir.sample.point_on_light_source) - shading_point;
-        sample_direction /= (distance_to_light = length(sample_direction));
+        float distance_to_light;
+        float3 sample_direction;
+        restir_visibility_reuse_ray(rd, reservoir.sample, shading_point, sample_direction, distance_to_light);
+        if (MODE == RESTIR_COLLECT)
+        {
+            sites.emit_any_hit(site, shading_point, sample_direction, distance_to_light, last_primitive_hit_index);
+            return;
+        }
+        visible = !evaluate_shadow_ray(rd, shading_point, sample_direction, distance_to_light, last_primitive_hit_index, rng);
     }
-    bool visible = !evaluate_shadow_ray(rd, shading_point, sample_direction, distance_to_light, last_primitive_hit_index, rng);
     if (!visible)
         reservoir.UCW = -1.0f;
     else
@@ -370,8 +447,11 @@ struct PairwiseDefensiveMISWeight
     // pass (SpatiotemporalMISWeight.h:241) from last frame's when the temporal pass is enabled; the arithmetic is the same
     bool neighbor_surface_of_current_frame = false;
 
+    // `site`: the ray site of the canonical sample seen from this neighbour's surface (phased passes)
+    template <int MODE = RESTIR_INLINE>
     PT_DEV float get(const HIPRTRenderData& rd, const ReSTIRDIReservoir& reservoir_being_resampled, const ReSTIRDIReservoir& center_pixel_reservoir, float target_function_at_center,
-                     int neighbor_pixel_index, int valid_neighbors_count, int valid_neighbors_M_sum, bool update_mc, bool resample_canonical, Rng& rng)
+                     int neighbor_pixel_index, int valid_neighbors_count, int valid_neighbors_M_sum, bool update_mc, bool resample_canonical, Rng& rng,
+                     const RestirSites sites = RestirSites(), int site = 0)
     {
         const bool confidence = rd.render_settings.restir_di_settings.use_confidence_weights;
         if (!resample_canonical)
@@ -393,8 +473,9 @@ struct PairwiseDefensiveMISWeight
             if (update_mc)
             {
                 ReSTIRSurface neighbor_pixel_surface;
-                get_pixel_surface(rd, neighbor_pixel_index, neighbor_surface_of_current_frame ? false : use_prev_frame_g_buffer(rd), neighbor_pixel_surface);
-                float at_neighbor = restir_evaluate_target_function<true>(rd, center_pixel_reservoir.sample, neighbor_pixel_surface, rng);
+                if (MODE != RESTIR_RESOLVE)
+                    get_pixel_surface(rd, neighbor_pixel_index, neighbor_surface_of_current_frame ? false : use_prev_frame_g_buffer(rd), neighbor_pixel_surface);
+                float at_neighbor = restir_evaluate_target_function<true, MODE>(rd, center_pixel_reservoir.sample, neighbor_pixel_surface, rng, sites, site);
                 float at_center = center_pixel_reservoir.sample.target_function;
                 float nume_mc = at_center / valid_neighbor_division_term * center_reservoir_M;
                 float denom_mc = at_neighbor * neighbors_confidence_sum + at_center / valid_neighbor_division_term * center_reservoir_M;

@@ -134,17 +134,60 @@ PT_DEV ReSTIRDISample restir_use_presampled_light_candidate(const HIPRTRenderDat
     return light_sample;
 }
 
-template <int GGX_SAMPLER>
-PT_DEV void restir_initial_candidates_pixel(const HIPRTRenderData& rd, int2 res, uint32_t x, uint32_t y)
+// The state of a pixel between the phases of the phased pass (RestirScratch::ic_state, 4 x float4): the reservoir after the light
+// candidates, the generator, the BSDF candidate's value and pdf and whether it refracts (its direction is in the queued ray)
+PT_DEV void restir_ic_state_store(const RestirSites& sites, const ReSTIRDIReservoir& r, const Rng& rng, RGB bsdf_color, float bsdf_sample_pdf, bool refraction_sampled)
 {
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(&r);
+    float4* st = sites.scratch->ic_state + sites.pixel;
+    const uint32_t n = sites.scratch->capacity;
+    st[0] = make_float4(__uint_as_float(w[0]), __uint_as_float(w[1]), __uint_as_float(w[2]), __uint_as_float(w[3]));
+    st[n] = make_float4(__uint_as_float(w[4]), __uint_as_float(w[5]), __uint_as_float(w[6]), __uint_as_float(w[7]));
+    st[2 * n] = make_float4(__uint_as_float(w[8]), __uint_as_float(rng.state), bsdf_sample_pdf, __uint_as_float(refraction_sampled ? 1u : 0u));
+    st[3 * n] = make_float4(bsdf_color.r, bsdf_color.g, bsdf_color.b, 0.0f);
+}
+PT_DEV void restir_ic_state_load(const RestirSites& sites, ReSTIRDIReservoir& r, Rng& rng, RGB& bsdf_color, float& bsdf_sample_pdf, bool& refraction_sampled)
+{
+    uint32_t* w = reinterpret_cast<uint32_t*>(&r);
+    const float4* st = sites.scratch->ic_state + sites.pixel;
+    const uint32_t n = sites.scratch->capacity;
+    const float4 a = st[0], b = st[n], c = st[2 * n], d = st[3 * n];
+    w[0] = __float_as_uint(a.x); w[1] = __float_as_uint(a.y); w[2] = __float_as_uint(a.z); w[3] = __float_as_uint(a.w);
+    w[4] = __float_as_uint(b.x); w[5] = __float_as_uint(b.y); w[6] = __float_as_uint(b.z); w[7] = __float_as_uint(b.w);
+    w[8] = __float_as_uint(c.x);
+    rng.state = __float_as_uint(c.y);
+    bsdf_sample_pdf = c.z;
+    refraction_sampled = __float_as_uint(c.w) != 0u;
+    bsdf_color = RGB(d.x, d.y, d.z);
+}
+
+// MODE (restir_di.cuh): INLINE = the whole pass, rays traced per thread. Phased, with one BSDF candidate per pixel: COLLECT = light
+// candidates + BSDF sample, the BSDF candidate's ray queued (site 0, closest hit), state saved; RESOLVE = the BSDF candidate finished
+// from the traced hit, reservoir closed and stored, its visibility ray queued (site 1; status 3) -- restir_initial_candidates_visibility
+// applies the answer to the stored reservoir.
+template <int GGX_SAMPLER, int MODE = RESTIR_INLINE>
+PT_DEV void restir_initial_candidates_pixel(const HIPRTRenderData& rd, int2 res, uint32_t x, uint32_t y, const RestirSites sites = RestirSites())
+{
+    if (MODE == RESTIR_COLLECT)
+        sites.scratch->status[sites.pixel] = 0u;
     if (rd.buffers.emissive_triangles_count == 0 && rd.world_settings.ambient_light_type != AMBIENT_ENVMAP)
         return;
     const uint32_t pixel_index = x + y * res.x;
+    const uint32_t status = MODE == RESTIR_RESOLVE ? sites.scratch->status[sites.pixel] : 0u;
+    if (MODE == RESTIR_RESOLVE)
+    {
+        if (status == 0u)
+            return;
+        sites.scratch->status[sites.pixel] = 0u;
+    }
 
     RayPayload payload;
-    load_material(payload.material, rd.g_buffer.materials + pixel_index);
-    if (material_is_emissive(payload.material))
-        return;
+    if (MODE != RESTIR_RESOLVE)
+    {
+        load_material(payload.material, rd.g_buffer.materials + pixel_index);
+        if (material_is_emissive(payload.material))
+            return;
+    }
     Rng rng(pixel_seed(rd, pixel_index));
     if (!rd.aux_buffers.pixel_active[pixel_index] || !rd.g_buffer.camera_ray_hit[pixel_index])
         return;
@@ -154,8 +197,12 @@ PT_DEV void restir_initial_candidates_pixel(const HIPRTRenderData& rd, int2 res,
     hit.shading_normal = ld3_rw(rd.g_buffer.shading_normals, pixel_index);
     hit.inter_point = ld3_rw(rd.g_buffer.first_hits, pixel_index);
     hit.primitive_index = rd.g_buffer.first_hit_prim_index[pixel_index];
-    copy_volume_state(&payload.volume_state, rd.g_buffer.ray_volume_states + pixel_index);
-    const float3 view_direction = ld3_rw(rd.g_buffer.view_directions, pixel_index);
+    float3 view_direction = f3(0.0f);
+    if (MODE != RESTIR_RESOLVE)
+    {
+        copy_volume_state(&payload.volume_state, rd.g_buffer.ray_volume_states + pixel_index);
+        view_direction = ld3_rw(rd.g_buffer.view_directions, pixel_index);
+    }
 
     // sample_initial_candidates (:413-446)
     const InitialCandidatesSettings& ic = rd.render_settings.restir_di_settings.initial_candidates;
@@ -170,7 +217,7 @@ PT_DEV void restir_initial_candidates_pixel(const HIPRTRenderData& rd, int2 res,
     const float3 evaluated_point = hit.inter_point + hit.shading_normal * 1.0e-4f * 1.0f;
 
     // sample_light_candidates (:185-279), presampled lights
-    for (int i = 0; i < nb_light_candidates; i++)
+    for (int i = 0; i < nb_light_candidates && MODE != RESTIR_RESOLVE; i++)
     {
         RGB sample_radiance;
         float sample_cosine_term = 0.0f, sample_pdf = 0.0f, distance_to_light = 0.0f;
@@ -205,14 +252,41 @@ PT_DEV void restir_initial_candidates_pixel(const HIPRTRenderData& rd, int2 res,
     {
         float bsdf_sample_pdf = 0.0f;
         float3 sampled_direction;
-        RayVolumeState trash = payload.volume_state;
-        RGB bsdf_color = bsdf_sample<GGX_SAMPLER>(rd, payload.material, trash, view_direction, hit.shading_normal, hit.geometric_normal, sampled_direction, bsdf_sample_pdf, rng);
-        bool refraction_sampled = dot(sampled_direction, view_direction) < 0.0f;
-        if (!(bsdf_sample_pdf > 0.0f))
-            continue;
+        RGB bsdf_color;
+        bool refraction_sampled;
+        if (MODE != RESTIR_RESOLVE)
+        {
+            RayVolumeState trash = payload.volume_state;
+            bsdf_color = bsdf_sample<GGX_SAMPLER>(rd, payload.material, trash, view_direction, hit.shading_normal, hit.geometric_normal, sampled_direction, bsdf_sample_pdf, rng);
+            refraction_sampled = dot(sampled_direction, view_direction) < 0.0f;
+            if (!(bsdf_sample_pdf > 0.0f))
+                continue;
+        }
+        if (MODE == RESTIR_COLLECT)
+        {
+            sites.emit(0, hit.inter_point, sampled_direction, 1.0e35f, hit.primitive_index, 0);
+            restir_ic_state_store(sites, reservoir, rng, bsdf_color, bsdf_sample_pdf, refraction_sampled);
+            sites.scratch->status[sites.pixel] = 2u;
+            return;
+        }
 
         ShadowLightRayHitInfo light_hit;
-        bool hit_found = evaluate_shadow_light_ray(rd, hit.inter_point, sampled_direction, 1.0e35f, light_hit, hit.primitive_index, rng);
+        bool hit_found;
+        if (MODE == RESTIR_RESOLVE)
+        {
+            if (status != 2u)
+                break;       // the BSDF sample had no pdf: no candidate
+            restir_ic_state_load(sites, reservoir, rng, bsdf_color, bsdf_sample_pdf, refraction_sampled);
+            const float4 d = sites.scratch->ray_d[sites.ray_id(0)];
+            sampled_direction = f3(d.x, d.y, d.z);
+            const float4 h = sites.scratch->hit_tuvp[sites.pixel];
+            Hit closest;
+            closest.t = h.x; closest.u = h.y; closest.v = h.z; closest.prim = __float_as_int(h.w);
+            closest.tri_slot = (int)sites.scratch->hit_tri_slot[sites.pixel];
+            hit_found = shadow_light_ray_resolve(rd, 1.0e35f, light_hit, closest);
+        }
+        else
+            hit_found = evaluate_shadow_light_ray(rd, hit.inter_point, sampled_direction, 1.0e35f, light_hit, hit.primitive_index, rng);
         if (hit_found && !light_hit.hit_emission.is_black())
         {
             float cosine_at_evaluated_point = fabsf(dot(hit.shading_normal, sampled_direction));
@@ -267,11 +341,45 @@ PT_DEV void restir_initial_candidates_pixel(const HIPRTRenderData& rd, int2 res,
         }
     }
 
+    if (MODE == RESTIR_COLLECT)
+    {
+        // no BSDF candidate to trace: the reservoir of the light candidates goes to the next phase as it is
+        restir_ic_state_store(sites, reservoir, rng, RGB(0.0f), 0.0f, false);
+        sites.scratch->status[sites.pixel] = 1u;
+        return;
+    }
+    if (MODE == RESTIR_RESOLVE && status == 1u)
+    {
+        RGB unused_color;
+        float unused_pdf;
+        bool unused_flag;
+        restir_ic_state_load(sites, reservoir, rng, unused_color, unused_pdf, unused_flag);
+    }
+
     reservoir_end(reservoir);
     reservoir.M = 1;
     // ReSTIR_DI_DoVisibilityReuse
-    restir_visibility_reuse(rd, reservoir, hit.inter_point + hit.shading_normal * 1.0e-4f, hit.primitive_index, rng);
+    if (MODE == RESTIR_RESOLVE)
+    {
+        if (reservoir.UCW > 0.0f && !(reservoir.sample.flags & RESTIR_DI_FLAGS_UNOCCLUDED))
+            sites.scratch->status[sites.pixel] = 3u;
+        restir_visibility_reuse<RESTIR_COLLECT>(rd, reservoir, hit.inter_point + hit.shading_normal * 1.0e-4f, hit.primitive_index, rng, sites, 1);
+    }
+    else
+        restir_visibility_reuse(rd, reservoir, hit.inter_point + hit.shading_normal * 1.0e-4f, hit.primitive_index, rng);
     store_reservoir(rd.render_settings.restir_di_settings.initial_candidates.output_reservoirs + pixel_index, reservoir);
+}
+
+// Last phase of the phased pass: the visibility of the candidate a pixel kept (ReSTIR_DI_visibility_reuse's two outcomes)
+PT_DEV void restir_initial_candidates_visibility(const HIPRTRenderData& rd, int2 res, uint32_t x, uint32_t y, const RestirSites sites)
+{
+    if (sites.scratch->status[sites.pixel] != 3u)
+        return;
+    ReSTIRDIReservoir* out = rd.render_settings.restir_di_settings.initial_candidates.output_reservoirs + (x + y * res.x);
+    if (sites.occluded(1))
+        out->UCW = -1.0f;
+    else
+        out->sample.flags |= RESTIR_DI_FLAGS_UNOCCLUDED;
 }
 
 // ---- K5: ReSTIR_DI_SpatiotemporalReuse (fused temporal + spatial pass) ------------------------------------------------------------
@@ -288,10 +396,18 @@ PT_DEV bool restir_include_spatial_visibility(const HIPRTRenderData& rd, int cur
     return include;     // ReSTIR_DI_SpatialTargetFunctionVisibility == TRUE
 }
 
-PT_DEV void restir_spatiotemporal_pixel(const HIPRTRenderData& rd, int2 res, uint32_t x, uint32_t y)
+// MODE (restir_di.cuh): INLINE = the whole pass with per-thread shadow rays; COLLECT = neighbour search + every target function before
+// visibility (stored per site) + the shadow rays queued; RESOLVE = neighbour search again (same generator, same draws), then the
+// resampling with the stored target functions and the traced visibilities. Sites: launch.h (RestirScratch).
+template <int MODE = RESTIR_INLINE>
+PT_DEV void restir_spatiotemporal_pixel(const HIPRTRenderData& rd, int2 res, uint32_t x, uint32_t y, const RestirSites sites = RestirSites())
 {
     const uint32_t center_pixel_index = x + y * res.x;
+    if (MODE == RESTIR_COLLECT)
+        sites.scratch->status[sites.pixel] = 0u;
     if (!rd.aux_buffers.pixel_active[center_pixel_index] || !rd.g_buffer.camera_ray_hit[center_pixel_index])
+        return;
+    if (MODE == RESTIR_RESOLVE && sites.scratch->status[sites.pixel] == 0u)
         return;
 
     const ReSTIRDISettings& rs = rd.render_settings.restir_di_settings;
@@ -299,9 +415,11 @@ PT_DEV void restir_spatiotemporal_pixel(const HIPRTRenderData& rd, int2 res, uin
     const bool prev_g = use_prev_frame_g_buffer(rd);
 
     ReSTIRSurface center;
-    get_pixel_surface(rd, center_pixel_index, false, center);
-    if (material_is_emissive(center.material))
+    get_pixel_surface<MODE != RESTIR_RESOLVE>(rd, center_pixel_index, false, center);
+    if (MODE != RESTIR_RESOLVE && material_is_emissive(center.material))
         return;
+    if (MODE == RESTIR_COLLECT)
+        sites.scratch->status[sites.pixel] = 1u;
 
     if (rs.temporal_pass.temporal_buffer_clear_requested)
         store_reservoir(rs.temporal_pass.input_reservoirs + center_pixel_index, empty_reservoir());
@@ -316,7 +434,7 @@ PT_DEV void restir_spatiotemporal_pixel(const HIPRTRenderData& rd, int2 res, uin
     {
         temporal_neighbor_reservoir = load_reservoir(rs.temporal_pass.input_reservoirs + temporal.x);
         if (temporal_neighbor_reservoir.M != 0)
-            get_pixel_surface(rd, temporal.x, prev_g, temporal_neighbor_surface);
+            get_pixel_surface<MODE != RESTIR_RESOLVE>(rd, temporal.x, prev_g, temporal_neighbor_surface);
     }
     const int2 temporal_position = make_int2(temporal.y, temporal.z);
 
@@ -356,7 +474,7 @@ PT_DEV void restir_spatiotemporal_pixel(const HIPRTRenderData& rd, int2 res, uin
     {
         float target_function_at_center = 0.0f;
         if (temporal_neighbor_reservoir.UCW > 0.0f)
-            target_function_at_center = restir_evaluate_target_function<true>(rd, temporal_neighbor_reservoir.sample, center, rng);
+            target_function_at_center = restir_evaluate_target_function<true, MODE>(rd, temporal_neighbor_reservoir.sample, center, rng, sites, 0);
 
         float jacobian_determinant = 1.0f;
         if (target_function_at_center > 0.0f && temporal_neighbor_reservoir.UCW > 0.0f && !(temporal_neighbor_reservoir.sample.flags & RESTIR_DI_FLAGS_ENVMAP_SAMPLE))
@@ -365,13 +483,15 @@ PT_DEV void restir_spatiotemporal_pixel(const HIPRTRenderData& rd, int2 res, uin
             if (jacobian_determinant == -1.0f)
                 jacobian_determinant = 0.0f;
         }
-        float w = mis_weight_function.get(rd, temporal_neighbor_reservoir, initial_candidates_reservoir, target_function_at_center, temporal.x, valid_neighbors_count, valid_neighbors_M_sum, update_mc, false, rng);
-        if (reservoir_combine_with(out, temporal_neighbor_reservoir, w, target_function_at_center, jacobian_determinant, rng))
+        float w = mis_weight_function.template get<MODE>(rd, temporal_neighbor_reservoir, initial_candidates_reservoir, target_function_at_center, temporal.x, valid_neighbors_count, valid_neighbors_M_sum,
+                                                         update_mc, false, rng, sites, 1);
+        if (MODE != RESTIR_COLLECT && reservoir_combine_with(out, temporal_neighbor_reservoir, w, target_function_at_center, jacobian_determinant, rng))
             out.sample.flags |= RESTIR_DI_FLAGS_UNOCCLUDED;       // ReSTIR_DI_BiasCorrectionUseVisibility == TRUE
     }
 
     // spatial neighbours around the temporal position, the canonical (initial candidates) sample last (:292-470)
     const ReSTIRDIReservoir* spatial_input = rs.spatial_pass.input_reservoirs;
+    int final_visibility_site = -1;       // phased: the site whose ray is the end-of-pass visibility ray of the sample `out` holds
     int start_index = valid_neighbors_M_sum == 0 ? reused_neighbors_count : 0;
     for (int spatial_neighbor_index = start_index; spatial_neighbor_index < reused_neighbors_count + 1; spatial_neighbor_index++)
     {
@@ -397,9 +517,19 @@ PT_DEV void restir_spatiotemporal_pixel(const HIPRTRenderData& rd, int2 res, uin
             if (canonical)
                 target_function_at_center = neighbor_reservoir.sample.target_function;
             else if (do_neighbor_target_function_visibility)
-                target_function_at_center = restir_evaluate_target_function<true>(rd, neighbor_reservoir.sample, center, rng);
+                target_function_at_center = restir_evaluate_target_function<true, MODE>(rd, neighbor_reservoir.sample, center, rng, sites, 2 + 2 * spatial_neighbor_index);
             else
-                target_function_at_center = restir_evaluate_target_function<false>(rd, neighbor_reservoir.sample, center, rng);
+            {
+                target_function_at_center = restir_evaluate_target_function<false, MODE>(rd, neighbor_reservoir.sample, center, rng, sites, 2 + 2 * spatial_neighbor_index);
+                if (MODE == RESTIR_COLLECT)
+                {
+                    // if this sample is the one the pass keeps, the end-of-pass visibility reuse traces it from the pixel: that ray takes this site
+                    float distance_to_light;
+                    float3 sample_direction;
+                    restir_visibility_reuse_ray(rd, neighbor_reservoir.sample, center.shading_point, sample_direction, distance_to_light);
+                    sites.emit_any_hit(2 + 2 * spatial_neighbor_index, center.shading_point, sample_direction, distance_to_light, center.last_hit_primitive_index);
+                }
+            }
         }
 
         float jacobian_determinant = 1.0f;
@@ -408,7 +538,7 @@ PT_DEV void restir_spatiotemporal_pixel(const HIPRTRenderData& rd, int2 res, uin
             const GBuffer& g = prev_g ? rd.g_buffer_prev_frame : rd.g_buffer;
             float3 neighbor_shading_point = ld3_rw(g.first_hits, neighbor_pixel_index) + ld3_rw(g.shading_normals, neighbor_pixel_index) * 1.0e-4f;
             jacobian_determinant = restir_jacobian_reconnection_shift(rd, neighbor_reservoir, center.shading_point, neighbor_shading_point);
-            if (jacobian_determinant == -1.0f)
+            if (jacobian_determinant == -1.0f && MODE != RESTIR_COLLECT)     // COLLECT saw the target function before visibility: the neighbour may still be resampled
             {
                 out.M += neighbor_reservoir.M;
                 continue;
@@ -419,26 +549,37 @@ PT_DEV void restir_spatiotemporal_pixel(const HIPRTRenderData& rd, int2 res, uin
         if (neighbor_reservoir.UCW == 0.0f && !update_mc)
             mis_weight = 1.0f;
         else
-            mis_weight = mis_weight_function.get(rd, neighbor_reservoir, initial_candidates_reservoir, target_function_at_center, neighbor_pixel_index, valid_neighbors_count, valid_neighbors_M_sum, update_mc,
-                                                 canonical, rng);
+            mis_weight = mis_weight_function.template get<MODE>(rd, neighbor_reservoir, initial_candidates_reservoir, target_function_at_center, neighbor_pixel_index, valid_neighbors_count,
+                                                                valid_neighbors_M_sum, update_mc, canonical, rng, sites, 3 + 2 * spatial_neighbor_index);
 
-        if (reservoir_combine_with(out, neighbor_reservoir, mis_weight, target_function_at_center, jacobian_determinant, rng))
+        if (MODE != RESTIR_COLLECT && reservoir_combine_with(out, neighbor_reservoir, mis_weight, target_function_at_center, jacobian_determinant, rng))
         {
+            final_visibility_site = -1;
             if (do_neighbor_target_function_visibility)
                 out.sample.flags |= RESTIR_DI_FLAGS_UNOCCLUDED;
             else if (canonical)
                 out.sample.flags |= neighbor_reservoir.sample.flags & RESTIR_DI_FLAGS_UNOCCLUDED;
             else
+            {
                 out.sample.flags &= ~RESTIR_DI_FLAGS_UNOCCLUDED;
+                final_visibility_site = 2 + 2 * spatial_neighbor_index;
+            }
         }
     }
+    if (MODE == RESTIR_COLLECT)
+        return;
 
     // pairwise MIS: nothing left to normalise (SpatiotemporalNormalizationWeight.h:270-278)
     reservoir_end_with_normalization(out, 1.0f, 1.0f);
 
     // end-of-pass visibility reuse (:560-575)
     if (rs.temporal_pass.do_temporal_reuse_pass || rs.spatial_pass.number_of_passes - 1 != rs.spatial_pass.spatial_pass_index)
-        restir_visibility_reuse(rd, out, center.shading_point, center.last_hit_primitive_index, rng);
+    {
+        if (MODE == RESTIR_RESOLVE && final_visibility_site >= 0)
+            restir_visibility_reuse<RESTIR_RESOLVE>(rd, out, center.shading_point, center.last_hit_primitive_index, rng, sites, final_visibility_site);
+        else
+            restir_visibility_reuse(rd, out, center.shading_point, center.last_hit_primitive_index, rng);     // RESOLVE: a sample whose ray was not queued (none by construction)
+    }
 
     if (rs.m_cap > 0)
         out.M = mini(out.M, rs.m_cap);

@@ -170,6 +170,11 @@ class Context:
         """Ray binning before traversal: 2^bits cells per axis, 0 off, -1 environment / built-in default (b200pt_set_ray_bin_bits)."""
         _capi.check(self.lib.b200pt_set_ray_bin_bits(self.handle, C.c_int(bits)), "b200pt_set_ray_bin_bits")
 
+    def set_restir_phases(self, enable=True):
+        """ReSTIR DI InitialCandidates / SpatiotemporalReuse as collect -> ray-queue traversal -> resolve phases (default) or as single kernels
+        with per-thread traversal (b200pt_set_restir_phases); the reservoirs are the same bits."""
+        _capi.check(self.lib.b200pt_set_restir_phases(self.handle, C.c_int(1 if enable else 0)), "b200pt_set_restir_phases")
+
     def counters_enable(self, enable=True):
         _capi.check(self.lib.b200pt_counters_enable(self.handle, C.c_int(1 if enable else 0)), "b200pt_counters_enable")
 

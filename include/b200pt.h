@@ -245,6 +245,13 @@ B200PT_API int b200pt_set_trace_flavour(b200pt_ctx* ctx, int flavour);
  * the same part of the BVH. A scheduling choice only: every ray's hit record, hence the frame, is the same bits. Process-wide. */
 B200PT_API int b200pt_set_ray_bin_bits(b200pt_ctx* ctx, int bits);
 
+/* Phased ReSTIR DI passes (new; default on): b200pt_launch_ReSTIR_DI_InitialCandidates and _SpatiotemporalReuse run as
+ * COLLECT kernel(s) -> ray-queue traversal of the pass's rays -> RESOLVE kernel instead of one kernel that traces per thread (the reference's
+ * shape: ReSTIR_DI_InitialCandidates.h, FusedSpatiotemporalReuse.h). Needs no alpha testing, full-resolution rendering, <= 1 BSDF candidate
+ * and <= 5 reused spatial neighbours; otherwise, or with enable = 0, or B200PT_RESTIR_PHASES=0, the single kernels run. The reservoirs a
+ * pass writes are the same bits either way. The phased passes of one context share scratch: do not overlap them on different streams. */
+B200PT_API int b200pt_set_restir_phases(b200pt_ctx* ctx, int enable);
+
 /* ---- per-function known-answer entry points (the parity pins of SURVEY.md 8c item 3; not used by the render path) -------------------
  * The device functions of the shading path on caller-provided inputs, one item per thread, so that an image difference can be bisected to
  * a function. render_data supplies the LUT / envmap pointers (take it from a renderer that has rendered a frame). Device pointers; layouts

@@ -405,6 +405,44 @@ def test_ris_phases_are_bit_identical(pt, wl, ctx, lss, ess):
         assert np.array_equal(frames["megakernel"], frames[mode]), mode
 
 
+@pytest.mark.parametrize("ess,neighbors,boost", [("none", 2, True), ("alias_table", 2, True), ("none", 5, False), ("none", 1, False)])
+def test_restir_phases_are_bit_identical(pt, wl, ctx, ess, neighbors, boost):
+    """Phased ReSTIR DI passes (InitialCandidates: collect -> closest-hit trace -> resolve -> any-hit trace -> visibility; fused
+    SpatiotemporalReuse: collect -> any-hit trace -> resolve, rays through the ray-queue kernel) against the single kernels that trace per
+    thread: every frame's initial-candidates and output reservoirs, and the accumulated image, are the same bits over 5 frames (temporal
+    history, disocclusion boost, neighbours with and without the visibility term, envmap candidates with the alias-table permutation)."""
+    procedural = importlib.import_module("hiprt-path-tracer_b200.procedural")
+    W, H = 160, 112
+    cfg = wl.many_lights(W, H, boxes=100, lights=1500)
+    cfg["options"] = dict(lss="restir_di", ess=ess, ggx=0, later=3)
+    if ess == "alias_table":
+        cfg["envmap"] = {"texels": procedural.procedural_envmap(256, 128), "alias_probas": None, "alias_alias": None, "total_sum": 0.0}
+    cfg["settings"] = dict(cfg["settings"], **{"restir_di_settings.spatial_pass.reuse_neighbor_count": neighbors,
+                                               "restir_di_settings.spatial_pass.do_disocclusion_reuse_boost": int(boost),
+                                               "restir_di_settings.spatial_pass.neighbor_visibility_count": 3 if neighbors == 5 else 5})
+    results = {}
+    try:
+        for phased in (False, True):
+            ctx.set_restir_phases(phased)
+            g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="gpu")
+            per_frame = []
+            for _ in range(5):
+                g.render_frame()
+                g.synchronize()
+                per_frame.append((g.download("restir_initial_candidates").copy(), g.download("restir_output_reservoirs").copy()))
+            results[phased] = (per_frame, g.download("pixels").copy())
+            g.close()
+    finally:
+        ctx.set_restir_phases(True)
+    assert np.isfinite(results[True][1]).all() and results[True][1].sum() > 0
+    for frame, (single, phased) in enumerate(zip(results[False][0], results[True][0])):
+        assert np.array_equal(single[0], phased[0]), f"initial candidates differ in frame {frame}"
+        assert np.array_equal(single[1], phased[1]), f"output reservoirs differ in frame {frame}"
+    assert np.array_equal(results[False][1], results[True][1])
+    out = _reservoirs(results[True][0][-1][1])
+    assert (out["M"] > 1).mean() > 0.5          # the temporal history was reused
+
+
 def test_edge_cases_empty_scene_and_misses(pt, ctx):
     """Empty scene (0 triangles): every query misses; rays pointing away from the geometry miss; zero-length batches work."""
     bvh = ctx.build_bvh(np.zeros((0, 3), np.float32), np.zeros((0,), np.int32))

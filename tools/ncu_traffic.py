@@ -33,9 +33,9 @@ for r in rows[2:]:
     if "k_trace_queue" not in r[col["Kernel Name"]]:
         continue
     seconds = float(r[col["gpu__time_duration.sum"]].replace(",", "")) * scale("gpu__time_duration.sum")
-    for name, key in WEIGHTED.items():
+    for name, short in WEIGHTED.items():
         if name in col and r[col[name]] not in ("", "n/a"):
-            weighted[key] += float(r[col[name]].replace(",", "")) * seconds
+            weighted[short] += float(r[col[name]].replace(",", "")) * seconds
     tot["read"] += float(r[col["dram__bytes_read.sum"]].replace(",", "")) * scale("dram__bytes_read.sum")
     tot["write"] += float(r[col["dram__bytes_write.sum"]].replace(",", "")) * scale("dram__bytes_write.sum")
     tot["seconds"] += float(r[col["gpu__time_duration.sum"]].replace(",", "")) * scale("gpu__time_duration.sum")
