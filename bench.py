@@ -222,6 +222,32 @@ def run_ours(args, cfg, pt):
             # (36 B/px; the G-buffer of those rows is recomputed locally by CameraRays over tile + halo)
             comm.exchange_halo(g.device_pointer("restir_output_reservoirs"), H, W * 36, halo)     # on the render stream: ordered after the frame
 
+    # Column bands of a landscape frame do not cost the same (sky columns end at the first miss, terrain columns bounce 8 times): before
+    # anything is measured the ranks balance the plan on the device time of their own band, three frames, with the C ABI's
+    # b200pt_comm_balanced_bounds (a tile only changes which rank renders a pixel, never its value: tests/test_gpu_parity.py::test_column_tile_*)
+    balance_log = []
+    if world > 1 and sharding == "columns" and not args.no_balance:
+        bounds = [t[0] for t in tiles] + [W]
+        evb0, evb1 = C.c_void_p(), C.c_void_p()
+        lib.b200pt_event_create(ctx.handle, C.byref(evb0))
+        lib.b200pt_event_create(ctx.handle, C.byref(evb1))
+        for _ in range(3):
+            restart()
+            step()                     # allocations for the new band size
+            g.synchronize()
+            lib.b200pt_event_record(ctx.handle, evb0, None)
+            step()
+            lib.b200pt_event_record(ctx.handle, evb1, None)
+            g.synchronize()
+            ctx.sync()
+            band_ms = C.c_float()
+            lib.b200pt_event_elapsed_ms(ctx.handle, evb0, evb1, C.byref(band_ms))
+            bounds, costs = comm.rebalance_columns(bounds, band_ms.value, W)
+            balance_log.append({"ms": [round(c, 2) for c in costs], "bounds": list(bounds)})
+            tiles = [(bounds[r], bounds[r + 1]) for r in range(world)]
+        lib.b200pt_event_destroy(ctx.handle, evb0)
+        lib.b200pt_event_destroy(ctx.handle, evb1)
+
     if args.profile:
         # under ncu: only what the timed pass launches (3 warm-up frames + K frames), so that the launch list is the step's
         restart()
@@ -232,8 +258,11 @@ def run_ours(args, cfg, pt):
         return None
 
     # ---- 1. counting pass: the same frames as the timed pass, counting build ----
+    # (ReSTIR DI passes counted as single kernels: their phased form queues a superset of the shadow rays -- the reference's ray count is the
+    # metric's numerator -- and the queue-only counters then belong to FullPathTracer alone, as the trace stage time does)
     restart()
     ctx.counters_enable(True)
+    ctx.set_restir_phases(False)
     for _ in range(args.warmup):
         step()
     g.synchronize()
@@ -242,6 +271,7 @@ def run_ours(args, cfg, pt):
         step()
     g.synchronize()
     total = ctx.counters_read(True)
+    ctx.set_restir_phases(True)
     res = pt.structs.Int2(W, H)
     pt._capi.check(lib.b200pt_launch_CameraRays(ctx.handle, C.byref(g.render_data), res, None, None), "b200pt_launch_CameraRays")
     ctx.sync()
@@ -386,7 +416,7 @@ def run_ours(args, cfg, pt):
         batches = -(-spf // max(1, in_flight))
         launches_per_step = batches * lanes * (3 + per_bounce + nb * (2 + per_bounce) + 1)
     else:
-        launches_per_step = spf * (1 + lanes * ((1 + per_bounce) + nb * (2 + per_bounce)) + (3 if restir else 0))      # every path lane launches its own band
+        launches_per_step = spf * (1 + lanes * ((1 + per_bounce) + nb * (2 + per_bounce)) + (9 if restir else 0))      # every path lane launches its own band; phased ReSTIR DI: presampling + 5 (initial candidates: collect, trace, resolve, trace, visibility) + 3 (spatiotemporal: collect, trace, resolve) + CameraRays counted in the leading 1
     # DRAM bytes of the kernel per step and its time-weighted ncu counters (L2 throughput as a fraction of the L2 peak, hit rates, issue rate, lanes
     # per instruction), from the committed `ncu --set full` capture of the same command (profiles/traffic.json); null when not captured
     traffic, ncu_weighted = measured_traffic(args.workload, W, H, cfg["settings"].get("samples_per_frame", 1))
@@ -394,10 +424,11 @@ def run_ours(args, cfg, pt):
         "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "strong" if (world > 1 and sharding in ("tiles", "columns")) else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {**workload_config(cfg, args), "parallelism": "single GPU" if world == 1 else ((f"row-tile sharding x{world}" + (f" + {halo}-row ReSTIR reservoir halo exchange" if restir else "") + ", frame gathered once per output") if sharding == "tiles"
-                                                                      else (f"column-tile sharding x{world}, frame gathered once per output; e2e reads the whole accumulation buffer back (a column band is strided)") if sharding == "columns"
+                                                                      else (f"column-tile sharding x{world}" + (" (bands balanced on measured band times)" if balance_log else "") + ", frame gathered once per output; e2e reads the whole accumulation buffer back (a column band is strided)") if sharding == "columns"
                                                                       else f"sample-pass sharding x{world}, accumulation all-reduce") + ", scene+BVH replicated",
                    "l2": "inputs larger than L2: the per-step G-buffer round trip is 345 B/px = 715 MB at 1080p (L2 = 126 MB)",
-                   "bvh": bvh_info, "path_lanes": lanes, "samples_in_flight": in_flight if batched else 0, "rays_per_step_per_gpu": rays_per_step, "allreduce_ms": reduce_ms},
+                   "bvh": bvh_info, "path_lanes": lanes, "samples_in_flight": in_flight if batched else 0, "rays_per_step_per_gpu": rays_per_step, "allreduce_ms": reduce_ms,
+                   **({"column_balance": {"band_ms_before": balance_log[0]["ms"], "band_ms_last_measured": balance_log[-1]["ms"], "bounds": balance_log[-1]["bounds"]}} if balance_log else {})},
         "samples_per_px_per_s": (1 if (world > 1 and sharding in ("tiles", "columns")) else world) * spf * args.steps / (elapsed_ms * 1e-3),
         "gpu_launches": launches_per_step * args.steps,
         "clocks": clocks,
@@ -443,6 +474,7 @@ def main():
                     help="N > 1: sample-pass sharding (weak scaling, default for cornell), column tiles (strong scaling, default otherwise) or row tiles (strong scaling; always for ReSTIR DI)")
     ap.add_argument("--samples-per-frame", type=int, default=16, help="sample passes per step (= per render() call): the reference's samples_per_frame render setting")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-balance", action="store_true", help="N > 1, column tiles: keep the uniform bands instead of balancing them on measured band times")
     ap.add_argument("--profile", action="store_true", help="for ncu: run only 3 warm-up + K frames of the timed pass (no counting / stage / e2e / CPU passes), print no bench line")
     args = ap.parse_args()
 

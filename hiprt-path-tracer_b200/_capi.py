@@ -84,6 +84,7 @@ API_SYMBOLS = [
 COMM_API_SYMBOLS = [
     "b200pt_comm_tile", "b200pt_comm_restir_halo_rows", "b200pt_comm_get_unique_id", "b200pt_comm_create", "b200pt_comm_destroy", "b200pt_comm_rank", "b200pt_comm_world",
     "b200pt_comm_gather_tiles", "b200pt_comm_exchange_halo", "b200pt_comm_allreduce_sum", "b200pt_comm_allreduce_host_f64", "b200pt_comm_barrier",
+    "b200pt_comm_balanced_bounds", "b200pt_comm_set_column_bounds",
 ]
 HOST_API_SYMBOLS = [
     "b200pt_host_last_error", "b200pt_renderer_create", "b200pt_renderer_destroy", "b200pt_renderer_set_seed_schedule", "b200pt_renderer_set_rng_seed",

@@ -1,3 +1,5 @@
+#include <vector>
+#include <algorithm>
 // Multi-GPU plumbing behind the C ABI (include/b200pt_comm.h): tile plan, frame gather, ReSTIR DI halo exchange, accumulation
 // all-reduce over NCCL, bound at run time with dlopen so that libb200pt.so has no link-time dependency on libnccl.
 // No counterpart in the reference (one device, src/main.cpp:57); SURVEY.md section 8(e).
@@ -97,6 +99,19 @@ struct b200pt_comm
     unsigned char* staging = nullptr;       // column-band gathers: the bands laid out contiguously, band r at its prefix offset
     size_t staging_bytes = 0;
     double* d_scalars = nullptr;            // b200pt_comm_allreduce_host_f64
+    std::vector<int> column_bounds;         // b200pt_comm_set_column_bounds: world + 1 entries, empty = the uniform plan of b200pt_comm_tile
+
+    // column band of rank r of a `width`-pixel image: the bounds set by the caller if they fit this width, else the uniform plan
+    void columns_of(int width, int r, int& begin, int& end) const
+    {
+        if ((int)column_bounds.size() == world + 1 && column_bounds.back() == width)
+        {
+            begin = column_bounds[r];
+            end = column_bounds[r + 1];
+        }
+        else
+            band_of(width, world, r, begin, end);
+    }
 };
 
 extern "C" {
@@ -111,6 +126,62 @@ int b200pt_comm_tile(int sharding, int width, int height, int world, int rank, b
     else
         band_of(width, world, rank, t.x0, t.x1);
     *out_tile = t;
+    return B200PT_SUCCESS;
+}
+
+int b200pt_comm_balanced_bounds(const int* bounds, const double* cost, int world, int extent, int align, int* out_bounds)
+{
+    REQUIRE(bounds != nullptr && cost != nullptr && out_bounds != nullptr && world >= 1 && extent >= 0 && align >= 1);
+    REQUIRE(bounds[0] == 0 && bounds[world] == extent);
+    double total = 0.0;
+    for (int r = 0; r < world; r++)
+    {
+        REQUIRE(bounds[r + 1] >= bounds[r] && cost[r] >= 0.0);
+        total += bounds[r + 1] > bounds[r] ? cost[r] : 0.0;
+    }
+    out_bounds[0] = 0;
+    out_bounds[world] = extent;
+    if (!(total > 0.0))
+    {
+        for (int r = 1; r < world; r++)
+            out_bounds[r] = bounds[r];
+        return B200PT_SUCCESS;
+    }
+    // cost is taken as uniform inside each old band: the cumulative cost is piecewise linear in the pixel coordinate; boundary k goes where it
+    // reaches k / world of the total, rounded to a multiple of `align`, kept monotonic and at least one `align` block wide while blocks last
+    int band = 0;
+    double before = 0.0;       // cumulative cost at bounds[band]
+    for (int k = 1; k < world; k++)
+    {
+        const double target = total * (double)k / (double)world;
+        while (band < world - 1 && (bounds[band + 1] == bounds[band] || before + cost[band] < target))
+        {
+            before += bounds[band + 1] > bounds[band] ? cost[band] : 0.0;
+            band++;
+        }
+        const double width = (double)(bounds[band + 1] - bounds[band]);
+        const double x = cost[band] > 0.0 ? bounds[band] + width * std::min(1.0, std::max(0.0, (target - before) / cost[band])) : (double)bounds[band];
+        long long rounded = (long long)((x + 0.5 * align) / align) * align;
+        const long long lowest = std::min<long long>(extent, (long long)out_bounds[k - 1] + align);
+        const long long highest = std::max<long long>(lowest, (long long)extent - (long long)(world - k) * align);
+        rounded = std::min(std::max(rounded, lowest), highest);
+        out_bounds[k] = (int)std::min<long long>(rounded, extent);
+    }
+    return B200PT_SUCCESS;
+}
+
+int b200pt_comm_set_column_bounds(b200pt_comm* comm, const int* bounds)
+{
+    REQUIRE(comm != nullptr);
+    if (bounds == nullptr)
+    {
+        comm->column_bounds.clear();
+        return B200PT_SUCCESS;
+    }
+    REQUIRE(bounds[0] == 0);
+    for (int r = 0; r < comm->world; r++)
+        REQUIRE(bounds[r + 1] >= bounds[r]);
+    comm->column_bounds.assign(bounds, bounds + comm->world + 1);
     return B200PT_SUCCESS;
 }
 
@@ -226,7 +297,7 @@ int b200pt_comm_gather_tiles(b200pt_comm* comm, void* d_image, int width, int he
         comm->staging_bytes = total;
     }
     int x0, x1;
-    band_of(width, comm->world, comm->rank, x0, x1);
+    comm->columns_of(width, comm->rank, x0, x1);
     if (x1 > x0)
         CUDA_TRY(cudaMemcpy2DAsync(comm->staging + (size_t)x0 * bytes_per_pixel * height, (size_t)(x1 - x0) * bytes_per_pixel, image + (size_t)x0 * bytes_per_pixel, row_bytes,
                                    (size_t)(x1 - x0) * bytes_per_pixel, (size_t)height, cudaMemcpyDeviceToDevice, st));
@@ -234,7 +305,7 @@ int b200pt_comm_gather_tiles(b200pt_comm* comm, void* d_image, int width, int he
     for (int r = 0; r < comm->world; r++)
     {
         int a, b;
-        band_of(width, comm->world, r, a, b);
+        comm->columns_of(width, r, a, b);
         if (b > a)
         {
             unsigned char* band = comm->staging + (size_t)a * bytes_per_pixel * height;
@@ -250,7 +321,7 @@ int b200pt_comm_gather_tiles(b200pt_comm* comm, void* d_image, int width, int he
     for (int r = 0; r < comm->world; r++)
     {
         int a, b;
-        band_of(width, comm->world, r, a, b);
+        comm->columns_of(width, r, a, b);
         if (b > a && r != comm->rank)
             CUDA_TRY(cudaMemcpy2DAsync(image + (size_t)a * bytes_per_pixel, row_bytes, comm->staging + (size_t)a * bytes_per_pixel * height, (size_t)(b - a) * bytes_per_pixel,
                                        (size_t)(b - a) * bytes_per_pixel, (size_t)height, cudaMemcpyDeviceToDevice, st));

@@ -604,12 +604,14 @@ int b200pt_launch_ReSTIR_DI_SpatiotemporalReuse(b200pt_ctx* ctx, const HIPRTRend
 
 int b200pt_launch_ReSTIR_DI_TemporalReuse(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream)
 {
-    LAUNCH_RESTIR_PIXEL_KERNEL(launch_ReSTIR_DI_TemporalReuse)
+    const pt::RestirScratch* scratch = ctx != nullptr && res.x > 0 && res.y > 0 ? ensure_restir_scratch(ctx, restir_tile_pixels(tile, res)) : nullptr;
+    LAUNCH_RESTIR_PIXEL_KERNEL(launch_ReSTIR_DI_TemporalReuse, , scratch)
 }
 
 int b200pt_launch_ReSTIR_DI_SpatialReuse(b200pt_ctx* ctx, const HIPRTRenderData* render_data, b200pt_int2 res, const b200pt_tile* tile, b200pt_stream stream)
 {
-    LAUNCH_RESTIR_PIXEL_KERNEL(launch_ReSTIR_DI_SpatialReuse)
+    const pt::RestirScratch* scratch = ctx != nullptr && res.x > 0 && res.y > 0 ? ensure_restir_scratch(ctx, restir_tile_pixels(tile, res)) : nullptr;
+    LAUNCH_RESTIR_PIXEL_KERNEL(launch_ReSTIR_DI_SpatialReuse, , scratch)
 }
 
 int b200pt_trace_closest(b200pt_ctx* ctx, b200pt_bvh* bvh, const float* d_rays, const int* d_last_prim, long long n, int* d_out_prim, float* d_out_t, float* d_out_uv, b200pt_stream stream)

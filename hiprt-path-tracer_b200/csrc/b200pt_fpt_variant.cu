@@ -396,8 +396,13 @@ __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_ReSTIR_DI_Spatiotemporal
 }
 
 // Phased passes (restir_di_kernels.cuh): COLLECT / RESOLVE kernels around launches of the ray-queue traversal kernel
-#define PT_RESTIR_PHASE_KERNEL(NAME, CALL)                                                                                                       \
-    __global__ void __launch_bounds__(64) PT_VARIANT_NAME(NAME)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ RestirScratch scratch) \
+// Registers of the COLLECT kernels are left uncapped (128-152): capped at 96 (10 blocks per SM, as the shade phases of b200pt_phase_variant.cu
+// are) the fused pass's COLLECT spilled 160 B more and C4 went 645 -> 639 Mrays/s (B200, gpurun call 14)
+#ifndef PT_RESTIR_COLLECT_BLOCKS_PER_SM
+#define PT_RESTIR_COLLECT_BLOCKS_PER_SM 1
+#endif
+#define PT_RESTIR_PHASE_KERNEL(NAME, CALL, MIN_BLOCKS)                                                                                           \
+    __global__ void __launch_bounds__(64, MIN_BLOCKS) PT_VARIANT_NAME(NAME)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ RestirScratch scratch) \
     {                                                                                                                                            \
         const uint32_t x = tile.x0 + blockIdx.x * blockDim.x + threadIdx.x;                                                                      \
         const uint32_t y = tile.y0 + blockIdx.y * blockDim.y + threadIdx.y;                                                                      \
@@ -410,11 +415,15 @@ __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_ReSTIR_DI_Spatiotemporal
     }
 #define PT_IC_COLLECT restir_initial_candidates_pixel<PT_GGX, RESTIR_COLLECT>
 #define PT_IC_RESOLVE restir_initial_candidates_pixel<PT_GGX, RESTIR_RESOLVE>
-PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_InitialCandidates_collect, PT_IC_COLLECT)
-PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_InitialCandidates_resolve, PT_IC_RESOLVE)
-PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_InitialCandidates_visibility, restir_initial_candidates_visibility)
-PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_SpatiotemporalReuse_collect, restir_spatiotemporal_pixel<RESTIR_COLLECT>)
-PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_SpatiotemporalReuse_resolve, restir_spatiotemporal_pixel<RESTIR_RESOLVE>)
+PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_InitialCandidates_collect, PT_IC_COLLECT, PT_RESTIR_COLLECT_BLOCKS_PER_SM)
+PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_InitialCandidates_resolve, PT_IC_RESOLVE, 1)
+PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_InitialCandidates_visibility, restir_initial_candidates_visibility, 1)
+PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_SpatiotemporalReuse_collect, restir_spatiotemporal_pixel<RESTIR_COLLECT>, PT_RESTIR_COLLECT_BLOCKS_PER_SM)
+PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_SpatiotemporalReuse_resolve, restir_spatiotemporal_pixel<RESTIR_RESOLVE>, 1)
+PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_TemporalReuse_collect, restir_temporal_pixel<RESTIR_COLLECT>, PT_RESTIR_COLLECT_BLOCKS_PER_SM)
+PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_TemporalReuse_resolve, restir_temporal_pixel<RESTIR_RESOLVE>, 1)
+PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_SpatialReuse_collect, restir_spatial_pixel<RESTIR_COLLECT>, PT_RESTIR_COLLECT_BLOCKS_PER_SM)
+PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_SpatialReuse_resolve, restir_spatial_pixel<RESTIR_RESOLVE>, 1)
 
 __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_ReSTIR_DI_TemporalReuse)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile)
 {
@@ -506,17 +515,41 @@ cudaError_t PT_VARIANT_NAME(launch_ReSTIR_DI_SpatiotemporalReuse)(const HIPRTRen
     return cudaGetLastError();
 }
 
-cudaError_t PT_VARIANT_NAME(launch_ReSTIR_DI_TemporalReuse)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream)
+cudaError_t PT_VARIANT_NAME(launch_ReSTIR_DI_TemporalReuse)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const RestirScratch* scratch)
 {
     dim3 grid((tile.x1 - tile.x0 + 7) / 8, (tile.y1 - tile.y0 + 7) / 8, 1);
-    PT_VARIANT_NAME(k_ReSTIR_DI_TemporalReuse)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile);
+    if (!restir_phased(rd, tile, scratch))
+    {
+        PT_VARIANT_NAME(k_ReSTIR_DI_TemporalReuse)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile);
+        return cudaGetLastError();
+    }
+    cudaError_t e = cudaMemsetAsync(scratch->counts, 0, 4 * sizeof(uint32_t), stream);
+    if (e != cudaSuccess)
+        return e;
+    PT_VARIANT_NAME(k_ReSTIR_DI_TemporalReuse_collect)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile, *scratch);
+    if ((e = restir_trace(rd, scratch, true, stream)) != cudaSuccess)
+        return e;
+    PT_VARIANT_NAME(k_ReSTIR_DI_TemporalReuse_resolve)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile, *scratch);
     return cudaGetLastError();
 }
 
-cudaError_t PT_VARIANT_NAME(launch_ReSTIR_DI_SpatialReuse)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream)
+cudaError_t PT_VARIANT_NAME(launch_ReSTIR_DI_SpatialReuse)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const RestirScratch* scratch)
 {
     dim3 grid((tile.x1 - tile.x0 + 7) / 8, (tile.y1 - tile.y0 + 7) / 8, 1);
-    PT_VARIANT_NAME(k_ReSTIR_DI_SpatialReuse)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile);
+    const SpatialPassSettings& sp = rd->render_settings.restir_di_settings.spatial_pass;
+    const int neighbors = sp.do_disocclusion_reuse_boost && sp.disocclusion_reuse_count > sp.reuse_neighbor_count ? sp.disocclusion_reuse_count : sp.reuse_neighbor_count;
+    if (!restir_phased(rd, tile, scratch) || neighbors > kRestirMaxNeighbors)
+    {
+        PT_VARIANT_NAME(k_ReSTIR_DI_SpatialReuse)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile);
+        return cudaGetLastError();
+    }
+    cudaError_t e = cudaMemsetAsync(scratch->counts, 0, 4 * sizeof(uint32_t), stream);
+    if (e != cudaSuccess)
+        return e;
+    PT_VARIANT_NAME(k_ReSTIR_DI_SpatialReuse_collect)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile, *scratch);
+    if ((e = restir_trace(rd, scratch, true, stream)) != cudaSuccess)
+        return e;
+    PT_VARIANT_NAME(k_ReSTIR_DI_SpatialReuse_resolve)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile, *scratch);
     return cudaGetLastError();
 }
 #endif

@@ -332,8 +332,8 @@ PT_FOR_EACH_VARIANT(PT_DECLARE_VARIANT)
     cudaError_t PT_VARIANT_NAME_OF(launch_ReSTIR_DI_LightsPresampling, LSS, ESS, LATER, GGX)(const LightPresamplingParameters* p, cudaStream_t stream);              \
     cudaError_t PT_VARIANT_NAME_OF(launch_ReSTIR_DI_InitialCandidates, LSS, ESS, LATER, GGX)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const RestirScratch* scratch);    \
     cudaError_t PT_VARIANT_NAME_OF(launch_ReSTIR_DI_SpatiotemporalReuse, LSS, ESS, LATER, GGX)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const RestirScratch* scratch); \
-    cudaError_t PT_VARIANT_NAME_OF(launch_ReSTIR_DI_TemporalReuse, LSS, ESS, LATER, GGX)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream);        \
-    cudaError_t PT_VARIANT_NAME_OF(launch_ReSTIR_DI_SpatialReuse, LSS, ESS, LATER, GGX)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream);
+    cudaError_t PT_VARIANT_NAME_OF(launch_ReSTIR_DI_TemporalReuse, LSS, ESS, LATER, GGX)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const RestirScratch* scratch);        \
+    cudaError_t PT_VARIANT_NAME_OF(launch_ReSTIR_DI_SpatialReuse, LSS, ESS, LATER, GGX)(const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const RestirScratch* scratch);
 #define PT_DECLARE_RESTIR_IF_5(LSS, ESS, LATER, GGX) PT_DECLARE_RESTIR_##LSS(LSS, ESS, LATER, GGX)
 #define PT_DECLARE_RESTIR_3(LSS, ESS, LATER, GGX)
 #define PT_DECLARE_RESTIR_4(LSS, ESS, LATER, GGX)
@@ -366,16 +366,16 @@ cudaError_t PT_SUFFIXED(launch_ReSTIR_DI_SpatiotemporalReuse)(const VariantOptio
     return cudaErrorInvalidDeviceFunction;
 }
 
-cudaError_t PT_SUFFIXED(launch_ReSTIR_DI_TemporalReuse)(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream)
+cudaError_t PT_SUFFIXED(launch_ReSTIR_DI_TemporalReuse)(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const RestirScratch* scratch)
 {
-#define PT_CASE_TEMPORAL(LSS, ESS, LATER, GGX) PT_CASE_RESTIR_##LSS(PT_VARIANT_NAME_OF(launch_ReSTIR_DI_TemporalReuse, LSS, ESS, LATER, GGX)(rd, res, tile, stream), LSS, ESS, LATER, GGX)
+#define PT_CASE_TEMPORAL(LSS, ESS, LATER, GGX) PT_CASE_RESTIR_##LSS(PT_VARIANT_NAME_OF(launch_ReSTIR_DI_TemporalReuse, LSS, ESS, LATER, GGX)(rd, res, tile, stream, scratch), LSS, ESS, LATER, GGX)
     PT_FOR_EACH_VARIANT(PT_CASE_TEMPORAL)
     return cudaErrorInvalidDeviceFunction;
 }
 
-cudaError_t PT_SUFFIXED(launch_ReSTIR_DI_SpatialReuse)(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream)
+cudaError_t PT_SUFFIXED(launch_ReSTIR_DI_SpatialReuse)(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const RestirScratch* scratch)
 {
-#define PT_CASE_SPATIAL(LSS, ESS, LATER, GGX) PT_CASE_RESTIR_##LSS(PT_VARIANT_NAME_OF(launch_ReSTIR_DI_SpatialReuse, LSS, ESS, LATER, GGX)(rd, res, tile, stream), LSS, ESS, LATER, GGX)
+#define PT_CASE_SPATIAL(LSS, ESS, LATER, GGX) PT_CASE_RESTIR_##LSS(PT_VARIANT_NAME_OF(launch_ReSTIR_DI_SpatialReuse, LSS, ESS, LATER, GGX)(rd, res, tile, stream, scratch), LSS, ESS, LATER, GGX)
     PT_FOR_EACH_VARIANT(PT_CASE_SPATIAL)
     return cudaErrorInvalidDeviceFunction;
 }

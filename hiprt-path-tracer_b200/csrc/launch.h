@@ -115,6 +115,7 @@ struct WavefrontProfile
 //   InitialCandidates:     site 0 = the BSDF candidate's ray (closest hit), site 1 = visibility of the chosen candidate
 //   SpatiotemporalReuse:   site 0 = temporal neighbour's sample seen from the pixel, site 1 = the pixel's sample seen from the temporal
 //                          neighbour's surface, sites 2 + 2 i / 3 + 2 i = the same pair for spatial neighbour i
+//   TemporalReuse:         sites 0 and 1 as above;   SpatialReuse: sites 2 + 2 i / 3 + 2 i as above, site 0 = the pixel's own input sample
 constexpr int kRestirMaxNeighbors = 5;                       // spatial neighbours per pixel the phased pass has sites for (more: unphased kernel)
 constexpr int kRestirSites = 2 + 2 * kRestirMaxNeighbors;
 struct RestirScratch
@@ -153,8 +154,8 @@ struct RayQueueView
     cudaError_t launch_ReSTIR_DI_LightsPresampling##S(const VariantOptions& opt, const LightPresamplingParameters* p, cudaStream_t stream);            \
     cudaError_t launch_ReSTIR_DI_InitialCandidates##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const RestirScratch* scratch); \
     cudaError_t launch_ReSTIR_DI_SpatiotemporalReuse##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const RestirScratch* scratch); \
-    cudaError_t launch_ReSTIR_DI_TemporalReuse##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream); \
-    cudaError_t launch_ReSTIR_DI_SpatialReuse##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream); \
+    cudaError_t launch_ReSTIR_DI_TemporalReuse##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const RestirScratch* scratch); \
+    cudaError_t launch_ReSTIR_DI_SpatialReuse##S(const VariantOptions& opt, const HIPRTRenderData* rd, int2 res, Tile tile, cudaStream_t stream, const RestirScratch* scratch); \
     cudaError_t launch_trace_queue##S(const void* bvh_device_handle, const RayQueueView& q, bool any_hit, unsigned blocks, TraversalCounters* counters, cudaStream_t stream); \
     cudaError_t launch_bin_rays##S(const void* bvh_device_handle, RayQueueView& q, uint32_t* hist, uint32_t* keys, uint32_t* out_ids, int bits, unsigned sm_count, cudaStream_t stream); \
     cudaError_t launch_trace_queue_pair##S(const void* bvh_device_handle, const RayQueueView& q_any, const RayQueueView& q_closest, unsigned blocks, TraversalCounters* counters, cudaStream_t stream); \

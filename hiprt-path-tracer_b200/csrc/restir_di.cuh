@@ -501,8 +501,10 @@ struct TemporalPairwiseDefensiveMISWeight
 {
     float mc = 0.0f;
 
+    template <int MODE = RESTIR_INLINE>
     PT_DEV float get(const HIPRTRenderData& rd, const ReSTIRDIReservoir& temporal_neighbor_reservoir, const ReSTIRDIReservoir& initial_candidates_reservoir,
-                     const ReSTIRSurface& temporal_neighbor_surface, float neighbor_sample_target_function_at_center, bool resample_initial_candidates, Rng& rng)
+                     const ReSTIRSurface& temporal_neighbor_surface, float neighbor_sample_target_function_at_center, bool resample_initial_candidates, Rng& rng,
+                     const RestirSites sites = RestirSites(), int site = 0)
     {
         const bool confidence = rd.render_settings.restir_di_settings.use_confidence_weights;
         if (!resample_initial_candidates)
@@ -519,7 +521,7 @@ struct TemporalPairwiseDefensiveMISWeight
             if (confidence)
                 mi *= neighbors_confidence_sum / (neighbors_confidence_sum + center_reservoir_M);
 
-            float at_neighbor = restir_evaluate_target_function<true>(rd, initial_candidates_reservoir.sample, temporal_neighbor_surface, rng);
+            float at_neighbor = restir_evaluate_target_function<true, MODE>(rd, initial_candidates_reservoir.sample, temporal_neighbor_surface, rng, sites, site);
             float at_center = initial_candidates_reservoir.sample.target_function;
             float nume_mc = at_center * center_reservoir_M;
             float denom_mc = at_neighbor * neighbors_confidence_sum + at_center * center_reservoir_M;

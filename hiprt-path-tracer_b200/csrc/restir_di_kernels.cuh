@@ -589,10 +589,19 @@ PT_DEV void restir_spatiotemporal_pixel(const HIPRTRenderData& rd, int2 res, uin
 // ---- ReSTIR_DI_TemporalReuse (TemporalReuse.h:48-306): the non-fused configuration's temporal pass ---------------------------------
 // Combines last frame's reservoir at the back-projected pixel with this frame's initial candidates (pairwise-defensive MIS,
 // bias correction with visibility). Pixels without a usable temporal neighbour copy their initial candidates through.
-PT_DEV void restir_temporal_pixel(const HIPRTRenderData& rd, int2 res, uint32_t x, uint32_t y)
+// Phased (MODE, restir_di.cuh): COLLECT stores nothing but the site values, the queued rays and the pixel's status (0 nothing to do,
+// 1 resample, 2 copy the initial candidates through); RESOLVE repeats the neighbour search (same draws) and writes the output.
+// Sites: 0 = the temporal neighbour's sample seen from the pixel, 1 = the pixel's sample seen from the temporal neighbour's surface.
+template <int MODE = RESTIR_INLINE>
+PT_DEV void restir_temporal_pixel(const HIPRTRenderData& rd, int2 res, uint32_t x, uint32_t y, const RestirSites sites = RestirSites())
 {
     const uint32_t center_pixel_index = x + y * res.x;
+    if (MODE == RESTIR_COLLECT)
+        sites.scratch->status[sites.pixel] = 0u;
     if (!rd.aux_buffers.pixel_active[center_pixel_index] || !rd.g_buffer.camera_ray_hit[center_pixel_index])
+        return;
+    const uint32_t status = MODE == RESTIR_RESOLVE ? sites.scratch->status[sites.pixel] : 0u;
+    if (MODE == RESTIR_RESOLVE && status == 0u)
         return;
 
     const ReSTIRDISettings& rs = rd.render_settings.restir_di_settings;
@@ -602,32 +611,39 @@ PT_DEV void restir_temporal_pixel(const HIPRTRenderData& rd, int2 res, uint32_t 
         store_reservoir(rs.temporal_pass.input_reservoirs + center_pixel_index, empty_reservoir());
 
     ReSTIRSurface center;
-    get_pixel_surface(rd, center_pixel_index, false, center);
-    if (material_is_emissive(center.material))
+    get_pixel_surface<MODE != RESTIR_RESOLVE>(rd, center_pixel_index, false, center);
+    if (MODE != RESTIR_RESOLVE && material_is_emissive(center.material))
         return;
+    if (MODE == RESTIR_COLLECT)
+        sites.scratch->status[sites.pixel] = 2u;
 
     const ReSTIRDIReservoir initial_candidates_reservoir = load_reservoir(rs.initial_candidates.output_reservoirs + center_pixel_index);
     ReSTIRDIReservoir* output = rs.temporal_pass.output_reservoirs + center_pixel_index;
 
     int temporal_neighbor_pixel_index = restir_find_temporal_neighbor_index(rd, ld3_rw(rd.g_buffer.first_hits, center_pixel_index), center.shading_normal, res, center_pixel_index, rng).x;
-    if (temporal_neighbor_pixel_index == -1 || rd.render_settings.freeze_random)
+    if (temporal_neighbor_pixel_index == -1 || rd.render_settings.freeze_random || (MODE == RESTIR_RESOLVE && status == 2u))
     {
-        store_reservoir(output, initial_candidates_reservoir);       // :88-97 (disocclusion, or frozen random: same samples every frame)
+        if (MODE != RESTIR_COLLECT)
+            store_reservoir(output, initial_candidates_reservoir);       // :88-97 (disocclusion, or frozen random: same samples every frame); RESOLVE: every copy-through case
         return;
     }
     const ReSTIRDIReservoir temporal_neighbor_reservoir = load_reservoir(rs.temporal_pass.input_reservoirs + temporal_neighbor_pixel_index);
     if (temporal_neighbor_reservoir.M == 0)
     {
-        store_reservoir(output, initial_candidates_reservoir);       // :100-108
+        if (MODE != RESTIR_COLLECT)
+            store_reservoir(output, initial_candidates_reservoir);       // :100-108
         return;
     }
     ReSTIRSurface temporal_neighbor_surface;
-    get_pixel_surface(rd, temporal_neighbor_pixel_index, use_prev_frame_g_buffer(rd), temporal_neighbor_surface);
-    if (material_is_emissive(temporal_neighbor_surface.material))
+    get_pixel_surface<MODE != RESTIR_RESOLVE>(rd, temporal_neighbor_pixel_index, use_prev_frame_g_buffer(rd), temporal_neighbor_surface);
+    if (MODE != RESTIR_RESOLVE && material_is_emissive(temporal_neighbor_surface.material))
     {
-        store_reservoir(output, initial_candidates_reservoir);       // :113-120
+        if (MODE != RESTIR_COLLECT)
+            store_reservoir(output, initial_candidates_reservoir);       // :113-120
         return;
     }
+    if (MODE == RESTIR_COLLECT)
+        sites.scratch->status[sites.pixel] = 1u;
 
     ReSTIRDIReservoir out = empty_reservoir();
     TemporalPairwiseDefensiveMISWeight mis_weight_function;
@@ -636,7 +652,7 @@ PT_DEV void restir_temporal_pixel(const HIPRTRenderData& rd, int2 res, uint32_t 
     {
         float target_function_at_center = 0.0f;
         if (temporal_neighbor_reservoir.UCW > 0.0f)
-            target_function_at_center = restir_evaluate_target_function<true>(rd, temporal_neighbor_reservoir.sample, center, rng);
+            target_function_at_center = restir_evaluate_target_function<true, MODE>(rd, temporal_neighbor_reservoir.sample, center, rng, sites, 0);
 
         float jacobian_determinant = 1.0f;
         if (target_function_at_center > 0.0f && temporal_neighbor_reservoir.UCW > 0.0f && !(temporal_neighbor_reservoir.sample.flags & RESTIR_DI_FLAGS_ENVMAP_SAMPLE))
@@ -645,7 +661,9 @@ PT_DEV void restir_temporal_pixel(const HIPRTRenderData& rd, int2 res, uint32_t 
             if (jacobian_determinant == -1.0f)
                 jacobian_determinant = 0.0f;
         }
-        float w = mis_weight_function.get(rd, temporal_neighbor_reservoir, initial_candidates_reservoir, temporal_neighbor_surface, target_function_at_center, false, rng);
+        float w = mis_weight_function.template get<MODE>(rd, temporal_neighbor_reservoir, initial_candidates_reservoir, temporal_neighbor_surface, target_function_at_center, false, rng, sites, 1);
+        if (MODE == RESTIR_COLLECT)
+            return;
         if (reservoir_combine_with(out, temporal_neighbor_reservoir, w, target_function_at_center, jacobian_determinant, rng))
             out.sample.flags |= RESTIR_DI_FLAGS_UNOCCLUDED;           // ReSTIR_DI_BiasCorrectionUseVisibility == TRUE
     }
@@ -666,10 +684,17 @@ PT_DEV void restir_temporal_pixel(const HIPRTRenderData& rd, int2 res, uint32_t 
 // ---- ReSTIR_DI_SpatialReuse (SpatialReuse.h:64-348): a spatial pass on its own -- the non-fused configuration, and the passes
 // 1..number_of_passes-1 that follow the fused pass on the GPU (ReSTIRDIRenderPass.cpp:492-501). Neighbours on the rotated
 // Hammersley disk around the pixel ITSELF, read from this frame's G-buffer; the centre reservoir is the pass input at the pixel.
-PT_DEV void restir_spatial_pixel(const HIPRTRenderData& rd, int2 res, uint32_t x, uint32_t y)
+// Phased (MODE): as restir_spatiotemporal_pixel; sites 2 + 2 i / 3 + 2 i for spatial neighbour i, site 0 = the end-of-pass visibility ray
+// of the pixel's own input sample when it arrives without the UNOCCLUDED flag.
+template <int MODE = RESTIR_INLINE>
+PT_DEV void restir_spatial_pixel(const HIPRTRenderData& rd, int2 res, uint32_t x, uint32_t y, const RestirSites sites = RestirSites())
 {
     const uint32_t center_pixel_index = x + y * res.x;
+    if (MODE == RESTIR_COLLECT)
+        sites.scratch->status[sites.pixel] = 0u;
     if (!rd.aux_buffers.pixel_active[center_pixel_index] || !rd.g_buffer.camera_ray_hit[center_pixel_index])
+        return;
+    if (MODE == RESTIR_RESOLVE && sites.scratch->status[sites.pixel] == 0u)
         return;
 
     const ReSTIRDISettings& rs = rd.render_settings.restir_di_settings;
@@ -678,9 +703,11 @@ PT_DEV void restir_spatial_pixel(const HIPRTRenderData& rd, int2 res, uint32_t x
     const int2 center_pixel_coords = make_int2(x, y);
 
     ReSTIRSurface center;
-    get_pixel_surface(rd, center_pixel_index, false, center);
-    if (material_is_emissive(center.material))
+    get_pixel_surface<MODE != RESTIR_RESOLVE>(rd, center_pixel_index, false, center);
+    if (MODE != RESTIR_RESOLVE && material_is_emissive(center.material))
         return;
+    if (MODE == RESTIR_COLLECT)
+        sites.scratch->status[sites.pixel] = 1u;
 
     float rotation_theta = rs.spatial_pass.do_neighbor_rotation ? kTwoPi * rng() : 0.0f;
     float2 cos_sin_theta_rotation = make_float2(cosf(rotation_theta), sinf(rotation_theta));
@@ -709,6 +736,7 @@ PT_DEV void restir_spatial_pixel(const HIPRTRenderData& rd, int2 res, uint32_t x
     mis_weight_function.neighbor_surface_of_current_frame = true;
     const bool update_mc = center_pixel_reservoir.M > 0 && center_pixel_reservoir.UCW > 0.0f;
 
+    int final_visibility_site = -1;       // phased: the site whose ray is the end-of-pass visibility ray of the sample `out` holds
     int start_index = valid_neighbors_M_sum == 0 ? reused_neighbors_count : 0;
     for (int neighbor_index = start_index; neighbor_index < reused_neighbors_count + 1; neighbor_index++)
     {
@@ -733,9 +761,17 @@ PT_DEV void restir_spatial_pixel(const HIPRTRenderData& rd, int2 res, uint32_t x
             if (canonical)
                 target_function_at_center = neighbor_reservoir.sample.target_function;
             else if (do_neighbor_target_function_visibility)
-                target_function_at_center = restir_evaluate_target_function<true>(rd, neighbor_reservoir.sample, center, rng);
+                target_function_at_center = restir_evaluate_target_function<true, MODE>(rd, neighbor_reservoir.sample, center, rng, sites, 2 + 2 * neighbor_index);
             else
-                target_function_at_center = restir_evaluate_target_function<false>(rd, neighbor_reservoir.sample, center, rng);
+                target_function_at_center = restir_evaluate_target_function<false, MODE>(rd, neighbor_reservoir.sample, center, rng, sites, 2 + 2 * neighbor_index);
+            if (MODE == RESTIR_COLLECT && (canonical ? !(neighbor_reservoir.sample.flags & RESTIR_DI_FLAGS_UNOCCLUDED) : !do_neighbor_target_function_visibility))
+            {
+                // if this sample is the one the pass keeps, the end-of-pass visibility reuse traces it from the pixel: that ray takes this site
+                float distance_to_light;
+                float3 sample_direction;
+                restir_visibility_reuse_ray(rd, neighbor_reservoir.sample, center.shading_point, sample_direction, distance_to_light);
+                sites.emit_any_hit(canonical ? 0 : 2 + 2 * neighbor_index, center.shading_point, sample_direction, distance_to_light, center.last_hit_primitive_index);
+            }
         }
 
         float jacobian_determinant = 1.0f;
@@ -743,31 +779,46 @@ PT_DEV void restir_spatial_pixel(const HIPRTRenderData& rd, int2 res, uint32_t x
         {
             // Utils.h:199-202: the neighbour's first hit WITHOUT the normal offset
             jacobian_determinant = restir_jacobian_reconnection_shift(rd, neighbor_reservoir, center.shading_point, ld3_rw(rd.g_buffer.first_hits, neighbor_pixel_index));
-            if (jacobian_determinant == -1.0f)
+            if (jacobian_determinant == -1.0f && MODE != RESTIR_COLLECT)     // COLLECT saw the target function before visibility: the neighbour may still be resampled
             {
                 out.M += neighbor_reservoir.M;
                 continue;
             }
         }
 
-        float mis_weight = mis_weight_function.get(rd, neighbor_reservoir, center_pixel_reservoir, target_function_at_center, neighbor_pixel_index, valid_neighbors_count, valid_neighbors_M_sum, update_mc, canonical, rng);
+        float mis_weight = mis_weight_function.template get<MODE>(rd, neighbor_reservoir, center_pixel_reservoir, target_function_at_center, neighbor_pixel_index, valid_neighbors_count, valid_neighbors_M_sum,
+                                                                  update_mc, canonical, rng, sites, 3 + 2 * neighbor_index);
 
-        if (reservoir_combine_with(out, neighbor_reservoir, mis_weight, target_function_at_center, jacobian_determinant, rng))
+        if (MODE != RESTIR_COLLECT && reservoir_combine_with(out, neighbor_reservoir, mis_weight, target_function_at_center, jacobian_determinant, rng))
         {
+            final_visibility_site = -1;
             if (do_neighbor_target_function_visibility)
                 out.sample.flags |= RESTIR_DI_FLAGS_UNOCCLUDED;
             else if (canonical)
+            {
                 out.sample.flags |= neighbor_reservoir.sample.flags & RESTIR_DI_FLAGS_UNOCCLUDED;
+                final_visibility_site = 0;
+            }
             else
+            {
                 out.sample.flags &= ~RESTIR_DI_FLAGS_UNOCCLUDED;
+                final_visibility_site = 2 + 2 * neighbor_index;
+            }
         }
     }
+    if (MODE == RESTIR_COLLECT)
+        return;
 
     reservoir_end_with_normalization(out, 1.0f, 1.0f);
 
     // end-of-pass visibility reuse (:262-336)
     if (rs.temporal_pass.do_temporal_reuse_pass || rs.spatial_pass.number_of_passes - 1 != rs.spatial_pass.spatial_pass_index)
-        restir_visibility_reuse(rd, out, center.shading_point, center.last_hit_primitive_index, rng);
+    {
+        if (MODE == RESTIR_RESOLVE && final_visibility_site >= 0)
+            restir_visibility_reuse<RESTIR_RESOLVE>(rd, out, center.shading_point, center.last_hit_primitive_index, rng, sites, final_visibility_site);
+        else
+            restir_visibility_reuse(rd, out, center.shading_point, center.last_hit_primitive_index, rng);     // RESOLVE: a sample whose ray was not queued (none by construction)
+    }
 
     if (rs.m_cap > 0)
         out.M = mini(out.M, rs.m_cap);

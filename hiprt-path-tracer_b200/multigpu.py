@@ -197,3 +197,30 @@ class Comm:
     def barrier(self):
         self._capi.check(self.lib.b200pt_comm_barrier(self.handle), "b200pt_comm_barrier")
 
+    @staticmethod
+    def balanced_bounds(lib, bounds, costs, extent, align=8):
+        """b200pt_comm_balanced_bounds: new band boundaries at which the bands would cost the same (cost uniform inside each old band)."""
+        import ctypes as C
+        from . import _capi
+        world = len(costs)
+        assert len(bounds) == world + 1
+        out = (C.c_int * (world + 1))()
+        _capi.check(lib.b200pt_comm_balanced_bounds((C.c_int * (world + 1))(*[int(b) for b in bounds]), (C.c_double * world)(*[float(c) for c in costs]), C.c_int(world),
+                                                    C.c_int(extent), C.c_int(align), out), "b200pt_comm_balanced_bounds")
+        return list(out)
+
+    def set_column_bounds(self, bounds):
+        """The column plan gather_tiles uses from now on (None: the uniform plan)."""
+        C = self._C
+        arr = None if bounds is None else (C.c_int * len(bounds))(*[int(b) for b in bounds])
+        self._capi.check(self.lib.b200pt_comm_set_column_bounds(self.handle, arr), "b200pt_comm_set_column_bounds")
+
+    def rebalance_columns(self, bounds, my_cost, extent, align=8):
+        """One balancing step: every rank contributes the cost of its band, all compute the same new plan and adopt it."""
+        costs = [0.0] * self.world
+        costs[self.rank] = float(my_cost)
+        costs = self.allreduce_host(costs)
+        new = Comm.balanced_bounds(self.lib, bounds, costs, extent, align)
+        self.set_column_bounds(new)
+        return new, costs
+

@@ -35,6 +35,14 @@ typedef enum b200pt_sharding
 /* The band of `rank` among `world` bands of a width x height image; bands tile the image, are multiples of 8 pixels except the last,
  * and may be empty when world exceeds the number of 8-pixel blocks. No communicator needed. */
 B200PT_API int b200pt_comm_tile(int sharding, int width, int height, int world, int rank, b200pt_tile* out_tile);
+/* Cost-balanced column bands (new). A landscape frame's columns do not cost the same (path lengths differ): after a frame every rank
+ * reports what its band cost (e.g. the milliseconds of its launches, shared with b200pt_comm_allreduce_host_f64) and all ranks compute the same
+ * new plan. bounds / out_bounds: world + 1 entries, band r = [bounds[r], bounds[r + 1]), bounds[0] = 0, bounds[world] = extent. The cost is
+ * taken as uniform inside each old band; new boundaries are multiples of `align` pixels, bands stay at least `align` wide while the image has
+ * that many blocks. Iterate over a few frames. No communicator needed. Tiles only change which rank renders a pixel, never its value. */
+B200PT_API int b200pt_comm_balanced_bounds(const int* bounds, const double* cost, int world, int extent, int align, int* out_bounds);
+/* The column plan b200pt_comm_gather_tiles uses from now on for images `bounds[world]` pixels wide (NULL: back to b200pt_comm_tile's). */
+B200PT_API int b200pt_comm_set_column_bounds(b200pt_comm* comm, const int* bounds);
 /* Rows of neighbour data the fused ReSTIR DI pass can reach above and below a tile: reuse_radius + neighbor_search_radius
  * (ReSTIRDISettings.h:42,65; Utils.h:301-366,426-478) + the camera's motion in rows since the last frame. */
 B200PT_API int b200pt_comm_restir_halo_rows(int reuse_radius, int neighbor_search_radius, int camera_motion_rows);

@@ -25,7 +25,7 @@ def test_every_declared_symbol_is_exported(pt):
     assert sorted(capi.API_SYMBOLS) == core
     assert sorted(capi.HOST_API_SYMBOLS) == hostsyms
     commsyms = _declared("b200pt_comm.h")            # the multi-GPU plumbing is part of libb200pt.so (NCCL itself is bound at run time)
-    assert len(commsyms) == 12 and sorted(capi.COMM_API_SYMBOLS) == commsyms
+    assert len(commsyms) == 14 and sorted(capi.COMM_API_SYMBOLS) == commsyms
     for s in commsyms:
         assert hasattr(lib, s), s
 
@@ -59,3 +59,30 @@ def test_comm_tile_plan_matches_the_python_plan(pt):
     t = pt.structs.Tile()
     assert lib.b200pt_comm_tile(0, 64, 64, 2, 2, ctypes.byref(t)) == -1          # rank out of range
     assert lib.b200pt_comm_restir_halo_rows(16, 4, 0) == 20
+
+
+def test_comm_balanced_bounds_equalise_a_known_cost_profile(pt):
+    """b200pt_comm_balanced_bounds (C ABI, no GPU): against a per-column cost profile (a cheap 'sky' third, an expensive middle, a ramp) the
+    plan converges in a few iterations to bands whose costs differ by no more than an alignment block; boundaries stay aligned, monotonic, and cover the image.
+    Degenerate inputs: zero costs keep the plan, a world larger than the number of blocks leaves empty bands at the end."""
+    import numpy as np
+    mg = __import__("importlib").import_module("hiprt-path-tracer_b200.multigpu")
+    lib = pt.lib()
+    W = 1920
+    x = np.arange(W)
+    column_cost = np.where(x < 600, 1.0, np.where(x < 1300, 4.0, 1.0 + 3.0 * (x - 1300) / 620.0))
+    for world in (2, 3, 8):
+        bounds = [t[0] for t in mg.column_tiles(W, world)] + [W]
+        first = None
+        for _ in range(4):
+            costs = [float(column_cost[bounds[r]:bounds[r + 1]].sum()) for r in range(world)]
+            first = first or max(costs) / (sum(costs) / world)
+            bounds = mg.Comm.balanced_bounds(lib, bounds, costs, W)
+            assert bounds[0] == 0 and bounds[-1] == W and all(b % 8 == 0 for b in bounds[:-1])
+            assert all(bounds[r + 1] - bounds[r] >= 8 for r in range(world))
+        costs = [float(column_cost[bounds[r]:bounds[r + 1]].sum()) for r in range(world)]
+        assert max(costs) / (sum(costs) / world) < 1.08 <= first, (world, first, costs)      # one 8-column block of the expensive part is 5 % of a band at 8 ranks
+    assert mg.Comm.balanced_bounds(lib, [0, 8, 16], [0.0, 0.0], 16) == [0, 8, 16]
+    assert mg.Comm.balanced_bounds(lib, [0, 8, 16, 16], [1.0, 3.0, 0.0], 16) == [0, 8, 16, 16]        # two blocks, three ranks: the last band stays empty
+    out = (ctypes.c_int * 3)()
+    assert lib.b200pt_comm_balanced_bounds((ctypes.c_int * 3)(0, 8, 15), (ctypes.c_double * 2)(1.0, 1.0), 2, 16, 8, out) == -1      # bounds must end at the extent

@@ -405,15 +405,17 @@ def test_ris_phases_are_bit_identical(pt, wl, ctx, lss, ess):
         assert np.array_equal(frames["megakernel"], frames[mode]), mode
 
 
-@pytest.mark.parametrize("ess,neighbors,boost", [("none", 2, True), ("alias_table", 2, True), ("none", 5, False), ("none", 1, False)])
-def test_restir_phases_are_bit_identical(pt, wl, ctx, ess, neighbors, boost):
+@pytest.mark.parametrize("ess,neighbors,boost,fused,passes", [("none", 2, True, True, 1), ("alias_table", 2, True, True, 1), ("none", 5, False, True, 1), ("none", 1, False, True, 1),
+                                                             ("none", 2, True, True, 2), ("none", 2, True, False, 2), ("alias_table", 3, False, False, 1)])
+def test_restir_phases_are_bit_identical(pt, wl, ctx, ess, neighbors, boost, fused, passes):
     """Phased ReSTIR DI passes (InitialCandidates: collect -> closest-hit trace -> resolve -> any-hit trace -> visibility; fused
     SpatiotemporalReuse: collect -> any-hit trace -> resolve, rays through the ray-queue kernel) against the single kernels that trace per
     thread: every frame's initial-candidates and output reservoirs, and the accumulated image, are the same bits over 5 frames (temporal
-    history, disocclusion boost, neighbours with and without the visibility term, envmap candidates with the alias-table permutation)."""
+    history, disocclusion boost, neighbours with and without the visibility term, envmap candidates with the alias-table permutation). The
+    stand-alone TemporalReuse / SpatialReuse passes (fused = False, and the spatial passes after the fused one) are phased the same way."""
     procedural = importlib.import_module("hiprt-path-tracer_b200.procedural")
     W, H = 160, 112
-    cfg = wl.many_lights(W, H, boxes=100, lights=1500)
+    cfg = wl.many_lights(W, H, boxes=100, lights=1500, fused=fused, spatial_passes=passes)
     cfg["options"] = dict(lss="restir_di", ess=ess, ggx=0, later=3)
     if ess == "alias_table":
         cfg["envmap"] = {"texels": procedural.procedural_envmap(256, 128), "alias_probas": None, "alias_alias": None, "total_sum": 0.0}

@@ -46,6 +46,9 @@ def main():
     render(ctx, ris, frames=1)
     render(ctx, wl.many_lights(W, H, boxes=60, lights=800), frames=3)
     render(ctx, wl.many_lights(W, H, boxes=60, lights=800, fused=False, spatial_passes=2), frames=3)
+    ctx.set_restir_phases(False)         # the single-kernel ReSTIR DI passes (per-thread traversal); phased above
+    render(ctx, wl.many_lights(W, H, boxes=60, lights=800), frames=2)
+    ctx.set_restir_phases(True)
     render(ctx, wl.adaptive_full(W, H, envmap_size=(128, 64)), frames=3)
     # ray batches + builders
     scene = wl.synthetic_small(W, H)["scene"]
