@@ -177,8 +177,8 @@ def run_ours(args, cfg, pt):
     mg = importlib.import_module("hiprt-path-tracer_b200.multigpu")
     restir = cfg["options"]["lss"] == "restir_di"
     sharding = args.sharding if args.sharding != "auto" else ("samples" if args.workload in ("cornell", "adaptive") else "columns")
-    if restir:
-        sharding = "tiles"              # reservoirs are per pixel and per frame: ReSTIR DI shards by row tiles + halo only
+    if restir and sharding != "samples":
+        sharding = "tiles"              # reservoirs are per pixel and per frame: ReSTIR DI shards by row tiles + halo (or, on request, by sample passes: every rank its own reservoir history)
     tiles = mg.column_tiles(W, world) if sharding == "columns" else mg.row_tiles(H, world)
     halo = mg.restir_halo_rows() if restir else 0
     device = torch.device("cuda", local_rank)

@@ -86,14 +86,17 @@ int b200pt_bvh_build(b200pt_ctx* ctx, const float* vertices, int vertex_count, c
     *out_bvh = nullptr;
     CUDA_TRY(cudaSetDevice(ctx->device));
 
-    // B200PT_BVH_BUILD_DEVICE (flag, or the environment variable of the same name set to 1): Morton LBVH + SAH-optimal collapse on the GPU
+    // B200PT_BVH_BUILD_DEVICE (flag, or the environment variable of the same name set to 1): Morton order + PLOC (or radix tree) + SAH-optimal collapse on the GPU
     // (bvh8_build_device.cu) instead of the host's binned-SAH builder, which stays the quality baseline and the default
     static const bool device_by_env = [] { const char* v = getenv("B200PT_BVH_BUILD_DEVICE"); return v && atoi(v) != 0; }();
     if (((flags & B200PT_BVH_BUILD_DEVICE) || device_by_env) && triangle_count > 0)
     {
         auto t0 = std::chrono::steady_clock::now();
         pt::Bvh8DeviceBuild built;
-        cudaError_t e = pt::build_bvh8_device(vertices, vertex_count, triangle_indices, triangle_count, ctx->main_stream, &built);
+        static const int algorithm_by_env = [] { const char* v = getenv("B200PT_BVH_DEVICE_ALGORITHM"); return v == nullptr ? -1 : (strcmp(v, "lbvh") == 0 ? (int)pt::BVH8_DEVICE_LBVH : (int)pt::BVH8_DEVICE_PLOC); }();
+        static const int ploc_radius = [] { const char* v = getenv("B200PT_PLOC_RADIUS"); int r = v ? atoi(v) : 0; return r > 0 ? (r > 256 ? 256 : r) : 16; }();
+        const int algorithm = (flags & B200PT_BVH_BUILD_DEVICE_LBVH) ? (int)pt::BVH8_DEVICE_LBVH : (algorithm_by_env >= 0 ? algorithm_by_env : (int)pt::BVH8_DEVICE_PLOC);
+        cudaError_t e = pt::build_bvh8_device(vertices, vertex_count, triangle_indices, triangle_count, ctx->main_stream, &built, algorithm, ploc_radius);
         if (e != cudaSuccess)
             return cuda_fail(e, "device BVH8 build");
         if (2 * built.max_depth + 1 > pt::kTraversalStackSize)

@@ -1,11 +1,13 @@
 // CUDA kernels and host driver of the device BVH8 builder (per-element functions: bvh8_build_device.cuh).
-// Pipeline: scene box (reduction) -> triangle boxes + 63-bit Morton codes -> radix sort of (code, triangle) pairs -> Karras radix tree ->
-// bottom-up boxes + SAH-optimal collapse costs -> top-down emission of the 8-wide nodes, one launch per tree level.
-// The radix sort is cub::DeviceRadixSort (CUDA toolkit header library): sorting is plumbing here, every tree-building step is ours.
+// Pipeline: scene box (reduction) -> triangle boxes + 63-bit Morton codes -> radix sort of (code, triangle) pairs -> binary topology (PLOC:
+// mutual-nearest-neighbour clustering along the Morton curve, the default; or the Karras radix tree) -> bottom-up boxes + SAH-optimal
+// collapse costs -> top-down emission of the 8-wide nodes, one launch per tree level.
+// The radix sort and the prefix sums are cub's (CUDA toolkit header library): plumbing here, every tree-building step is ours.
 #include "bvh8_build_device.cuh"
 #include "bvh8_build_device.h"
 
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -96,6 +98,76 @@ __global__ void __launch_bounds__(128) k_lbvh_collapse(lbvh::Tree tree, lbvh::Wi
     lbvh::collapse_wide_node(tree, wide, queue[i], next_queue, next_count, root_area);
 }
 
+// ---- PLOC (bvh8_build_device.cuh) ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_ploc_init(lbvh::Tree tree, const float* __restrict__ prim_lo, const float* __restrict__ prim_hi, int* cluster, float* box, uint32_t* subtree_count)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= tree.n)
+        return;
+    const uint32_t p = tree.prim[i];
+    cluster[i] = (int)(tree.n - 1u + i);
+    subtree_count[tree.n - 1u + i] = 1u;
+    for (int a = 0; a < 3; a++)
+    {
+        box[6 * (size_t)i + a] = prim_lo[3 * (size_t)p + a];
+        box[6 * (size_t)i + 3 + a] = prim_hi[3 * (size_t)p + a];
+    }
+}
+__global__ void __launch_bounds__(256) k_ploc_nearest(lbvh::Ploc p)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < p.count)
+        lbvh::ploc_nearest(p, i);
+}
+__global__ void __launch_bounds__(256) k_ploc_flags(lbvh::Ploc p)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < p.count)
+        lbvh::ploc_flags(p, i);
+}
+__global__ void __launch_bounds__(256) k_ploc_merge(lbvh::Ploc p, lbvh::Tree tree)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < p.count)
+        lbvh::ploc_merge(p, tree, i);
+}
+// Depth-first leaf layout of the clustered tree: first leaf of every node, then the triangles move to that order and the leaves are renumbered
+__global__ void __launch_bounds__(256) k_ploc_first_leaf(lbvh::Tree tree, const uint32_t* __restrict__ subtree_count)
+{
+    const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v < 2u * tree.n - 1u)
+        tree.first[v] = lbvh::ploc_first_leaf(tree, subtree_count, (int)v);
+}
+__global__ void __launch_bounds__(256) k_ploc_move_leaves(lbvh::Tree tree, uint32_t* new_prim, int* new_leaf_parent, uint32_t* new_position)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= tree.n)
+        return;
+    const uint32_t leaf = tree.n - 1u + i, q = tree.first[leaf];
+    new_prim[q] = tree.prim[i];
+    new_leaf_parent[q] = tree.parent[leaf];
+    new_position[i] = q;
+}
+__global__ void __launch_bounds__(256) k_ploc_renumber(lbvh::Tree tree, const uint32_t* __restrict__ subtree_count, const uint32_t* __restrict__ new_position)
+{
+    const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v + 1u >= tree.n)
+        return;                  // internal nodes: 0 .. n - 2
+    const int leaf0 = (int)tree.n - 1;
+    const int l = tree.left[v], r = tree.right[v];
+    if (l >= leaf0)
+        tree.left[v] = leaf0 + (int)new_position[l - leaf0];
+    if (r >= leaf0)
+        tree.right[v] = leaf0 + (int)new_position[r - leaf0];
+    tree.last[v] = tree.first[v] + subtree_count[v] - 1u;
+}
+__global__ void __launch_bounds__(256) k_ploc_leaf_parents(lbvh::Tree tree, const int* __restrict__ new_leaf_parent)
+{
+    const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q < tree.n)
+        tree.parent[tree.n - 1u + q] = new_leaf_parent[q];
+}
+
 struct DeviceArena
 {
     std::vector<void*> blocks;
@@ -119,7 +191,7 @@ struct DeviceArena
 
 // vertices / indices: HOST arrays, as b200pt_bvh_build receives them. On success *out_nodes / *out_triangles are device arrays the caller
 // owns (cudaFree), trimmed to the node / triangle counts.
-cudaError_t build_bvh8_device(const float* vertices, int vertex_count, const int* indices, int triangle_count, cudaStream_t stream, Bvh8DeviceBuild* out)
+cudaError_t build_bvh8_device(const float* vertices, int vertex_count, const int* indices, int triangle_count, cudaStream_t stream, Bvh8DeviceBuild* out, int algorithm, int ploc_radius)
 {
     *out = Bvh8DeviceBuild();
     const uint32_t n = (uint32_t)triangle_count;
@@ -192,7 +264,63 @@ cudaError_t build_bvh8_device(const float* vertices, int vertex_count, const int
     lbvh::Tree tree = {n, d_keys, d_prim, d_left, d_right, d_parent, d_first, d_last, d_lo, d_hi, d_visits, d_cost, d_choice};
     cudaMemsetAsync(d_visits, 0, sizeof(uint32_t) * (size_t)n, stream);
     cudaMemsetAsync(d_parent, 0xFF, sizeof(int) * nodes2, stream);                  // -1: the root (and the only node of a one-triangle scene) has no parent
-    if (n > 1)
+    int ploc_iterations = 0;
+    if (n > 1 && algorithm == BVH8_DEVICE_PLOC)
+    {
+        int* d_cluster[2] = {arena.alloc<int>(n), arena.alloc<int>(n)};
+        float* d_box[2] = {arena.alloc<float>(6 * (size_t)n), arena.alloc<float>(6 * (size_t)n)};
+        uint32_t* d_nearest = arena.alloc<uint32_t>(n);
+        uint64_t* d_flags = arena.alloc<uint64_t>(n);
+        uint64_t* d_scanned = arena.alloc<uint64_t>(n);
+        uint32_t* d_subtree = arena.alloc<uint32_t>(nodes2);
+        int* d_leaf_parent = arena.alloc<int>(n);
+        uint32_t* d_new_position = arena.alloc<uint32_t>(n);
+        size_t scan_bytes = 0;
+        e = cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, d_flags, d_scanned, (int)n, stream);
+        if (e != cudaSuccess)
+            return fail(e);
+        void* d_scan_temp = arena.alloc<unsigned char>(scan_bytes);
+        if (arena.error != cudaSuccess)
+            return fail(arena.error);
+        k_ploc_init<<<grid_n, 256, 0, stream>>>(tree, d_prim_lo, d_prim_hi, d_cluster[0], d_box[0], d_subtree);
+        uint32_t clusters = n;
+        int next_free = (int)n - 1;          // internal nodes n - 2 .. 0
+        while (clusters > 1)
+        {
+            const int in = ploc_iterations & 1, outb = in ^ 1;
+            lbvh::Ploc p = {clusters, ploc_radius, d_cluster[in], d_box[in], d_nearest, d_flags, d_scanned, d_cluster[outb], d_box[outb], d_subtree, next_free};
+            const unsigned grid_c = (clusters + 255u) / 256u;
+            k_ploc_nearest<<<grid_c, 256, 0, stream>>>(p);
+            k_ploc_flags<<<grid_c, 256, 0, stream>>>(p);
+            e = cub::DeviceScan::ExclusiveSum(d_scan_temp, scan_bytes, d_flags, d_scanned, (int)clusters, stream);
+            if (e != cudaSuccess)
+                return fail(e);
+            k_ploc_merge<<<grid_c, 256, 0, stream>>>(p, tree);
+            uint64_t last[2];
+            e = cudaMemcpyAsync(&last[0], d_scanned + (clusters - 1u), sizeof(uint64_t), cudaMemcpyDeviceToHost, stream);
+            if (e == cudaSuccess)
+                e = cudaMemcpyAsync(&last[1], d_flags + (clusters - 1u), sizeof(uint64_t), cudaMemcpyDeviceToHost, stream);
+            if (e == cudaSuccess)
+                e = cudaStreamSynchronize(stream);
+            if (e != cudaSuccess)
+                return fail(e);
+            const uint64_t total = last[0] + last[1];
+            const uint32_t merges = (uint32_t)(total >> 32);
+            if (merges == 0u || ++ploc_iterations > 4096)
+                return fail(cudaErrorUnknown);          // cannot happen: the cheapest pair is always mutual
+            clusters = (uint32_t)(total & 0xFFFFFFFFull);
+            next_free -= (int)merges;
+        }
+        if (next_free != 0)
+            return fail(cudaErrorUnknown);
+        // leaves in depth-first order: every node covers a contiguous range of the triangle order again
+        k_ploc_first_leaf<<<(unsigned)((nodes2 + 255) / 256), 256, 0, stream>>>(tree, d_subtree);
+        k_ploc_move_leaves<<<grid_n, 256, 0, stream>>>(tree, d_ids, d_leaf_parent, d_new_position);
+        k_ploc_renumber<<<grid_n, 256, 0, stream>>>(tree, d_subtree, d_new_position);
+        k_ploc_leaf_parents<<<grid_n, 256, 0, stream>>>(tree, d_leaf_parent);
+        tree.prim = d_ids;
+    }
+    else if (n > 1)
         k_lbvh_internal<<<grid_n, 256, 0, stream>>>(tree);
     k_lbvh_refit<<<grid_n, 256, 0, stream>>>(tree, d_prim_lo, d_prim_hi);
 
@@ -259,6 +387,7 @@ cudaError_t build_bvh8_device(const float* vertices, int vertex_count, const int
     memcpy(sah, counters + 4, sizeof(sah));
     out->sah_cost = sah[0] + sah[1];
     out->device_seconds = ms * 1.0e-3;
+    out->ploc_iterations = ploc_iterations;
     for (int a = 0; a < 3; a++)
     {
         out->scene_min[a] = bounds[a];

@@ -257,6 +257,104 @@ LBVH_HD void refit_from_leaf(const Tree& t, uint32_t i, const float* prim_lo, co
     }
 }
 
+// ---- PLOC (Meister & Bittner 2018, "Parallel Locally-Ordered Clustering for BVH Construction"): the binary topology by agglomerative
+// clustering along the Morton curve instead of the radix tree. Every iteration each cluster looks for the neighbour within `radius`
+// positions whose union with it has the smallest surface area; mutual nearest neighbours merge into a new internal node; the clusters
+// are compacted (order kept) and the loop repeats until one cluster is left. The globally cheapest pair is always mutual (ties go to the
+// lower position on both sides), so every iteration merges at least one pair. Costs ~10 ms more than the radix tree on 10 M triangles
+// and gives a tree whose SAH is a few percent from the host builder's binned-SAH sweep (the radix tree: ~10 %).
+struct Ploc
+{
+    uint32_t count;              // clusters of this iteration
+    int radius;
+    const int* cluster;          // [count] binary node of cluster i
+    const float* box;            // [count][6] lo xyz, hi xyz of cluster i
+    uint32_t* nearest;           // [count]
+    uint64_t* flags;             // [count] low word 1: the position survives (unmerged cluster, or the lower position of a merging pair); high word 1: it merges
+    const uint64_t* scanned;     // exclusive prefix sums of flags: low word = position in the next iteration, high word = rank among this iteration's merges
+    int* next_cluster;           // output of the iteration
+    float* next_box;
+    uint32_t* subtree_count;     // [2n-1] leaves below a binary node
+    int next_free_node;          // internal nodes are numbered downwards from n - 2, so that the last merge creates node 0, the root
+};
+
+LBVH_HD void ploc_nearest(const Ploc& p, uint32_t i)
+{
+    const float* b = p.box + 6 * (size_t)i;
+    const int begin = (int)i - p.radius < 0 ? 0 : (int)i - p.radius;
+    const int end = (int)i + p.radius >= (int)p.count ? (int)p.count - 1 : (int)i + p.radius;
+    float best = INFINITY;
+    uint32_t best_j = i;
+    for (int j = begin; j <= end; j++)
+    {
+        if (j == (int)i)
+            continue;
+        const float* o = p.box + 6 * (size_t)j;
+        const float lo[3] = {fminf(b[0], o[0]), fminf(b[1], o[1]), fminf(b[2], o[2])};
+        const float hi[3] = {fmaxf(b[3], o[3]), fmaxf(b[4], o[4]), fmaxf(b[5], o[5])};
+        const float d = half_area(lo, hi);
+        if (d < best)          // ascending j: ties keep the lower position
+        {
+            best = d;
+            best_j = (uint32_t)j;
+        }
+    }
+    p.nearest[i] = best_j;
+}
+
+LBVH_HD void ploc_flags(const Ploc& p, uint32_t i)
+{
+    const uint32_t j = p.nearest[i];
+    const bool mutual = j != i && p.nearest[j] == i;
+    p.flags[i] = (mutual && i > j ? 0ull : 1ull) | (mutual && i < j ? 1ull << 32 : 0ull);
+}
+
+LBVH_HD void ploc_merge(const Ploc& p, const Tree& t, uint32_t i)
+{
+    const uint64_t f = p.flags[i];
+    if ((f & 1ull) == 0ull)
+        return;                  // the upper position of a merging pair: its partner writes the new cluster
+    const uint32_t out = (uint32_t)(p.scanned[i] & 0xFFFFFFFFull);
+    const float* b = p.box + 6 * (size_t)i;
+    float* nb = p.next_box + 6 * (size_t)out;
+    if ((f >> 32) == 0ull)
+    {
+        p.next_cluster[out] = p.cluster[i];
+        for (int a = 0; a < 6; a++)
+            nb[a] = b[a];
+        return;
+    }
+    const uint32_t j = p.nearest[i];
+    const float* o = p.box + 6 * (size_t)j;
+    const int node = p.next_free_node - 1 - (int)(p.scanned[i] >> 32);
+    const int left = p.cluster[i], right = p.cluster[j];
+    t.left[node] = left;
+    t.right[node] = right;
+    t.parent[left] = node;
+    t.parent[right] = node;
+    if (node == 0)
+        t.parent[0] = -1;
+    p.subtree_count[node] = p.subtree_count[left] + p.subtree_count[right];
+    for (int a = 0; a < 3; a++)
+    {
+        nb[a] = fminf(b[a], o[a]);
+        nb[3 + a] = fmaxf(b[3 + a], o[3 + a]);
+    }
+    p.next_cluster[out] = node;
+}
+
+// Position of the first leaf below binary node v when the leaves are laid out in depth-first order (left before right): the sum, over the
+// ancestors entered through their right child, of the leaves below the left sibling. The radix tree has this property by construction
+// (a node covers a contiguous range of the sorted triangles); after PLOC the triangles are re-ordered to restore it.
+LBVH_HD uint32_t ploc_first_leaf(const Tree& t, const uint32_t* subtree_count, int v)
+{
+    uint32_t first = 0;
+    for (int parent = t.parent[v]; parent >= 0; v = parent, parent = t.parent[parent])
+        if (t.right[parent] == v)
+            first += subtree_count[t.left[parent]];
+    return first;
+}
+
 // Output of the collapse
 struct Wide
 {

@@ -74,11 +74,12 @@ class Context:
 
     # ---- acceleration structure + ray batches ------------------------------------------------
     def build_bvh(self, vertices, indices, device=False):
+        """device: False = the host binned-SAH builder, True / "ploc" = the device builder (PLOC clustering), "lbvh" = the device builder with the radix tree."""
         vertices = np.ascontiguousarray(vertices, dtype=np.float32)
         indices = np.ascontiguousarray(indices, dtype=np.int32)
         bvh = C.c_void_p()
         _capi.check(self.lib.b200pt_bvh_build(self.handle, _ptr(vertices), C.c_int(len(vertices)), _ptr(indices), C.c_int(len(indices) // 3 if indices.ndim == 1 else len(indices)),
-                                              C.c_uint(1 if device else 0), C.byref(bvh)), "b200pt_bvh_build")
+                                              C.c_uint((3 if device == "lbvh" else 1) if device else 0), C.byref(bvh)), "b200pt_bvh_build")
         return bvh
 
     def bvh_info(self, bvh):

@@ -144,8 +144,10 @@ B200PT_API int b200pt_tex2d_array_create(b200pt_ctx* ctx, void* const* descripto
 
 /* ---- acceleration structure ---------------------------------------------------------------------------------- */
 /* vertices: 3 floats per vertex; triangle_indices: 3 ints per triangle (host pointers). The primitive index reported
- * by the kernels is the index into triangle_indices / 3, as in the reference. flags: 0 or B200PT_BVH_BUILD_DEVICE. */
-#define B200PT_BVH_BUILD_DEVICE 1u   /* flags: build on the GPU (Morton LBVH + SAH-optimal collapse) instead of the host's binned-SAH builder */
+ * by the kernels is the index into triangle_indices / 3, as in the reference. flags: 0, B200PT_BVH_BUILD_DEVICE, or that | B200PT_BVH_BUILD_DEVICE_LBVH.
+ * Environment: B200PT_BVH_BUILD_DEVICE=1 forces the device builder, B200PT_BVH_DEVICE_ALGORITHM=lbvh|ploc and B200PT_PLOC_RADIUS (default 16) tune it. */
+#define B200PT_BVH_BUILD_DEVICE 1u   /* flags: build on the GPU (Morton order -> PLOC clustering -> SAH-optimal collapse) instead of the host's binned-SAH builder */
+#define B200PT_BVH_BUILD_DEVICE_LBVH 2u   /* with B200PT_BVH_BUILD_DEVICE: the Karras radix tree instead of PLOC (faster to build, ~10 % higher SAH cost) */
 B200PT_API int b200pt_bvh_build(b200pt_ctx* ctx, const float* vertices, int vertex_count, const int* triangle_indices, int triangle_count, unsigned flags, b200pt_bvh** out_bvh);
 B200PT_API int b200pt_bvh_destroy(b200pt_ctx* ctx, b200pt_bvh* bvh);
 B200PT_API void* b200pt_bvh_device_handle(b200pt_bvh* bvh);             /* value for HIPRTRenderData::geom */

@@ -36,7 +36,10 @@ static float frand() { return rand() / (float)RAND_MAX; }
 
 int main(int argc, char** argv)
 {
-    const int mode = argc > 1 ? atoi(argv[1]) : 0;   // 0 random soup, 1 height field, 2 one triangle, 3 axis-aligned quads with duplicates, 4 two triangles
+    const int mode_arg = argc > 1 ? atoi(argv[1]) : 0;
+    const bool ploc = mode_arg >= 10;                // 10 + mode: the binary topology by PLOC clustering instead of the radix tree
+    const int ploc_radius = argc > 2 ? atoi(argv[2]) : 8;
+    const int mode = mode_arg % 10;                  // 0 random soup, 1 height field, 2 one triangle, 3 axis-aligned quads with duplicates, 4 two triangles
     const int N = mode == 2 ? 1 : mode == 4 ? 2 : mode == 1 ? 2 * 70 * 70 : 3000;
     std::vector<float> v;
     std::vector<int> idx;
@@ -98,8 +101,60 @@ int main(int argc, char** argv)
     std::vector<float> cost(7 * nodes2);
     std::vector<lbvh::Choice> choice(nodes2);
     lbvh::Tree t = {n, keys.data(), order.data(), left.data(), right.data(), parent.data(), first.data(), last.data(), lo.data(), hi.data(), visits.data(), cost.data(), choice.data()};
-    for (int i = 0; i + 1 < (int)n; i++)
-        lbvh::build_internal_node(t, i);
+    std::vector<uint32_t> reordered(n);
+    int ploc_iterations = 0;
+    if (ploc && n > 1)
+    {
+        // the kernels of bvh8_build_device.cu, serially: init, then (nearest, flags, exclusive scan, merge) until one cluster is left
+        std::vector<int> cluster[2] = {std::vector<int>(n), std::vector<int>(n)};
+        std::vector<float> box[2] = {std::vector<float>(6 * (size_t)n), std::vector<float>(6 * (size_t)n)};
+        std::vector<uint32_t> nearest(n), subtree(nodes2, 0u);
+        std::vector<uint64_t> flags(n), scanned(n);
+        for (uint32_t i = 0; i < n; i++)
+        {
+            cluster[0][i] = (int)(n - 1 + i);
+            subtree[n - 1 + i] = 1;
+            for (int a = 0; a < 3; a++) { box[0][6 * i + a] = plo[3 * order[i] + a]; box[0][6 * i + 3 + a] = phi[3 * order[i] + a]; }
+        }
+        uint32_t clusters = n;
+        int next_free = (int)n - 1;
+        while (clusters > 1)
+        {
+            const int in = ploc_iterations & 1, out = in ^ 1;
+            lbvh::Ploc p = {clusters, ploc_radius, cluster[in].data(), box[in].data(), nearest.data(), flags.data(), scanned.data(), cluster[out].data(), box[out].data(), subtree.data(), next_free};
+            for (uint32_t i = 0; i < clusters; i++) lbvh::ploc_nearest(p, i);
+            for (uint32_t i = 0; i < clusters; i++) lbvh::ploc_flags(p, i);
+            uint64_t sum = 0;
+            for (uint32_t i = 0; i < clusters; i++) { scanned[i] = sum; sum += flags[i]; }
+            for (uint32_t i = 0; i < clusters; i++) lbvh::ploc_merge(p, t, i);
+            const uint32_t merges = (uint32_t)(sum >> 32);
+            if (merges == 0) { printf("FAIL: PLOC iteration %d merged nothing\n", ploc_iterations); return 1; }
+            clusters = (uint32_t)(sum & 0xFFFFFFFFull);
+            next_free -= (int)merges;
+            ploc_iterations++;
+        }
+        if (next_free != 0 || parent[0] != -1) { printf("FAIL: PLOC left %d unused internal nodes, root parent %d\n", next_free, parent[0]); return 1; }
+        // depth-first leaf layout, triangles moved, leaves renumbered (k_ploc_first_leaf / _move_leaves / _renumber / _leaf_parents)
+        for (size_t v2 = 0; v2 < nodes2; v2++) first[v2] = lbvh::ploc_first_leaf(t, subtree.data(), (int)v2);
+        std::vector<int> leaf_parent(n);
+        std::vector<uint32_t> new_position(n);
+        for (uint32_t i = 0; i < n; i++) { const uint32_t q = first[n - 1 + i]; reordered[q] = order[i]; leaf_parent[q] = parent[n - 1 + i]; new_position[i] = q; }
+        for (uint32_t v2 = 0; v2 + 1 < n; v2++)
+        {
+            const int leaf0 = (int)n - 1;
+            if (left[v2] >= leaf0) left[v2] = leaf0 + (int)new_position[left[v2] - leaf0];
+            if (right[v2] >= leaf0) right[v2] = leaf0 + (int)new_position[right[v2] - leaf0];
+            last[v2] = first[v2] + subtree[v2] - 1;
+        }
+        for (uint32_t q = 0; q < n; q++) parent[n - 1 + q] = leaf_parent[q];
+        std::vector<int> once(n, 0);
+        for (uint32_t q = 0; q < n; q++) once[reordered[q]]++;
+        for (uint32_t q = 0; q < n; q++) if (once[q] != 1) { printf("FAIL: the depth-first order is not a permutation\n"); return 1; }
+        t.prim = reordered.data();
+    }
+    else
+        for (int i = 0; i + 1 < (int)n; i++)
+            lbvh::build_internal_node(t, i);
     for (uint32_t i = 0; i < n; i++)
         lbvh::refit_from_leaf(t, i, plo.data(), phi.data());
     std::vector<Bvh8Node> nodes(std::max<size_t>(n, 1));
@@ -156,7 +211,7 @@ int main(int argc, char** argv)
         bool occluded = bvh8_trace<true>(d, o, dir, tmax - 1.0e-4f, lastp, sh, nullptr);
         if (occluded != (best >= 0 && bt < tmax - 1.0e-4f)) shadow_bad++;
     }
-    printf("mode %d: %u wide nodes, depth %d, fill %.2f, sah %.2f, hits %d, closest_mismatches %d, shadow_mismatches %d\n", mode, node_count, depth, slots / (8.0 * node_count),
-           sah[0] + sah[1], hits, bad, shadow_bad);
+    printf("mode %d (%s, %d clustering iterations): %u wide nodes, depth %d, fill %.2f, sah %.2f, hits %d, closest_mismatches %d, shadow_mismatches %d\n", mode, ploc ? "PLOC" : "radix tree",
+           ploc_iterations, node_count, depth, slots / (8.0 * node_count), sah[0] + sah[1], hits, bad, shadow_bad);
     return (bad || shadow_bad || 2 * depth + 1 > kTraversalStackSize) ? 1 : 0;
 }

@@ -60,11 +60,13 @@ def lbvh_shim_binary(tmp_path_factory):
     return out
 
 
-@pytest.mark.parametrize("mode", [0, 1, 2, 3, 4])
+@pytest.mark.parametrize("mode", [0, 1, 2, 3, 4, 10, 11, 12, 13, 14])
 def test_device_builder_steps_equal_brute_force(lbvh_shim_binary, mode):
-    """The per-element functions of the DEVICE BVH8 builder (Morton codes, Karras radix tree, bottom-up boxes + collapse costs, emission;
-    csrc/bvh8_build_device.cuh) in serial loops on the host: every triangle emitted once, traversal equals brute force, depth fits the stack.
-    Modes: soup, height field, one triangle, duplicated axis-aligned triangles (equal Morton codes, flat boxes), two triangles."""
+    """The per-element functions of the DEVICE BVH8 builder (Morton codes, Karras radix tree or PLOC clustering, bottom-up boxes + collapse
+    costs, emission; csrc/bvh8_build_device.cuh) in serial loops on the host: every triangle emitted once, traversal equals brute force, depth
+    fits the stack. Modes: soup, height field, one triangle, duplicated axis-aligned triangles (equal Morton codes, flat boxes), two triangles;
+    10 + mode: the same scenes with the binary topology from PLOC (every iteration merges, the last merge is node 0, the depth-first
+    re-ordering of the triangles is a permutation)."""
     r = subprocess.run([lbvh_shim_binary, str(mode)], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout + r.stderr
 
@@ -98,7 +100,7 @@ def sanitized_shims(tmp_path_factory):
 
 
 @pytest.mark.parametrize("name,mode", [("traverse_host_test", 0), ("traverse_host_test", 3), ("trace_queue_host_test", 0), ("trace_queue_host_test", 1), ("lbvh_host_test", 0),
-                                       ("lbvh_host_test", 3), ("lbvh_host_test", 4)])
+                                       ("lbvh_host_test", 3), ("lbvh_host_test", 4), ("lbvh_host_test", 10), ("lbvh_host_test", 13)])
 def test_host_shims_are_clean_under_asan_and_ubsan(sanitized_shims, name, mode):
     env = dict(os.environ, ASAN_OPTIONS="detect_leaks=0:abort_on_error=0", UBSAN_OPTIONS="print_stacktrace=1", OMP_NUM_THREADS="4")
     r = subprocess.run([sanitized_shims[name], str(mode)], capture_output=True, text=True, timeout=900, env=env)

@@ -22,6 +22,12 @@ def test_single_rank_communicator_runs_every_collective(pt, ctx):
             comm.gather_tiles(d_image.value, W, H, 12, sharding)
             ctx.sync()
             assert np.array_equal(ctx.download(d_image, (H, W, 3), np.float32), image)      # one rank owns the whole frame
+        new_bounds, costs = comm.rebalance_columns([0, W], 3.5, W)         # cost-balanced plan: with one rank it is the whole frame, whatever the cost
+        assert new_bounds == [0, W] and costs == [3.5]
+        comm.gather_tiles(d_image.value, W, H, 12, mg.Comm.COLUMNS)
+        ctx.sync()
+        assert np.array_equal(ctx.download(d_image, (H, W, 3), np.float32), image)
+        comm.set_column_bounds(None)
         d_sum = ctx.malloc(image.nbytes)
         comm.allreduce_sum(d_image.value, d_sum.value, image.size, "f32")
         counts = rng.integers(0, 100, (H, W)).astype(np.int32)

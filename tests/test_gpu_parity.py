@@ -154,27 +154,30 @@ def test_c3_hit_ids_on_the_10m_triangle_bvh(pt, wl, ctx, ref):
         assert c["stack_overflows"] == 0, c
         # the same rays on the tree the DEVICE builder makes of the scene: hit ids are a property of the triangles, not
         # of the tree, so they must again equal the reference's
-        bvh_d = ctx.build_bvh(cfg["scene"].vertices, cfg["scene"].indices, device=True)
-        try:
-            info_d = ctx.bvh_info(bvh_d)
-            print("host build:", info, "\ndevice build:", info_d)
-            assert info_d["built_on_device"] and info_d["triangles"] == 9_998_802 and 2 * info_d["max_depth"] + 1 <= 48, info_d
-            assert info_d["device_build_seconds"] < 1.0, info_d
-            dprim, dt, _ = ctx.trace_queue(bvh_d, log["rays"], None, log["last_prim"])
-            _assert_hits_equal(dprim, dt, log, "ray-queue kernel on the device-built tree")
-            assert np.array_equal(ctx.trace_queue(bvh_d, rays, t_max, last), occ_ref)
-            assert ctx.counters_read(True)["stack_overflows"] == 0
-        finally:
-            ctx.destroy_bvh(bvh_d)
+        for algorithm in ("ploc", "lbvh"):
+            bvh_d = ctx.build_bvh(cfg["scene"].vertices, cfg["scene"].indices, device=algorithm)
+            try:
+                info_d = ctx.bvh_info(bvh_d)
+                print("host build:", info, f"\ndevice build ({algorithm}):", info_d)
+                assert info_d["built_on_device"] and info_d["triangles"] == 9_998_802 and 2 * info_d["max_depth"] + 1 <= 48, info_d
+                assert info_d["device_build_seconds"] < 1.0, info_d
+                assert info_d["sah_cost"] < 1.15 * info["sah_cost"], (algorithm, info_d["sah_cost"], info["sah_cost"])
+                dprim, dt, _ = ctx.trace_queue(bvh_d, log["rays"], None, log["last_prim"])
+                _assert_hits_equal(dprim, dt, log, f"ray-queue kernel on the device-built tree ({algorithm})")
+                assert np.array_equal(ctx.trace_queue(bvh_d, rays, t_max, last), occ_ref)
+                assert ctx.counters_read(True)["stack_overflows"] == 0
+            finally:
+                ctx.destroy_bvh(bvh_d)
     finally:
         ctx.set_trace_flavour(-1)
         ctx.counters_enable(False)
         ctx.destroy_bvh(bvh)
 
 
+@pytest.mark.parametrize("algorithm", ["ploc", "lbvh"])
 @pytest.mark.parametrize("scene_name", ["cornell", "synthetic_small", "tiny"])
-def test_device_built_bvh_gives_the_same_hits(pt, wl, ctx, scene_name):
-    """b200pt_bvh_build with B200PT_BVH_BUILD_DEVICE (Morton LBVH + SAH-optimal collapse on the GPU) against the host builder's tree:
+def test_device_built_bvh_gives_the_same_hits(pt, wl, ctx, scene_name, algorithm):
+    """b200pt_bvh_build with B200PT_BVH_BUILD_DEVICE (Morton order, PLOC clustering or radix tree, SAH-optimal collapse on the GPU) against the host builder's tree:
     closest hits (id, t, uv bits; exact-distance ties excluded) and occlusion flags of random + axis-parallel rays, per-thread traversal and
     ray-queue kernel; edge cases: one and two triangles."""
     rng = np.random.default_rng(17)
@@ -185,7 +188,7 @@ def test_device_built_bvh_gives_the_same_hits(pt, wl, ctx, scene_name):
         scene = getattr(wl, scene_name)(64, 48)["scene"]
         cases = [(scene.vertices, scene.indices)]
     for vertices, indices in cases:
-        host, dev = ctx.build_bvh(vertices, indices), ctx.build_bvh(vertices, indices, device=True)
+        host, dev = ctx.build_bvh(vertices, indices), ctx.build_bvh(vertices, indices, device=algorithm)
         try:
             ih, idv = ctx.bvh_info(host), ctx.bvh_info(dev)
             assert idv["built_on_device"] and not ih["built_on_device"] and idv["triangles"] == ih["triangles"] == len(indices) // 3
