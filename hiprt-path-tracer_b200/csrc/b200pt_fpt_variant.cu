@@ -94,7 +94,13 @@ __global__ void __launch_bounds__(64) PT_VARIANT_NAME(k_wf_bsdf)(const __grid_co
 enum PhaseKernel { PHASE_NEE_LIGHT_EVAL, PHASE_NEE_BSDF_SAMPLE, PHASE_ENV_LIGHT_EVAL, PHASE_ENV_BSDF_SAMPLE, PHASE_BSDF_RESOLVED, PHASE_NEE_PAIR, PHASE_ENV_PAIR, PHASE_RIS_CANDIDATES, PHASE_RIS_SELECT };
 cudaError_t PT_VARIANT_NAME(launch_phase)(int which, unsigned blocks, cudaStream_t stream, const HIPRTRenderData* rd, int2 res, Tile tile, const WavefrontState* wf, int bounce,
                                           bool lights_sampled, bool envmap_sampled);
-__global__ void __launch_bounds__(128) PT_VARIANT_NAME(k_wf_surface)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce)
+// SURFACE waits on two dependent scattered fetches per path (triangle indices -> vertex normals / texcoords, material index -> material): ncu on C3
+// shows 22 % issue-active with 12 warps per issue on a long scoreboard at 96 registers = 20 warps per SM (profiles/r02_shade_c3_spf16.txt).
+// More resident warps by capping the registers did not pay: at 7 blocks per SM (72 registers) the stage went 24.0 -> 27.1 ms (gpurun call 19).
+#ifndef PT_SURFACE_BLOCKS_PER_SM
+#define PT_SURFACE_BLOCKS_PER_SM 1
+#endif
+__global__ void __launch_bounds__(128, PT_SURFACE_BLOCKS_PER_SM) PT_VARIANT_NAME(k_wf_surface)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf, int bounce)
 {
     PT_FOR_EACH_QUEUED(i, wf.counts[kCountsPerBounce * bounce], 8)
         wf_surface_path<PT_ESS>(rd, res, tile, wf, bounce, i);
@@ -112,7 +118,7 @@ __global__ void __launch_bounds__(128) PT_VARIANT_NAME(k_wf_camera)(const __grid
         wf_camera_slot(rd, res, tile, wf, batch, slot);
 }
 
-__global__ void __launch_bounds__(128) PT_VARIANT_NAME(k_wf_camera_surface)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf,
+__global__ void __launch_bounds__(128, PT_SURFACE_BLOCKS_PER_SM) PT_VARIANT_NAME(k_wf_camera_surface)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile, const __grid_constant__ WavefrontState wf,
                                                                            const __grid_constant__ SampleBatch batch)
 {
     const int bounce = 0;
@@ -159,12 +165,14 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
 
     // Queue lengths are only known on the device: queue kernels run grid-stride loops on a grid capped at a few blocks per
     // SM (an uncapped grid of mostly empty blocks costs ~1.5 ns per block: 50 us per launch at 1080p)
-    static const unsigned blocks_per_sm = [] { const char* v = getenv("B200PT_QUEUE_BLOCKS_PER_SM"); int n = v ? atoi(v) : 0; return n > 0 ? (unsigned)n : 16u; }();
+    // B200PT_QUEUE_BLOCKS_PER_SM: blocks of 64 threads per SM for all lanes together; default 12 per lane = what the phases' register cap admits
+    // (16 for two lanes before: C3 1034 -> 1065 Mrays/s at 24, 1056 -> 1073 with three lanes at 36; profiles/r02_knob_sweep_lanes_queue_grid.txt)
+    static const unsigned blocks_per_sm = [] { const char* v = getenv("B200PT_QUEUE_BLOCKS_PER_SM"); int n = v ? atoi(v) : 0; return n > 0 ? (unsigned)n : 0u; }();
     // Path lanes: when the host runs several band launches on concurrent streams (trace of one band under the shade phases of
     // another), each launch sizes its grids for its share of an SM so that blocks of both are resident together
     static const unsigned share_override = [] { const char* v = getenv("B200PT_GRID_SHARE"); int n = v ? atoi(v) : 0; return n > 0 ? (unsigned)n : 0u; }();
     const unsigned share = share_override ? share_override : (wf->grid_share > 0u ? wf->grid_share : 1u);
-    const unsigned cap = wf->sm_count * ((blocks_per_sm + share - 1u) / share);
+    const unsigned cap = wf->sm_count * (blocks_per_sm ? (blocks_per_sm + share - 1u) / share : 12u);
     auto blocks = [&](unsigned block) { unsigned g = (paths + block - 1) / block, c = cap * 64u / block; return g < c ? g : c; };
     cudaError_t e = cudaMemsetAsync(wf->counts, 0, sizeof(uint32_t) * (kCountsPerBounce + kCursorsPerBounce) * (wf->max_bounces + 2), stream);
     if (e != cudaSuccess)
@@ -419,6 +427,8 @@ PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_InitialCandidates_collect, PT_IC_COLLECT, PT_
 PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_InitialCandidates_resolve, PT_IC_RESOLVE, 1)
 PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_InitialCandidates_visibility, restir_initial_candidates_visibility, 1)
 PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_SpatiotemporalReuse_collect, restir_spatiotemporal_pixel<RESTIR_COLLECT>, PT_RESTIR_COLLECT_BLOCKS_PER_SM)
+PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_SpatiotemporalReuse_search, restir_spatiotemporal_pixel<RESTIR_SEARCH>, 1)
+cudaError_t PT_VARIANT_NAME(launch_restir_sites)(cudaStream_t stream, const HIPRTRenderData* rd, int2 res, Tile tile, const RestirScratch* scratch);     // b200pt_phase_variant.cu
 PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_SpatiotemporalReuse_resolve, restir_spatiotemporal_pixel<RESTIR_RESOLVE>, 1)
 PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_TemporalReuse_collect, restir_temporal_pixel<RESTIR_COLLECT>, PT_RESTIR_COLLECT_BLOCKS_PER_SM)
 PT_RESTIR_PHASE_KERNEL(k_ReSTIR_DI_TemporalReuse_resolve, restir_temporal_pixel<RESTIR_RESOLVE>, 1)
@@ -508,7 +518,17 @@ cudaError_t PT_VARIANT_NAME(launch_ReSTIR_DI_SpatiotemporalReuse)(const HIPRTRen
     cudaError_t e = cudaMemsetAsync(scratch->counts, 0, 4 * sizeof(uint32_t), stream);
     if (e != cudaSuccess)
         return e;
-    PT_VARIANT_NAME(k_ReSTIR_DI_SpatiotemporalReuse_collect)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile, *scratch);
+    // COLLECT as one kernel per pixel (B200PT_RESTIR_SITE_PARALLEL=0), or cut again: neighbour SEARCH per pixel, then the target functions with one
+    // thread per (pixel, neighbour) -- the BSDF evaluations of a pixel's up to six neighbours run side by side instead of one after the other
+    static const bool site_parallel = [] { const char* v = getenv("B200PT_RESTIR_SITE_PARALLEL"); return v ? atoi(v) != 0 : true; }();
+    if (site_parallel)
+    {
+        PT_VARIANT_NAME(k_ReSTIR_DI_SpatiotemporalReuse_search)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile, *scratch);
+        if ((e = PT_VARIANT_NAME(launch_restir_sites)(stream, rd, res, tile, scratch)) != cudaSuccess)
+            return e;
+    }
+    else
+        PT_VARIANT_NAME(k_ReSTIR_DI_SpatiotemporalReuse_collect)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile, *scratch);
     if ((e = restir_trace(rd, scratch, true, stream)) != cudaSuccess)
         return e;
     PT_VARIANT_NAME(k_ReSTIR_DI_SpatiotemporalReuse_resolve)<<<grid, dim3(8, 8, 1), 0, stream>>>(*rd, res, tile, *scratch);
