@@ -129,9 +129,10 @@ int b200pt_comm_tile(int sharding, int width, int height, int world, int rank, b
     return B200PT_SUCCESS;
 }
 
-int b200pt_comm_balanced_bounds(const int* bounds, const double* cost, int world, int extent, int align, int* out_bounds)
+int b200pt_comm_balanced_bounds(const int* bounds_in, const double* cost, int world, int extent, int align, int* out_bounds)
 {
-    REQUIRE(bounds != nullptr && cost != nullptr && out_bounds != nullptr && world >= 1 && extent >= 0 && align >= 1);
+    REQUIRE(bounds_in != nullptr && cost != nullptr && out_bounds != nullptr && world >= 1 && extent >= 0 && align >= 1);
+    const std::vector<int> bounds(bounds_in, bounds_in + world + 1);       // out_bounds may be the same array
     REQUIRE(bounds[0] == 0 && bounds[world] == extent);
     double total = 0.0;
     for (int r = 0; r < world; r++)

@@ -4,9 +4,6 @@
 // (stack frames 700 -> 240-270 bytes, shade stage -13 %; profiles/r01_experiments_shade_and_trace.txt). The other kernels of
 // the permutation keep the BSDF out of line (b200pt_fpt_variant.cu): inlined at their many call sites they take 9x longer to build.
 #include "wavefront_mis.cuh"
-#if PT_LSS == 5
-#include "restir_di_kernels.cuh"
-#endif
 
 namespace pt
 {
@@ -51,33 +48,6 @@ __global__ void __launch_bounds__(64, PT_PHASE_BLOCKS_PER_SM) PT_VARIANT_NAME(k_
     PT_FOR_EACH_QUEUED(i, wf.counts[kCountsPerBounce * bounce + 1], 7)
         wf_bsdf_resolved_path<PT_ESS, PT_GGX, PT_PHASED_RIS>(rd, res, tile, wf, bounce, i, lights_sampled, envmap_sampled);
 }
-
-#if PT_LSS == 5
-// Second half of the fused ReSTIR DI pass's COLLECT (restir_di_kernels.cuh: restir_spatiotemporal_sites), here for the inlined BSDF and the
-// register cap of this translation unit: one thread per (pixel, neighbour), neighbour-major so that a warp works on one kind of site
-__global__ void __launch_bounds__(64, PT_PHASE_BLOCKS_PER_SM) PT_VARIANT_NAME(k_ReSTIR_DI_SpatiotemporalReuse_sites)(const __grid_constant__ HIPRTRenderData rd, int2 res, Tile tile,
-                                                                                                                const __grid_constant__ RestirScratch scratch)
-{
-    const uint32_t tile_width = (uint32_t)(tile.x1 - tile.x0), tile_pixels = tile_width * (uint32_t)(tile.y1 - tile.y0);
-    const uint32_t total = tile_pixels * (uint32_t)(1 + kRestirMaxNeighbors);
-    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x)
-    {
-        const uint32_t k = t / tile_pixels, local = t - k * tile_pixels;
-        RestirSites sites;
-        sites.scratch = &scratch;
-        sites.pixel = local;
-        restir_spatiotemporal_sites(rd, res, (uint32_t)tile.x0 + local % tile_width, (uint32_t)tile.y0 + local / tile_width, sites, (int)k);
-    }
-}
-
-cudaError_t PT_VARIANT_NAME(launch_restir_sites)(cudaStream_t stream, const HIPRTRenderData* rd, int2 res, Tile tile, const RestirScratch* scratch)
-{
-    const uint32_t total = (uint32_t)(tile.x1 - tile.x0) * (uint32_t)(tile.y1 - tile.y0) * (uint32_t)(1 + kRestirMaxNeighbors);
-    const unsigned cap = scratch->sm_count * (unsigned)PT_PHASE_BLOCKS_PER_SM * 4u, want = (total + 63u) / 64u;
-    PT_VARIANT_NAME(k_ReSTIR_DI_SpatiotemporalReuse_sites)<<<want < cap ? want : cap, 64, 0, stream>>>(*rd, res, tile, *scratch);
-    return cudaGetLastError();
-}
-#endif
 
 enum PhaseKernel { PHASE_NEE_LIGHT_EVAL, PHASE_NEE_BSDF_SAMPLE, PHASE_ENV_LIGHT_EVAL, PHASE_ENV_BSDF_SAMPLE, PHASE_BSDF_RESOLVED, PHASE_NEE_PAIR, PHASE_ENV_PAIR, PHASE_RIS_CANDIDATES, PHASE_RIS_SELECT };
 

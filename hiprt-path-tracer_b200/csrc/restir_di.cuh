@@ -152,9 +152,7 @@ PT_DEV RGB restir_sample_emission(const HIPRTRenderData& rd, const ReSTIRDISampl
 // ray-queue traversal -> RESOLVE (the resampling itself, with the traced answers). INLINE is the unphased pass: one kernel that
 // traces per thread. Which rays a pass needs does not depend on the answers of earlier ones (the samples and surfaces are inputs,
 // no random number is drawn between the neighbour search and the resampling), so COLLECT can queue them all.
-// SEARCH + one SITES thread per (pixel, neighbour) are COLLECT cut in two (fused spatiotemporal pass): the neighbour search is a chain of
-// loads per pixel, the target functions are BSDF evaluations that do not depend on each other.
-enum { RESTIR_INLINE = 0, RESTIR_COLLECT = 1, RESTIR_RESOLVE = 2, RESTIR_SEARCH = 3 };
+enum { RESTIR_INLINE = 0, RESTIR_COLLECT = 1, RESTIR_RESOLVE = 2 };
 struct RestirSites
 {
     const RestirScratch* scratch = nullptr;

@@ -403,7 +403,7 @@ template <int MODE = RESTIR_INLINE>
 PT_DEV void restir_spatiotemporal_pixel(const HIPRTRenderData& rd, int2 res, uint32_t x, uint32_t y, const RestirSites sites = RestirSites())
 {
     const uint32_t center_pixel_index = x + y * res.x;
-    if (MODE == RESTIR_COLLECT || MODE == RESTIR_SEARCH)
+    if (MODE == RESTIR_COLLECT)
         sites.scratch->status[sites.pixel] = 0u;
     if (!rd.aux_buffers.pixel_active[center_pixel_index] || !rd.g_buffer.camera_ray_hit[center_pixel_index])
         return;
@@ -418,12 +418,8 @@ PT_DEV void restir_spatiotemporal_pixel(const HIPRTRenderData& rd, int2 res, uin
     get_pixel_surface<MODE != RESTIR_RESOLVE>(rd, center_pixel_index, false, center);
     if (MODE != RESTIR_RESOLVE && material_is_emissive(center.material))
         return;
-    if (MODE == RESTIR_COLLECT || MODE == RESTIR_SEARCH)
+    if (MODE == RESTIR_COLLECT)
         sites.scratch->status[sites.pixel] = 1u;
-    // SEARCH: the neighbours restir_spatiotemporal_sites evaluates, [0] temporal, [1 + i] spatial neighbour i (pixel index, bit 30 = with the visibility term; -1 none)
-    int search_work[1 + kRestirMaxNeighbors];
-    for (int k = 0; k < 1 + kRestirMaxNeighbors; k++)
-        search_work[k] = -1;
 
     if (rs.temporal_pass.temporal_buffer_clear_requested)
         store_reservoir(rs.temporal_pass.input_reservoirs + center_pixel_index, empty_reservoir());
@@ -438,7 +434,7 @@ PT_DEV void restir_spatiotemporal_pixel(const HIPRTRenderData& rd, int2 res, uin
     {
         temporal_neighbor_reservoir = load_reservoir(rs.temporal_pass.input_reservoirs + temporal.x);
         if (temporal_neighbor_reservoir.M != 0)
-            get_pixel_surface<MODE != RESTIR_RESOLVE && MODE != RESTIR_SEARCH>(rd, temporal.x, prev_g, temporal_neighbor_surface);
+            get_pixel_surface<MODE != RESTIR_RESOLVE>(rd, temporal.x, prev_g, temporal_neighbor_surface);
     }
     const int2 temporal_position = make_int2(temporal.y, temporal.z);
 
@@ -474,12 +470,7 @@ PT_DEV void restir_spatiotemporal_pixel(const HIPRTRenderData& rd, int2 res, uin
     const bool update_mc = initial_candidates_reservoir.M > 0 && initial_candidates_reservoir.UCW > 0.0f;
 
     // temporal neighbour (:206-290)
-    if (MODE == RESTIR_SEARCH)
-    {
-        if (temporal.x != -1 && temporal_neighbor_reservoir.M > 0)
-            search_work[0] = temporal.x;
-    }
-    else if (temporal.x != -1 && temporal_neighbor_reservoir.M > 0)
+    if (temporal.x != -1 && temporal_neighbor_reservoir.M > 0)
     {
         float target_function_at_center = 0.0f;
         if (temporal_neighbor_reservoir.UCW > 0.0f)
@@ -517,16 +508,10 @@ PT_DEV void restir_spatiotemporal_pixel(const HIPRTRenderData& rd, int2 res, uin
             if (!restir_check_neighbor_similarity_heuristics(rd, neighbor_pixel_index, center_pixel_index, center.shading_point, center.shading_normal, prev_g))
                 continue;
 
-        const bool do_neighbor_target_function_visibility = restir_include_spatial_visibility(rd, spatial_neighbor_index, reused_neighbors_count);
-        if (MODE == RESTIR_SEARCH)
-        {
-            if (!canonical)
-                search_work[1 + spatial_neighbor_index] = neighbor_pixel_index | (do_neighbor_target_function_visibility ? 0x40000000 : 0);
-            continue;
-        }
         ReSTIRDIReservoir neighbor_reservoir = canonical ? initial_candidates_reservoir : load_reservoir(spatial_input + neighbor_pixel_index);
 
         float target_function_at_center = 0.0f;
+        const bool do_neighbor_target_function_visibility = restir_include_spatial_visibility(rd, spatial_neighbor_index, reused_neighbors_count);
         if (neighbor_reservoir.UCW > 0.0f)
         {
             if (canonical)
@@ -581,13 +566,6 @@ PT_DEV void restir_spatiotemporal_pixel(const HIPRTRenderData& rd, int2 res, uin
             }
         }
     }
-    if (MODE == RESTIR_SEARCH)
-    {
-        float4* work = sites.scratch->ic_state + sites.pixel;       // the initial-candidates state is dead by now: two planes hold the six entries
-        work[0] = make_float4(__int_as_float(search_work[0]), __int_as_float(search_work[1]), __int_as_float(search_work[2]), __int_as_float(search_work[3]));
-        work[sites.scratch->capacity] = make_float4(__int_as_float(search_work[4]), __int_as_float(search_work[5]), 0.0f, 0.0f);
-        return;
-    }
     if (MODE == RESTIR_COLLECT)
         return;
 
@@ -606,50 +584,6 @@ PT_DEV void restir_spatiotemporal_pixel(const HIPRTRenderData& rd, int2 res, uin
     if (rs.m_cap > 0)
         out.M = mini(out.M, rs.m_cap);
     store_reservoir(rs.spatial_pass.output_reservoirs + center_pixel_index, out);
-}
-
-// Second half of COLLECT for the fused pass, one thread per (pixel, neighbour k): k = 0 the temporal neighbour, k = 1 + i spatial neighbour i
-// (the list SEARCH left). Exactly what restir_spatiotemporal_pixel<RESTIR_COLLECT> evaluates for that neighbour: the neighbour's sample seen from
-// the pixel (site 2 k; for a neighbour without the visibility term also the ray of the end-of-pass visibility reuse), and -- where the
-// pairwise weights update m_c (PairwiseDefensiveMISWeight::get) -- the pixel's own sample seen from the neighbour's surface (site 2 k + 1).
-PT_DEV void restir_spatiotemporal_sites(const HIPRTRenderData& rd, int2 res, uint32_t x, uint32_t y, const RestirSites sites, int k)
-{
-    if (sites.scratch->status[sites.pixel] == 0u)
-        return;
-    const float4 plane = sites.scratch->ic_state[(size_t)(k >> 2) * sites.scratch->capacity + sites.pixel];
-    const int work = __float_as_int((k & 3) == 0 ? plane.x : (k & 3) == 1 ? plane.y : (k & 3) == 2 ? plane.z : plane.w);
-    if (work < 0)
-        return;
-    const uint32_t center_pixel_index = x + y * res.x;
-    const ReSTIRDISettings& rs = rd.render_settings.restir_di_settings;
-    const int neighbor_pixel_index = work & 0x3FFFFFFF;
-    const bool with_visibility = k == 0 || (work & 0x40000000) != 0;
-    Rng rng(0u);        // shadow rays draw random numbers only with alpha testing, which the phased passes exclude
-    const ReSTIRDIReservoir initial_candidates_reservoir = load_reservoir(rs.initial_candidates.output_reservoirs + center_pixel_index);
-    const bool update_mc = initial_candidates_reservoir.M > 0 && initial_candidates_reservoir.UCW > 0.0f;
-    const ReSTIRDIReservoir neighbor_reservoir = load_reservoir((k == 0 ? rs.temporal_pass.input_reservoirs : rs.spatial_pass.input_reservoirs) + neighbor_pixel_index);
-    const int site = 2 * k;
-    if (neighbor_reservoir.UCW > 0.0f)
-    {
-        ReSTIRSurface center;
-        get_pixel_surface(rd, center_pixel_index, false, center);
-        if (with_visibility)
-            restir_evaluate_target_function<true, RESTIR_COLLECT>(rd, neighbor_reservoir.sample, center, rng, sites, site);
-        else
-        {
-            restir_evaluate_target_function<false, RESTIR_COLLECT>(rd, neighbor_reservoir.sample, center, rng, sites, site);
-            float distance_to_light;
-            float3 sample_direction;
-            restir_visibility_reuse_ray(rd, neighbor_reservoir.sample, center.shading_point, sample_direction, distance_to_light);
-            sites.emit_any_hit(site, center.shading_point, sample_direction, distance_to_light, center.last_hit_primitive_index);
-        }
-    }
-    if (update_mc)
-    {
-        ReSTIRSurface neighbor_surface;
-        get_pixel_surface(rd, neighbor_pixel_index, use_prev_frame_g_buffer(rd), neighbor_surface);
-        restir_evaluate_target_function<true, RESTIR_COLLECT>(rd, initial_candidates_reservoir.sample, neighbor_surface, rng, sites, site + 1);
-    }
 }
 
 // ---- ReSTIR_DI_TemporalReuse (TemporalReuse.h:48-306): the non-fused configuration's temporal pass ---------------------------------

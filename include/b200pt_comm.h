@@ -39,7 +39,7 @@ B200PT_API int b200pt_comm_tile(int sharding, int width, int height, int world, 
  * reports what its band cost (e.g. the milliseconds of its launches, shared with b200pt_comm_allreduce_host_f64) and all ranks compute the same
  * new plan. bounds / out_bounds: world + 1 entries, band r = [bounds[r], bounds[r + 1]), bounds[0] = 0, bounds[world] = extent. The cost is
  * taken as uniform inside each old band; new boundaries are multiples of `align` pixels, bands stay at least `align` wide while the image has
- * that many blocks. Iterate over a few frames. No communicator needed. Tiles only change which rank renders a pixel, never its value. */
+ * that many blocks; out_bounds may be the bounds array itself. Iterate over a few frames. No communicator needed. Tiles only change which rank renders a pixel, never its value. */
 B200PT_API int b200pt_comm_balanced_bounds(const int* bounds, const double* cost, int world, int extent, int align, int* out_bounds);
 /* The column plan b200pt_comm_gather_tiles uses from now on for images `bounds[world]` pixels wide (NULL: back to b200pt_comm_tile's). */
 B200PT_API int b200pt_comm_set_column_bounds(b200pt_comm* comm, const int* bounds);

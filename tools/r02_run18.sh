@@ -23,6 +23,6 @@ run c4_lanes2 many_lights B200PT_PATH_LANES=2
 run c4_lanes3 many_lights B200PT_PATH_LANES=3
 run c4_lanes2_q24 many_lights B200PT_PATH_LANES=2 B200PT_QUEUE_BLOCKS_PER_SM=24
 W=many_lights
-ncu --set full --clock-control none --import-source on -k regex:"k_ReSTIR_DI" --launch-skip 21 -c 7 -f -o /tmp/p_restir python bench.py --profile --steps 1 --samples-per-frame 1 --workload $W > $O/p18_${W}_ncu_restir.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:"k_ReSTIR_DI" --launch-skip 27 -c 9 -f -o /tmp/p_restir python bench.py --profile --steps 1 --samples-per-frame 1 --workload $W > $O/p18_${W}_ncu_restir.log 2>&1
 python tools/ncu_summary.py /tmp/p_restir.ncu-rep > $O/p18_${W}_restir_phased_full.txt 2>&1
 grep -E "^kernel|gpu__time_duration|registers_per_thread|smsp__issue_active|thread_inst_executed_per_inst_executed.ratio|long_scoreboard_per|dram__bytes_read|sm__warps_active" $O/p18_${W}_restir_phased_full.txt | head -60
