@@ -95,7 +95,7 @@ enum PhaseKernel { PHASE_NEE_LIGHT_EVAL, PHASE_NEE_BSDF_SAMPLE, PHASE_ENV_LIGHT_
 cudaError_t PT_VARIANT_NAME(launch_phase)(int which, unsigned blocks, cudaStream_t stream, const HIPRTRenderData* rd, int2 res, Tile tile, const WavefrontState* wf, int bounce,
                                           bool lights_sampled, bool envmap_sampled);
 // SURFACE waits on two dependent scattered fetches per path (triangle indices -> vertex normals / texcoords, material index -> material): ncu on C3
-// shows 22 % issue-active with 12 warps per issue on a long scoreboard at 96 registers = 20 warps per SM (profiles/r02_shade_c3_spf16.txt).
+// shows 22 % issue-active with 12 warps per issue on a long scoreboard at 96 registers = 20 warps per SM (profiles/r02_shade_c3_final.txt).
 // More resident warps by capping the registers did not pay: at 7 blocks per SM (72 registers) the stage went 24.0 -> 27.1 ms (gpurun call 19).
 #ifndef PT_SURFACE_BLOCKS_PER_SM
 #define PT_SURFACE_BLOCKS_PER_SM 1
