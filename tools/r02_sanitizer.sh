@@ -1,4 +1,5 @@
 #!/bin/bash
+# NOTE: compute-sanitizer is closed on the GPU pool of this project (it prints "closed on this pool and stays closed" and exits 86): kept for pools where it runs.
 # compute-sanitizer pass over every kernel family: memcheck (out-of-bounds / misaligned accesses, leaks at exit) on the
 # whole tour, racecheck (shared-memory hazards: the traversal kernel's shared stacks, the scan kernels) and initcheck on the Cornell part.
 cd "$GRAFT_REPO_ROOT"
