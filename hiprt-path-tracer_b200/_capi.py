@@ -86,6 +86,11 @@ COMM_API_SYMBOLS = [
     "b200pt_comm_gather_tiles", "b200pt_comm_exchange_halo", "b200pt_comm_allreduce_sum", "b200pt_comm_allreduce_host_f64", "b200pt_comm_barrier",
     "b200pt_comm_balanced_bounds", "b200pt_comm_set_column_bounds",
 ]
+# include/b200pt_bake.h (directional-albedo LUT bakers; part of libb200pt.so)
+BAKE_API_SYMBOLS = [
+    "b200pt_bake_plan_for", "b200pt_bake_ggx_conductor_directional_albedo", "b200pt_bake_ggx_fresnel_directional_albedo",
+    "b200pt_bake_glossy_dielectric_directional_albedo", "b200pt_bake_ggx_glass_directional_albedo", "b200pt_bake_ggx_thin_glass_directional_albedo",
+]
 HOST_API_SYMBOLS = [
     "b200pt_host_last_error", "b200pt_renderer_create", "b200pt_renderer_destroy", "b200pt_renderer_set_seed_schedule", "b200pt_renderer_set_rng_seed",
     "b200pt_renderer_set_kernel_options", "b200pt_renderer_set_brdf_luts", "b200pt_renderer_add_texture", "b200pt_renderer_set_scene",

@@ -71,7 +71,8 @@ def build(force=False, verbose=False):
             jobs.append((o, [NVCC, *NVCC_FLAGS, *extra, "-MD", "-MF", o[:-2] + ".d", "-c", os.path.join(CSRC, src), "-o", o]))
         return o
 
-    objects = [add("bvh8_build.o", "bvh8_build.cpp", ["-x", "cu"]), add("bvh8_build_device.o", "bvh8_build_device.cu"), add("capi.o", "b200pt_capi.cu")]
+    objects = [add("bvh8_build.o", "bvh8_build.cpp", ["-x", "cu"]), add("bvh8_build_device.o", "bvh8_build_device.cu"), add("capi.o", "b200pt_capi.cu"),
+               add("bake.o", "b200pt_bake.cu")]
     for suffix, defs in (("t", []), ("c", ["-DPT_COUNTERS"])):
         objects.append(add(f"kernels_{suffix}.o", "b200pt_kernels.cu", defs))
         for (lss, ess, later, ggx) in variants():

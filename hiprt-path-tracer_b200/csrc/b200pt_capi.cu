@@ -371,3 +371,4 @@ int b200pt_event_elapsed_ms(b200pt_ctx* ctx, b200pt_event start, b200pt_event st
 #include "b200pt_capi_scene.inl"
 #include "b200pt_capi_noalloc.inl"
 #include "b200pt_capi_comm.inl"
+#include "b200pt_capi_bake.inl"

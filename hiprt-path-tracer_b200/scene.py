@@ -5,7 +5,13 @@ ASSIMP (the reference's importer, pinned TomClabault/assimp@c867ddbc) is absent 
 below restates what SceneParser::parse_scene_file (src/Scene/SceneParser.cpp:22-253, 362-407) obtains from it: one mesh
 per material with node transforms pre-applied (aiProcess_PreTransformVertices), material factors mapped like ASSIMP's
 glTF2 importer maps them, emissive triangles listed per ThreadFunctions.cpp:116-143. Import parity is "unpinned" (no
-reference test pins it); the SAME arrays feed the oracle and the CUDA path, so import differences cancel in parity."""
+reference test pins it); the SAME arrays feed the oracle and the CUDA path, so import differences cancel in parity.
+
+Textures (SURVEY.md 8(f) rank 4): the 8-bit texture pipeline of SceneParser::prepare_textures / assign_material_texture_indices
+(SceneParser.cpp:277-353, 409-471) and ThreadFunctions::load_scene_texture (src/Threads/ThreadFunctions.cpp:30-114) is restated below:
+per material the reference's slot order and global index offsets, its channel count per slot, constant emissive textures folded into
+the material's emission. Files are decoded with Pillow in place of stb_image and converted between channel counts by stb_image's rules;
+tests/test_scene_import.py checks the decode against the reference's own loader (oracle/ref_image.cpp) on the textures it ships."""
 import ctypes as C
 import json
 import os
@@ -134,6 +140,147 @@ class Scene:
         self.material_indices = np.concatenate([self.material_indices, np.full(len(indices) // 3, material_index, np.int32)])
 
 
+# ---- 8-bit textures (src/Image/Image.cpp, src/Threads/ThreadFunctions.cpp) ----------------------------
+NO_TEXTURE = -1                    # RendererMaterial::NO_TEXTURE (src/HostDeviceCommon/Material.h:231)
+CONSTANT_EMISSIVE_TEXTURE = -2     # RendererMaterial::CONSTANT_EMISSIVE_TEXTURE (Material.h:237)
+
+
+def convert_channels(texels, output_channels):
+    """stb_image's stbi__convert_format: what Image8Bit::read_image(path, output_channels) gets when the file has another channel count.
+    Grey from colour is the integer luma (77 r + 150 g + 29 b) >> 8, a missing alpha is 255, grey replicates into r, g, b."""
+    texels = np.asarray(texels, np.uint8)
+    if texels.ndim == 2:
+        texels = texels[:, :, None]
+    n = texels.shape[2]
+    if n == output_channels:
+        return np.ascontiguousarray(texels)
+    h, w = texels.shape[:2]
+    alpha = texels[:, :, n - 1] if n in (2, 4) else np.full((h, w), 255, np.uint8)
+    if n >= 3:
+        rgb = texels[:, :, :3]
+        grey = ((rgb[:, :, 0].astype(np.uint32) * 77 + rgb[:, :, 1].astype(np.uint32) * 150 + rgb[:, :, 2].astype(np.uint32) * 29) >> 8).astype(np.uint8)
+    else:
+        grey = texels[:, :, 0]
+        rgb = np.repeat(grey[:, :, None], 3, axis=2)
+    if output_channels == 1:
+        out = grey[:, :, None]
+    elif output_channels == 2:
+        out = np.stack([grey, alpha], axis=2)
+    elif output_channels == 3:
+        out = rgb
+    elif output_channels == 4:
+        out = np.concatenate([rgb, alpha[:, :, None]], axis=2)
+    else:
+        raise ValueError("output_channels must be 1..4")
+    return np.ascontiguousarray(out)
+
+
+def read_image_8bit(path, output_channels):
+    """Image8Bit::read_image(path, output_channels, flipY = false) (src/Image/Image.cpp:33-61): rows top to bottom, 8 bits per channel."""
+    from PIL import Image
+    with Image.open(path) as im:
+        if im.mode in ("1", "I", "I;16", "I;16B", "I;16L", "F"):
+            # 16-bit files: stb_image keeps the high byte
+            arr = np.asarray(im.convert("I"), np.int64)
+            texels = (np.clip(arr, 0, 65535) >> 8).astype(np.uint8) if im.mode != "1" else (np.asarray(im.convert("L")))
+        elif im.mode == "P":
+            texels = np.asarray(im.convert("RGBA" if "transparency" in im.info else "RGB"))
+        elif im.mode in ("L", "LA", "RGB", "RGBA"):
+            texels = np.asarray(im)
+        else:   # CMYK, YCbCr, ...
+            texels = np.asarray(im.convert("RGB"))
+    return convert_channels(texels, output_channels)
+
+
+def image_is_constant_color(texels, threshold=5):
+    """Image8Bit::is_constant_color (Image.cpp:250-271): every channel of every texel within `threshold` of the first texel."""
+    if texels.size == 0:
+        return False
+    first = texels[0, 0].astype(np.int32)
+    return bool((np.abs(texels.astype(np.int32) - first) <= threshold).all())
+
+
+def image_sample_rgba32f(texels, u, v):
+    """Image8Bit::sample_rgba32f (Image.cpp:161-195): repeat addressing, v flipped, x = int(u (w - 1)), nearest texel, / 255."""
+    u, v = np.float32(u), np.float32(v)
+    if u != 1.0:
+        u = np.float32(u - int(u))
+    if v != 1.0:
+        v = np.float32(v - int(v))
+    u = np.float32(1.0 + u) if u < 0 else u
+    v = np.float32(1.0 + v) if v < 0 else v
+    v = np.float32(1.0) - v
+    h, w = texels.shape[:2]
+    x, y = int(u * np.float32(w - 1)), int(v * np.float32(h - 1))
+    out = np.zeros(4, np.float32)
+    out[:texels.shape[2]] = texels[y, x].astype(np.float32) / np.float32(255.0)
+    return out
+
+
+# Texture slots in the order SceneParser::get_textures_paths_and_indices queries them (SceneParser.cpp:409-447), with the channel count
+# ThreadFunctions::load_scene_texture asks for (ThreadFunctions.cpp:43-89). "roughness_metallic" is the packed glTF texture: ASSIMP reports
+# pbrMetallicRoughness.metallicRoughnessTexture as DIFFUSE_ROUGHNESS and as METALNESS with one path, which the parser folds into one 3-channel load.
+TEXTURE_SLOTS = (("base_color", 4), ("emission", 4), ("roughness_metallic", 3), ("roughness", 1), ("metallic", 1), ("specular", 1), ("coat", 1), ("sheen", 1),
+                 ("specular_transmission", 1), ("normal_map", 4))
+
+
+def _gltf_texture_uri(g, info):
+    if not info or "index" not in info:
+        return None
+    tex = g["textures"][info["index"]]
+    if "source" not in tex:
+        return None
+    uri = g["images"][tex["source"]].get("uri")
+    if not uri or uri.startswith("data:"):
+        return None
+    return uri.replace("%20", " ")          # SceneParser::normalize_texture_paths (SceneParser.cpp:472-490)
+
+
+def _gltf_material_textures(g, gm):
+    """(slot, uri) of one material, in the order the reference pushes them into its texture list."""
+    pbr = gm.get("pbrMetallicRoughness", {})
+    ext = gm.get("extensions", {})
+    found = {
+        "base_color": _gltf_texture_uri(g, pbr.get("baseColorTexture")),
+        "emission": _gltf_texture_uri(g, gm.get("emissiveTexture")),
+        "roughness_metallic": _gltf_texture_uri(g, pbr.get("metallicRoughnessTexture")),
+        "specular": _gltf_texture_uri(g, ext.get("KHR_materials_specular", {}).get("specularTexture")),
+        "coat": _gltf_texture_uri(g, ext.get("KHR_materials_clearcoat", {}).get("clearcoatTexture")),
+        "sheen": _gltf_texture_uri(g, ext.get("KHR_materials_sheen", {}).get("sheenColorTexture")),
+        "specular_transmission": _gltf_texture_uri(g, ext.get("KHR_materials_transmission", {}).get("transmissionTexture")),
+        "normal_map": _gltf_texture_uri(g, gm.get("normalTexture")),
+    }
+    return [(slot, found[slot]) for slot, _ in TEXTURE_SLOTS if found.get(slot)]
+
+
+def import_textures(scene, material_textures, base_directory, read_image=read_image_8bit):
+    """prepare_textures + assign_material_texture_indices + load_scene_texture for `material_textures[i]` = [(slot, path)] of material i.
+    Fills scene.textures (one (h, w, c) uint8 array per listed texture; a constant emissive texture leaves an empty 1x1 placeholder, like the
+    default-constructed Image8Bit the reference leaves there) and the *_texture_index members of the materials."""
+    channels = dict(TEXTURE_SLOTS)
+    offset = 0
+    scene.textures = []
+    scene.texture_paths = []
+    for material_index, listed in enumerate(material_textures):
+        m = scene.materials[material_index]
+        for local, (slot, path) in enumerate(listed):
+            setattr(m, slot + "_texture_index", local + offset)
+            full = os.path.join(base_directory, path)
+            texels = read_image(full, channels[slot])
+            if slot == "emission" and image_is_constant_color(texels, 5):
+                # ThreadFunctions.cpp:91-101: the texture is not kept; its colour becomes the material's emission
+                m.emission_texture_index = CONSTANT_EMISSIVE_TEXTURE
+                c = image_sample_rgba32f(texels, 0.0, 0.0)
+                m.base.emission.set(float(c[0]), float(c[1]), float(c[2]))
+                texels = np.zeros((1, 1, channels[slot]), np.uint8)
+            scene.textures.append(texels)
+            scene.texture_paths.append(full)
+        offset += len(listed)
+    # emissive_texture_used stays false on the host (only get_intersection_material sets it, Device/includes/Material.h:82), so
+    # load_scene_parse_emissive_triangles lists the triangles of a material with a non-zero emission factor whatever its textures
+    return scene
+
+
 # ---- glTF 2.0 loader shim ---------------------------------------------------------------------------
 _COMPONENT = {5120: np.int8, 5121: np.uint8, 5122: np.int16, 5123: np.uint16, 5125: np.uint32, 5126: np.float32}
 _NCOMP = {"SCALAR": 1, "VEC2": 2, "VEC3": 3, "VEC4": 4, "MAT4": 16}
@@ -197,7 +344,7 @@ def _gltf_material(gm):
     return make_safe(m)
 
 
-def load_gltf(path):
+def load_gltf(path, load_textures=True):
     g = json.load(open(path))
     base = os.path.dirname(path)
     buffers = [np.fromfile(os.path.join(base, b["uri"]), dtype=np.uint8) for b in g["buffers"]]
@@ -220,6 +367,7 @@ def load_gltf(path):
     scene = Scene()
     scene.name = os.path.basename(path)
     scene.materials = [_gltf_material(m) for m in g.get("materials", [])]
+    material_textures = [_gltf_material_textures(g, m) if load_textures else [] for m in g.get("materials", [])]
 
     # Walk the node hierarchy; collect (primitive, world matrix) instances and the first camera
     instances = []
@@ -251,9 +399,16 @@ def load_gltf(path):
             nrm = accessor(prim["attributes"]["NORMAL"]).astype(np.float64) @ nm.T
             nrm = (nrm / np.maximum(np.linalg.norm(nrm, axis=1, keepdims=True), 1e-30)).astype(np.float32)
         idx = accessor(prim["indices"]).reshape(-1) if "indices" in prim else np.arange(len(pos))
-        # texcoords are only kept when the material has textures (SceneParser.cpp:136-140); none of the shipped scenes has any
-        scene.append_mesh(pos, idx, nrm, prim.get("material", 0))
+        # texcoords are only kept when the material has textures (SceneParser.cpp:136-140); ASSIMP's glTF2 importer flips v (y = 1 - y)
+        tc = None
+        mi = prim.get("material", 0)
+        if "TEXCOORD_0" in prim["attributes"] and mi < len(material_textures) and len(material_textures[mi]) > 0:
+            tc = accessor(prim["attributes"]["TEXCOORD_0"]).astype(np.float32)
+            tc = np.stack([tc[:, 0], np.float32(1.0) - tc[:, 1]], axis=1)
+        scene.append_mesh(pos, idx, nrm, mi, tc)
 
+    if any(material_textures):
+        import_textures(scene, material_textures, base)
     scene.compute_emissive_triangles()
 
     if camera is not None:
@@ -324,9 +479,10 @@ def scene_camera(scene, width, height, jitter=True):
 def save_scene(scene, path):
     a = scene.arrays()
     cam = scene.camera or {}
-    np.savez_compressed(path, material_count=scene.material_count, name=scene.name,
+    textures = {f"texture_{i}": np.ascontiguousarray(t, np.uint8) for i, t in enumerate(scene.textures)}
+    np.savez_compressed(path, material_count=scene.material_count, name=scene.name, texture_count=len(scene.textures),
                         camera_keys=np.array(sorted(cam.keys())), camera_values=np.array([np.asarray(cam[k], np.float64).ravel() for k in sorted(cam.keys())], dtype=object),
-                        **a)
+                        **a, **textures)
 
 
 def load_scene(path):
@@ -338,6 +494,7 @@ def load_scene(path):
     raw = np.ascontiguousarray(z["materials"])
     n = int(z["material_count"])
     s.materials = [S.RendererMaterial.from_buffer_copy(raw[i].tobytes()) for i in range(n)]
+    s.textures = [z[f"texture_{i}"] for i in range(int(z["texture_count"]) if "texture_count" in z.files else 0)]
     keys = [str(k) for k in z["camera_keys"]]
     if keys:
         vals = z["camera_values"]

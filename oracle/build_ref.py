@@ -43,6 +43,9 @@ VARIANTS = {
                           "PrincipledBSDFAnisotropicGGXSampleFunction": "GGX_VNDF_SPHERICAL_CAPS"},
 }
 
+# bake oracle name -> the variant whose KernelOptions overlay it is compiled with (only PrincipledBSDFAnisotropicGGXSampleFunction matters there)
+BAKE_VARIANTS = {"vndf": "mis", "caps": "mis_caps"}
+
 CXXFLAGS = ["-std=c++20", "-O2", "-fopenmp", "-ffp-contract=off", "-fPIC", "-w"]
 
 
@@ -126,6 +129,22 @@ def build(variants=None, force=False):
         if force or not newer(o, harness_src + [os.path.join(overlay, "HostDeviceCommon/KernelOptions.h")]):
             jobs.append(["g++", *CXXFLAGS, *includes(overlay), "-c", harness_src[0], "-o", o])
 
+    # the reference's LUT bake kernels (src/Device/kernels/Baking/*.h) behind oracle/ref_bake.cpp, once per GGX sampling routine
+    bake_src = os.path.join(HERE, "ref_bake.cpp")
+    bake_objs = {}
+    for name, v in BAKE_VARIANTS.items():
+        overlay = make_overlay(v, VARIANTS[v])
+        o = os.path.join(OUT, f"bake_{name}.o")
+        bake_objs[name] = o
+        if force or not newer(o, [bake_src, os.path.join(overlay, "HostDeviceCommon/KernelOptions.h")]):
+            jobs.append(["g++", *CXXFLAGS, *includes(overlay), "-c", bake_src, "-o", o])
+
+    # the reference's 8-bit texture loader behind oracle/ref_image.cpp
+    image_src = os.path.join(HERE, "ref_image.cpp")
+    image_obj = os.path.join(OUT, "ref_image.o")
+    if force or not newer(image_obj, [image_src]):
+        jobs.append(["g++", *CXXFLAGS, *includes(), "-c", image_src, "-o", image_obj])
+
     with ThreadPoolExecutor(max_workers=os.cpu_count() or 4) as ex:
         list(ex.map(run, jobs))
 
@@ -135,6 +154,17 @@ def build(variants=None, force=False):
         deps = [harness_objs[v]] + [os.path.join(OUT, o) for o in common]
         if force or not newer(so, deps):
             run(["g++", "-shared", "-fopenmp", wrap, "-o", so, *deps])
+        print(f"[oracle] {so}")
+    so = os.path.join(OUT, "libhippt_ref_image.so")
+    deps = [image_obj] + [os.path.join(OUT, c) for c in common]
+    if force or not newer(so, deps):
+        run(["g++", "-shared", "-fopenmp", "-o", so, *deps])
+    print(f"[oracle] {so}")
+    for name, o in bake_objs.items():
+        so = os.path.join(OUT, f"libhippt_ref_bake_{name}.so")
+        deps = [o] + [os.path.join(OUT, c) for c in common]
+        if force or not newer(so, deps):
+            run(["g++", "-shared", "-fopenmp", "-o", so, *deps])
         print(f"[oracle] {so}")
     return True
 

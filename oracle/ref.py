@@ -43,6 +43,53 @@ def load(variant="mis"):
     return _libs[variant]
 
 
+def image_lib_path():
+    return os.path.join(REF_DIR, "libhippt_ref_image.so")
+
+
+def read_image_8bit(path, output_channels):
+    """Image8Bit::read_image(path, output_channels, flipY=false) of the reference (stb_image), oracle/ref_image.cpp.
+    Returns (texels[h, w, c] uint8, is_constant_color(5), sample_rgba32f((0, 0)))."""
+    if "image" not in _libs:
+        if not os.path.exists(image_lib_path()):
+            raise FileNotFoundError(f"{image_lib_path()} missing: run `python oracle/build_ref.py` where /root/reference exists")
+        _libs["image"] = C.CDLL(image_lib_path())
+    l = _libs["image"]
+    w, h, const = C.c_int(), C.c_int(), C.c_int()
+    rgba = (C.c_float * 4)()
+    if l.ref_read_image_8bit(path.encode(), output_channels, None, C.c_longlong(0), C.byref(w), C.byref(h), C.byref(const), rgba) != 0:
+        raise IOError(f"the reference's loader cannot read {path}")
+    out = np.empty((h.value, w.value, output_channels), np.uint8)
+    rc = l.ref_read_image_8bit(path.encode(), output_channels, out.ctypes.data_as(C.c_void_p), C.c_longlong(out.size), C.byref(w), C.byref(h), None, None)
+    assert rc == 0
+    return out, bool(const.value), np.array(list(rgba), np.float32)
+
+
+def bake_lib_path(sampler="vndf"):
+    return os.path.join(REF_DIR, f"libhippt_ref_bake_{sampler}.so")
+
+
+def bake(kind, size_cos_theta, size_roughness, size_ior, sample_count, sampler="vndf", z_range=None, plan_only=False):
+    """The reference's bake kernel `kind` (0 conductor, 1 Fresnel, 2 glossy dielectric, 3 glass entering, 4 glass exiting, 5 thin glass)
+    driven like GPUBakerKernel::bake_internal (oracle/ref_bake.cpp). Returns (table[z, y, x], iterations_per_kernel, nb_kernel_launch);
+    z_range = (begin, end) integrates only those ior slices (the rest of the table stays zero), plan_only returns table = None."""
+    key = "bake_" + sampler
+    if key not in _libs:
+        path = bake_lib_path(sampler)
+        if not os.path.exists(path):
+            raise FileNotFoundError(f"{path} missing: run `python oracle/build_ref.py` where /root/reference exists")
+        _libs[key] = C.CDLL(path)
+    sz = 1 if kind == 0 else size_ior
+    out = None if plan_only else np.zeros((sz, size_roughness, size_cos_theta), np.float32)
+    ipk, launches = C.c_int(), C.c_int()
+    z0, z1 = z_range if z_range is not None else (0, sz)
+    rc = _libs[key].ref_bake(kind, size_cos_theta, size_roughness, sz, sample_count, z0, z1, out.ctypes.data_as(C.c_void_p) if out is not None else None,
+                             C.byref(ipk), C.byref(launches))
+    if rc != 0:
+        raise ValueError("ref_bake rejected its arguments")
+    return out, ipk.value, launches.value
+
+
 def _p(a):
     return a.ctypes.data_as(C.c_void_p) if a is not None else None
 

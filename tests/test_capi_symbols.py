@@ -28,6 +28,10 @@ def test_every_declared_symbol_is_exported(pt):
     assert len(commsyms) == 14 and sorted(capi.COMM_API_SYMBOLS) == commsyms
     for s in commsyms:
         assert hasattr(lib, s), s
+    bakesyms = _declared("b200pt_bake.h")            # the LUT bakers
+    assert len(bakesyms) == 6 and sorted(capi.BAKE_API_SYMBOLS) == bakesyms
+    for s in bakesyms:
+        assert hasattr(lib, s), s
 
 
 def test_no_cpu_fallback(pt):
