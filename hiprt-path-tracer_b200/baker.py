@@ -109,7 +109,8 @@ def write_table(table, output_filename, directory="."):
         names = [f"{i}{output_filename}" for i in range(table.shape[0])]
     for sl, name in zip(table, names):
         path = os.path.join(directory, name)
-        write_hdr(path, np.repeat(sl[:, :, None], 3, axis=2))
+        # NaN texels (the thin-glass table has some by the reference's own arithmetic) have no RGBE encoding: written as 0
+        write_hdr(path, np.repeat(np.nan_to_num(sl, nan=0.0, posinf=0.0, neginf=0.0)[:, :, None], 3, axis=2))
         paths.append(path)
     return paths
 

