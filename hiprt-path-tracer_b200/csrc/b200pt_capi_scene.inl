@@ -657,7 +657,7 @@ int b200pt_trace_queue(b200pt_ctx* ctx, b200pt_bvh* bvh, const float* d_rays, co
 
 int b200pt_set_trace_flavour(b200pt_ctx* ctx, int flavour)
 {
-    REQUIRE(ctx != nullptr && (flavour == -1 || flavour == 0 || flavour == 1 || (flavour >= 5 && flavour <= 7)));
+    REQUIRE(ctx != nullptr && (flavour == -1 || flavour == 0 || flavour == 1 || flavour == 2 || (flavour >= 5 && flavour <= 7)));
     pt::g_trace_flavour = flavour;
     return B200PT_SUCCESS;
 }

@@ -49,15 +49,18 @@ __global__ void PT_SUFFIXED(k_trace_shadow)(Bvh8Device bvh, const float* __restr
 
 // FLAVOUR 0: the classic loop (load, wait, test) at kTraceBlocksPerSM resident blocks; FLAVOUR 5 / 6 / 7: the pipelined loop
 // (trace_queue_body_pipelined) compiled for that many resident blocks per SM (95 / 80 / 72 registers: the loads in flight stay
-// live across the box tests, so fewer warps fit, each with more memory-level parallelism). B200PT_TRACE_PIPELINE selects at run time.
+// live across the box tests, so fewer warps fit, each with more memory-level parallelism); FLAVOUR 2: the classic loop WITH the
+// distance cull at pop time (trace_queue.cuh: PT_TRACE_POP_CULL; measured slower, kept for A/B). B200PT_TRACE_PIPELINE selects at run time.
 template <bool ANY_HIT, int FLAVOUR>
-__global__ void __launch_bounds__(kTraceBlock, FLAVOUR ? FLAVOUR : kTraceBlocksPerSM) PT_SUFFIXED(k_trace_queue)(const Bvh8Device* __restrict__ bvh, const __grid_constant__ RayQueueView q,
+__global__ void __launch_bounds__(kTraceBlock, FLAVOUR >= 5 ? FLAVOUR : kTraceBlocksPerSM) PT_SUFFIXED(k_trace_queue)(const Bvh8Device* __restrict__ bvh, const __grid_constant__ RayQueueView q,
                                                                                                               TraversalCounters* counters, unsigned refill_idle_lanes)
 {
     __shared__ uint2 shared_stack[kSharedStackEntries * kTraceBlock];
     const Bvh8Device b = *bvh;
-    if (FLAVOUR)
+    if (FLAVOUR >= 5)
         trace_queue_body_pipelined<ANY_HIT>(b, q, shared_stack, counters, refill_idle_lanes);
+    else if (FLAVOUR == 2)
+        trace_queue_body<ANY_HIT, true>(b, q, shared_stack, counters, refill_idle_lanes);
     else
         trace_queue_body<ANY_HIT>(b, q, shared_stack, counters, refill_idle_lanes);
 }
@@ -67,16 +70,21 @@ __global__ void __launch_bounds__(kTraceBlock, FLAVOUR ? FLAVOUR : kTraceBlocksP
 // profiles/r01_launches_c2_bench_profile.txt): the NEE shadow rays and the NEE light rays of a bounce do not depend on each
 // other, so the second queue's rays fill the lanes the first queue's stragglers leave idle instead of paying that tail twice.
 template <int FLAVOUR>
-__global__ void __launch_bounds__(kTraceBlock, FLAVOUR ? FLAVOUR : kTraceBlocksPerSM) PT_SUFFIXED(k_trace_queue_pair)(const Bvh8Device* __restrict__ bvh, const __grid_constant__ RayQueueView q_any,
+__global__ void __launch_bounds__(kTraceBlock, FLAVOUR >= 5 ? FLAVOUR : kTraceBlocksPerSM) PT_SUFFIXED(k_trace_queue_pair)(const Bvh8Device* __restrict__ bvh, const __grid_constant__ RayQueueView q_any,
                                                                                                                    const __grid_constant__ RayQueueView q_closest, TraversalCounters* counters,
                                                                                                                    unsigned refill_idle_lanes)
 {
     __shared__ uint2 shared_stack[kSharedStackEntries * kTraceBlock];
     const Bvh8Device b = *bvh;
-    if (FLAVOUR)
+    if (FLAVOUR >= 5)
     {
         trace_queue_body_pipelined<true>(b, q_any, shared_stack, counters, refill_idle_lanes);
         trace_queue_body_pipelined<false>(b, q_closest, shared_stack, counters, refill_idle_lanes);
+    }
+    else if (FLAVOUR == 2)
+    {
+        trace_queue_body<true, true>(b, q_any, shared_stack, counters, refill_idle_lanes);
+        trace_queue_body<false, true>(b, q_closest, shared_stack, counters, refill_idle_lanes);
     }
     else
     {
@@ -91,14 +99,14 @@ static int trace_knob_flavour()
 {
     static const int from_env = [] { const char* e = getenv("B200PT_TRACE_PIPELINE"); return e ? atoi(e) : PT_TRACE_PIPELINED_DEFAULT; }();
     const int n = g_trace_flavour >= 0 ? g_trace_flavour : from_env;
-    return n == 5 || n == 6 || n == 7 ? n : (n == 1 ? 6 : 0);
+    return n == 5 || n == 6 || n == 7 || n == 2 ? n : (n == 1 ? 6 : 0);
 }
 static unsigned trace_knob_grid(unsigned blocks)
 {
     static const unsigned pct = [] { const char* v = getenv("B200PT_TRACE_GRID_PCT"); int n = v ? atoi(v) : 0; return n > 0 ? (unsigned)n : 100u; }();
     // `blocks` is sized for kTraceBlocksPerSM resident blocks per SM: a flavour with fewer resident blocks starts fewer
     const int flavour = trace_knob_flavour();
-    const unsigned resident = flavour ? blocks * (unsigned)flavour / (unsigned)kTraceBlocksPerSM : blocks;
+    const unsigned resident = flavour >= 5 ? blocks * (unsigned)flavour / (unsigned)kTraceBlocksPerSM : blocks;
     const unsigned scaled = resident * pct / 100u;
     return scaled > 0u ? scaled : 1u;
 }
@@ -113,6 +121,7 @@ cudaError_t PT_SUFFIXED(launch_trace_queue_pair)(const void* bvh_device_handle, 
     case 5: PT_SUFFIXED(k_trace_queue_pair)<5><<<blocks, kTraceBlock, 0, stream>>>(bvh, q_any, q_closest, counters, refill); break;
     case 6: PT_SUFFIXED(k_trace_queue_pair)<6><<<blocks, kTraceBlock, 0, stream>>>(bvh, q_any, q_closest, counters, refill); break;
     case 7: PT_SUFFIXED(k_trace_queue_pair)<7><<<blocks, kTraceBlock, 0, stream>>>(bvh, q_any, q_closest, counters, refill); break;
+    case 2: PT_SUFFIXED(k_trace_queue_pair)<2><<<blocks, kTraceBlock, 0, stream>>>(bvh, q_any, q_closest, counters, refill); break;
     default: PT_SUFFIXED(k_trace_queue_pair)<0><<<blocks, kTraceBlock, 0, stream>>>(bvh, q_any, q_closest, counters, refill); break;
     }
     return cudaGetLastError();
@@ -126,6 +135,7 @@ static void launch_trace_queue_flavour(const Bvh8Device* bvh, const RayQueueView
     case 5: PT_SUFFIXED(k_trace_queue)<ANY_HIT, 5><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters, refill); break;
     case 6: PT_SUFFIXED(k_trace_queue)<ANY_HIT, 6><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters, refill); break;
     case 7: PT_SUFFIXED(k_trace_queue)<ANY_HIT, 7><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters, refill); break;
+    case 2: PT_SUFFIXED(k_trace_queue)<ANY_HIT, 2><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters, refill); break;
     default: PT_SUFFIXED(k_trace_queue)<ANY_HIT, 0><<<blocks, kTraceBlock, 0, stream>>>(bvh, q, counters, refill); break;
     }
 }

@@ -38,6 +38,9 @@ namespace pt
 #ifndef PT_TRACE_PIPELINED_DEFAULT
 #define PT_TRACE_PIPELINED_DEFAULT 0
 #endif
+#ifndef PT_TRACE_POP_CULL
+#define PT_TRACE_POP_CULL 0
+#endif
 constexpr int kSharedStackEntries = PT_TRACE_SHARED_STACK;
 constexpr int kTraceBlock = 128;
 constexpr int kTraceBlocksPerSM = PT_TRACE_BLOCKS_PER_SM;         // 72 registers per thread; 64 (8 blocks) measured no faster
@@ -84,7 +87,11 @@ struct RaySlabs
 
 // The 8 box tests of one 80-byte node: bit (24 + s ^ oct_inv) of the result for a hit internal child in slot s (ray-octant order:
 // the highest bit is the child to visit first), bits 0..23 = triangles of the hit leaves. Same arithmetic as round 1's kernel.
-PT_DEV uint32_t node_hitmask(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3, const uint4 n4, const RaySlabs& r, const float t_best, const uint32_t one)
+// WITH_TMIN: group_tmin = the smallest (padded, i.e. conservative) entry distance among the hit INTERNAL children: a lower bound of the
+// distance of every triangle below any child of the group (+inf when no internal child is hit).
+template <bool WITH_TMIN>
+PT_DEV uint32_t node_hitmask_t(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3, const uint4 n4, const RaySlabs& r, const float t_best, const uint32_t one,
+                               float& group_tmin)
 {
     // cell size * 2^15 / direction, per axis; near / far offsets pushed 2^-7 of a cell outwards (see above)
     const float adx = __uint_as_float((n0.w & 0xFFu) << 23) * r.idx * 32768.0f;
@@ -100,6 +107,7 @@ PT_DEV uint32_t node_hitmask(const uint4 n0, const uint4 n1, const uint4 n2, con
     const uint32_t oct_inv4 = r.oct_inv * 0x01010101u;
 
     uint32_t hitmask = 0;
+    float tmin = INFINITY;
 #pragma unroll
     for (int half = 0; half < 2; half++)
     {
@@ -126,10 +134,31 @@ PT_DEV uint32_t node_hitmask(const uint4 n0, const uint4 n1, const uint4 n2, con
             const float cmax = fminf(fminf(fminf(tfx, tfy), tfz), t_best);
             if (cmin <= cmax)
                 hitmask |= ((child_bits4 >> (8 * j)) & 0xFFu) << ((bit_index4 >> (8 * j)) & 0xFFu);
+            if (WITH_TMIN && cmin <= cmax && ((is_inner4 >> (8 * j + 4)) & 1u) != 0u)
+                tmin = fminf(tmin, cmin);
         }
     }
+    group_tmin = tmin;
     return hitmask;
 }
+
+PT_DEV uint32_t node_hitmask(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3, const uint4 n4, const RaySlabs& r, const float t_best, const uint32_t one)
+{
+    float unused;
+    return node_hitmask_t<false>(n0, n1, n2, n3, n4, r, t_best, one, unused);
+}
+
+// Distance cull at pop time (PT_TRACE_POP_CULL): a node group waits on the stack while nearer subtrees are searched and t_best shrinks; without
+// a distance it is fetched and box-tested again whatever the ray has found meanwhile. Bits 8..23 of a node group's second word are free (hit
+// bits in 24..31, imask in 0..7): they hold the group's entry distance as the upper 16 bits of the float, i.e. truncated towards zero = rounded
+// DOWN (distances are >= 0), so the bound stays conservative. A group whose bound exceeds t_best cannot hold a hit that is closer or equal:
+// dropping it changes neither the hit nor the tie rule (equal distances are still visited), only the number of nodes fetched.
+// MEASURED AND LEFT OFF (gpurun call 26, profiles/r02_pop_cull_and_surface_occupancy.txt): on C3 the cull removes 0.36 % of the node visits
+// (17.815 -> 17.751 nodes per ray; C2 2.035 -> 2.031) -- a ray's deferred groups almost always start in front of its final hit, the per-child
+// test against t_best when a node IS fetched already does the culling that matters -- while the 8 extra FMNMX per node and the pop loop cost the
+// trace stage 4.9 % (83.3 -> 87.4 ms). Kept as FLAVOUR 2 of k_trace_queue (B200PT_TRACE_PIPELINE=2), hit records identical (parity tests run it).
+PT_DEV uint32_t pack_group_tmin(const float tmin) { return (__float_as_uint(tmin) >> 8) & 0x00FFFF00u; }
+PT_DEV float group_tmin_of(const uint2 group) { return __uint_as_float((group.y & 0x00FFFF00u) << 8); }
 
 // Index of the node behind the highest internal-child bit of a node group (first child, hit bits << 24 | imask)
 PT_DEV uint32_t group_next_node(const uint2 group, const uint32_t oct_inv, uint32_t& bit)
@@ -217,7 +246,7 @@ PT_DEV void trace_queue_store_hit(const RayQueueView& q, const uint32_t ray_id, 
         atomicAdd(&counters->queue_triangles, (unsigned long long)n_tris);                                                          \
         if (n_overflows) atomicAdd(&counters->overflows, (unsigned long long)n_overflows); })
 
-template <bool ANY_HIT>
+template <bool ANY_HIT, bool POP_CULL = (PT_TRACE_POP_CULL != 0)>
 __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const RayQueueView& q, uint2* shared_stack, TraversalCounters* counters,
                                                  const unsigned refill_idle_lanes = kRefillIdleLanes)
 {
@@ -238,7 +267,7 @@ __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const Ra
     hit.prim = -1; hit.tri_slot = -1; hit.t = -1.0f; hit.u = 0.0f; hit.v = 0.0f;
     uint2 ngroup = make_uint2(0u, 0u);   // (first child node, hit internal children << 24 | imask): node work of this lane
     uint2 tgroup = make_uint2(0u, 0u);   // (first triangle, hit-leaf triangle bits): triangle work of this lane
-    PT_COUNT(unsigned int n_nodes = 0; unsigned int n_tris = 0; unsigned int n_rays = 0; unsigned int n_overflows = 0;)
+    PT_COUNT(unsigned int n_nodes = 0; unsigned int n_tris = 0; unsigned int n_rays = 0; unsigned int n_overflows = 0; unsigned int n_culled = 0;)
 
     while (true)
     {
@@ -284,9 +313,12 @@ __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const Ra
             const uint4* np = reinterpret_cast<const uint4*>(bvh.nodes + node_index);
             const uint4 n0 = __ldg(np + 0), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
             PT_COUNT(n_nodes++;)
-            const uint32_t hitmask = node_hitmask(n0, n1, n2, n3, n4, r, t_best, one);
+            float group_tmin;
+            const uint32_t hitmask = node_hitmask_t<POP_CULL && !ANY_HIT>(n0, n1, n2, n3, n4, r, t_best, one, group_tmin);
             ngroup.x = n1.x;
             ngroup.y = (hitmask & 0xFF000000u) | (n0.w >> 24);
+            if (POP_CULL && !ANY_HIT)
+                ngroup.y |= pack_group_tmin(group_tmin);
             if ((hitmask & 0x00FFFFFFu) != 0u)
             {
                 // the node handed out triangles: they become the lane's triangle work, older triangle work waits on the stack
@@ -332,6 +364,15 @@ __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const Ra
         // set aside is taken only once the current one is done.
         if (!finished && ngroup.y <= 0x00FFFFFFu)
         {
+            // (any-hit rays never shrink t_best: nothing to cull)
+            while (POP_CULL && !ANY_HIT && stack.size > 0)
+            {
+                const uint2 e = stack.top();
+                if (e.y <= 0x00FFFFFFu || !(group_tmin_of(e) > t_best))
+                    break;
+                stack.size--;                   // every child of this group starts beyond the closest hit found since it was pushed
+                PT_COUNT(n_culled++;)
+            }
             if (stack.size == 0)
                 finished = tgroup.y == 0u;
             else

@@ -103,7 +103,7 @@ def test_trace_queue_flavours_agree(pt, wl, ctx, ref):
     ctx.counters_enable(True)
     ctx.counters_read(True)
     try:
-        for flavour in (0, 5, 6, 7):
+        for flavour in (0, 2, 5, 6, 7):
             ctx.set_trace_flavour(flavour)
             prim, t, uv = ctx.trace_queue(g.bvh, log["rays"], None, log["last_prim"])
             _assert_hits_equal(prim, t, log, f"flavour {flavour}")
@@ -111,7 +111,7 @@ def test_trace_queue_flavours_agree(pt, wl, ctx, ref):
             occ = ctx.trace_queue(g.bvh, log["rays"], t_max, log["last_prim"])
             assert np.array_equal(occ, occ0), f"flavour {flavour}: occlusion flags differ"
         c = ctx.counters_read(True)
-        assert c["stack_overflows"] == 0 and c["queue_rays"] == 8 * n
+        assert c["stack_overflows"] == 0 and c["queue_rays"] == 10 * n
     finally:
         ctx.set_trace_flavour(-1)
         ctx.counters_enable(False)
@@ -138,7 +138,7 @@ def test_c3_hit_ids_on_the_10m_triangle_bvh(pt, wl, ctx, ref):
     try:
         prim, t, _ = ctx.trace_closest(bvh, log["rays"], log["last_prim"])
         _assert_hits_equal(prim, t, log, "per-thread traversal")
-        for flavour in (0, 6):
+        for flavour in (0, 2, 6):
             ctx.set_trace_flavour(flavour)
             qprim, qt, _ = ctx.trace_queue(bvh, log["rays"], None, log["last_prim"])
             _assert_hits_equal(qprim, qt, log, f"ray-queue kernel, flavour {flavour}")
