@@ -602,6 +602,38 @@ def test_restir_di_separate_reuse_passes_parity(pt, wl, ctx, ref, temporal, spat
         g.close()
 
 
+@pytest.mark.parametrize("temporal,spatial,passes", [(True, True, 1), (True, True, 2)])
+def test_restir_di_separate_reuse_passes_own_history(pt, wl, ctx, ref, temporal, spatial, passes):
+    """The same non-fused configuration WITHOUT handing the oracle's reservoirs to the GPU between frames: the temporal pass of frame k reads what
+    the GPU's own passes left in frame k - 1 (the host ping-pong of ReSTIRDIRenderPass.cpp:332-425 carried over several frames). A reservoir that
+    differs (a sinf / cosf ulp moves a disk-sampled neighbour by a pixel) now spreads by the reuse radius per pass and frame, so the share of equal
+    reservoirs is bounded per frame instead of pinned, as in the fused test; the accumulated image stays within the north-star tolerance."""
+    cfg = wl.many_lights(128, 96, boxes=150, lights=3000, fused=False, temporal=temporal, spatial=spatial, spatial_passes=passes)
+    r = wl.setup_oracle(ref, pt.structs, cfg)
+    g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="cpu")
+    frames = 5
+    shares = []
+    try:
+        for f in range(frames):
+            r.render(1)
+            g.render_frame()
+            g.synchronize()
+            oa, ob = _reservoirs(np.ascontiguousarray(r.buffer("restir_output_reservoirs"))), _reservoirs(g.download("restir_output_reservoirs"))
+            same = (oa["tri"] == ob["tri"]) & (oa["M"] == ob["M"])
+            shares.append(float(same.mean()))
+            assert same.mean() > (0.998 if f == 0 else 0.97), (f, shares)
+            ok = same & np.isfinite(oa["UCW"])
+            assert np.isclose(oa["UCW"][ok], ob["UCW"][ok], rtol=1e-4, atol=1e-12).mean() > 0.99, (f, shares)
+        assert (ob["M"] > 4).mean() > 0.3, (ob["M"] > 4).mean()          # history did accumulate over the frames
+        print("share of reservoirs equal to the reference's, per frame, own history:", shares)
+        a, b = r.pixels() / frames, g.download("pixels") / frames
+        err = _rel_err(a, b)
+        assert err < 1e-3, err
+        assert abs(a.mean() - b.mean()) / a.mean() < 1e-3
+    finally:
+        g.close()
+
+
 def test_restir_di_extra_spatial_pass_after_fused(pt, wl, ctx):
     """GPU schedule of the reference (ReSTIRDIRenderPass.cpp:476-503): number_of_passes = 2 runs one SpatialReuse pass after the
     fused spatiotemporal pass. The CPU renderer never does (CPURenderer.cpp:405-411), so there is no oracle run for this shape:
