@@ -51,6 +51,8 @@ def host():
         _host.b200pt_renderer_bvh.argtypes = [C.c_void_p]
         _host.b200pt_renderer_device_pointer.restype = C.c_void_p
         _host.b200pt_renderer_device_pointer.argtypes = [C.c_void_p, C.c_int]
+        _host.b200pt_baker_last_table.restype = C.c_longlong
+        _host.b200pt_baker_last_table.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_longlong, C.c_void_p]
         _host.b200pt_renderer_download.restype = C.c_longlong
         _host.b200pt_renderer_download.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_longlong]
     return _host
@@ -98,4 +100,5 @@ HOST_API_SYMBOLS = [
     "b200pt_renderer_reset", "b200pt_renderer_render_settings", "b200pt_renderer_world_settings", "b200pt_renderer_bsdfs_data",
     "b200pt_renderer_render_data", "b200pt_renderer_bvh", "b200pt_renderer_render_frame", "b200pt_renderer_synchronize",
     "b200pt_renderer_last_frame_ms", "b200pt_renderer_last_kernel_ms", "b200pt_renderer_download", "b200pt_renderer_device_pointer",
+    "b200pt_baker_create", "b200pt_baker_destroy", "b200pt_baker_set_options", "b200pt_baker_bake", "b200pt_baker_is_complete", "b200pt_baker_wait", "b200pt_baker_last_table",
 ]

@@ -95,12 +95,12 @@ def build(force=False, verbose=False):
 
     # Host layer (C++ mirror of the reference's GPURenderer) above the C ABI: plain g++, links against libb200pt.so
     host_dir = os.path.join(HERE, "host")
-    host_src = [os.path.join(host_dir, f) for f in ("GPURenderer.cpp", "host_capi.cpp")]
+    host_src = [os.path.join(host_dir, f) for f in ("GPURenderer.cpp", "GPUBaker.cpp", "host_capi.cpp")]
     host_newest = max(os.path.getmtime(os.path.join(host_dir, f)) for f in os.listdir(host_dir))
     host_newest = max(host_newest, os.path.getmtime(LIB), newest)
     if force or not os.path.exists(HOST_LIB) or os.path.getmtime(HOST_LIB) < host_newest:
         run(["g++", "-std=c++17", "-O2", "-fPIC", "-shared", "-fvisibility=hidden", "-I", os.path.join(HERE, "..", "include"), "-I", host_dir,
-             *host_src, "-o", HOST_LIB, "-L", HERE, "-lb200pt", "-Wl,-rpath,$ORIGIN"])
+             *host_src, "-o", HOST_LIB, "-L", HERE, "-lb200pt", "-pthread", "-Wl,-rpath,$ORIGIN"])
     return LIB
 
 

@@ -1,4 +1,5 @@
 // C handle API over b200pt_host::GPURenderer (include/b200pt_host.h).
+#include "GPUBaker.h"
 #include "GPURenderer.h"
 #include "b200pt_host.h"
 
@@ -6,6 +7,12 @@
 #include <string>
 
 using namespace b200pt_host;
+
+struct b200pt_baker
+{
+    explicit b200pt_baker(b200pt_ctx* c) : baker(c) {}
+    GPUBaker baker;
+};
 
 struct b200pt_renderer
 {
@@ -223,6 +230,111 @@ long long b200pt_renderer_download(b200pt_renderer* r, int which, void* out_host
         return e;
     }
     return bytes;
+}
+
+// ---- GPUBaker -----------------------------------------------------------------------------------------------------------------------
+int b200pt_baker_create(b200pt_ctx* ctx, b200pt_baker** out)
+{
+    if (!ctx || !out)
+    {
+        g_host_error = "invalid argument";
+        return B200PT_ERROR_INVALID_ARGUMENT;
+    }
+    *out = nullptr;
+    return guarded([&] { *out = new b200pt_baker(ctx); });
+}
+
+int b200pt_baker_destroy(b200pt_baker* b)
+{
+    delete b;
+    return B200PT_SUCCESS;
+}
+
+int b200pt_baker_set_options(b200pt_baker* b, int ggx_sample_function, int ggx_masking_shadowing, int chunks, const char* output_directory)
+{
+    if (!b)
+    {
+        g_host_error = "invalid argument";
+        return B200PT_ERROR_INVALID_ARGUMENT;
+    }
+    b200pt_bake_options o;
+    o.ggx_sample_function = ggx_sample_function;
+    o.GGX_masking_shadowing = ggx_masking_shadowing;
+    o.chunks = chunks;
+    b->baker.set_options(o);
+    b->baker.set_output_directory(output_directory ? output_directory : "");
+    return B200PT_SUCCESS;
+}
+
+int b200pt_baker_bake(b200pt_baker* b, int table, int size_cos_theta, int size_roughness, int size_ior, int integration_sample_count, const char* output_filename)
+{
+    if (!b || table < B200PT_BAKE_GGX_CONDUCTOR || table > B200PT_BAKE_GGX_THIN_GLASS || table == B200PT_BAKE_GGX_GLASS_EXITING)
+    {
+        g_host_error = "invalid argument (table: a b200pt_bake_kind; the two glass tables are baked together through B200PT_BAKE_GGX_GLASS_ENTERING)";
+        return B200PT_ERROR_INVALID_ARGUMENT;
+    }
+    // the plan validates the sizes before a worker is started
+    b200pt_bake_plan plan;
+    int rc = b200pt_bake_plan_for(table, size_cos_theta, size_roughness, size_ior, integration_sample_count, nullptr, &plan);
+    if (rc != B200PT_SUCCESS)
+    {
+        g_host_error = b200pt_last_error();
+        return rc;
+    }
+    const std::string name = output_filename ? output_filename : "";
+    return guarded([&] {
+        switch (table)
+        {
+        case B200PT_BAKE_GGX_CONDUCTOR: b->baker.bake_ggx_conductor_directional_albedo({size_cos_theta, size_roughness, integration_sample_count}, name); break;
+        case B200PT_BAKE_GGX_FRESNEL: b->baker.bake_ggx_fresnel_directional_albedo({size_cos_theta, size_roughness, size_ior, integration_sample_count}, name); break;
+        case B200PT_BAKE_GLOSSY_DIELECTRIC: b->baker.bake_glossy_dielectric_directional_albedo({size_cos_theta, size_roughness, size_ior, integration_sample_count}, name); break;
+        case B200PT_BAKE_GGX_GLASS_ENTERING: b->baker.bake_ggx_glass_directional_albedo({size_cos_theta, size_roughness, size_ior, integration_sample_count}, name); break;
+        default: b->baker.bake_ggx_thin_glass_directional_albedo({size_cos_theta, size_roughness, size_ior, integration_sample_count}, name); break;
+        }
+    });
+}
+
+int b200pt_baker_is_complete(b200pt_baker* b, int table)
+{
+    if (!b)
+        return B200PT_ERROR_INVALID_ARGUMENT;
+    switch (table)
+    {
+    case B200PT_BAKE_GGX_CONDUCTOR: return b->baker.is_ggx_conductor_directional_albedo_bake_complete() ? 1 : 0;
+    case B200PT_BAKE_GGX_FRESNEL: return b->baker.is_ggx_fresnel_directional_albedo_bake_complete() ? 1 : 0;
+    case B200PT_BAKE_GLOSSY_DIELECTRIC: return b->baker.is_glossy_dielectric_directional_albedo_bake_complete() ? 1 : 0;
+    case B200PT_BAKE_GGX_GLASS_ENTERING:
+    case B200PT_BAKE_GGX_GLASS_EXITING: return b->baker.is_ggx_glass_directional_albedo_bake_complete() ? 1 : 0;
+    case B200PT_BAKE_GGX_THIN_GLASS: return b->baker.is_ggx_thin_glass_directional_albedo_bake_complete() ? 1 : 0;
+    }
+    return B200PT_ERROR_INVALID_ARGUMENT;
+}
+
+int b200pt_baker_wait(b200pt_baker* b)
+{
+    if (!b)
+        return B200PT_ERROR_INVALID_ARGUMENT;
+    b->baker.wait();
+    for (int kind = 0; kind < 6; kind++)
+        if (!b->baker.last_error(kind).empty())
+        {
+            g_host_error = b->baker.last_error(kind);
+            return B200PT_ERROR_CUDA;
+        }
+    return B200PT_SUCCESS;
+}
+
+long long b200pt_baker_last_table(b200pt_baker* b, int kind, float* out, long long capacity_floats, float* out_kernel_ms)
+{
+    if (!b || kind < 0 || kind > 5 || !b200pt_baker_is_complete(b, kind))
+        return 0;
+    const std::vector<float>& t = b->baker.last_table(kind);
+    if ((long long)t.size() > capacity_floats || out == nullptr)
+        return -(long long)t.size();
+    std::memcpy(out, t.data(), t.size() * sizeof(float));
+    if (out_kernel_ms)
+        *out_kernel_ms = b->baker.last_bake_ms(kind);
+    return (long long)t.size();
 }
 
 } // extern "C"

@@ -74,6 +74,20 @@ B200PT_API int b200pt_renderer_last_kernel_ms(b200pt_renderer* r, int which, flo
 B200PT_API long long b200pt_renderer_download(b200pt_renderer* r, int which, void* out_host, long long capacity_bytes);
 B200PT_API void* b200pt_renderer_device_pointer(b200pt_renderer* r, int which);
 
+/* ---- b200pt_host::GPUBaker (hiprt-path-tracer_b200/host/GPUBaker.h): the reference's GPUBaker (src/Renderer/Baker/GPUBaker.cpp:12-96) ----------
+ * table: a b200pt_bake_kind (b200pt_bake.h); B200PT_BAKE_GGX_GLASS_ENTERING bakes BOTH glass tables like GPUBaker::bake_ggx_glass_directional_albedo
+ * (the exiting one goes to "inv_" + output_filename). b200pt_baker_bake returns at once; a worker writes the .hdr slices into output_directory
+ * ("" / NULL: the working directory, as the reference does; NULL output_filename: no files) and raises the flag b200pt_baker_is_complete polls. */
+typedef struct b200pt_baker b200pt_baker;
+B200PT_API int b200pt_baker_create(b200pt_ctx* ctx, b200pt_baker** out);
+B200PT_API int b200pt_baker_destroy(b200pt_baker* baker);                      /* waits for the bakes in flight */
+B200PT_API int b200pt_baker_set_options(b200pt_baker* baker, int ggx_sample_function, int ggx_masking_shadowing, int chunks, const char* output_directory);
+B200PT_API int b200pt_baker_bake(b200pt_baker* baker, int table, int size_cos_theta, int size_roughness, int size_ior, int integration_sample_count, const char* output_filename);
+B200PT_API int b200pt_baker_is_complete(b200pt_baker* baker, int table);       /* 1 complete (also: never started), 0 in flight */
+B200PT_API int b200pt_baker_wait(b200pt_baker* baker);                         /* every bake finished; B200PT_ERROR_CUDA + message if one of them failed */
+/* The last finished table of that kind: floats copied (or the required count negated); out_kernel_ms may be NULL. */
+B200PT_API long long b200pt_baker_last_table(b200pt_baker* baker, int kind, float* out, long long capacity_floats, float* out_kernel_ms);
+
 #ifdef __cplusplus
 }
 #endif

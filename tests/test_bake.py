@@ -195,3 +195,67 @@ def test_bake_argument_errors(bk, ctx):
         assert lib.b200pt_bake_ggx_glass_directional_albedo(ctx.handle, C.byref(g), None, None, None, None) == -1           # neither table wanted
     finally:
         ctx.free(buf)
+
+
+def _read_flat_hdr(path):
+    """Reader for the flat (not run-length encoded) Radiance files the bakers write."""
+    io = __import__("importlib").import_module("hiprt-path-tracer_b200.image_io")
+    data = open(path, "rb").read()
+    head, _, rest = data.partition(b"\n\n")
+    assert head.startswith(b"#?RADIANCE") and b"32-bit_rle_rgbe" in head
+    dims, _, body = rest.partition(b"\n")
+    _, h, _, w = dims.split()
+    rgbe = np.frombuffer(body, np.uint8).reshape(int(h), int(w), 4)
+    return io.rgbe_to_float(rgbe)[..., 0]
+
+
+@pytest.mark.gpu
+def test_host_layer_gpubaker_is_asynchronous_and_writes_the_reference_files(bk, pt, ctx, golden, tmp_path):
+    """b200pt_host::GPUBaker (C++, hiprt-path-tracer_b200/host/GPUBaker.cpp) through its C handles: bake_*() returns while the table is being
+    integrated, is_*_complete() goes from false to true (GPUBakerKernel's flag, src/Renderer/Baker/GPUBakerKernel.cpp:24,130), the tables equal the
+    reference kernels' (golden), and the files carry the reference's names and decode -- with the reference's own loader where the oracle is
+    built -- to the table within the 8-bit RGBE mantissa."""
+    host = pt.host()
+    baker = C.c_void_p()
+    pt._capi.check_host(host.b200pt_baker_create(ctx.handle, C.byref(baker)), "b200pt_baker_create")
+    try:
+        assert host.b200pt_baker_is_complete(baker, 0) == 1                                   # never started: complete, as in the reference
+        pt._capi.check_host(host.b200pt_baker_set_options(baker, 0, 0, 1, str(tmp_path).encode()), "b200pt_baker_set_options")
+        assert host.b200pt_baker_bake(baker, 4, 12, 8, 8, 4096, None) == -1                   # the exiting glass table is not baked on its own
+        assert host.b200pt_baker_bake(baker, 0, 1, 16, 1, 4096, None) == -1                   # sizes are validated before a worker starts
+        # the big one first: 2e9 samples keep the GPU busy for tens of milliseconds, long enough to see the flag down
+        pt._capi.check_host(host.b200pt_baker_bake(baker, 2, 64, 32, 16, 65536, b"Glossy_Ess_64x32x16.hdr"), "b200pt_baker_bake")
+        in_flight = host.b200pt_baker_is_complete(baker, 2) == 0
+        pt._capi.check_host(host.b200pt_baker_bake(baker, 0, 16, 16, 1, 4096, bk.get_GGX_conductor_Ess_filename(16, 16).encode()), "b200pt_baker_bake")
+        pt._capi.check_host(host.b200pt_baker_bake(baker, 3, 12, 8, 8, 4096, bk.get_GGX_glass_Ess_filename(12, 8, 8).encode()), "b200pt_baker_bake")
+        pt._capi.check_host(host.b200pt_baker_bake(baker, 5, 12, 8, 8, 4096, bk.get_GGX_thin_glass_Ess_filename(12, 8, 8).encode()), "b200pt_baker_bake")
+        pt._capi.check_host(host.b200pt_baker_wait(baker), "b200pt_baker_wait")
+        assert in_flight and all(host.b200pt_baker_is_complete(baker, k) == 1 for k in (0, 2, 3, 4, 5))
+        tables = {}
+        for kind, shape, key in ((0, (1, 16, 16), "small/conductor_vndf"), (3, (8, 8, 12), "small/glass_vndf"), (4, (8, 8, 12), "small/glass_inverse_vndf"),
+                                 (5, (8, 8, 12), "small/thin_glass_vndf")):
+            out = np.empty(shape, np.float32)
+            ms = C.c_float()
+            n = host.b200pt_baker_last_table(baker, kind, out.ctypes.data_as(C.c_void_p), C.c_longlong(out.size), C.byref(ms))
+            assert n == out.size and ms.value > 0.0, (kind, n)
+            _compare(out, golden[key], key, nan_mismatch=NAN_MASK_MISMATCH_THIN_GLASS if kind == 5 else 0.0)
+            tables[kind] = out
+        assert host.b200pt_baker_last_table(baker, 0, None, C.c_longlong(0), None) == -256    # capacity too small: the size, negated
+        names = ["GGX_Conductor_16x16.hdr"] + [f"{z}{n}" for z in (0, 7) for n in ("GGX_Glass_Ess_12x8x8.hdr", "inv_GGX_Glass_Ess_12x8x8.hdr", "GGX_Thin_Glass_Ess_12x8x8.hdr")]
+        names += ["0Glossy_Ess_64x32x16.hdr", "15Glossy_Ess_64x32x16.hdr"]
+        for name in names:
+            assert os.path.exists(os.path.join(str(tmp_path), name)), name
+        for name, table in (("GGX_Conductor_16x16.hdr", tables[0][0]), ("7GGX_Glass_Ess_12x8x8.hdr", tables[3][7]), ("3inv_GGX_Glass_Ess_12x8x8.hdr", tables[4][3])):
+            path = os.path.join(str(tmp_path), name)
+            decoded = _read_flat_hdr(path)
+            assert decoded.shape == table.shape and np.all(np.abs(decoded - table) <= table / 128.0 + 1e-30), name
+            from oracle import ref
+            if ref.available("mis"):
+                # Image32Bit::read_image_hdr of the reference (stb_image), unflipped, first channel
+                lib = ref.load("mis")
+                got = np.empty(table.shape, np.float32)
+                w, h = C.c_int(), C.c_int()
+                assert lib.ref_load_hdr(path.encode(), 1, 0, got.ctypes.data_as(C.c_void_p), got.size, C.byref(w), C.byref(h)) == 0 and (w.value, h.value) == table.shape[::-1]
+                assert np.all(np.abs(got - table) <= table / 128.0 + 1e-30), name
+    finally:
+        host.b200pt_baker_destroy(baker)
