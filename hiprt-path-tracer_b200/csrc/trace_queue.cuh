@@ -77,6 +77,33 @@ PT_DEV void prefetch_global(const void* p)
 #endif
 }
 
+// Triangle fetch policy (PT_TRACE_TRI_LOAD): the 48-byte triangle records of a big scene (480 MB on C3) are touched about once per ray batch,
+// the 80-byte nodes of the upper levels by every ray. 0: plain read-only loads that allocate in L1 like the nodes (LDG.CONSTANT); 1: streaming
+// loads (ld.global.cs: evict-first in L1 and L2) and the triangle prefetch into L2 only; 2: ld.global.nc.L1::no_allocate, prefetch into L2 only.
+#ifndef PT_TRACE_TRI_LOAD
+#define PT_TRACE_TRI_LOAD 0
+#endif
+PT_DEV float4 load_triangle_f4(const float4* p)
+{
+#if defined(__CUDA_ARCH__) && PT_TRACE_TRI_LOAD == 1
+    return __ldcs(p);
+#elif defined(__CUDA_ARCH__) && PT_TRACE_TRI_LOAD == 2
+    float4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+#else
+    return __ldg(p);
+#endif
+}
+PT_DEV void prefetch_triangle(const void* p)
+{
+#if defined(__CUDA_ARCH__) && PT_TRACE_TRI_LOAD != 0
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+#else
+    prefetch_global(p);
+#endif
+}
+
 // Per-ray constants of the slab test
 struct RaySlabs
 {
@@ -326,8 +353,8 @@ __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const Ra
                 tgroup = make_uint2(n1.y, hitmask & 0x00FFFFFFu);
                 // the triangles are tested in later iterations (one per iteration): start fetching them now
                 const char* first_triangle = reinterpret_cast<const char*>(bvh.triangles + (n1.y + (uint32_t)__ffs((int)tgroup.y) - 1u));
-                prefetch_global(first_triangle);
-                prefetch_global(first_triangle + 128);
+                prefetch_triangle(first_triangle);
+                prefetch_triangle(first_triangle + 128);
             }
             if (ngroup.y > 0x00FFFFFFu)
             {
@@ -345,7 +372,7 @@ __device__ __forceinline__ void trace_queue_body(const Bvh8Device& bvh, const Ra
             tgroup.y &= tgroup.y - 1u;
             const uint32_t tri_index = tgroup.x + tbit;
             const float4* tp = reinterpret_cast<const float4*>(bvh.triangles + tri_index);
-            const float4 v0 = __ldg(tp + 0), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+            const float4 v0 = load_triangle_f4(tp + 0), v1 = load_triangle_f4(tp + 1), v2 = load_triangle_f4(tp + 2);
             PT_COUNT(n_tris++;)
             const int prim = __float_as_int(v0.w);
             float t, u, v;
@@ -540,7 +567,7 @@ __device__ __forceinline__ void trace_queue_body_pipelined(const Bvh8Device& bvh
             tgroup.y &= tgroup.y - 1u;
             tri_loaded_index = tgroup.x + tbit;
             const float4* tp = reinterpret_cast<const float4*>(bvh.triangles + tri_loaded_index);
-            v0 = __ldg(tp + 0); v1 = __ldg(tp + 1); v2 = __ldg(tp + 2);
+            v0 = load_triangle_f4(tp + 0); v1 = load_triangle_f4(tp + 1); v2 = load_triangle_f4(tp + 2);
             tri_loaded = true;
         }
         if (!finished)
