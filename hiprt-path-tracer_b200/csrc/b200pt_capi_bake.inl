@@ -3,6 +3,7 @@
 
 #include "../../include/b200pt_bake.h"
 
+#include <algorithm>
 #include <cmath>
 
 namespace
@@ -46,9 +47,27 @@ int bake_plan(int kind, int sx, int sy, int sz, int sample_count, const b200pt_b
     if (chunks == 0)
     {
         // enough threads for 148 SMs x 1024: small tables split a texel's launches, large ones keep the reference's summation order
+        const long long fill = 148LL * 1024;
         chunks = 1;
-        while (chunks < kBakeMaxChunksHost && texels * chunks < 148LL * 1024 && chunks * 2 <= nb_kernel_launch)
+        while (chunks < kBakeMaxChunksHost && texels * chunks < fill && chunks * 2 <= nb_kernel_launch)
             chunks *= 2;
+        if (chunks > 1)
+        {
+            // ... and among the splits up to two fills of the GPU, the one whose longest chunk is shortest (11 launches over 8 threads leave
+            // two of them idle and the others with 2 launches each; over 11 threads every thread runs one)
+            const int most = (int)std::min<long long>(kBakeMaxChunksHost, std::max<long long>(chunks, 2 * fill / texels));
+            int best = chunks, best_longest = (nb_kernel_launch + chunks - 1) / chunks;
+            for (int c = chunks + 1; c <= most && c <= nb_kernel_launch; c++)
+            {
+                const int longest = (nb_kernel_launch + c - 1) / c;
+                if (longest < best_longest)
+                {
+                    best = c;
+                    best_longest = longest;
+                }
+            }
+            chunks = best;
+        }
     }
     if (chunks > nb_kernel_launch)
         chunks = nb_kernel_launch;

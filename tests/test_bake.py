@@ -47,7 +47,8 @@ def test_bake_plan_restates_the_reference_launch_arithmetic(bk, golden):
     assert (p.iterations_per_kernel, p.nb_kernel_launch, p.nb_samples) == (1017, 65, 66105)
     # chunks: explicit, automatic (small tables are split, large ones are not), clamped to the number of launches
     assert bk.bake_plan(0, 128, 128, 1, 65536, bk.BakeOptions(0, 0, 1)).chunks == 1
-    assert bk.bake_plan(0, 128, 128, 1, 65536).chunks == 8
+    assert bk.bake_plan(0, 128, 128, 1, 65536).chunks == 11                  # 11 launches: one per thread (8 threads would leave two idle)
+    assert bk.bake_plan(5, 32, 32, 96, 65536).chunks == 3                   # 65 launches: 22 + 22 + 21
     assert bk.bake_plan(2, 128, 64, 128, 65536).chunks == 1
     assert bk.bake_plan(0, 16, 16, 1, 4096, bk.BakeOptions(0, 0, 8)).chunks == 1
     lib = bk._capi.lib()
@@ -141,10 +142,10 @@ def test_full_size_tables_match_the_reference_slices_and_the_shipped_luts(bk, ct
               "thin_glass": baker.bake_ggx_thin_glass_directional_albedo(output_filename=bk.get_GGX_thin_glass_Ess_filename())}
     tables["glass"], tables["glass_inverse"] = baker.bake_ggx_glass_directional_albedo(output_filename=bk.get_GGX_glass_Ess_filename())
     assert baker.is_ggx_glass_directional_albedo_bake_complete() and not baker.is_ggx_fresnel_directional_albedo_bake_complete()
-    # the default plan splits the two small tables over 8 and 2 threads per texel: same samples, the sum regrouped. 67 k additions of ~1.5e-5 to a
+    # the default plan splits the two small tables over 11 and 3 threads per texel: same samples, the sum regrouped. 67 k additions of ~1.5e-5 to a
     # running sum near 1 carry ~1e-4 of rounding in the reference's sequential order itself, so the regrouped sum differs from it by that much
     split = bk.GPUBaker(ctx)
-    assert bk.bake_plan(0, 128, 128, 1, 65536).chunks == 8 and bk.bake_plan(5, 32, 32, 96, 65536).chunks == 2
+    assert bk.bake_plan(0, 128, 128, 1, 65536).chunks == 11 and bk.bake_plan(5, 32, 32, 96, 65536).chunks == 3
     regrouped = {"conductor": split.bake_ggx_conductor_directional_albedo()[None], "thin_glass": split.bake_ggx_thin_glass_directional_albedo()}
     for name, table in regrouped.items():
         assert np.array_equal(np.isfinite(table), np.isfinite(tables[name])), name
