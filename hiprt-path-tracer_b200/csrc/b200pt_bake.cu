@@ -20,7 +20,8 @@ namespace pt
 {
 namespace
 {
-constexpr int kBakeTexelsPerBlock = 32;
+constexpr int kBakeTexelsPerBlock = 32;         // with chunks > 1: one warp of texels per chunk row
+constexpr int kBakeTexelsPerBlockUnsplit = 128; // chunks == 1: plain 128-thread blocks (32-thread blocks would cap an SM at 32 resident warps)
 constexpr int kBakeMaxChunks = 16;   // b200pt_capi_bake.inl clamps b200pt_bake_options::chunks to this
 
 struct BakeTexel
@@ -239,7 +240,7 @@ __global__ void __launch_bounds__(kBakeTexelsPerBlock * kBakeMaxChunks) k_bake(B
     __shared__ float partial[kBakeMaxChunks][kBakeTexelsPerBlock];
 
     const long long texels = (long long)p.size_x * p.size_y * p.size_z;
-    const long long texel = (long long)blockIdx.x * kBakeTexelsPerBlock + threadIdx.x;
+    const long long texel = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const int chunk = threadIdx.y;
     float sum = 0.0f;
     if (texel < texels)
@@ -297,8 +298,9 @@ cudaError_t launch_bake_kind(const BakeLaunch& p, float* d_out, cudaStream_t str
     const long long texels = (long long)p.size_x * p.size_y * p.size_z;
     if (p.chunks < 1 || p.chunks > kBakeMaxChunks || texels <= 0 || texels > 0x7fffffffLL)
         return cudaErrorInvalidValue;
-    dim3 block(kBakeTexelsPerBlock, p.chunks, 1);
-    dim3 grid((unsigned int)((texels + kBakeTexelsPerBlock - 1) / kBakeTexelsPerBlock), 1, 1);
+    const int texels_per_block = p.chunks == 1 ? kBakeTexelsPerBlockUnsplit : kBakeTexelsPerBlock;
+    dim3 block(texels_per_block, p.chunks, 1);
+    dim3 grid((unsigned int)((texels + texels_per_block - 1) / texels_per_block), 1, 1);
     if (p.ggx_sampler == 0)
         k_bake<KIND, 0><<<grid, block, 0, stream>>>(p, d_out);
     else
