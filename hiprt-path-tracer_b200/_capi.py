@@ -77,7 +77,7 @@ API_SYMBOLS = [
     "b200pt_host_alloc_pinned", "b200pt_host_free_pinned", "b200pt_stream_create", "b200pt_stream_destroy", "b200pt_stream_query",
     "b200pt_stream_sync", "b200pt_event_create", "b200pt_event_destroy", "b200pt_event_record", "b200pt_event_elapsed_ms",
     "b200pt_tex2d_create", "b200pt_tex3d_create", "b200pt_tex_destroy", "b200pt_tex2d_array_create", "b200pt_bvh_build",
-    "b200pt_bvh_destroy", "b200pt_bvh_device_handle", "b200pt_bvh_info", "b200pt_bvh_get_stats", "b200pt_kernel_variant_select", "b200pt_set_path_mode", "b200pt_get_path_mode", "b200pt_path_profile_enable", "b200pt_path_profile_read", "b200pt_launch_CameraRays",
+    "b200pt_bvh_destroy", "b200pt_bvh_attach_shading_data", "b200pt_bvh_device_handle", "b200pt_bvh_info", "b200pt_bvh_get_stats", "b200pt_kernel_variant_select", "b200pt_set_path_mode", "b200pt_get_path_mode", "b200pt_path_profile_enable", "b200pt_path_profile_read", "b200pt_launch_CameraRays",
     "b200pt_launch_FullPathTracer", "b200pt_launch_FullPathTracer_lane", "b200pt_launch_PathTraceSamples", "b200pt_stream_wait_event", "b200pt_launch_ReSTIR_DI_LightsPresampling", "b200pt_launch_ReSTIR_DI_InitialCandidates",
     "b200pt_launch_ReSTIR_DI_SpatiotemporalReuse", "b200pt_launch_ReSTIR_DI_TemporalReuse", "b200pt_launch_ReSTIR_DI_SpatialReuse", "b200pt_tonemap", "b200pt_trace_closest", "b200pt_trace_shadow", "b200pt_trace_queue", "b200pt_trace_queue_static", "b200pt_set_trace_flavour", "b200pt_set_ray_bin_bits", "b200pt_set_restir_phases", "b200pt_debug_bsdf_eval", "b200pt_debug_bsdf_sample", "b200pt_debug_envmap_sample", "b200pt_debug_thin_film_fresnel", "b200pt_counters_enable",
     "b200pt_counters_read",

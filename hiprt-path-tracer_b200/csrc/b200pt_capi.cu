@@ -41,6 +41,7 @@ struct b200pt_bvh
     pt::Bvh8Device* d_view = nullptr;
     void* d_nodes = nullptr;
     void* d_triangles = nullptr;
+    void* d_shading = nullptr;      // b200pt_bvh_attach_shading_data: 64 bytes per triangle slot
     float sah_cost = 0.0f;
     double build_seconds = 0.0;
     int max_depth = 0;

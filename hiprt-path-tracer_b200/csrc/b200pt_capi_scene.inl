@@ -199,12 +199,66 @@ int b200pt_bvh_destroy(b200pt_ctx* ctx, b200pt_bvh* bvh)
     cudaSetDevice(ctx->device);
     cudaFree(bvh->d_nodes);
     cudaFree(bvh->d_triangles);
+    cudaFree(bvh->d_shading);
     cudaFree(bvh->d_view);
     delete bvh;
     return B200PT_SUCCESS;
 }
 
 void* b200pt_bvh_device_handle(b200pt_bvh* bvh) { return bvh ? bvh->d_view : nullptr; }
+
+// One thread per triangle slot of the BVH: gather what a hit on that triangle needs for shading (see Bvh8Device::shading, bvh8.h)
+static __global__ void k_attach_shading(pt::Bvh8Triangle* triangles, float4* shading, uint32_t triangle_count, const int* __restrict__ triangle_indices,
+                                        const float* __restrict__ vertex_normals, const unsigned char* __restrict__ has_vertex_normals, const float* __restrict__ texcoords,
+                                        const int* __restrict__ material_indices)
+{
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= triangle_count)
+        return;
+    const int prim = triangles[slot].prim_id;
+    const int a = triangle_indices[3 * (size_t)prim], b = triangle_indices[3 * (size_t)prim + 1], c = triangle_indices[3 * (size_t)prim + 2];
+    const float* na = vertex_normals + 3 * (size_t)a;
+    const float* nb = vertex_normals + 3 * (size_t)b;
+    const float* nc = vertex_normals + 3 * (size_t)c;
+    const float* ta = texcoords + 2 * (size_t)a;
+    const float* tb = texcoords + 2 * (size_t)b;
+    const float* tc = texcoords + 2 * (size_t)c;
+    float4* out = shading + 4 * (size_t)slot;
+    out[0] = make_float4(na[0], na[1], na[2], nb[0]);
+    out[1] = make_float4(nb[1], nb[2], nc[0], nc[1]);
+    out[2] = make_float4(nc[2], ta[0], ta[1], tb[0]);
+    out[3] = make_float4(tb[1], tc[0], tc[1], 0.0f);
+    triangles[slot].pad1 = material_indices[prim];
+    triangles[slot].pad2 = has_vertex_normals[a] ? 1 : 0;
+}
+
+int b200pt_bvh_attach_shading_data(b200pt_ctx* ctx, b200pt_bvh* bvh, const int* d_triangle_indices, const float* d_vertex_normals, const unsigned char* d_has_vertex_normals,
+                                   const float* d_texcoords, const int* d_material_indices, b200pt_stream stream)
+{
+    REQUIRE(ctx != nullptr && bvh != nullptr);
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    if (d_triangle_indices == nullptr)
+    {
+        // detach: hits go back to the reference's buffers
+        bvh->view.shading = nullptr;
+        CUDA_TRY(cudaMemcpyAsync(bvh->d_view, &bvh->view, sizeof(pt::Bvh8Device), cudaMemcpyHostToDevice, stream_of(ctx, stream)));
+        CUDA_TRY(cudaStreamSynchronize(stream_of(ctx, stream)));
+        return B200PT_SUCCESS;
+    }
+    REQUIRE(d_vertex_normals != nullptr && d_has_vertex_normals != nullptr && d_texcoords != nullptr && d_material_indices != nullptr);
+    const uint32_t n = bvh->view.triangle_count;
+    if (n == 0)
+        return B200PT_SUCCESS;
+    if (bvh->d_shading == nullptr)
+        CUDA_TRY(cudaMalloc(&bvh->d_shading, (size_t)n * 64));
+    k_attach_shading<<<(n + 255) / 256, 256, 0, stream_of(ctx, stream)>>>(reinterpret_cast<pt::Bvh8Triangle*>(bvh->d_triangles), reinterpret_cast<float4*>(bvh->d_shading), n,
+                                                                           d_triangle_indices, d_vertex_normals, d_has_vertex_normals, d_texcoords, d_material_indices);
+    CUDA_TRY(cudaGetLastError());
+    bvh->view.shading = bvh->d_shading;
+    CUDA_TRY(cudaMemcpyAsync(bvh->d_view, &bvh->view, sizeof(pt::Bvh8Device), cudaMemcpyHostToDevice, stream_of(ctx, stream)));
+    CUDA_TRY(cudaStreamSynchronize(stream_of(ctx, stream)));     // bvh->view is host memory of this call's lifetime only through the copy above
+    return B200PT_SUCCESS;
+}
 
 int b200pt_bvh_info(b200pt_bvh* bvh, unsigned* out_node_count, unsigned* out_triangle_count, float* out_sah_cost, double* out_build_seconds)
 {

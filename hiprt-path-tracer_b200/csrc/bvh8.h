@@ -29,8 +29,8 @@ static_assert(sizeof(Bvh8Node) == 80, "BVH8 node must be 80 bytes");
 struct alignas(16) Bvh8Triangle
 {
     float v0x, v0y, v0z; int prim_id;     // index of the triangle in the scene's index buffer
-    float v1x, v1y, v1z; int pad1;
-    float v2x, v2y, v2z; int pad2;
+    float v1x, v1y, v1z; int pad1;        // builders write 0; b200pt_bvh_attach_shading_data: the triangle's material index
+    float v2x, v2y, v2z; int pad2;        //                                                    has_vertex_normals of vertex A (0 / 1)
 };
 static_assert(sizeof(Bvh8Triangle) == 48, "BVH8 triangle must be 48 bytes");
 
@@ -43,6 +43,10 @@ struct Bvh8Device
     uint32_t triangle_count;
     float scene_min[3];
     float scene_max[3];
+    // Per-triangle-SLOT shading records (b200pt_bvh_attach_shading_data; null until attached): 64 bytes = four 16-byte loads holding the three
+    // vertex normals (9 floats), the three texcoords (6 floats) and one spare word -- what SURFACE otherwise gathers through the index buffer
+    // from three scattered vertices (indices, 3 normals, 3 texcoords, a flag byte, the material index: ~10 sectors per hit against 2).
+    const void* shading;
 };
 
 constexpr int kBvh8MaxLeafTriangles = 3;

@@ -50,6 +50,46 @@ PT_DEV float2 ld2(const void* base, size_t index)
     return make_float2(__ldg(p), __ldg(p + 1));
 }
 
+// What a hit needs of its triangle besides the geometry: the three vertices' normals and texcoords, whether vertex A has a normal, the
+// material index (and the vertex indices, for normal mapping only). Two sources with the same values: the reference's buffers through the
+// index buffer (RenderBuffers, src/HostDeviceCommon/RenderBuffers.h), or -- when b200pt_bvh_attach_shading_data has run -- the 64-byte record
+// of the triangle's BVH slot plus the two spare words of its 48-byte triangle record.
+struct TriangleShading
+{
+    float3 na, nb, nc;
+    float2 ta, tb, tc;
+    int material_index;
+    int has_normals;          // has_vertex_normals[vertex A], the only one get_shading_normal looks at (Intersect.h:69)
+    int prim;
+    bool from_record;
+};
+
+PT_DEV TriangleShading load_triangle_shading(const HIPRTRenderData& rd, int prim, int tri_slot)
+{
+    TriangleShading ts;
+    ts.prim = prim;
+    const Bvh8Device& bvh = scene_bvh(rd);
+    if (bvh.shading != nullptr && tri_slot >= 0)
+    {
+        const float4* sp = reinterpret_cast<const float4*>(bvh.shading) + (size_t)tri_slot * 4;
+        const float4 s0 = __ldg(sp + 0), s1 = __ldg(sp + 1), s2 = __ldg(sp + 2), s3 = __ldg(sp + 3);
+        const int* tw = reinterpret_cast<const int*>(bvh.triangles + tri_slot);
+        ts.na = f3(s0.x, s0.y, s0.z); ts.nb = f3(s0.w, s1.x, s1.y); ts.nc = f3(s1.z, s1.w, s2.x);
+        ts.ta = make_float2(s2.y, s2.z); ts.tb = make_float2(s2.w, s3.x); ts.tc = make_float2(s3.y, s3.z);
+        ts.material_index = __ldg(tw + 7);
+        ts.has_normals = __ldg(tw + 11);
+        ts.from_record = true;
+        return ts;
+    }
+    const int3 vi = triangle_vertex_indices(rd, prim);
+    ts.na = ld3(rd.buffers.vertex_normals, vi.x); ts.nb = ld3(rd.buffers.vertex_normals, vi.y); ts.nc = ld3(rd.buffers.vertex_normals, vi.z);
+    ts.ta = ld2(rd.buffers.texcoords, vi.x); ts.tb = ld2(rd.buffers.texcoords, vi.y); ts.tc = ld2(rd.buffers.texcoords, vi.z);
+    ts.material_index = __ldg(rd.buffers.material_indices + prim);
+    ts.has_normals = __ldg(rd.buffers.has_vertex_normals + vi.x);
+    ts.from_record = false;
+    return ts;
+}
+
 // uv_interpolate: data[B] * u + data[C] * v + data[A] * (1 - u - v)
 PT_DEV float2 interpolate_texcoords(const HIPRTRenderData& rd, int3 vi, float2 uv)
 {
@@ -58,10 +98,21 @@ PT_DEV float2 interpolate_texcoords(const HIPRTRenderData& rd, int3 vi, float2 u
     return make_float2(b.x * uv.x + c.x * uv.y + a.x * w, b.y * uv.x + c.y * uv.y + a.y * w);
 }
 
+PT_DEV float2 interpolate_texcoords(const TriangleShading& ts, float2 uv)
+{
+    float w = 1.0f - uv.x - uv.y;
+    return make_float2(ts.tb.x * uv.x + ts.tc.x * uv.y + ts.ta.x * w, ts.tb.y * uv.x + ts.tc.y * uv.y + ts.ta.y * w);
+}
+
 PT_DEV float3 interpolate_normals(const HIPRTRenderData& rd, int3 vi, float2 uv)
 {
     float3 a = ld3(rd.buffers.vertex_normals, vi.x), b = ld3(rd.buffers.vertex_normals, vi.y), c = ld3(rd.buffers.vertex_normals, vi.z);
     return b * uv.x + c * uv.y + a * (1.0f - uv.x - uv.y);
+}
+
+PT_DEV float3 interpolate_normals(const TriangleShading& ts, float2 uv)
+{
+    return ts.nb * uv.x + ts.nc * uv.y + ts.na * (1.0f - uv.x - uv.y);
 }
 
 // normal_mapping (Intersect.h:30-62)
@@ -85,18 +136,17 @@ PT_DEV float3 normal_mapping(const HIPRTRenderData& rd, int normal_map_texture_i
 }
 
 // get_shading_normal (Intersect.h:64-83)
-PT_DEV float3 get_shading_normal(const HIPRTRenderData& rd, float3 geometric_normal, int primitive_index, int3 vi, float2 uv, float2 texcoords)
+PT_DEV float3 get_shading_normal(const HIPRTRenderData& rd, float3 geometric_normal, const TriangleShading& ts, float2 uv, float2 texcoords)
 {
-    int mat_index = __ldg(rd.buffers.material_indices + primitive_index);
     float3 surface_normal;
-    if (__ldg(rd.buffers.has_vertex_normals + vi.x))
-        surface_normal = normalize(interpolate_normals(rd, vi, uv));
+    if (ts.has_normals)
+        surface_normal = normalize(interpolate_normals(ts, uv));
     else
         surface_normal = geometric_normal;
 
-    int normal_map = material_field_i(rd, mat_index, offsetof(RendererMaterial, normal_map_texture_index));
+    int normal_map = material_field_i(rd, ts.material_index, offsetof(RendererMaterial, normal_map_texture_index));
     if (normal_map != B200PT_NO_TEXTURE)
-        surface_normal = normal_mapping(rd, normal_map, vi, texcoords, surface_normal);
+        surface_normal = normal_mapping(rd, normal_map, triangle_vertex_indices(rd, ts.prim), texcoords, surface_normal);   // (positions: by index, rare)
     return surface_normal;
 }
 
@@ -149,20 +199,20 @@ PT_DEV_NOINLINE bool trace_ray_from(const HIPRTRenderData& rd, float3 origin, fl
             return false;
         have_first = false;
 
-        int3 vi = triangle_vertex_indices(rd, hit.prim);
+        const TriangleShading ts = load_triangle_shading(rd, hit.prim, hit.tri_slot);
         float2 uv = make_float2(hit.u, hit.v);
         out.inter_point = origin + hit.t * direction;
         out.primitive_index = hit.prim;
-        out.texcoords = interpolate_texcoords(rd, vi, uv);
+        out.texcoords = interpolate_texcoords(ts, uv);
         out.geometric_normal = hit_geometric_normal(rd, hit);
-        out.shading_normal = get_shading_normal(rd, out.geometric_normal, hit.prim, vi, uv, out.texcoords);
+        out.shading_normal = get_shading_normal(rd, out.geometric_normal, ts, uv, out.texcoords);
         out.t = hit.t;
         out.uv = uv;
 
         if (is_inside_volume(payload.volume_state))
             payload.volume_state.distance_in_volume += hit.t;
 
-        int material_index = __ldg(rd.buffers.material_indices + hit.prim);
+        int material_index = ts.material_index;
         out.material_ref = get_intersection_material(rd, material_index, out.texcoords, payload.material) ? material_index + 1 : 0;
 
         if ((!is_inside_volume(payload.volume_state) || payload.material.specular_transmission == 0.0f) && !payload.material.thin_walled)
@@ -219,11 +269,11 @@ PT_DEV_NOINLINE bool shadow_light_ray_resolve(const HIPRTRenderData& rd, float t
     if (!(hit.t < t_max - 1.0e-4f))
         return false;
 
-    int material_index = __ldg(rd.buffers.material_indices + hit.prim);
+    const TriangleShading ts = load_triangle_shading(rd, hit.prim, hit.tri_slot);
+    int material_index = ts.material_index;
     int emission_texture_index = material_field_i(rd, material_index, offsetof(RendererMaterial, emission_texture_index));
-    int3 vi = triangle_vertex_indices(rd, hit.prim);
     float2 uv = make_float2(hit.u, hit.v);
-    float2 texcoords = interpolate_texcoords(rd, vi, uv);
+    float2 texcoords = interpolate_texcoords(ts, uv);
     if (emission_texture_index != B200PT_NO_TEXTURE)
     {
         // get_material_property leaves the (uninitialised) output untouched for CONSTANT_EMISSIVE_TEXTURE; black here
@@ -238,7 +288,7 @@ PT_DEV_NOINLINE bool shadow_light_ray_resolve(const HIPRTRenderData& rd, float t
         out.hit_emission = material_buffer_emission(rd, material_index);
 
     float3 ng = normalize(normalize(bvh8_triangle_normal(scene_bvh(rd), hit.tri_slot)));
-    out.hit_shading_normal = get_shading_normal(rd, ng, hit.prim, vi, uv, texcoords);
+    out.hit_shading_normal = get_shading_normal(rd, ng, ts, uv, texcoords);
     out.hit_distance = hit.t;
     out.hit_prim_index = hit.prim;
     return true;

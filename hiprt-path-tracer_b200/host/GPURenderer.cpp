@@ -148,6 +148,15 @@ void GPURenderer::set_scene(const Scene& scene)
     check(b200pt_tex2d_array_create(m_ctx, m_texture_descriptors.data(), (int)m_texture_descriptors.size(), &m_texture_array), "b200pt_tex2d_array_create");
     m_textures_dims.upload_data(dims);
 
+    // Per-triangle-slot shading records (b200pt.h): what a hit needs of its three vertices, gathered once instead of per hit.
+    // B200PT_SHADING_RECORDS=0 keeps the reference's buffers as the only source (A/B and the bit-identity test).
+    const char* records = std::getenv("B200PT_SHADING_RECORDS");
+    if (ntris > 0 && !(records && records[0] == '0'))
+        check(b200pt_bvh_attach_shading_data(m_ctx, m_bvh, m_triangle_indices.get_device_pointer(), reinterpret_cast<const float*>(m_normals.get_device_pointer()),
+                                             reinterpret_cast<const unsigned char*>(m_has_vertex_normals.get_device_pointer()),
+                                             reinterpret_cast<const float*>(m_texcoords.get_device_pointer()), m_material_indices.get_device_pointer(), nullptr),
+              "b200pt_bvh_attach_shading_data");
+
     RenderBuffers& b = m_render_data.buffers;
     m_render_data.geom = b200pt_bvh_device_handle(m_bvh);
     b.triangles_indices = m_triangle_indices.get_device_pointer();

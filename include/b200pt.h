@@ -150,6 +150,15 @@ B200PT_API int b200pt_tex2d_array_create(b200pt_ctx* ctx, void* const* descripto
 #define B200PT_BVH_BUILD_DEVICE_LBVH 2u   /* with B200PT_BVH_BUILD_DEVICE: the Karras radix tree instead of PLOC (faster to build, ~10 % higher SAH cost) */
 B200PT_API int b200pt_bvh_build(b200pt_ctx* ctx, const float* vertices, int vertex_count, const int* triangle_indices, int triangle_count, unsigned flags, b200pt_bvh** out_bvh);
 B200PT_API int b200pt_bvh_destroy(b200pt_ctx* ctx, b200pt_bvh* bvh);
+/* Optional, after the scene's vertex data is on the device (GPURenderer::set_scene, src/Renderer/GPURenderer.cpp:1041-1134 uploads it next to
+ * the geometry build): gathers, per triangle SLOT of the BVH, the three vertex normals and texcoords (one 64-byte record) plus the material index
+ * and vertex A's has_vertex_normals flag (the two spare words of the 48-byte triangle record). A hit then reads 2 + 2 sectors of its own slot
+ * instead of following the index buffer to three scattered vertices (~10 sectors): same values, so results are bit-identical with and without.
+ * The pointers are the device arrays RenderBuffers carries (triangles_indices, vertex_normals, has_vertex_normals, texcoords,
+ * material_indices); call it again after changing any of them, or with d_triangle_indices = NULL to detach. No counterpart in the reference
+ * (HIPRT hands out primitive ids only). Synchronous with respect to `stream`. */
+B200PT_API int b200pt_bvh_attach_shading_data(b200pt_ctx* ctx, b200pt_bvh* bvh, const int* d_triangle_indices, const float* d_vertex_normals,
+                                              const unsigned char* d_has_vertex_normals, const float* d_texcoords, const int* d_material_indices, b200pt_stream stream);
 B200PT_API void* b200pt_bvh_device_handle(b200pt_bvh* bvh);             /* value for HIPRTRenderData::geom */
 B200PT_API int b200pt_bvh_info(b200pt_bvh* bvh, unsigned* out_node_count, unsigned* out_triangle_count, float* out_sah_cost, double* out_build_seconds);
 B200PT_API int b200pt_bvh_get_stats(b200pt_bvh* bvh, b200pt_bvh_stats* out_stats);

@@ -850,6 +850,46 @@ def test_textured_materials_parity(pt, wl, ctx, ref):
         g.close()
 
 
+@pytest.mark.parametrize("workload", ["textured_cornell", "synthetic_small", "many_lights", "nested_dielectrics"])
+def test_shading_records_are_bit_identical(pt, wl, ctx, workload, monkeypatch):
+    """b200pt_bvh_attach_shading_data: the per-triangle-slot records (three vertex normals + texcoords in 64 bytes, material index and the
+    has-normals flag in the spare words of the triangle record) hold the very values a hit otherwise gathers through the index buffer, so
+    every buffer of a render -- G-buffer (materials from textures, normal-mapped shading normals), accumulation, reservoirs -- is equal bit
+    for bit with the records attached (the host layer's default) and without (B200PT_SHADING_RECORDS=0), in every path shape."""
+    W, H, frames = 160, 96, 3
+    def make():
+        if workload == "textured_cornell":
+            return _textured_cornell(wl, W, H)
+        if workload == "synthetic_small":
+            return wl.synthetic_small(W, H)
+        if workload == "many_lights":
+            return wl.many_lights(W, H, boxes=150, lights=3000)
+        return wl.golden_scene("nested-dielectrics-complex", W, H)
+    outputs = {}
+    for records in ("1", "0"):
+        monkeypatch.setenv("B200PT_SHADING_RECORDS", records)
+        cfg = make()
+        for mode in ("phased", "megakernel") if workload != "many_lights" else ("phased",):
+            ctx.set_path_mode(mode)
+            g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="gpu")
+            try:
+                for _ in range(frames):
+                    g.render_frame()
+                g.synchronize()
+                names = ["pixels", "first_hit_prim_index", "shading_normals", "geometric_normals", "materials", "denoiser_normals", "denoiser_albedo"]
+                if workload == "many_lights":
+                    names.append("restir_output_reservoirs")
+                outputs[(records, mode)] = {n: g.download(n).copy() for n in names}
+            finally:
+                g.close()
+                ctx.set_path_mode("phased")
+    for (records, mode), out in outputs.items():
+        if records == "0":
+            for name, value in out.items():
+                assert np.array_equal(value, outputs[("1", mode)][name], equal_nan=(value.dtype.kind == "f")), (workload, mode, name)
+    assert outputs[("1", "phased")]["pixels"].any()
+
+
 def test_column_tile_sharding_is_bit_identical(pt, wl, ctx):
     """The strong-scaling shard shape of config C3 (bench.py --sharding columns) on one device: three renderers own three column
     bands of the envmap scene; the union of their accumulation buffers equals the unsharded render bit for bit."""
