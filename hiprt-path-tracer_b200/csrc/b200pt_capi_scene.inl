@@ -306,7 +306,12 @@ static int ensure_wavefront(b200pt_ctx* ctx, int lane, uint32_t paths, uint32_t 
 {
     pt::WavefrontState& wf = ctx->wf[lane];
     std::vector<void*>& allocations = ctx->wf_allocations[lane];
-    if (paths <= wf.capacity && bounces <= wf.max_bounces)
+    // The seven per-path float4 records in three groups (launch.h: WavefrontState::stride_*): one array of 32- / 64- / 32-byte records per group by
+    // default, seven separate arrays with B200PT_PATH_RECORDS=0 (round 1's layout, kept for A/B; results do not depend on it). Read at every call
+    // so that a test can switch within one process: a change of layout reallocates.
+    const char* records_env = getenv("B200PT_PATH_RECORDS");
+    const bool grouped = !(records_env && records_env[0] == '0');
+    if (paths <= wf.capacity && bounces <= wf.max_bounces && wf.stride_ray == (grouped ? 2u : 1u))
         return B200PT_SUCCESS;
     CUDA_TRY(cudaSetDevice(ctx->device));
     CUDA_TRY(cudaDeviceSynchronize());
@@ -324,8 +329,23 @@ static int ensure_wavefront(b200pt_ctx* ctx, int lane, uint32_t paths, uint32_t 
         return p;
     };
     const size_t n = capacity;
-    float4** f4[] = {&wf.origin_rng, &wf.dir_prim, &wf.throughput, &wf.color, &wf.hit_point, &wf.hit_ns, &wf.hit_ng, &wf.final_color, &wf.aov_normal, &wf.aov_albedo, &wf.ris_a, &wf.ris_b};
     bool ok = true;
+    struct Group { float4** fields[3]; int count; uint32_t stride; };
+    const Group groups[] = {{{&wf.origin_rng, &wf.dir_prim, nullptr}, 2, 2u}, {{&wf.hit_point, &wf.hit_ns, &wf.hit_ng}, 3, 4u}, {{&wf.throughput, &wf.color, nullptr}, 2, 2u}};
+    for (const Group& g : groups)
+    {
+        if (grouped)
+        {
+            float4* base = static_cast<float4*>(alloc(n * g.stride * sizeof(float4)));
+            ok &= base != nullptr;
+            for (int k = 0; k < g.count; k++)
+                *g.fields[k] = base ? base + k : nullptr;
+        }
+        else
+            for (int k = 0; k < g.count; k++)
+                ok &= (*g.fields[k] = static_cast<float4*>(alloc(n * sizeof(float4)))) != nullptr;
+    }
+    float4** f4[] = {&wf.final_color, &wf.aov_normal, &wf.aov_albedo, &wf.ris_a, &wf.ris_b};
     for (float4** a : f4)
         ok &= (*a = static_cast<float4*>(alloc(n * sizeof(float4)))) != nullptr;
     float4** nee[] = {&wf.nee_ray_o, &wf.nee_ray_d, &wf.nee_pending};
@@ -365,6 +385,9 @@ static int ensure_wavefront(b200pt_ctx* ctx, int lane, uint32_t paths, uint32_t 
     wf.cursors = wf.counts + pt::kCountsPerBounce * (max_bounces + 2);
     wf.capacity = capacity;
     wf.max_bounces = max_bounces;
+    wf.stride_ray = grouped ? 2u : 1u;
+    wf.stride_hit = grouped ? 4u : 1u;
+    wf.stride_radiance = grouped ? 2u : 1u;
     return B200PT_SUCCESS;
 }
 

@@ -187,7 +187,8 @@ __global__ void __launch_bounds__(256) PT_SUFFIXED(k_bin_count)(const Bvh8Device
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
     {
         const uint32_t id = q.ids[i];
-        const uint32_t key = ray_bin_key(b, q.ray_o[id], q.ray_d[id], bits);
+        const size_t at = (size_t)id * (q.ray_stride_minus_1 + 1u);
+        const uint32_t key = ray_bin_key(b, q.ray_o[at], q.ray_d[at], bits);
         keys[i] = key;
         // one atomic per distinct key of the warp: neighbouring queue entries often share a cell, and a popular cell's counter would
         // otherwise serialise the whole grid (first version: 2 M rays of the Cornell box in a few hundred cells, +4 ms)

@@ -71,6 +71,13 @@ struct WavefrontState
     uint32_t* bin_keys;      // 3 * capacity: bin of queue entry i (histogram pass -> scatter pass)
     float4* ris_a;           // phased RIS (wavefront_mis.cuh): the reservoir between R1, R2 and the resolve, 2 x float4 per slot
     float4* ris_b;
+    // Layout of the seven per-path float4 records above, in three groups that are read and written together: RAY (origin_rng, dir_prim), HIT
+    // (hit_point, hit_ns, hit_ng) and RADIANCE (throughput, color). Entry of `slot` = array[slot * stride of its group]. Strides 1 / 1 / 1: seven
+    // separate arrays (round 1). Strides 2 / 4 / 2 (default): each group is one array of 32- / 64- / 32-byte records and the pointers of a group are
+    // base + 0, 1, .. of it, so that a phase working on a material-sorted (scattered) queue moves whole 32-byte sectors it uses entirely instead
+    // of one half-used sector per field, and does not pull the groups it does not read. (One 128-byte record per path was measured too: it is
+    // what wins on scattered queues and loses on queues in slot order, where every load instruction of a warp then touches 32 lines.)
+    uint32_t stride_ray, stride_hit, stride_radiance;
 };
 constexpr int kRayBinBitsMax = 6;                                   // cells per axis = 2^bits
 constexpr uint32_t kRayBinsMax = 1u << (3 * kRayBinBitsMax + 3);    // cells x 8 direction octants
@@ -144,6 +151,8 @@ struct RayQueueView
     float4* hit_tuvp;           // closest: [id] t, u, v, primitive (int bits; -1 = miss)
     uint32_t* hit_tri_slot;     // closest: [id] index of the triangle in the BVH triangle array
     float4* occluded_flag;      // any-hit: the ray_o array; .w is set to -1 when the ray is occluded
+    uint32_t ray_stride_minus_1; // ray_o / ray_d entry of `id` = array[id * (1 + this)]: 0 for contiguous ray arrays (what aggregate initialisers
+                                 // that stop at occluded_flag give), stride_ray - 1 for the grouped path records (WavefrontState)
 };
 
 #define PT_DECLARE_LAUNCHERS(S)                                                                                                        \

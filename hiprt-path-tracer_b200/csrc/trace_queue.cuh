@@ -238,7 +238,8 @@ struct LaneStack
 
 PT_DEV void trace_queue_load_ray(const RayQueueView& q, const uint32_t ray_id, const bool any_hit, RaySlabs& r, int& last_prim, float& t_best)
 {
-    const float4 ro = q.ray_o[ray_id], rdir = q.ray_d[ray_id];
+    const size_t at = (size_t)ray_id * (q.ray_stride_minus_1 + 1u);
+    const float4 ro = q.ray_o[at], rdir = q.ray_d[at];
     r.o = f3(ro.x, ro.y, ro.z);
     r.d = f3(rdir.x, rdir.y, rdir.z);
     last_prim = __float_as_int(rdir.w);

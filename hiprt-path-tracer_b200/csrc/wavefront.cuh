@@ -88,18 +88,23 @@ struct PathRegs
     PT_DEV PathRegs() : rng(0u) {}
 };
 
+// index of a path's entry in the per-path float4 records of each group (WavefrontState::stride_*)
+PT_DEV size_t wf_ray_at(const WavefrontState& wf, uint32_t slot) { return (size_t)slot * wf.stride_ray; }
+PT_DEV size_t wf_hit_at(const WavefrontState& wf, uint32_t slot) { return (size_t)slot * wf.stride_hit; }
+PT_DEV size_t wf_radiance_at(const WavefrontState& wf, uint32_t slot) { return (size_t)slot * wf.stride_radiance; }
+
 PT_DEV void wf_store_ray(const WavefrontState& wf, uint32_t slot, const PathRegs& p)
 {
-    wf.origin_rng[slot] = make_float4(p.origin.x, p.origin.y, p.origin.z, __uint_as_float(p.rng.state));
-    wf.dir_prim[slot] = make_float4(p.direction.x, p.direction.y, p.direction.z, __int_as_float(p.hit.primitive_index));
-    wf.throughput[slot] = make_float4(p.payload.throughput.r, p.payload.throughput.g, p.payload.throughput.b, 0.0f);
-    wf.color[slot] = make_float4(p.payload.ray_color.r, p.payload.ray_color.g, p.payload.ray_color.b, 0.0f);
+    wf.origin_rng[wf_ray_at(wf, slot)] = make_float4(p.origin.x, p.origin.y, p.origin.z, __uint_as_float(p.rng.state));
+    wf.dir_prim[wf_ray_at(wf, slot)] = make_float4(p.direction.x, p.direction.y, p.direction.z, __int_as_float(p.hit.primitive_index));
+    wf.throughput[wf_radiance_at(wf, slot)] = make_float4(p.payload.throughput.r, p.payload.throughput.g, p.payload.throughput.b, 0.0f);
+    wf.color[wf_radiance_at(wf, slot)] = make_float4(p.payload.ray_color.r, p.payload.ray_color.g, p.payload.ray_color.b, 0.0f);
     copy_volume_state(reinterpret_cast<RayVolumeState*>(wf.volume + (size_t)slot * 9), &p.payload.volume_state);
 }
 
 PT_DEV void wf_load_ray(const WavefrontState& wf, uint32_t slot, PathRegs& p)
 {
-    const float4 o = wf.origin_rng[slot], d = wf.dir_prim[slot], t = wf.throughput[slot], c = wf.color[slot];
+    const float4 o = wf.origin_rng[wf_ray_at(wf, slot)], d = wf.dir_prim[wf_ray_at(wf, slot)], t = wf.throughput[wf_radiance_at(wf, slot)], c = wf.color[wf_radiance_at(wf, slot)];
     p.origin = f3(o.x, o.y, o.z);
     p.rng.state = __float_as_uint(o.w);
     p.direction = f3(d.x, d.y, d.z);
@@ -113,15 +118,15 @@ PT_DEV void wf_load_ray(const WavefrontState& wf, uint32_t slot, PathRegs& p)
 // SPLIT mode: what the extend kernel hands to the shade kernel (the ray fields other than rng/prim/volume are unchanged)
 PT_DEV void wf_store_hit(const WavefrontState& wf, uint32_t slot, const PathRegs& p)
 {
-    wf.origin_rng[slot].w = __uint_as_float(p.rng.state);          // trace_ray may have drawn a wavelength
-    wf.hit_point[slot] = make_float4(p.hit.inter_point.x, p.hit.inter_point.y, p.hit.inter_point.z, __int_as_float(p.hit.primitive_index));
+    wf.origin_rng[wf_ray_at(wf, slot)].w = __uint_as_float(p.rng.state);          // trace_ray may have drawn a wavelength
+    wf.hit_point[wf_hit_at(wf, slot)] = make_float4(p.hit.inter_point.x, p.hit.inter_point.y, p.hit.inter_point.z, __int_as_float(p.hit.primitive_index));
     // A material without texture overrides is a function of its index alone: the slot keeps the index (in the spare word of
     // the shading normal) and the shading kernels rebuild it from the material buffer (L1/L2 resident) where they load the
     // vertex; only textured hits write their 256-byte material to the slot. B200PT_SLOT_MATERIALS=1 (a debug switch read by
     // the launcher into wf.force_slot_materials) restores the copy for every hit.
     const int material_ref = wf.force_slot_materials ? 0 : p.hit.material_ref;
-    wf.hit_ns[slot] = make_float4(p.hit.shading_normal.x, p.hit.shading_normal.y, p.hit.shading_normal.z, __int_as_float(material_ref));
-    wf.hit_ng[slot] = make_float4(p.hit.geometric_normal.x, p.hit.geometric_normal.y, p.hit.geometric_normal.z, 0.0f);
+    wf.hit_ns[wf_hit_at(wf, slot)] = make_float4(p.hit.shading_normal.x, p.hit.shading_normal.y, p.hit.shading_normal.z, __int_as_float(material_ref));
+    wf.hit_ng[wf_hit_at(wf, slot)] = make_float4(p.hit.geometric_normal.x, p.hit.geometric_normal.y, p.hit.geometric_normal.z, 0.0f);
     copy_volume_state(reinterpret_cast<RayVolumeState*>(wf.volume + (size_t)slot * 9), &p.payload.volume_state);
     if (material_ref == 0)
         store_material(reinterpret_cast<SimplifiedRendererMaterial*>(wf.materials) + slot, p.payload.material);
@@ -140,7 +145,7 @@ PT_DEV void wf_load_hit(const HIPRTRenderData& rd, const WavefrontState& wf, uin
         load_material(p.payload.material, rd.g_buffer.materials + pixel_index);
         return;
     }
-    const float4 hp = wf.hit_point[slot], ns = wf.hit_ns[slot], ng = wf.hit_ng[slot];
+    const float4 hp = wf.hit_point[wf_hit_at(wf, slot)], ns = wf.hit_ns[wf_hit_at(wf, slot)], ng = wf.hit_ng[wf_hit_at(wf, slot)];
     p.hit.inter_point = f3(hp.x, hp.y, hp.z);
     p.hit.primitive_index = __float_as_int(hp.w);
     p.hit.shading_normal = f3(ns.x, ns.y, ns.z);
@@ -472,8 +477,8 @@ PT_DEV void wf_direct_path(const HIPRTRenderData& rd, int2 res, const Tile& tile
     wf_load_ray(wf, slot, p);
     wf_load_hit(rd, wf, slot, pixel_index, bounce, p);
     shade_vertex_direct<LSS, ESS, LATER, GGX_SAMPLER>(rd, p.payload, p.hit, p.direction, p.rng, make_int2(x, y), res, bounce);
-    wf.origin_rng[slot].w = __uint_as_float(p.rng.state);
-    wf.color[slot] = make_float4(p.payload.ray_color.r, p.payload.ray_color.g, p.payload.ray_color.b, 0.0f);
+    wf.origin_rng[wf_ray_at(wf, slot)].w = __uint_as_float(p.rng.state);
+    wf.color[wf_radiance_at(wf, slot)] = make_float4(p.payload.ray_color.r, p.payload.ray_color.g, p.payload.ray_color.b, 0.0f);
 }
 
 template <int GGX_SAMPLER>

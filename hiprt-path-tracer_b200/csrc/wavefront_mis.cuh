@@ -83,7 +83,7 @@ PT_DEV void nee_load_vertex(const HIPRTRenderData& rd, const WavefrontState& wf,
     }
 }
 
-PT_DEV void nee_store_rng(const WavefrontState& wf, uint32_t slot, const Rng& rng) { wf.origin_rng[slot].w = __uint_as_float(rng.state); }
+PT_DEV void nee_store_rng(const WavefrontState& wf, uint32_t slot, const Rng& rng) { wf.origin_rng[wf_ray_at(wf, slot)].w = __uint_as_float(rng.state); }
 
 // ---- P1: light sample + BSDF eval (sample_one_light_MIS, first half: Lights.h:115-170) ------------------------------------
 PT_DEV void nee_light_eval_body(const HIPRTRenderData& rd, const WavefrontState& wf, int bounce, uint32_t slot, PathRegs& p)

@@ -890,6 +890,53 @@ def test_shading_records_are_bit_identical(pt, wl, ctx, workload, monkeypatch):
     assert outputs[("1", "phased")]["pixels"].any()
 
 
+@pytest.mark.parametrize("workload", ["cornell", "synthetic_small", "many_lights", "cornell_ris"])
+def test_path_record_layouts_are_bit_identical(pt, wl, ctx, workload, monkeypatch):
+    """WavefrontState::stride_*: the seven per-path float4 records grouped into ray / hit / radiance records of 32 / 64 / 32 bytes (default) against seven separate
+    arrays (B200PT_PATH_RECORDS=0, round 1's layout). Only addresses change: every path shape (phased with sample batches, split, fused) and the
+    ray-queue kernel's strided view of origin / direction give the same bits."""
+    W, H, frames = 160, 96, 3
+    def make():
+        if workload == "cornell":
+            return wl.cornell(W, H)
+        if workload == "cornell_ris":
+            cfg = wl.cornell(W, H)
+            cfg["options"] = dict(lss="ris", ess="none", ggx=0, later=3)
+            return cfg
+        if workload == "synthetic_small":
+            return wl.synthetic_small(W, H)
+        return wl.many_lights(W, H, boxes=150, lights=3000)
+    outputs = {}
+    try:
+        for layout in ("1", "0", "1"):
+            monkeypatch.setenv("B200PT_PATH_RECORDS", layout)
+            for mode in ("phased", "split", "fused") if workload != "many_lights" else ("phased",):
+                ctx.set_path_mode(mode)
+                cfg = make()
+                cfg["settings"] = dict(cfg["settings"], samples_per_frame=2)
+                g = wl.setup_gpu(pt, ctx, cfg, seed_schedule="gpu")
+                try:
+                    for _ in range(frames):
+                        g.render_frame()
+                    g.synchronize()
+                    out = {n: g.download(n).copy() for n in ("pixels", "first_hit_prim_index", "shading_normals", "denoiser_albedo")}
+                finally:
+                    g.close()
+                key = (layout, mode)
+                if key in outputs:       # the second "1" run: switching back works too
+                    for n, v in out.items():
+                        assert np.array_equal(v, outputs[key][n], equal_nan=(v.dtype.kind == "f")), (workload, mode, n, "second run")
+                outputs[key] = out
+    finally:
+        ctx.set_path_mode("phased")
+        monkeypatch.delenv("B200PT_PATH_RECORDS", raising=False)
+    for (layout, mode), out in outputs.items():
+        if layout == "0":
+            for n, v in out.items():
+                assert np.array_equal(v, outputs[("1", mode)][n], equal_nan=(v.dtype.kind == "f")), (workload, mode, n)
+    assert outputs[("1", "phased")]["pixels"].any()
+
+
 def test_column_tile_sharding_is_bit_identical(pt, wl, ctx):
     """The strong-scaling shard shape of config C3 (bench.py --sharding columns) on one device: three renderers own three column
     bands of the envmap scene; the union of their accumulation buffers equals the unsharded render bit for bit."""
