@@ -348,9 +348,21 @@ static int ensure_wavefront(b200pt_ctx* ctx, int lane, uint32_t paths, uint32_t 
     float4** f4[] = {&wf.final_color, &wf.aov_normal, &wf.aov_albedo, &wf.ris_a, &wf.ris_b};
     for (float4** a : f4)
         ok &= (*a = static_cast<float4*>(alloc(n * sizeof(float4)))) != nullptr;
-    float4** nee[] = {&wf.nee_ray_o, &wf.nee_ray_d, &wf.nee_pending};
-    for (float4** a : nee)
-        ok &= (*a = static_cast<float4*>(alloc(4 * n * sizeof(float4)))) != nullptr;
+    if (grouped)
+    {
+        // 64-byte NEE records: origin | t_max, pending contribution, direction | primitive, spare
+        float4* base = static_cast<float4*>(alloc(4 * n * 4 * sizeof(float4)));
+        ok &= base != nullptr;
+        wf.nee_ray_o = base;
+        wf.nee_pending = base ? base + 1 : nullptr;
+        wf.nee_ray_d = base ? base + 2 : nullptr;
+    }
+    else
+    {
+        float4** nee[] = {&wf.nee_ray_o, &wf.nee_ray_d, &wf.nee_pending};
+        for (float4** a : nee)
+            ok &= (*a = static_cast<float4*>(alloc(4 * n * sizeof(float4)))) != nullptr;
+    }
     ok &= (wf.volume = static_cast<uint32_t*>(alloc(n * 36))) != nullptr;
     ok &= (wf.materials = alloc(n * 256)) != nullptr;
     ok &= (wf.ray_queue[0] = static_cast<uint32_t*>(alloc(n * 4))) != nullptr;
@@ -361,8 +373,19 @@ static int ensure_wavefront(b200pt_ctx* ctx, int lane, uint32_t paths, uint32_t 
     ok &= (wf.bucket_count = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * pt::kSortBuckets))) != nullptr;
     if (ok)
         ok &= cudaMemset(wf.bucket_count, 0, sizeof(uint32_t) * pt::kSortBuckets) == cudaSuccess;
-    ok &= (wf.hit_tuvp = static_cast<float4*>(alloc(2 * n * sizeof(float4)))) != nullptr;
-    ok &= (wf.hit_tri_slot = static_cast<uint32_t*>(alloc(2 * n * 4))) != nullptr;
+    if (grouped)
+    {
+        // 32-byte hit records: t, u, v, primitive | triangle slot, 3 spare words
+        float4* base = static_cast<float4*>(alloc(2 * n * 2 * sizeof(float4)));
+        ok &= base != nullptr;
+        wf.hit_tuvp = base;
+        wf.hit_tri_slot = base ? reinterpret_cast<uint32_t*>(base + 1) : nullptr;
+    }
+    else
+    {
+        ok &= (wf.hit_tuvp = static_cast<float4*>(alloc(2 * n * sizeof(float4)))) != nullptr;
+        ok &= (wf.hit_tri_slot = static_cast<uint32_t*>(alloc(2 * n * 4))) != nullptr;
+    }
     ok &= (wf.any_queue = static_cast<uint32_t*>(alloc(3 * n * 4))) != nullptr;
     ok &= (wf.closest_queue = static_cast<uint32_t*>(alloc(n * 4))) != nullptr;
     ok &= (wf.bin_hist = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * (pt::kRayBinsMax + 1u)))) != nullptr;
@@ -388,6 +411,9 @@ static int ensure_wavefront(b200pt_ctx* ctx, int lane, uint32_t paths, uint32_t 
     wf.stride_ray = grouped ? 2u : 1u;
     wf.stride_hit = grouped ? 4u : 1u;
     wf.stride_radiance = grouped ? 2u : 1u;
+    wf.stride_nee = grouped ? 4u : 1u;
+    wf.stride_hitrec = grouped ? 2u : 1u;
+    wf.stride_hitrec_words = grouped ? 8u : 1u;
     return B200PT_SUCCESS;
 }
 

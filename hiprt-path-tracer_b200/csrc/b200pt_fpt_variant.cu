@@ -225,7 +225,7 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
         {
             PT_VARIANT_NAME(k_wf_camera)<<<blocks(128), 128, 0, stream>>>(*rd, res, tile, *wf, *batch);
             stage(STAGE_TRACE);
-            RayQueueView q = {wf->ray_queue[1], counts + 0, cursors + 0, wf->origin_rng, wf->dir_prim, wf->hit_tuvp, wf->hit_tri_slot, nullptr, wf->stride_ray - 1u};
+            RayQueueView q = {wf->ray_queue[1], counts + 0, cursors + 0, wf->origin_rng, wf->dir_prim, wf->hit_tuvp, wf->hit_tri_slot, nullptr, wf->stride_ray - 1u, wf->stride_hitrec - 1u, wf->stride_hitrec_words - 1u};
             e = PT_SUFFIXED(launch_trace_queue)(rd->geom, q, false, trace_blocks, counters, stream);
             if (e != cudaSuccess)
                 return e;
@@ -239,7 +239,7 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
         else if (phased)
         {
             stage(bin_bits_ext > 0 ? STAGE_SORT : STAGE_TRACE);
-            RayQueueView q = {wf->ray_queue[(bounce - 1) & 1], counts + 0, cursors + 0, wf->origin_rng, wf->dir_prim, wf->hit_tuvp, wf->hit_tri_slot, nullptr, wf->stride_ray - 1u};
+            RayQueueView q = {wf->ray_queue[(bounce - 1) & 1], counts + 0, cursors + 0, wf->origin_rng, wf->dir_prim, wf->hit_tuvp, wf->hit_tri_slot, nullptr, wf->stride_ray - 1u, wf->stride_hitrec - 1u, wf->stride_hitrec_words - 1u};
             // rays regrouped by origin cell and direction octant (launch_bin_rays); SURFACE then walks the same order: the rays of a
             // cell hit neighbouring triangles, so its vertex / normal gathers share cache lines too
             e = PT_SUFFIXED(launch_bin_rays)(rd->geom, q, wf->bin_hist, wf->bin_keys, wf->binned_ext, bin_bits_ext, wf->sm_count, stream);
@@ -269,8 +269,9 @@ cudaError_t PT_VARIANT_NAME(launch_FullPathTracer)(const HIPRTRenderData* rd, in
             const unsigned g64 = blocks(64);
             const bool lights = rd->buffers.emissive_triangles_count > 0;
             const bool envmap = PT_ESS != 0 && rd->world_settings.ambient_light_type == AMBIENT_ENVMAP;
-            RayQueueView qa = {wf->any_queue, counts + 2, cursors + 6, wf->nee_ray_o, wf->nee_ray_d, nullptr, nullptr, wf->nee_ray_o};
-            RayQueueView qc = {wf->closest_queue, counts + 3, cursors + 9, wf->nee_ray_o, wf->nee_ray_d, wf->hit_tuvp, wf->hit_tri_slot, nullptr};
+            RayQueueView qa = {wf->any_queue, counts + 2, cursors + 6, wf->nee_ray_o, wf->nee_ray_d, nullptr, nullptr, wf->nee_ray_o, wf->stride_nee - 1u, 0u, 0u};
+            RayQueueView qc = {wf->closest_queue, counts + 3, cursors + 9, wf->nee_ray_o, wf->nee_ray_d, wf->hit_tuvp, wf->hit_tri_slot, nullptr, wf->stride_nee - 1u,
+                               wf->stride_hitrec - 1u, wf->stride_hitrec_words - 1u};
             if (kPhasesRis)
             {
                 // R1 -> closest trace of the BSDF candidates' rays -> R2 -> envmap phases -> any-hit trace of the winners' shadow rays (+ the

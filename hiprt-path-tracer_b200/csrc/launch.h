@@ -78,6 +78,11 @@ struct WavefrontState
     // of one half-used sector per field, and does not pull the groups it does not read. (One 128-byte record per path was measured too: it is
     // what wins on scattered queues and loses on queues in slot order, where every load instruction of a warp then touches 32 lines.)
     uint32_t stride_ray, stride_hit, stride_radiance;
+    // Likewise the NEE records (nee_ray_o | nee_pending, then nee_ray_d: 64-byte records, so that the resolve phase reads a ray's t_max flag
+    // and its pending contribution out of ONE sector and the generating phases write two whole sectors) and the hit records of the ray-queue
+    // kernel (hit_tuvp and hit_tri_slot in one 32-byte record: one sector written per ray and read per hit instead of two). Entry of id k =
+    // nee_*[k * stride_nee], hit_tuvp[k * stride_hitrec], hit_tri_slot[k * stride_hitrec_words]; 1 / 1 / 1 = separate arrays.
+    uint32_t stride_nee, stride_hitrec, stride_hitrec_words;
 };
 constexpr int kRayBinBitsMax = 6;                                   // cells per axis = 2^bits
 constexpr uint32_t kRayBinsMax = 1u << (3 * kRayBinBitsMax + 3);    // cells x 8 direction octants
@@ -151,8 +156,10 @@ struct RayQueueView
     float4* hit_tuvp;           // closest: [id] t, u, v, primitive (int bits; -1 = miss)
     uint32_t* hit_tri_slot;     // closest: [id] index of the triangle in the BVH triangle array
     float4* occluded_flag;      // any-hit: the ray_o array; .w is set to -1 when the ray is occluded
-    uint32_t ray_stride_minus_1; // ray_o / ray_d entry of `id` = array[id * (1 + this)]: 0 for contiguous ray arrays (what aggregate initialisers
-                                 // that stop at occluded_flag give), stride_ray - 1 for the grouped path records (WavefrontState)
+    uint32_t ray_stride_minus_1; // ray_o / ray_d / occluded_flag entry of `id` = array[id * (1 + this)]: 0 for contiguous ray arrays (what aggregate initialisers
+                                 // that stop at occluded_flag give), stride_ray - 1 / stride_nee - 1 for the grouped records (WavefrontState)
+    uint32_t hit_stride_minus_1;      // likewise hit_tuvp[id * (1 + this)]
+    uint32_t hit_word_stride_minus_1; // and hit_tri_slot[id * (1 + this)]
 };
 
 #define PT_DECLARE_LAUNCHERS(S)                                                                                                        \

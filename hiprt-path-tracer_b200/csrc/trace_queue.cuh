@@ -257,12 +257,12 @@ PT_DEV void trace_queue_store_hit(const RayQueueView& q, const uint32_t ray_id, 
     if (ANY_HIT)
     {
         if (hit.prim >= 0)
-            q.occluded_flag[ray_id].w = -1.0f;
+            q.occluded_flag[(size_t)ray_id * (q.ray_stride_minus_1 + 1u)].w = -1.0f;
     }
     else
     {
-        q.hit_tuvp[ray_id] = make_float4(hit.t, hit.u, hit.v, __int_as_float(hit.prim));
-        q.hit_tri_slot[ray_id] = (uint32_t)hit.tri_slot;
+        q.hit_tuvp[(size_t)ray_id * (q.hit_stride_minus_1 + 1u)] = make_float4(hit.t, hit.u, hit.v, __int_as_float(hit.prim));
+        q.hit_tri_slot[(size_t)ray_id * (q.hit_word_stride_minus_1 + 1u)] = (uint32_t)hit.tri_slot;
     }
 }
 

@@ -92,6 +92,10 @@ struct PathRegs
 PT_DEV size_t wf_ray_at(const WavefrontState& wf, uint32_t slot) { return (size_t)slot * wf.stride_ray; }
 PT_DEV size_t wf_hit_at(const WavefrontState& wf, uint32_t slot) { return (size_t)slot * wf.stride_hit; }
 PT_DEV size_t wf_radiance_at(const WavefrontState& wf, uint32_t slot) { return (size_t)slot * wf.stride_radiance; }
+// ... of an id k (slot, or which * capacity + slot) in the NEE records and in the ray-queue kernel's hit records
+PT_DEV size_t nee_at(const WavefrontState& wf, size_t k) { return k * wf.stride_nee; }
+PT_DEV size_t hitrec_at(const WavefrontState& wf, size_t k) { return k * wf.stride_hitrec; }
+PT_DEV size_t hitrec_word_at(const WavefrontState& wf, size_t k) { return k * wf.stride_hitrec_words; }
 
 PT_DEV void wf_store_ray(const WavefrontState& wf, uint32_t slot, const PathRegs& p)
 {
@@ -326,11 +330,11 @@ PT_DEV void wf_camera_surface_path(const HIPRTRenderData& rd, int2 res, const Ti
     const uint32_t pass = slot / wf.tile_pixels;
     PathRegs p;
     wf_load_ray(wf, slot, p);
-    const float4 h = wf.hit_tuvp[slot];
+    const float4 h = wf.hit_tuvp[hitrec_at(wf, slot)];
     Hit first;
     first.t = h.x; first.u = h.y; first.v = h.z;
     first.prim = __float_as_int(h.w);
-    first.tri_slot = (int)wf.hit_tri_slot[slot];
+    first.tri_slot = (int)wf.hit_tri_slot[hitrec_word_at(wf, slot)];
     // ---- the rest of CameraRays (CameraRays.h:150-170)
     const bool found = trace_ray_from(rd, p.origin, p.direction, p.payload, p.hit, -1, p.rng, first, true);
     if (found && material_is_emissive(p.payload.material) && dot(-p.direction, p.hit.geometric_normal) < 0)
@@ -512,11 +516,11 @@ PT_DEV void wf_surface_path(const HIPRTRenderData& rd, int2 res, const Tile& til
     const uint32_t slot = wf.ray_queue[(bounce - 1) & 1][i];
     PathRegs p;
     wf_load_ray(wf, slot, p);
-    const float4 h = wf.hit_tuvp[slot];
+    const float4 h = wf.hit_tuvp[hitrec_at(wf, slot)];
     Hit first;
     first.t = h.x; first.u = h.y; first.v = h.z;
     first.prim = __float_as_int(h.w);
-    first.tri_slot = (int)wf.hit_tri_slot[slot];
+    first.tri_slot = (int)wf.hit_tri_slot[hitrec_word_at(wf, slot)];
     const bool found = trace_ray_from(rd, p.origin, p.direction, p.payload, p.hit, p.hit.primitive_index, p.rng, first, true);
     if (found)
     {

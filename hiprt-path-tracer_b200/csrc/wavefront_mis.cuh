@@ -28,16 +28,16 @@ PT_DEV size_t nee_index(const WavefrontState& wf, int which, uint32_t slot) { re
 
 PT_DEV void nee_store_none(const WavefrontState& wf, int which, uint32_t slot)
 {
-    wf.nee_ray_o[nee_index(wf, which, slot)] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
+    wf.nee_ray_o[nee_at(wf, nee_index(wf, which, slot))] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
 }
 
 // Records NEE ray `which` of the path and appends it to the bounce's any-hit (rays 0, 2, 3) or closest-hit (ray 1) id list
 PT_DEV void nee_store(const WavefrontState& wf, int bounce, int which, uint32_t slot, float3 origin, float t_max, float3 direction, int last_prim, RGB pending, float pending_w)
 {
     const size_t k = nee_index(wf, which, slot);
-    wf.nee_ray_o[k] = make_float4(origin.x, origin.y, origin.z, t_max);
-    wf.nee_ray_d[k] = make_float4(direction.x, direction.y, direction.z, __int_as_float(last_prim));
-    wf.nee_pending[k] = make_float4(pending.r, pending.g, pending.b, pending_w);
+    wf.nee_ray_o[nee_at(wf, k)] = make_float4(origin.x, origin.y, origin.z, t_max);
+    wf.nee_ray_d[nee_at(wf, k)] = make_float4(direction.x, direction.y, direction.z, __int_as_float(last_prim));
+    wf.nee_pending[nee_at(wf, k)] = make_float4(pending.r, pending.g, pending.b, pending_w);
     if (which == NEE_LIGHT_BSDF)
         queue_push(wf.closest_queue, wf.counts + kCountsPerBounce * bounce + 3, true, (uint32_t)k);
     else
@@ -91,7 +91,7 @@ PT_DEV void nee_light_eval_body(const HIPRTRenderData& rd, const WavefrontState&
     nee_store_none(wf, NEE_LIGHT, slot);
     // ray 1 doubles as the "P2 has work" flag: t_max = -2 tells P2 to skip its BSDF sample (light pdf <= 0: the
     // reference returns before sampling the BSDF, Lights.h:127-128)
-    wf.nee_ray_o[nee_index(wf, NEE_LIGHT_BSDF, slot)] = make_float4(0.0f, 0.0f, 0.0f, -2.0f);
+    wf.nee_ray_o[nee_at(wf, nee_index(wf, NEE_LIGHT_BSDF, slot))] = make_float4(0.0f, 0.0f, 0.0f, -2.0f);
     if (lights_prelude(rd, p.payload.material, bounce) != LIGHTS_SAMPLE)
         return;
 
@@ -107,7 +107,7 @@ PT_DEV void nee_light_eval_body(const HIPRTRenderData& rd, const WavefrontState&
     nee_store_rng(wf, slot, p.rng);
     if (light_sample_pdf <= 0.0f)
         return;
-    wf.nee_ray_o[nee_index(wf, NEE_LIGHT_BSDF, slot)].w = -1.0f;   // P2 runs
+    wf.nee_ray_o[nee_at(wf, nee_index(wf, NEE_LIGHT_BSDF, slot))].w = -1.0f;   // P2 runs
 
     float3 shadow_ray_direction = random_light_point - evaluated_point;
     float distance_to_light = length(shadow_ray_direction);
@@ -164,10 +164,10 @@ template <int ESS>
 PT_DEV void env_light_eval_body(const HIPRTRenderData& rd, const WavefrontState& wf, int bounce, uint32_t slot, PathRegs& p)
 {
     nee_store_none(wf, NEE_ENV, slot);
-    wf.nee_ray_o[nee_index(wf, NEE_ENV_BSDF, slot)] = make_float4(0.0f, 0.0f, 0.0f, -2.0f);
+    wf.nee_ray_o[nee_at(wf, nee_index(wf, NEE_ENV_BSDF, slot))] = make_float4(0.0f, 0.0f, 0.0f, -2.0f);
     if (!envmap_prelude<ESS>(rd, p.payload.material))
         return;
-    wf.nee_ray_o[nee_index(wf, NEE_ENV_BSDF, slot)].w = -1.0f;   // P4 runs
+    wf.nee_ray_o[nee_at(wf, nee_index(wf, NEE_ENV_BSDF, slot))].w = -1.0f;   // P4 runs
 
     const float3 view_direction = -p.direction;
     const HitInfo& hit = p.hit;
@@ -233,7 +233,7 @@ template <int GGX_SAMPLER>
 PT_DEV void nee_bsdf_sample_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
 {
     const uint32_t slot = wf.sorted_queue[i];
-    if (wf.nee_ray_o[nee_index(wf, NEE_LIGHT_BSDF, slot)].w != -1.0f)
+    if (wf.nee_ray_o[nee_at(wf, nee_index(wf, NEE_LIGHT_BSDF, slot))].w != -1.0f)
         return;
     uint32_t x, y, pixel_index;
     wf_slot_to_pixel(wf, tile, res, slot, x, y, pixel_index);
@@ -257,7 +257,7 @@ template <int GGX_SAMPLER>
 PT_DEV void env_bsdf_sample_path(const HIPRTRenderData& rd, int2 res, const Tile& tile, const WavefrontState& wf, int bounce, uint32_t i)
 {
     const uint32_t slot = wf.sorted_queue[i];
-    if (wf.nee_ray_o[nee_index(wf, NEE_ENV_BSDF, slot)].w != -1.0f)
+    if (wf.nee_ray_o[nee_at(wf, nee_index(wf, NEE_ENV_BSDF, slot))].w != -1.0f)
         return;
     uint32_t x, y, pixel_index;
     wf_slot_to_pixel(wf, tile, res, slot, x, y, pixel_index);
@@ -275,7 +275,7 @@ PT_DEV void nee_pair_path(const HIPRTRenderData& rd, int2 res, const Tile& tile,
     PathRegs p;
     nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
     nee_light_eval_body(rd, wf, bounce, slot, p);
-    if (wf.nee_ray_o[nee_index(wf, NEE_LIGHT_BSDF, slot)].w == -1.0f)
+    if (wf.nee_ray_o[nee_at(wf, nee_index(wf, NEE_LIGHT_BSDF, slot))].w == -1.0f)
         nee_bsdf_sample_body<GGX_SAMPLER>(rd, wf, bounce, slot, p);
 }
 
@@ -288,7 +288,7 @@ PT_DEV void env_pair_path(const HIPRTRenderData& rd, int2 res, const Tile& tile,
     PathRegs p;
     nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
     env_light_eval_body<ESS>(rd, wf, bounce, slot, p);
-    if (wf.nee_ray_o[nee_index(wf, NEE_ENV_BSDF, slot)].w == -1.0f)
+    if (wf.nee_ray_o[nee_at(wf, nee_index(wf, NEE_ENV_BSDF, slot))].w == -1.0f)
         env_bsdf_sample_body<GGX_SAMPLER>(rd, wf, bounce, slot, p);
 }
 
@@ -313,7 +313,7 @@ PT_DEV void ris_candidates_path(const HIPRTRenderData& rd, int2 res, const Tile&
     nee_load_vertex(rd, wf, slot, pixel_index, bounce, p);
     nee_store_none(wf, NEE_LIGHT, slot);
     const size_t kb = nee_index(wf, NEE_LIGHT_BSDF, slot);
-    wf.nee_ray_o[kb] = make_float4(0.0f, 0.0f, 0.0f, -2.0f);          // -2: RIS does not run at this vertex (R2 and the resolve skip it)
+    wf.nee_ray_o[nee_at(wf, kb)] = make_float4(0.0f, 0.0f, 0.0f, -2.0f);          // -2: RIS does not run at this vertex (R2 and the resolve skip it)
     if (lights_prelude(rd, p.payload.material, bounce) != LIGHTS_SAMPLE)
         return;
 
@@ -331,10 +331,10 @@ PT_DEV void ris_candidates_path(const HIPRTRenderData& rd, int2 res, const Tile&
     nee_store_rng(wf, slot, p.rng);
     wf.ris_a[slot] = make_float4(reservoir.weight_sum, reservoir.sample.target_function, __uint_as_float(reservoir.M), __int_as_float(reservoir.sample.emissive_triangle_index));
     wf.ris_b[slot] = make_float4(reservoir.sample.point_on_light_source.x, reservoir.sample.point_on_light_source.y, reservoir.sample.point_on_light_source.z, 0.0f);
-    wf.nee_ray_o[kb].w = -1.0f;                                       // R2 runs; no candidate ray unless the sample has a pdf
+    wf.nee_ray_o[nee_at(wf, kb)].w = -1.0f;                                       // R2 runs; no candidate ray unless the sample has a pdf
     // the candidate's direction and colour travel in its ray record even when no ray is traced (pdf <= 0): R2 rebuilds the candidate from it
-    wf.nee_ray_d[kb] = make_float4(c.direction.x, c.direction.y, c.direction.z, __int_as_float(hit.primitive_index));
-    wf.nee_pending[kb] = make_float4(c.color.r, c.color.g, c.color.b, c.pdf);
+    wf.nee_ray_d[nee_at(wf, kb)] = make_float4(c.direction.x, c.direction.y, c.direction.z, __int_as_float(hit.primitive_index));
+    wf.nee_pending[nee_at(wf, kb)] = make_float4(c.color.r, c.color.g, c.color.b, c.pdf);
     if (c.pdf > 0.0f)
         nee_store(wf, bounce, NEE_LIGHT_BSDF, slot, c.origin, 1.0e35f, c.direction, hit.primitive_index, c.color, c.pdf);
 }
@@ -343,7 +343,7 @@ PT_DEV void ris_select_path(const HIPRTRenderData& rd, int2 res, const Tile& til
 {
     const uint32_t slot = wf.sorted_queue[i];
     const size_t kb = nee_index(wf, NEE_LIGHT_BSDF, slot);
-    const float4 o = wf.nee_ray_o[kb];
+    const float4 o = wf.nee_ray_o[nee_at(wf, kb)];
     if (o.w == -2.0f)
         return;
     uint32_t x, y, pixel_index;
@@ -366,7 +366,7 @@ PT_DEV void ris_select_path(const HIPRTRenderData& rd, int2 res, const Tile& til
     reservoir.sample.point_on_light_source = f3(b.x, b.y, b.z);
     reservoir.sample.is_bsdf_sample = false;
 
-    const float4 d = wf.nee_ray_d[kb], pc = wf.nee_pending[kb];
+    const float4 d = wf.nee_ray_d[nee_at(wf, kb)], pc = wf.nee_pending[nee_at(wf, kb)];
     RISBsdfCandidate c;
     c.direction = f3(d.x, d.y, d.z);
     c.color = RGB(pc.x, pc.y, pc.z);
@@ -378,11 +378,11 @@ PT_DEV void ris_select_path(const HIPRTRenderData& rd, int2 res, const Tile& til
     RISSample bsdf_RIS_sample;
     if (c.pdf > 0.0f)
     {
-        const float4 h = wf.hit_tuvp[kb];
+        const float4 h = wf.hit_tuvp[hitrec_at(wf, kb)];
         Hit light_ray_hit;
         light_ray_hit.t = h.x; light_ray_hit.u = h.y; light_ray_hit.v = h.z;
         light_ray_hit.prim = __float_as_int(h.w);
-        light_ray_hit.tri_slot = (int)wf.hit_tri_slot[kb];
+        light_ray_hit.tri_slot = (int)wf.hit_tri_slot[hitrec_word_at(wf, kb)];
         ShadowLightRayHitInfo light_hit;
         bool hit_found = shadow_light_ray_resolve(rd, 1.0e35f, light_hit, light_ray_hit);
         ris_bsdf_candidate_finish(rd, hit, c, hit_found, light_hit, nb_light_candidates, nb_bsdf_candidates, bsdf_RIS_sample, candidate_weight);
@@ -406,7 +406,7 @@ PT_DEV void ris_select_path(const HIPRTRenderData& rd, int2 res, const Tile& til
 // second half of evaluate_reservoir_sample (RIS.h:50-80), from the traced shadow ray
 PT_DEV RGB ris_resolve_light(const HIPRTRenderData& rd, const WavefrontState& wf, uint32_t slot, PathRegs& p)
 {
-    if (wf.nee_ray_o[nee_index(wf, NEE_LIGHT_BSDF, slot)].w == -2.0f)
+    if (wf.nee_ray_o[nee_at(wf, nee_index(wf, NEE_LIGHT_BSDF, slot))].w == -2.0f)
         return RGB(0.0f);
     const float4 a = wf.ris_a[slot];
     const float UCW = a.x;
@@ -417,7 +417,7 @@ PT_DEV RGB ris_resolve_light(const HIPRTRenderData& rd, const WavefrontState& wf
     bool in_shadow = false;
     const size_t k = nee_index(wf, NEE_LIGHT, slot);
     if (!is_bsdf_sample)
-        in_shadow = !(wf.nee_ray_o[k].w > 0.0f);          // the any-hit kernel set t_max = -1 on occluded rays
+        in_shadow = !(wf.nee_ray_o[nee_at(wf, k)].w > 0.0f);          // the any-hit kernel set t_max = -1 on occluded rays
     if (!in_shadow)
     {
         float bsdf_pdf;
@@ -432,7 +432,7 @@ PT_DEV RGB ris_resolve_light(const HIPRTRenderData& rd, const WavefrontState& wf
         }
         else
         {
-            const float4 d = wf.nee_ray_d[k];
+            const float4 d = wf.nee_ray_d[nee_at(wf, k)];
             const float3 dir = f3(d.x, d.y, d.z);
             bsdf_color = bsdf_eval(rd, p.payload.material, trash, -p.direction, p.hit.shading_normal, dir, bsdf_pdf);
             cosine_at_evaluated_point = maxf(0.0f, dot(p.hit.shading_normal, dir));
@@ -452,9 +452,9 @@ PT_DEV RGB ris_resolve_light(const HIPRTRenderData& rd, const WavefrontState& wf
 PT_DEV RGB nee_unoccluded_contribution(const WavefrontState& wf, int which, uint32_t slot)
 {
     const size_t k = nee_index(wf, which, slot);
-    if (!(wf.nee_ray_o[k].w > 0.0f))
+    if (!(wf.nee_ray_o[nee_at(wf, k)].w > 0.0f))
         return RGB(0.0f);
-    const float4 c = wf.nee_pending[k];
+    const float4 c = wf.nee_pending[nee_at(wf, k)];
     return RGB(c.x, c.y, c.z);
 }
 
@@ -477,22 +477,22 @@ PT_DEV void nee_resolve(const HIPRTRenderData& rd, const WavefrontState& wf, uin
         RGB light_source_radiance_mis = nee_unoccluded_contribution(wf, NEE_LIGHT, slot);
         RGB bsdf_radiance_mis;
         const size_t k = nee_index(wf, NEE_LIGHT_BSDF, slot);
-        const float4 o = wf.nee_ray_o[k];
+        const float4 o = wf.nee_ray_o[nee_at(wf, k)];
         bool sampled = o.w != -2.0f;
         if (o.w > 0.0f)
         {
-            const float4 d = wf.nee_ray_d[k];
+            const float4 d = wf.nee_ray_d[nee_at(wf, k)];
             const float3 sampled_bsdf_direction = f3(d.x, d.y, d.z);
-            const float4 h = wf.hit_tuvp[k];
+            const float4 h = wf.hit_tuvp[hitrec_at(wf, k)];
             Hit light_ray_hit;
             light_ray_hit.t = h.x; light_ray_hit.u = h.y; light_ray_hit.v = h.z;
             light_ray_hit.prim = __float_as_int(h.w);
-            light_ray_hit.tri_slot = (int)wf.hit_tri_slot[k];
+            light_ray_hit.tri_slot = (int)wf.hit_tri_slot[hitrec_word_at(wf, k)];
             ShadowLightRayHitInfo light_hit;
             bool inter_found = shadow_light_ray_resolve(rd, 1.0e35f, light_hit, light_ray_hit);
             if (inter_found && !light_hit.hit_emission.is_black())
             {
-                const float4 c = wf.nee_pending[k];
+                const float4 c = wf.nee_pending[nee_at(wf, k)];
                 const RGB bsdf_color_cosine(c.x, c.y, c.z);      // bsdf_color * cosine_term, the expression's first product
                 const float direction_pdf = c.w;
                 float light_pdf = pdf_of_emissive_triangle_hit(rd, light_hit, sampled_bsdf_direction);
