@@ -307,11 +307,13 @@ static int ensure_wavefront(b200pt_ctx* ctx, int lane, uint32_t paths, uint32_t 
     pt::WavefrontState& wf = ctx->wf[lane];
     std::vector<void*>& allocations = ctx->wf_allocations[lane];
     // The seven per-path float4 records in three groups (launch.h: WavefrontState::stride_*): one array of 32- / 64- / 32-byte records per group by
-    // default, seven separate arrays with B200PT_PATH_RECORDS=0 (round 1's layout, kept for A/B; results do not depend on it). Read at every call
-    // so that a test can switch within one process: a change of layout reallocates.
+    // default (B200PT_PATH_RECORDS unset or 1); 0: seven separate arrays (round 1's layout); 2: the NEE records (64 B) and the ray-queue
+    // kernel's hit records (32 B) grouped as well -- measured neutral on C3 and -2 % on C5 (gpurun calls 39 / 41), so not the default. Results do
+    // not depend on the layout. Read at every call so that a test can switch within one process: a change of layout reallocates.
     const char* records_env = getenv("B200PT_PATH_RECORDS");
     const bool grouped = !(records_env && records_env[0] == '0');
-    if (paths <= wf.capacity && bounces <= wf.max_bounces && wf.stride_ray == (grouped ? 2u : 1u))
+    const bool grouped_rays = records_env && records_env[0] == '2';
+    if (paths <= wf.capacity && bounces <= wf.max_bounces && wf.stride_ray == (grouped ? 2u : 1u) && wf.stride_nee == (grouped_rays ? 4u : 1u))
         return B200PT_SUCCESS;
     CUDA_TRY(cudaSetDevice(ctx->device));
     CUDA_TRY(cudaDeviceSynchronize());
@@ -348,7 +350,7 @@ static int ensure_wavefront(b200pt_ctx* ctx, int lane, uint32_t paths, uint32_t 
     float4** f4[] = {&wf.final_color, &wf.aov_normal, &wf.aov_albedo, &wf.ris_a, &wf.ris_b};
     for (float4** a : f4)
         ok &= (*a = static_cast<float4*>(alloc(n * sizeof(float4)))) != nullptr;
-    if (grouped)
+    if (grouped_rays)
     {
         // 64-byte NEE records: origin | t_max, pending contribution, direction | primitive, spare
         float4* base = static_cast<float4*>(alloc(4 * n * 4 * sizeof(float4)));
@@ -373,7 +375,7 @@ static int ensure_wavefront(b200pt_ctx* ctx, int lane, uint32_t paths, uint32_t 
     ok &= (wf.bucket_count = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * pt::kSortBuckets))) != nullptr;
     if (ok)
         ok &= cudaMemset(wf.bucket_count, 0, sizeof(uint32_t) * pt::kSortBuckets) == cudaSuccess;
-    if (grouped)
+    if (grouped_rays)
     {
         // 32-byte hit records: t, u, v, primitive | triangle slot, 3 spare words
         float4* base = static_cast<float4*>(alloc(2 * n * 2 * sizeof(float4)));
@@ -411,9 +413,9 @@ static int ensure_wavefront(b200pt_ctx* ctx, int lane, uint32_t paths, uint32_t 
     wf.stride_ray = grouped ? 2u : 1u;
     wf.stride_hit = grouped ? 4u : 1u;
     wf.stride_radiance = grouped ? 2u : 1u;
-    wf.stride_nee = grouped ? 4u : 1u;
-    wf.stride_hitrec = grouped ? 2u : 1u;
-    wf.stride_hitrec_words = grouped ? 8u : 1u;
+    wf.stride_nee = grouped_rays ? 4u : 1u;
+    wf.stride_hitrec = grouped_rays ? 2u : 1u;
+    wf.stride_hitrec_words = grouped_rays ? 8u : 1u;
     return B200PT_SUCCESS;
 }
 

@@ -893,7 +893,7 @@ def test_shading_records_are_bit_identical(pt, wl, ctx, workload, monkeypatch):
 @pytest.mark.parametrize("workload", ["cornell", "synthetic_small", "many_lights", "cornell_ris"])
 def test_path_record_layouts_are_bit_identical(pt, wl, ctx, workload, monkeypatch):
     """WavefrontState::stride_*: the seven per-path float4 records grouped into ray / hit / radiance records of 32 / 64 / 32 bytes (default) against seven separate
-    arrays (B200PT_PATH_RECORDS=0, round 1's layout). Only addresses change: every path shape (phased with sample batches, split, fused) and the
+    arrays (B200PT_PATH_RECORDS=0, round 1's layout) and against the layout that also groups the NEE and hit records (=2). Only addresses change: every path shape (phased with sample batches, split, fused) and the
     ray-queue kernel's strided view of origin / direction give the same bits."""
     W, H, frames = 160, 96, 3
     def make():
@@ -908,7 +908,7 @@ def test_path_record_layouts_are_bit_identical(pt, wl, ctx, workload, monkeypatc
         return wl.many_lights(W, H, boxes=150, lights=3000)
     outputs = {}
     try:
-        for layout in ("1", "0", "1"):
+        for layout in ("1", "0", "2", "1"):
             monkeypatch.setenv("B200PT_PATH_RECORDS", layout)
             for mode in ("phased", "split", "fused") if workload != "many_lights" else ("phased",):
                 ctx.set_path_mode(mode)
@@ -931,9 +931,9 @@ def test_path_record_layouts_are_bit_identical(pt, wl, ctx, workload, monkeypatc
         ctx.set_path_mode("phased")
         monkeypatch.delenv("B200PT_PATH_RECORDS", raising=False)
     for (layout, mode), out in outputs.items():
-        if layout == "0":
+        if layout != "1":
             for n, v in out.items():
-                assert np.array_equal(v, outputs[("1", mode)][n], equal_nan=(v.dtype.kind == "f")), (workload, mode, n)
+                assert np.array_equal(v, outputs[("1", mode)][n], equal_nan=(v.dtype.kind == "f")), (workload, mode, n, layout)
     assert outputs[("1", "phased")]["pixels"].any()
 
 
