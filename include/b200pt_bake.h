@@ -75,7 +75,7 @@ typedef struct b200pt_bake_options
 {
     int ggx_sample_function B200PT_DEFAULT(0);   /* PrincipledBSDFAnisotropicGGXSampleFunction (KernelOptions.h:155): 0 = GGX_VNDF_SAMPLING, 1 = GGX_VNDF_SPHERICAL_CAPS */
     int GGX_masking_shadowing B200PT_DEFAULT(0); /* BRDFsData::GGX_masking_shadowing of the default-constructed HIPRTRenderData the kernels evaluate with (BSDFsData.h:62) */
-    int chunks B200PT_DEFAULT(0);                /* threads per texel: 1 = the reference's summation order exactly, 2..32 = launches split in order, 0 = chosen from the table size */
+    int chunks B200PT_DEFAULT(0);                /* threads per texel: 1 = the reference's summation order exactly, 2..16 = a texel's launches split in order over that many threads, 0 = chosen from the table size */
 } b200pt_bake_options;
 
 /* The launch plan GPUBakerKernel::bake_internal derives from a table's resolution (GPUBakerKernel.cpp:82-83) and the sample count the KERNEL
