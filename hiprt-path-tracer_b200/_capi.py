@@ -101,4 +101,5 @@ HOST_API_SYMBOLS = [
     "b200pt_renderer_render_data", "b200pt_renderer_bvh", "b200pt_renderer_render_frame", "b200pt_renderer_synchronize",
     "b200pt_renderer_last_frame_ms", "b200pt_renderer_last_kernel_ms", "b200pt_renderer_download", "b200pt_renderer_device_pointer",
     "b200pt_baker_create", "b200pt_baker_destroy", "b200pt_baker_set_options", "b200pt_baker_bake", "b200pt_baker_is_complete", "b200pt_baker_wait", "b200pt_baker_last_table",
+    "b200pt_host_write_hdr_1channel",
 ]

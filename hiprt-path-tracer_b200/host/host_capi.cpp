@@ -337,4 +337,19 @@ long long b200pt_baker_last_table(b200pt_baker* b, int kind, float* out, long lo
     return (long long)t.size();
 }
 
+int b200pt_host_write_hdr_1channel(const char* filename, const float* texels, int width, int height)
+{
+    if (!filename || !texels || width <= 0 || height <= 0)
+    {
+        g_host_error = "invalid argument";
+        return B200PT_ERROR_INVALID_ARGUMENT;
+    }
+    if (!write_image_hdr_1channel(filename, texels, width, height))
+    {
+        g_host_error = std::string("cannot write ") + filename;
+        return B200PT_ERROR_INVALID_ARGUMENT;
+    }
+    return B200PT_SUCCESS;
+}
+
 } // extern "C"

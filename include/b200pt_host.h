@@ -87,6 +87,9 @@ B200PT_API int b200pt_baker_is_complete(b200pt_baker* baker, int table);       /
 B200PT_API int b200pt_baker_wait(b200pt_baker* baker);                         /* every bake finished; B200PT_ERROR_CUDA + message if one of them failed */
 /* The last finished table of that kind: floats copied (or the required count negated); out_kernel_ms may be NULL. */
 B200PT_API long long b200pt_baker_last_table(b200pt_baker* baker, int kind, float* out, long long capacity_floats, float* out_kernel_ms);
+/* The file writer the baker uses for a table slice (Image32Bit::write_image_hdr of a 1-channel image, src/Image/Image.cpp:440-452): Radiance RGBE,
+ * grey replicated, rows top to bottom, non-finite texels written as 0. Host only. */
+B200PT_API int b200pt_host_write_hdr_1channel(const char* filename, const float* texels, int width, int height);
 
 #ifdef __cplusplus
 }

@@ -78,6 +78,45 @@ def test_oracle_bake_reproduces_golden_and_the_shipped_conductor_table(golden, p
     assert d.max() < 5e-3 and d.mean() < 2.5e-3, (d.max(), d.mean())
 
 
+def test_host_hdr_writer_is_read_back_by_the_reference_loader(pt, tmp_path):
+    """The C++ host layer's slice writer (GPUBaker.cpp: write_image_hdr_1channel) on a table-like array with the awkward values in it: what it
+    writes decodes -- with the reference's own loader (Image32Bit::read_image_hdr over stb_image) where the oracle is built, and with a plain
+    RGBE decoder -- to the input within the 8-bit mantissa (1 / 256 relative, rounded down); zeros, denormal-small and non-finite texels give 0."""
+    host = pt.host()
+    rng = np.random.default_rng(3)
+    table = (rng.random((24, 40)) ** 3).astype(np.float32)
+    table[0, :6] = [0.0, 1.0, 1.0e-35, np.nan, np.inf, 0.999999]
+    table[1, 0] = 7.5
+    path = str(tmp_path / "slice.hdr")
+    pt._capi.check_host(host.b200pt_host_write_hdr_1channel(path.encode(), table.ctypes.data_as(C.c_void_p), 40, 24), "b200pt_host_write_hdr_1channel")
+    assert host.b200pt_host_write_hdr_1channel(str(tmp_path / "missing" / "x.hdr").encode(), table.ctypes.data_as(C.c_void_p), 40, 24) == -1
+    want = np.where(np.isfinite(table) & (table >= 1.0e-32), table, 0.0).astype(np.float32)
+    data = open(path, "rb").read()
+    head, _, rest = data.partition(b"\n\n")
+    assert head.startswith(b"#?RADIANCE") and b"FORMAT=32-bit_rle_rgbe" in head and rest.startswith(b"-Y 24 +X 40\n")
+    decoded = [_read_flat_hdr_file(path)]
+    from oracle import ref
+    if ref.available("mis"):
+        lib = ref.load("mis")
+        got = np.empty((24, 40), np.float32)
+        w, h = C.c_int(), C.c_int()
+        assert lib.ref_load_hdr(path.encode(), 1, 0, got.ctypes.data_as(C.c_void_p), got.size, C.byref(w), C.byref(h)) == 0 and (w.value, h.value) == (40, 24)
+        decoded.append(got)
+    for got in decoded:
+        assert got.shape == want.shape
+        assert np.all(got <= want * (1.0 + 1e-6)) and np.all(want - got <= want / 128.0), float(np.abs(got - want).max())
+        assert got[0, 0] == 0.0 and got[0, 2] == 0.0 and got[0, 3] == 0.0 and got[0, 4] == 0.0 and got[0, 1] == 1.0
+
+
+def _read_flat_hdr_file(path):
+    io = __import__("importlib").import_module("hiprt-path-tracer_b200.image_io")
+    data = open(path, "rb").read()
+    _, _, rest = data.partition(b"\n\n")
+    dims, _, body = rest.partition(b"\n")
+    _, h, _, w = dims.split()
+    return io.rgbe_to_float(np.frombuffer(body, np.uint8).reshape(int(h), int(w), 4))[..., 0]
+
+
 # ---- GPU ------------------------------------------------------------------------------------------------------------------------------------
 def _compare(got, want, what, max_abs=1e-3, mean_abs=1e-5, nan_mismatch=0.0):
     """Texels finite on both sides to the tolerance; the thin-glass kernel of the reference ITSELF yields NaN texels (ior -> 1: the generalised
