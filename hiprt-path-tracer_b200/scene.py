@@ -179,10 +179,11 @@ def read_image_8bit(path, output_channels):
     """Image8Bit::read_image(path, output_channels, flipY = false) (src/Image/Image.cpp:33-61): rows top to bottom, 8 bits per channel."""
     from PIL import Image
     with Image.open(path) as im:
-        if im.mode in ("1", "I", "I;16", "I;16B", "I;16L", "F"):
+        if im.mode == "1":
+            texels = np.asarray(im.convert("L"))
+        elif im.mode in ("I", "I;16", "I;16B", "I;16L", "F"):
             # 16-bit files: stb_image keeps the high byte
-            arr = np.asarray(im.convert("I"), np.int64)
-            texels = (np.clip(arr, 0, 65535) >> 8).astype(np.uint8) if im.mode != "1" else (np.asarray(im.convert("L")))
+            texels = (np.clip(np.asarray(im.convert("I"), np.int64), 0, 65535) >> 8).astype(np.uint8)
         elif im.mode == "P":
             texels = np.asarray(im.convert("RGBA" if "transparency" in im.info else "RGB"))
         elif im.mode in ("L", "LA", "RGB", "RGBA"):
